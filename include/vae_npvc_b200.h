@@ -1,0 +1,199 @@
+/*
+ * vae_npvc_b200 - C ABI of the B200-native VQ-VAE hot path (sm_100a).
+ *
+ * The reference (Sinica-SLAM/vae_npvc) is pure Python/PyTorch and has NO native boundary;
+ * this header is the thin layer the Python mirror classes (vae_npvc_b200/model/*.py,
+ * vae_npvc_b200/trainer/basic.py) bind with ctypes.  Each entry point names the reference
+ * torch-op sequence it replaces (paths relative to the reference repo root).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless named host_*; nothing is allocated or kept
+ *     by the library; every kernel is launched on `stream` (a cudaStream_t passed as void*)
+ *   - return value: 0 on success, negative VNB_E_* otherwise; vnb_last_error() gives the
+ *     thread-local message.  There is no CPU fallback anywhere.
+ *   - activations are float32, contiguous (B, C, T) ("NCT", the reference's layout)
+ *   - GEMM operands are bf16 "planes": (P, B, C, Tp) for activations, Tp = row pitch
+ *     (multiple of 8, >= T);  P = 1: bf16 operands (fast path);  P = 3: hi/mid/lo split of
+ *     the fp32 value, contracted with 6 plane-pair products = fp32-faithful on tensor cores
+ *   - conv weights as GEMM operands: (P, taps, Cout, Cin_p) bf16, Cin_p = Cin rounded up to 8
+ *   - indices are int64, like torch.argmin
+ */
+#ifndef VAE_NPVC_B200_H
+#define VAE_NPVC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VNB_OK 0
+#define VNB_E_ARG (-1)      /* bad argument / unsupported shape */
+#define VNB_E_CUDA (-2)     /* a CUDA runtime/driver call or launch failed */
+#define VNB_E_NODEV (-3)    /* no sm_100 device / driver entry point missing */
+
+#define VNB_BACKEND_AUTO 0
+#define VNB_BACKEND_SIMT 1  /* fp32 CUDA-core GEMM: debug / cross-check backend */
+#define VNB_BACKEND_TC 2    /* tcgen05 + TMEM + TMA GEMM */
+
+#define VNB_ACT_NONE 0
+#define VNB_ACT_LRELU 1     /* LeakyReLU(0.2) */
+#define VNB_ACT_RELU 2
+
+const char* vnb_last_error(void);
+int vnb_version(void);
+/* number of kernels launched by this library since the last reset (bench "gpu_launches") */
+int64_t vnb_launch_count(void);
+void vnb_launch_count_reset(void);
+/* 0 = auto (TC where the shape allows), 1 = SIMT everywhere, 2 = TC (error if impossible) */
+void vnb_set_backend(int backend);
+int vnb_get_backend(void);
+
+/* ---- weight-norm materialisation: nn.utils.weight_norm pre-hook, vqvae.py:203-208,329-334
+ * v: (d0,d1,k) fp32, g: (d0) fp32 or NULL (plain weight).  transposed=0: Conv1d (co=d0,ci=d1);
+ * transposed=1: ConvTranspose1d stride 1 (ci=d0, co=d1, conv tap = k-1-j).
+ * Optional outputs (NULL to skip): wf (P,k,co,ci_p) forward operand; wb (P,k,ci,co_p) data-grad
+ * operand (taps flipped); w32 (d0,d1,k) fp32 effective weight. */
+int vnb_wn_prepare(const float* v, const float* g, int d0, int d1, int k, int transposed, int P,
+                   void* wf, void* wb, float* w32, void* stream);
+/* backward of the same: dw (d0,d1,k) -> dv (d0,d1,k), dg (d0).   */
+int vnb_wn_backward(const float* dw, const float* v, const float* g, int d0, int d1, int k,
+                    float* dv, float* dg, void* stream);
+
+/* ---- stride-1 'same' conv as GEMM: nn.Conv1d / nn.ConvTranspose1d call sites layers.py:152,165,
+ * 229,231,244; vqvae.py:155,174,256,283,285.  Also the data-gradient (pass the wb operand).
+ * out[b,co,t] = beta*out + bias[b*bias_bstride+co] + residual[b,co,t]
+ *             + sum_{tap,ci} W[tap][co][ci] * in[b,ci,t+(tap-(taps-1)/2)*dil]   (zero padded) */
+int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T, int Tp,
+                 const void* w_planes, int taps, int dil, int Cout,
+                 const float* bias, int bias_bstride, const float* residual,
+                 float* out, int accumulate, void* stream);
+/* weight gradient in the reference parameter layout (d0,d1,k):
+ * conv tap j: dW[co][ci][j] = sum_{b,t} dy[b,co,t] * u[b,ci,t+(j-(taps-1)/2)*dil];
+ * transposed=0 -> dw[co][ci][j];  transposed=1 -> dw[ci][co][taps-1-j] */
+int vnb_conv_wgrad(const void* dy_planes, const void* u_planes, int P, int B, int Cout, int Cin,
+                   int T, int Tp, int taps, int dil, int transposed, float* dw, void* stream);
+
+/* ---- operand planes from fp32 activations (B,C,T): out_id <- x*scale, out_act <- act(x*scale) */
+int vnb_make_planes(const float* x, int B, int C, int T, int Tp, int P, float scale, int act,
+                    void* out_id, void* out_act, void* stream);
+/* channel-concat [xa (B,Ca,T); xb (B,Cb,T)] -> planes (P,B,Ca+Cb,Tp) */
+int vnb_concat_planes(const float* xa, int Ca, const float* xb, int Cb, int B, int T, int Tp, int P,
+                      void* out, void* stream);
+
+/* ---- nn.GroupNorm statistics (layers.py:154,201): mean,rstd (B,groups), biased var, eps */
+int vnb_gn_stats(const float* h, int B, int C, int T, int groups, float eps, float* mean, float* rstd,
+                 void* stream);
+/* encoder residual block epilogue (layers.py:176): y = GN1(h)*gamma+beta (+ s); optional outputs:
+ * y fp32, planes of y, planes of LeakyReLU_0.2(y) */
+int vnb_enc_out(const float* h, const float* s, const float* mean, const float* rstd,
+                const float* gamma, const float* beta, int B, int C, int T, int Tp, int P,
+                float* y, void* y_planes, void* u_planes, void* stream);
+/* decoder gate (layers.py:236-242): hn = GN2(a); g = tanh(hn[:C])*sigmoid(hn[C:]) -> planes of g */
+int vnb_dec_gate(const float* a, const float* mean, const float* rstd, const float* gamma,
+                 const float* beta, int B, int C, int T, int Tp, int P, void* g_planes, void* stream);
+/* decoder residual/skip split (layers.py:246-247, vqvae.py:313): r (B,C+S,T);
+ * x_out = r[:C]+x (fp32 + planes);  skip_sum (+)= r[C:]  (first=1 assigns) */
+int vnb_dec_out(const float* r, const float* x, int B, int C, int S, int T, int Tp, int P,
+                float* x_out, void* x_planes, float* skip_sum, int first, void* stream);
+
+/* ---- backward reductions.  rows: per (b,c) sums over t */
+/* R[b,c,0..2] = sum_t dn, sum_t dn*xhat, sum_t xhat   with xhat=(h-mean)*rstd (GroupNorm bwd) */
+int vnb_gn_bwd_rows(const float* dn, const float* h, const float* mean, const float* rstd,
+                    int B, int C, int T, int groups, float* R, void* stream);
+/* same for the gated decoder block: dn is recomputed from dg (B,C,T) through tanh*sigmoid;
+ * a (B,2C,T) pre-norm */
+int vnb_gate_bwd_rows(const float* dg, const float* a, const float* mean, const float* rstd,
+                      const float* gamma, const float* beta, int B, int C, int T, float* R, void* stream);
+/* from R: dgamma[c], dbeta[c], S[b,group,0..1] = sum_c gamma*R0, sum_c gamma*R1, and (optional)
+ * dpre_bsum[b,c] = sum_t dpre, dpre_csum[c] = sum_{b,t} dpre  (dpre = grad wrt the GN input) */
+int vnb_gn_bwd_finalize(const float* R, const float* gamma, const float* rstd, int B, int C, int T,
+                        int groups, float* dgamma, float* dbeta, float* S, float* dpre_bsum,
+                        float* dpre_csum, void* stream);
+/* dpre = rstd*(gamma*dn - S0/n - xhat*S1/n) -> planes (+ optional planes of dn itself) */
+int vnb_gn_bwd_apply(const float* dn, const float* h, const float* mean, const float* rstd,
+                     const float* gamma, const float* S, int B, int C, int T, int groups, int Tp, int P,
+                     void* dpre_planes, void* dn_planes, void* stream);
+int vnb_gate_bwd_apply(const float* dg, const float* a, const float* mean, const float* rstd,
+                       const float* gamma, const float* beta, const float* S, int B, int C, int T,
+                       int Tp, int P, void* da_planes, void* stream);
+/* out = add + scale * act'(c*scale) * du   (e.g. encoder block input gradient: dskip_path +
+ * lrelu'(c)*du) ; act as VNB_ACT_* ; add may be NULL */
+int vnb_act_bwd_add(const float* du, const float* c, const float* add, int64_t n, int act, float scale,
+                    float* out, void* stream);
+/* out[c] = sum_{b,t} x[b,c,t]  (bias gradients) */
+int vnb_channel_sum(const float* x, int B, int C, int T, float* out, void* stream);
+
+/* ---- speaker conditioning (layers.py:42-54 Conditions; layers.py:231 conv_cond on a
+ * time-invariant input, vqvae.py:309-312) */
+int vnb_embed_fwd(const float* table, const int64_t* idx, int n, int dim, float* out, void* stream);
+int vnb_embed_bwd(const float* dout, const int64_t* idx, int n, int dim, float* dtable, void* stream);
+/* p[b,o] = bias[o] + sum_i W[o,i]*y[b,i] */
+int vnb_linear_fwd(const float* y, const float* W, const float* bias, int B, int I, int O, float* p,
+                   void* stream);
+/* dW[o,i] = sum_b dp[b,o]*y[b,i];  dy[b,i] (+)= sum_o W[o,i]*dp[b,o] */
+int vnb_linear_bwd(const float* dp, const float* y, const float* W, int B, int I, int O, float* dW,
+                   float* dy, int accumulate_dy, void* stream);
+
+/* ---- vector quantiser (layers_vq.py:79-150 VectorQuantizer.forward, :268-323 EMA) */
+/* codebook: normalize!=0 -> E <- E/||E|| IN PLACE (embed_norm, :28-33) then e_hat = E/||E||;
+ * else e_hat = E.  e_planes (3,K,Dp) hi/mid/lo, e_sq[k] = sum e_hat^2 */
+int vnb_vq_prep_codebook(float* E, int K, int D, int normalize, int inplace_renorm, float* e_hat,
+                         void* e_planes, float* e_sq, void* stream);
+/* frames: zn = z/||z|| (or z); z_planes (3,B,D,Tp); z_sq[n], z_norm[n] with n = b*T+t */
+int vnb_vq_prep_z(const float* z, int B, int D, int T, int Tp, int normalize, float* zn,
+                  void* z_planes, float* z_sq, float* z_norm, void* stream);
+/* idx[n] = argmin_k ((z_sq[n] + e_sq[k]) - 2 zn[n].e_hat[k]), ties -> lowest k (:103-108) */
+int vnb_vq_lookup(const float* zn, const void* z_planes, const float* z_sq, const float* e_hat,
+                  const void* e_planes, const float* e_sq, int B, int D, int T, int Tp, int K,
+                  int64_t* idx, void* stream);
+/* q = e_hat[idx] -> q_out (B,D,T); sums[0] += sum (q-zn)^2, sums[1] += sum (zn-z)^2;
+ * counts[k] += #{idx==k}  (sums, counts must be zeroed by the caller) */
+int vnb_vq_gather(const int64_t* idx, const float* e_hat, const float* zn, const float* z, int B, int D,
+                  int T, int K, float* q_out, float* sums, int* counts, void* stream);
+/* scal[0]=l_q, scal[1]=l_e, scal[2]=perplexity(eps) from sums/counts; scale = 1/(B*T) etc. */
+int vnb_vq_finalize(const float* sums, const int* counts, int K, int64_t N, float scale, int normalize,
+                    float eps, float* scal, void* stream);
+/* backward.  g_out (B,D,T) or NULL; g_lq,g_le device scalars or NULL;
+ * scale as in finalize.  dz (B,D,T); dE (K,D) must be zeroed by the caller (atomic adds) */
+int vnb_vq_bwd(const float* g_out, const float* g_lq, const float* g_le, const int64_t* idx,
+               const float* z, const float* zn, const float* z_norm, const float* e_hat, const float* E,
+               int B, int D, int T, int K, float scale, int normalize, float* dz, float* dE_hat,
+               void* stream);
+/* dE = (I - e e^T) dE_hat / ||E||  (normalised codebook) ; else copy */
+int vnb_vq_bwd_codebook(const float* dE_hat, const float* E, int K, int D, int normalize, float* dE,
+                        void* stream);
+/* EMA update (layers_vq.py:203-233).  zsum (K,D) zeroed scratch; rand_rows (K,D) restart rows;
+ * stats[0..3] = entropy, used_curr, usage, diff_emb */
+int vnb_vq_ema_update(const int64_t* idx, const float* z, int B, int D, int T, int K, float mu,
+                      float threshold, const float* rand_rows, float* zsum, int* counts, float* emb_sum,
+                      float* emb_elem, float* embeddings, float* stats, void* stream);
+/* gather rows of the frame matrix: out[k,:] = z[:, :, .] at flat frame perm[k] % N (+ optional
+ * noise) - EMA init / restart candidates (:183-201,212-213) */
+int vnb_vq_frame_rows(const float* z, const int64_t* perm, int B, int D, int T, int K, float* out,
+                      void* stream);
+/* Jitter (layers_vq.py:353-379): out[:,:,t] = in[:,:,src[t]] */
+int vnb_jitter_fwd(const float* in, const int64_t* src, int B, int D, int T, float* out, void* stream);
+/* grad: zero where src[t] != t */
+int vnb_jitter_bwd(const float* dout, const int64_t* src, int B, int D, int T, float* din, void* stream);
+
+/* ---- log-loss (layers.py:283-296): acc[0] += sum 0.5*(log2pi + (xhat-x)^2) (zeroed by caller) */
+int vnb_logloss_fwd(const float* xhat, const float* x, int64_t n, float* acc, void* stream);
+/* dxhat = g * (xhat-x) * scale ; g device scalar (NULL = 1) */
+int vnb_logloss_bwd(const float* xhat, const float* x, const float* g, int64_t n, float scale,
+                    float* dxhat, void* stream);
+
+/* ---- optimiser (trainer/basic.py:62-72): global L2 norm -> clip coef -> Adam, on flat buffers */
+/* acc[0] += sum g^2 (zeroed by caller) */
+int vnb_sqnorm(const float* g, int64_t n, float* acc, void* stream);
+/* state[0] = step count (float), updated on device; lr_base*gamma^floor(step/step_size);
+ * clip: coef = min(1, max_norm/(sqrt(sqn[0])+1e-6)) when max_norm > 0 */
+int vnb_adam_step(float* p, const float* g, float* m, float* v, int64_t n, const float* sqn,
+                  float max_norm, float lr, float beta1, float beta2, float eps, float* state,
+                  int step_size, float gamma, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,105 @@
+// Shared helpers for the vae_npvc_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/vae_npvc_b200.h"
+
+namespace vnb {
+
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+int backend();
+
+#define VNB_REQUIRE(cond, ...)              \
+    do {                                    \
+        if (!(cond)) {                      \
+            vnb::set_error(__VA_ARGS__);    \
+            return VNB_E_ARG;               \
+        }                                   \
+    } while (0)
+
+// Check the launch itself (not completion - never synchronise inside the library).
+#define VNB_LAUNCH_CHECK(name)                                                      \
+    do {                                                                            \
+        cudaError_t e_ = cudaGetLastError();                                        \
+        if (e_ != cudaSuccess) {                                                    \
+            vnb::set_error("%s: launch failed: %s", name, cudaGetErrorString(e_));  \
+            return VNB_E_CUDA;                                                      \
+        }                                                                           \
+        vnb::count_launch();                                                        \
+    } while (0)
+
+static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+static inline int round_up8(int x) { return (x + 7) & ~7; }
+
+typedef __nv_bfloat16 bf16;
+
+// hi/mid/lo split of an fp32 value into bf16 planes: x == hi + mid + lo exactly (3 x 8
+// significant bits) unless the tail underflows.
+__device__ __forceinline__ void split3(float x, bf16& hi, bf16& mid, bf16& lo) {
+    hi = __float2bfloat16_rn(x);
+    float r = x - __bfloat162float(hi);
+    mid = __float2bfloat16_rn(r);
+    r = r - __bfloat162float(mid);
+    lo = __float2bfloat16_rn(r);
+}
+
+// Write value x at element offset `off` of plane 0 (and planes 1,2 at +stride each for P==3).
+__device__ __forceinline__ void store_planes(bf16* base, int64_t off, int64_t plane_stride, int P, float x) {
+    if (P == 1) {
+        base[off] = __float2bfloat16_rn(x);
+    } else {
+        bf16 a, b, c;
+        split3(x, a, b, c);
+        base[off] = a;
+        base[off + plane_stride] = b;
+        base[off + 2 * plane_stride] = c;
+    }
+}
+
+__device__ __forceinline__ float load_planes(const bf16* base, int64_t off, int64_t plane_stride, int P) {
+    float x = __bfloat162float(base[off]);
+    if (P == 3) {
+        x += __bfloat162float(base[off + plane_stride]);
+        x += __bfloat162float(base[off + 2 * plane_stride]);
+    }
+    return x;
+}
+
+__device__ __forceinline__ float lrelu02(float x) { return x >= 0.f ? x : 0.2f * x; }
+__device__ __forceinline__ float apply_act(float x, int act) {
+    if (act == VNB_ACT_LRELU) return lrelu02(x);
+    if (act == VNB_ACT_RELU) return x > 0.f ? x : 0.f;
+    return x;
+}
+__device__ __forceinline__ float act_grad(float x, int act) {
+    if (act == VNB_ACT_LRELU) return x >= 0.f ? 1.f : 0.2f;
+    if (act == VNB_ACT_RELU) return x > 0.f ? 1.f : 0.f;
+    return 1.f;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Block-wide sum; result valid in every thread.  `red` needs 32 floats of shared memory.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+    v = warp_sum(v);
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) red[w] = v;
+    __syncthreads();
+    int nw = (blockDim.x + 31) >> 5;
+    float r = (threadIdx.x < nw) ? red[threadIdx.x] : 0.f;
+    if (w == 0) r = warp_sum(r);
+    if (threadIdx.x == 0) red[0] = r;
+    __syncthreads();
+    return red[0];
+}
+
+}  // namespace vnb

@@ -1,0 +1,281 @@
+// CUDA-core (fp32 FFMA) GEMM backend: conv forward / data-gradient, weight-gradient and the VQ
+// distance+argmin.  It consumes exactly the same bf16 operand planes as the tcgen05 backend
+// (summing the P planes back to fp32 on load), so it is a drop-in cross-check for it and the
+// backend for shapes the tensor-core kernel does not take.  Not a CPU fallback: CUDA only.
+#include "common.cuh"
+
+namespace vnb {
+
+constexpr int TM = 64, TN = 64, KC = 16;
+
+// out[b,co,t] = beta*out + bias + residual + sum_{tap,ci} W[tap][co][ci] * in[b,ci,t+off(tap)]
+template <int P>
+__global__ void __launch_bounds__(256) conv_fwd_simt_kernel(
+    const bf16* __restrict__ in, int B, int Cin, int T, int Tp, const bf16* __restrict__ w, int taps, int dil,
+    int Cout, int Cin_p, const float* __restrict__ bias, int bias_bstride, const float* __restrict__ residual,
+    float* __restrict__ out, int accumulate) {
+    __shared__ float Ws[KC][TM + 4];
+    __shared__ float Xs[KC][TN + 4];
+    const int t0 = blockIdx.x * TN, co0 = blockIdx.y * TM, b = blockIdx.z;
+    const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+    const int64_t in_plane = (int64_t)B * Cin * Tp;
+    const int64_t w_plane = (int64_t)taps * Cout * Cin_p;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+
+    for (int tap = 0; tap < taps; tap++) {
+        const int off = (tap - (taps - 1) / 2) * dil;
+        for (int c0 = 0; c0 < Cin; c0 += KC) {
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const int idx = tid * 4 + e;
+                {   // W tile: 64 co x 16 ci, ci contiguous
+                    const int m = idx >> 4, kk = idx & 15;
+                    const int co = co0 + m, ci = c0 + kk;
+                    float x = 0.f;
+                    if (co < Cout && ci < Cin) x = load_planes(w, ((int64_t)tap * Cout + co) * Cin_p + ci, w_plane, P);
+                    Ws[kk][m] = x;
+                }
+                {   // X tile: 16 ci x 64 t, t contiguous, zero padded
+                    const int kk = idx >> 6, n = idx & 63;
+                    const int ci = c0 + kk, t = t0 + n + off;
+                    float x = 0.f;
+                    if (ci < Cin && t >= 0 && t < T) x = load_planes(in, ((int64_t)b * Cin + ci) * Tp + t, in_plane, P);
+                    Xs[kk][n] = x;
+                }
+            }
+            __syncthreads();
+#pragma unroll
+            for (int kk = 0; kk < KC; kk++) {
+                float a[4], x[4];
+#pragma unroll
+                for (int i = 0; i < 4; i++) a[i] = Ws[kk][ty * 4 + i];
+#pragma unroll
+                for (int j = 0; j < 4; j++) x[j] = Xs[kk][tx * 4 + j];
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int j = 0; j < 4; j++) acc[i][j] = fmaf(a[i], x[j], acc[i][j]);
+            }
+            __syncthreads();
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int co = co0 + ty * 4 + i;
+        if (co >= Cout) continue;
+        const float bv = bias ? bias[(int64_t)b * bias_bstride + co] : 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int t = t0 + tx * 4 + j;
+            if (t >= T) continue;
+            const int64_t o = ((int64_t)b * Cout + co) * T + t;
+            float r = acc[i][j] + bv;
+            if (residual) r += residual[o];
+            if (accumulate) r += out[o];
+            out[o] = r;
+        }
+    }
+}
+
+// dW[co][ci][tap] = sum_{b,t} dy[b,co,t] * u[b,ci,t+off(tap)]
+template <int P>
+__global__ void __launch_bounds__(256) conv_wgrad_simt_kernel(
+    const bf16* __restrict__ dy, const bf16* __restrict__ u, int B, int Cout, int Cin, int T, int Tp, int taps,
+    int dil, int transposed, float* __restrict__ dw) {
+    __shared__ float As[KC][TM + 4];
+    __shared__ float Bs[KC][TN + 4];
+    const int ci0 = blockIdx.x * TN, co0 = blockIdx.y * TM, tap = blockIdx.z;
+    const int off = (tap - (taps - 1) / 2) * dil;
+    const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+    const int64_t dy_plane = (int64_t)B * Cout * Tp, u_plane = (int64_t)B * Cin * Tp;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+    for (int b = 0; b < B; b++) {
+        for (int tt = 0; tt < T; tt += KC) {
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const int idx = tid * 4 + e;
+                const int m = idx >> 4, kk = idx & 15;
+                const int t = tt + kk;
+                {
+                    const int co = co0 + m;
+                    float x = 0.f;
+                    if (co < Cout && t < T) x = load_planes(dy, ((int64_t)b * Cout + co) * Tp + t, dy_plane, P);
+                    As[kk][m] = x;
+                }
+                {
+                    const int ci = ci0 + m, ts = t + off;
+                    float x = 0.f;
+                    if (ci < Cin && t < T && ts >= 0 && ts < T)
+                        x = load_planes(u, ((int64_t)b * Cin + ci) * Tp + ts, u_plane, P);
+                    Bs[kk][m] = x;
+                }
+            }
+            __syncthreads();
+#pragma unroll
+            for (int kk = 0; kk < KC; kk++) {
+                float a[4], x[4];
+#pragma unroll
+                for (int i = 0; i < 4; i++) a[i] = As[kk][ty * 4 + i];
+#pragma unroll
+                for (int j = 0; j < 4; j++) x[j] = Bs[kk][tx * 4 + j];
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int j = 0; j < 4; j++) acc[i][j] = fmaf(a[i], x[j], acc[i][j]);
+            }
+            __syncthreads();
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int co = co0 + ty * 4 + i;
+        if (co >= Cout) continue;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int ci = ci0 + tx * 4 + j;
+            if (ci >= Cin) continue;
+            const int64_t o = transposed ? (((int64_t)ci * Cout + co) * taps + (taps - 1 - tap))
+                                         : (((int64_t)co * Cin + ci) * taps + tap);
+            dw[o] = acc[i][j];
+        }
+    }
+}
+
+// VQ lookup: 16 frames per block, every thread scans codes tid, tid+256, ...
+constexpr int VQ_FR = 16;
+__global__ void __launch_bounds__(256) vq_lookup_simt_kernel(const float* __restrict__ zn, const float* __restrict__ z_sq,
+                                                             const float* __restrict__ e_hat,
+                                                             const float* __restrict__ e_sq, int B, int D, int T,
+                                                             int K, int64_t* __restrict__ idx) {
+    extern __shared__ float sm[];
+    float* zs = sm;                                   // [VQ_FR][D]
+    float* bd = sm + VQ_FR * D;                       // [VQ_FR][256] best distance
+    int* bi = (int*)(bd + VQ_FR * 256);               // [VQ_FR][256] best index
+    const int64_t N = (int64_t)B * T;
+    const int64_t n0 = (int64_t)blockIdx.x * VQ_FR;
+    const int tid = threadIdx.x;
+    for (int e = tid; e < VQ_FR * D; e += 256) {
+        const int f = e % VQ_FR, d = e / VQ_FR;
+        const int64_t n = n0 + f;
+        float x = 0.f;
+        if (n < N) {
+            const int64_t b = n / T, t = n - b * T;
+            x = zn[(b * D + d) * T + t];
+        }
+        zs[f * D + d] = x;
+    }
+    __syncthreads();
+    float best[VQ_FR];
+    int bestk[VQ_FR];
+    float zq[VQ_FR];
+#pragma unroll
+    for (int f = 0; f < VQ_FR; f++) {
+        best[f] = INFINITY;
+        bestk[f] = 0x7fffffff;
+        zq[f] = (n0 + f < N) ? z_sq[n0 + f] : 0.f;
+    }
+    for (int k = tid; k < K; k += 256) {
+        float dot[VQ_FR];
+#pragma unroll
+        for (int f = 0; f < VQ_FR; f++) dot[f] = 0.f;
+        const float* er = e_hat + (int64_t)k * D;
+        for (int d = 0; d < D; d++) {
+            const float ev = er[d];
+#pragma unroll
+            for (int f = 0; f < VQ_FR; f++) dot[f] = fmaf(zs[f * D + d], ev, dot[f]);
+        }
+        const float es = e_sq[k];
+#pragma unroll
+        for (int f = 0; f < VQ_FR; f++) {
+            const float dist = fmaf(-2.f, dot[f], zq[f] + es);
+            if (dist < best[f]) {
+                best[f] = dist;
+                bestk[f] = k;
+            }
+        }
+    }
+#pragma unroll
+    for (int f = 0; f < VQ_FR; f++) {
+        bd[f * 256 + tid] = best[f];
+        bi[f * 256 + tid] = bestk[f];
+    }
+    __syncthreads();
+    // one warp per 2 frames: reduce 256 candidates, lowest index wins ties
+    const int w = tid >> 5, lane = tid & 31;
+    for (int f = w; f < VQ_FR; f += 8) {
+        float d = INFINITY;
+        int k = 0x7fffffff;
+        for (int c = lane; c < 256; c += 32) {
+            const float dc = bd[f * 256 + c];
+            const int kc = bi[f * 256 + c];
+            if (dc < d || (dc == d && kc < k)) {
+                d = dc;
+                k = kc;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float d2 = __shfl_xor_sync(0xffffffffu, d, o);
+            const int k2 = __shfl_xor_sync(0xffffffffu, k, o);
+            if (d2 < d || (d2 == d && k2 < k)) {
+                d = d2;
+                k = k2;
+            }
+        }
+        if (lane == 0 && n0 + f < N) idx[n0 + f] = (int64_t)k;
+    }
+}
+
+int conv_fwd_simt(const void* in, int P, int B, int Cin, int T, int Tp, const void* w, int taps, int dil, int Cout,
+                  const float* bias, int bias_bstride, const float* residual, float* out, int accumulate,
+                  cudaStream_t st) {
+    dim3 grid(ceil_div(T, TN), ceil_div(Cout, TM), B);
+    const int Cin_p = round_up8(Cin);
+    if (P == 1)
+        conv_fwd_simt_kernel<1><<<grid, 256, 0, st>>>((const bf16*)in, B, Cin, T, Tp, (const bf16*)w, taps, dil, Cout,
+                                                      Cin_p, bias, bias_bstride, residual, out, accumulate);
+    else
+        conv_fwd_simt_kernel<3><<<grid, 256, 0, st>>>((const bf16*)in, B, Cin, T, Tp, (const bf16*)w, taps, dil, Cout,
+                                                      Cin_p, bias, bias_bstride, residual, out, accumulate);
+    VNB_LAUNCH_CHECK("conv_fwd_simt");
+    return VNB_OK;
+}
+
+int conv_wgrad_simt(const void* dy, const void* u, int P, int B, int Cout, int Cin, int T, int Tp, int taps, int dil,
+                    int transposed, float* dw, cudaStream_t st) {
+    dim3 grid(ceil_div(Cin, TN), ceil_div(Cout, TM), taps);
+    if (P == 1)
+        conv_wgrad_simt_kernel<1><<<grid, 256, 0, st>>>((const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, Tp, taps, dil,
+                                                        transposed, dw);
+    else
+        conv_wgrad_simt_kernel<3><<<grid, 256, 0, st>>>((const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, Tp, taps, dil,
+                                                        transposed, dw);
+    VNB_LAUNCH_CHECK("conv_wgrad_simt");
+    return VNB_OK;
+}
+
+int vq_lookup_simt(const float* zn, const float* z_sq, const float* e_hat, const float* e_sq, int B, int D, int T,
+                   int K, int64_t* idx, cudaStream_t st) {
+    const int64_t N = (int64_t)B * T;
+    const size_t smem = (size_t)VQ_FR * D * 4 + (size_t)VQ_FR * 256 * 8;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(vq_lookup_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) {
+            set_error("vq_lookup_simt: smem %zu: %s", smem, cudaGetErrorString(e));
+            return VNB_E_CUDA;
+        }
+    }
+    vq_lookup_simt_kernel<<<ceil_div(N, VQ_FR), 256, smem, st>>>(zn, z_sq, e_hat, e_sq, B, D, T, K, idx);
+    VNB_LAUNCH_CHECK("vq_lookup_simt");
+    return VNB_OK;
+}
+
+}  // namespace vnb

@@ -1,0 +1,199 @@
+// Speaker-embedding gather/scatter, the time-invariant conditioning linear, log-loss and the
+// flat-buffer optimiser (global-norm clip + Adam + StepLR).
+// Reference: vae_npvc/model/layers.py:42-54 (Conditions), :231 (conv_cond), :283-296 (log_loss);
+// vae_npvc/trainer/basic.py:38-46, 62-72 (clip_grad_norm_, Adam(betas=(0.5,0.999)), StepLR).
+#include "common.cuh"
+
+namespace vnb {
+
+__global__ void embed_fwd_kernel(const float* __restrict__ table, const int64_t* __restrict__ idx, int n, int dim,
+                                 float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * dim) return;
+    const int r = i / dim, d = i - r * dim;
+    out[i] = table[idx[r] * dim + d];
+}
+
+// deterministic scatter-add: thread per column, sequential over the (few) rows
+__global__ void embed_bwd_kernel(const float* __restrict__ dout, const int64_t* __restrict__ idx, int n, int dim,
+                                 float* __restrict__ dtable) {
+    const int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= dim) return;
+    for (int r = 0; r < n; r++) dtable[idx[r] * dim + d] += dout[r * dim + d];
+}
+
+// one warp per output (b,o)
+__global__ void __launch_bounds__(256) linear_fwd_kernel(const float* __restrict__ y, const float* __restrict__ W,
+                                                         const float* __restrict__ bias, int B, int I, int O,
+                                                         float* __restrict__ p) {
+    const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (w >= (int64_t)B * O) return;
+    const int lane = threadIdx.x & 31;
+    const int b = (int)(w / O), o = (int)(w - (int64_t)b * O);
+    float s = 0.f;
+    for (int i = lane; i < I; i += 32) s = fmaf(W[(int64_t)o * I + i], y[(int64_t)b * I + i], s);
+    s = warp_sum(s);
+    if (lane == 0) p[w] = s + (bias ? bias[o] : 0.f);
+}
+
+__global__ void linear_bwd_w_kernel(const float* __restrict__ dp, const float* __restrict__ y, int B, int I, int O,
+                                    float* __restrict__ dW) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (int64_t)O * I) return;
+    const int o = (int)(e / I), i = (int)(e - (int64_t)o * I);
+    float s = 0.f;
+    for (int b = 0; b < B; b++) s = fmaf(dp[(int64_t)b * O + o], y[(int64_t)b * I + i], s);
+    dW[e] = s;
+}
+
+__global__ void linear_bwd_y_kernel(const float* __restrict__ dp, const float* __restrict__ W, int B, int I, int O,
+                                    float* __restrict__ dy, int accumulate) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (int64_t)B * I) return;
+    const int b = (int)(e / I), i = (int)(e - (int64_t)b * I);
+    float s = 0.f;
+    for (int o = 0; o < O; o++) s = fmaf(W[(int64_t)o * I + i], dp[(int64_t)b * O + o], s);
+    dy[e] = accumulate ? dy[e] + s : s;
+}
+
+constexpr float LOG_2PI_F = 1.8378770664093453f;
+
+__global__ void __launch_bounds__(256) logloss_fwd_kernel(const float* __restrict__ xhat, const float* __restrict__ x,
+                                                          int64_t n, float* __restrict__ acc) {
+    __shared__ float red[32];
+    float s = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float d = xhat[i] - x[i];
+        s += 0.5f * (LOG_2PI_F + d * d);
+    }
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) atomicAdd(acc, s);
+}
+
+__global__ void logloss_bwd_kernel(const float* __restrict__ xhat, const float* __restrict__ x,
+                                   const float* __restrict__ g, int64_t n, float scale, float* __restrict__ dxhat) {
+    const float gs = (g ? g[0] : 1.f) * scale;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        dxhat[i] = gs * (xhat[i] - x[i]);
+}
+
+__global__ void __launch_bounds__(256) sqnorm_kernel(const float* __restrict__ g, int64_t n, float* __restrict__ acc) {
+    __shared__ float red[32];
+    float s = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        s += g[i] * g[i];
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) atomicAdd(acc, s);
+}
+
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                   float* __restrict__ m, float* __restrict__ v, int64_t n,
+                                                   const float* __restrict__ sqn, float max_norm, float lr, float beta1,
+                                                   float beta2, float eps, const float* __restrict__ state,
+                                                   int step_size, float gamma) {
+    __shared__ float sh[3];
+    if (threadIdx.x == 0) {
+        const double s = (double)state[0];                       // optimiser steps already taken
+        const double t = s + 1.0;
+        double lr_t = (double)lr;
+        if (step_size > 0) lr_t *= pow((double)gamma, floor(s / (double)step_size));
+        const double bc1 = 1.0 - pow((double)beta1, t), bc2 = 1.0 - pow((double)beta2, t);
+        float coef = 1.f;
+        if (max_norm > 0.f && sqn) coef = fminf(1.f, max_norm / (sqrtf(sqn[0]) + 1e-6f));
+        sh[0] = (float)(lr_t / bc1);
+        sh[1] = (float)(1.0 / sqrt(bc2));
+        sh[2] = coef;
+    }
+    __syncthreads();
+    const float step = sh[0], rs2 = sh[1], coef = sh[2];
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float gi = g[i] * coef;
+        const float mi = beta1 * m[i] + (1.f - beta1) * gi;
+        const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+        m[i] = mi;
+        v[i] = vi;
+        p[i] -= step * mi / (sqrtf(vi) * rs2 + eps);
+    }
+}
+
+__global__ void adam_tick_kernel(float* state) { state[0] += 1.f; }
+
+static inline int flat_grid(int64_t n) {
+    int64_t g = (n + 255) / 256;
+    const int64_t cap = 148 * 8;
+    return (int)(g < cap ? g : cap);
+}
+
+}  // namespace vnb
+using namespace vnb;
+
+extern "C" int vnb_embed_fwd(const float* table, const int64_t* idx, int n, int dim, float* out, void* stream) {
+    VNB_REQUIRE(table && idx && out && n > 0 && dim > 0, "embed_fwd: bad arguments");
+    embed_fwd_kernel<<<ceil_div((int64_t)n * dim, 256), 256, 0, (cudaStream_t)stream>>>(table, idx, n, dim, out);
+    VNB_LAUNCH_CHECK("embed_fwd");
+    return VNB_OK;
+}
+
+extern "C" int vnb_embed_bwd(const float* dout, const int64_t* idx, int n, int dim, float* dtable, void* stream) {
+    VNB_REQUIRE(dout && idx && dtable && n > 0 && dim > 0, "embed_bwd: bad arguments");
+    embed_bwd_kernel<<<ceil_div(dim, 128), 128, 0, (cudaStream_t)stream>>>(dout, idx, n, dim, dtable);
+    VNB_LAUNCH_CHECK("embed_bwd");
+    return VNB_OK;
+}
+
+extern "C" int vnb_linear_fwd(const float* y, const float* W, const float* bias, int B, int I, int O, float* p,
+                              void* stream) {
+    VNB_REQUIRE(y && W && p && B > 0 && I > 0 && O > 0, "linear_fwd: bad arguments");
+    linear_fwd_kernel<<<ceil_div((int64_t)B * O, 8), 256, 0, (cudaStream_t)stream>>>(y, W, bias, B, I, O, p);
+    VNB_LAUNCH_CHECK("linear_fwd");
+    return VNB_OK;
+}
+
+extern "C" int vnb_linear_bwd(const float* dp, const float* y, const float* W, int B, int I, int O, float* dW,
+                              float* dy, int accumulate_dy, void* stream) {
+    VNB_REQUIRE(dp && y && W && B > 0 && I > 0 && O > 0, "linear_bwd: bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dW) {
+        linear_bwd_w_kernel<<<ceil_div((int64_t)O * I, 256), 256, 0, st>>>(dp, y, B, I, O, dW);
+        VNB_LAUNCH_CHECK("linear_bwd_w");
+    }
+    if (dy) {
+        linear_bwd_y_kernel<<<ceil_div((int64_t)B * I, 128), 128, 0, st>>>(dp, W, B, I, O, dy, accumulate_dy);
+        VNB_LAUNCH_CHECK("linear_bwd_y");
+    }
+    return VNB_OK;
+}
+
+extern "C" int vnb_logloss_fwd(const float* xhat, const float* x, int64_t n, float* acc, void* stream) {
+    VNB_REQUIRE(xhat && x && acc && n > 0, "logloss_fwd: bad arguments");
+    logloss_fwd_kernel<<<flat_grid(n), 256, 0, (cudaStream_t)stream>>>(xhat, x, n, acc);
+    VNB_LAUNCH_CHECK("logloss_fwd");
+    return VNB_OK;
+}
+
+extern "C" int vnb_logloss_bwd(const float* xhat, const float* x, const float* g, int64_t n, float scale, float* dxhat,
+                               void* stream) {
+    VNB_REQUIRE(xhat && x && dxhat && n > 0, "logloss_bwd: bad arguments");
+    logloss_bwd_kernel<<<flat_grid(n), 256, 0, (cudaStream_t)stream>>>(xhat, x, g, n, scale, dxhat);
+    VNB_LAUNCH_CHECK("logloss_bwd");
+    return VNB_OK;
+}
+
+extern "C" int vnb_sqnorm(const float* g, int64_t n, float* acc, void* stream) {
+    VNB_REQUIRE(g && acc && n > 0, "sqnorm: bad arguments");
+    sqnorm_kernel<<<flat_grid(n), 256, 0, (cudaStream_t)stream>>>(g, n, acc);
+    VNB_LAUNCH_CHECK("sqnorm");
+    return VNB_OK;
+}
+
+extern "C" int vnb_adam_step(float* p, const float* g, float* m, float* v, int64_t n, const float* sqn, float max_norm,
+                             float lr, float beta1, float beta2, float eps, float* state, int step_size, float gamma,
+                             void* stream) {
+    VNB_REQUIRE(p && g && m && v && state && n > 0, "adam_step: bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    adam_kernel<<<flat_grid(n), 256, 0, st>>>(p, g, m, v, n, sqn, max_norm, lr, beta1, beta2, eps, state, step_size, gamma);
+    VNB_LAUNCH_CHECK("adam_step");
+    adam_tick_kernel<<<1, 1, 0, st>>>(state);
+    VNB_LAUNCH_CHECK("adam_tick");
+    return VNB_OK;
+}

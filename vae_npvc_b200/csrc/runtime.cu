@@ -1,0 +1,32 @@
+// Error string, launch counter and backend switch of the C ABI.
+#include <stdarg.h>
+
+#include <atomic>
+
+#include "common.cuh"
+
+namespace vnb {
+
+static thread_local char g_err[512] = "";
+static std::atomic<int64_t> g_launches{0};
+static std::atomic<int> g_backend{VNB_BACKEND_AUTO};
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+int backend() { return g_backend.load(std::memory_order_relaxed); }
+
+}  // namespace vnb
+
+extern "C" {
+const char* vnb_last_error(void) { return vnb::g_err; }
+int vnb_version(void) { return 100; }
+int64_t vnb_launch_count(void) { return vnb::g_launches.load(); }
+void vnb_launch_count_reset(void) { vnb::g_launches.store(0); }
+void vnb_set_backend(int b) { vnb::g_backend.store(b); }
+int vnb_get_backend(void) { return vnb::g_backend.load(); }
+}

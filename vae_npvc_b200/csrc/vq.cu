@@ -1,0 +1,351 @@
+// Vector-quantiser kernels around the distance GEMM: codebook / frame preparation, gather + loss
+// sums + histogram, scalar finalisation, backward, EMA codebook update, jitter.
+// Reference: vae_npvc/model/layers_vq.py:28-33, 79-150 (VectorQuantizer), 192-233, 268-323 (EMA),
+// 353-379 (Jitter).  Math: SURVEY.md section 9 C/D/E.
+#include "common.cuh"
+
+namespace vnb {
+
+// one block (128 threads) per code row
+__global__ void __launch_bounds__(128) vq_prep_codebook_kernel(float* __restrict__ E, int K, int D, int normalize,
+                                                               int inplace_renorm, float* __restrict__ e_hat,
+                                                               bf16* __restrict__ e_planes,
+                                                               float* __restrict__ e_sq) {
+    __shared__ float red[32];
+    const int k = blockIdx.x;
+    float* row = E + (int64_t)k * D;
+    const int Dp = (D + 7) & ~7;
+    const int64_t plane = (int64_t)K * Dp;
+    float ss = 0.f;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) ss += row[d] * row[d];
+    ss = block_sum(ss, red);
+    float s1 = 1.f, s2 = 1.f;
+    if (normalize) {
+        s1 = inplace_renorm ? 1.f / sqrtf(ss) : 1.f;      // embed_norm(): E *= (1/||E||)
+        // second, differentiable normalisation of the (renormalised) rows: e_hat = E / ||E||
+        float ss2 = 0.f;
+        for (int d = threadIdx.x; d < D; d += blockDim.x) {
+            const float v = row[d] * s1;
+            ss2 += v * v;
+        }
+        ss2 = block_sum(ss2, red);
+        s2 = sqrtf(ss2);
+    }
+    float q = 0.f;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+        const float v = row[d] * s1;
+        if (normalize && inplace_renorm) row[d] = v;
+        const float e = normalize ? v / s2 : v;
+        if (e_hat) e_hat[(int64_t)k * D + d] = e;
+        if (e_planes) store_planes(e_planes, (int64_t)k * Dp + d, plane, 3, e);
+        q += e * e;
+    }
+    q = block_sum(q, red);
+    if (threadIdx.x == 0 && e_sq) e_sq[k] = q;
+}
+
+// one thread per frame (t fastest => coalesced over the NCT layout)
+__global__ void vq_prep_z_kernel(const float* __restrict__ z, int B, int D, int T, int Tp, int normalize,
+                                 float* __restrict__ zn, bf16* __restrict__ z_planes, float* __restrict__ z_sq,
+                                 float* __restrict__ z_norm) {
+    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= (int64_t)B * T) return;
+    const int64_t b = n / T, t = n - b * T;
+    const float* p = z + b * D * T + t;
+    float ss = 0.f;
+    for (int d = 0; d < D; d++) {
+        const float v = p[(int64_t)d * T];
+        ss += v * v;
+    }
+    const float nrm = sqrtf(ss);
+    const int64_t plane = (int64_t)B * D * Tp;
+    float q = 0.f;
+    for (int d = 0; d < D; d++) {
+        float v = p[(int64_t)d * T];
+        if (normalize) v = v / nrm;
+        if (zn) zn[(b * D + d) * T + t] = v;
+        if (z_planes) store_planes(z_planes, (b * D + d) * Tp + t, plane, 3, v);
+        q += v * v;
+    }
+    if (z_sq) z_sq[n] = q;
+    if (z_norm) z_norm[n] = nrm;
+}
+
+__global__ void __launch_bounds__(256) vq_gather_kernel(const int64_t* __restrict__ idx,
+                                                        const float* __restrict__ e_hat,
+                                                        const float* __restrict__ zn, const float* __restrict__ z,
+                                                        int B, int D, int T, int K, float* __restrict__ q_out,
+                                                        float* __restrict__ sums, int* __restrict__ counts) {
+    __shared__ float red[32];
+    const int64_t N = (int64_t)B * T;
+    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    float lq = 0.f, ln = 0.f;
+    if (n < N) {
+        const int64_t b = n / T, t = n - b * T;
+        const int k = (int)idx[n];
+        const float* er = e_hat + (int64_t)k * D;
+        for (int d = 0; d < D; d++) {
+            const int64_t o = (b * D + d) * T + t;
+            const float q = er[d], a = zn[o];
+            if (q_out) q_out[o] = q;
+            lq += (q - a) * (q - a);
+            if (z) ln += (a - z[o]) * (a - z[o]);
+        }
+        if (counts) atomicAdd(&counts[k], 1);
+    }
+    lq = block_sum(lq, red);
+    ln = block_sum(ln, red);
+    if (threadIdx.x == 0 && sums) {
+        atomicAdd(&sums[0], lq);
+        atomicAdd(&sums[1], ln);
+    }
+}
+
+__global__ void __launch_bounds__(256) vq_finalize_kernel(const float* __restrict__ sums, const int* __restrict__ counts,
+                                                          int K, float N, float scale, int normalize, float eps,
+                                                          float* __restrict__ scal) {
+    __shared__ float red[32];
+    float h = 0.f;
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        const float p = (float)counts[k] / N;
+        h += p * logf(p + eps);
+    }
+    h = block_sum(h, red);
+    if (threadIdx.x == 0) {
+        scal[0] = sums[0] * scale;                                       // z_qut_loss
+        scal[1] = (sums[0] + (normalize ? sums[1] : 0.f)) * scale;       // z_enc_loss (value)
+        scal[2] = expf(-h);                                              // perplexity
+    }
+}
+
+// dz and dE_hat (atomic scatter).  One thread per frame.
+__global__ void vq_bwd_kernel(const float* __restrict__ g_out, const float* __restrict__ g_lq,
+                              const float* __restrict__ g_le, const int64_t* __restrict__ idx,
+                              const float* __restrict__ z, const float* __restrict__ zn,
+                              const float* __restrict__ z_norm, const float* __restrict__ e_hat, int B, int D, int T,
+                              float scale, int normalize, float* __restrict__ dz, float* __restrict__ dE_hat) {
+    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= (int64_t)B * T) return;
+    const int64_t b = n / T, t = n - b * T;
+    const float glq = (g_lq ? g_lq[0] : 0.f) * 2.f * scale;
+    const float gle = (g_le ? g_le[0] : 0.f) * 2.f * scale;
+    const int k = (int)idx[n];
+    const float* er = e_hat + (int64_t)k * D;
+    if (!normalize) {
+        for (int d = 0; d < D; d++) {
+            const int64_t o = (b * D + d) * T + t;
+            const float q = er[d], a = zn[o];
+            dz[o] = (g_out ? g_out[o] : 0.f) + gle * (a - q);
+            if (dE_hat && glq != 0.f) atomicAdd(&dE_hat[(int64_t)k * D + d], glq * (q - a));
+        }
+        return;
+    }
+    // normalised: dzn = g_out + gle*[(zn-q) + (zn-z)];  dz = (dzn - zn*<zn,dzn>)/||z|| - gle*(zn-z)
+    const float inv = 1.f / z_norm[n];
+    float dot = 0.f;
+    for (int d = 0; d < D; d++) {
+        const int64_t o = (b * D + d) * T + t;
+        const float q = er[d], a = zn[o];
+        const float dzn = (g_out ? g_out[o] : 0.f) + gle * ((a - q) + (a - z[o]));
+        dot += a * dzn;
+        if (dE_hat && glq != 0.f) atomicAdd(&dE_hat[(int64_t)k * D + d], glq * (q - a));
+    }
+    for (int d = 0; d < D; d++) {
+        const int64_t o = (b * D + d) * T + t;
+        const float q = er[d], a = zn[o];
+        const float dzn = (g_out ? g_out[o] : 0.f) + gle * ((a - q) + (a - z[o]));
+        dz[o] = (dzn - a * dot) * inv - gle * (a - z[o]);
+    }
+}
+
+__global__ void __launch_bounds__(128) vq_bwd_codebook_kernel(const float* __restrict__ dE_hat,
+                                                              const float* __restrict__ E, int D, int normalize,
+                                                              float* __restrict__ dE) {
+    __shared__ float red[32];
+    const int k = blockIdx.x;
+    const float* e = E + (int64_t)k * D;
+    const float* g = dE_hat + (int64_t)k * D;
+    if (!normalize) {
+        for (int d = threadIdx.x; d < D; d += blockDim.x) dE[(int64_t)k * D + d] = g[d];
+        return;
+    }
+    float ss = 0.f, dot = 0.f;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+        ss += e[d] * e[d];
+        dot += e[d] * g[d];
+    }
+    ss = block_sum(ss, red);
+    dot = block_sum(dot, red);
+    const float inv = 1.f / sqrtf(ss);
+    for (int d = threadIdx.x; d < D; d += blockDim.x)
+        dE[(int64_t)k * D + d] = (g[d] - e[d] * dot / ss) * inv;
+}
+
+// EMA: per-code sums of assigned frames
+__global__ void vq_ema_scatter_kernel(const int64_t* __restrict__ idx, const float* __restrict__ z, int B, int D, int T,
+                                      float* __restrict__ zsum, int* __restrict__ counts) {
+    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= (int64_t)B * T) return;
+    const int64_t b = n / T, t = n - b * T;
+    const int k = (int)idx[n];
+    for (int d = 0; d < D; d++) atomicAdd(&zsum[(int64_t)k * D + d], z[(b * D + d) * T + t]);
+    atomicAdd(&counts[k], 1);
+}
+
+// single block: EMA buffers, alive mask, new codebook, statistics
+__global__ void __launch_bounds__(512) vq_ema_update_kernel(const float* __restrict__ zsum,
+                                                            const int* __restrict__ counts,
+                                                            const float* __restrict__ rand_rows, int K, int D,
+                                                            float N, float mu, float threshold,
+                                                            float* __restrict__ emb_sum, float* __restrict__ emb_elem,
+                                                            float* __restrict__ embeddings,
+                                                            float* __restrict__ stats) {
+    __shared__ float red[32];
+    float ent = 0.f, used = 0.f, alive_n = 0.f, diff = 0.f;
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        const float c = (float)counts[k];
+        const float el = mu * emb_elem[k] + (1.f - mu) * c;
+        emb_elem[k] = el;
+        const float p = c / N;
+        ent += p * logf(p + 1e-8f);
+        used += (c >= threshold) ? 1.f : 0.f;
+        alive_n += (el >= threshold) ? 1.f : 0.f;
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < K * D; e += blockDim.x) {
+        const int k = e / D;
+        const float s = mu * emb_sum[e] + (1.f - mu) * zsum[e];
+        emb_sum[e] = s;
+        const float el = emb_elem[k];
+        const float nv = (el >= threshold) ? s / el : rand_rows[e];
+        const float dlt = nv - embeddings[e];
+        diff += dlt * dlt;
+        embeddings[e] = nv;
+    }
+    ent = block_sum(ent, red);
+    used = block_sum(used, red);
+    alive_n = block_sum(alive_n, red);
+    diff = block_sum(diff, red);
+    if (threadIdx.x == 0) {
+        stats[0] = expf(-ent);
+        stats[1] = used;
+        stats[2] = alive_n;
+        stats[3] = sqrtf(diff) / sqrtf((float)K * (float)D);
+    }
+}
+
+__global__ void vq_frame_rows_kernel(const float* __restrict__ z, const int64_t* __restrict__ perm, int B, int D, int T,
+                                     int K, float* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)K * D) return;
+    const int k = (int)(i / D), d = (int)(i - (int64_t)k * D);
+    const int64_t n = perm[k] % ((int64_t)B * T);
+    const int64_t b = n / T, t = n - b * T;
+    out[i] = z[(b * D + d) * T + t];
+}
+
+__global__ void jitter_kernel(const float* __restrict__ in, const int64_t* __restrict__ src, int64_t rows, int T,
+                              int backward, float* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * T) return;
+    const int64_t r = i / T;
+    const int t = (int)(i - r * T);
+    const int s = (int)src[t];
+    out[i] = backward ? (s == t ? in[i] : 0.f) : in[r * T + s];
+}
+
+}  // namespace vnb
+using namespace vnb;
+
+extern "C" int vnb_vq_prep_codebook(float* E, int K, int D, int normalize, int inplace_renorm, float* e_hat,
+                                    void* e_planes, float* e_sq, void* stream) {
+    VNB_REQUIRE(E && K > 0 && D > 0, "vq_prep_codebook: bad arguments");
+    vq_prep_codebook_kernel<<<K, 128, 0, (cudaStream_t)stream>>>(E, K, D, normalize, inplace_renorm, e_hat,
+                                                                 (bf16*)e_planes, e_sq);
+    VNB_LAUNCH_CHECK("vq_prep_codebook");
+    return VNB_OK;
+}
+
+extern "C" int vnb_vq_prep_z(const float* z, int B, int D, int T, int Tp, int normalize, float* zn, void* z_planes,
+                             float* z_sq, float* z_norm, void* stream) {
+    VNB_REQUIRE(z && B > 0 && D > 0 && T > 0 && Tp >= T, "vq_prep_z: bad arguments");
+    vq_prep_z_kernel<<<ceil_div((int64_t)B * T, 128), 128, 0, (cudaStream_t)stream>>>(z, B, D, T, Tp, normalize, zn,
+                                                                                     (bf16*)z_planes, z_sq, z_norm);
+    VNB_LAUNCH_CHECK("vq_prep_z");
+    return VNB_OK;
+}
+
+extern "C" int vnb_vq_gather(const int64_t* idx, const float* e_hat, const float* zn, const float* z, int B, int D,
+                             int T, int K, float* q_out, float* sums, int* counts, void* stream) {
+    VNB_REQUIRE(idx && e_hat && zn && B > 0 && D > 0 && T > 0 && K > 0, "vq_gather: bad arguments");
+    vq_gather_kernel<<<ceil_div((int64_t)B * T, 256), 256, 0, (cudaStream_t)stream>>>(idx, e_hat, zn, z, B, D, T, K,
+                                                                                     q_out, sums, counts);
+    VNB_LAUNCH_CHECK("vq_gather");
+    return VNB_OK;
+}
+
+extern "C" int vnb_vq_finalize(const float* sums, const int* counts, int K, int64_t N, float scale, int normalize,
+                               float eps, float* scal, void* stream) {
+    VNB_REQUIRE(sums && counts && scal && K > 0 && N > 0, "vq_finalize: bad arguments");
+    vq_finalize_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(sums, counts, K, (float)N, scale, normalize, eps, scal);
+    VNB_LAUNCH_CHECK("vq_finalize");
+    return VNB_OK;
+}
+
+extern "C" int vnb_vq_bwd(const float* g_out, const float* g_lq, const float* g_le, const int64_t* idx, const float* z,
+                          const float* zn, const float* z_norm, const float* e_hat, const float* E, int B, int D, int T,
+                          int K, float scale, int normalize, float* dz, float* dE_hat, void* stream) {
+    (void)E;
+    (void)K;
+    VNB_REQUIRE(idx && zn && e_hat && dz && B > 0 && D > 0 && T > 0, "vq_bwd: bad arguments");
+    VNB_REQUIRE(!normalize || (z && z_norm), "vq_bwd: normalised mode needs z and z_norm");
+    vq_bwd_kernel<<<ceil_div((int64_t)B * T, 128), 128, 0, (cudaStream_t)stream>>>(
+        g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, B, D, T, scale, normalize, dz, dE_hat);
+    VNB_LAUNCH_CHECK("vq_bwd");
+    return VNB_OK;
+}
+
+extern "C" int vnb_vq_bwd_codebook(const float* dE_hat, const float* E, int K, int D, int normalize, float* dE,
+                                   void* stream) {
+    VNB_REQUIRE(dE_hat && E && dE && K > 0 && D > 0, "vq_bwd_codebook: bad arguments");
+    vq_bwd_codebook_kernel<<<K, 128, 0, (cudaStream_t)stream>>>(dE_hat, E, D, normalize, dE);
+    VNB_LAUNCH_CHECK("vq_bwd_codebook");
+    return VNB_OK;
+}
+
+extern "C" int vnb_vq_ema_update(const int64_t* idx, const float* z, int B, int D, int T, int K, float mu,
+                                 float threshold, const float* rand_rows, float* zsum, int* counts, float* emb_sum,
+                                 float* emb_elem, float* embeddings, float* stats, void* stream) {
+    VNB_REQUIRE(idx && z && rand_rows && zsum && counts && emb_sum && emb_elem && embeddings && stats, "vq_ema_update: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    vq_ema_scatter_kernel<<<ceil_div((int64_t)B * T, 128), 128, 0, st>>>(idx, z, B, D, T, zsum, counts);
+    VNB_LAUNCH_CHECK("vq_ema_scatter");
+    vq_ema_update_kernel<<<1, 512, 0, st>>>(zsum, counts, rand_rows, K, D, (float)((int64_t)B * T), mu, threshold,
+                                            emb_sum, emb_elem, embeddings, stats);
+    VNB_LAUNCH_CHECK("vq_ema_update");
+    return VNB_OK;
+}
+
+extern "C" int vnb_vq_frame_rows(const float* z, const int64_t* perm, int B, int D, int T, int K, float* out,
+                                 void* stream) {
+    VNB_REQUIRE(z && perm && out && B > 0 && D > 0 && T > 0 && K > 0, "vq_frame_rows: bad arguments");
+    vq_frame_rows_kernel<<<ceil_div((int64_t)K * D, 256), 256, 0, (cudaStream_t)stream>>>(z, perm, B, D, T, K, out);
+    VNB_LAUNCH_CHECK("vq_frame_rows");
+    return VNB_OK;
+}
+
+extern "C" int vnb_jitter_fwd(const float* in, const int64_t* src, int B, int D, int T, float* out, void* stream) {
+    VNB_REQUIRE(in && src && out && B > 0 && D > 0 && T > 0, "jitter_fwd: bad arguments");
+    const int64_t rows = (int64_t)B * D;
+    jitter_kernel<<<ceil_div(rows * T, 256), 256, 0, (cudaStream_t)stream>>>(in, src, rows, T, 0, out);
+    VNB_LAUNCH_CHECK("jitter_fwd");
+    return VNB_OK;
+}
+
+extern "C" int vnb_jitter_bwd(const float* dout, const int64_t* src, int B, int D, int T, float* din, void* stream) {
+    VNB_REQUIRE(dout && src && din && B > 0 && D > 0 && T > 0, "jitter_bwd: bad arguments");
+    const int64_t rows = (int64_t)B * D;
+    jitter_kernel<<<ceil_div(rows * T, 256), 256, 0, (cudaStream_t)stream>>>(dout, src, rows, T, 1, din);
+    VNB_LAUNCH_CHECK("jitter_bwd");
+    return VNB_OK;
+}
