@@ -129,9 +129,9 @@ int vnb_channel_sum(const float* x, int B, int C, int T, float* out, void* strea
  * time-invariant input, vqvae.py:309-312) */
 int vnb_embed_fwd(const float* table, const int64_t* idx, int n, int dim, float* out, void* stream);
 int vnb_embed_bwd(const float* dout, const int64_t* idx, int n, int dim, float* dtable, void* stream);
-/* p[b,o] = bias[o] + sum_i W[o,i]*y[b,i] */
-int vnb_linear_fwd(const float* y, const float* W, const float* bias, int B, int I, int O, float* p,
-                   void* stream);
+/* p[b,o] = bias[o] + bias2[o] + sum_i W[o,i]*y[b,i]   (either bias may be NULL) */
+int vnb_linear_fwd(const float* y, const float* W, const float* bias, const float* bias2, int B, int I,
+                   int O, float* p, void* stream);
 /* dW[o,i] = sum_b dp[b,o]*y[b,i];  dy[b,i] (+)= sum_o W[o,i]*dp[b,o] */
 int vnb_linear_bwd(const float* dp, const float* y, const float* W, int B, int I, int O, float* dW,
                    float* dy, int accumulate_dy, void* stream);
@@ -178,8 +178,8 @@ int vnb_jitter_fwd(const float* in, const int64_t* src, int B, int D, int T, flo
 /* grad: zero where src[t] != t */
 int vnb_jitter_bwd(const float* dout, const int64_t* src, int B, int D, int T, float* din, void* stream);
 
-/* ---- log-loss (layers.py:283-296): acc[0] += sum 0.5*(log2pi + (xhat-x)^2) (zeroed by caller) */
-int vnb_logloss_fwd(const float* xhat, const float* x, int64_t n, float* acc, void* stream);
+/* ---- log-loss (layers.py:283-296): acc[0] += scale * sum 0.5*(log2pi + (xhat-x)^2) (zeroed by caller) */
+int vnb_logloss_fwd(const float* xhat, const float* x, int64_t n, float scale, float* acc, void* stream);
 /* dxhat = g * (xhat-x) * scale ; g device scalar (NULL = 1) */
 int vnb_logloss_bwd(const float* xhat, const float* x, const float* g, int64_t n, float scale,
                     float* dxhat, void* stream);

@@ -24,7 +24,8 @@ __global__ void embed_bwd_kernel(const float* __restrict__ dout, const int64_t* 
 
 // one warp per output (b,o)
 __global__ void __launch_bounds__(256) linear_fwd_kernel(const float* __restrict__ y, const float* __restrict__ W,
-                                                         const float* __restrict__ bias, int B, int I, int O,
+                                                         const float* __restrict__ bias,
+                                                         const float* __restrict__ bias2, int B, int I, int O,
                                                          float* __restrict__ p) {
     const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (w >= (int64_t)B * O) return;
@@ -33,7 +34,7 @@ __global__ void __launch_bounds__(256) linear_fwd_kernel(const float* __restrict
     float s = 0.f;
     for (int i = lane; i < I; i += 32) s = fmaf(W[(int64_t)o * I + i], y[(int64_t)b * I + i], s);
     s = warp_sum(s);
-    if (lane == 0) p[w] = s + (bias ? bias[o] : 0.f);
+    if (lane == 0) p[w] = s + (bias ? bias[o] : 0.f) + (bias2 ? bias2[o] : 0.f);
 }
 
 __global__ void linear_bwd_w_kernel(const float* __restrict__ dp, const float* __restrict__ y, int B, int I, int O,
@@ -59,7 +60,7 @@ __global__ void linear_bwd_y_kernel(const float* __restrict__ dp, const float* _
 constexpr float LOG_2PI_F = 1.8378770664093453f;
 
 __global__ void __launch_bounds__(256) logloss_fwd_kernel(const float* __restrict__ xhat, const float* __restrict__ x,
-                                                          int64_t n, float* __restrict__ acc) {
+                                                          int64_t n, float scale, float* __restrict__ acc) {
     __shared__ float red[32];
     float s = 0.f;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -67,7 +68,7 @@ __global__ void __launch_bounds__(256) logloss_fwd_kernel(const float* __restric
         s += 0.5f * (LOG_2PI_F + d * d);
     }
     s = block_sum(s, red);
-    if (threadIdx.x == 0) atomicAdd(acc, s);
+    if (threadIdx.x == 0) atomicAdd(acc, s * scale);
 }
 
 __global__ void logloss_bwd_kernel(const float* __restrict__ xhat, const float* __restrict__ x,
@@ -141,10 +142,10 @@ extern "C" int vnb_embed_bwd(const float* dout, const int64_t* idx, int n, int d
     return VNB_OK;
 }
 
-extern "C" int vnb_linear_fwd(const float* y, const float* W, const float* bias, int B, int I, int O, float* p,
-                              void* stream) {
+extern "C" int vnb_linear_fwd(const float* y, const float* W, const float* bias, const float* bias2, int B, int I,
+                              int O, float* p, void* stream) {
     VNB_REQUIRE(y && W && p && B > 0 && I > 0 && O > 0, "linear_fwd: bad arguments");
-    linear_fwd_kernel<<<ceil_div((int64_t)B * O, 8), 256, 0, (cudaStream_t)stream>>>(y, W, bias, B, I, O, p);
+    linear_fwd_kernel<<<ceil_div((int64_t)B * O, 8), 256, 0, (cudaStream_t)stream>>>(y, W, bias, bias2, B, I, O, p);
     VNB_LAUNCH_CHECK("linear_fwd");
     return VNB_OK;
 }
@@ -164,9 +165,9 @@ extern "C" int vnb_linear_bwd(const float* dp, const float* y, const float* W, i
     return VNB_OK;
 }
 
-extern "C" int vnb_logloss_fwd(const float* xhat, const float* x, int64_t n, float* acc, void* stream) {
+extern "C" int vnb_logloss_fwd(const float* xhat, const float* x, int64_t n, float scale, float* acc, void* stream) {
     VNB_REQUIRE(xhat && x && acc && n > 0, "logloss_fwd: bad arguments");
-    logloss_fwd_kernel<<<flat_grid(n), 256, 0, (cudaStream_t)stream>>>(xhat, x, n, acc);
+    logloss_fwd_kernel<<<flat_grid(n), 256, 0, (cudaStream_t)stream>>>(xhat, x, n, scale, acc);
     VNB_LAUNCH_CHECK("logloss_fwd");
     return VNB_OK;
 }

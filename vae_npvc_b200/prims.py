@@ -1,0 +1,365 @@
+"""Python-level primitives: one function per C-ABI entry point (include/vae_npvc_b200.h).
+
+Each allocates its outputs with torch (the library itself allocates nothing) and launches on
+the current CUDA stream.  This module is the single seam between the host-side mirror of the
+reference classes (functional.py, model/*.py) and the CUDA kernels; there is no other
+implementation behind it.
+"""
+import torch
+
+from . import _C
+from ._C import ACT_LRELU, ACT_NONE, ACT_RELU  # noqa: F401
+
+
+def pitch(T):
+    return (T + 7) // 8 * 8
+
+
+class Planes:
+    """bf16 GEMM-operand planes of an activation: data (P, B, C, Tp)."""
+    __slots__ = ('data', 'P', 'B', 'C', 'T', 'Tp')
+
+    def __init__(self, data, P, B, C, T, Tp):
+        self.data, self.P, self.B, self.C, self.T, self.Tp = data, P, B, C, T, Tp
+
+    @staticmethod
+    def empty(P, B, C, T, device):
+        Tp = pitch(T)
+        # zero-filled so the pitch padding is finite (the kernels never read it as data)
+        alloc = torch.zeros if Tp != T else torch.empty
+        return Planes(alloc((P, B, C, Tp), dtype=torch.bfloat16, device=device), P, B, C, T, Tp)
+
+
+class ConvWeights:
+    """Materialised conv weights: wf (P,k,co,ci_p) forward operand, wb (P,k,ci,co_p) data-grad
+    operand, w32 optional fp32 effective weight in the parameter layout."""
+    __slots__ = ('wf', 'wb', 'w32', 'taps', 'Cout', 'Cin', 'transposed')
+
+    def __init__(self, wf, wb, w32, taps, Cout, Cin, transposed):
+        self.wf, self.wb, self.w32, self.taps, self.Cout, self.Cin, self.transposed = wf, wb, w32, taps, Cout, Cin, transposed
+
+
+def _f32(shape, like):
+    return torch.empty(shape, dtype=torch.float32, device=like.device)
+
+
+# --------------------------------------------------------------------------------------------
+# weight norm
+# --------------------------------------------------------------------------------------------
+def _wbuf(shape, inner, device):
+    # pitch padding (if any) must be finite; otherwise skip the memset
+    alloc = torch.zeros if shape[-1] != inner else torch.empty
+    return alloc(shape, dtype=torch.bfloat16, device=device)
+
+
+def wn_prepare(v, g, transposed, P, need_wf=True, need_wb=True, need_w32=False):
+    d0, d1, k = v.shape
+    co, ci = (d1, d0) if transposed else (d0, d1)
+    wf = _wbuf((P, k, co, pitch(ci)), ci, v.device) if need_wf else None
+    wb = _wbuf((P, k, ci, pitch(co)), co, v.device) if need_wb else None
+    w32 = _f32((d0, d1, k), v) if need_w32 else None
+    _C.call('wn_prepare', v, g, d0, d1, k, int(transposed), P, wf, wb, w32)
+    return ConvWeights(wf, wb, w32, k, co, ci, bool(transposed))
+
+
+def wn_backward(dw, v, g):
+    d0, d1, k = v.shape
+    dv, dg = torch.empty_like(v), torch.empty_like(g)
+    _C.call('wn_backward', dw, v, g, d0, d1, k, dv, dg)
+    return dv, dg
+
+
+# --------------------------------------------------------------------------------------------
+# GEMM-shaped ops
+# --------------------------------------------------------------------------------------------
+def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False):
+    """x_pl: Planes (B,Cin,T); w_op: (P,taps,Cout,Cin_p) bf16 -> out fp32 (B,Cout,T)."""
+    if out is None:
+        out = torch.empty((x_pl.B, Cout, x_pl.T), dtype=torch.float32, device=x_pl.data.device)
+    _C.call('conv_fwd', x_pl.data, x_pl.P, x_pl.B, x_pl.C, x_pl.T, x_pl.Tp, w_op, taps, dil, Cout, bias,
+            bias_bstride, residual, out, int(accumulate))
+    return out
+
+
+def conv_wgrad(dy_pl, u_pl, taps, dil, transposed):
+    Cout, Cin = dy_pl.C, u_pl.C
+    shape = (Cin, Cout, taps) if transposed else (Cout, Cin, taps)
+    dw = torch.empty(shape, dtype=torch.float32, device=dy_pl.data.device)
+    _C.call('conv_wgrad', dy_pl.data, u_pl.data, dy_pl.P, dy_pl.B, Cout, Cin, dy_pl.T, dy_pl.Tp, taps, dil,
+            int(transposed), dw)
+    return dw
+
+
+# --------------------------------------------------------------------------------------------
+# operand planes
+# --------------------------------------------------------------------------------------------
+def make_planes(x, P, scale=1.0, act=ACT_NONE, want_id=True, want_act=False):
+    B, C, T = x.shape
+    pid = Planes.empty(P, B, C, T, x.device) if want_id else None
+    pact = Planes.empty(P, B, C, T, x.device) if want_act else None
+    _C.call('make_planes', x, B, C, T, pitch(T), P, scale, act, pid.data if pid else None,
+            pact.data if pact else None)
+    return pid, pact
+
+
+def concat_planes(xa, xb, P):
+    B, Ca, T = xa.shape
+    Cb = xb.shape[1]
+    out = Planes.empty(P, B, Ca + Cb, T, xa.device)
+    _C.call('concat_planes', xa, Ca, xb, Cb, B, T, out.Tp, P, out.data)
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# forward elementwise / reductions
+# --------------------------------------------------------------------------------------------
+def gn_stats(h, groups, eps=1e-5):
+    B, C, T = h.shape
+    mean, rstd = _f32((B, groups), h), _f32((B, groups), h)
+    _C.call('gn_stats', h, B, C, T, groups, eps, mean, rstd)
+    return mean, rstd
+
+
+def enc_out(h, s, mean, rstd, gamma, beta, P, want_y=True, want_ypl=True, want_upl=True):
+    B, C, T = h.shape
+    y = torch.empty_like(h) if want_y else None
+    ypl = Planes.empty(P, B, C, T, h.device) if want_ypl else None
+    upl = Planes.empty(P, B, C, T, h.device) if want_upl else None
+    _C.call('enc_out', h, s, mean, rstd, gamma, beta, B, C, T, pitch(T), P, y, ypl.data if ypl else None,
+            upl.data if upl else None)
+    return y, ypl, upl
+
+
+def dec_gate(a, mean, rstd, gamma, beta, P):
+    B, C2, T = a.shape
+    C = C2 // 2
+    gpl = Planes.empty(P, B, C, T, a.device)
+    _C.call('dec_gate', a, mean, rstd, gamma, beta, B, C, T, gpl.Tp, P, gpl.data)
+    return gpl
+
+
+def dec_out(r, x, S, P, skip_sum=None, first=True, want_x=True, want_xpl=True):
+    """r (B,C+S,T), x (B,C,T) -> x_out, x_planes, skip_sum (allocated when None)."""
+    B, C, T = x.shape
+    x_out = torch.empty_like(x) if want_x else None
+    xpl = Planes.empty(P, B, C, T, x.device) if want_xpl else None
+    if skip_sum is None and S > 0:
+        skip_sum = _f32((B, S, T), x)
+        first = True
+    _C.call('dec_out', r, x, B, C, S, T, pitch(T), P, x_out, xpl.data if xpl else None, skip_sum, int(first))
+    return x_out, xpl, skip_sum
+
+
+# --------------------------------------------------------------------------------------------
+# backward elementwise / reductions
+# --------------------------------------------------------------------------------------------
+def gn_bwd_rows(dn, h, mean, rstd, groups):
+    B, C, T = h.shape
+    R = _f32((B, C, 3), h)
+    _C.call('gn_bwd_rows', dn, h, mean, rstd, B, C, T, groups, R)
+    return R
+
+
+def gate_bwd_rows(dg, a, mean, rstd, gamma, beta):
+    B, C2, T = a.shape
+    R = _f32((B, C2, 3), a)
+    _C.call('gate_bwd_rows', dg, a, mean, rstd, gamma, beta, B, C2 // 2, T, R)
+    return R
+
+
+def gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums=False):
+    """-> dgamma (C), dbeta (C), S (B,groups,2), dpre_bsum (B,C)|None, dpre_csum (C)|None"""
+    B, C, _ = R.shape
+    dgamma, dbeta = _f32((C,), R), _f32((C,), R)
+    S = _f32((B, groups, 2), R)
+    bsum = _f32((B, C), R) if want_sums else None
+    csum = _f32((C,), R) if want_sums else None
+    _C.call('gn_bwd_finalize', R, gamma, rstd, B, C, T, groups, dgamma, dbeta, S, bsum, csum)
+    return dgamma, dbeta, S, bsum, csum
+
+
+def gn_bwd_apply(dn, h, mean, rstd, gamma, S, groups, P, want_dn_planes=False):
+    B, C, T = h.shape
+    dpre = Planes.empty(P, B, C, T, h.device)
+    dnp = Planes.empty(P, B, C, T, h.device) if want_dn_planes else None
+    _C.call('gn_bwd_apply', dn, h, mean, rstd, gamma, S, B, C, T, groups, dpre.Tp, P, dpre.data,
+            dnp.data if dnp else None)
+    return dpre, dnp
+
+
+def gate_bwd_apply(dg, a, mean, rstd, gamma, beta, S, P):
+    B, C2, T = a.shape
+    da = Planes.empty(P, B, C2, T, a.device)
+    _C.call('gate_bwd_apply', dg, a, mean, rstd, gamma, beta, S, B, C2 // 2, T, da.Tp, P, da.data)
+    return da
+
+
+def act_bwd_add(du, c, add, act, scale=1.0):
+    out = torch.empty_like(du)
+    _C.call('act_bwd_add', du, c, add, du.numel(), act, scale, out)
+    return out
+
+
+def channel_sum(x, out=None):
+    B, C, T = x.shape
+    if out is None:
+        out = _f32((C,), x)
+    _C.call('channel_sum', x, B, C, T, out)
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# speaker conditioning
+# --------------------------------------------------------------------------------------------
+def embed_fwd(table, idx):
+    n, dim = idx.numel(), table.shape[1]
+    out = _f32(tuple(idx.shape) + (dim,), table)
+    _C.call('embed_fwd', table, idx.contiguous(), n, dim, out)
+    return out
+
+
+def embed_bwd(dout, idx, num_rows):
+    dim = dout.shape[-1]
+    dtable = torch.zeros((num_rows, dim), dtype=torch.float32, device=dout.device)
+    _C.call('embed_bwd', dout.contiguous(), idx.contiguous(), idx.numel(), dim, dtable)
+    return dtable
+
+
+def linear_fwd(y, W, bias, bias2=None):
+    B, I = y.shape
+    O = W.shape[0]
+    p = _f32((B, O), y)
+    _C.call('linear_fwd', y, W, bias, bias2, B, I, O, p)
+    return p
+
+
+def linear_bwd(dp, y, W, dy=None):
+    """-> dW (O,I), dy (B,I); accumulates into ``dy`` when given."""
+    B, I = y.shape
+    O = W.shape[0]
+    dW = _f32((O, I), y)
+    acc = dy is not None
+    if dy is None:
+        dy = _f32((B, I), y)
+    _C.call('linear_bwd', dp, y, W, B, I, O, dW, dy, int(acc))
+    return dW, dy
+
+
+# --------------------------------------------------------------------------------------------
+# vector quantiser
+# --------------------------------------------------------------------------------------------
+def vq_prep_codebook(E, normalize, inplace_renorm=True):
+    K, D = E.shape
+    e_hat = torch.empty_like(E)
+    e_pl = torch.zeros((3, K, pitch(D)), dtype=torch.bfloat16, device=E.device)
+    e_sq = _f32((K,), E)
+    _C.call('vq_prep_codebook', E, K, D, int(normalize), int(inplace_renorm), e_hat, e_pl, e_sq)
+    return e_hat, e_pl, e_sq
+
+
+def vq_prep_z(z, normalize):
+    B, D, T = z.shape
+    zn = torch.empty_like(z)
+    zpl = Planes.empty(3, B, D, T, z.device)
+    z_sq, z_norm = _f32((B * T,), z), _f32((B * T,), z)
+    _C.call('vq_prep_z', z, B, D, T, zpl.Tp, int(normalize), zn, zpl.data, z_sq, z_norm)
+    return zn, zpl, z_sq, z_norm
+
+
+def vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq):
+    B, D, T = zn.shape
+    K = e_hat.shape[0]
+    idx = torch.empty((B * T,), dtype=torch.int64, device=zn.device)
+    _C.call('vq_lookup', zn, zpl.data if zpl is not None else None, z_sq, e_hat, e_pl, e_sq, B, D, T,
+            zpl.Tp if zpl is not None else pitch(T), K, idx)
+    return idx
+
+
+def vq_gather(idx, e_hat, zn, z, want_q=True, want_stats=True):
+    """-> q (B,D,T), sums (2,) [sum (q-zn)^2, sum (zn-z)^2], counts (K,) int32"""
+    B, D, T = zn.shape
+    K = e_hat.shape[0]
+    q = torch.empty_like(zn) if want_q else None
+    sums = torch.zeros((2,), dtype=torch.float32, device=zn.device) if want_stats else None
+    counts = torch.zeros((K,), dtype=torch.int32, device=zn.device) if want_stats else None
+    _C.call('vq_gather', idx, e_hat, zn, z, B, D, T, K, q, sums, counts)
+    return q, sums, counts
+
+
+def vq_finalize(sums, counts, N, scale, normalize, eps):
+    scal = _f32((3,), sums)
+    _C.call('vq_finalize', sums, counts, counts.numel(), N, scale, int(normalize), eps, scal)
+    return scal
+
+
+def vq_bwd(g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, E, scale, normalize, want_dE=True):
+    B, D, T = zn.shape
+    K = e_hat.shape[0]
+    dz = torch.empty_like(zn)
+    dEh = torch.zeros_like(e_hat) if want_dE else None
+    _C.call('vq_bwd', g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, E, B, D, T, K, scale, int(normalize), dz, dEh)
+    return dz, dEh
+
+
+def vq_bwd_codebook(dE_hat, E, normalize):
+    K, D = E.shape
+    dE = torch.empty_like(E)
+    _C.call('vq_bwd_codebook', dE_hat, E, K, D, int(normalize), dE)
+    return dE
+
+
+def vq_ema_update(idx, z, mu, threshold, rand_rows, emb_sum, emb_elem, embeddings):
+    """In-place EMA update of the three buffers; -> stats (4,) [entropy, used_curr, usage, diff_emb]"""
+    B, D, T = z.shape
+    K = embeddings.shape[0]
+    zsum = torch.zeros((K, D), dtype=torch.float32, device=z.device)
+    counts = torch.zeros((K,), dtype=torch.int32, device=z.device)
+    stats = _f32((4,), z)
+    _C.call('vq_ema_update', idx, z, B, D, T, K, mu, threshold, rand_rows, zsum, counts, emb_sum, emb_elem,
+            embeddings, stats)
+    return stats
+
+
+def vq_frame_rows(z, perm, K):
+    B, D, T = z.shape
+    out = _f32((K, D), z)
+    _C.call('vq_frame_rows', z, perm, B, D, T, K, out)
+    return out
+
+
+def jitter_fwd(x, src):
+    B, D, T = x.shape
+    out = torch.empty_like(x)
+    _C.call('jitter_fwd', x, src, B, D, T, out)
+    return out
+
+
+def jitter_bwd(dout, src):
+    B, D, T = dout.shape
+    din = torch.empty_like(dout)
+    _C.call('jitter_bwd', dout, src, B, D, T, din)
+    return din
+
+
+# --------------------------------------------------------------------------------------------
+# losses / optimiser
+# --------------------------------------------------------------------------------------------
+def logloss_fwd(xhat, x, scale=1.0):
+    acc = torch.zeros((1,), dtype=torch.float32, device=x.device)
+    _C.call('logloss_fwd', xhat, x, x.numel(), scale, acc)
+    return acc
+
+
+def logloss_bwd(xhat, x, g, scale):
+    dx = torch.empty_like(xhat)
+    _C.call('logloss_bwd', xhat, x, g, x.numel(), scale, dx)
+    return dx
+
+
+def sqnorm(g, acc):
+    _C.call('sqnorm', g, g.numel(), acc)
+    return acc
+
+
+def adam_step(p, g, m, v, sqn, max_norm, lr, beta1, beta2, eps, state, step_size, gamma):
+    _C.call('adam_step', p, g, m, v, p.numel(), sqn, max_norm, lr, beta1, beta2, eps, state, step_size, gamma)
