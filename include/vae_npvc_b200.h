@@ -164,11 +164,17 @@ int vnb_vq_bwd(const float* g_out, const float* g_lq, const float* g_le, const i
 /* dE = (I - e e^T) dE_hat / ||E||  (normalised codebook) ; else copy */
 int vnb_vq_bwd_codebook(const float* dE_hat, const float* E, int K, int D, int normalize, float* dE,
                         void* stream);
-/* EMA update (layers_vq.py:203-233).  zsum (K,D) zeroed scratch; rand_rows (K,D) restart rows;
+/* EMA update (layers_vq.py:203-233) in two steps so that a data-parallel caller can all-reduce
+ * zsum/counts in between.  scatter: zsum[k,:] += z frames with idx==k, counts[k] += 1 (both
+ * zeroed by the caller). */
+int vnb_vq_ema_scatter(const int64_t* idx, const float* z, int B, int D, int T, int K, float* zsum,
+                       int* counts, void* stream);
+/* update: emb_sum/emb_elem EMA, codebook <- emb_sum/emb_elem where emb_elem >= threshold else
+ * rand_rows (K,D); n_frames = total frames behind counts;
  * stats[0..3] = entropy, used_curr, usage, diff_emb */
-int vnb_vq_ema_update(const int64_t* idx, const float* z, int B, int D, int T, int K, float mu,
-                      float threshold, const float* rand_rows, float* zsum, int* counts, float* emb_sum,
-                      float* emb_elem, float* embeddings, float* stats, void* stream);
+int vnb_vq_ema_update(const float* zsum, const int* counts, int K, int D, int64_t n_frames, float mu,
+                      float threshold, const float* rand_rows, float* emb_sum, float* emb_elem,
+                      float* embeddings, float* stats, void* stream);
 /* gather rows of the frame matrix: out[k,:] = z[:, :, .] at flat frame perm[k] % N (+ optional
  * noise) - EMA init / restart candidates (:183-201,212-213) */
 int vnb_vq_frame_rows(const float* z, const int64_t* perm, int B, int D, int T, int K, float* out,

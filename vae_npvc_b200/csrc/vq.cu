@@ -313,15 +313,22 @@ extern "C" int vnb_vq_bwd_codebook(const float* dE_hat, const float* E, int K, i
     return VNB_OK;
 }
 
-extern "C" int vnb_vq_ema_update(const int64_t* idx, const float* z, int B, int D, int T, int K, float mu,
-                                 float threshold, const float* rand_rows, float* zsum, int* counts, float* emb_sum,
-                                 float* emb_elem, float* embeddings, float* stats, void* stream) {
-    VNB_REQUIRE(idx && z && rand_rows && zsum && counts && emb_sum && emb_elem && embeddings && stats, "vq_ema_update: null pointer");
-    cudaStream_t st = (cudaStream_t)stream;
-    vq_ema_scatter_kernel<<<ceil_div((int64_t)B * T, 128), 128, 0, st>>>(idx, z, B, D, T, zsum, counts);
+extern "C" int vnb_vq_ema_scatter(const int64_t* idx, const float* z, int B, int D, int T, int K, float* zsum,
+                                  int* counts, void* stream) {
+    (void)K;
+    VNB_REQUIRE(idx && z && zsum && counts && B > 0 && D > 0 && T > 0, "vq_ema_scatter: bad arguments");
+    vq_ema_scatter_kernel<<<ceil_div((int64_t)B * T, 128), 128, 0, (cudaStream_t)stream>>>(idx, z, B, D, T, zsum, counts);
     VNB_LAUNCH_CHECK("vq_ema_scatter");
-    vq_ema_update_kernel<<<1, 512, 0, st>>>(zsum, counts, rand_rows, K, D, (float)((int64_t)B * T), mu, threshold,
-                                            emb_sum, emb_elem, embeddings, stats);
+    return VNB_OK;
+}
+
+extern "C" int vnb_vq_ema_update(const float* zsum, const int* counts, int K, int D, int64_t n_frames, float mu,
+                                 float threshold, const float* rand_rows, float* emb_sum, float* emb_elem,
+                                 float* embeddings, float* stats, void* stream) {
+    VNB_REQUIRE(zsum && counts && rand_rows && emb_sum && emb_elem && embeddings && stats && K > 0 && D > 0 && n_frames > 0,
+                "vq_ema_update: bad arguments");
+    vq_ema_update_kernel<<<1, 512, 0, (cudaStream_t)stream>>>(zsum, counts, rand_rows, K, D, (float)n_frames, mu,
+                                                              threshold, emb_sum, emb_elem, embeddings, stats);
     VNB_LAUNCH_CHECK("vq_ema_update");
     return VNB_OK;
 }

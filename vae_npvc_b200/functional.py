@@ -192,3 +192,227 @@ def enc_block(c, params, n_layers=1, dil=1, P=None):
     for k, pl in box.items():
         attach_planes(y, k, pl)
     return y
+
+
+class DecBlockFn(Function):
+    """DeConv1d_Layernorm_GLU_ResSkip.forward (vae_npvc/model/layers.py:218-249), non-causal:
+    a = ConvT_k(x) + Conv_1(cond); h = GroupNorm(2)(a); g = tanh(h[:C]) * sigmoid(h[C:]);
+    r = Conv_1(g); x' = r[:C] + x; skip = r[C:].
+    ``cond`` is (B,Y) when it is time-invariant (the Decoder's c.repeat, vqvae.py:309-312: the
+    1x1 cond conv collapses to a per-utterance bias) or (B,Y,T) in general.
+    ``skip_acc``: optional running skip sum updated IN PLACE (vqvae.py:313).
+    Math: SURVEY.md section 9 B."""
+
+    @staticmethod
+    def forward(ctx, x, cond, skip_acc, P, dil, box, v_in, g_in, b_in, gamma, beta, v_c, g_c, b_c, v_rs, g_rs, b_rs):
+        x = x.contiguous()
+        B, C, T = x.shape
+        S = v_rs.shape[0] - C
+        xpl = _input_planes(x, P)
+        Win = Pm.wn_prepare(v_in, g_in, True, P, need_wb=ctx.needs_input_grad[0])
+        has_cond = v_c is not None and cond is not None
+        bcast = has_cond and cond.dim() == 2
+        cpl = wc32 = wc_wb = None
+        if has_cond and bcast:
+            cond = cond.contiguous()
+            Wc = Pm.wn_prepare(v_c, g_c, False, P, need_wf=False, need_wb=False, need_w32=True)
+            wc32 = Wc.w32.view(2 * C, -1)
+            p = Pm.linear_fwd(cond, wc32, b_c, b_in)
+            a = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, p, 2 * C)
+        else:
+            a = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, b_in, 0)
+            if has_cond:
+                cond = cond.contiguous()
+                cpl = _input_planes(cond, P)
+                Wc = Pm.wn_prepare(v_c, g_c, False, P, need_wb=ctx.needs_input_grad[1])
+                wc_wb = Wc.wb
+                Pm.conv_fwd(cpl, Wc.wf, 1, 1, 2 * C, b_c, 0, None, a, True)
+        mean, rstd = Pm.gn_stats(a, 2)
+        gpl = Pm.dec_gate(a, mean, rstd, gamma, beta, P)
+        Wrs = Pm.wn_prepare(v_rs, g_rs, False, P)
+        r = Pm.conv_fwd(gpl, Wrs.wf, 1, 1, C + S, b_rs, 0)
+        x_out, xopl, skip = Pm.dec_out(r, x, S, P, skip_acc, skip_acc is None)
+        if skip_acc is not None:
+            ctx.mark_dirty(skip_acc)
+        if box is not None:
+            box['id'] = xopl
+        ctx.save_for_backward(cond if has_cond else None, a, mean, rstd, gamma, beta, v_in, g_in, v_c, g_c, v_rs, g_rs)
+        ctx.xpl, ctx.gpl, ctx.cpl = xpl, gpl, cpl
+        ctx.win_wb, ctx.wrs_wb, ctx.wc_wb, ctx.wc32 = Win.wb, Wrs.wb, wc_wb, wc32
+        ctx.cfg = (P, dil, B, C, S, T, Win.taps, has_cond, bcast)
+        ctx.has_acc = skip_acc is not None
+        return x_out, skip
+
+    @staticmethod
+    def backward(ctx, dxo, dskip):
+        cond, a, mean, rstd, gamma, beta, v_in, g_in, v_c, g_c, v_rs, g_rs = ctx.saved_tensors
+        P, dil, B, C, S, T, taps, has_cond, bcast = ctx.cfg
+        dev = a.device
+        dxo = torch.zeros((B, C, T), device=dev) if dxo is None else dxo.contiguous()
+        dskip = torch.zeros((B, S, T), device=dev) if dskip is None else dskip.contiguous()
+        drpl = Pm.concat_planes(dxo, dskip, P)
+        db_rs = torch.empty((C + S,), dtype=torch.float32, device=dev)
+        Pm.channel_sum(dxo, db_rs[:C])
+        Pm.channel_sum(dskip, db_rs[C:])
+        dg = Pm.conv_fwd(drpl, ctx.wrs_wb, 1, 1, C)
+        dv_rs, dg_rs = _dw_to_param_grads(Pm.conv_wgrad(drpl, ctx.gpl, 1, 1, False), v_rs, g_rs)
+        R = Pm.gate_bwd_rows(dg, a, mean, rstd, gamma, beta)
+        dgamma, dbeta, Ssum, bsum, csum = Pm.gn_bwd_finalize(R, gamma, rstd, T, 2, True)
+        dapl = Pm.gate_bwd_apply(dg, a, mean, rstd, gamma, beta, Ssum, P)
+        dx = Pm.conv_fwd(dapl, ctx.win_wb, taps, dil, C, None, 0, dxo) if ctx.needs_input_grad[0] else None
+        dv_in, dg_in = _dw_to_param_grads(Pm.conv_wgrad(dapl, ctx.xpl, taps, dil, True), v_in, g_in)
+        dcond = dv_c = dg_c = db_c = None
+        if has_cond:
+            db_c = csum.clone()
+            if bcast:
+                dwc, dcond = Pm.linear_bwd(bsum, cond, ctx.wc32)
+                dv_c, dg_c = _dw_to_param_grads(dwc.view_as(v_c), v_c, g_c)
+            else:
+                dv_c, dg_c = _dw_to_param_grads(Pm.conv_wgrad(dapl, ctx.cpl, 1, 1, False), v_c, g_c)
+                if ctx.needs_input_grad[1]:
+                    dcond = Pm.conv_fwd(dapl, ctx.wc_wb, 1, 1, cond.shape[1])
+            if not ctx.needs_input_grad[1]:
+                dcond = None
+        return (dx, dcond, dskip if ctx.has_acc else None, None, None, None, dv_in, dg_in, csum, dgamma, dbeta, dv_c, dg_c, db_c,
+                dv_rs, dg_rs, db_rs)
+
+
+def dec_block(x, cond, params, skip_acc=None, dil=1, P=None):
+    """params = (v_in, g_in, b_in, gamma, beta, v_c, g_c, b_c, v_rs, g_rs, b_rs) -> (x', skip)"""
+    box = {}
+    x_out, skip = DecBlockFn.apply(x, cond, skip_acc, P or get_precision(), dil, box, *params)
+    attach_planes(x_out, 'id', box.get('id'))
+    return x_out, skip
+
+
+def _vq_scale(reduction, B, T, D):
+    """Scalar the summed squared error is multiplied by (layers_vq.py:123-134)."""
+    return {'sum': 1.0, 'mean': 1.0 / (B * T * D), 'batch_mean': 1.0 / B, 'frame_mean': 1.0 / (B * T)}[reduction]
+
+
+class VQFn(Function):
+    """VectorQuantizer.forward for the scalar reductions (layers_vq.py:79-150): in-place codebook
+    renormalisation, distance GEMM + argmin, gather, both losses, perplexity, straight-through
+    output.  Returns (z_vq, z_qut_loss, z_enc_loss, perplexity, idx).  SURVEY.md section 9 C/D."""
+
+    @staticmethod
+    def forward(ctx, z, E, normalize, reduction):
+        z = z.contiguous()
+        B, D, T = z.shape
+        e_hat, e_pl, e_sq = Pm.vq_prep_codebook(E.detach(), normalize, True)
+        zn, zpl, z_sq, z_norm = Pm.vq_prep_z(z, normalize)
+        idx = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
+        q, sums, counts = Pm.vq_gather(idx, e_hat, zn, z if normalize else None)
+        scale = _vq_scale(reduction, B, T, D)
+        scal = Pm.vq_finalize(sums, counts, B * T, scale, normalize, 1e-10)
+        ctx.save_for_backward(z, zn, z_norm, e_hat, E, idx)
+        ctx.cfg = (scale, normalize)
+        lq, le, perp = scal[0], scal[1], scal[2]
+        ctx.mark_non_differentiable(perp, idx)
+        return q, lq, le, perp, idx
+
+    @staticmethod
+    def backward(ctx, g_out, g_lq, g_le, _gp, _gi):
+        z, zn, z_norm, e_hat, E, idx = ctx.saved_tensors
+        scale, normalize = ctx.cfg
+        g_out = g_out.contiguous() if g_out is not None else None
+        g_lq = g_lq.contiguous() if g_lq is not None else None
+        g_le = g_le.contiguous() if g_le is not None else None
+        want_dE = ctx.needs_input_grad[1]
+        dz, dEh = Pm.vq_bwd(g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, E, scale, normalize, want_dE)
+        dE = Pm.vq_bwd_codebook(dEh, E.detach(), normalize) if want_dE else None
+        return dz, dE, None, None
+
+
+class VQLookupFn(Function):
+    """Lookup only (VectorQuantizer.encode, layers_vq.py:35-58; the EMA twin :236-252)."""
+
+    @staticmethod
+    def forward(ctx, z, E, normalize):
+        z = z.contiguous()
+        e_hat, e_pl, e_sq = Pm.vq_prep_codebook(E.detach(), normalize, False)
+        zn, zpl, z_sq, _ = Pm.vq_prep_z(z, normalize)
+        idx = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
+        ctx.mark_non_differentiable(idx)
+        return idx
+
+    @staticmethod
+    def backward(ctx, _g):
+        return None, None, None
+
+
+class EMAVQFn(Function):
+    """Lookup + gather + commitment loss of EMAVectorQuantizer.forward (layers_vq.py:285-308).
+    Bug-compatible with the reference: for the scalar reductions the quantised output carries
+    NO gradient; only z_enc_loss reaches z.  Returns (z_vq, z_enc_loss, idx)."""
+
+    @staticmethod
+    def forward(ctx, z, embeddings, reduction):
+        z = z.contiguous()
+        B, D, T = z.shape
+        e_hat, e_pl, e_sq = Pm.vq_prep_codebook(embeddings, False, False)
+        zn, zpl, z_sq, _ = Pm.vq_prep_z(z, False)
+        idx = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
+        q, sums, counts = Pm.vq_gather(idx, e_hat, zn, None)
+        scale = _vq_scale(reduction, B, T, D)
+        scal = Pm.vq_finalize(sums, counts, B * T, scale, False, 1e-8)
+        ctx.save_for_backward(z, e_hat, idx)
+        ctx.scale = scale
+        ctx.mark_non_differentiable(q, idx)
+        return q, scal[1], idx
+
+    @staticmethod
+    def backward(ctx, _gq, g_le, _gi):
+        z, e_hat, idx = ctx.saved_tensors
+        g_le = g_le.contiguous() if g_le is not None else None
+        dz, _ = Pm.vq_bwd(None, None, g_le, idx, None, z, None, e_hat, e_hat, ctx.scale, False, False)
+        return dz, None, None
+
+
+class JitterFn(Function):
+    """Jitter.forward (layers_vq.py:353-379) with the host draws given as a source table."""
+
+    @staticmethod
+    def forward(ctx, q, src):
+        ctx.save_for_backward(src)
+        return Pm.jitter_fwd(q.contiguous(), src)
+
+    @staticmethod
+    def backward(ctx, dout):
+        (src,) = ctx.saved_tensors
+        return Pm.jitter_bwd(dout.contiguous(), src), None
+
+
+class LogLossFn(Function):
+    """log_loss (layers.py:283-296) for the scalar reductions: scale * sum 0.5*(log 2pi + (x-mu)^2)."""
+
+    @staticmethod
+    def forward(ctx, x, mu, scale):
+        x, mu = x.contiguous(), mu.contiguous()
+        ctx.save_for_backward(x, mu)
+        ctx.scale = scale
+        return Pm.logloss_fwd(x, mu, scale)[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        x, mu = ctx.saved_tensors
+        g = g.contiguous()
+        # d/dx = g*scale*(x-mu); d/dmu = -that
+        dx = Pm.logloss_bwd(x, mu, g, ctx.scale) if ctx.needs_input_grad[0] else None
+        dmu = Pm.logloss_bwd(mu, x, g, ctx.scale) if ctx.needs_input_grad[1] else None
+        return dx, dmu, None
+
+
+class EmbedFn(Function):
+    """nn.Embedding row gather of Conditions (layers.py:42-54) and its scatter-add backward."""
+
+    @staticmethod
+    def forward(ctx, table, idx):
+        ctx.save_for_backward(idx)
+        ctx.rows = table.shape[0]
+        return Pm.embed_fwd(table, idx)
+
+    @staticmethod
+    def backward(ctx, dout):
+        (idx,) = ctx.saved_tensors
+        return Pm.embed_bwd(dout, idx, ctx.rows), None

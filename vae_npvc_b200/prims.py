@@ -308,14 +308,20 @@ def vq_bwd_codebook(dE_hat, E, normalize):
     return dE
 
 
-def vq_ema_update(idx, z, mu, threshold, rand_rows, emb_sum, emb_elem, embeddings):
-    """In-place EMA update of the three buffers; -> stats (4,) [entropy, used_curr, usage, diff_emb]"""
+def vq_ema_scatter(idx, z, K):
+    """-> zsum (K,D) per-code frame sums, counts (K,) int32"""
     B, D, T = z.shape
-    K = embeddings.shape[0]
     zsum = torch.zeros((K, D), dtype=torch.float32, device=z.device)
     counts = torch.zeros((K,), dtype=torch.int32, device=z.device)
-    stats = _f32((4,), z)
-    _C.call('vq_ema_update', idx, z, B, D, T, K, mu, threshold, rand_rows, zsum, counts, emb_sum, emb_elem,
+    _C.call('vq_ema_scatter', idx, z, B, D, T, K, zsum, counts)
+    return zsum, counts
+
+
+def vq_ema_update(zsum, counts, n_frames, mu, threshold, rand_rows, emb_sum, emb_elem, embeddings):
+    """In-place EMA update of the three buffers; -> stats (4,) [entropy, used_curr, usage, diff_emb]"""
+    K, D = embeddings.shape
+    stats = _f32((4,), zsum)
+    _C.call('vq_ema_update', zsum, counts, K, D, n_frames, mu, threshold, rand_rows, emb_sum, emb_elem,
             embeddings, stats)
     return stats
 
