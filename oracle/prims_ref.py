@@ -1,0 +1,416 @@
+"""torch-CPU restatement of every primitive in vae_npvc_b200/prims.py (the C-ABI contract).
+
+TEST INFRASTRUCTURE ONLY (see oracle/__init__.py).  Two uses:
+  * tests monkeypatch this module in place of ``vae_npvc_b200.prims`` to check the host-side
+    composition (forward sequencing and every hand-written backward in functional.py) against
+    the oracle on CPU, before any GPU time is spent;
+  * on the GPU box each CUDA primitive is compared with the function of the same name here.
+The product never imports it.
+"""
+import math
+
+import torch
+import torch.nn.functional as F
+
+ACT_NONE, ACT_LRELU, ACT_RELU = 0, 1, 2
+
+
+def pitch(T):
+    return (T + 7) // 8 * 8
+
+
+def _split(x, P):
+    """fp32 -> P bf16 planes (hi[/mid/lo])."""
+    hi = x.to(torch.bfloat16)
+    if P == 1:
+        return hi.unsqueeze(0)
+    r = x - hi.float()
+    mid = r.to(torch.bfloat16)
+    lo = (r - mid.float()).to(torch.bfloat16)
+    return torch.stack([hi, mid, lo])
+
+
+def _join(data):
+    return data.float().sum(0) if data.shape[0] == 3 else data[0].float()
+
+
+class Planes:
+    __slots__ = ('data', 'P', 'B', 'C', 'T', 'Tp')
+
+    def __init__(self, data, P, B, C, T, Tp):
+        self.data, self.P, self.B, self.C, self.T, self.Tp = data, P, B, C, T, Tp
+
+    @staticmethod
+    def of(x, P):
+        B, C, T = x.shape
+        Tp = pitch(T)
+        data = torch.zeros((P, B, C, Tp), dtype=torch.bfloat16)
+        data[..., :T] = _split(x, P)
+        return Planes(data, P, B, C, T, Tp)
+
+    def value(self):
+        return _join(self.data)[..., :self.T]
+
+
+class ConvWeights:
+    __slots__ = ('wf', 'wb', 'w32', 'taps', 'Cout', 'Cin', 'transposed')
+
+    def __init__(self, wf, wb, w32, taps, Cout, Cin, transposed):
+        self.wf, self.wb, self.w32, self.taps, self.Cout, self.Cin, self.transposed = wf, wb, w32, taps, Cout, Cin, transposed
+
+
+def _act(x, act):
+    if act == ACT_LRELU:
+        return torch.where(x >= 0, x, 0.2 * x)
+    if act == ACT_RELU:
+        return torch.relu(x)
+    return x
+
+
+def _act_grad(x, act):
+    if act == ACT_LRELU:
+        return torch.where(x >= 0, torch.ones_like(x), torch.full_like(x, 0.2))
+    if act == ACT_RELU:
+        return (x > 0).to(x.dtype)
+    return torch.ones_like(x)
+
+
+# ---- weight norm -----------------------------------------------------------------------------
+def wn_prepare(v, g, transposed, P, need_wf=True, need_wb=True, need_w32=False):
+    v = v.detach()
+    d0, d1, k = v.shape
+    w = v if g is None else v * (g.detach().view(d0, 1, 1) / v.pow(2).sum(dim=(1, 2), keepdim=True).sqrt())
+    # conv weight in (co, ci, tap) form
+    wc = w.transpose(0, 1).flip(2) if transposed else w
+    co, ci = wc.shape[0], wc.shape[1]
+    wf = wb = None
+    if need_wf:
+        wf = torch.zeros((P, k, co, pitch(ci)), dtype=torch.bfloat16)
+        wf[..., :ci] = _split(wc.permute(2, 0, 1).contiguous(), P)             # [tap][co][ci]
+    if need_wb:
+        wb = torch.zeros((P, k, ci, pitch(co)), dtype=torch.bfloat16)
+        wb[..., :co] = _split(wc.flip(2).permute(2, 1, 0).contiguous(), P)     # [k-1-tap][ci][co]
+    return ConvWeights(wf, wb, w.clone() if need_w32 else None, k, co, ci, bool(transposed))
+
+
+def wn_backward(dw, v, g):
+    v, g = v.detach(), g.detach()
+    d0 = v.shape[0]
+    ss = v.pow(2).sum(dim=(1, 2), keepdim=True)
+    norm = ss.sqrt()
+    dot = (dw * v).sum(dim=(1, 2), keepdim=True)
+    gi = g.view(d0, 1, 1)
+    return gi / norm * dw - gi * dot / (norm * ss) * v, (dot / norm).view_as(g)
+
+
+# ---- GEMM-shaped -----------------------------------------------------------------------------
+def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False):
+    x = x_pl.value()
+    Cin = x_pl.C
+    w = _join(w_op)[:, :Cout, :Cin].permute(1, 2, 0).contiguous()               # (co, ci, tap)
+    r = F.conv1d(x, w, None, padding=(taps - 1) // 2 * dil, dilation=dil)
+    if bias is not None:
+        b = bias.detach()
+        r = r + (b.view(-1, Cout, 1) if bias_bstride else b.view(1, Cout, 1))
+    if residual is not None:
+        r = r + residual
+    if out is not None:
+        if accumulate:
+            out += r
+        else:
+            out.copy_(r)
+        return out
+    return r
+
+
+def conv_wgrad(dy_pl, u_pl, taps, dil, transposed):
+    dy, u = dy_pl.value(), u_pl.value()
+    pad = (taps - 1) // 2 * dil
+    up = F.pad(u, (pad, pad))
+    T = dy.shape[2]
+    dw = torch.stack([torch.einsum('bot,bit->oi', dy, up[:, :, j * dil:j * dil + T]) for j in range(taps)], dim=2)
+    return dw.transpose(0, 1).flip(2).contiguous() if transposed else dw
+
+
+# ---- planes ----------------------------------------------------------------------------------
+def make_planes(x, P, scale=1.0, act=ACT_NONE, want_id=True, want_act=False):
+    v = x.detach() * scale
+    return (Planes.of(v, P) if want_id else None, Planes.of(_act(v, act), P) if want_act else None)
+
+
+def concat_planes(xa, xb, P):
+    return Planes.of(torch.cat([xa, xb], dim=1), P)
+
+
+# ---- forward elementwise ---------------------------------------------------------------------
+def gn_stats(h, groups, eps=1e-5):
+    B = h.shape[0]
+    hg = h.reshape(B, groups, -1)
+    mean = hg.mean(dim=2)
+    var = (hg - mean.unsqueeze(2)).pow(2).mean(dim=2)
+    return mean, torch.rsqrt(var + eps)
+
+
+def _xhat(h, mean, rstd, groups):
+    B, C, T = h.shape
+    return ((h.reshape(B, groups, -1) - mean.view(B, groups, 1)) * rstd.view(B, groups, 1)).reshape(B, C, T)
+
+
+def enc_out(h, s, mean, rstd, gamma, beta, P, want_y=True, want_ypl=True, want_upl=True):
+    y = _xhat(h, mean, rstd, 1) * gamma.detach().view(1, -1, 1) + beta.detach().view(1, -1, 1)
+    if s is not None:
+        y = y + s
+    return (y if want_y else None, Planes.of(y, P) if want_ypl else None,
+            Planes.of(_act(y, ACT_LRELU), P) if want_upl else None)
+
+
+def dec_gate(a, mean, rstd, gamma, beta, P):
+    C = a.shape[1] // 2
+    hn = _xhat(a, mean, rstd, 2) * gamma.detach().view(1, -1, 1) + beta.detach().view(1, -1, 1)
+    return Planes.of(torch.tanh(hn[:, :C]) * torch.sigmoid(hn[:, C:]), P)
+
+
+def dec_out(r, x, S, P, skip_sum=None, first=True, want_x=True, want_xpl=True):
+    C = x.shape[1]
+    xo = r[:, :C] + x
+    if S > 0:
+        if skip_sum is None:
+            skip_sum = r[:, C:].clone()
+        elif first:
+            skip_sum.copy_(r[:, C:])
+        else:
+            skip_sum += r[:, C:]
+    return (xo if want_x else None, Planes.of(xo, P) if want_xpl else None, skip_sum)
+
+
+# ---- backward elementwise --------------------------------------------------------------------
+def gn_bwd_rows(dn, h, mean, rstd, groups):
+    xh = _xhat(h, mean, rstd, groups)
+    return torch.stack([dn.sum(2), (dn * xh).sum(2), xh.sum(2)], dim=2)
+
+
+def _gate_dn(dg, a, mean, rstd, gamma, beta):
+    C = a.shape[1] // 2
+    xh = _xhat(a, mean, rstd, 2)
+    hn = xh * gamma.detach().view(1, -1, 1) + beta.detach().view(1, -1, 1)
+    th, sg = torch.tanh(hn[:, :C]), torch.sigmoid(hn[:, C:])
+    return torch.cat([dg * sg * (1 - th * th), dg * th * sg * (1 - sg)], dim=1), xh
+
+
+def gate_bwd_rows(dg, a, mean, rstd, gamma, beta):
+    dn, xh = _gate_dn(dg, a, mean, rstd, gamma, beta)
+    return torch.stack([dn.sum(2), (dn * xh).sum(2), xh.sum(2)], dim=2)
+
+
+def gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums=False):
+    B, C, _ = R.shape
+    gm = gamma.detach().view(1, C)
+    dgamma, dbeta = R[:, :, 1].sum(0), R[:, :, 0].sum(0)
+    cg = C // groups
+    S = torch.stack([(gm * R[:, :, 0]).view(B, groups, cg).sum(2), (gm * R[:, :, 1]).view(B, groups, cg).sum(2)], dim=2)
+    bsum = csum = None
+    if want_sums:
+        n = cg * T
+        S0 = S[:, :, 0].repeat_interleave(cg, dim=1)
+        S1 = S[:, :, 1].repeat_interleave(cg, dim=1)
+        rs = rstd.repeat_interleave(cg, dim=1)
+        bsum = rs * (gm * R[:, :, 0] - T * S0 / n - R[:, :, 2] * S1 / n)
+        csum = bsum.sum(0)
+    return dgamma, dbeta, S, bsum, csum
+
+
+def _gn_dpre(dn, xh, rstd, gamma, S, groups):
+    B, C, T = dn.shape
+    cg = C // groups
+    n = cg * T
+    S0 = S[:, :, 0].repeat_interleave(cg, dim=1).view(B, C, 1)
+    S1 = S[:, :, 1].repeat_interleave(cg, dim=1).view(B, C, 1)
+    rs = rstd.repeat_interleave(cg, dim=1).view(B, C, 1)
+    return rs * (gamma.detach().view(1, C, 1) * dn - S0 / n - xh * S1 / n)
+
+
+def gn_bwd_apply(dn, h, mean, rstd, gamma, S, groups, P, want_dn_planes=False):
+    dpre = _gn_dpre(dn, _xhat(h, mean, rstd, groups), rstd, gamma, S, groups)
+    return Planes.of(dpre, P), (Planes.of(dn, P) if want_dn_planes else None)
+
+
+def gate_bwd_apply(dg, a, mean, rstd, gamma, beta, S, P):
+    dn, xh = _gate_dn(dg, a, mean, rstd, gamma, beta)
+    return Planes.of(_gn_dpre(dn, xh, rstd, gamma, S, 2), P)
+
+
+def act_bwd_add(du, c, add, act, scale=1.0):
+    out = scale * du * _act_grad(c * scale, act)
+    return out + add if add is not None else out
+
+
+def channel_sum(x, out=None):
+    r = x.sum(dim=(0, 2))
+    if out is not None:
+        out.copy_(r)
+        return out
+    return r
+
+
+# ---- speaker conditioning --------------------------------------------------------------------
+def embed_fwd(table, idx):
+    return table.detach()[idx]
+
+
+def embed_bwd(dout, idx, num_rows):
+    dim = dout.shape[-1]
+    return torch.zeros(num_rows, dim).index_add_(0, idx.reshape(-1), dout.reshape(-1, dim))
+
+
+def linear_fwd(y, W, bias, bias2=None):
+    p = y @ W.t()
+    if bias is not None:
+        p = p + bias.detach()
+    if bias2 is not None:
+        p = p + bias2.detach()
+    return p
+
+
+def linear_bwd(dp, y, W, dy=None):
+    dW = dp.t() @ y
+    d = dp @ W
+    if dy is not None:
+        dy += d
+        return dW, dy
+    return dW, d
+
+
+# ---- vector quantiser ------------------------------------------------------------------------
+def vq_prep_codebook(E, normalize, inplace_renorm=True):
+    K, D = E.shape
+    if normalize:
+        if inplace_renorm:
+            E.mul_(1.0 / E.norm(dim=1, keepdim=True))
+        e_hat = E / E.norm(dim=1, keepdim=True)
+    else:
+        e_hat = E.clone()
+    e_pl = torch.zeros((3, K, pitch(D)), dtype=torch.bfloat16)
+    e_pl[..., :D] = _split(e_hat, 3)
+    return e_hat, e_pl, e_hat.pow(2).sum(1)
+
+
+def _frames(z):
+    B, D, T = z.shape
+    return z.transpose(1, 2).reshape(B * T, D)
+
+
+def vq_prep_z(z, normalize):
+    z = z.detach()
+    zf = _frames(z)
+    nrm = zf.norm(dim=1)
+    zn = z / z.norm(dim=1, keepdim=True) if normalize else z.clone()
+    return zn, Planes.of(zn, 3), _frames(zn).pow(2).sum(1), nrm
+
+
+def vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq):
+    d = (z_sq.view(-1, 1) + e_sq.view(1, -1)) - 2 * (_frames(zn) @ e_hat.t())
+    return torch.argmin(d, dim=1)
+
+
+def vq_gather(idx, e_hat, zn, z, want_q=True, want_stats=True):
+    B, D, T = zn.shape
+    q = e_hat[idx].view(B, T, D).transpose(1, 2).contiguous()
+    sums = counts = None
+    if want_stats:
+        s1 = (zn - z).pow(2).sum() if z is not None else torch.zeros(())
+        sums = torch.stack([(q - zn).pow(2).sum(), s1])
+        counts = torch.bincount(idx, minlength=e_hat.shape[0]).to(torch.int32)
+    return (q if want_q else None), sums, counts
+
+
+def vq_finalize(sums, counts, N, scale, normalize, eps):
+    p = counts.float() / N
+    return torch.stack([sums[0] * scale, (sums[0] + (sums[1] if normalize else 0.0)) * scale,
+                        torch.exp(-(p * torch.log(p + eps)).sum())])
+
+
+def vq_bwd(g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, E, scale, normalize, want_dE=True):
+    B, D, T = zn.shape
+    q = e_hat[idx].view(B, T, D).transpose(1, 2)
+    glq = (float(g_lq) if g_lq is not None else 0.0) * 2 * scale
+    gle = (float(g_le) if g_le is not None else 0.0) * 2 * scale
+    go = g_out if g_out is not None else torch.zeros_like(zn)
+    dEh = None
+    if want_dE:
+        dEh = torch.zeros_like(e_hat).index_add_(0, idx, _frames(glq * (q - zn)))
+    if not normalize:
+        return go + gle * (zn - q), dEh
+    dzn = go + gle * ((zn - q) + (zn - z))
+    dot = (zn * dzn).sum(1, keepdim=True)
+    dz = (dzn - zn * dot) / z_norm.view(B, 1, T) - gle * (zn - z)
+    return dz, dEh
+
+
+def vq_bwd_codebook(dE_hat, E, normalize):
+    if not normalize:
+        return dE_hat.clone()
+    ss = E.pow(2).sum(1, keepdim=True)
+    dot = (E * dE_hat).sum(1, keepdim=True)
+    return (dE_hat - E * dot / ss) / ss.sqrt()
+
+
+def vq_ema_scatter(idx, z, K):
+    zf = _frames(z.detach())
+    return torch.zeros(K, zf.shape[1]).index_add_(0, idx, zf), torch.bincount(idx, minlength=K).to(torch.int32)
+
+
+def vq_ema_update(zsum, counts, n_frames, mu, threshold, rand_rows, emb_sum, emb_elem, embeddings):
+    K, D = embeddings.shape
+    c = counts.float()
+    emb_sum.mul_(mu).add_((1 - mu) * zsum)
+    emb_elem.mul_(mu).add_((1 - mu) * c)
+    alive = (emb_elem >= threshold).view(K, 1)
+    new = torch.where(alive, emb_sum / emb_elem.view(K, 1), rand_rows)
+    diff = (new - embeddings).norm() / math.sqrt(K * D)
+    embeddings.copy_(new)
+    p = c / n_frames
+    return torch.stack([torch.exp(-(p * torch.log(p + 1e-8)).sum()), (c >= threshold).sum().float(),
+                        alive.sum().float(), diff])
+
+
+def vq_frame_rows(z, perm, K):
+    zf = _frames(z.detach())
+    return zf[perm[:K] % zf.shape[0]].clone()
+
+
+def jitter_fwd(x, src):
+    return x[:, :, src]
+
+
+def jitter_bwd(dout, src):
+    keep = (src == torch.arange(src.numel())).view(1, 1, -1)
+    return torch.where(keep, dout, torch.zeros_like(dout))
+
+
+# ---- losses / optimiser ----------------------------------------------------------------------
+LOG_2PI = math.log(2.0 * math.pi)
+
+
+def logloss_fwd(xhat, x, scale=1.0):
+    return (scale * (0.5 * (LOG_2PI + (xhat - x).pow(2))).sum()).view(1)
+
+
+def logloss_bwd(xhat, x, g, scale):
+    return (float(g) if g is not None else 1.0) * scale * (xhat - x)
+
+
+def sqnorm(g, acc):
+    acc += g.pow(2).sum()
+    return acc
+
+
+def adam_step(p, g, m, v, sqn, max_norm, lr, beta1, beta2, eps, state, step_size, gamma):
+    s = float(state[0])
+    t = s + 1
+    lr_t = lr * (gamma ** math.floor(s / step_size) if step_size > 0 else 1.0)
+    coef = min(1.0, max_norm / (math.sqrt(float(sqn[0])) + 1e-6)) if (max_norm > 0 and sqn is not None) else 1.0
+    gi = g * coef
+    m.mul_(beta1).add_((1 - beta1) * gi)
+    v.mul_(beta2).add_((1 - beta2) * gi * gi)
+    p.sub_((lr_t / (1 - beta1 ** t)) * m / (v.sqrt() / math.sqrt(1 - beta2 ** t) + eps))
+    state[0] += 1
