@@ -193,7 +193,8 @@ int vnb_logloss_bwd(const float* xhat, const float* x, const float* g, int64_t n
 /* ---- optimiser (trainer/basic.py:62-72): global L2 norm -> clip coef -> Adam, on flat buffers */
 /* acc[0] += sum g^2 (zeroed by caller) */
 int vnb_sqnorm(const float* g, int64_t n, float* acc, void* stream);
-/* state[0] = step count (float), updated on device; lr_base*gamma^floor(step/step_size);
+/* state[0] = Adam step count, state[1] = StepLR step count (floats, both incremented on device);
+ * lr = lr*gamma^floor(state[1]/step_size) (step_size<=0: constant);
  * clip: coef = min(1, max_norm/(sqrt(sqn[0])+1e-6)) when max_norm > 0 */
 int vnb_adam_step(float* p, const float* g, float* m, float* v, int64_t n, const float* sqn,
                   float max_norm, float lr, float beta1, float beta2, float eps, float* state,

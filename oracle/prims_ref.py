@@ -405,8 +405,8 @@ def sqnorm(g, acc):
 
 
 def adam_step(p, g, m, v, sqn, max_norm, lr, beta1, beta2, eps, state, step_size, gamma):
-    s = float(state[0])
-    t = s + 1
+    t = float(state[0]) + 1
+    s = float(state[1])
     lr_t = lr * (gamma ** math.floor(s / step_size) if step_size > 0 else 1.0)
     coef = min(1.0, max_norm / (math.sqrt(float(sqn[0])) + 1e-6)) if (max_norm > 0 and sqn is not None) else 1.0
     gi = g * coef
@@ -414,3 +414,4 @@ def adam_step(p, g, m, v, sqn, max_norm, lr, beta1, beta2, eps, state, step_size
     v.mul_(beta2).add_((1 - beta2) * gi * gi)
     p.sub_((lr_t / (1 - beta1 ** t)) * m / (v.sqrt() / math.sqrt(1 - beta2 ** t) + eps))
     state[0] += 1
+    state[1] += 1

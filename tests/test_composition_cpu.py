@@ -203,3 +203,52 @@ def test_remove_weight_norm_keeps_outputs(cpu_prims, golden_meta):
         assert 'encoder.encode.0.weight' in m.state_dict() and 'encoder.encode.0.weight_g' not in m.state_dict()
         b = m.infer((x, y))
     assert rel_err(b, a) < TOL
+
+
+def _trainer(cpu_prims, monkeypatch, arch, extra):
+    import vae_npvc_b200.trainer.basic as TB
+    monkeypatch.setattr(TB, 'Pm', prims_ref)
+    cfg = dict(arch)
+    cfg.update(model_type='vae_npvc_b200.model.vqvae', device='cpu', cuda_graph=False, precision='fp32')
+    cfg.update(extra)
+    return TB.Trainer(cfg)
+
+
+def test_trainer_three_clipped_adam_steps(cpu_prims, monkeypatch, golden_meta, tmp_path):
+    """trainer/basic.py:55-79 semantics: clip_grad_norm_ -> Adam(0.5, 0.999) -> StepLR, on the flat
+    buffers, against parameters recorded from the reference after 3 steps."""
+    case = golden_meta['cases']['small_train3']
+    arch = case['arch']
+    tr = _trainer(cpu_prims, monkeypatch, arch, dict(
+        learning_rate=case['lr'], max_grad_norm=case['max_grad_norm'], lr_scheduler='StepLR',
+        lr_param={'step_size': case['step_size'], 'gamma': case['gamma'], 'last_epoch': -1}))
+    tr.model.load_state_dict(synth.synthetic_state_dict(arch, 777))
+    it = 0
+    for i, seed in enumerate(case['batch_seeds']):
+        x, y = synth.synthetic_batch(arch, case['B'], case['T'], seed)
+        it, detail = tr.train_step([x, y], it)
+        assert it == i + 1 and all(isinstance(v, float) for v in detail.values())
+        for k, v in case['losses'][i].items():
+            assert abs(detail[k] - v) <= TOL * max(1.0, abs(v)), (i, k)
+    gold = load_npz('small_train3')
+    params = dict(tr.model.named_parameters())
+    for key, p in gold.items():
+        assert rel_err(params[key[6:]], p) < TOL, key
+    # parameters are views of one flat buffer; checkpoint round trip in the reference's format
+    assert all(p.data_ptr() >= tr._flat_p.data_ptr() for p in tr._params)
+    ck = tmp_path / 'iter.3'
+    tr.save_checkpoint(str(ck))
+    data = torch.load(str(ck), map_location='cpu')
+    assert set(data) == {'model', 'optimizer', 'iteration'} and data['iteration'] == 3
+    assert set(data['optimizer']) == {'state', 'param_groups'} and len(data['optimizer']['state']) == len(tr._params)
+    assert float(data['optimizer']['state'][0]['step']) == 3.0
+    tr2 = _trainer(cpu_prims, monkeypatch, arch, dict(learning_rate=case['lr'], max_grad_norm=case['max_grad_norm']))
+    assert tr2.load_checkpoint(str(ck)) == 3
+    assert torch.equal(tr2._flat_p, tr._flat_p) and torch.equal(tr2.optimizer.m, tr.optimizer.m)
+    assert float(tr2.optimizer.state[0]) == 3.0 and float(tr2.optimizer.state[1]) == 0.0
+    # validation leaves the model in train mode; the only write is the reference's own in-place
+    # codebook renormalisation, which also runs in eval mode (layers_vq.py:96)
+    before = tr._flat_p.clone()
+    x, y = synth.synthetic_batch(arch, case['B'], case['T'], 5)
+    out = tr.valid([[x, y], [x, y]])
+    assert tr.model.training and rel_err(tr._flat_p, before) < 1e-6 and len(out['Total']) == 2

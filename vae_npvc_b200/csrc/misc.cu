@@ -94,8 +94,8 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
                                                    int step_size, float gamma) {
     __shared__ float sh[3];
     if (threadIdx.x == 0) {
-        const double s = (double)state[0];                       // optimiser steps already taken
-        const double t = s + 1.0;
+        const double t = (double)state[0] + 1.0;                 // Adam step (bias correction)
+        const double s = (double)state[1];                       // StepLR steps taken so far
         double lr_t = (double)lr;
         if (step_size > 0) lr_t *= pow((double)gamma, floor(s / (double)step_size));
         const double bc1 = 1.0 - pow((double)beta1, t), bc2 = 1.0 - pow((double)beta2, t);
@@ -117,7 +117,10 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
     }
 }
 
-__global__ void adam_tick_kernel(float* state) { state[0] += 1.f; }
+__global__ void adam_tick_kernel(float* state) {
+    state[0] += 1.f;
+    state[1] += 1.f;
+}
 
 static inline int flat_grid(int64_t n) {
     int64_t g = (n + 255) / 256;
