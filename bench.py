@@ -1,0 +1,262 @@
+"""Benchmark of the VQ-VAE training step (BASELINE.json metric: train frames/s, fwd+bwd+optimiser).
+
+    python bench.py --gpus 1 --steps 20 --warmup 5                  # our CUDA path, one B200
+    torchrun --nproc-per-node N ... bench.py --gpus N ...           # batch-sharded DP, weak scaling
+    python bench.py --impl reference ...                            # the reference's CPU path (oracle port)
+
+Prints ONE JSON line on rank 0.  A "step" = zero-grad, forward, backward, [all-reduce], clip, Adam,
+StepLR over one synthetic batch of 16 x 128 frames PER GPU of the VCC2020-shape model
+(80-dim mel, C512, codebook 512 x 64).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+B_PER_GPU, T_FRAMES = 16, 128
+FLOP_PER_FRAME = 178_757_632          # algorithmic fwd+bwd FLOP/frame, SURVEY.md section 8(d)
+
+
+def workload_arch():
+    from oracle import synth
+    return synth.arch_config(X=80, C=512, D=64, K=512, Y=128, S=128, y_num=117, stacks=10, use_ema=False,
+                             embed_norm=True)
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d['hbm_gbs'], tf_burst=d['bf16_tflops'], tf_sus=d.get('bf16_tflops_sustained', d['bf16_tflops']),
+                    src='measured')
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sus=1400.0, src='fallback')
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi SM clock / throttle-reason samples during the timed region."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                                      '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
+                f = [s.strip() for s in out.strip().split(',')]
+                if len(f) >= 6:
+                    self.rows.append(f)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        if not self.rows:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['unsampled']}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith('active') for r in self.rows)]
+        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': float(self.rows[0][1]), 'reasons': reasons,
+                'samples': len(self.rows)}
+
+
+def cpu_oracle_step_rate(steps, warmup, threads=None):
+    """The reference's CPU path restated (oracle port): full train step, fp32, torch CPU."""
+    from oracle import synth
+    from oracle import vqvae_oracle as O
+    arch = workload_arch()
+    cores = threads or os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = synth.synthetic_state_dict(arch, 777)
+    params = O.params_from_state_dict(sd)
+    opt = O.AdamState(O.trainable_names(params), lr=1e-3, step_size=100000, gamma=0.5)
+    x, y = synth.synthetic_batch(arch, B_PER_GPU, T_FRAMES, 777)
+    for _ in range(warmup):
+        O.train_step(params, arch, opt, x, y, max_grad_norm=10)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        O.train_step(params, arch, opt, x, y, max_grad_norm=10)
+    dt = (time.perf_counter() - t0) / steps
+    return B_PER_GPU * T_FRAMES / dt, dt, cores
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    steps, warm = max(1, min(args.steps, 12)), max(1, min(args.warmup, 3))
+    fps, dt, cores = cpu_oracle_step_rate(steps, warm)
+    line = {
+        'impl': 'reference', 'metric': 'train frames/sec (fwd+bwd+optimizer)', 'value': fps, 'unit': 'frames/s',
+        'n_gpus': args.gpus, 'steps': steps, 'warmup': warm, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': 'VQ-VAE VCC2020 shape: 80-mel, 16x128 frames, C512, codebook 512x64, fp32 on host CPU'},
+        'cpu_baseline': {'value': fps, 'unit': 'frames/s', 'cores': cores, 'kind': 'port',
+                         'sample': '%d full train steps of 16x128 frames (oracle restatement of the reference '
+                                   'Model + trainer/basic.py step, torch CPU fp32)' % steps},
+        'e2e': {'value': fps, 'unit': 'frames/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line))
+
+
+def time_dominant_kernel(P, iters=20):
+    """CUDA-event time of the step's dominant kernel in isolation: the decoder block's k=3
+    ConvTranspose as a GEMM (Cout=1024, Cin=512, 3 taps, 16x128 frames) - 20 of the step's
+    ~110 GEMM launches have this shape or its data-/weight-gradient twin, ~2/3 of all FLOPs."""
+    from vae_npvc_b200 import prims as Pm
+    B, T, Cin, Cout, taps = B_PER_GPU, T_FRAMES, 512, 1024, 3
+    x = torch.randn(B, Cin, T, device='cuda')
+    v = torch.randn(Cin, Cout, taps, device='cuda') * 0.02
+    W = Pm.wn_prepare(v, None, True, P)
+    xpl = Pm.make_planes(x, P)[0]
+    out = torch.empty(B, Cout, T, device='cuda')
+    flush = torch.empty(256 * 1024 * 1024 // 4, device='cuda')          # > 126 MB L2
+    for _ in range(3):
+        Pm.conv_fwd(xpl, W.wf, taps, 1, Cout, None, 0, None, out)
+    times = []
+    for _ in range(iters):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        Pm.conv_fwd(xpl, W.wf, taps, 1, Cout, None, 0, None, out)
+        e1.record()
+        e1.synchronize()
+        times.append(e0.elapsed_time(e1) * 1e-3)
+    dt = sum(times) / len(times)
+    pairs = 1 if P == 1 else 6
+    flops = 2.0 * B * T * Cout * Cin * taps            # algorithmic (the fp32-faithful mode executes 6x)
+    return dt, flops, flops * pairs
+
+
+def run_ours(args, rank, world):
+    from vae_npvc_b200 import _C
+    from vae_npvc_b200.trainer.basic import Trainer
+    from oracle import synth
+    _C.require_cuda()
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    arch = workload_arch()
+    cfg = dict(arch)
+    warm = max(3, args.warmup)
+    cfg.update(model_type='vae_npvc_b200.model.vqvae', precision=args.precision, cuda_graph=not args.no_graph,
+               graph_warmup=min(3, warm - 1), learning_rate=1e-3, max_grad_norm=10, lr_scheduler='StepLR',
+               lr_param={'step_size': 100000, 'gamma': 0.5, 'last_epoch': -1})
+    torch.manual_seed(777)
+    tr = Trainer(cfg)
+    tr.model.load_state_dict(synth.synthetic_state_dict(arch, 777))       # same weights on every rank
+    x, y = synth.synthetic_batch(arch, B_PER_GPU, T_FRAMES, 777 + rank)   # each rank its own shard
+    xh, yh = x.pin_memory(), y.pin_memory()
+    xd, yd = x.cuda(), y.cuda()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(warm):
+        tr.train_step_device(xd, yd)
+    barrier()
+    # ---- device-resident timing: CUDA events on the launching stream ----
+    sampler = ClockSampler(local)
+    sampler.start()
+    _C.launch_count_reset()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        keys, scal = tr.train_step_device(xd, yd)
+    e1.record()
+    barrier()
+    dt = e0.elapsed_time(e1) * 1e-3
+    eager_launches = _C.launch_count()
+    # ---- end to end through Trainer.train_step: pinned host batch in, python floats out ----
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        it, detail = tr.train_step([xh, yh], i)
+    torch.cuda.synchronize()
+    dt_e2e = time.perf_counter() - t0
+    clocks = sampler.stop()
+    tmax = torch.tensor([dt, dt_e2e], device='cuda', dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    dt, dt_e2e = float(tmax[0]), float(tmax[1])
+    on_graph = tr.last_step_on_graph
+    per_step = tr.launches_per_step if on_graph else eager_launches // max(1, args.steps)
+    if rank == 0:
+        frames = B_PER_GPU * T_FRAMES * world * args.steps
+        value, e2e = frames / dt, frames / dt_e2e
+        pk = peaks()
+        P = 1 if args.precision == 'bf16' else 3
+        kdt, kflops, kexec = time_dominant_kernel(P)
+        line = {
+            'metric': 'train frames/sec (fwd+bwd+optimizer)', 'value': value, 'unit': 'frames/s', 'n_gpus': world,
+            'steps': args.steps, 'warmup': warm, 'ms_per_step': dt / args.steps * 1e3, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16' if P == 1 else 'f32 (3xbf16 split planes)',
+            'data': 'synthetic',
+            'config': {'workload': 'VQ-VAE VCC2020 shape (BASELINE configs[1]): 80-mel, 16x128 frames per GPU, C512, '
+                                   '10+10 blocks, codebook 512x64 (use_ema false, embed_norm true), Adam+clip+StepLR',
+                       'frames_per_gpu_per_step': B_PER_GPU * T_FRAMES, 'parallelism': 'dp%d' % world,
+                       'cuda_graph': bool(on_graph),
+                       'l2': 'no explicit flush: each step streams params+grads+Adam moments+operand planes '
+                             '(~0.7 GB) > 126 MB L2; the isolated-kernel timing flushes L2 with a 256 MB write',
+                       'step_roofline_frac_tensor': value * FLOP_PER_FRAME / (world * pk['tf_sus'] * 1e12)},
+            'clocks': clocks,
+            'e2e': {'value': e2e, 'unit': 'frames/s', 'h2d_bytes_per_step': x.numel() * 4 + y.numel() * 8,
+                    'd2h_bytes_per_step': 4 * len(detail)},
+            'gpu_launches': int(per_step * args.steps),
+            'roofline': {'bound': 'tensor', 'kernel': 'conv_fwd Cout1024 Cin512 k3 (decoder conv_in), backend %s'
+                         % {0: 'auto', 1: 'simt', 2: 'tc'}[_C.get_backend()],
+                         'achieved': kflops / kdt / 1e12, 'peak': pk['tf_burst'], 'unit': 'TFLOP/s',
+                         'frac': kflops / kdt / 1e12 / pk['tf_burst'], 'traffic': None,
+                         'executed_tflops': kexec / kdt / 1e12, 'peak_source': pk['src'], 'kernel_ms': kdt * 1e3},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            fps, cdt, cores = cpu_oracle_step_rate(8, 2)
+            line['cpu_baseline'] = {'value': fps, 'unit': 'frames/s', 'cores': cores, 'kind': 'port',
+                                    'sample': '8 full train steps of 16x128 frames (oracle restatement of the '
+                                              'reference Model + trainer step, torch CPU fp32), %.0f ms/step' % (cdt * 1e3)}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'])
+    ap.add_argument('--no-graph', action='store_true')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    rank, world = int(os.environ.get('RANK', 0)), int(os.environ.get('WORLD_SIZE', 1))
+    if args.impl == 'reference':
+        run_reference(args, rank)
+    else:
+        run_ours(args, rank, world)
+
+
+if __name__ == '__main__':
+    main()

@@ -125,6 +125,7 @@ class Trainer(object):
         self._graphs = {}                 # (B, X, T) -> captured step
         self._eager_steps = 0
         self.last_step_on_graph = False
+        self.launches_per_step = 0
 
     # ---- flat parameter / gradient buffers -------------------------------------------------------
     def _flatten(self):
@@ -164,10 +165,13 @@ class Trainer(object):
         return keys, scal
 
     def _capture(self, x, y):
+        from .. import _C
         static_x, static_y = x.clone(), y.clone()
         g = torch.cuda.CUDAGraph()
+        n0 = _C.launch_count()
         with torch.cuda.graph(g):
             keys, scal = self._step_body(static_x, static_y)
+        self.launches_per_step = int(_C.launch_count() - n0)      # our kernels inside one replay
         return dict(graph=g, x=static_x, y=static_y, keys=keys, scal=scal)
 
     def train_step_device(self, x, y):
