@@ -197,7 +197,7 @@ int vnb_sqnorm(const float* g, int64_t n, float* acc, void* stream);
  * lr = lr*gamma^floor(state[1]/step_size) (step_size<=0: constant);
  * clip: coef = min(1, max_norm/(sqrt(sqn[0])+1e-6)) when max_norm > 0 */
 int vnb_adam_step(float* p, const float* g, float* m, float* v, int64_t n, const float* sqn,
-                  float max_norm, float lr, float beta1, float beta2, float eps, float* state,
+                  float max_norm, float lr, double beta1, double beta2, float eps, float* state,
                   int step_size, float gamma, void* stream);
 
 #ifdef __cplusplus

@@ -27,7 +27,8 @@ _PTR_DTYPES = {
     'int*': (torch.int32,), 'const int*': (torch.int32,),
     'void*': None, 'const void*': None,
 }
-_SCALARS = {'int': ctypes.c_int, 'int64_t': ctypes.c_int64, 'float': ctypes.c_float, 'size_t': ctypes.c_size_t}
+_SCALARS = {'int': ctypes.c_int, 'int64_t': ctypes.c_int64, 'float': ctypes.c_float, 'double': ctypes.c_double,
+            'size_t': ctypes.c_size_t}
 _RET = {'int': ctypes.c_int, 'int64_t': ctypes.c_int64, 'void': None, 'const char*': ctypes.c_char_p}
 
 
@@ -106,7 +107,7 @@ def call(name, *args):
     for (ctype, pname), v in zip(params, args):
         if ctype.endswith('*'):
             cargs.append(_ptr(full, pname, ctype, v))
-        elif ctype == 'float':
+        elif ctype in ('float', 'double'):
             cargs.append(float(v))
         else:
             cargs.append(int(v))

@@ -89,16 +89,19 @@ __global__ void __launch_bounds__(256) sqnorm_kernel(const float* __restrict__ g
 
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                    float* __restrict__ m, float* __restrict__ v, int64_t n,
-                                                   const float* __restrict__ sqn, float max_norm, float lr, float beta1,
-                                                   float beta2, float eps, const float* __restrict__ state,
-                                                   int step_size, float gamma) {
+                                                   const float* __restrict__ sqn, float max_norm, float lr,
+                                                   double beta1d, double beta2d, float eps,
+                                                   const float* __restrict__ state, int step_size, float gamma) {
     __shared__ float sh[3];
+    // like torch.optim.Adam: 1 - beta is formed in double, then used in fp32 arithmetic
+    const float beta1 = (float)beta1d, beta2 = (float)beta2d;
+    const float omb1 = (float)(1.0 - beta1d), omb2 = (float)(1.0 - beta2d);
     if (threadIdx.x == 0) {
         const double t = (double)state[0] + 1.0;                 // Adam step (bias correction)
         const double s = (double)state[1];                       // StepLR steps taken so far
         double lr_t = (double)lr;
         if (step_size > 0) lr_t *= pow((double)gamma, floor(s / (double)step_size));
-        const double bc1 = 1.0 - pow((double)beta1, t), bc2 = 1.0 - pow((double)beta2, t);
+        const double bc1 = 1.0 - pow(beta1d, t), bc2 = 1.0 - pow(beta2d, t);
         float coef = 1.f;
         if (max_norm > 0.f && sqn) coef = fminf(1.f, max_norm / (sqrtf(sqn[0]) + 1e-6f));
         sh[0] = (float)(lr_t / bc1);
@@ -109,8 +112,8 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
     const float step = sh[0], rs2 = sh[1], coef = sh[2];
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         const float gi = g[i] * coef;
-        const float mi = beta1 * m[i] + (1.f - beta1) * gi;
-        const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+        const float mi = beta1 * m[i] + omb1 * gi;
+        const float vi = beta2 * v[i] + omb2 * gi * gi;
         m[i] = mi;
         v[i] = vi;
         p[i] -= step * mi / (sqrtf(vi) * rs2 + eps);
@@ -191,7 +194,7 @@ extern "C" int vnb_sqnorm(const float* g, int64_t n, float* acc, void* stream) {
 }
 
 extern "C" int vnb_adam_step(float* p, const float* g, float* m, float* v, int64_t n, const float* sqn, float max_norm,
-                             float lr, float beta1, float beta2, float eps, float* state, int step_size, float gamma,
+                             float lr, double beta1, double beta2, float eps, float* state, int step_size, float gamma,
                              void* stream) {
     VNB_REQUIRE(p && g && m && v && state && n > 0, "adam_step: bad arguments");
     cudaStream_t st = (cudaStream_t)stream;
