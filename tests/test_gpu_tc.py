@@ -1,0 +1,76 @@
+"""-m gpu: the tcgen05/TMEM/TMA GEMM backend against the SIMT backend and the CPU contract on the SAME
+operand planes.  bf16 planes (P=1): both backends contract identical bf16 operands in fp32, so they
+must agree to fp32 round-off.  P=3 (hi/mid/lo): fp32-faithful, tolerance stated per assert."""
+import pytest
+import torch
+
+from conftest import rel_err
+from oracle import prims_ref as R
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def backends():
+    from vae_npvc_b200 import _C, prims
+    _C.require_cuda()
+    yield _C, prims
+    _C.set_backend(_C.BACKEND_AUTO)
+
+
+def g(*shape, seed=0, scale=1.0):
+    return torch.randn(*shape, generator=torch.Generator().manual_seed(seed)) * scale
+
+
+CONV_SHAPES = [
+    # B, Cin, Cout, T, taps, dil
+    (2, 64, 128, 128, 3, 1),
+    (2, 80, 512, 128, 3, 1),         # first encoder conv: K = 80 does not fill a 64-wide stage
+    (3, 512, 1024, 128, 3, 1),       # decoder conv_in
+    (2, 512, 640, 128, 1, 1),        # res/skip 1x1, Cout not a multiple of 128
+    (2, 128, 80, 64, 1, 1),          # final layer, BN = 64 tile
+    (2, 64, 64, 100, 3, 2),          # ragged T (multiple of 4), dilation 2
+    (1, 72, 96, 37, 3, 1),           # T not a multiple of 4 -> scalar stores; pitch padding
+    (2, 16, 16, 24, 3, 1),           # tiny (the small golden model)
+    (1, 512, 512, 317, 3, 1),        # conversion-length utterance, 3 time tiles
+]
+
+
+@pytest.mark.parametrize('P', [1, 3])
+@pytest.mark.parametrize('B,Cin,Cout,T,k,dil', CONV_SHAPES)
+def test_conv_fwd_tc_vs_simt(backends, P, B, Cin, Cout, T, k, dil):
+    _C, Pm = backends
+    x = g(B, Cin, T, seed=1)
+    w = g(Cout, Cin, k, seed=2, scale=1.0 / (Cin * k) ** 0.5)
+    bias, res = g(B, Cout, seed=3), g(B, Cout, T, seed=4)
+    xpl = Pm.make_planes(x.cuda(), P)[0]
+    W = Pm.wn_prepare(w.cuda(), None, False, P)
+    outs = {}
+    for name, be in (('simt', _C.BACKEND_SIMT), ('tc', _C.BACKEND_TC)):
+        _C.set_backend(be)
+        o1 = Pm.conv_fwd(xpl, W.wf, k, dil, Cout)
+        o2 = Pm.conv_fwd(xpl, W.wf, k, dil, Cout, bias.cuda(), Cout, res.cuda(), o1.clone(), True)
+        outs[name] = (o1, o2)
+    torch.cuda.synchronize()
+    tol = 2e-6 if P == 1 else 2e-5
+    assert rel_err(outs['tc'][0], outs['simt'][0]) < tol, rel_err(outs['tc'][0], outs['simt'][0])
+    assert rel_err(outs['tc'][1], outs['simt'][1]) < tol
+    # and against the exact value in float64 (P=3 reproduces fp32 operands; P=1 rounds them to bf16)
+    ref = torch.nn.functional.conv1d(x.double(), w.double(), padding=(k - 1) // 2 * dil, dilation=dil)
+    err = rel_err(outs['tc'][0], ref)
+    assert err < (2e-5 if P == 3 else 1e-2), err
+
+
+def test_conv_tc_data_gradient_operand(backends):
+    """dgrad = the same kernel on the wb operand (taps flipped, channels transposed)."""
+    _C, Pm = backends
+    B, Cin, Cout, T, k = 2, 512, 1024, 128, 3
+    wt = g(Cin, Cout, k, seed=1, scale=0.03)          # ConvTranspose1d layout
+    dy = g(B, Cout, T, seed=2)
+    W = Pm.wn_prepare(wt.cuda(), None, True, 1)
+    dypl = Pm.make_planes(dy.cuda(), 1)[0]
+    _C.set_backend(_C.BACKEND_SIMT)
+    a = Pm.conv_fwd(dypl, W.wb, k, 1, Cin)
+    _C.set_backend(_C.BACKEND_TC)
+    b = Pm.conv_fwd(dypl, W.wb, k, 1, Cin)
+    assert rel_err(b, a) < 2e-6
