@@ -11,9 +11,14 @@
  *     by the library; every kernel is launched on `stream` (a cudaStream_t passed as void*)
  *   - return value: 0 on success, negative VNB_E_* otherwise; vnb_last_error() gives the
  *     thread-local message.  There is no CPU fallback anywhere.
- *   - activations are float32, contiguous (B, C, T) ("NCT", the reference's layout)
- *   - GEMM operands are bf16 "planes": (P, B, C, Tp) for activations, Tp = row pitch
- *     (multiple of 8, >= T);  P = 1: bf16 operands (fast path);  P = 3: hi/mid/lo split of
+ *   - activations are float32 CHANNELS-LAST: logical (B, C, T) [the reference's shape], element
+ *     (b, c, t) stored at (b*T + t)*C + c, i.e. a contiguous (B, T, C) array.  The Python layer
+ *     hands these out as (B, C, T) tensors with permuted strides, so the reference-facing shapes
+ *     are unchanged; vnb_transpose converts a reference-layout (B, C, T)-contiguous tensor.
+ *     Reason: TMA needs 16-byte-aligned innermost coordinates, so the +-1 frame shift of a k=3
+ *     conv must be a ROW coordinate - frames are rows, channels are the contiguous dimension.
+ *   - GEMM operands are bf16 "planes": (P, B, T, Cp) for activations, Cp = C rounded up to 8
+ *     (padding never read as data);  P = 1: bf16 operands (fast path);  P = 3: hi/mid/lo split of
  *     the fp32 value, contracted with 6 plane-pair products = fp32-faithful on tensor cores
  *   - conv weights as GEMM operands: (P, taps, Cout, Cin_p) bf16, Cin_p = Cin rounded up to 8
  *   - indices are int64, like torch.argmin
@@ -49,6 +54,9 @@ void vnb_launch_count_reset(void);
 /* 0 = auto (TC where the shape allows), 1 = SIMT everywhere, 2 = TC (error if impossible) */
 void vnb_set_backend(int backend);
 int vnb_get_backend(void);
+/* debug: how many bounded mbarrier waits of the tcgen05 kernels timed out since load (must stay 0);
+ * synchronises the device */
+int vnb_debug_tc_timeouts(void);
 
 /* ---- weight-norm materialisation: nn.utils.weight_norm pre-hook, vqvae.py:203-208,329-334
  * v: (d0,d1,k) fp32, g: (d0) fp32 or NULL (plain weight).  transposed=0: Conv1d (co=d0,ci=d1);
@@ -65,7 +73,7 @@ int vnb_wn_backward(const float* dw, const float* v, const float* g, int d0, int
  * 229,231,244; vqvae.py:155,174,256,283,285.  Also the data-gradient (pass the wb operand).
  * out[b,co,t] = beta*out + bias[b*bias_bstride+co] + residual[b,co,t]
  *             + sum_{tap,ci} W[tap][co][ci] * in[b,ci,t+(tap-(taps-1)/2)*dil]   (zero padded) */
-int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T, int Tp,
+int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T,
                  const void* w_planes, int taps, int dil, int Cout,
                  const float* bias, int bias_bstride, const float* residual,
                  float* out, int accumulate, void* stream);
@@ -73,29 +81,33 @@ int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T, int Tp,
  * conv tap j: dW[co][ci][j] = sum_{b,t} dy[b,co,t] * u[b,ci,t+(j-(taps-1)/2)*dil];
  * transposed=0 -> dw[co][ci][j];  transposed=1 -> dw[ci][co][taps-1-j] */
 int vnb_conv_wgrad(const void* dy_planes, const void* u_planes, int P, int B, int Cout, int Cin,
-                   int T, int Tp, int taps, int dil, int transposed, float* dw, void* stream);
+                   int T, int taps, int dil, int transposed, float* dw, void* stream);
 
-/* ---- operand planes from fp32 activations (B,C,T): out_id <- x*scale, out_act <- act(x*scale) */
-int vnb_make_planes(const float* x, int B, int C, int T, int Tp, int P, float scale, int act,
+/* ---- layout conversion: (B, R, S) contiguous -> (B, S, R) contiguous (reference NCT <-> channels-last) */
+int vnb_transpose(const float* in, int B, int R, int S, float* out, void* stream);
+/* ---- operand planes from fp32 activations: out_id <- x*scale, out_act <- act(x*scale) */
+int vnb_make_planes(const float* x, int B, int C, int T, int P, float scale, int act,
                     void* out_id, void* out_act, void* stream);
-/* channel-concat [xa (B,Ca,T); xb (B,Cb,T)] -> planes (P,B,Ca+Cb,Tp) */
-int vnb_concat_planes(const float* xa, int Ca, const float* xb, int Cb, int B, int T, int Tp, int P,
+/* channel-concat [xa (B,Ca,T); xb (B,Cb,T)] -> planes (P,B,T,(Ca+Cb)p) */
+int vnb_concat_planes(const float* xa, int Ca, const float* xb, int Cb, int B, int T, int P,
                       void* out, void* stream);
 
-/* ---- nn.GroupNorm statistics (layers.py:154,201): mean,rstd (B,groups), biased var, eps */
-int vnb_gn_stats(const float* h, int B, int C, int T, int groups, float eps, float* mean, float* rstd,
-                 void* stream);
+/* ---- nn.GroupNorm statistics (layers.py:154,201): mean,rstd (B,groups), biased var, eps.
+ * ws: scratch of vnb_gn_stats_ws_floats(B, groups) floats (chunk-wise mean/M2, merged exactly) */
+int vnb_gn_stats_ws_floats(int B, int groups);
+int vnb_gn_stats(const float* h, int B, int C, int T, int groups, float eps, float* ws, float* mean,
+                 float* rstd, void* stream);
 /* encoder residual block epilogue (layers.py:176): y = GN1(h)*gamma+beta (+ s); optional outputs:
  * y fp32, planes of y, planes of LeakyReLU_0.2(y) */
 int vnb_enc_out(const float* h, const float* s, const float* mean, const float* rstd,
-                const float* gamma, const float* beta, int B, int C, int T, int Tp, int P,
+                const float* gamma, const float* beta, int B, int C, int T, int P,
                 float* y, void* y_planes, void* u_planes, void* stream);
 /* decoder gate (layers.py:236-242): hn = GN2(a); g = tanh(hn[:C])*sigmoid(hn[C:]) -> planes of g */
 int vnb_dec_gate(const float* a, const float* mean, const float* rstd, const float* gamma,
-                 const float* beta, int B, int C, int T, int Tp, int P, void* g_planes, void* stream);
+                 const float* beta, int B, int C, int T, int P, void* g_planes, void* stream);
 /* decoder residual/skip split (layers.py:246-247, vqvae.py:313): r (B,C+S,T);
  * x_out = r[:C]+x (fp32 + planes);  skip_sum (+)= r[C:]  (first=1 assigns) */
-int vnb_dec_out(const float* r, const float* x, int B, int C, int S, int T, int Tp, int P,
+int vnb_dec_out(const float* r, const float* x, int B, int C, int S, int T, int P,
                 float* x_out, void* x_planes, float* skip_sum, int first, void* stream);
 
 /* ---- backward reductions.  rows: per (b,c) sums over t */
@@ -113,11 +125,11 @@ int vnb_gn_bwd_finalize(const float* R, const float* gamma, const float* rstd, i
                         float* dpre_csum, void* stream);
 /* dpre = rstd*(gamma*dn - S0/n - xhat*S1/n) -> planes (+ optional planes of dn itself) */
 int vnb_gn_bwd_apply(const float* dn, const float* h, const float* mean, const float* rstd,
-                     const float* gamma, const float* S, int B, int C, int T, int groups, int Tp, int P,
+                     const float* gamma, const float* S, int B, int C, int T, int groups, int P,
                      void* dpre_planes, void* dn_planes, void* stream);
 int vnb_gate_bwd_apply(const float* dg, const float* a, const float* mean, const float* rstd,
                        const float* gamma, const float* beta, const float* S, int B, int C, int T,
-                       int Tp, int P, void* da_planes, void* stream);
+                       int P, void* da_planes, void* stream);
 /* out = add + scale * act'(c*scale) * du   (e.g. encoder block input gradient: dskip_path +
  * lrelu'(c)*du) ; act as VNB_ACT_* ; add may be NULL */
 int vnb_act_bwd_add(const float* du, const float* c, const float* add, int64_t n, int act, float scale,
@@ -141,12 +153,12 @@ int vnb_linear_bwd(const float* dp, const float* y, const float* W, int B, int I
  * else e_hat = E.  e_planes (3,K,Dp) hi/mid/lo, e_sq[k] = sum e_hat^2 */
 int vnb_vq_prep_codebook(float* E, int K, int D, int normalize, int inplace_renorm, float* e_hat,
                          void* e_planes, float* e_sq, void* stream);
-/* frames: zn = z/||z|| (or z); z_planes (3,B,D,Tp); z_sq[n], z_norm[n] with n = b*T+t */
-int vnb_vq_prep_z(const float* z, int B, int D, int T, int Tp, int normalize, float* zn,
+/* frames: zn = z/||z|| (or z); z_planes (3,B,T,Dp); z_sq[n], z_norm[n] with n = b*T+t */
+int vnb_vq_prep_z(const float* z, int B, int D, int T, int normalize, float* zn,
                   void* z_planes, float* z_sq, float* z_norm, void* stream);
 /* idx[n] = argmin_k ((z_sq[n] + e_sq[k]) - 2 zn[n].e_hat[k]), ties -> lowest k (:103-108) */
 int vnb_vq_lookup(const float* zn, const void* z_planes, const float* z_sq, const float* e_hat,
-                  const void* e_planes, const float* e_sq, int B, int D, int T, int Tp, int K,
+                  const void* e_planes, const float* e_sq, int B, int D, int T, int K,
                   int64_t* idx, void* stream);
 /* q = e_hat[idx] -> q_out (B,D,T); sums[0] += sum (q-zn)^2, sums[1] += sum (zn-z)^2;
  * counts[k] += #{idx==k}  (sums, counts must be zeroed by the caller) */

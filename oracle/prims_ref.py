@@ -15,8 +15,30 @@ import torch.nn.functional as F
 ACT_NONE, ACT_LRELU, ACT_RELU = 0, 1, 2
 
 
-def pitch(T):
-    return (T + 7) // 8 * 8
+def pitch(C):
+    return (C + 7) // 8 * 8
+
+
+# layout helpers of vae_npvc_b200.prims: on the CPU contract side layout is immaterial (every
+# function here works on logical (B,C,T) tensors), so they are (near-)identities
+def as_cl(x):
+    return x
+
+
+def to_nct(x):
+    return x.contiguous()
+
+
+def is_cl(x):
+    return True
+
+
+def cl_empty(B, C, T, device=None, dtype=torch.float32):
+    return torch.empty((B, T, C), dtype=dtype).transpose(1, 2)
+
+
+def cl_zeros(B, C, T, device=None, dtype=torch.float32):
+    return torch.zeros((B, T, C), dtype=dtype).transpose(1, 2)
 
 
 def _split(x, P):
@@ -35,21 +57,22 @@ def _join(data):
 
 
 class Planes:
-    __slots__ = ('data', 'P', 'B', 'C', 'T', 'Tp')
+    """Same memory layout as the CUDA side: data (P, B, T, Cp) bf16, channels-last."""
+    __slots__ = ('data', 'P', 'B', 'C', 'T', 'Cp')
 
-    def __init__(self, data, P, B, C, T, Tp):
-        self.data, self.P, self.B, self.C, self.T, self.Tp = data, P, B, C, T, Tp
+    def __init__(self, data, P, B, C, T, Cp):
+        self.data, self.P, self.B, self.C, self.T, self.Cp = data, P, B, C, T, Cp
 
     @staticmethod
     def of(x, P):
         B, C, T = x.shape
-        Tp = pitch(T)
-        data = torch.zeros((P, B, C, Tp), dtype=torch.bfloat16)
-        data[..., :T] = _split(x, P)
-        return Planes(data, P, B, C, T, Tp)
+        Cp = pitch(C)
+        data = torch.zeros((P, B, T, Cp), dtype=torch.bfloat16)
+        data[..., :C] = _split(x.transpose(1, 2), P)
+        return Planes(data, P, B, C, T, Cp)
 
     def value(self):
-        return _join(self.data)[..., :self.T]
+        return _join(self.data)[..., :self.C].transpose(1, 2)
 
 
 class ConvWeights:

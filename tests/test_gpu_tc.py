@@ -52,7 +52,7 @@ def test_conv_fwd_tc_vs_simt(backends, P, B, Cin, Cout, T, k, dil):
         o2 = Pm.conv_fwd(xpl, W.wf, k, dil, Cout, bias.cuda(), Cout, res.cuda(), o1.clone(), True)
         outs[name] = (o1, o2)
     torch.cuda.synchronize()
-    tol = 2e-6 if P == 1 else 2e-5
+    tol = 1e-5 if P == 1 else 2e-5
     assert rel_err(outs['tc'][0], outs['simt'][0]) < tol, rel_err(outs['tc'][0], outs['simt'][0])
     assert rel_err(outs['tc'][1], outs['simt'][1]) < tol
     # and against the exact value in float64 (P=3 reproduces fp32 operands; P=1 rounds them to bf16)
@@ -73,4 +73,4 @@ def test_conv_tc_data_gradient_operand(backends):
     a = Pm.conv_fwd(dypl, W.wb, k, 1, Cin)
     _C.set_backend(_C.BACKEND_TC)
     b = Pm.conv_fwd(dypl, W.wb, k, 1, Cin)
-    assert rel_err(b, a) < 2e-6
+    assert rel_err(b, a) < 1e-5          # K = 3072 products: fp32 summation-order differences only

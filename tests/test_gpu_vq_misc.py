@@ -157,5 +157,6 @@ def test_no_cpu_path_and_errors(Pm):
     with pytest.raises(RuntimeError, match='no CPU path'):
         Pm.gn_stats(torch.zeros(1, 2, 3), 1)
     with pytest.raises(RuntimeError, match='bad'):
-        _C.call('gn_stats', torch.zeros(1, 3, 3).cuda(), 1, 3, 3, 2, 1e-5, torch.zeros(2).cuda(), torch.zeros(2).cuda())
+        _C.call('gn_stats', torch.zeros(1, 3, 3).cuda(), 1, 3, 3, 2, 1e-5, torch.zeros(256).cuda(), torch.zeros(2).cuda(),
+                 torch.zeros(2).cuda())
     assert 'gn_stats' in _C.last_error()

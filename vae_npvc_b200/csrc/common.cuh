@@ -60,6 +60,48 @@ __device__ __forceinline__ void store_planes(bf16* base, int64_t off, int64_t pl
     }
 }
 
+// ---- VEC-wide (1 or 4 channels) accessors for the channels-last kernels --------------------
+template <int VEC>
+__device__ __forceinline__ void ld_vec(const float* __restrict__ p, float (&v)[VEC]) {
+    if constexpr (VEC == 4) {
+        const float4 t = *reinterpret_cast<const float4*>(p);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < VEC; j++) v[j] = p[j];
+    }
+}
+template <int VEC>
+__device__ __forceinline__ void st_vec(float* __restrict__ p, const float (&v)[VEC]) {
+    if constexpr (VEC == 4) {
+        *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+#pragma unroll
+        for (int j = 0; j < VEC; j++) p[j] = v[j];
+    }
+}
+// VEC consecutive channels into plane 0 (and 1,2 for P==3) at element offset `off` (8-byte aligned for VEC==4)
+template <int VEC>
+__device__ __forceinline__ void st_planes_vec(bf16* base, int64_t off, int64_t plane_stride, int P, const float (&x)[VEC]) {
+    if constexpr (VEC == 4) {
+        bf16 h[3][4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (P == 1) h[0][j] = __float2bfloat16_rn(x[j]);
+            else split3(x[j], h[0][j], h[1][j], h[2][j]);
+        }
+        for (int p = 0; p < P; p++) {
+            uint2 u;
+            u.x = (uint32_t)__bfloat16_as_ushort(h[p][0]) | ((uint32_t)__bfloat16_as_ushort(h[p][1]) << 16);
+            u.y = (uint32_t)__bfloat16_as_ushort(h[p][2]) | ((uint32_t)__bfloat16_as_ushort(h[p][3]) << 16);
+            *reinterpret_cast<uint2*>(base + off + p * plane_stride) = u;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < VEC; j++) store_planes(base, off + j, plane_stride, P, x[j]);
+    }
+}
+
 __device__ __forceinline__ float load_planes(const bf16* base, int64_t off, int64_t plane_stride, int P) {
     float x = __bfloat162float(base[off]);
     if (P == 3) {

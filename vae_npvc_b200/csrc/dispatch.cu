@@ -2,35 +2,35 @@
 #include "common.cuh"
 
 namespace vnb {
-int conv_fwd_simt(const void* in, int P, int B, int Cin, int T, int Tp, const void* w, int taps, int dil, int Cout,
+int conv_fwd_simt(const void* in, int P, int B, int Cin, int T, const void* w, int taps, int dil, int Cout,
                   const float* bias, int bias_bstride, const float* residual, float* out, int accumulate,
                   cudaStream_t st);
-int conv_wgrad_simt(const void* dy, const void* u, int P, int B, int Cout, int Cin, int T, int Tp, int taps, int dil,
+int conv_wgrad_simt(const void* dy, const void* u, int P, int B, int Cout, int Cin, int T, int taps, int dil,
                     int transposed, float* dw, cudaStream_t st);
 int vq_lookup_simt(const float* zn, const float* z_sq, const float* e_hat, const float* e_sq, int B, int D, int T,
                    int K, int64_t* idx, cudaStream_t st);
 // tensor-core backend: return VNB_OK, a negative error, or +1 = "shape not taken by this backend"
-int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, int Tp, const void* w, int taps, int dil, int Cout,
+int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int taps, int dil, int Cout,
                 const float* bias, int bias_bstride, const float* residual, float* out, int accumulate,
                 cudaStream_t st);
-int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin, int T, int Tp, int taps, int dil,
+int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin, int T, int taps, int dil,
                   int transposed, float* dw, cudaStream_t st);
 int vq_lookup_tc(const void* z_planes, const float* z_sq, const void* e_planes, const float* e_sq, int B, int D,
-                 int T, int Tp, int K, int64_t* idx, cudaStream_t st);
+                 int T, int K, int64_t* idx, cudaStream_t st);
 }  // namespace vnb
 
 using namespace vnb;
 
-extern "C" int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T, int Tp, const void* w_planes, int taps,
+extern "C" int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T, const void* w_planes, int taps,
                             int dil, int Cout, const float* bias, int bias_bstride, const float* residual, float* out,
                             int accumulate, void* stream) {
     VNB_REQUIRE(in_planes && w_planes && out, "conv_fwd: null pointer");
-    VNB_REQUIRE(B > 0 && Cin > 0 && Cout > 0 && T > 0 && Tp >= T && (Tp & 7) == 0, "conv_fwd: bad shape B=%d Cin=%d Cout=%d T=%d Tp=%d", B, Cin, Cout, T, Tp);
+    VNB_REQUIRE(B > 0 && Cin > 0 && Cout > 0 && T > 0, "conv_fwd: bad shape B=%d Cin=%d Cout=%d T=%d", B, Cin, Cout, T);
     VNB_REQUIRE((P == 1 || P == 3) && taps >= 1 && (taps & 1) && dil >= 1, "conv_fwd: P=%d taps=%d dil=%d unsupported", P, taps, dil);
     cudaStream_t st = (cudaStream_t)stream;
     const int be = backend();
     if (be != VNB_BACKEND_SIMT) {
-        int r = conv_fwd_tc(in_planes, P, B, Cin, T, Tp, w_planes, taps, dil, Cout, bias, bias_bstride, residual, out,
+        int r = conv_fwd_tc(in_planes, P, B, Cin, T, w_planes, taps, dil, Cout, bias, bias_bstride, residual, out,
                             accumulate, st);
         if (r <= 0) return r;
         if (be == VNB_BACKEND_TC) {
@@ -38,37 +38,37 @@ extern "C" int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T,
             return VNB_E_ARG;
         }
     }
-    return conv_fwd_simt(in_planes, P, B, Cin, T, Tp, w_planes, taps, dil, Cout, bias, bias_bstride, residual, out,
+    return conv_fwd_simt(in_planes, P, B, Cin, T, w_planes, taps, dil, Cout, bias, bias_bstride, residual, out,
                          accumulate, st);
 }
 
 extern "C" int vnb_conv_wgrad(const void* dy_planes, const void* u_planes, int P, int B, int Cout, int Cin, int T,
-                              int Tp, int taps, int dil, int transposed, float* dw, void* stream) {
+                              int taps, int dil, int transposed, float* dw, void* stream) {
     VNB_REQUIRE(dy_planes && u_planes && dw, "conv_wgrad: null pointer");
-    VNB_REQUIRE(B > 0 && Cin > 0 && Cout > 0 && T > 0 && Tp >= T && (Tp & 7) == 0, "conv_wgrad: bad shape");
+    VNB_REQUIRE(B > 0 && Cin > 0 && Cout > 0 && T > 0, "conv_wgrad: bad shape");
     VNB_REQUIRE((P == 1 || P == 3) && taps >= 1 && (taps & 1) && dil >= 1, "conv_wgrad: P=%d taps=%d dil=%d unsupported", P, taps, dil);
     cudaStream_t st = (cudaStream_t)stream;
     const int be = backend();
     if (be != VNB_BACKEND_SIMT) {
-        int r = conv_wgrad_tc(dy_planes, u_planes, P, B, Cout, Cin, T, Tp, taps, dil, transposed, dw, st);
+        int r = conv_wgrad_tc(dy_planes, u_planes, P, B, Cout, Cin, T, taps, dil, transposed, dw, st);
         if (r <= 0) return r;
         if (be == VNB_BACKEND_TC) {
             set_error("conv_wgrad: shape not supported by the tcgen05 backend");
             return VNB_E_ARG;
         }
     }
-    return conv_wgrad_simt(dy_planes, u_planes, P, B, Cout, Cin, T, Tp, taps, dil, transposed, dw, st);
+    return conv_wgrad_simt(dy_planes, u_planes, P, B, Cout, Cin, T, taps, dil, transposed, dw, st);
 }
 
 extern "C" int vnb_vq_lookup(const float* zn, const void* z_planes, const float* z_sq, const float* e_hat,
-                             const void* e_planes, const float* e_sq, int B, int D, int T, int Tp, int K, int64_t* idx,
+                             const void* e_planes, const float* e_sq, int B, int D, int T, int K, int64_t* idx,
                              void* stream) {
     VNB_REQUIRE(zn && z_sq && e_hat && e_sq && idx, "vq_lookup: null pointer");
     VNB_REQUIRE(B > 0 && D > 0 && T > 0 && K > 0 && D <= 1024, "vq_lookup: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
     const int be = backend();
     if (be != VNB_BACKEND_SIMT && z_planes && e_planes) {
-        int r = vq_lookup_tc(z_planes, z_sq, e_planes, e_sq, B, D, T, Tp, K, idx, st);
+        int r = vq_lookup_tc(z_planes, z_sq, e_planes, e_sq, B, D, T, K, idx, st);
         if (r <= 0) return r;
         if (be == VNB_BACKEND_TC) {
             set_error("vq_lookup: shape not supported by the tcgen05 backend (D=%d K=%d)", D, K);

@@ -1,5 +1,8 @@
-// Memory-bound fused kernels around the GEMMs: operand-plane writers, GroupNorm statistics /
-// apply / backward, the decoder gate, residual/skip bookkeeping, bias reductions.
+// Memory-bound fused kernels around the GEMMs (forward side): layout conversion, operand-plane
+// writers, GroupNorm statistics, encoder-block epilogue, decoder gate, residual/skip bookkeeping.
+// Everything is CHANNELS-LAST: activation element (b, c, t) lives at (b*T + t)*C + c, operand
+// planes at (b*T + t)*Cp + c, so consecutive threads touch consecutive channels (float4 / 4 x bf16
+// per thread when C % 4 == 0) and no kernel transposes.
 // Reference op sequences: vae_npvc/model/layers.py:151-155,168-176 (encoder residual block),
 // :229-247 (gated decoder block); math in SURVEY.md section 9 A/B.
 #include "common.cuh"
@@ -9,113 +12,251 @@ namespace vnb {
 constexpr int EW_THREADS = 256;
 static inline int ew_grid(int64_t n) {
     int64_t g = (n + EW_THREADS - 1) / EW_THREADS;
-    const int64_t cap = 148 * 16;          // grid-stride beyond 16 CTAs per SM
+    const int64_t cap = 148 * 8;           // grid-stride beyond 8 CTAs per SM
     return (int)(g < cap ? g : cap);
 }
 #define GRID_STRIDE(i, n) \
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < (n); i += (int64_t)gridDim.x * blockDim.x)
 
+// launch a VEC-templated kernel with VEC = 4 when every channel count involved is a multiple of 4
+#define VEC_DISPATCH(cond4, KERNEL, n_scalar, st, ...)                                        \
+    do {                                                                                      \
+        if (cond4)                                                                            \
+            KERNEL<4><<<ew_grid((n_scalar) / 4), EW_THREADS, 0, st>>>(__VA_ARGS__);           \
+        else                                                                                  \
+            KERNEL<1><<<ew_grid(n_scalar), EW_THREADS, 0, st>>>(__VA_ARGS__);                 \
+    } while (0)
+
 // ------------------------------------------------------------------------------------------
-__global__ void make_planes_kernel(const float* __restrict__ x, int64_t rows, int T, int Tp, int P, float scale,
+// (B, R, S) -> (B, S, R), 32x32 shared-memory tiles (both sides coalesced)
+__global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict__ in, int R, int S,
+                                                        float* __restrict__ out) {
+    __shared__ float tile[32][33];
+    const int64_t base = (int64_t)blockIdx.z * R * S;
+    const int s0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int j = ty; j < 32; j += 8) {
+        const int r = r0 + j, s = s0 + tx;
+        if (r < R && s < S) tile[j][tx] = in[base + (int64_t)r * S + s];
+    }
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8) {
+        const int s = s0 + j, r = r0 + tx;
+        if (r < R && s < S) out[base + (int64_t)s * R + r] = tile[tx][j];
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+template <int VEC>
+__global__ void make_planes_kernel(const float* __restrict__ x, int64_t rows, int C, int Cp, int P, float scale,
                                    int act, bf16* __restrict__ out_id, bf16* __restrict__ out_act) {
-    const int64_t n = rows * T, plane = rows * Tp;
+    const int Cv = C / VEC;
+    const int64_t n = rows * Cv, plane = rows * Cp;
     GRID_STRIDE(i, n) {
-        const int64_t r = i / T;
-        const int t = (int)(i - r * T);
-        const float v = x[i] * scale;
-        const int64_t o = r * Tp + t;
-        if (out_id) store_planes(out_id, o, plane, P, v);
-        if (out_act) store_planes(out_act, o, plane, P, apply_act(v, act));
+        const int64_t r = i / Cv;
+        const int c = (int)(i - r * Cv) * VEC;
+        float v[VEC], u[VEC];
+        ld_vec<VEC>(x + r * C + c, v);
+#pragma unroll
+        for (int j = 0; j < VEC; j++) {
+            v[j] *= scale;
+            u[j] = apply_act(v[j], act);
+        }
+        const int64_t o = r * Cp + c;
+        if (out_id) st_planes_vec<VEC>(out_id, o, plane, P, v);
+        if (out_act) st_planes_vec<VEC>(out_act, o, plane, P, u);
     }
 }
 
-__global__ void concat_planes_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb, int Cb, int B,
-                                     int T, int Tp, int P, bf16* __restrict__ out) {
-    const int Cc = Ca + Cb;
-    const int64_t n = (int64_t)B * Cc * T, plane = (int64_t)B * Cc * Tp;
+template <int VEC>
+__global__ void concat_planes_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb, int Cb,
+                                     int64_t rows, int Cp, int P, bf16* __restrict__ out) {
+    const int Cc = Ca + Cb, Cv = Cc / VEC;
+    const int64_t n = rows * Cv, plane = rows * Cp;
     GRID_STRIDE(i, n) {
-        const int64_t r = i / T;
-        const int t = (int)(i - r * T);
-        const int b = (int)(r / Cc), c = (int)(r - (int64_t)b * Cc);
-        const float v = c < Ca ? xa[((int64_t)b * Ca + c) * T + t] : xb[((int64_t)b * Cb + (c - Ca)) * T + t];
-        store_planes(out, r * Tp + t, plane, P, v);
+        const int64_t r = i / Cv;
+        const int c = (int)(i - r * Cv) * VEC;
+        float v[VEC];
+        if (c < Ca) ld_vec<VEC>(xa + r * Ca + c, v);
+        else ld_vec<VEC>(xb + r * Cb + (c - Ca), v);
+        st_planes_vec<VEC>(out, r * Cp + c, plane, P, v);
     }
 }
 
-// one block per (sample, group); the group's (C/groups)*T values are contiguous in NCT
-__global__ void __launch_bounds__(512) gn_stats_kernel(const float* __restrict__ h, int64_t n, float eps,
-                                                       float* __restrict__ mean, float* __restrict__ rstd) {
-    __shared__ float red[32];
-    const float* p = h + (int64_t)blockIdx.x * n;
-    float s = 0.f;
-    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) s += p[i];
-    const float m = block_sum(s, red) / (float)n;
-    float q = 0.f;
-    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
-        const float d = p[i] - m;
-        q += d * d;
-    }
-    const float var = block_sum(q, red) / (float)n;
-    if (threadIdx.x == 0) {
-        mean[blockIdx.x] = m;
-        rstd[blockIdx.x] = rsqrtf(var + eps);
+// ------------------------------------------------------------------------------------------
+// GroupNorm statistics, two launches.  Pass 1: grid (chunks, B); each CTA owns `rows_per` frames
+// of one sample and writes, per group, (local mean, local M2) of its slice - a CTA-local two-pass,
+// so there is no E[x^2]-E[x]^2 cancellation.  Pass 2 merges the chunks with Chan's formula.
+constexpr int GN_MAX_CHUNKS = 64;
+constexpr int GN_MAX_GROUPS = 8;
+
+__global__ void __launch_bounds__(256) gn_stats_partial_kernel(const float* __restrict__ h, int C, int T, int groups,
+                                                               int rows_per, float* __restrict__ ws) {
+    __shared__ float acc[GN_MAX_GROUPS];
+    __shared__ float lmean[GN_MAX_GROUPS];
+    const int b = blockIdx.y, chunk = blockIdx.x, chunks = gridDim.x;
+    const int t0 = chunk * rows_per;
+    const int t1 = min(T, t0 + rows_per);
+    const int nrow = max(0, t1 - t0);
+    const int cg = C / groups;
+    const float* p = h + ((int64_t)b * T + t0) * C;
+    const int n = nrow * C;
+    for (int pass = 0; pass < 2; pass++) {
+        if (threadIdx.x < GN_MAX_GROUPS) acc[threadIdx.x] = 0.f;
+        __syncthreads();
+        // a thread's channel advances by blockDim mod C per step; keep a per-group register pair
+        float s[2] = {0.f, 0.f};
+        int cur = -1;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const int g = (i % C) / cg;
+            if (g != cur) {
+                if (cur >= 0) atomicAdd(&acc[cur], s[0]);
+                s[0] = 0.f;
+                cur = g;
+            }
+            const float x = p[i];
+            if (pass == 0) s[0] += x;
+            else {
+                const float d = x - lmean[g];
+                s[0] += d * d;
+            }
+        }
+        if (cur >= 0) atomicAdd(&acc[cur], s[0]);
+        __syncthreads();
+        if (threadIdx.x < groups) {
+            const float cnt = (float)nrow * (float)cg;
+            float* o = ws + (((int64_t)b * groups + threadIdx.x) * chunks + chunk) * 2;
+            if (pass == 0) lmean[threadIdx.x] = cnt > 0.f ? acc[threadIdx.x] / cnt : 0.f;
+            else {
+                o[0] = lmean[threadIdx.x];
+                o[1] = acc[threadIdx.x];
+            }
+        }
+        __syncthreads();
     }
 }
 
+// one warp per (b, group)
+__global__ void gn_stats_merge_kernel(const float* __restrict__ ws, int BG, int chunks, int T, int rows_per, int cg,
+                                      float eps, float* __restrict__ mean, float* __restrict__ rstd) {
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w >= BG) return;
+    const float* p = ws + (int64_t)w * chunks * 2;
+    float sm = 0.f;
+    for (int c = lane; c < chunks; c += 32) {
+        const int nrow = max(0, min(T, (c + 1) * rows_per) - c * rows_per);
+        sm += p[2 * c] * (float)nrow * (float)cg;
+    }
+    const float n = (float)T * (float)cg;
+    const float m = warp_sum(sm) / n;
+    float m2 = 0.f;
+    for (int c = lane; c < chunks; c += 32) {
+        const int nrow = max(0, min(T, (c + 1) * rows_per) - c * rows_per);
+        const float d = p[2 * c] - m;
+        m2 += p[2 * c + 1] + (float)nrow * (float)cg * d * d;
+    }
+    m2 = warp_sum(m2);
+    if (lane == 0) {
+        mean[w] = m;
+        rstd[w] = rsqrtf(m2 / n + eps);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// encoder block epilogue: y = GN1(h)*gamma+beta (+ s) -> y fp32, planes(y), planes(lrelu(y))
+template <int VEC>
 __global__ void enc_out_kernel(const float* __restrict__ h, const float* __restrict__ s, const float* __restrict__ mean,
                                const float* __restrict__ rstd, const float* __restrict__ gamma,
-                               const float* __restrict__ beta, int B, int C, int T, int Tp, int P,
+                               const float* __restrict__ beta, int64_t rows, int C, int T, int Cp, int P,
                                float* __restrict__ y, bf16* __restrict__ y_planes, bf16* __restrict__ u_planes) {
-    const int64_t n = (int64_t)B * C * T, plane = (int64_t)B * C * Tp;
+    const int Cv = C / VEC;
+    const int64_t n = rows * Cv, plane = rows * Cp;
     GRID_STRIDE(i, n) {
-        const int64_t r = i / T;
-        const int t = (int)(i - r * T);
-        const int b = (int)(r / C), c = (int)(r - (int64_t)b * C);
-        float v = (h[i] - mean[b]) * rstd[b] * gamma[c] + beta[c];
-        if (s) v += s[i];
-        if (y) y[i] = v;
-        const int64_t o = r * Tp + t;
-        if (y_planes) store_planes(y_planes, o, plane, P, v);
-        if (u_planes) store_planes(u_planes, o, plane, P, lrelu02(v));
+        const int64_t r = i / Cv;
+        const int c = (int)(i - r * Cv) * VEC;
+        const int b = (int)(r / T);
+        const float m = mean[b], rs = rstd[b];
+        float v[VEC], gm[VEC], bt[VEC], u[VEC];
+        ld_vec<VEC>(h + r * C + c, v);
+        ld_vec<VEC>(gamma + c, gm);
+        ld_vec<VEC>(beta + c, bt);
+#pragma unroll
+        for (int j = 0; j < VEC; j++) v[j] = (v[j] - m) * rs * gm[j] + bt[j];
+        if (s) {
+            float sv[VEC];
+            ld_vec<VEC>(s + r * C + c, sv);
+#pragma unroll
+            for (int j = 0; j < VEC; j++) v[j] += sv[j];
+        }
+#pragma unroll
+        for (int j = 0; j < VEC; j++) u[j] = lrelu02(v[j]);
+        if (y) st_vec<VEC>(y + r * C + c, v);
+        const int64_t o = r * Cp + c;
+        if (y_planes) st_planes_vec<VEC>(y_planes, o, plane, P, v);
+        if (u_planes) st_planes_vec<VEC>(u_planes, o, plane, P, u);
     }
 }
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
 
+// decoder gate: a (rows, 2C); hn = GN2(a)*gamma+beta; g = tanh(hn[:C]) * sigmoid(hn[C:]) -> planes (rows, Cp)
+template <int VEC>
 __global__ void dec_gate_kernel(const float* __restrict__ a, const float* __restrict__ mean,
                                 const float* __restrict__ rstd, const float* __restrict__ gamma,
-                                const float* __restrict__ beta, int B, int C, int T, int Tp, int P,
+                                const float* __restrict__ beta, int64_t rows, int C, int T, int Cp, int P,
                                 bf16* __restrict__ g_planes) {
-    const int64_t n = (int64_t)B * C * T, plane = (int64_t)B * C * Tp;
+    const int Cv = C / VEC;
+    const int64_t n = rows * Cv, plane = rows * Cp;
     GRID_STRIDE(i, n) {
-        const int64_t r = i / T;
-        const int t = (int)(i - r * T);
-        const int b = (int)(r / C), c = (int)(r - (int64_t)b * C);
-        const int64_t i1 = ((int64_t)b * 2 * C + c) * T + t, i2 = i1 + (int64_t)C * T;
-        const float h1 = (a[i1] - mean[2 * b]) * rstd[2 * b] * gamma[c] + beta[c];
-        const float h2 = (a[i2] - mean[2 * b + 1]) * rstd[2 * b + 1] * gamma[C + c] + beta[C + c];
-        store_planes(g_planes, r * Tp + t, plane, P, tanhf(h1) * sigmoidf_(h2));
+        const int64_t r = i / Cv;
+        const int c = (int)(i - r * Cv) * VEC;
+        const int b = (int)(r / T);
+        const float m1 = mean[2 * b], r1 = rstd[2 * b], m2 = mean[2 * b + 1], r2 = rstd[2 * b + 1];
+        float a1[VEC], a2[VEC], g1[VEC], g2[VEC], b1[VEC], b2[VEC], o[VEC];
+        ld_vec<VEC>(a + r * 2 * C + c, a1);
+        ld_vec<VEC>(a + r * 2 * C + C + c, a2);
+        ld_vec<VEC>(gamma + c, g1);
+        ld_vec<VEC>(gamma + C + c, g2);
+        ld_vec<VEC>(beta + c, b1);
+        ld_vec<VEC>(beta + C + c, b2);
+#pragma unroll
+        for (int j = 0; j < VEC; j++) {
+            const float h1 = (a1[j] - m1) * r1 * g1[j] + b1[j];
+            const float h2 = (a2[j] - m2) * r2 * g2[j] + b2[j];
+            o[j] = tanhf(h1) * sigmoidf_(h2);
+        }
+        st_planes_vec<VEC>(g_planes, r * Cp + c, plane, P, o);
     }
 }
 
-__global__ void dec_out_kernel(const float* __restrict__ r, const float* __restrict__ x, int B, int C, int S, int T,
-                               int Tp, int P, float* __restrict__ x_out, bf16* __restrict__ x_planes,
+// decoder residual/skip split: r (rows, C+S): x_out = r[:C] + x ; skip_sum (+)= r[C:]
+template <int VEC>
+__global__ void dec_out_kernel(const float* __restrict__ r, const float* __restrict__ x, int64_t rows, int C, int S,
+                               int Cp, int P, float* __restrict__ x_out, bf16* __restrict__ x_planes,
                                float* __restrict__ skip_sum, int first) {
-    const int Cc = C + S;
-    const int64_t n = (int64_t)B * Cc * T, plane = (int64_t)B * C * Tp;
+    const int Cc = C + S, Cv = Cc / VEC;
+    const int64_t n = rows * Cv, plane = rows * Cp;
     GRID_STRIDE(i, n) {
-        const int64_t row = i / T;
-        const int t = (int)(i - row * T);
-        const int b = (int)(row / Cc), c = (int)(row - (int64_t)b * Cc);
-        const float v = r[i];
+        const int64_t row = i / Cv;
+        const int c = (int)(i - row * Cv) * VEC;
+        float v[VEC];
+        ld_vec<VEC>(r + row * Cc + c, v);
         if (c < C) {
-            const int64_t o = ((int64_t)b * C + c) * T + t;
-            const float xo = v + x[o];
-            if (x_out) x_out[o] = xo;
-            if (x_planes) store_planes(x_planes, ((int64_t)b * C + c) * Tp + t, plane, P, xo);
+            float xv[VEC];
+            ld_vec<VEC>(x + row * C + c, xv);
+#pragma unroll
+            for (int j = 0; j < VEC; j++) v[j] += xv[j];
+            if (x_out) st_vec<VEC>(x_out + row * C + c, v);
+            if (x_planes) st_planes_vec<VEC>(x_planes, row * Cp + c, plane, P, v);
         } else if (skip_sum) {
-            const int64_t o = ((int64_t)b * S + (c - C)) * T + t;
-            skip_sum[o] = first ? v : skip_sum[o] + v;
+            float* sp = skip_sum + row * S + (c - C);
+            if (!first) {
+                float sv[VEC];
+                ld_vec<VEC>(sp, sv);
+#pragma unroll
+                for (int j = 0; j < VEC; j++) v[j] += sv[j];
+            }
+            st_vec<VEC>(sp, v);
         }
     }
 }
@@ -123,59 +264,88 @@ __global__ void dec_out_kernel(const float* __restrict__ r, const float* __restr
 }  // namespace vnb
 using namespace vnb;
 
-extern "C" int vnb_make_planes(const float* x, int B, int C, int T, int Tp, int P, float scale, int act, void* out_id,
+#define ST ((cudaStream_t)stream)
+
+extern "C" int vnb_transpose(const float* in, int B, int R, int S, float* out, void* stream) {
+    VNB_REQUIRE(in && out && B > 0 && R > 0 && S > 0 && B <= 65535, "transpose: bad arguments");
+    dim3 grid(ceil_div(S, 32), ceil_div(R, 32), B);
+    transpose_kernel<<<grid, 256, 0, ST>>>(in, R, S, out);
+    VNB_LAUNCH_CHECK("transpose");
+    return VNB_OK;
+}
+
+extern "C" int vnb_make_planes(const float* x, int B, int C, int T, int P, float scale, int act, void* out_id,
                                void* out_act, void* stream) {
-    VNB_REQUIRE(x && (out_id || out_act) && B > 0 && C > 0 && T > 0 && Tp >= T && (P == 1 || P == 3), "make_planes: bad arguments");
-    const int64_t rows = (int64_t)B * C;
-    make_planes_kernel<<<ew_grid(rows * T), EW_THREADS, 0, (cudaStream_t)stream>>>(x, rows, T, Tp, P, scale, act,
-                                                                                  (bf16*)out_id, (bf16*)out_act);
+    VNB_REQUIRE(x && (out_id || out_act) && B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "make_planes: bad arguments");
+    const int64_t rows = (int64_t)B * T;
+    VEC_DISPATCH((C & 3) == 0, make_planes_kernel, rows * C, ST, x, rows, C, round_up8(C), P, scale, act, (bf16*)out_id,
+                 (bf16*)out_act);
     VNB_LAUNCH_CHECK("make_planes");
     return VNB_OK;
 }
 
-extern "C" int vnb_concat_planes(const float* xa, int Ca, const float* xb, int Cb, int B, int T, int Tp, int P,
-                                 void* out, void* stream) {
-    VNB_REQUIRE(xa && xb && out && Ca > 0 && Cb > 0 && B > 0 && T > 0 && Tp >= T && (P == 1 || P == 3), "concat_planes: bad arguments");
-    concat_planes_kernel<<<ew_grid((int64_t)B * (Ca + Cb) * T), EW_THREADS, 0, (cudaStream_t)stream>>>(
-        xa, Ca, xb, Cb, B, T, Tp, P, (bf16*)out);
+extern "C" int vnb_concat_planes(const float* xa, int Ca, const float* xb, int Cb, int B, int T, int P, void* out,
+                                 void* stream) {
+    VNB_REQUIRE(xa && xb && out && Ca > 0 && Cb > 0 && B > 0 && T > 0 && (P == 1 || P == 3), "concat_planes: bad arguments");
+    const int64_t rows = (int64_t)B * T;
+    VEC_DISPATCH(((Ca | Cb) & 3) == 0, concat_planes_kernel, rows * (Ca + Cb), ST, xa, Ca, xb, Cb, rows,
+                 round_up8(Ca + Cb), P, (bf16*)out);
     VNB_LAUNCH_CHECK("concat_planes");
     return VNB_OK;
 }
 
-extern "C" int vnb_gn_stats(const float* h, int B, int C, int T, int groups, float eps, float* mean, float* rstd,
-                            void* stream) {
-    VNB_REQUIRE(h && mean && rstd && B > 0 && groups > 0 && C % groups == 0 && T > 0, "gn_stats: bad arguments");
-    gn_stats_kernel<<<B * groups, 512, 0, (cudaStream_t)stream>>>(h, (int64_t)(C / groups) * T, eps, mean, rstd);
-    VNB_LAUNCH_CHECK("gn_stats");
+extern "C" int vnb_gn_stats_ws_floats(int B, int groups) { return B * groups * GN_MAX_CHUNKS * 2; }
+
+extern "C" int vnb_gn_stats(const float* h, int B, int C, int T, int groups, float eps, float* ws, float* mean,
+                            float* rstd, void* stream) {
+    VNB_REQUIRE(h && ws && mean && rstd && B > 0 && B <= 65535 && groups > 0 && groups <= GN_MAX_GROUPS &&
+                    C % groups == 0 && T > 0, "gn_stats: bad arguments");
+    int rows_per = 8192 / C;
+    if (rows_per < 1) rows_per = 1;
+    int chunks = ceil_div(T, rows_per);
+    if (chunks > GN_MAX_CHUNKS) {
+        chunks = GN_MAX_CHUNKS;
+        rows_per = ceil_div(T, chunks);
+        chunks = ceil_div(T, rows_per);
+    }
+    gn_stats_partial_kernel<<<dim3(chunks, B), 256, 0, ST>>>(h, C, T, groups, rows_per, ws);
+    VNB_LAUNCH_CHECK("gn_stats_partial");
+    const int BG = B * groups;
+    gn_stats_merge_kernel<<<ceil_div((int64_t)BG * 32, 128), 128, 0, ST>>>(ws, BG, chunks, T, rows_per, C / groups, eps,
+                                                                           mean, rstd);
+    VNB_LAUNCH_CHECK("gn_stats_merge");
     return VNB_OK;
 }
 
 extern "C" int vnb_enc_out(const float* h, const float* s, const float* mean, const float* rstd, const float* gamma,
-                           const float* beta, int B, int C, int T, int Tp, int P, float* y, void* y_planes,
-                           void* u_planes, void* stream) {
+                           const float* beta, int B, int C, int T, int P, float* y, void* y_planes, void* u_planes,
+                           void* stream) {
     VNB_REQUIRE(h && mean && rstd && gamma && beta && (y || y_planes || u_planes), "enc_out: null pointer");
-    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && Tp >= T && (P == 1 || P == 3), "enc_out: bad shape");
-    enc_out_kernel<<<ew_grid((int64_t)B * C * T), EW_THREADS, 0, (cudaStream_t)stream>>>(
-        h, s, mean, rstd, gamma, beta, B, C, T, Tp, P, y, (bf16*)y_planes, (bf16*)u_planes);
+    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "enc_out: bad shape");
+    const int64_t rows = (int64_t)B * T;
+    VEC_DISPATCH((C & 3) == 0, enc_out_kernel, rows * C, ST, h, s, mean, rstd, gamma, beta, rows, C, T, round_up8(C), P,
+                 y, (bf16*)y_planes, (bf16*)u_planes);
     VNB_LAUNCH_CHECK("enc_out");
     return VNB_OK;
 }
 
 extern "C" int vnb_dec_gate(const float* a, const float* mean, const float* rstd, const float* gamma,
-                            const float* beta, int B, int C, int T, int Tp, int P, void* g_planes, void* stream) {
+                            const float* beta, int B, int C, int T, int P, void* g_planes, void* stream) {
     VNB_REQUIRE(a && mean && rstd && gamma && beta && g_planes, "dec_gate: null pointer");
-    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && Tp >= T && (P == 1 || P == 3), "dec_gate: bad shape");
-    dec_gate_kernel<<<ew_grid((int64_t)B * C * T), EW_THREADS, 0, (cudaStream_t)stream>>>(a, mean, rstd, gamma, beta, B,
-                                                                                         C, T, Tp, P, (bf16*)g_planes);
+    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "dec_gate: bad shape");
+    const int64_t rows = (int64_t)B * T;
+    VEC_DISPATCH((C & 3) == 0, dec_gate_kernel, rows * C, ST, a, mean, rstd, gamma, beta, rows, C, T, round_up8(C), P,
+                 (bf16*)g_planes);
     VNB_LAUNCH_CHECK("dec_gate");
     return VNB_OK;
 }
 
-extern "C" int vnb_dec_out(const float* r, const float* x, int B, int C, int S, int T, int Tp, int P, float* x_out,
+extern "C" int vnb_dec_out(const float* r, const float* x, int B, int C, int S, int T, int P, float* x_out,
                            void* x_planes, float* skip_sum, int first, void* stream) {
-    VNB_REQUIRE(r && x && B > 0 && C > 0 && S >= 0 && T > 0 && Tp >= T && (P == 1 || P == 3), "dec_out: bad arguments");
-    dec_out_kernel<<<ew_grid((int64_t)B * (C + S) * T), EW_THREADS, 0, (cudaStream_t)stream>>>(
-        r, x, B, C, S, T, Tp, P, x_out, (bf16*)x_planes, skip_sum, first);
+    VNB_REQUIRE(r && x && B > 0 && C > 0 && S >= 0 && T > 0 && (P == 1 || P == 3), "dec_out: bad arguments");
+    const int64_t rows = (int64_t)B * T;
+    VEC_DISPATCH(((C | S) & 3) == 0, dec_out_kernel, rows * (C + S), ST, r, x, rows, C, S, round_up8(C), P, x_out,
+                 (bf16*)x_planes, skip_sum, first);
     VNB_LAUNCH_CHECK("dec_out");
     return VNB_OK;
 }

@@ -8,7 +8,7 @@ namespace vnb {
 constexpr int EW_THREADS = 256;
 static inline int ew_grid(int64_t n) {
     int64_t g = (n + EW_THREADS - 1) / EW_THREADS;
-    const int64_t cap = 148 * 16;
+    const int64_t cap = 148 * 8;
     return (int)(g < cap ? g : cap);
 }
 #define GRID_STRIDE(i, n) \
@@ -16,18 +16,18 @@ static inline int ew_grid(int64_t n) {
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
 
-// gradient wrt the normalised+affine gate input row c2 in [0,2C) at (b,t), recomputed from dg
+// gradient wrt the normalised+affine gate input channel c2 in [0,2C) of frame row r (channels-last:
+// a (rows, 2C), dg (rows, C)), recomputed from dg
 __device__ __forceinline__ float gate_dn(const float* __restrict__ dg, const float* __restrict__ a,
                                          const float* __restrict__ mean, const float* __restrict__ rstd,
-                                         const float* __restrict__ gamma, const float* __restrict__ beta, int b, int c2,
-                                         int t, int C, int T, float& xhat) {
+                                         const float* __restrict__ gamma, const float* __restrict__ beta, int b,
+                                         int64_t r, int c2, int C, float& xhat) {
     const int c = c2 < C ? c2 : c2 - C;
-    const int64_t i1 = ((int64_t)b * 2 * C + c) * T + t, i2 = i1 + (int64_t)C * T;
-    const float x1 = (a[i1] - mean[2 * b]) * rstd[2 * b];
-    const float x2 = (a[i2] - mean[2 * b + 1]) * rstd[2 * b + 1];
+    const float x1 = (a[r * 2 * C + c] - mean[2 * b]) * rstd[2 * b];
+    const float x2 = (a[r * 2 * C + C + c] - mean[2 * b + 1]) * rstd[2 * b + 1];
     const float th = tanhf(x1 * gamma[c] + beta[c]);
     const float sg = sigmoidf_(x2 * gamma[C + c] + beta[C + c]);
-    const float d = dg[((int64_t)b * C + c) * T + t];
+    const float d = dg[r * C + c];
     if (c2 < C) {
         xhat = x1;
         return d * sg * (1.f - th * th);
@@ -36,60 +36,42 @@ __device__ __forceinline__ float gate_dn(const float* __restrict__ dg, const flo
     return d * th * sg * (1.f - sg);
 }
 
-// one warp per (b,c) row: R[row] = { sum_t dn, sum_t dn*xhat, sum_t xhat }
-__global__ void __launch_bounds__(256) gn_bwd_rows_kernel(const float* __restrict__ dn, const float* __restrict__ h,
-                                                          const float* __restrict__ mean,
-                                                          const float* __restrict__ rstd, int B, int C, int T,
-                                                          int groups, float* __restrict__ R) {
-    const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (row >= (int64_t)B * C) return;
-    const int lane = threadIdx.x & 31;
-    const int b = (int)(row / C), c = (int)(row - (int64_t)b * C);
-    const int gi = b * groups + c / (C / groups);
-    const float m = mean[gi], rs = rstd[gi];
+// R[b,c] = { sum_t dn, sum_t dn*xhat, sum_t xhat }.  grid (ceil(C/32), B), block 32 x 8: a warp reads
+// 32 consecutive channels of one frame, the 8 warps stride over frames, shared-memory reduce.
+template <bool GATE>
+__global__ void __launch_bounds__(256) bwd_rows_kernel(const float* __restrict__ dn, const float* __restrict__ h,
+                                                       const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                       int Cn, int T, int groups, float* __restrict__ R) {
+    __shared__ float red[3][8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int b = blockIdx.y, c = blockIdx.x * 32 + tx;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f;
-    for (int t = lane; t < T; t += 32) {
-        const float d = dn[row * T + t];
-        const float xh = (h[row * T + t] - m) * rs;
-        s0 += d;
-        s1 += d * xh;
-        s2 += xh;
+    if (c < Cn) {
+        const int gi = b * groups + c / (Cn / groups);
+        const float m = mean[gi], rs = rstd[gi];
+        for (int t = ty; t < T; t += 8) {
+            const int64_t r = (int64_t)b * T + t;
+            float d, xh;
+            if (GATE) d = gate_dn(dn, h, mean, rstd, gamma, beta, b, r, c, Cn / 2, xh);
+            else {
+                d = dn[r * Cn + c];
+                xh = (h[r * Cn + c] - m) * rs;
+            }
+            s0 += d;
+            s1 += d * xh;
+            s2 += xh;
+        }
     }
-    s0 = warp_sum(s0);
-    s1 = warp_sum(s1);
-    s2 = warp_sum(s2);
-    if (lane == 0) {
-        R[row * 3 + 0] = s0;
-        R[row * 3 + 1] = s1;
-        R[row * 3 + 2] = s2;
-    }
-}
-
-__global__ void __launch_bounds__(256) gate_bwd_rows_kernel(const float* __restrict__ dg, const float* __restrict__ a,
-                                                            const float* __restrict__ mean,
-                                                            const float* __restrict__ rstd,
-                                                            const float* __restrict__ gamma,
-                                                            const float* __restrict__ beta, int B, int C, int T,
-                                                            float* __restrict__ R) {
-    const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (row >= (int64_t)B * 2 * C) return;
-    const int lane = threadIdx.x & 31;
-    const int b = (int)(row / (2 * C)), c2 = (int)(row - (int64_t)b * 2 * C);
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f;
-    for (int t = lane; t < T; t += 32) {
-        float xh;
-        const float d = gate_dn(dg, a, mean, rstd, gamma, beta, b, c2, t, C, T, xh);
-        s0 += d;
-        s1 += d * xh;
-        s2 += xh;
-    }
-    s0 = warp_sum(s0);
-    s1 = warp_sum(s1);
-    s2 = warp_sum(s2);
-    if (lane == 0) {
-        R[row * 3 + 0] = s0;
-        R[row * 3 + 1] = s1;
-        R[row * 3 + 2] = s2;
+    red[0][ty][tx] = s0;
+    red[1][ty][tx] = s1;
+    red[2][ty][tx] = s2;
+    __syncthreads();
+    if (ty < 3 && c < Cn) {
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; j++) s += red[ty][j][tx];
+        R[((int64_t)b * Cn + c) * 3 + ty] = s;
     }
 }
 
@@ -143,46 +125,59 @@ __global__ void gn_bwd_channel_kernel(const float* __restrict__ R, const float* 
     if (dpre_csum) dpre_csum[c] = dcs;
 }
 
+template <int VEC>
 __global__ void gn_bwd_apply_kernel(const float* __restrict__ dn, const float* __restrict__ h,
                                     const float* __restrict__ mean, const float* __restrict__ rstd,
-                                    const float* __restrict__ gamma, const float* __restrict__ S, int B, int C, int T,
-                                    int groups, int Tp, int P, bf16* __restrict__ dpre_planes,
+                                    const float* __restrict__ gamma, const float* __restrict__ S, int64_t rows, int C,
+                                    int T, int groups, int Cp, int P, bf16* __restrict__ dpre_planes,
                                     bf16* __restrict__ dn_planes) {
-    const int64_t n = (int64_t)B * C * T, plane = (int64_t)B * C * Tp;
+    const int Cv = C / VEC;
+    const int64_t n = rows * Cv, plane = rows * Cp;
     const int cg = C / groups;
     const float inv_n = 1.f / ((float)cg * (float)T);
     GRID_STRIDE(i, n) {
-        const int64_t r = i / T;
-        const int t = (int)(i - r * T);
-        const int b = (int)(r / C), c = (int)(r - (int64_t)b * C);
-        const int gi = b * groups + c / cg;
-        const float rs = rstd[gi];
-        const float xh = (h[i] - mean[gi]) * rs;
-        const float d = dn[i];
-        const float v = rs * (gamma[c] * d - S[gi * 2] * inv_n - xh * S[gi * 2 + 1] * inv_n);
-        const int64_t o = r * Tp + t;
-        store_planes(dpre_planes, o, plane, P, v);
-        if (dn_planes) store_planes(dn_planes, o, plane, P, d);
+        const int64_t r = i / Cv;
+        const int c = (int)(i - r * Cv) * VEC;
+        const int b = (int)(r / T);
+        float d[VEC], hv[VEC], v[VEC];
+        ld_vec<VEC>(dn + r * C + c, d);
+        ld_vec<VEC>(h + r * C + c, hv);
+#pragma unroll
+        for (int j = 0; j < VEC; j++) {
+            const int gi = b * groups + (c + j) / cg;
+            const float rs = rstd[gi];
+            const float xh = (hv[j] - mean[gi]) * rs;
+            v[j] = rs * (gamma[c + j] * d[j] - S[gi * 2] * inv_n - xh * S[gi * 2 + 1] * inv_n);
+        }
+        const int64_t o = r * Cp + c;
+        st_planes_vec<VEC>(dpre_planes, o, plane, P, v);
+        if (dn_planes) st_planes_vec<VEC>(dn_planes, o, plane, P, d);
     }
 }
 
+// da planes (rows, (2C)p) from dg (rows, C), a (rows, 2C)
+template <int VEC>
 __global__ void gate_bwd_apply_kernel(const float* __restrict__ dg, const float* __restrict__ a,
                                       const float* __restrict__ mean, const float* __restrict__ rstd,
                                       const float* __restrict__ gamma, const float* __restrict__ beta,
-                                      const float* __restrict__ S, int B, int C, int T, int Tp, int P,
+                                      const float* __restrict__ S, int64_t rows, int C, int T, int Cp, int P,
                                       bf16* __restrict__ da_planes) {
-    const int C2 = 2 * C;
-    const int64_t n = (int64_t)B * C2 * T, plane = (int64_t)B * C2 * Tp;
+    const int C2 = 2 * C, Cv = C2 / VEC;
+    const int64_t n = rows * Cv, plane = rows * Cp;
     const float inv_n = 1.f / ((float)C * (float)T);
     GRID_STRIDE(i, n) {
-        const int64_t r = i / T;
-        const int t = (int)(i - r * T);
-        const int b = (int)(r / C2), c2 = (int)(r - (int64_t)b * C2);
-        const int gi = b * 2 + (c2 >= C ? 1 : 0);
-        float xh;
-        const float d = gate_dn(dg, a, mean, rstd, gamma, beta, b, c2, t, C, T, xh);
-        const float v = rstd[gi] * (gamma[c2] * d - S[gi * 2] * inv_n - xh * S[gi * 2 + 1] * inv_n);
-        store_planes(da_planes, r * Tp + t, plane, P, v);
+        const int64_t r = i / Cv;
+        const int c2 = (int)(i - r * Cv) * VEC;
+        const int b = (int)(r / T);
+        float v[VEC];
+#pragma unroll
+        for (int j = 0; j < VEC; j++) {
+            const int gi = b * 2 + (c2 + j >= C ? 1 : 0);
+            float xh;
+            const float d = gate_dn(dg, a, mean, rstd, gamma, beta, b, r, c2 + j, C, xh);
+            v[j] = rstd[gi] * (gamma[c2 + j] * d - S[gi * 2] * inv_n - xh * S[gi * 2 + 1] * inv_n);
+        }
+        st_planes_vec<VEC>(da_planes, r * Cp + c2, plane, P, v);
     }
 }
 
@@ -196,18 +191,23 @@ __global__ void act_bwd_add_kernel(const float* __restrict__ du, const float* __
     }
 }
 
-// one block per channel
-__global__ void __launch_bounds__(256) channel_sum_kernel(const float* __restrict__ x, int B, int C, int T,
-                                                          float* __restrict__ out) {
-    __shared__ float red[32];
-    const int c = blockIdx.x;
+// out[c] = sum over the B*T frame rows; one block (32 x 32) per 32 channels
+__global__ void __launch_bounds__(1024) channel_sum_kernel(const float* __restrict__ x, int64_t rows, int C,
+                                                           float* __restrict__ out) {
+    __shared__ float red[32][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
     float s = 0.f;
-    for (int b = 0; b < B; b++) {
-        const float* p = x + ((int64_t)b * C + c) * T;
-        for (int t = threadIdx.x; t < T; t += blockDim.x) s += p[t];
+    if (c < C)
+        for (int64_t r = ty; r < rows; r += 32) s += x[r * C + c];
+    red[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0 && c < C) {
+        float t = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; j++) t += red[j][tx];
+        out[c] = t;
     }
-    s = block_sum(s, red);
-    if (threadIdx.x == 0) out[c] = s;
 }
 
 }  // namespace vnb
@@ -215,16 +215,20 @@ using namespace vnb;
 
 extern "C" int vnb_gn_bwd_rows(const float* dn, const float* h, const float* mean, const float* rstd, int B, int C,
                                int T, int groups, float* R, void* stream) {
-    VNB_REQUIRE(dn && h && mean && rstd && R && B > 0 && C > 0 && T > 0 && groups > 0 && C % groups == 0, "gn_bwd_rows: bad arguments");
-    gn_bwd_rows_kernel<<<ceil_div((int64_t)B * C, 8), 256, 0, (cudaStream_t)stream>>>(dn, h, mean, rstd, B, C, T, groups, R);
+    VNB_REQUIRE(dn && h && mean && rstd && R && B > 0 && B <= 65535 && C > 0 && T > 0 && groups > 0 && C % groups == 0,
+                "gn_bwd_rows: bad arguments");
+    bwd_rows_kernel<false><<<dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream>>>(dn, h, mean, rstd, nullptr, nullptr,
+                                                                                       C, T, groups, R);
     VNB_LAUNCH_CHECK("gn_bwd_rows");
     return VNB_OK;
 }
 
 extern "C" int vnb_gate_bwd_rows(const float* dg, const float* a, const float* mean, const float* rstd,
                                  const float* gamma, const float* beta, int B, int C, int T, float* R, void* stream) {
-    VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && R && B > 0 && C > 0 && T > 0, "gate_bwd_rows: bad arguments");
-    gate_bwd_rows_kernel<<<ceil_div((int64_t)B * 2 * C, 8), 256, 0, (cudaStream_t)stream>>>(dg, a, mean, rstd, gamma, beta, B, C, T, R);
+    VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && R && B > 0 && B <= 65535 && C > 0 && T > 0,
+                "gate_bwd_rows: bad arguments");
+    bwd_rows_kernel<true><<<dim3(ceil_div(2 * C, 32), B), 256, 0, (cudaStream_t)stream>>>(dg, a, mean, rstd, gamma, beta,
+                                                                                          2 * C, T, 2, R);
     VNB_LAUNCH_CHECK("gate_bwd_rows");
     return VNB_OK;
 }
@@ -241,24 +245,34 @@ extern "C" int vnb_gn_bwd_finalize(const float* R, const float* gamma, const flo
     return VNB_OK;
 }
 
+#define VEC_DISPATCH(cond4, KERNEL, n_scalar, st, ...)                                        \
+    do {                                                                                      \
+        if (cond4)                                                                            \
+            KERNEL<4><<<ew_grid((n_scalar) / 4), EW_THREADS, 0, st>>>(__VA_ARGS__);           \
+        else                                                                                  \
+            KERNEL<1><<<ew_grid(n_scalar), EW_THREADS, 0, st>>>(__VA_ARGS__);                 \
+    } while (0)
+
 extern "C" int vnb_gn_bwd_apply(const float* dn, const float* h, const float* mean, const float* rstd,
-                                const float* gamma, const float* S, int B, int C, int T, int groups, int Tp, int P,
+                                const float* gamma, const float* S, int B, int C, int T, int groups, int P,
                                 void* dpre_planes, void* dn_planes, void* stream) {
     VNB_REQUIRE(dn && h && mean && rstd && gamma && S && dpre_planes, "gn_bwd_apply: null pointer");
-    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && Tp >= T && groups > 0 && C % groups == 0 && (P == 1 || P == 3), "gn_bwd_apply: bad shape");
-    gn_bwd_apply_kernel<<<ew_grid((int64_t)B * C * T), EW_THREADS, 0, (cudaStream_t)stream>>>(
-        dn, h, mean, rstd, gamma, S, B, C, T, groups, Tp, P, (bf16*)dpre_planes, (bf16*)dn_planes);
+    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && groups > 0 && C % groups == 0 && (P == 1 || P == 3), "gn_bwd_apply: bad shape");
+    const int64_t rows = (int64_t)B * T;
+    VEC_DISPATCH((C & 3) == 0, gn_bwd_apply_kernel, rows * C, (cudaStream_t)stream, dn, h, mean, rstd, gamma, S, rows, C, T,
+                 groups, round_up8(C), P, (bf16*)dpre_planes, (bf16*)dn_planes);
     VNB_LAUNCH_CHECK("gn_bwd_apply");
     return VNB_OK;
 }
 
 extern "C" int vnb_gate_bwd_apply(const float* dg, const float* a, const float* mean, const float* rstd,
-                                  const float* gamma, const float* beta, const float* S, int B, int C, int T, int Tp,
-                                  int P, void* da_planes, void* stream) {
+                                  const float* gamma, const float* beta, const float* S, int B, int C, int T, int P,
+                                  void* da_planes, void* stream) {
     VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && S && da_planes, "gate_bwd_apply: null pointer");
-    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && Tp >= T && (P == 1 || P == 3), "gate_bwd_apply: bad shape");
-    gate_bwd_apply_kernel<<<ew_grid((int64_t)B * 2 * C * T), EW_THREADS, 0, (cudaStream_t)stream>>>(
-        dg, a, mean, rstd, gamma, beta, S, B, C, T, Tp, P, (bf16*)da_planes);
+    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "gate_bwd_apply: bad shape");
+    const int64_t rows = (int64_t)B * T;
+    VEC_DISPATCH((C & 3) == 0, gate_bwd_apply_kernel, rows * 2 * C, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, S,
+                 rows, C, T, round_up8(2 * C), P, (bf16*)da_planes);
     VNB_LAUNCH_CHECK("gate_bwd_apply");
     return VNB_OK;
 }
@@ -273,7 +287,7 @@ extern "C" int vnb_act_bwd_add(const float* du, const float* c, const float* add
 
 extern "C" int vnb_channel_sum(const float* x, int B, int C, int T, float* out, void* stream) {
     VNB_REQUIRE(x && out && B > 0 && C > 0 && T > 0, "channel_sum: bad arguments");
-    channel_sum_kernel<<<C, 256, 0, (cudaStream_t)stream>>>(x, B, C, T, out);
+    channel_sum_kernel<<<ceil_div(C, 32), 1024, 0, (cudaStream_t)stream>>>(x, (int64_t)B * T, C, out);
     VNB_LAUNCH_CHECK("channel_sum");
     return VNB_OK;
 }

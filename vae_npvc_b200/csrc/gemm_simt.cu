@@ -8,17 +8,18 @@ namespace vnb {
 
 constexpr int TM = 64, TN = 64, KC = 16;
 
-// out[b,co,t] = beta*out + bias + residual + sum_{tap,ci} W[tap][co][ci] * in[b,ci,t+off(tap)]
+// out[b,t,co] = (accumulate ? out : 0) + bias + residual + sum_{tap,ci} W[tap][co][ci] * in[b,t+off(tap),ci]
+// channels-last: rows = frames (one sample per blockIdx.z so that the zero padding is per sample)
 template <int P>
 __global__ void __launch_bounds__(256) conv_fwd_simt_kernel(
-    const bf16* __restrict__ in, int B, int Cin, int T, int Tp, const bf16* __restrict__ w, int taps, int dil,
-    int Cout, int Cin_p, const float* __restrict__ bias, int bias_bstride, const float* __restrict__ residual,
+    const bf16* __restrict__ in, int B, int Cin, int T, const bf16* __restrict__ w, int taps, int dil, int Cout,
+    int Cin_p, const float* __restrict__ bias, int bias_bstride, const float* __restrict__ residual,
     float* __restrict__ out, int accumulate) {
-    __shared__ float Ws[KC][TM + 4];
-    __shared__ float Xs[KC][TN + 4];
-    const int t0 = blockIdx.x * TN, co0 = blockIdx.y * TM, b = blockIdx.z;
+    __shared__ float Xs[KC][TM + 4];
+    __shared__ float Ws[KC][TN + 4];
+    const int t0 = blockIdx.x * TM, co0 = blockIdx.y * TN, b = blockIdx.z;
     const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
-    const int64_t in_plane = (int64_t)B * Cin * Tp;
+    const int64_t in_plane = (int64_t)B * T * Cin_p;
     const int64_t w_plane = (int64_t)taps * Cout * Cin_p;
     float acc[4][4];
 #pragma unroll
@@ -32,19 +33,19 @@ __global__ void __launch_bounds__(256) conv_fwd_simt_kernel(
 #pragma unroll
             for (int e = 0; e < 4; e++) {
                 const int idx = tid * 4 + e;
-                {   // W tile: 64 co x 16 ci, ci contiguous
-                    const int m = idx >> 4, kk = idx & 15;
-                    const int co = co0 + m, ci = c0 + kk;
+                const int m = idx >> 4, kk = idx & 15;       // 64 rows x 16 ci, ci contiguous
+                const int ci = c0 + kk;
+                {
+                    const int t = t0 + m + off;
+                    float x = 0.f;
+                    if (ci < Cin && t >= 0 && t < T) x = load_planes(in, ((int64_t)b * T + t) * Cin_p + ci, in_plane, P);
+                    Xs[kk][m] = x;
+                }
+                {
+                    const int co = co0 + m;
                     float x = 0.f;
                     if (co < Cout && ci < Cin) x = load_planes(w, ((int64_t)tap * Cout + co) * Cin_p + ci, w_plane, P);
                     Ws[kk][m] = x;
-                }
-                {   // X tile: 16 ci x 64 t, t contiguous, zero padded
-                    const int kk = idx >> 6, n = idx & 63;
-                    const int ci = c0 + kk, t = t0 + n + off;
-                    float x = 0.f;
-                    if (ci < Cin && t >= 0 && t < T) x = load_planes(in, ((int64_t)b * Cin + ci) * Tp + t, in_plane, P);
-                    Xs[kk][n] = x;
                 }
             }
             __syncthreads();
@@ -52,9 +53,9 @@ __global__ void __launch_bounds__(256) conv_fwd_simt_kernel(
             for (int kk = 0; kk < KC; kk++) {
                 float a[4], x[4];
 #pragma unroll
-                for (int i = 0; i < 4; i++) a[i] = Ws[kk][ty * 4 + i];
+                for (int i = 0; i < 4; i++) a[i] = Xs[kk][ty * 4 + i];
 #pragma unroll
-                for (int j = 0; j < 4; j++) x[j] = Xs[kk][tx * 4 + j];
+                for (int j = 0; j < 4; j++) x[j] = Ws[kk][tx * 4 + j];
 #pragma unroll
                 for (int i = 0; i < 4; i++)
 #pragma unroll
@@ -65,15 +66,14 @@ __global__ void __launch_bounds__(256) conv_fwd_simt_kernel(
     }
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-        const int co = co0 + ty * 4 + i;
-        if (co >= Cout) continue;
-        const float bv = bias ? bias[(int64_t)b * bias_bstride + co] : 0.f;
+        const int t = t0 + ty * 4 + i;
+        if (t >= T) continue;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const int t = t0 + tx * 4 + j;
-            if (t >= T) continue;
-            const int64_t o = ((int64_t)b * Cout + co) * T + t;
-            float r = acc[i][j] + bv;
+            const int co = co0 + tx * 4 + j;
+            if (co >= Cout) continue;
+            const int64_t o = ((int64_t)b * T + t) * Cout + co;
+            float r = acc[i][j] + (bias ? bias[(int64_t)b * bias_bstride + co] : 0.f);
             if (residual) r += residual[o];
             if (accumulate) r += out[o];
             out[o] = r;
@@ -81,17 +81,18 @@ __global__ void __launch_bounds__(256) conv_fwd_simt_kernel(
     }
 }
 
-// dW[co][ci][tap] = sum_{b,t} dy[b,co,t] * u[b,ci,t+off(tap)]
+// dW[co][ci][tap] = sum_{b,t} dy[b,t,co] * u[b,t+off(tap),ci]
 template <int P>
 __global__ void __launch_bounds__(256) conv_wgrad_simt_kernel(
-    const bf16* __restrict__ dy, const bf16* __restrict__ u, int B, int Cout, int Cin, int T, int Tp, int taps,
-    int dil, int transposed, float* __restrict__ dw) {
+    const bf16* __restrict__ dy, const bf16* __restrict__ u, int B, int Cout, int Cin, int T, int taps, int dil,
+    int transposed, float* __restrict__ dw) {
     __shared__ float As[KC][TM + 4];
     __shared__ float Bs[KC][TN + 4];
     const int ci0 = blockIdx.x * TN, co0 = blockIdx.y * TM, tap = blockIdx.z;
     const int off = (tap - (taps - 1) / 2) * dil;
     const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
-    const int64_t dy_plane = (int64_t)B * Cout * Tp, u_plane = (int64_t)B * Cin * Tp;
+    const int Cout_p = (Cout + 7) & ~7, Cin_p = (Cin + 7) & ~7;
+    const int64_t dy_plane = (int64_t)B * T * Cout_p, u_plane = (int64_t)B * T * Cin_p;
     float acc[4][4];
 #pragma unroll
     for (int i = 0; i < 4; i++)
@@ -102,19 +103,19 @@ __global__ void __launch_bounds__(256) conv_wgrad_simt_kernel(
 #pragma unroll
             for (int e = 0; e < 4; e++) {
                 const int idx = tid * 4 + e;
-                const int m = idx >> 4, kk = idx & 15;
+                const int kk = idx >> 6, m = idx & 63;       // 16 frames x 64 channels, channels contiguous
                 const int t = tt + kk;
                 {
                     const int co = co0 + m;
                     float x = 0.f;
-                    if (co < Cout && t < T) x = load_planes(dy, ((int64_t)b * Cout + co) * Tp + t, dy_plane, P);
+                    if (co < Cout && t < T) x = load_planes(dy, ((int64_t)b * T + t) * Cout_p + co, dy_plane, P);
                     As[kk][m] = x;
                 }
                 {
                     const int ci = ci0 + m, ts = t + off;
                     float x = 0.f;
                     if (ci < Cin && t < T && ts >= 0 && ts < T)
-                        x = load_planes(u, ((int64_t)b * Cin + ci) * Tp + ts, u_plane, P);
+                        x = load_planes(u, ((int64_t)b * T + ts) * Cin_p + ci, u_plane, P);
                     Bs[kk][m] = x;
                 }
             }
@@ -153,24 +154,17 @@ __global__ void __launch_bounds__(256) conv_wgrad_simt_kernel(
 constexpr int VQ_FR = 16;
 __global__ void __launch_bounds__(256) vq_lookup_simt_kernel(const float* __restrict__ zn, const float* __restrict__ z_sq,
                                                              const float* __restrict__ e_hat,
-                                                             const float* __restrict__ e_sq, int B, int D, int T,
+                                                             const float* __restrict__ e_sq, int64_t N, int D,
                                                              int K, int64_t* __restrict__ idx) {
     extern __shared__ float sm[];
     float* zs = sm;                                   // [VQ_FR][D]
     float* bd = sm + VQ_FR * D;                       // [VQ_FR][256] best distance
     int* bi = (int*)(bd + VQ_FR * 256);               // [VQ_FR][256] best index
-    const int64_t N = (int64_t)B * T;
     const int64_t n0 = (int64_t)blockIdx.x * VQ_FR;
     const int tid = threadIdx.x;
     for (int e = tid; e < VQ_FR * D; e += 256) {
-        const int f = e % VQ_FR, d = e / VQ_FR;
-        const int64_t n = n0 + f;
-        float x = 0.f;
-        if (n < N) {
-            const int64_t b = n / T, t = n - b * T;
-            x = zn[(b * D + d) * T + t];
-        }
-        zs[f * D + d] = x;
+        const int64_t n = n0 + e / D;
+        zs[e] = n < N ? zn[n0 * D + e] : 0.f;          // frames are contiguous rows of D floats
     }
     __syncthreads();
     float best[VQ_FR];
@@ -234,29 +228,29 @@ __global__ void __launch_bounds__(256) vq_lookup_simt_kernel(const float* __rest
     }
 }
 
-int conv_fwd_simt(const void* in, int P, int B, int Cin, int T, int Tp, const void* w, int taps, int dil, int Cout,
+int conv_fwd_simt(const void* in, int P, int B, int Cin, int T, const void* w, int taps, int dil, int Cout,
                   const float* bias, int bias_bstride, const float* residual, float* out, int accumulate,
                   cudaStream_t st) {
-    dim3 grid(ceil_div(T, TN), ceil_div(Cout, TM), B);
+    dim3 grid(ceil_div(T, TM), ceil_div(Cout, TN), B);
     const int Cin_p = round_up8(Cin);
     if (P == 1)
-        conv_fwd_simt_kernel<1><<<grid, 256, 0, st>>>((const bf16*)in, B, Cin, T, Tp, (const bf16*)w, taps, dil, Cout,
-                                                      Cin_p, bias, bias_bstride, residual, out, accumulate);
+        conv_fwd_simt_kernel<1><<<grid, 256, 0, st>>>((const bf16*)in, B, Cin, T, (const bf16*)w, taps, dil, Cout, Cin_p,
+                                                      bias, bias_bstride, residual, out, accumulate);
     else
-        conv_fwd_simt_kernel<3><<<grid, 256, 0, st>>>((const bf16*)in, B, Cin, T, Tp, (const bf16*)w, taps, dil, Cout,
-                                                      Cin_p, bias, bias_bstride, residual, out, accumulate);
+        conv_fwd_simt_kernel<3><<<grid, 256, 0, st>>>((const bf16*)in, B, Cin, T, (const bf16*)w, taps, dil, Cout, Cin_p,
+                                                      bias, bias_bstride, residual, out, accumulate);
     VNB_LAUNCH_CHECK("conv_fwd_simt");
     return VNB_OK;
 }
 
-int conv_wgrad_simt(const void* dy, const void* u, int P, int B, int Cout, int Cin, int T, int Tp, int taps, int dil,
+int conv_wgrad_simt(const void* dy, const void* u, int P, int B, int Cout, int Cin, int T, int taps, int dil,
                     int transposed, float* dw, cudaStream_t st) {
     dim3 grid(ceil_div(Cin, TN), ceil_div(Cout, TM), taps);
     if (P == 1)
-        conv_wgrad_simt_kernel<1><<<grid, 256, 0, st>>>((const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, Tp, taps, dil,
+        conv_wgrad_simt_kernel<1><<<grid, 256, 0, st>>>((const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, taps, dil,
                                                         transposed, dw);
     else
-        conv_wgrad_simt_kernel<3><<<grid, 256, 0, st>>>((const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, Tp, taps, dil,
+        conv_wgrad_simt_kernel<3><<<grid, 256, 0, st>>>((const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, taps, dil,
                                                         transposed, dw);
     VNB_LAUNCH_CHECK("conv_wgrad_simt");
     return VNB_OK;
@@ -273,7 +267,7 @@ int vq_lookup_simt(const float* zn, const float* z_sq, const float* e_hat, const
             return VNB_E_CUDA;
         }
     }
-    vq_lookup_simt_kernel<<<ceil_div(N, VQ_FR), 256, smem, st>>>(zn, z_sq, e_hat, e_sq, B, D, T, K, idx);
+    vq_lookup_simt_kernel<<<ceil_div(N, VQ_FR), 256, smem, st>>>(zn, z_sq, e_hat, e_sq, N, D, K, idx);
     VNB_LAUNCH_CHECK("vq_lookup_simt");
     return VNB_OK;
 }

@@ -44,54 +44,58 @@ __global__ void __launch_bounds__(128) vq_prep_codebook_kernel(float* __restrict
     if (threadIdx.x == 0 && e_sq) e_sq[k] = q;
 }
 
-// one thread per frame (t fastest => coalesced over the NCT layout)
-__global__ void vq_prep_z_kernel(const float* __restrict__ z, int B, int D, int T, int Tp, int normalize,
-                                 float* __restrict__ zn, bf16* __restrict__ z_planes, float* __restrict__ z_sq,
-                                 float* __restrict__ z_norm) {
-    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= (int64_t)B * T) return;
-    const int64_t b = n / T, t = n - b * T;
-    const float* p = z + b * D * T + t;
+// Frames are rows of the channels-last latent: z (N = B*T, D).  One warp per frame, lanes over d.
+constexpr int VQ_WARPS = 8;
+
+__global__ void __launch_bounds__(VQ_WARPS * 32) vq_prep_z_kernel(const float* __restrict__ z, int64_t N, int D, int Dp,
+                                                                  int normalize, float* __restrict__ zn,
+                                                                  bf16* __restrict__ z_planes, float* __restrict__ z_sq,
+                                                                  float* __restrict__ z_norm) {
+    const int64_t n = (int64_t)blockIdx.x * VQ_WARPS + (threadIdx.x >> 5);
+    if (n >= N) return;
+    const int lane = threadIdx.x & 31;
+    const float* p = z + n * D;
     float ss = 0.f;
-    for (int d = 0; d < D; d++) {
-        const float v = p[(int64_t)d * T];
-        ss += v * v;
-    }
+    for (int d = lane; d < D; d += 32) ss += p[d] * p[d];
+    ss = warp_sum(ss);
     const float nrm = sqrtf(ss);
-    const int64_t plane = (int64_t)B * D * Tp;
+    const int64_t plane = N * Dp;
     float q = 0.f;
-    for (int d = 0; d < D; d++) {
-        float v = p[(int64_t)d * T];
+    for (int d = lane; d < D; d += 32) {
+        float v = p[d];
         if (normalize) v = v / nrm;
-        if (zn) zn[(b * D + d) * T + t] = v;
-        if (z_planes) store_planes(z_planes, (b * D + d) * Tp + t, plane, 3, v);
+        if (zn) zn[n * D + d] = v;
+        if (z_planes) store_planes(z_planes, n * Dp + d, plane, 3, v);
         q += v * v;
     }
-    if (z_sq) z_sq[n] = q;
-    if (z_norm) z_norm[n] = nrm;
+    q = warp_sum(q);
+    if (lane == 0) {
+        if (z_sq) z_sq[n] = q;
+        if (z_norm) z_norm[n] = nrm;
+    }
 }
 
-__global__ void __launch_bounds__(256) vq_gather_kernel(const int64_t* __restrict__ idx,
-                                                        const float* __restrict__ e_hat,
-                                                        const float* __restrict__ zn, const float* __restrict__ z,
-                                                        int B, int D, int T, int K, float* __restrict__ q_out,
-                                                        float* __restrict__ sums, int* __restrict__ counts) {
+__global__ void __launch_bounds__(VQ_WARPS * 32) vq_gather_kernel(const int64_t* __restrict__ idx,
+                                                                  const float* __restrict__ e_hat,
+                                                                  const float* __restrict__ zn,
+                                                                  const float* __restrict__ z, int64_t N, int D,
+                                                                  float* __restrict__ q_out, float* __restrict__ sums,
+                                                                  int* __restrict__ counts) {
     __shared__ float red[32];
-    const int64_t N = (int64_t)B * T;
-    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t n = (int64_t)blockIdx.x * VQ_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
     float lq = 0.f, ln = 0.f;
     if (n < N) {
-        const int64_t b = n / T, t = n - b * T;
         const int k = (int)idx[n];
         const float* er = e_hat + (int64_t)k * D;
-        for (int d = 0; d < D; d++) {
-            const int64_t o = (b * D + d) * T + t;
+        for (int d = lane; d < D; d += 32) {
+            const int64_t o = n * D + d;
             const float q = er[d], a = zn[o];
             if (q_out) q_out[o] = q;
             lq += (q - a) * (q - a);
             if (z) ln += (a - z[o]) * (a - z[o]);
         }
-        if (counts) atomicAdd(&counts[k], 1);
+        if (counts && lane == 0) atomicAdd(&counts[k], 1);
     }
     lq = block_sum(lq, red);
     ln = block_sum(ln, red);
@@ -118,22 +122,26 @@ __global__ void __launch_bounds__(256) vq_finalize_kernel(const float* __restric
     }
 }
 
-// dz and dE_hat (atomic scatter).  One thread per frame.
-__global__ void vq_bwd_kernel(const float* __restrict__ g_out, const float* __restrict__ g_lq,
-                              const float* __restrict__ g_le, const int64_t* __restrict__ idx,
-                              const float* __restrict__ z, const float* __restrict__ zn,
-                              const float* __restrict__ z_norm, const float* __restrict__ e_hat, int B, int D, int T,
-                              float scale, int normalize, float* __restrict__ dz, float* __restrict__ dE_hat) {
-    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= (int64_t)B * T) return;
-    const int64_t b = n / T, t = n - b * T;
+// dz and dE_hat (atomic scatter).  One warp per frame.
+__global__ void __launch_bounds__(VQ_WARPS * 32) vq_bwd_kernel(const float* __restrict__ g_out,
+                                                               const float* __restrict__ g_lq,
+                                                               const float* __restrict__ g_le,
+                                                               const int64_t* __restrict__ idx,
+                                                               const float* __restrict__ z, const float* __restrict__ zn,
+                                                               const float* __restrict__ z_norm,
+                                                               const float* __restrict__ e_hat, int64_t N, int D,
+                                                               float scale, int normalize, float* __restrict__ dz,
+                                                               float* __restrict__ dE_hat) {
+    const int64_t n = (int64_t)blockIdx.x * VQ_WARPS + (threadIdx.x >> 5);
+    if (n >= N) return;
+    const int lane = threadIdx.x & 31;
     const float glq = (g_lq ? g_lq[0] : 0.f) * 2.f * scale;
     const float gle = (g_le ? g_le[0] : 0.f) * 2.f * scale;
     const int k = (int)idx[n];
     const float* er = e_hat + (int64_t)k * D;
     if (!normalize) {
-        for (int d = 0; d < D; d++) {
-            const int64_t o = (b * D + d) * T + t;
+        for (int d = lane; d < D; d += 32) {
+            const int64_t o = n * D + d;
             const float q = er[d], a = zn[o];
             dz[o] = (g_out ? g_out[o] : 0.f) + gle * (a - q);
             if (dE_hat && glq != 0.f) atomicAdd(&dE_hat[(int64_t)k * D + d], glq * (q - a));
@@ -143,15 +151,16 @@ __global__ void vq_bwd_kernel(const float* __restrict__ g_out, const float* __re
     // normalised: dzn = g_out + gle*[(zn-q) + (zn-z)];  dz = (dzn - zn*<zn,dzn>)/||z|| - gle*(zn-z)
     const float inv = 1.f / z_norm[n];
     float dot = 0.f;
-    for (int d = 0; d < D; d++) {
-        const int64_t o = (b * D + d) * T + t;
+    for (int d = lane; d < D; d += 32) {
+        const int64_t o = n * D + d;
         const float q = er[d], a = zn[o];
         const float dzn = (g_out ? g_out[o] : 0.f) + gle * ((a - q) + (a - z[o]));
         dot += a * dzn;
         if (dE_hat && glq != 0.f) atomicAdd(&dE_hat[(int64_t)k * D + d], glq * (q - a));
     }
-    for (int d = 0; d < D; d++) {
-        const int64_t o = (b * D + d) * T + t;
+    dot = warp_sum(dot);
+    for (int d = lane; d < D; d += 32) {
+        const int64_t o = n * D + d;
         const float q = er[d], a = zn[o];
         const float dzn = (g_out ? g_out[o] : 0.f) + gle * ((a - q) + (a - z[o]));
         dz[o] = (dzn - a * dot) * inv - gle * (a - z[o]);
@@ -181,15 +190,17 @@ __global__ void __launch_bounds__(128) vq_bwd_codebook_kernel(const float* __res
         dE[(int64_t)k * D + d] = (g[d] - e[d] * dot / ss) * inv;
 }
 
-// EMA: per-code sums of assigned frames
-__global__ void vq_ema_scatter_kernel(const int64_t* __restrict__ idx, const float* __restrict__ z, int B, int D, int T,
-                                      float* __restrict__ zsum, int* __restrict__ counts) {
-    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= (int64_t)B * T) return;
-    const int64_t b = n / T, t = n - b * T;
+// EMA: per-code sums of assigned frames (one warp per frame)
+__global__ void __launch_bounds__(VQ_WARPS * 32) vq_ema_scatter_kernel(const int64_t* __restrict__ idx,
+                                                                       const float* __restrict__ z, int64_t N, int D,
+                                                                       float* __restrict__ zsum,
+                                                                       int* __restrict__ counts) {
+    const int64_t n = (int64_t)blockIdx.x * VQ_WARPS + (threadIdx.x >> 5);
+    if (n >= N) return;
+    const int lane = threadIdx.x & 31;
     const int k = (int)idx[n];
-    for (int d = 0; d < D; d++) atomicAdd(&zsum[(int64_t)k * D + d], z[(b * D + d) * T + t]);
-    atomicAdd(&counts[k], 1);
+    for (int d = lane; d < D; d += 32) atomicAdd(&zsum[(int64_t)k * D + d], z[n * D + d]);
+    if (lane == 0) atomicAdd(&counts[k], 1);
 }
 
 // single block: EMA buffers, alive mask, new codebook, statistics
@@ -234,24 +245,25 @@ __global__ void __launch_bounds__(512) vq_ema_update_kernel(const float* __restr
     }
 }
 
-__global__ void vq_frame_rows_kernel(const float* __restrict__ z, const int64_t* __restrict__ perm, int B, int D, int T,
+__global__ void vq_frame_rows_kernel(const float* __restrict__ z, const int64_t* __restrict__ perm, int64_t N, int D,
                                      int K, float* __restrict__ out) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (int64_t)K * D) return;
     const int k = (int)(i / D), d = (int)(i - (int64_t)k * D);
-    const int64_t n = perm[k] % ((int64_t)B * T);
-    const int64_t b = n / T, t = n - b * T;
-    out[i] = z[(b * D + d) * T + t];
+    out[i] = z[(perm[k] % N) * D + d];
 }
 
-__global__ void jitter_kernel(const float* __restrict__ in, const int64_t* __restrict__ src, int64_t rows, int T,
+// channels-last (B, T, D): out[b,t,:] = in[b,src[t],:]  (backward: zero the rows with src[t] != t)
+__global__ void jitter_kernel(const float* __restrict__ in, const int64_t* __restrict__ src, int64_t n, int D, int T,
                               int backward, float* __restrict__ out) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= rows * T) return;
-    const int64_t r = i / T;
-    const int t = (int)(i - r * T);
+    if (i >= n) return;
+    const int64_t r = i / D;
+    const int d = (int)(i - r * D);
+    const int64_t b = r / T;
+    const int t = (int)(r - b * T);
     const int s = (int)src[t];
-    out[i] = backward ? (s == t ? in[i] : 0.f) : in[r * T + s];
+    out[i] = backward ? (s == t ? in[i] : 0.f) : in[(b * T + s) * D + d];
 }
 
 }  // namespace vnb
@@ -266,11 +278,12 @@ extern "C" int vnb_vq_prep_codebook(float* E, int K, int D, int normalize, int i
     return VNB_OK;
 }
 
-extern "C" int vnb_vq_prep_z(const float* z, int B, int D, int T, int Tp, int normalize, float* zn, void* z_planes,
+extern "C" int vnb_vq_prep_z(const float* z, int B, int D, int T, int normalize, float* zn, void* z_planes,
                              float* z_sq, float* z_norm, void* stream) {
-    VNB_REQUIRE(z && B > 0 && D > 0 && T > 0 && Tp >= T, "vq_prep_z: bad arguments");
-    vq_prep_z_kernel<<<ceil_div((int64_t)B * T, 128), 128, 0, (cudaStream_t)stream>>>(z, B, D, T, Tp, normalize, zn,
-                                                                                     (bf16*)z_planes, z_sq, z_norm);
+    VNB_REQUIRE(z && B > 0 && D > 0 && T > 0, "vq_prep_z: bad arguments");
+    const int64_t N = (int64_t)B * T;
+    vq_prep_z_kernel<<<ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream>>>(z, N, D, round_up8(D), normalize,
+                                                                                        zn, (bf16*)z_planes, z_sq, z_norm);
     VNB_LAUNCH_CHECK("vq_prep_z");
     return VNB_OK;
 }
@@ -278,8 +291,9 @@ extern "C" int vnb_vq_prep_z(const float* z, int B, int D, int T, int Tp, int no
 extern "C" int vnb_vq_gather(const int64_t* idx, const float* e_hat, const float* zn, const float* z, int B, int D,
                              int T, int K, float* q_out, float* sums, int* counts, void* stream) {
     VNB_REQUIRE(idx && e_hat && zn && B > 0 && D > 0 && T > 0 && K > 0, "vq_gather: bad arguments");
-    vq_gather_kernel<<<ceil_div((int64_t)B * T, 256), 256, 0, (cudaStream_t)stream>>>(idx, e_hat, zn, z, B, D, T, K,
-                                                                                     q_out, sums, counts);
+    const int64_t N = (int64_t)B * T;
+    vq_gather_kernel<<<ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream>>>(idx, e_hat, zn, z, N, D, q_out,
+                                                                                        sums, counts);
     VNB_LAUNCH_CHECK("vq_gather");
     return VNB_OK;
 }
@@ -299,8 +313,9 @@ extern "C" int vnb_vq_bwd(const float* g_out, const float* g_lq, const float* g_
     (void)K;
     VNB_REQUIRE(idx && zn && e_hat && dz && B > 0 && D > 0 && T > 0, "vq_bwd: bad arguments");
     VNB_REQUIRE(!normalize || (z && z_norm), "vq_bwd: normalised mode needs z and z_norm");
-    vq_bwd_kernel<<<ceil_div((int64_t)B * T, 128), 128, 0, (cudaStream_t)stream>>>(
-        g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, B, D, T, scale, normalize, dz, dE_hat);
+    const int64_t N = (int64_t)B * T;
+    vq_bwd_kernel<<<ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream>>>(
+        g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, N, D, scale, normalize, dz, dE_hat);
     VNB_LAUNCH_CHECK("vq_bwd");
     return VNB_OK;
 }
@@ -317,7 +332,8 @@ extern "C" int vnb_vq_ema_scatter(const int64_t* idx, const float* z, int B, int
                                   int* counts, void* stream) {
     (void)K;
     VNB_REQUIRE(idx && z && zsum && counts && B > 0 && D > 0 && T > 0, "vq_ema_scatter: bad arguments");
-    vq_ema_scatter_kernel<<<ceil_div((int64_t)B * T, 128), 128, 0, (cudaStream_t)stream>>>(idx, z, B, D, T, zsum, counts);
+    const int64_t N = (int64_t)B * T;
+    vq_ema_scatter_kernel<<<ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream>>>(idx, z, N, D, zsum, counts);
     VNB_LAUNCH_CHECK("vq_ema_scatter");
     return VNB_OK;
 }
@@ -336,23 +352,23 @@ extern "C" int vnb_vq_ema_update(const float* zsum, const int* counts, int K, in
 extern "C" int vnb_vq_frame_rows(const float* z, const int64_t* perm, int B, int D, int T, int K, float* out,
                                  void* stream) {
     VNB_REQUIRE(z && perm && out && B > 0 && D > 0 && T > 0 && K > 0, "vq_frame_rows: bad arguments");
-    vq_frame_rows_kernel<<<ceil_div((int64_t)K * D, 256), 256, 0, (cudaStream_t)stream>>>(z, perm, B, D, T, K, out);
+    vq_frame_rows_kernel<<<ceil_div((int64_t)K * D, 256), 256, 0, (cudaStream_t)stream>>>(z, perm, (int64_t)B * T, D, K, out);
     VNB_LAUNCH_CHECK("vq_frame_rows");
     return VNB_OK;
 }
 
 extern "C" int vnb_jitter_fwd(const float* in, const int64_t* src, int B, int D, int T, float* out, void* stream) {
     VNB_REQUIRE(in && src && out && B > 0 && D > 0 && T > 0, "jitter_fwd: bad arguments");
-    const int64_t rows = (int64_t)B * D;
-    jitter_kernel<<<ceil_div(rows * T, 256), 256, 0, (cudaStream_t)stream>>>(in, src, rows, T, 0, out);
+    const int64_t n = (int64_t)B * D * T;
+    jitter_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(in, src, n, D, T, 0, out);
     VNB_LAUNCH_CHECK("jitter_fwd");
     return VNB_OK;
 }
 
 extern "C" int vnb_jitter_bwd(const float* dout, const int64_t* src, int B, int D, int T, float* din, void* stream) {
     VNB_REQUIRE(dout && src && din && B > 0 && D > 0 && T > 0, "jitter_bwd: bad arguments");
-    const int64_t rows = (int64_t)B * D;
-    jitter_kernel<<<ceil_div(rows * T, 256), 256, 0, (cudaStream_t)stream>>>(dout, src, rows, T, 1, din);
+    const int64_t n = (int64_t)B * D * T;
+    jitter_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(dout, src, n, D, T, 1, din);
     VNB_LAUNCH_CHECK("jitter_bwd");
     return VNB_OK;
 }

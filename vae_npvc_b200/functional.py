@@ -77,7 +77,7 @@ class ConvFn(Function):
 
     @staticmethod
     def forward(ctx, x, v, g, bias, transposed, dil, act, scale, P, box):
-        x = x.contiguous()
+        x = Pm.as_cl(x)
         xpl = _input_planes(x, P, act, scale)
         need_dx = ctx.needs_input_grad[0]
         W = Pm.wn_prepare(v, g, transposed, P, need_wb=need_dx)
@@ -91,7 +91,7 @@ class ConvFn(Function):
     def backward(ctx, dy):
         x, v, g = ctx.saved_tensors
         transposed, dil, act, scale, P, taps, Cin, has_bias = ctx.cfg
-        dy = dy.contiguous()
+        dy = Pm.as_cl(dy)
         dypl = Pm.make_planes(dy, P)[0]
         db = Pm.channel_sum(dy) if (has_bias and ctx.needs_input_grad[3]) else None
         dx = None
@@ -118,7 +118,7 @@ class EncBlockFn(Function):
 
     @staticmethod
     def forward(ctx, c, P, dil, box, n_layers, *params):
-        c = c.contiguous()
+        c = Pm.as_cl(c)
         cpl = cached_planes(c, 'id', P)
         upl = cached_planes(c, 'lrelu', P)
         if cpl is None or upl is None:
@@ -155,7 +155,7 @@ class EncBlockFn(Function):
     def backward(ctx, dy):
         c, *params = ctx.saved_tensors
         P, n_layers, C = ctx.cfg
-        dy = dy.contiguous()
+        dy = Pm.as_cl(dy)
         T = dy.shape[2]
         grads = [None] * len(params)
         dn = dy
@@ -200,12 +200,15 @@ class DecBlockFn(Function):
     r = Conv_1(g); x' = r[:C] + x; skip = r[C:].
     ``cond`` is (B,Y) when it is time-invariant (the Decoder's c.repeat, vqvae.py:309-312: the
     1x1 cond conv collapses to a per-utterance bias) or (B,Y,T) in general.
-    ``skip_acc``: optional running skip sum updated IN PLACE (vqvae.py:313).
+    ``skip_acc``: optional running skip sum updated IN PLACE (vqvae.py:313).  It is passed and
+    returned in its PHYSICAL (B, T, S) form (a base tensor, not a transposed view: autograd does not
+    allow in-place updates of view inputs of multi-output Functions); callers take ``.transpose(1, 2)``
+    once at the end.
     Math: SURVEY.md section 9 B."""
 
     @staticmethod
     def forward(ctx, x, cond, skip_acc, P, dil, box, v_in, g_in, b_in, gamma, beta, v_c, g_c, b_c, v_rs, g_rs, b_rs):
-        x = x.contiguous()
+        x = Pm.as_cl(x)
         B, C, T = x.shape
         S = v_rs.shape[0] - C
         xpl = _input_planes(x, P)
@@ -222,7 +225,7 @@ class DecBlockFn(Function):
         else:
             a = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, b_in, 0)
             if has_cond:
-                cond = cond.contiguous()
+                cond = Pm.as_cl(cond)
                 cpl = _input_planes(cond, P)
                 Wc = Pm.wn_prepare(v_c, g_c, False, P, need_wb=ctx.needs_input_grad[1])
                 wc_wb = Wc.wb
@@ -231,8 +234,12 @@ class DecBlockFn(Function):
         gpl = Pm.dec_gate(a, mean, rstd, gamma, beta, P)
         Wrs = Pm.wn_prepare(v_rs, g_rs, False, P)
         r = Pm.conv_fwd(gpl, Wrs.wf, 1, 1, C + S, b_rs, 0)
-        x_out, xopl, skip = Pm.dec_out(r, x, S, P, skip_acc, skip_acc is None)
-        if skip_acc is not None:
+        first = skip_acc is None
+        if first:
+            skip_acc = torch.empty((B, T, S), dtype=torch.float32, device=x.device)
+        x_out, xopl, _ = Pm.dec_out(r, x, S, P, skip_acc.transpose(1, 2), first)
+        skip = skip_acc
+        if not first:
             ctx.mark_dirty(skip_acc)
         if box is not None:
             box['id'] = xopl
@@ -240,7 +247,7 @@ class DecBlockFn(Function):
         ctx.xpl, ctx.gpl, ctx.cpl = xpl, gpl, cpl
         ctx.win_wb, ctx.wrs_wb, ctx.wc_wb, ctx.wc32 = Win.wb, Wrs.wb, wc_wb, wc32
         ctx.cfg = (P, dil, B, C, S, T, Win.taps, has_cond, bcast)
-        ctx.has_acc = skip_acc is not None
+        ctx.has_acc = not first
         return x_out, skip
 
     @staticmethod
@@ -248,8 +255,10 @@ class DecBlockFn(Function):
         cond, a, mean, rstd, gamma, beta, v_in, g_in, v_c, g_c, v_rs, g_rs = ctx.saved_tensors
         P, dil, B, C, S, T, taps, has_cond, bcast = ctx.cfg
         dev = a.device
-        dxo = torch.zeros((B, C, T), device=dev) if dxo is None else dxo.contiguous()
-        dskip = torch.zeros((B, S, T), device=dev) if dskip is None else dskip.contiguous()
+        dxo = Pm.cl_zeros(B, C, T, dev) if dxo is None else Pm.as_cl(dxo)
+        # dskip arrives in the physical (B, T, S) form of the skip accumulator
+        dskip_phys = torch.zeros((B, T, S), device=dev) if dskip is None else dskip.contiguous()
+        dskip = dskip_phys.transpose(1, 2)
         drpl = Pm.concat_planes(dxo, dskip, P)
         db_rs = torch.empty((C + S,), dtype=torch.float32, device=dev)
         Pm.channel_sum(dxo, db_rs[:C])
@@ -273,12 +282,13 @@ class DecBlockFn(Function):
                     dcond = Pm.conv_fwd(dapl, ctx.wc_wb, 1, 1, cond.shape[1])
             if not ctx.needs_input_grad[1]:
                 dcond = None
-        return (dx, dcond, dskip if ctx.has_acc else None, None, None, None, dv_in, dg_in, csum, dgamma, dbeta, dv_c, dg_c, db_c,
+        return (dx, dcond, dskip_phys if ctx.has_acc else None, None, None, None, dv_in, dg_in, csum, dgamma, dbeta, dv_c, dg_c, db_c,
                 dv_rs, dg_rs, db_rs)
 
 
 def dec_block(x, cond, params, skip_acc=None, dil=1, P=None):
-    """params = (v_in, g_in, b_in, gamma, beta, v_c, g_c, b_c, v_rs, g_rs, b_rs) -> (x', skip)"""
+    """params = (v_in, g_in, b_in, gamma, beta, v_c, g_c, b_c, v_rs, g_rs, b_rs) -> (x', skip_phys);
+    skip_acc / skip_phys are physical (B, T, S) tensors (see DecBlockFn)."""
     box = {}
     x_out, skip = DecBlockFn.apply(x, cond, skip_acc, P or get_precision(), dil, box, *params)
     attach_planes(x_out, 'id', box.get('id'))
@@ -297,7 +307,7 @@ class VQFn(Function):
 
     @staticmethod
     def forward(ctx, z, E, normalize, reduction):
-        z = z.contiguous()
+        z = Pm.as_cl(z)
         B, D, T = z.shape
         e_hat, e_pl, e_sq = Pm.vq_prep_codebook(E.detach(), normalize, True)
         zn, zpl, z_sq, z_norm = Pm.vq_prep_z(z, normalize)
@@ -315,7 +325,7 @@ class VQFn(Function):
     def backward(ctx, g_out, g_lq, g_le, _gp, _gi):
         z, zn, z_norm, e_hat, E, idx = ctx.saved_tensors
         scale, normalize = ctx.cfg
-        g_out = g_out.contiguous() if g_out is not None else None
+        g_out = Pm.as_cl(g_out) if g_out is not None else None
         g_lq = g_lq.contiguous() if g_lq is not None else None
         g_le = g_le.contiguous() if g_le is not None else None
         want_dE = ctx.needs_input_grad[1]
@@ -329,7 +339,7 @@ class VQLookupFn(Function):
 
     @staticmethod
     def forward(ctx, z, E, normalize):
-        z = z.contiguous()
+        z = Pm.as_cl(z)
         e_hat, e_pl, e_sq = Pm.vq_prep_codebook(E.detach(), normalize, False)
         zn, zpl, z_sq, _ = Pm.vq_prep_z(z, normalize)
         idx = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
@@ -348,7 +358,7 @@ class EMAVQFn(Function):
 
     @staticmethod
     def forward(ctx, z, embeddings, reduction):
-        z = z.contiguous()
+        z = Pm.as_cl(z)
         B, D, T = z.shape
         e_hat, e_pl, e_sq = Pm.vq_prep_codebook(embeddings, False, False)
         zn, zpl, z_sq, _ = Pm.vq_prep_z(z, False)
@@ -375,12 +385,12 @@ class JitterFn(Function):
     @staticmethod
     def forward(ctx, q, src):
         ctx.save_for_backward(src)
-        return Pm.jitter_fwd(q.contiguous(), src)
+        return Pm.jitter_fwd(Pm.as_cl(q), src)
 
     @staticmethod
     def backward(ctx, dout):
         (src,) = ctx.saved_tensors
-        return Pm.jitter_bwd(dout.contiguous(), src), None
+        return Pm.jitter_bwd(Pm.as_cl(dout), src), None
 
 
 class LogLossFn(Function):
@@ -388,7 +398,7 @@ class LogLossFn(Function):
 
     @staticmethod
     def forward(ctx, x, mu, scale):
-        x, mu = x.contiguous(), mu.contiguous()
+        x, mu = Pm.as_cl(x), Pm.as_cl(mu)
         ctx.save_for_backward(x, mu)
         ctx.scale = scale
         return Pm.logloss_fwd(x, mu, scale)[0]

@@ -132,9 +132,14 @@ class DeConv1d_Layernorm_GLU_ResSkip(nn.Module):
         return (list(conv_params(self.conv_in)) + [self.norm_layer.weight, self.norm_layer.bias] + pc
                 + list(conv_params(self.res_skip_layers)))
 
-    def forward(self, x, c, skip_acc=None):
-        """x (B,C,T); c (B,Y,T), or time-invariant as (B,Y,1) / (B,Y).  Returns (x, x_skip);
-        with ``skip_acc`` the skip output is accumulated into it in place and returned."""
+    def forward(self, x, c):
+        """x (B,C,T); c (B,Y,T), or time-invariant as (B,Y,1) / (B,Y).  Returns (x, x_skip)."""
+        x, skip = self.forward_acc(x, c, None)
+        return x, skip.transpose(1, 2)
+
+    def forward_acc(self, x, c, skip_acc):
+        """As forward, but the skip output is ADDED IN PLACE into ``skip_acc``, the Decoder's running
+        skip sum in its physical channels-last (B, T, S) form (None: a fresh one is returned)."""
         if c is not None and c.dim() == 3 and c.size(2) == 1:
             c = c.squeeze(2)
         return Fn.dec_block(x, c, self._params(), skip_acc, self.dilation)

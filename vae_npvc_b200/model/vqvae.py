@@ -130,12 +130,12 @@ class Decoder(nn.Module, _WeightNormMixin):
         skip = None
         for layer in self.layers:
             if isinstance(layer, DeConv1d_Layernorm_GLU_ResSkip):
-                x, skip = layer(x, c, skip)
+                x, skip = layer.forward_acc(x, c, skip)
             else:
                 x = run_conv(layer, x)
         # x_out * sqrt(1/len(layers)) then ReLU -> 1x1 -> ReLU -> 1x1 (vqvae.py:316-317)
         scale = math.sqrt(1.0 / len(self.layers))
-        o = run_conv(self.final_layer[1], skip, act=ACT_RELU, scale=scale)
+        o = run_conv(self.final_layer[1], skip.transpose(1, 2), act=ACT_RELU, scale=scale)
         return run_conv(self.final_layer[3], o, act=ACT_RELU)
 
 
@@ -168,7 +168,10 @@ class Model(nn.Module):
         z_idx, y_idx = input
         y = self.embeds(y_idx).transpose(1, 2).contiguous()      # (B, y_dim, n)
         z_vq = self.quantizer.decode(z_idx)
-        return self.decoder((z_vq, y))
+        xhat = self.decoder((z_vq, y))
+        # conversion output in the reference's (B, X, T)-contiguous layout (decoder/basic.py:73-75
+        # hands it to numpy); forward() keeps the channels-last tensor, the loss consumes it directly
+        return xhat.contiguous() if xhat.requires_grad else Fn.Pm.to_nct(xhat)
 
     def infer(self, input):
         x, y_idx = input

@@ -11,23 +11,69 @@ from . import _C
 from ._C import ACT_LRELU, ACT_NONE, ACT_RELU  # noqa: F401
 
 
-def pitch(T):
-    return (T + 7) // 8 * 8
+def pitch(C):
+    return (C + 7) // 8 * 8
+
+
+# ---- channels-last helpers -------------------------------------------------------------------
+# Activations keep the reference's LOGICAL shape (B, C, T) but live in memory as a contiguous
+# (B, T, C) array (strides (T*C, 1, C)): frames are rows, channels contiguous.  Any torch op sees
+# an ordinary (B, C, T) tensor; the kernels get the contiguous (B, T, C) view.
+def cl_empty(B, C, T, device, dtype=torch.float32):
+    return torch.empty((B, T, C), dtype=dtype, device=device).transpose(1, 2)
+
+
+def cl_zeros(B, C, T, device, dtype=torch.float32):
+    return torch.zeros((B, T, C), dtype=dtype, device=device).transpose(1, 2)
+
+
+def is_cl(x):
+    return x.dim() == 3 and x.transpose(1, 2).is_contiguous()
+
+
+def as_cl(x):
+    """Same logical (B,C,T) tensor, channels-last in memory (converted by vnb_transpose if needed)."""
+    if is_cl(x):
+        return x
+    if x.dtype == torch.float32 and x.is_cuda:
+        xc = x.contiguous()
+        B, C, T = xc.shape
+        out = cl_empty(B, C, T, x.device)
+        _C.call('transpose', xc, B, C, T, out.transpose(1, 2))
+        return out
+    return x.transpose(1, 2).contiguous().transpose(1, 2)
+
+
+def to_nct(x):
+    """Logical (B,C,T) tensor -> reference-layout contiguous copy (for callers that need it)."""
+    if x.is_contiguous():
+        return x
+    if is_cl(x) and x.dtype == torch.float32 and x.is_cuda:
+        B, C, T = x.shape
+        out = torch.empty((B, C, T), dtype=torch.float32, device=x.device)
+        _C.call('transpose', x.transpose(1, 2), B, T, C, out)
+        return out
+    return x.contiguous()
+
+
+def _r(x):
+    """contiguous (B,T,C) storage view of a logical (B,C,T) activation (None passes through)."""
+    return None if x is None else as_cl(x).transpose(1, 2)
 
 
 class Planes:
-    """bf16 GEMM-operand planes of an activation: data (P, B, C, Tp)."""
-    __slots__ = ('data', 'P', 'B', 'C', 'T', 'Tp')
+    """bf16 GEMM-operand planes of an activation: data (P, B, T, Cp), channels-last."""
+    __slots__ = ('data', 'P', 'B', 'C', 'T', 'Cp')
 
-    def __init__(self, data, P, B, C, T, Tp):
-        self.data, self.P, self.B, self.C, self.T, self.Tp = data, P, B, C, T, Tp
+    def __init__(self, data, P, B, C, T, Cp):
+        self.data, self.P, self.B, self.C, self.T, self.Cp = data, P, B, C, T, Cp
 
     @staticmethod
     def empty(P, B, C, T, device):
-        Tp = pitch(T)
+        Cp = pitch(C)
         # zero-filled so the pitch padding is finite (the kernels never read it as data)
-        alloc = torch.zeros if Tp != T else torch.empty
-        return Planes(alloc((P, B, C, Tp), dtype=torch.bfloat16, device=device), P, B, C, T, Tp)
+        alloc = torch.zeros if Cp != C else torch.empty
+        return Planes(alloc((P, B, T, Cp), dtype=torch.bfloat16, device=device), P, B, C, T, Cp)
 
 
 class ConvWeights:
@@ -73,11 +119,17 @@ def wn_backward(dw, v, g):
 # GEMM-shaped ops
 # --------------------------------------------------------------------------------------------
 def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False):
-    """x_pl: Planes (B,Cin,T); w_op: (P,taps,Cout,Cin_p) bf16 -> out fp32 (B,Cout,T)."""
+    """x_pl: Planes (B,Cin,T); w_op: (P,taps,Cout,Cin_p) bf16 -> out fp32, logical (B,Cout,T)."""
+    user_out = None
     if out is None:
-        out = torch.empty((x_pl.B, Cout, x_pl.T), dtype=torch.float32, device=x_pl.data.device)
-    _C.call('conv_fwd', x_pl.data, x_pl.P, x_pl.B, x_pl.C, x_pl.T, x_pl.Tp, w_op, taps, dil, Cout, bias,
-            bias_bstride, residual, out, int(accumulate))
+        out = cl_empty(x_pl.B, Cout, x_pl.T, x_pl.data.device)
+    elif not is_cl(out):                      # reference-layout buffer from a caller: stage through channels-last
+        user_out, out = out, as_cl(out)
+    _C.call('conv_fwd', x_pl.data, x_pl.P, x_pl.B, x_pl.C, x_pl.T, w_op, taps, dil, Cout, bias,
+            bias_bstride, _r(residual), out.transpose(1, 2), int(accumulate))
+    if user_out is not None:
+        user_out.copy_(out)
+        return user_out
     return out
 
 
@@ -85,7 +137,7 @@ def conv_wgrad(dy_pl, u_pl, taps, dil, transposed):
     Cout, Cin = dy_pl.C, u_pl.C
     shape = (Cin, Cout, taps) if transposed else (Cout, Cin, taps)
     dw = torch.empty(shape, dtype=torch.float32, device=dy_pl.data.device)
-    _C.call('conv_wgrad', dy_pl.data, u_pl.data, dy_pl.P, dy_pl.B, Cout, Cin, dy_pl.T, dy_pl.Tp, taps, dil,
+    _C.call('conv_wgrad', dy_pl.data, u_pl.data, dy_pl.P, dy_pl.B, Cout, Cin, dy_pl.T, taps, dil,
             int(transposed), dw)
     return dw
 
@@ -97,7 +149,7 @@ def make_planes(x, P, scale=1.0, act=ACT_NONE, want_id=True, want_act=False):
     B, C, T = x.shape
     pid = Planes.empty(P, B, C, T, x.device) if want_id else None
     pact = Planes.empty(P, B, C, T, x.device) if want_act else None
-    _C.call('make_planes', x, B, C, T, pitch(T), P, scale, act, pid.data if pid else None,
+    _C.call('make_planes', _r(x), B, C, T, P, scale, act, pid.data if pid else None,
             pact.data if pact else None)
     return pid, pact
 
@@ -106,7 +158,7 @@ def concat_planes(xa, xb, P):
     B, Ca, T = xa.shape
     Cb = xb.shape[1]
     out = Planes.empty(P, B, Ca + Cb, T, xa.device)
-    _C.call('concat_planes', xa, Ca, xb, Cb, B, T, out.Tp, P, out.data)
+    _C.call('concat_planes', _r(xa), Ca, _r(xb), Cb, B, T, P, out.data)
     return out
 
 
@@ -116,16 +168,17 @@ def concat_planes(xa, xb, P):
 def gn_stats(h, groups, eps=1e-5):
     B, C, T = h.shape
     mean, rstd = _f32((B, groups), h), _f32((B, groups), h)
-    _C.call('gn_stats', h, B, C, T, groups, eps, mean, rstd)
+    ws = _f32((_C.call('gn_stats_ws_floats', B, groups),), h)
+    _C.call('gn_stats', _r(h), B, C, T, groups, eps, ws, mean, rstd)
     return mean, rstd
 
 
 def enc_out(h, s, mean, rstd, gamma, beta, P, want_y=True, want_ypl=True, want_upl=True):
     B, C, T = h.shape
-    y = torch.empty_like(h) if want_y else None
+    y = cl_empty(B, C, T, h.device) if want_y else None
     ypl = Planes.empty(P, B, C, T, h.device) if want_ypl else None
     upl = Planes.empty(P, B, C, T, h.device) if want_upl else None
-    _C.call('enc_out', h, s, mean, rstd, gamma, beta, B, C, T, pitch(T), P, y, ypl.data if ypl else None,
+    _C.call('enc_out', _r(h), _r(s), mean, rstd, gamma, beta, B, C, T, P, _r(y), ypl.data if ypl else None,
             upl.data if upl else None)
     return y, ypl, upl
 
@@ -134,19 +187,21 @@ def dec_gate(a, mean, rstd, gamma, beta, P):
     B, C2, T = a.shape
     C = C2 // 2
     gpl = Planes.empty(P, B, C, T, a.device)
-    _C.call('dec_gate', a, mean, rstd, gamma, beta, B, C, T, gpl.Tp, P, gpl.data)
+    _C.call('dec_gate', _r(a), mean, rstd, gamma, beta, B, C, T, P, gpl.data)
     return gpl
 
 
 def dec_out(r, x, S, P, skip_sum=None, first=True, want_x=True, want_xpl=True):
     """r (B,C+S,T), x (B,C,T) -> x_out, x_planes, skip_sum (allocated when None)."""
     B, C, T = x.shape
-    x_out = torch.empty_like(x) if want_x else None
+    x_out = cl_empty(B, C, T, x.device) if want_x else None
     xpl = Planes.empty(P, B, C, T, x.device) if want_xpl else None
     if skip_sum is None and S > 0:
-        skip_sum = _f32((B, S, T), x)
+        skip_sum = cl_empty(B, S, T, x.device)
         first = True
-    _C.call('dec_out', r, x, B, C, S, T, pitch(T), P, x_out, xpl.data if xpl else None, skip_sum, int(first))
+    if skip_sum is not None:
+        assert is_cl(skip_sum), 'skip accumulator must be channels-last'
+    _C.call('dec_out', _r(r), _r(x), B, C, S, T, P, _r(x_out), xpl.data if xpl else None, _r(skip_sum), int(first))
     return x_out, xpl, skip_sum
 
 
@@ -156,14 +211,14 @@ def dec_out(r, x, S, P, skip_sum=None, first=True, want_x=True, want_xpl=True):
 def gn_bwd_rows(dn, h, mean, rstd, groups):
     B, C, T = h.shape
     R = _f32((B, C, 3), h)
-    _C.call('gn_bwd_rows', dn, h, mean, rstd, B, C, T, groups, R)
+    _C.call('gn_bwd_rows', _r(dn), _r(h), mean, rstd, B, C, T, groups, R)
     return R
 
 
 def gate_bwd_rows(dg, a, mean, rstd, gamma, beta):
     B, C2, T = a.shape
     R = _f32((B, C2, 3), a)
-    _C.call('gate_bwd_rows', dg, a, mean, rstd, gamma, beta, B, C2 // 2, T, R)
+    _C.call('gate_bwd_rows', _r(dg), _r(a), mean, rstd, gamma, beta, B, C2 // 2, T, R)
     return R
 
 
@@ -182,7 +237,7 @@ def gn_bwd_apply(dn, h, mean, rstd, gamma, S, groups, P, want_dn_planes=False):
     B, C, T = h.shape
     dpre = Planes.empty(P, B, C, T, h.device)
     dnp = Planes.empty(P, B, C, T, h.device) if want_dn_planes else None
-    _C.call('gn_bwd_apply', dn, h, mean, rstd, gamma, S, B, C, T, groups, dpre.Tp, P, dpre.data,
+    _C.call('gn_bwd_apply', _r(dn), _r(h), mean, rstd, gamma, S, B, C, T, groups, P, dpre.data,
             dnp.data if dnp else None)
     return dpre, dnp
 
@@ -190,13 +245,14 @@ def gn_bwd_apply(dn, h, mean, rstd, gamma, S, groups, P, want_dn_planes=False):
 def gate_bwd_apply(dg, a, mean, rstd, gamma, beta, S, P):
     B, C2, T = a.shape
     da = Planes.empty(P, B, C2, T, a.device)
-    _C.call('gate_bwd_apply', dg, a, mean, rstd, gamma, beta, S, B, C2 // 2, T, da.Tp, P, da.data)
+    _C.call('gate_bwd_apply', _r(dg), _r(a), mean, rstd, gamma, beta, S, B, C2 // 2, T, P, da.data)
     return da
 
 
 def act_bwd_add(du, c, add, act, scale=1.0):
-    out = torch.empty_like(du)
-    _C.call('act_bwd_add', du, c, add, du.numel(), act, scale, out)
+    B, C, T = du.shape
+    out = cl_empty(B, C, T, du.device)
+    _C.call('act_bwd_add', _r(du), _r(c), _r(add), du.numel(), act, scale, out.transpose(1, 2))
     return out
 
 
@@ -204,7 +260,7 @@ def channel_sum(x, out=None):
     B, C, T = x.shape
     if out is None:
         out = _f32((C,), x)
-    _C.call('channel_sum', x, B, C, T, out)
+    _C.call('channel_sum', _r(x), B, C, T, out)
     return out
 
 
@@ -259,10 +315,10 @@ def vq_prep_codebook(E, normalize, inplace_renorm=True):
 
 def vq_prep_z(z, normalize):
     B, D, T = z.shape
-    zn = torch.empty_like(z)
+    zn = cl_empty(B, D, T, z.device)
     zpl = Planes.empty(3, B, D, T, z.device)
     z_sq, z_norm = _f32((B * T,), z), _f32((B * T,), z)
-    _C.call('vq_prep_z', z, B, D, T, zpl.Tp, int(normalize), zn, zpl.data, z_sq, z_norm)
+    _C.call('vq_prep_z', _r(z), B, D, T, int(normalize), zn.transpose(1, 2), zpl.data, z_sq, z_norm)
     return zn, zpl, z_sq, z_norm
 
 
@@ -270,8 +326,7 @@ def vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq):
     B, D, T = zn.shape
     K = e_hat.shape[0]
     idx = torch.empty((B * T,), dtype=torch.int64, device=zn.device)
-    _C.call('vq_lookup', zn, zpl.data if zpl is not None else None, z_sq, e_hat, e_pl, e_sq, B, D, T,
-            zpl.Tp if zpl is not None else pitch(T), K, idx)
+    _C.call('vq_lookup', _r(zn), zpl.data if zpl is not None else None, z_sq, e_hat, e_pl, e_sq, B, D, T, K, idx)
     return idx
 
 
@@ -279,10 +334,10 @@ def vq_gather(idx, e_hat, zn, z, want_q=True, want_stats=True):
     """-> q (B,D,T), sums (2,) [sum (q-zn)^2, sum (zn-z)^2], counts (K,) int32"""
     B, D, T = zn.shape
     K = e_hat.shape[0]
-    q = torch.empty_like(zn) if want_q else None
+    q = cl_empty(B, D, T, zn.device) if want_q else None
     sums = torch.zeros((2,), dtype=torch.float32, device=zn.device) if want_stats else None
     counts = torch.zeros((K,), dtype=torch.int32, device=zn.device) if want_stats else None
-    _C.call('vq_gather', idx, e_hat, zn, z, B, D, T, K, q, sums, counts)
+    _C.call('vq_gather', idx, e_hat, _r(zn), _r(z), B, D, T, K, _r(q), sums, counts)
     return q, sums, counts
 
 
@@ -295,9 +350,10 @@ def vq_finalize(sums, counts, N, scale, normalize, eps):
 def vq_bwd(g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, E, scale, normalize, want_dE=True):
     B, D, T = zn.shape
     K = e_hat.shape[0]
-    dz = torch.empty_like(zn)
+    dz = cl_empty(B, D, T, zn.device)
     dEh = torch.zeros_like(e_hat) if want_dE else None
-    _C.call('vq_bwd', g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, E, B, D, T, K, scale, int(normalize), dz, dEh)
+    _C.call('vq_bwd', _r(g_out), g_lq, g_le, idx, _r(z), _r(zn), z_norm, e_hat, E, B, D, T, K, scale, int(normalize),
+            dz.transpose(1, 2), dEh)
     return dz, dEh
 
 
@@ -313,7 +369,7 @@ def vq_ema_scatter(idx, z, K):
     B, D, T = z.shape
     zsum = torch.zeros((K, D), dtype=torch.float32, device=z.device)
     counts = torch.zeros((K,), dtype=torch.int32, device=z.device)
-    _C.call('vq_ema_scatter', idx, z, B, D, T, K, zsum, counts)
+    _C.call('vq_ema_scatter', idx, _r(z), B, D, T, K, zsum, counts)
     return zsum, counts
 
 
@@ -329,21 +385,21 @@ def vq_ema_update(zsum, counts, n_frames, mu, threshold, rand_rows, emb_sum, emb
 def vq_frame_rows(z, perm, K):
     B, D, T = z.shape
     out = _f32((K, D), z)
-    _C.call('vq_frame_rows', z, perm, B, D, T, K, out)
+    _C.call('vq_frame_rows', _r(z), perm, B, D, T, K, out)
     return out
 
 
 def jitter_fwd(x, src):
     B, D, T = x.shape
-    out = torch.empty_like(x)
-    _C.call('jitter_fwd', x, src, B, D, T, out)
+    out = cl_empty(B, D, T, x.device)
+    _C.call('jitter_fwd', _r(x), src, B, D, T, out.transpose(1, 2))
     return out
 
 
 def jitter_bwd(dout, src):
     B, D, T = dout.shape
-    din = torch.empty_like(dout)
-    _C.call('jitter_bwd', dout, src, B, D, T, din)
+    din = cl_empty(B, D, T, dout.device)
+    _C.call('jitter_bwd', _r(dout), src, B, D, T, din.transpose(1, 2))
     return din
 
 
@@ -351,14 +407,16 @@ def jitter_bwd(dout, src):
 # losses / optimiser
 # --------------------------------------------------------------------------------------------
 def logloss_fwd(xhat, x, scale=1.0):
+    # elementwise + full reduction: any common layout works, channels-last avoids a copy of xhat
     acc = torch.zeros((1,), dtype=torch.float32, device=x.device)
-    _C.call('logloss_fwd', xhat, x, x.numel(), scale, acc)
+    _C.call('logloss_fwd', _r(xhat), _r(x), x.numel(), scale, acc)
     return acc
 
 
 def logloss_bwd(xhat, x, g, scale):
-    dx = torch.empty_like(xhat)
-    _C.call('logloss_bwd', xhat, x, g, x.numel(), scale, dx)
+    B, C, T = xhat.shape
+    dx = cl_empty(B, C, T, xhat.device)
+    _C.call('logloss_bwd', _r(xhat), _r(x), g, x.numel(), scale, dx.transpose(1, 2))
     return dx
 
 
