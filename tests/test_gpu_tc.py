@@ -74,3 +74,65 @@ def test_conv_tc_data_gradient_operand(backends):
     _C.set_backend(_C.BACKEND_TC)
     b = Pm.conv_fwd(dypl, W.wb, k, 1, Cin)
     assert rel_err(b, a) < 1e-5          # K = 3072 products: fp32 summation-order differences only
+
+
+WGRAD_SHAPES = [
+    # B, Cin, Cout, T, taps, dil
+    (2, 64, 128, 128, 3, 1),
+    (16, 512, 512, 128, 3, 1),       # encoder block k3 (k-split over samples, atomic reduce)
+    (4, 512, 1024, 128, 3, 1),       # decoder conv_in: dy has 2C channels
+    (3, 512, 640, 128, 1, 1),        # res/skip 1x1: Cout not a multiple of 128
+    (2, 80, 512, 100, 3, 1),         # first conv: Cin = 80, ragged T
+    (2, 128, 80, 64, 1, 1),          # final layer
+    (1, 72, 96, 37, 3, 2),           # ragged everything, dilation 2
+    (2, 16, 16, 24, 3, 1),           # the small golden model
+]
+
+
+@pytest.mark.parametrize('P', [1, 3])
+@pytest.mark.parametrize('transposed', [False, True])
+@pytest.mark.parametrize('B,Cin,Cout,T,k,dil', WGRAD_SHAPES)
+def test_conv_wgrad_tc_vs_simt(backends, P, transposed, B, Cin, Cout, T, k, dil):
+    _C, Pm = backends
+    dy, u = g(B, Cout, T, seed=5), g(B, Cin, T, seed=6)
+    dypl, upl = Pm.make_planes(dy.cuda(), P)[0], Pm.make_planes(u.cuda(), P)[0]
+    _C.set_backend(_C.BACKEND_SIMT)
+    a = Pm.conv_wgrad(dypl, upl, k, dil, transposed)
+    _C.set_backend(_C.BACKEND_TC)
+    b = Pm.conv_wgrad(dypl, upl, k, dil, transposed)
+    torch.cuda.synchronize()
+    assert _C.call('debug_tc_timeouts') == 0
+    assert a.shape == b.shape == ((Cin, Cout, k) if transposed else (Cout, Cin, k))
+    assert rel_err(b, a) < 2e-5, rel_err(b, a)
+    pad = (k - 1) // 2 * dil
+    up = torch.nn.functional.pad(u.double(), (pad, pad))
+    ref = torch.stack([torch.einsum('bot,bit->oi', dy.double(), up[:, :, j * dil:j * dil + T]) for j in range(k)], dim=2)
+    if transposed:
+        ref = ref.transpose(0, 1).flip(2)
+    err = rel_err(b, ref)
+    assert err < (2e-5 if P == 3 else 1e-2), err
+
+
+@pytest.mark.parametrize('B,D,T,K,normalize', [(16, 64, 128, 512, True), (16, 64, 128, 512, False), (3, 128, 77, 300, True),
+                                               (2, 24, 50, 40, False), (8, 256, 128, 1024, False)])
+def test_vq_lookup_tc_vs_simt_and_fp64(backends, B, D, T, K, normalize):
+    """Indices of the tcgen05 distance+argmin kernel: identical to the fp32 SIMT kernel and to an fp64
+    argmin wherever the top-2 distance gap exceeds fp32 rounding (north_star's criterion)."""
+    _C, Pm = backends
+    z, E = g(B, D, T, seed=1).cuda(), g(K, D, seed=2).cuda()
+    e_hat, e_pl, e_sq = Pm.vq_prep_codebook(E.clone(), normalize, False)
+    zn, zpl, z_sq, _ = Pm.vq_prep_z(z, normalize)
+    _C.set_backend(_C.BACKEND_SIMT)
+    i_simt = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
+    _C.set_backend(_C.BACKEND_TC)
+    i_tc = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
+    torch.cuda.synchronize()
+    assert _C.call('debug_tc_timeouts') == 0
+    zf = zn.double().transpose(1, 2).reshape(B * T, D)
+    d = (zf.pow(2).sum(1, keepdim=True) + e_hat.double().pow(2).sum(1).view(1, -1)) - 2 * zf @ e_hat.double().t()
+    top2 = d.topk(2, dim=1, largest=False)
+    clear = (top2.values[:, 1] - top2.values[:, 0]) > 1e-5 * d.abs().max()
+    assert clear.float().mean() > 0.9
+    assert torch.equal(i_tc[clear], top2.indices[clear, 0])
+    assert torch.equal(i_simt[clear], top2.indices[clear, 0])
+    assert (i_tc != i_simt).float().mean() < 1e-3

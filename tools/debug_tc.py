@@ -28,3 +28,38 @@ for (B, Cin, Cout, T, k, dil, P) in shapes:
     except Exception as e:
         print((B, Cin, Cout, T, k, dil, P), 'FAILED', str(e)[:300], flush=True)
         break
+
+# ---- weight gradient ----
+for (B, Cin, Cout, T, k, dil, P) in [(2, 64, 128, 128, 3, 1, 1), (16, 512, 512, 128, 3, 1, 1), (2, 16, 16, 24, 3, 1, 3)]:
+    g = torch.Generator().manual_seed(2)
+    dy, u = torch.randn(B, Cout, T, generator=g).cuda(), torch.randn(B, Cin, T, generator=g).cuda()
+    dypl, upl = Pm.make_planes(dy, P)[0], Pm.make_planes(u, P)[0]
+    _C.set_backend(_C.BACKEND_SIMT)
+    a = Pm.conv_wgrad(dypl, upl, k, dil, False)
+    torch.cuda.synchronize()
+    _C.set_backend(_C.BACKEND_TC)
+    try:
+        b = Pm.conv_wgrad(dypl, upl, k, dil, False)
+        torch.cuda.synchronize()
+        print('wgrad', (B, Cin, Cout, T, k, dil, P), 'rel err tc vs simt %.3e' % rel(b, a), 'timeouts', _C.call('debug_tc_timeouts'), flush=True)
+    except Exception as e:
+        print('wgrad', (B, Cin, Cout, T, k, dil, P), 'FAILED', str(e)[:300], flush=True)
+        break
+
+# ---- VQ lookup ----
+for (B, D, T, K) in [(16, 64, 128, 512), (2, 24, 50, 40)]:
+    g = torch.Generator().manual_seed(3)
+    z, E = torch.randn(B, D, T, generator=g).cuda(), torch.randn(K, D, generator=g).cuda()
+    e_hat, e_pl, e_sq = Pm.vq_prep_codebook(E, False, False)
+    zn, zpl, z_sq, _ = Pm.vq_prep_z(z, False)
+    _C.set_backend(_C.BACKEND_SIMT)
+    i0 = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
+    torch.cuda.synchronize()
+    _C.set_backend(_C.BACKEND_TC)
+    try:
+        i1 = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
+        torch.cuda.synchronize()
+        print('vq', (B, D, T, K), 'mismatch frac %.2e' % float((i0 != i1).float().mean()), 'timeouts', _C.call('debug_tc_timeouts'), flush=True)
+    except Exception as e:
+        print('vq', (B, D, T, K), 'FAILED', str(e)[:300], flush=True)
+        break

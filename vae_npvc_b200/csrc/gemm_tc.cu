@@ -282,13 +282,5 @@ extern "C" int vnb_debug_tc_timeouts(void) {
     if (cudaMemcpyFromSymbol(&v, vnb::tc::g_tc_timeouts, sizeof(int)) != cudaSuccess) return -1;
     return v;
 }
-namespace vnb {
-
-int conv_wgrad_tc(const void*, const void*, int, int, int, int, int, int, int, int, float*, cudaStream_t) {
-    return 1;
-}
-int vq_lookup_tc(const void*, const float*, const void*, const float*, int, int, int, int, int64_t*, cudaStream_t) {
-    return 1;
-}
-
-}  // namespace vnb
+#include "tc_wgrad.cuh"
+#include "tc_vq.cuh"
