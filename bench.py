@@ -123,7 +123,7 @@ def time_dominant_kernel(P, iters=20):
     v = torch.randn(Cin, Cout, taps, device='cuda') * 0.02
     W = Pm.wn_prepare(v, None, True, P)
     xpl = Pm.make_planes(x, P)[0]
-    out = torch.empty(B, Cout, T, device='cuda')
+    out = Pm.cl_empty(B, Cout, T, 'cuda')
     flush = torch.empty(256 * 1024 * 1024 // 4, device='cuda')          # > 126 MB L2
     for _ in range(3):
         Pm.conv_fwd(xpl, W.wf, taps, 1, Cout, None, 0, None, out)
