@@ -76,7 +76,12 @@ int vnb_wn_backward(const float* dw, const float* v, const float* g, int d0, int
 int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T,
                  const void* w_planes, int taps, int dil, int Cout,
                  const float* bias, int bias_bstride, const float* residual,
-                 float* out, int accumulate, void* stream);
+                 float* out, int accumulate, double* gn_sums, int gn_groups, void* stream);
+/* gn_sums (optional, (B, gn_groups, 2) doubles ZEROED by the caller): the epilogue also accumulates
+ * sum and sum-of-squares of the final output values per (sample, channel group) - the GroupNorm
+ * statistics of layers.py:154,201 without a second pass over the activation.
+ * vnb_gn_finalize turns them into mean / rstd (biased variance, eps), n = values per (sample, group) */
+int vnb_gn_finalize(const double* gn_sums, int BG, double n, float eps, float* mean, float* rstd, void* stream);
 /* weight gradient in the reference parameter layout (d0,d1,k):
  * conv tap j: dW[co][ci][j] = sum_{b,t} dy[b,co,t] * u[b,ci,t+(j-(taps-1)/2)*dil];
  * transposed=0 -> dw[co][ci][j];  transposed=1 -> dw[ci][co][taps-1-j] */

@@ -127,7 +127,16 @@ def wn_backward(dw, v, g):
 
 
 # ---- GEMM-shaped -----------------------------------------------------------------------------
-def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False):
+def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False,
+             gn_groups=0, eps=1e-5):
+    r = _conv_fwd(x_pl, w_op, taps, dil, Cout, bias, bias_bstride, residual, out, accumulate)
+    if not gn_groups:
+        return r
+    mean, rstd = gn_stats(r, gn_groups, eps)
+    return r, mean, rstd
+
+
+def _conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False):
     x = x_pl.value()
     Cin = x_pl.C
     w = _join(w_op)[:, :Cout, :Cin].permute(1, 2, 0).contiguous()               # (co, ci, tap)

@@ -136,3 +136,22 @@ def test_vq_lookup_tc_vs_simt_and_fp64(backends, B, D, T, K, normalize):
     assert torch.equal(i_tc[clear], top2.indices[clear, 0])
     assert torch.equal(i_simt[clear], top2.indices[clear, 0])
     assert (i_tc != i_simt).float().mean() < 1e-3
+
+
+@pytest.mark.parametrize('be', ['simt', 'tc'])
+@pytest.mark.parametrize('B,Cin,Cout,T,k,groups', [(4, 512, 1024, 128, 3, 2), (3, 64, 64, 100, 3, 1), (2, 512, 512, 317, 3, 1)])
+def test_conv_fused_groupnorm_statistics(backends, be, B, Cin, Cout, T, k, groups):
+    """GroupNorm mean / rstd accumulated in the GEMM epilogue == torch statistics of the conv output."""
+    _C, Pm = backends
+    _C.set_backend(_C.BACKEND_SIMT if be == 'simt' else _C.BACKEND_TC)
+    x = g(B, Cin, T, seed=1) + 0.5
+    w = g(Cout, Cin, k, seed=2, scale=1.0 / (Cin * k) ** 0.5)
+    bias = g(B, Cout, seed=3)
+    xpl = Pm.make_planes(x.cuda(), 3)[0]
+    W = Pm.wn_prepare(w.cuda(), None, False, 3)
+    out, mean, rstd = Pm.conv_fwd(xpl, W.wf, k, 1, Cout, bias.cuda(), Cout, gn_groups=groups)
+    og = out.double().cpu().reshape(B, groups, -1) if out.is_contiguous() else \
+        Pm.to_nct(out).double().cpu().reshape(B, groups, -1)
+    m = og.mean(2)
+    rs = 1.0 / (og.var(2, unbiased=False) + 1e-5).sqrt()
+    assert rel_err(mean, m) < 1e-5 and rel_err(rstd, rs) < 1e-5

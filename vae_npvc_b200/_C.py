@@ -26,6 +26,7 @@ _PTR_DTYPES = {
     'int64_t*': (torch.int64,), 'const int64_t*': (torch.int64,),
     'int*': (torch.int32,), 'const int*': (torch.int32,),
     'void*': None, 'const void*': None,
+    'double*': (torch.float64,), 'const double*': (torch.float64,),
 }
 _SCALARS = {'int': ctypes.c_int, 'int64_t': ctypes.c_int64, 'float': ctypes.c_float, 'double': ctypes.c_double,
             'size_t': ctypes.c_size_t}

@@ -4,7 +4,7 @@
 namespace vnb {
 int conv_fwd_simt(const void* in, int P, int B, int Cin, int T, const void* w, int taps, int dil, int Cout,
                   const float* bias, int bias_bstride, const float* residual, float* out, int accumulate,
-                  cudaStream_t st);
+                  double* gn_sums, int gn_groups, cudaStream_t st);
 int conv_wgrad_simt(const void* dy, const void* u, int P, int B, int Cout, int Cin, int T, int taps, int dil,
                     int transposed, float* dw, cudaStream_t st);
 int vq_lookup_simt(const float* zn, const float* z_sq, const float* e_hat, const float* e_sq, int B, int D, int T,
@@ -12,7 +12,7 @@ int vq_lookup_simt(const float* zn, const float* z_sq, const float* e_hat, const
 // tensor-core backend: return VNB_OK, a negative error, or +1 = "shape not taken by this backend"
 int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int taps, int dil, int Cout,
                 const float* bias, int bias_bstride, const float* residual, float* out, int accumulate,
-                cudaStream_t st);
+                double* gn_sums, int gn_groups, cudaStream_t st);
 int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin, int T, int taps, int dil,
                   int transposed, float* dw, cudaStream_t st);
 int vq_lookup_tc(const void* z_planes, const float* z_sq, const void* e_planes, const float* e_sq, int B, int D,
@@ -23,15 +23,17 @@ using namespace vnb;
 
 extern "C" int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T, const void* w_planes, int taps,
                             int dil, int Cout, const float* bias, int bias_bstride, const float* residual, float* out,
-                            int accumulate, void* stream) {
+                            int accumulate, double* gn_sums, int gn_groups, void* stream) {
     VNB_REQUIRE(in_planes && w_planes && out, "conv_fwd: null pointer");
     VNB_REQUIRE(B > 0 && Cin > 0 && Cout > 0 && T > 0, "conv_fwd: bad shape B=%d Cin=%d Cout=%d T=%d", B, Cin, Cout, T);
     VNB_REQUIRE((P == 1 || P == 3) && taps >= 1 && (taps & 1) && dil >= 1, "conv_fwd: P=%d taps=%d dil=%d unsupported", P, taps, dil);
+    VNB_REQUIRE(!gn_sums || (gn_groups > 0 && Cout % gn_groups == 0), "conv_fwd: gn_groups=%d does not divide Cout=%d", gn_groups, Cout);
+    if (!gn_sums) gn_groups = 0;
     cudaStream_t st = (cudaStream_t)stream;
     const int be = backend();
     if (be != VNB_BACKEND_SIMT) {
         int r = conv_fwd_tc(in_planes, P, B, Cin, T, w_planes, taps, dil, Cout, bias, bias_bstride, residual, out,
-                            accumulate, st);
+                            accumulate, gn_sums, gn_groups, st);
         if (r <= 0) return r;
         if (be == VNB_BACKEND_TC) {
             set_error("conv_fwd: shape not supported by the tcgen05 backend (Cin=%d Cout=%d T=%d)", Cin, Cout, T);
@@ -39,7 +41,7 @@ extern "C" int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T,
         }
     }
     return conv_fwd_simt(in_planes, P, B, Cin, T, w_planes, taps, dil, Cout, bias, bias_bstride, residual, out,
-                         accumulate, st);
+                         accumulate, gn_sums, gn_groups, st);
 }
 
 extern "C" int vnb_conv_wgrad(const void* dy_planes, const void* u_planes, int P, int B, int Cout, int Cin, int T,

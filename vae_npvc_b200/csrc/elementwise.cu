@@ -162,6 +162,18 @@ __global__ void gn_stats_merge_kernel(const float* __restrict__ ws, int BG, int 
     }
 }
 
+// mean / rstd from the fp64 (sum, sum of squares) pairs accumulated by the conv epilogue
+__global__ void gn_finalize_kernel(const double* __restrict__ sums, int BG, double n, float eps,
+                                   float* __restrict__ mean, float* __restrict__ rstd) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= BG) return;
+    const double m = sums[2 * i] / n;
+    double var = sums[2 * i + 1] / n - m * m;
+    if (var < 0.0) var = 0.0;
+    mean[i] = (float)m;
+    rstd[i] = (float)(1.0 / sqrt(var + (double)eps));
+}
+
 // ------------------------------------------------------------------------------------------
 // encoder block epilogue: y = GN1(h)*gamma+beta (+ s) -> y fp32, planes(y), planes(lrelu(y))
 template <int VEC>
@@ -314,6 +326,14 @@ extern "C" int vnb_gn_stats(const float* h, int B, int C, int T, int groups, flo
     gn_stats_merge_kernel<<<ceil_div((int64_t)BG * 32, 128), 128, 0, ST>>>(ws, BG, chunks, T, rows_per, C / groups, eps,
                                                                            mean, rstd);
     VNB_LAUNCH_CHECK("gn_stats_merge");
+    return VNB_OK;
+}
+
+extern "C" int vnb_gn_finalize(const double* gn_sums, int BG, double n, float eps, float* mean, float* rstd,
+                               void* stream) {
+    VNB_REQUIRE(gn_sums && mean && rstd && BG > 0 && n > 0, "gn_finalize: bad arguments");
+    gn_finalize_kernel<<<ceil_div(BG, 128), 128, 0, ST>>>(gn_sums, BG, n, eps, mean, rstd);
+    VNB_LAUNCH_CHECK("gn_finalize");
     return VNB_OK;
 }
 

@@ -14,7 +14,7 @@ template <int P>
 __global__ void __launch_bounds__(256) conv_fwd_simt_kernel(
     const bf16* __restrict__ in, int B, int Cin, int T, const bf16* __restrict__ w, int taps, int dil, int Cout,
     int Cin_p, const float* __restrict__ bias, int bias_bstride, const float* __restrict__ residual,
-    float* __restrict__ out, int accumulate) {
+    float* __restrict__ out, int accumulate, double* __restrict__ gn_sums, int gn_groups) {
     __shared__ float Xs[KC][TM + 4];
     __shared__ float Ws[KC][TN + 4];
     const int t0 = blockIdx.x * TM, co0 = blockIdx.y * TN, b = blockIdx.z;
@@ -77,6 +77,11 @@ __global__ void __launch_bounds__(256) conv_fwd_simt_kernel(
             if (residual) r += residual[o];
             if (accumulate) r += out[o];
             out[o] = r;
+            if (gn_sums) {       // debug backend: plain per-element fp64 atomics
+                double* gs = gn_sums + ((int64_t)b * gn_groups + co / (Cout / gn_groups)) * 2;
+                atomicAdd(gs, (double)r);
+                atomicAdd(gs + 1, (double)r * (double)r);
+            }
         }
     }
 }
@@ -230,15 +235,15 @@ __global__ void __launch_bounds__(256) vq_lookup_simt_kernel(const float* __rest
 
 int conv_fwd_simt(const void* in, int P, int B, int Cin, int T, const void* w, int taps, int dil, int Cout,
                   const float* bias, int bias_bstride, const float* residual, float* out, int accumulate,
-                  cudaStream_t st) {
+                  double* gn_sums, int gn_groups, cudaStream_t st) {
     dim3 grid(ceil_div(T, TM), ceil_div(Cout, TN), B);
     const int Cin_p = round_up8(Cin);
     if (P == 1)
         conv_fwd_simt_kernel<1><<<grid, 256, 0, st>>>((const bf16*)in, B, Cin, T, (const bf16*)w, taps, dil, Cout, Cin_p,
-                                                      bias, bias_bstride, residual, out, accumulate);
+                                                      bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups);
     else
         conv_fwd_simt_kernel<3><<<grid, 256, 0, st>>>((const bf16*)in, B, Cin, T, (const bf16*)w, taps, dil, Cout, Cin_p,
-                                                      bias, bias_bstride, residual, out, accumulate);
+                                                      bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups);
     VNB_LAUNCH_CHECK("conv_fwd_simt");
     return VNB_OK;
 }

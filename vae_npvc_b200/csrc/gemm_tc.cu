@@ -36,8 +36,16 @@ struct ConvTcArgs {
     const float* residual;
     float* out;
     int accumulate;
+    double* gn_sums;      // optional (B, gn_groups, 2): fused GroupNorm sum / sum-of-squares
+    int gn_groups;
     int dbg;      // VNB_TC_DBG bisect level (0 = normal)
 };
+
+__device__ __forceinline__ double warp_sum_f64(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
 
 template <int BN>
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -133,15 +141,38 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
             const size_t row_off = ((size_t)b * a.T + (row_ok ? t : 0)) * a.Cout;
             const float* bias = a.bias ? a.bias + (size_t)b * a.bias_bstride : nullptr;
             const bool vec_ok = (a.Cout & 3) == 0;
+            // fused GroupNorm statistics: per-thread fp64 running sums of the current channel group
+            // (32-column blocks never straddle a group: host checks (Cout/groups) % 32 == 0)
+            const int cg = a.gn_sums ? a.Cout / a.gn_groups : 1;
+            double gs0 = 0.0, gs1 = 0.0;
+            int gcur = -1;
 #pragma unroll 1
-            for (int c0 = 0; c0 < BN; c0 += 32) {
+            for (int c0 = 0; c0 <= BN; c0 += 32) {
+                const int co = co0 + c0;
+                if (a.gn_sums) {
+                    const int g = (c0 < BN && co < a.Cout) ? co / cg : -1;       // warp-uniform
+                    if (g != gcur) {
+                        if (gcur >= 0) {
+                            gs0 = warp_sum_f64(gs0);
+                            gs1 = warp_sum_f64(gs1);
+                            if (lane == 0) {
+                                double* gp = a.gn_sums + ((size_t)b * a.gn_groups + gcur) * 2;
+                                atomicAdd(gp, gs0);
+                                atomicAdd(gp + 1, gs1);
+                            }
+                        }
+                        gs0 = gs1 = 0.0;
+                        gcur = g;
+                    }
+                }
+                if (c0 == BN) break;
                 float v[32];
                 __syncwarp();                                                            // tcgen05.ld is .sync.aligned
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);     // warp-collective
-                const int co = co0 + c0;
                 if (!row_ok || co >= a.Cout || a.dbg == 4) continue;
                 float* op = a.out + row_off + co;
                 const float* rp = a.residual ? a.residual + row_off + co : nullptr;
+                float bs0 = 0.f, bs1 = 0.f;
                 if (vec_ok) {
 #pragma unroll
                     for (int i = 0; i < 32; i += 4) {
@@ -160,6 +191,8 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                             r.x += x.x; r.y += x.y; r.z += x.z; r.w += x.w;
                         }
                         *reinterpret_cast<float4*>(op + i) = r;
+                        bs0 += (r.x + r.y) + (r.z + r.w);
+                        bs1 += (r.x * r.x + r.y * r.y) + (r.z * r.z + r.w * r.w);
                     }
                 } else {
 #pragma unroll
@@ -169,9 +202,13 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                             if (rp) r += rp[i];
                             if (a.accumulate) r += op[i];
                             op[i] = r;
+                            bs0 += r;
+                            bs1 += r * r;
                         }
                     }
                 }
+                gs0 += (double)bs0;
+                gs1 += (double)bs1;
             }
         }
     }
@@ -262,11 +299,12 @@ static int launch_conv_tc(const void* in, const void* w, int Tdim, int Cin_p, co
 
 int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int taps, int dil, int Cout,
                 const float* bias, int bias_bstride, const float* residual, float* out, int accumulate,
-                cudaStream_t st) {
+                double* gn_sums, int gn_groups, cudaStream_t st) {
     // shapes this backend takes; everything else goes to the SIMT backend (or errors under VNB_BACKEND_TC)
     if (Cout < 8 || Cin < 8 || B > 65535) return 1;
+    if (gn_sums && ((Cout / gn_groups) & 31) != 0) return 1;      // statistics blocks of 32 channels must not straddle groups
     static const int dbg = getenv("VNB_TC_DBG") ? atoi(getenv("VNB_TC_DBG")) : 0;
-    ConvTcArgs a{B, Cin, Cout, T, taps, dil, P, bias, bias_bstride, residual, out, accumulate, dbg};
+    ConvTcArgs a{B, Cin, Cout, T, taps, dil, P, bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups, dbg};
     const int Cin_p = round_up8(Cin);
     // widest N tile that still gives the 148 SMs about one CTA each
     const int64_t mt = (int64_t)ceil_div(T, TC_BM) * B;

@@ -47,14 +47,26 @@ __global__ void linear_bwd_w_kernel(const float* __restrict__ dp, const float* _
     dW[e] = s;
 }
 
-__global__ void linear_bwd_y_kernel(const float* __restrict__ dp, const float* __restrict__ W, int B, int I, int O,
-                                    float* __restrict__ dy, int accumulate) {
-    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= (int64_t)B * I) return;
-    const int b = (int)(e / I), i = (int)(e - (int64_t)b * I);
+// dy[b,i] (+)= sum_o W[o,i]*dp[b,o].  grid (ceil(I/32), B), block 32 x 8: lanes over i (coalesced W rows),
+// the 8 warps split o, shared-memory reduce.
+__global__ void __launch_bounds__(256) linear_bwd_y_kernel(const float* __restrict__ dp, const float* __restrict__ W,
+                                                           int B, int I, int O, float* __restrict__ dy,
+                                                           int accumulate) {
+    __shared__ float red[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int b = blockIdx.y, i = blockIdx.x * 32 + tx;
     float s = 0.f;
-    for (int o = 0; o < O; o++) s = fmaf(W[(int64_t)o * I + i], dp[(int64_t)b * O + o], s);
-    dy[e] = accumulate ? dy[e] + s : s;
+    if (i < I)
+        for (int o = ty; o < O; o += 8) s = fmaf(W[(int64_t)o * I + i], dp[(int64_t)b * O + o], s);
+    red[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0 && i < I) {
+        float t = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; j++) t += red[j][tx];
+        const int64_t e = (int64_t)b * I + i;
+        dy[e] = accumulate ? dy[e] + t : t;
+    }
 }
 
 constexpr float LOG_2PI_F = 1.8378770664093453f;
@@ -165,7 +177,7 @@ extern "C" int vnb_linear_bwd(const float* dp, const float* y, const float* W, i
         VNB_LAUNCH_CHECK("linear_bwd_w");
     }
     if (dy) {
-        linear_bwd_y_kernel<<<ceil_div((int64_t)B * I, 128), 128, 0, st>>>(dp, W, B, I, O, dy, accumulate_dy);
+        linear_bwd_y_kernel<<<dim3(ceil_div(I, 32), B), 256, 0, st>>>(dp, W, B, I, O, dy, accumulate_dy);
         VNB_LAUNCH_CHECK("linear_bwd_y");
     }
     return VNB_OK;

@@ -132,8 +132,7 @@ class EncBlockFn(Function):
             v, g, bias, gamma, beta = params[5 * j:5 * j + 5]
             d = dil if j == 0 else 1
             W = Pm.wn_prepare(v, g, False, P)
-            h = Pm.conv_fwd(inp, W.wf, W.taps, d, C, bias, 0)
-            mean, rstd = Pm.gn_stats(h, 1)
+            h, mean, rstd = Pm.conv_fwd(inp, W.wf, W.taps, d, C, bias, 0, gn_groups=1)
             if j < n_layers - 1:
                 yj, _, nxt = Pm.enc_out(h, None, mean, rstd, gamma, beta, P, True, False, True)
             else:
@@ -221,7 +220,9 @@ class DecBlockFn(Function):
             Wc = Pm.wn_prepare(v_c, g_c, False, P, need_wf=False, need_wb=False, need_w32=True)
             wc32 = Wc.w32.view(2 * C, -1)
             p = Pm.linear_fwd(cond, wc32, b_c, b_in)
-            a = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, p, 2 * C)
+            a, mean, rstd = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, p, 2 * C, gn_groups=2)
+        elif not has_cond:
+            a, mean, rstd = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, b_in, 0, gn_groups=2)
         else:
             a = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, b_in, 0)
             if has_cond:
@@ -229,8 +230,7 @@ class DecBlockFn(Function):
                 cpl = _input_planes(cond, P)
                 Wc = Pm.wn_prepare(v_c, g_c, False, P, need_wb=ctx.needs_input_grad[1])
                 wc_wb = Wc.wb
-                Pm.conv_fwd(cpl, Wc.wf, 1, 1, 2 * C, b_c, 0, None, a, True)
-        mean, rstd = Pm.gn_stats(a, 2)
+                a, mean, rstd = Pm.conv_fwd(cpl, Wc.wf, 1, 1, 2 * C, b_c, 0, None, a, True, gn_groups=2)
         gpl = Pm.dec_gate(a, mean, rstd, gamma, beta, P)
         Wrs = Pm.wn_prepare(v_rs, g_rs, False, P)
         r = Pm.conv_fwd(gpl, Wrs.wf, 1, 1, C + S, b_rs, 0)

@@ -118,19 +118,28 @@ def wn_backward(dw, v, g):
 # --------------------------------------------------------------------------------------------
 # GEMM-shaped ops
 # --------------------------------------------------------------------------------------------
-def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False):
-    """x_pl: Planes (B,Cin,T); w_op: (P,taps,Cout,Cin_p) bf16 -> out fp32, logical (B,Cout,T)."""
+def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False,
+             gn_groups=0, eps=1e-5):
+    """x_pl: Planes (B,Cin,T); w_op: (P,taps,Cout,Cin_p) bf16 -> out fp32, logical (B,Cout,T).
+    gn_groups > 0: also returns the GroupNorm (mean, rstd) (B, gn_groups) of the result, accumulated
+    in the GEMM epilogue -> (out, mean, rstd)."""
     user_out = None
+    dev = x_pl.data.device
     if out is None:
-        out = cl_empty(x_pl.B, Cout, x_pl.T, x_pl.data.device)
+        out = cl_empty(x_pl.B, Cout, x_pl.T, dev)
     elif not is_cl(out):                      # reference-layout buffer from a caller: stage through channels-last
         user_out, out = out, as_cl(out)
+    sums = torch.zeros((x_pl.B, gn_groups, 2), dtype=torch.float64, device=dev) if gn_groups else None
     _C.call('conv_fwd', x_pl.data, x_pl.P, x_pl.B, x_pl.C, x_pl.T, w_op, taps, dil, Cout, bias,
-            bias_bstride, _r(residual), out.transpose(1, 2), int(accumulate))
+            bias_bstride, _r(residual), out.transpose(1, 2), int(accumulate), sums, gn_groups)
     if user_out is not None:
         user_out.copy_(out)
-        return user_out
-    return out
+        out = user_out
+    if not gn_groups:
+        return out
+    mean, rstd = _f32((x_pl.B, gn_groups), out), _f32((x_pl.B, gn_groups), out)
+    _C.call('gn_finalize', sums, x_pl.B * gn_groups, float(Cout // gn_groups * x_pl.T), eps, mean, rstd)
+    return out, mean, rstd
 
 
 def conv_wgrad(dy_pl, u_pl, taps, dil, transposed):
