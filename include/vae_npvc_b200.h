@@ -69,6 +69,17 @@ int vnb_wn_prepare(const float* v, const float* g, int d0, int d1, int k, int tr
 int vnb_wn_backward(const float* dw, const float* v, const float* g, int d0, int d1, int k,
                     float* dv, float* dg, void* stream);
 
+/* Batched forms over the trainer's flat fp32 parameter / gradient buffers: ONE launch for all conv
+ * layers of the model (55 in the VCC2020 recipe).  desc: int64 [n_layers][10] = {v_off, g_off (-1 =
+ * plain weight), d0, d1, k, transposed, wf_off, wb_off, w32_off (-1 = none), row0} with element
+ * offsets into flat_p / wbuf (bf16) / w32buf; row2layer: int32 [total_rows] (total_rows = sum of d0).
+ * backward: on entry the v slot of flat_g holds dw (written there by vnb_conv_wgrad), on exit dv; the
+ * g slot receives dg. */
+int vnb_wn_prepare_batch(const float* flat_p, const int64_t* desc, const int* row2layer, int total_rows,
+                         int P, void* wbuf, float* w32buf, void* stream);
+int vnb_wn_backward_batch(const float* flat_p, float* flat_g, const int64_t* desc, const int* row2layer,
+                          int total_rows, void* stream);
+
 /* ---- stride-1 'same' conv as GEMM: nn.Conv1d / nn.ConvTranspose1d call sites layers.py:152,165,
  * 229,231,244; vqvae.py:155,174,256,283,285.  Also the data-gradient (pass the wb operand).
  * out[b,co,t] = beta*out + bias[b*bias_bstride+co] + residual[b,co,t]
@@ -124,10 +135,12 @@ int vnb_gn_bwd_rows(const float* dn, const float* h, const float* mean, const fl
 int vnb_gate_bwd_rows(const float* dg, const float* a, const float* mean, const float* rstd,
                       const float* gamma, const float* beta, int B, int C, int T, float* R, void* stream);
 /* from R: dgamma[c], dbeta[c], S[b,group,0..1] = sum_c gamma*R0, sum_c gamma*R1, and (optional)
- * dpre_bsum[b,c] = sum_t dpre, dpre_csum[c] = sum_{b,t} dpre  (dpre = grad wrt the GN input) */
+ * dpre_bsum[b,c] = sum_t dpre, dpre_csum[c] = sum_{b,t} dpre  (dpre = grad wrt the GN input);
+ * dbeta2 / dpre_csum2: optional second copies (two biases that receive the same gradient, written
+ * straight into their gradient slots) */
 int vnb_gn_bwd_finalize(const float* R, const float* gamma, const float* rstd, int B, int C, int T,
                         int groups, float* dgamma, float* dbeta, float* S, float* dpre_bsum,
-                        float* dpre_csum, void* stream);
+                        float* dpre_csum, float* dbeta2, float* dpre_csum2, void* stream);
 /* dpre = rstd*(gamma*dn - S0/n - xhat*S1/n) -> planes (+ optional planes of dn itself) */
 int vnb_gn_bwd_apply(const float* dn, const float* h, const float* mean, const float* rstd,
                      const float* gamma, const float* S, int B, int C, int T, int groups, int P,

@@ -155,7 +155,41 @@ def _conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=N
     return r
 
 
-def conv_wgrad(dy_pl, u_pl, taps, dil, transposed):
+def wn_prepare_batch(flat_p, desc, row2layer, P, wbuf, w32buf):
+    for L in desc.tolist():
+        v_off, g_off, d0, d1, k, tr, wf_off, wb_off, w32_off, _ = L
+        v = flat_p[v_off:v_off + d0 * d1 * k].view(d0, d1, k)
+        g = flat_p[g_off:g_off + d0].view(d0, 1, 1) if g_off >= 0 else None
+        W = wn_prepare(v, g, tr, P, wf_off >= 0, wb_off >= 0, w32_off >= 0)
+        if wf_off >= 0:
+            wbuf[wf_off:wf_off + W.wf.numel()].copy_(W.wf.reshape(-1))
+        if wb_off >= 0:
+            wbuf[wb_off:wb_off + W.wb.numel()].copy_(W.wb.reshape(-1))
+        if w32_off >= 0:
+            w32buf[w32_off:w32_off + W.w32.numel()].copy_(W.w32.reshape(-1))
+
+
+def wn_backward_batch(flat_p, flat_g, desc, row2layer):
+    for L in desc.tolist():
+        v_off, g_off, d0, d1, k = L[:5]
+        if g_off < 0:
+            continue
+        n = d0 * d1 * k
+        dv, dg = wn_backward(flat_g[v_off:v_off + n].view(d0, d1, k).clone(), flat_p[v_off:v_off + n].view(d0, d1, k),
+                             flat_p[g_off:g_off + d0].view(d0, 1, 1))
+        flat_g[v_off:v_off + n].copy_(dv.reshape(-1))
+        flat_g[g_off:g_off + d0].copy_(dg.reshape(-1))
+
+
+def conv_wgrad(dy_pl, u_pl, taps, dil, transposed, out=None):
+    dw = _conv_wgrad(dy_pl, u_pl, taps, dil, transposed)
+    if out is not None:
+        out.copy_(dw)
+        return out
+    return dw
+
+
+def _conv_wgrad(dy_pl, u_pl, taps, dil, transposed):
     dy, u = dy_pl.value(), u_pl.value()
     pad = (taps - 1) // 2 * dil
     up = F.pad(u, (pad, pad))
@@ -234,7 +268,19 @@ def gate_bwd_rows(dg, a, mean, rstd, gamma, beta):
     return torch.stack([dn.sum(2), (dn * xh).sum(2), xh.sum(2)], dim=2)
 
 
-def gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums=False):
+def gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums=False, out=None):
+    out = out or {}
+    dgamma, dbeta, S, bsum, csum = _gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums or out.get('csum') is not None
+                                                    or out.get('csum2') is not None)
+    res = {'dgamma': dgamma, 'dbeta': dbeta, 'csum': csum, 'dbeta2': dbeta, 'csum2': csum}
+    for k, dst in out.items():
+        if dst is not None:
+            dst.copy_(res[k])
+    return (None if out.get('dgamma') is not None else dgamma, None if out.get('dbeta') is not None else dbeta, S,
+            bsum if want_sums else None, None if out.get('csum') is not None else (csum if want_sums else None))
+
+
+def _gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums=False):
     B, C, _ = R.shape
     gm = gamma.detach().view(1, C)
     dgamma, dbeta = R[:, :, 1].sum(0), R[:, :, 0].sum(0)
@@ -289,9 +335,10 @@ def embed_fwd(table, idx):
     return table.detach()[idx]
 
 
-def embed_bwd(dout, idx, num_rows):
+def embed_bwd(dout, idx, num_rows, out=None):
     dim = dout.shape[-1]
-    return torch.zeros(num_rows, dim).index_add_(0, idx.reshape(-1), dout.reshape(-1, dim))
+    t = out if out is not None else torch.zeros(num_rows, dim)
+    return t.index_add_(0, idx.reshape(-1), dout.reshape(-1, dim))
 
 
 def linear_fwd(y, W, bias, bias2=None):
@@ -303,8 +350,11 @@ def linear_fwd(y, W, bias, bias2=None):
     return p
 
 
-def linear_bwd(dp, y, W, dy=None):
+def linear_bwd(dp, y, W, dy=None, dW_out=None):
     dW = dp.t() @ y
+    if dW_out is not None:
+        dW_out.copy_(dW)
+        dW = dW_out
     d = dp @ W
     if dy is not None:
         dy += d
@@ -378,12 +428,17 @@ def vq_bwd(g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, E, scale, normalize, wa
     return dz, dEh
 
 
-def vq_bwd_codebook(dE_hat, E, normalize):
+def vq_bwd_codebook(dE_hat, E, normalize, out=None):
     if not normalize:
-        return dE_hat.clone()
-    ss = E.pow(2).sum(1, keepdim=True)
-    dot = (E * dE_hat).sum(1, keepdim=True)
-    return (dE_hat - E * dot / ss) / ss.sqrt()
+        r = dE_hat.clone()
+    else:
+        ss = E.pow(2).sum(1, keepdim=True)
+        dot = (E * dE_hat).sum(1, keepdim=True)
+        r = (dE_hat - E * dot / ss) / ss.sqrt()
+    if out is not None:
+        out.copy_(r)
+        return out
+    return r
 
 
 def vq_ema_scatter(idx, z, K):

@@ -1,0 +1,94 @@
+"""WeightBank: all conv weights of a model materialised by ONE kernel per optimiser step.
+
+The reference re-derives ``w = g * v / ||v||`` in a forward pre-hook of each of its 55 conv modules
+(old-style nn.utils.weight_norm, vae_npvc/model/vqvae.py:203-208, 329-334) and autograd walks 55
+separate weight-norm backward graphs.  Here the trainer keeps parameters and gradients in two flat fp32
+buffers; the bank holds a device-side table of where every conv's (v, g) sits in them and
+
+  * ``prepare()``          one launch: every layer's bf16 GEMM operand planes (forward operand ``wf``,
+                           data-gradient operand ``wb``, fp32 effective weight for the 1x1 speaker-
+                           conditioning convs) straight from the flat parameter buffer
+  * ``finish_backward()``  one launch: the weight-gradient GEMMs have written raw dW into the v slots of
+                           the flat gradient buffer; this turns them into (dv, dg) in place
+
+While a bank is installed (functional.set_bank) the autograd Functions take their operands from it and
+write parameter gradients directly into the gradient slots instead of returning them to autograd.
+"""
+import torch
+import torch.nn as nn
+
+from . import prims as Pm
+
+
+def _align(n, a=64):
+    return (n + a - 1) // a * a
+
+
+class _Entry(object):
+    __slots__ = ('W', 'v', 'g')
+
+    def __init__(self, W, v, g):
+        self.W, self.v, self.g = W, v, g
+
+
+class WeightBank(object):
+    def __init__(self, model, flat_p, flat_g, P, prims=None):
+        self.Pm = prims or Pm
+        self.P = P
+        self.flat_p, self.flat_g = flat_p, flat_g
+        dev = flat_p.device
+        base, end = flat_p.data_ptr(), flat_p.data_ptr() + flat_p.numel() * 4
+        rows, desc, entries = [], [], []
+        w_off = w32_off = row0 = 0
+        for name, m in model.named_modules():
+            if not isinstance(m, (nn.Conv1d, nn.ConvTranspose1d)):
+                continue
+            if hasattr(m, 'weight_g'):
+                v, g = m.weight_v, m.weight_g
+            else:
+                v, g = m.weight, None
+            if not (base <= v.data_ptr() < end) or (g is not None and not (base <= g.data_ptr() < end)):
+                continue                                  # not a flat-buffer parameter (frozen / foreign)
+            transposed = isinstance(m, nn.ConvTranspose1d)
+            d0, d1, k = v.shape
+            co, ci = (d1, d0) if transposed else (d0, d1)
+            n_wf, n_wb = P * k * co * Pm.pitch(ci), P * k * ci * Pm.pitch(co)
+            wf_off, wb_off = w_off, w_off + _align(n_wf)
+            w_off = wb_off + _align(n_wb)
+            want32 = name.endswith('conv_cond')
+            e32 = w32_off if want32 else -1
+            if want32:
+                w32_off += _align(v.numel())
+            desc.append([(v.data_ptr() - base) // 4, (g.data_ptr() - base) // 4 if g is not None else -1, d0, d1, k,
+                         int(transposed), wf_off, wb_off, e32, row0])
+            rows += [len(desc) - 1] * d0
+            row0 += d0
+            entries.append((v, g, transposed, k, co, ci, wf_off, n_wf, wb_off, n_wb, e32))
+        self.n_layers = len(desc)
+        # zero-filled once: the pitch padding of the operand planes must stay finite
+        self.wbuf = torch.zeros(max(w_off, 1), dtype=torch.bfloat16, device=dev)
+        self.w32buf = torch.zeros(max(w32_off, 1), dtype=torch.float32, device=dev)
+        self.desc = torch.tensor(desc if desc else [[0] * 10], dtype=torch.int64, device=dev)
+        self.row2layer = torch.tensor(rows if rows else [0], dtype=torch.int32, device=dev)
+        self.by_ptr = {}
+        for (v, g, transposed, k, co, ci, wf_off, n_wf, wb_off, n_wb, e32) in entries:
+            wf = self.wbuf[wf_off:wf_off + n_wf].view(P, k, co, Pm.pitch(ci))
+            wb = self.wbuf[wb_off:wb_off + n_wb].view(P, k, ci, Pm.pitch(co))
+            w32 = self.w32buf[e32:e32 + v.numel()].view_as(v) if e32 >= 0 else None
+            self.by_ptr[v.data_ptr()] = _Entry(self.Pm.ConvWeights(wf, wb, w32, k, co, ci, transposed), v, g)
+        self.fresh = False
+
+    def has(self, v):
+        return v is not None and v.data_ptr() in self.by_ptr
+
+    def weights(self, v):
+        return self.by_ptr[v.data_ptr()].W
+
+    def prepare(self):
+        if self.n_layers:
+            self.Pm.wn_prepare_batch(self.flat_p, self.desc, self.row2layer, self.P, self.wbuf, self.w32buf)
+        self.fresh = True
+
+    def finish_backward(self):
+        if self.n_layers:
+            self.Pm.wn_backward_batch(self.flat_p, self.flat_g, self.desc, self.row2layer)

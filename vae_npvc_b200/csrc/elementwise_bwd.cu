@@ -102,7 +102,8 @@ __global__ void __launch_bounds__(256) gn_bwd_groupsum_kernel(const float* __res
 __global__ void gn_bwd_channel_kernel(const float* __restrict__ R, const float* __restrict__ gamma,
                                       const float* __restrict__ rstd, const float* __restrict__ S, int B, int C, int T,
                                       int groups, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                      float* __restrict__ dpre_bsum, float* __restrict__ dpre_csum) {
+                                      float* __restrict__ dpre_bsum, float* __restrict__ dpre_csum,
+                                      float* __restrict__ dbeta2, float* __restrict__ dpre_csum2) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const int cg = C / groups, g = c / cg;
@@ -113,7 +114,7 @@ __global__ void gn_bwd_channel_kernel(const float* __restrict__ R, const float* 
         const float* r = R + ((int64_t)b * C + c) * 3;
         dbt += r[0];
         dgm += r[1];
-        if (dpre_bsum || dpre_csum) {
+        if (dpre_bsum || dpre_csum || dpre_csum2) {
             const float* s = S + (b * groups + g) * 2;
             const float v = rstd[b * groups + g] * (gm * r[0] - (float)T * s[0] * inv_n - r[2] * s[1] * inv_n);
             if (dpre_bsum) dpre_bsum[(int64_t)b * C + c] = v;
@@ -123,6 +124,8 @@ __global__ void gn_bwd_channel_kernel(const float* __restrict__ R, const float* 
     if (dgamma) dgamma[c] = dgm;
     if (dbeta) dbeta[c] = dbt;
     if (dpre_csum) dpre_csum[c] = dcs;
+    if (dbeta2) dbeta2[c] = dbt;
+    if (dpre_csum2) dpre_csum2[c] = dcs;
 }
 
 template <int VEC>
@@ -235,12 +238,13 @@ extern "C" int vnb_gate_bwd_rows(const float* dg, const float* a, const float* m
 
 extern "C" int vnb_gn_bwd_finalize(const float* R, const float* gamma, const float* rstd, int B, int C, int T,
                                    int groups, float* dgamma, float* dbeta, float* S, float* dpre_bsum,
-                                   float* dpre_csum, void* stream) {
+                                   float* dpre_csum, float* dbeta2, float* dpre_csum2, void* stream) {
     VNB_REQUIRE(R && gamma && rstd && S && B > 0 && C > 0 && groups > 0 && C % groups == 0, "gn_bwd_finalize: bad arguments");
     cudaStream_t st = (cudaStream_t)stream;
     gn_bwd_groupsum_kernel<<<B * groups, 256, 0, st>>>(R, gamma, C, groups, S);
     VNB_LAUNCH_CHECK("gn_bwd_groupsum");
-    gn_bwd_channel_kernel<<<ceil_div(C, 128), 128, 0, st>>>(R, gamma, rstd, S, B, C, T, groups, dgamma, dbeta, dpre_bsum, dpre_csum);
+    gn_bwd_channel_kernel<<<ceil_div(C, 128), 128, 0, st>>>(R, gamma, rstd, S, B, C, T, groups, dgamma, dbeta, dpre_bsum, dpre_csum, dbeta2,
+                                                            dpre_csum2);
     VNB_LAUNCH_CHECK("gn_bwd_channel");
     return VNB_OK;
 }

@@ -32,6 +32,46 @@ def get_precision():
     return _PRECISION['P']
 
 
+_BANK = {'bank': None}
+
+
+def set_bank(bank):
+    """Install (or remove, with None) a bank.WeightBank: conv operands then come from it and parameter
+    gradients are written straight into the parameters' ``.grad`` slots (the Functions return None for
+    them).  Used by the Trainer; plain module-level use of the layers never sets one."""
+    _BANK['bank'] = bank
+
+
+def get_bank():
+    return _BANK['bank']
+
+
+def _slot(p):
+    """The gradient slot of leaf parameter ``p`` when gradients are written directly, else None."""
+    if _BANK['bank'] is None or p is None or not getattr(p, 'is_leaf', False):
+        return None
+    return p.grad
+
+
+def _weights(v, g, transposed, P, need_wf=True, need_wb=True, need_w32=False):
+    bank = _BANK['bank']
+    if bank is not None and bank.P == P and bank.has(v):
+        W = bank.weights(v)
+        if not need_w32 or W.w32 is not None:
+            return W
+    return Pm.wn_prepare(v, g, transposed, P, need_wf=need_wf, need_wb=need_wb, need_w32=need_w32)
+
+
+def _wgrad(dypl, upl, taps, dil, transposed, v, g):
+    """Weight gradient of a conv -> (dv, dg) for autograd, or (None, None) after writing raw dW into the
+    v gradient slot (the bank's finish_backward turns it into dv, dg)."""
+    bank = _BANK['bank']
+    if bank is not None and bank.has(v) and _slot(v) is not None:
+        Pm.conv_wgrad(dypl, upl, taps, dil, transposed, out=v.grad)
+        return None, None
+    return _dw_to_param_grads(Pm.conv_wgrad(dypl, upl, taps, dil, transposed), v, g)
+
+
 def attach_planes(t, kind, planes):
     if planes is None:
         return
@@ -80,20 +120,25 @@ class ConvFn(Function):
         x = Pm.as_cl(x)
         xpl = _input_planes(x, P, act, scale)
         need_dx = ctx.needs_input_grad[0]
-        W = Pm.wn_prepare(v, g, transposed, P, need_wb=need_dx)
+        W = _weights(v, g, transposed, P, need_wb=need_dx)
         out = Pm.conv_fwd(xpl, W.wf, W.taps, dil, W.Cout, bias, 0)
-        ctx.save_for_backward(x if (act != ACT_NONE or scale != 1.0) else None, v, g)
+        ctx.save_for_backward(x if (act != ACT_NONE or scale != 1.0) else None, v, g, bias)
         ctx.xpl, ctx.wb = xpl, W.wb
         ctx.cfg = (transposed, dil, act, scale, P, W.taps, W.Cin, bias is not None)
         return out
 
     @staticmethod
     def backward(ctx, dy):
-        x, v, g = ctx.saved_tensors
+        x, v, g, bias = ctx.saved_tensors
         transposed, dil, act, scale, P, taps, Cin, has_bias = ctx.cfg
         dy = Pm.as_cl(dy)
         dypl = Pm.make_planes(dy, P)[0]
-        db = Pm.channel_sum(dy) if (has_bias and ctx.needs_input_grad[3]) else None
+        db = None
+        if has_bias and ctx.needs_input_grad[3]:
+            slot = _slot(bias)
+            db = Pm.channel_sum(dy, slot)
+            if slot is not None:
+                db = None
         dx = None
         if ctx.needs_input_grad[0]:
             dx = Pm.conv_fwd(dypl, ctx.wb, taps, dil, Cin)
@@ -101,8 +146,7 @@ class ConvFn(Function):
                 dx = Pm.act_bwd_add(dx, x, None, act, scale)
         dv = dg = None
         if ctx.needs_input_grad[1]:
-            dw = Pm.conv_wgrad(dypl, ctx.xpl, taps, dil, transposed)
-            dv, dg = _dw_to_param_grads(dw, v, g)
+            dv, dg = _wgrad(dypl, ctx.xpl, taps, dil, transposed, v, g)
         return dx, dv, dg, db, None, None, None, None, None, None
 
 
@@ -131,13 +175,13 @@ class EncBlockFn(Function):
         for j in range(n_layers):
             v, g, bias, gamma, beta = params[5 * j:5 * j + 5]
             d = dil if j == 0 else 1
-            W = Pm.wn_prepare(v, g, False, P)
+            W = _weights(v, g, False, P)
             h, mean, rstd = Pm.conv_fwd(inp, W.wf, W.taps, d, C, bias, 0, gn_groups=1)
             if j < n_layers - 1:
                 yj, _, nxt = Pm.enc_out(h, None, mean, rstd, gamma, beta, P, True, False, True)
             else:
                 vs, gs, bs = params[5 * n_layers:5 * n_layers + 3]
-                Ws = Pm.wn_prepare(vs, gs, False, P)
+                Ws = _weights(vs, gs, False, P)
                 s = Pm.conv_fwd(cpl, Ws.wf, Ws.taps, 1, C, bs, 0)
                 y, ypl, yupl = Pm.enc_out(h, s, mean, rstd, gamma, beta, P, True, True, True)
                 yj, nxt = None, None
@@ -164,20 +208,22 @@ class EncBlockFn(Function):
             v, g, bias, gamma, beta = params[5 * j:5 * j + 5]
             last = j == n_layers - 1
             R = Pm.gn_bwd_rows(dn, L['h'], L['mean'], L['rstd'], 1)
-            dgamma, dbeta, S, _, csum = Pm.gn_bwd_finalize(R, gamma, L['rstd'], T, 1, True)
+            bs = params[5 * n_layers + 2]
+            slots = {'dgamma': _slot(gamma), 'dbeta': _slot(beta), 'csum': _slot(bias),
+                     'dbeta2': _slot(bs) if last else None}          # skip bias grad = sum_{b,t} dy = dbeta
+            dgamma, dbeta, S, _, csum = Pm.gn_bwd_finalize(R, gamma, L['rstd'], T, 1, True, slots)
             dpre, dnpl = Pm.gn_bwd_apply(dn, L['h'], L['mean'], L['rstd'], gamma, S, 1, P, last)
             if last:
                 dypl = dnpl
-                grads[5 * n_layers + 2] = dbeta.clone()               # skip bias: sum_{b,t} dy
-            dw = Pm.conv_wgrad(dpre, L['inp'], L['taps'], L['d'], False)
-            dv, dg = _dw_to_param_grads(dw, v, g)
+                if slots['dbeta2'] is None:
+                    grads[5 * n_layers + 2] = (dbeta if dbeta is not None else beta.grad).clone()
+            dv, dg = _wgrad(dpre, L['inp'], L['taps'], L['d'], False, v, g)
             grads[5 * j:5 * j + 5] = [dv, dg, csum, dgamma, dbeta]
             du = Pm.conv_fwd(dpre, L['wb'], L['taps'], L['d'], C)
             if j > 0:
                 dn = Pm.act_bwd_add(du, ctx.layers[j - 1]['yj'], None, ACT_LRELU)
         vs, gs, bs = params[5 * n_layers:5 * n_layers + 3]
-        dws = Pm.conv_wgrad(dypl, ctx.cpl, 1, 1, False)
-        grads[5 * n_layers], grads[5 * n_layers + 1] = _dw_to_param_grads(dws, vs, gs)
+        grads[5 * n_layers], grads[5 * n_layers + 1] = _wgrad(dypl, ctx.cpl, 1, 1, False, vs, gs)
         dc = None
         if ctx.needs_input_grad[0]:
             dcs = Pm.conv_fwd(dypl, ctx.ws_wb, 1, 1, C)
@@ -211,13 +257,13 @@ class DecBlockFn(Function):
         B, C, T = x.shape
         S = v_rs.shape[0] - C
         xpl = _input_planes(x, P)
-        Win = Pm.wn_prepare(v_in, g_in, True, P, need_wb=ctx.needs_input_grad[0])
+        Win = _weights(v_in, g_in, True, P, need_wb=ctx.needs_input_grad[0])
         has_cond = v_c is not None and cond is not None
         bcast = has_cond and cond.dim() == 2
         cpl = wc32 = wc_wb = None
         if has_cond and bcast:
             cond = cond.contiguous()
-            Wc = Pm.wn_prepare(v_c, g_c, False, P, need_wf=False, need_wb=False, need_w32=True)
+            Wc = _weights(v_c, g_c, False, P, need_wf=False, need_wb=False, need_w32=True)
             wc32 = Wc.w32.view(2 * C, -1)
             p = Pm.linear_fwd(cond, wc32, b_c, b_in)
             a, mean, rstd = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, p, 2 * C, gn_groups=2)
@@ -228,11 +274,11 @@ class DecBlockFn(Function):
             if has_cond:
                 cond = Pm.as_cl(cond)
                 cpl = _input_planes(cond, P)
-                Wc = Pm.wn_prepare(v_c, g_c, False, P, need_wb=ctx.needs_input_grad[1])
+                Wc = _weights(v_c, g_c, False, P, need_wb=ctx.needs_input_grad[1])
                 wc_wb = Wc.wb
                 a, mean, rstd = Pm.conv_fwd(cpl, Wc.wf, 1, 1, 2 * C, b_c, 0, None, a, True, gn_groups=2)
         gpl = Pm.dec_gate(a, mean, rstd, gamma, beta, P)
-        Wrs = Pm.wn_prepare(v_rs, g_rs, False, P)
+        Wrs = _weights(v_rs, g_rs, False, P)
         r = Pm.conv_fwd(gpl, Wrs.wf, 1, 1, C + S, b_rs, 0)
         first = skip_acc is None
         if first:
@@ -243,7 +289,8 @@ class DecBlockFn(Function):
             ctx.mark_dirty(skip_acc)
         if box is not None:
             box['id'] = xopl
-        ctx.save_for_backward(cond if has_cond else None, a, mean, rstd, gamma, beta, v_in, g_in, v_c, g_c, v_rs, g_rs)
+        ctx.save_for_backward(cond if has_cond else None, a, mean, rstd, gamma, beta, v_in, g_in, v_c, g_c, v_rs, g_rs,
+                              b_in, b_c, b_rs)
         ctx.xpl, ctx.gpl, ctx.cpl = xpl, gpl, cpl
         ctx.win_wb, ctx.wrs_wb, ctx.wc_wb, ctx.wc32 = Win.wb, Wrs.wb, wc_wb, wc32
         ctx.cfg = (P, dil, B, C, S, T, Win.taps, has_cond, bcast)
@@ -252,7 +299,7 @@ class DecBlockFn(Function):
 
     @staticmethod
     def backward(ctx, dxo, dskip):
-        cond, a, mean, rstd, gamma, beta, v_in, g_in, v_c, g_c, v_rs, g_rs = ctx.saved_tensors
+        cond, a, mean, rstd, gamma, beta, v_in, g_in, v_c, g_c, v_rs, g_rs, b_in, b_c, b_rs = ctx.saved_tensors
         P, dil, B, C, S, T, taps, has_cond, bcast = ctx.cfg
         dev = a.device
         dxo = Pm.cl_zeros(B, C, T, dev) if dxo is None else Pm.as_cl(dxo)
@@ -260,24 +307,34 @@ class DecBlockFn(Function):
         dskip_phys = torch.zeros((B, T, S), device=dev) if dskip is None else dskip.contiguous()
         dskip = dskip_phys.transpose(1, 2)
         drpl = Pm.concat_planes(dxo, dskip, P)
-        db_rs = torch.empty((C + S,), dtype=torch.float32, device=dev)
+        rs_slot = _slot(b_rs)
+        db_rs = rs_slot if rs_slot is not None else torch.empty((C + S,), dtype=torch.float32, device=dev)
         Pm.channel_sum(dxo, db_rs[:C])
         Pm.channel_sum(dskip, db_rs[C:])
+        if rs_slot is not None:
+            db_rs = None
         dg = Pm.conv_fwd(drpl, ctx.wrs_wb, 1, 1, C)
-        dv_rs, dg_rs = _dw_to_param_grads(Pm.conv_wgrad(drpl, ctx.gpl, 1, 1, False), v_rs, g_rs)
+        dv_rs, dg_rs = _wgrad(drpl, ctx.gpl, 1, 1, False, v_rs, g_rs)
         R = Pm.gate_bwd_rows(dg, a, mean, rstd, gamma, beta)
-        dgamma, dbeta, Ssum, bsum, csum = Pm.gn_bwd_finalize(R, gamma, rstd, T, 2, True)
+        slots = {'dgamma': _slot(gamma), 'dbeta': _slot(beta), 'csum': _slot(b_in),
+                 'csum2': _slot(b_c) if has_cond else None}          # both biases add to the GN input
+        dgamma, dbeta, Ssum, bsum, csum = Pm.gn_bwd_finalize(R, gamma, rstd, T, 2, True, slots)
         dapl = Pm.gate_bwd_apply(dg, a, mean, rstd, gamma, beta, Ssum, P)
         dx = Pm.conv_fwd(dapl, ctx.win_wb, taps, dil, C, None, 0, dxo) if ctx.needs_input_grad[0] else None
-        dv_in, dg_in = _dw_to_param_grads(Pm.conv_wgrad(dapl, ctx.xpl, taps, dil, True), v_in, g_in)
+        dv_in, dg_in = _wgrad(dapl, ctx.xpl, taps, dil, True, v_in, g_in)
         dcond = dv_c = dg_c = db_c = None
         if has_cond:
-            db_c = csum.clone()
+            if slots['csum2'] is None:
+                db_c = (csum if csum is not None else b_in.grad).clone()
             if bcast:
-                dwc, dcond = Pm.linear_bwd(bsum, cond, ctx.wc32)
-                dv_c, dg_c = _dw_to_param_grads(dwc.view_as(v_c), v_c, g_c)
+                bank = get_bank()
+                if bank is not None and bank.has(v_c) and _slot(v_c) is not None:
+                    _, dcond = Pm.linear_bwd(bsum, cond, ctx.wc32, None, v_c.grad.view(2 * C, -1))
+                else:
+                    dwc, dcond = Pm.linear_bwd(bsum, cond, ctx.wc32)
+                    dv_c, dg_c = _dw_to_param_grads(dwc.view_as(v_c), v_c, g_c)
             else:
-                dv_c, dg_c = _dw_to_param_grads(Pm.conv_wgrad(dapl, ctx.cpl, 1, 1, False), v_c, g_c)
+                dv_c, dg_c = _wgrad(dapl, ctx.cpl, 1, 1, False, v_c, g_c)
                 if ctx.needs_input_grad[1]:
                     dcond = Pm.conv_fwd(dapl, ctx.wc_wb, 1, 1, cond.shape[1])
             if not ctx.needs_input_grad[1]:
@@ -330,7 +387,12 @@ class VQFn(Function):
         g_le = g_le.contiguous() if g_le is not None else None
         want_dE = ctx.needs_input_grad[1]
         dz, dEh = Pm.vq_bwd(g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, E, scale, normalize, want_dE)
-        dE = Pm.vq_bwd_codebook(dEh, E.detach(), normalize) if want_dE else None
+        dE = None
+        if want_dE:
+            slot = _slot(E)
+            dE = Pm.vq_bwd_codebook(dEh, E.detach(), normalize, slot)
+            if slot is not None:
+                dE = None
         return dz, dE, None, None
 
 
@@ -418,11 +480,13 @@ class EmbedFn(Function):
 
     @staticmethod
     def forward(ctx, table, idx):
-        ctx.save_for_backward(idx)
+        ctx.save_for_backward(idx, table)
         ctx.rows = table.shape[0]
         return Pm.embed_fwd(table, idx)
 
     @staticmethod
     def backward(ctx, dout):
-        (idx,) = ctx.saved_tensors
-        return Pm.embed_bwd(dout, idx, ctx.rows), None
+        idx, table = ctx.saved_tensors
+        slot = _slot(table)                    # zeroed by the trainer's flat-gradient memset
+        dt = Pm.embed_bwd(dout, idx, ctx.rows, slot)
+        return (None if slot is not None else dt), None

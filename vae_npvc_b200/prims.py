@@ -108,6 +108,14 @@ def wn_prepare(v, g, transposed, P, need_wf=True, need_wb=True, need_w32=False):
     return ConvWeights(wf, wb, w32, k, co, ci, bool(transposed))
 
 
+def wn_prepare_batch(flat_p, desc, row2layer, P, wbuf, w32buf):
+    _C.call('wn_prepare_batch', flat_p, desc, row2layer, row2layer.numel(), P, wbuf, w32buf)
+
+
+def wn_backward_batch(flat_p, flat_g, desc, row2layer):
+    _C.call('wn_backward_batch', flat_p, flat_g, desc, row2layer, row2layer.numel())
+
+
 def wn_backward(dw, v, g):
     d0, d1, k = v.shape
     dv, dg = torch.empty_like(v), torch.empty_like(g)
@@ -142,10 +150,12 @@ def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=No
     return out, mean, rstd
 
 
-def conv_wgrad(dy_pl, u_pl, taps, dil, transposed):
+def conv_wgrad(dy_pl, u_pl, taps, dil, transposed, out=None):
+    """-> dw in the parameter layout; ``out``: write it there (e.g. the parameter's gradient slot)."""
     Cout, Cin = dy_pl.C, u_pl.C
     shape = (Cin, Cout, taps) if transposed else (Cout, Cin, taps)
-    dw = torch.empty(shape, dtype=torch.float32, device=dy_pl.data.device)
+    dw = out if out is not None else torch.empty(shape, dtype=torch.float32, device=dy_pl.data.device)
+    assert tuple(dw.shape) == shape
     _C.call('conv_wgrad', dy_pl.data, u_pl.data, dy_pl.P, dy_pl.B, Cout, Cin, dy_pl.T, taps, dil,
             int(transposed), dw)
     return dw
@@ -231,15 +241,21 @@ def gate_bwd_rows(dg, a, mean, rstd, gamma, beta):
     return R
 
 
-def gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums=False):
-    """-> dgamma (C), dbeta (C), S (B,groups,2), dpre_bsum (B,C)|None, dpre_csum (C)|None"""
+def gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums=False, out=None):
+    """-> dgamma (C), dbeta (C), S (B,groups,2), dpre_bsum (B,C)|None, dpre_csum (C)|None.
+    ``out``: dict of destination tensors (gradient slots) for 'dgamma', 'dbeta', 'csum' and the optional
+    second copies 'dbeta2', 'csum2'; values written there are returned as None."""
     B, C, _ = R.shape
-    dgamma, dbeta = _f32((C,), R), _f32((C,), R)
+    out = out or {}
+    dgamma = out.get('dgamma') if out.get('dgamma') is not None else _f32((C,), R)
+    dbeta = out.get('dbeta') if out.get('dbeta') is not None else _f32((C,), R)
     S = _f32((B, groups, 2), R)
     bsum = _f32((B, C), R) if want_sums else None
-    csum = _f32((C,), R) if want_sums else None
-    _C.call('gn_bwd_finalize', R, gamma, rstd, B, C, T, groups, dgamma, dbeta, S, bsum, csum)
-    return dgamma, dbeta, S, bsum, csum
+    csum = out.get('csum') if out.get('csum') is not None else (_f32((C,), R) if want_sums else None)
+    _C.call('gn_bwd_finalize', R, gamma, rstd, B, C, T, groups, dgamma, dbeta, S, bsum, csum, out.get('dbeta2'),
+            out.get('csum2'))
+    return (None if out.get('dgamma') is not None else dgamma, None if out.get('dbeta') is not None else dbeta, S,
+            bsum, None if out.get('csum') is not None else csum)
 
 
 def gn_bwd_apply(dn, h, mean, rstd, gamma, S, groups, P, want_dn_planes=False):
@@ -283,9 +299,10 @@ def embed_fwd(table, idx):
     return out
 
 
-def embed_bwd(dout, idx, num_rows):
+def embed_bwd(dout, idx, num_rows, out=None):
+    """scatter-add into a zeroed table (``out``: an already zeroed gradient slot)"""
     dim = dout.shape[-1]
-    dtable = torch.zeros((num_rows, dim), dtype=torch.float32, device=dout.device)
+    dtable = out if out is not None else torch.zeros((num_rows, dim), dtype=torch.float32, device=dout.device)
     _C.call('embed_bwd', dout.contiguous(), idx.contiguous(), idx.numel(), dim, dtable)
     return dtable
 
@@ -298,11 +315,11 @@ def linear_fwd(y, W, bias, bias2=None):
     return p
 
 
-def linear_bwd(dp, y, W, dy=None):
-    """-> dW (O,I), dy (B,I); accumulates into ``dy`` when given."""
+def linear_bwd(dp, y, W, dy=None, dW_out=None):
+    """-> dW (O,I), dy (B,I); accumulates into ``dy`` when given; dW written to ``dW_out`` when given."""
     B, I = y.shape
     O = W.shape[0]
-    dW = _f32((O, I), y)
+    dW = dW_out if dW_out is not None else _f32((O, I), y)
     acc = dy is not None
     if dy is None:
         dy = _f32((B, I), y)
@@ -366,9 +383,9 @@ def vq_bwd(g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, E, scale, normalize, wa
     return dz, dEh
 
 
-def vq_bwd_codebook(dE_hat, E, normalize):
+def vq_bwd_codebook(dE_hat, E, normalize, out=None):
     K, D = E.shape
-    dE = torch.empty_like(E)
+    dE = out if out is not None else torch.empty_like(E)
     _C.call('vq_bwd_codebook', dE_hat, E, K, D, int(normalize), dE)
     return dE
 

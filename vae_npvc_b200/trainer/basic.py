@@ -25,6 +25,7 @@ import torch
 
 from .. import functional as Fn
 from .. import prims as Pm
+from ..bank import WeightBank
 from ..model import layers_vq as _lvq
 
 
@@ -111,6 +112,8 @@ class Trainer(object):
         self.max_grad_norm = max_grad_norm
         self._flatten()
         self.optimizer = FlatAdam(self._params, self._flat_p, self._flat_g, learning_rate)
+        # all conv weights materialised / back-propagated through weight-norm by one kernel each per step
+        self.bank = WeightBank(self.model, self._flat_p, self._flat_g, Fn.get_precision(), Pm)
         if lr_scheduler is not None:
             self._step_size, self._gamma = int(lr_param.get('step_size', 100000)), float(lr_param.get('gamma', 0.5))
             self.scheduler = 'StepLR'
@@ -148,18 +151,23 @@ class Trainer(object):
         (trainer/basic.py:57-72).  Returns (loss-detail keys, stacked 0-d device scalars)."""
         self._flat_g.zero_()
         _lvq.defer_items(True)
+        Fn.set_bank(self.bank)
         try:
+            self.bank.prepare()
             if jitter_src is not None:
                 self.model.jitter.sources = lambda length: jitter_src
             output, loss, detail = self.model([x, y])
+            loss.backward()
+            self.bank.finish_backward()
         finally:
+            Fn.set_bank(None)
             _lvq.defer_items(False)
-        loss.backward()
         dist = _dist()
         if dist is not None:
             dist.all_reduce(self._flat_g)
             self._flat_g.mul_(1.0 / dist.get_world_size())
         self.optimizer.step(self.max_grad_norm, self._step_size, self._gamma)
+        self.bank.fresh = False
         keys = list(detail.keys())
         scal = torch.stack([detail[k].t.reshape(()).float() for k in keys])
         return keys, scal
@@ -214,9 +222,15 @@ class Trainer(object):
 
     def valid_step(self, input):
         self.model.eval()
-        with torch.no_grad():
-            input = [t.to(self.device) for t in input]
-            output, loss, loss_detail = self.model(input)
+        Fn.set_bank(self.bank)
+        try:
+            with torch.no_grad():
+                if not self.bank.fresh:
+                    self.bank.prepare()
+                input = [t.to(self.device) for t in input]
+                output, loss, loss_detail = self.model(input)
+        finally:
+            Fn.set_bank(None)
         self.model.train()
         return loss_detail
 
@@ -232,5 +246,6 @@ class Trainer(object):
         checkpoint_data = torch.load(checkpoint_file, map_location='cpu')
         # copy INTO the flat-buffer views (keeps parameter storage and captured graphs valid)
         self.model.load_state_dict(checkpoint_data['model'])
+        self.bank.fresh = False
         self.optimizer.load_state_dict(checkpoint_data['optimizer'])
         return checkpoint_data['iteration']
