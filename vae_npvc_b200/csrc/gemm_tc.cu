@@ -7,12 +7,27 @@
 //       the tap shift is the ROW coordinate (TMA wants 16-byte aligned innermost coordinates, rows are
 //       free) and the conv zero padding is TMA out-of-bounds fill, per sample
 //   B = weight planes (N = BN output channels, K-major, SWIZZLE_128B) via a 3-D map (ci, co, plane*tap)
-//   accumulator 128 x BN fp32 in TMEM; epilogue warps tcgen05.ld it (lane = frame, 32 consecutive
-//   output channels per load), add bias / residual and store channels-last rows.
+//   accumulator 128 x BN fp32 in TMEM.
 //   P = 3 (fp32-faithful) contracts the 6 significant hi/mid/lo plane pairs on the same pipeline.
+//
+// What the VNB_TC_DBG=9 in-kernel timeline showed on B200 and how the kernel is shaped by it:
+//   * one thread pays ~70 cycles to issue a tcgen05.mma, ~190 for an mbarrier wait and ~85 for a commit, whatever
+//     the tile; a 128 x 64 MMA executes in 32 cycles, so narrow tiles are ISSUE bound (700 cycles per 64-deep
+//     k-step, measured, tensor pipe 13 % busy).  Hence the widest N tile that fits (up to 256: 128 cycles of
+//     tensor work per issue) ...
+//   * ... and, because 2048 frames x 512 channels are then only 32 tiles, SPLIT-K over a thread-block
+//     cluster: the CTAs of a cluster (1, 2, 4 or 8) take consecutive slices of the (pair, tap, ci) loop, park their
+//     partial accumulators in their own shared memory, and after one cluster barrier CTA r reduces rows
+//     [128 r / ks, 128 (r+1) / ks) of the tile from all peers through distributed shared memory
+//   * the same staging makes the epilogue coalesced: bias / residual / accumulate / GroupNorm statistics and
+//     the global stores run with 4 consecutive channels per thread and a whole row per (half-)warp, instead
+//     of one 2 KB-strided row per thread (1200 cycles per 32 columns before)
 // Warp roles (192 threads): warp 0 TMA producer, warp 1 MMA issuer + TMEM allocator,
-// warps 2..5 epilogue (TMEM lane quarter = warp_id % 4).
+// warps 2..5 TMEM -> shared staging (TMEM lane quarter = warp_id % 4) and the reduction / store.
+#include <stdint.h>
 #include <stdlib.h>
+
+#include <type_traits>
 
 #include "tc_common.cuh"
 
@@ -22,12 +37,15 @@ using namespace tc;
 
 constexpr int TC_BM = 128;         // frames per tile (UMMA M)
 constexpr int TC_BK = 64;          // K elements per pipeline stage (one 128-byte swizzle row)
-constexpr int TC_STAGES = 4;
-constexpr int TC_THREADS = 192;
+constexpr int TC_THREADS = 256;     // 8 warps: with one warp per scheduler every epilogue latency is exposed
 
 // plane pairs (a-plane, b-plane) of the 3-way split, smallest terms first
 __constant__ int c_pair_a[6] = {1, 2, 0, 1, 0, 0};
 __constant__ int c_pair_b[6] = {1, 0, 2, 0, 1, 0};
+
+// debug timeline (VNB_TC_DBG=9): clock64 stamps of CTA (0,0,0), read by vnb_debug_tc_timeline
+__device__ long long g_tc_ts[2][64];
+#define TS(i) do { if (ts) ts[i] = clock64(); } while (0)
 
 struct ConvTcArgs {
     int B, Cin, Cout, T, taps, dil, P;
@@ -38,7 +56,9 @@ struct ConvTcArgs {
     int accumulate;
     double* gn_sums;      // optional (B, gn_groups, 2): fused GroupNorm sum / sum-of-squares
     int gn_groups;
-    int dbg;      // VNB_TC_DBG bisect level (0 = normal)
+    int dbg;              // VNB_TC_DBG (0 = normal, 9 = record the timeline)
+    int nstages;          // depth of the TMA ring (<= 8)
+    uint32_t recv_off;    // byte offset of the receive slots in dynamic shared memory
 };
 
 __device__ __forceinline__ double warp_sum_f64(double v) {
@@ -47,179 +67,298 @@ __device__ __forceinline__ double warp_sum_f64(double v) {
     return v;
 }
 
+// Shared-memory plan (dynamic, after 1 KB alignment):  [ TMA ring: nstages x (16 KB + BN*128 B) | receive slots ]
+// The staged 128 x BN fp32 accumulator (row pitch BN+4 floats) reuses the ring; the (ks-1) receive slots of
+// rows_own x PITCH floats sit behind max(ring, staging) and are never touched by the main loop.
+template <int BN> struct ConvTcCfg {
+    static constexpr int MAX_STAGES = 8;
+    static constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2;
+    static constexpr uint32_t B_BYTES = BN * TC_BK * 2;
+    static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int PITCH = BN + 4;                       // floats per staged accumulator row (16 B pad)
+    static constexpr uint32_t STAGING_BYTES = (uint32_t)TC_BM * PITCH * 4;
+    static constexpr uint32_t SMEM_BUDGET = 227 * 1024 - 2048;  // minus alignment slack and static barriers
+    static uint32_t recv_bytes(int ks) { return (uint32_t)(ks - 1) * (TC_BM / ks) * PITCH * 4; }
+    static int stages(int ks) {
+        int n = (int)((SMEM_BUDGET - recv_bytes(ks)) / STAGE_BYTES);
+        return n > MAX_STAGES ? MAX_STAGES : n;
+    }
+    static uint32_t recv_offset(int ks) {
+        uint32_t ring = (uint32_t)stages(ks) * STAGE_BYTES;
+        uint32_t o = ring > STAGING_BYTES ? ring : STAGING_BYTES;
+        return (o + 1023u) & ~1023u;
+    }
+};
+
 template <int BN>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                    const ConvTcArgs a) {
-    constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2;              // 16 KB of activations
-    constexpr uint32_t B_BYTES = BN * TC_BK * 2;                 // BN x 128 B of weights
-    constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+    using Cfg = ConvTcCfg<BN>;
+    constexpr int MAX_STAGES = Cfg::MAX_STAGES;
+    const int STAGES = a.nstages;
+    constexpr uint32_t A_BYTES = Cfg::A_BYTES, STAGE_BYTES = Cfg::STAGE_BYTES;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    // 1024-byte alignment is required by SWIZZLE_128B
+    // 1024-byte alignment is required by SWIZZLE_128B (same offset in every CTA of the cluster)
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    __shared__ __align__(8) uint64_t full_bar[TC_STAGES];
-    __shared__ __align__(8) uint64_t empty_bar[TC_STAGES];
+    __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
     __shared__ __align__(8) uint64_t tmem_full_bar;
+    __shared__ __align__(8) uint64_t recv_bar;        // completes when every peer's partial rows have landed here
     __shared__ uint32_t tmem_slot;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int t0 = blockIdx.x * TC_BM, co0 = blockIdx.y * BN, b = blockIdx.z;
+    // grid (ksplit, n tiles, samples * frame tiles), cluster (ksplit, 1, 1): blockIdx.x = k-slice = cluster rank
+    const int ks = gridDim.x, kr = blockIdx.x;
+    const int mtiles = (a.T + TC_BM - 1) / TC_BM;
+    const int b = blockIdx.z / mtiles, t0 = (blockIdx.z - b * mtiles) * TC_BM, co0 = blockIdx.y * BN;
     const int pairs = a.P == 1 ? 1 : 6;
     const int kc_per = (a.Cin + TC_BK - 1) / TC_BK;
-    int nk = pairs * a.taps * kc_per;
-    if (a.dbg && nk > TC_STAGES) nk = TC_STAGES;
+    const int nkc = pairs * a.taps * kc_per;
+    const int kc0 = (int)((int64_t)nkc * kr / ks), kc1 = (int)((int64_t)nkc * (kr + 1) / ks);
+    const int nk = kc1 - kc0;                                  // may be 0 (more slices than chunks)
+    long long* ts = (a.dbg >= 9 && (blockIdx.x | blockIdx.y | blockIdx.z) == 0) ? g_tc_ts[0] : nullptr;
+    if (threadIdx.x == 0) TS(0);
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&map_w);
         tma_prefetch_desc(&map_x);
-        for (int s = 0; s < TC_STAGES; s++) {
+        for (int s = 0; s < STAGES; s++) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(&tmem_full_bar, 1);
+        mbar_init(&recv_bar, 1);
         fence_barrier_init();
+        if (ks > 1) mbar_expect_tx(&recv_bar, (uint32_t)(ks - 1) * (TC_BM / ks) * Cfg::PITCH * 4);
     }
     if (warp == 1) tmem_alloc<BN>(&tmem_slot);
     tc_fence_before();
-    __syncthreads();
+    if (ks > 1) cluster_sync_all();   // peers complete_tx on recv_bar: it must be initialised cluster-wide first
+    else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
+    if (threadIdx.x == 0) TS(1);
 
-    if (a.dbg == 1) {
-    } else if (warp == 0) {
+    if (warp == 0) {
         if (lane == 0) {
-            // ===== TMA producer =====
-            int kc = 0;
-            for (int pr = 0; pr < pairs && kc < nk; pr++) {
+            // ===== TMA producer =====  (no divisions in the loop: this is ONE thread, nothing hides their latency)
+            const int per_pair = a.taps * kc_per;
+            int pr = kc0 / per_pair, rem = kc0 - pr * per_pair;
+            int tap = rem / kc_per, c = rem - tap * kc_per;
+            int s = 0;
+            uint32_t ph = 1;                          // ((i / STAGES) - 1) & 1, kept incrementally
+            for (int i = 0; i < nk; i++) {
                 const int pa = a.P == 1 ? 0 : c_pair_a[pr], pb = a.P == 1 ? 0 : c_pair_b[pr];
-                for (int tap = 0; tap < a.taps && kc < nk; tap++) {
-                    const int off = (tap - (a.taps - 1) / 2) * a.dil;
-                    for (int c = 0; c < kc_per && kc < nk; c++, kc++) {
-                        const int s = kc % TC_STAGES;
-                        if (kc >= TC_STAGES) mbar_wait(&empty_bar[s], ((kc / TC_STAGES) - 1) & 1);
-                        uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
-                        mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-                        tma_load_3d(sa, &map_x, &full_bar[s], c * TC_BK, t0 + off, pb * a.B + b);
-                        tma_load_3d(sa + A_BYTES, &map_w, &full_bar[s], c * TC_BK, co0, pa * a.taps + tap);
-                    }
-                }
+                const int off = (tap - (a.taps - 1) / 2) * a.dil;
+                if (i >= STAGES) mbar_wait(&empty_bar[s], ph);
+                uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
+                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                tma_load_3d(sa, &map_x, &full_bar[s], c * TC_BK, t0 + off, pb * a.B + b);
+                tma_load_3d(sa + A_BYTES, &map_w, &full_bar[s], c * TC_BK, co0, pa * a.taps + tap);
+                if (++c == kc_per) { c = 0; if (++tap == a.taps) { tap = 0; ++pr; } }
+                if (++s == STAGES) { s = 0; ph ^= 1; }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             // ===== MMA issuer =====
             constexpr uint32_t idesc = instr_desc_bf16(TC_BM, BN, /*a_mn=*/0, /*b_mn=*/0);
-            for (int kc = 0; kc < nk; kc++) {
-                const int s = kc % TC_STAGES;
-                mbar_wait(&full_bar[s], (kc / TC_STAGES) & 1);
+            // the NEXT stage's barrier is probed (non-blocking) before this stage's MMAs are issued, so the
+            // ~190-cycle barrier round trip overlaps the tensor work instead of preceding it
+            bool ready = nk > 0 && mbar_test(&full_bar[0], 0);
+            int s = 0;
+            uint32_t ph = 0;                          // (i / STAGES) & 1, kept incrementally
+            for (int i = 0; i < nk; i++) {
+                if (!ready) mbar_wait(&full_bar[s], ph);
                 tc_fence_after();
+                if (i == 0) TS(2);
+                int s1 = s + 1;
+                uint32_t ph1 = ph;
+                if (s1 == STAGES) { s1 = 0; ph1 ^= 1; }
+                bool next_ready = false;
+                if (i + 1 < nk) next_ready = mbar_test(&full_bar[s1], ph1);
                 const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
-                const uint32_t sb = sa + A_BYTES;
-                if (a.dbg == 2) continue;
+                // K-major operands: 16 K-elements = 32 bytes along the swizzled 128-byte row (+2 in the
+                // descriptor's 16-byte address units); 8-row groups are 1024 B apart (SBO); LBO unused
+                const uint64_t da = smem_desc_sw128(sa, 16, 1024), db = smem_desc_sw128(sa + A_BYTES, 16, 1024);
 #pragma unroll
-                for (int j = 0; j < TC_BK / 16; j++) {
-                    // K-major operands: 16 K-elements = 32 bytes along the swizzled 128-byte row;
-                    // 8-row groups are 1024 B apart (SBO); LBO is unused for swizzled K-major layouts
-                    const uint64_t da = smem_desc_sw128(sa + j * 32, 16, 1024);
-                    const uint64_t db = smem_desc_sw128(sb + j * 32, 16, 1024);
-                    umma_bf16(tmem_base, da, db, idesc, (kc | j) != 0);
-                }
+                for (int j = 0; j < TC_BK / 16; j++) umma_bf16(tmem_base, da + 2 * j, db + 2 * j, idesc, (i | j) != 0);
                 umma_commit(&empty_bar[s]);           // frees the smem stage when these MMAs retire
+                ready = next_ready;
+                s = s1;
+                ph = ph1;
             }
-            if (a.dbg != 2) umma_commit(&tmem_full_bar);              // accumulator complete
-        }
-    } else {
-        // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4; lane = frame =====
-        const int q = warp & 3;
-        const int t = t0 + q * 32 + lane;
-        if (a.dbg == 2) goto done;
-        mbar_wait(&tmem_full_bar, 0);
-        if (a.dbg == 3) goto done;
-        tc_fence_after();
-        {
-            const bool row_ok = t < a.T;
-            const size_t row_off = ((size_t)b * a.T + (row_ok ? t : 0)) * a.Cout;
-            const float* bias = a.bias ? a.bias + (size_t)b * a.bias_bstride : nullptr;
-            const bool vec_ok = (a.Cout & 3) == 0;
-            // fused GroupNorm statistics: per-thread fp64 running sums of the current channel group
-            // (32-column blocks never straddle a group: host checks (Cout/groups) % 32 == 0)
-            const int cg = a.gn_sums ? a.Cout / a.gn_groups : 1;
-            double gs0 = 0.0, gs1 = 0.0;
-            int gcur = -1;
-#pragma unroll 1
-            for (int c0 = 0; c0 <= BN; c0 += 32) {
-                const int co = co0 + c0;
-                if (a.gn_sums) {
-                    const int g = (c0 < BN && co < a.Cout) ? co / cg : -1;       // warp-uniform
-                    if (g != gcur) {
-                        if (gcur >= 0) {
-                            gs0 = warp_sum_f64(gs0);
-                            gs1 = warp_sum_f64(gs1);
-                            if (lane == 0) {
-                                double* gp = a.gn_sums + ((size_t)b * a.gn_groups + gcur) * 2;
-                                atomicAdd(gp, gs0);
-                                atomicAdd(gp + 1, gs1);
-                            }
-                        }
-                        gs0 = gs1 = 0.0;
-                        gcur = g;
-                    }
-                }
-                if (c0 == BN) break;
-                float v[32];
-                __syncwarp();                                                            // tcgen05.ld is .sync.aligned
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);     // warp-collective
-                if (!row_ok || co >= a.Cout || a.dbg == 4) continue;
-                float* op = a.out + row_off + co;
-                const float* rp = a.residual ? a.residual + row_off + co : nullptr;
-                float bs0 = 0.f, bs1 = 0.f;
-                if (vec_ok) {
-#pragma unroll
-                    for (int i = 0; i < 32; i += 4) {
-                        if (co + i >= a.Cout) break;
-                        float4 r = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-                        if (bias) {
-                            const float4 x = *reinterpret_cast<const float4*>(bias + co + i);
-                            r.x += x.x; r.y += x.y; r.z += x.z; r.w += x.w;
-                        }
-                        if (rp) {
-                            const float4 x = *reinterpret_cast<const float4*>(rp + i);
-                            r.x += x.x; r.y += x.y; r.z += x.z; r.w += x.w;
-                        }
-                        if (a.accumulate) {
-                            const float4 x = *reinterpret_cast<const float4*>(op + i);
-                            r.x += x.x; r.y += x.y; r.z += x.z; r.w += x.w;
-                        }
-                        *reinterpret_cast<float4*>(op + i) = r;
-                        bs0 += (r.x + r.y) + (r.z + r.w);
-                        bs1 += (r.x * r.x + r.y * r.y) + (r.z * r.z + r.w * r.w);
-                    }
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 32; i++) {
-                        if (co + i < a.Cout) {
-                            float r = v[i] + (bias ? bias[co + i] : 0.f);
-                            if (rp) r += rp[i];
-                            if (a.accumulate) r += op[i];
-                            op[i] = r;
-                            bs0 += r;
-                            bs1 += r * r;
-                        }
-                    }
-                }
-                gs0 += (double)bs0;
-                gs1 += (double)bs1;
-            }
+            umma_commit(&tmem_full_bar);              // accumulator complete (immediately, when nk == 0)
         }
     }
-done:
-    tc_fence_before();
+
+    // ===== exchange.  Each CTA stages its partial 128 x BN accumulator in its OWN shared memory (the TMA ring is
+    // idle once tmem_full fires: every load was consumed by an MMA that has retired).  CTA r of the cluster owns
+    // rows [128 r / ks, 128 (r+1) / ks) of the tile: one thread sends each peer ITS rows with a bulk
+    // shared::cta -> shared::cluster copy (TMA engine, one instruction per peer) that completes on the peer's
+    // recv_bar.  Per-thread DSMEM loads / stores managed only ~16 B/cycle/SM here (measured: 8-10k cycles for
+    // the same exchange). =====
+    constexpr int PITCH = Cfg::PITCH;
+    float* stage = reinterpret_cast<float*>(smem);
+    const float* recv = reinterpret_cast<const float*>(smem + a.recv_off);
+    const int rows_own = TC_BM / ks, r_base = kr * rows_own;
+    {
+        // all 8 warps: TMEM lane quarter = warp % 4 (hardware rule), column half = warp / 4
+        const int q = warp & 3, h = warp >> 2;
+        mbar_wait_warp(&tmem_full_bar, 0, 32);        // (lanes 1..31 of warps 0/1 arrive here while lane 0 still issues)
+        tc_fence_after();
+        if (threadIdx.x == 64) TS(3);
+        float* srow = stage + (size_t)(q * 32 + lane) * PITCH;
+#pragma unroll 1
+        for (int c0 = h * (BN / 2); c0 < (h + 1) * (BN / 2); c0 += 32) {
+            float v[32];
+            if (nk > 0) {
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);     // warp-collective
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; i++) v[i] = 0.f;                                 // empty k-slice
+            }
+#pragma unroll
+            for (int i = 0; i < 32; i += 4)
+                *reinterpret_cast<float4*>(srow + c0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();                     // generic-proxy stores -> visible to the bulk-copy engine
+        __syncthreads();
+        if (threadIdx.x == 64) {
+            TS(4);
+            const uint32_t slot_bytes = (uint32_t)rows_own * PITCH * 4;
+            for (int p = 0; p < ks; p++) {
+                if (p == kr) continue;
+                const int slot = kr < p ? kr : kr - 1;                                   // my slot at peer p
+                bulk_copy_to_cta(map_to_cta(smem_u32(recv) + (uint32_t)slot * slot_bytes, p),
+                                 smem_u32(stage + (size_t)p * rows_own * PITCH), slot_bytes,
+                                 map_to_cta(smem_u32(&recv_bar), p));
+            }
+        }
+        if (ks > 1) mbar_wait_warp(&recv_bar, 0, 32);
+        if (threadIdx.x == 64) TS(5);
+
+        // ===== reduction over the k-slices (fixed order: sender rank) + fused epilogue, coalesced: 4 consecutive
+        // channels per thread, BN/4 threads per row, two rows per iteration with their loads issued together.
+        // Kept small on purpose: this code runs once per CTA out of a cold instruction cache (a fully unrolled
+        // version spent 2/3 of its time fetching itself), and with two warps per scheduler nothing else hides
+        // a dependent load.
+        constexpr int TPR = BN / 4;                   // threads per output row
+        constexpr int RPP = TC_THREADS / TPR;         // rows per pass of the 256 threads
+        const int tid = threadIdx.x;
+        const int cv = (tid % TPR) * 4, rsub = tid / TPR;
+        const int co = co0 + cv;
+        const int Cout = a.Cout, Tn = a.T;
+        const bool vec_ok = (Cout & 3) == 0;
+        const bool col_ok = co < Cout;
+        const float* __restrict__ resid = a.residual;
+        float* __restrict__ outp = a.out;
+        const bool accum = a.accumulate != 0;
+        const float* bias = a.bias ? a.bias + (size_t)b * a.bias_bstride : nullptr;
+        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (bias && col_ok) {
+            if (vec_ok) bv = *reinterpret_cast<const float4*>(bias + co);
+            else {
+                bv.x = bias[co];
+                if (co + 1 < Cout) bv.y = bias[co + 1];
+                if (co + 2 < Cout) bv.z = bias[co + 2];
+                if (co + 3 < Cout) bv.w = bias[co + 3];
+            }
+        }
+        // shared::cta addresses of this thread's column in row 0 of every sender's block of MY rows
+        const uint32_t own_base = smem_u32(stage + (size_t)r_base * PITCH + cv);
+        const uint32_t recv_base = smem_u32(recv + cv);
+        const uint32_t slot_stride = (uint32_t)rows_own * PITCH * 4;
+        // fused GroupNorm statistics of the FINAL values: a thread's 4 channels share a group (host checks
+        // (Cout / groups) % 32 == 0); fp32 over the thread's <= 32 rows, fp64 from there on
+        const int cg = a.gn_sums ? Cout / a.gn_groups : 1;
+        const int g = (a.gn_sums && col_ok) ? co / cg : -1;
+        float fs0 = 0.f, fs1 = 0.f;
+        const size_t row0 = (size_t)b * Tn + t0 + r_base;
+#pragma unroll 1
+        for (int rl = rsub; rl < rows_own; rl += 2 * RPP) {
+            const int rl2 = rl + RPP;
+            const bool ok1 = col_ok && t0 + r_base + rl < Tn;
+            const bool ok2 = col_ok && rl2 < rows_own && t0 + r_base + rl2 < Tn;
+            float4 acc1 = bv, acc2 = bv;
+#pragma unroll 1
+            for (int p = 0; p < ks; p++) {
+                const uint32_t base = p == kr ? own_base : recv_base + (uint32_t)(p < kr ? p : p - 1) * slot_stride;
+                const float4 x1 = ok1 ? ld_shared_f4(base + (uint32_t)rl * (PITCH * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 x2 = ok2 ? ld_shared_f4(base + (uint32_t)rl2 * (PITCH * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                acc1.x += x1.x; acc1.y += x1.y; acc1.z += x1.z; acc1.w += x1.w;
+                acc2.x += x2.x; acc2.y += x2.y; acc2.z += x2.z; acc2.w += x2.w;
+            }
+            const size_t o1 = (row0 + rl) * Cout + co, o2 = (row0 + rl2) * Cout + co;
+            if (vec_ok) {
+                float4 r1 = make_float4(0.f, 0.f, 0.f, 0.f), r2 = r1, u1 = r1, u2 = r1;
+                if (resid && ok1) r1 = *reinterpret_cast<const float4*>(resid + o1);
+                if (resid && ok2) r2 = *reinterpret_cast<const float4*>(resid + o2);
+                if (accum && ok1) u1 = *reinterpret_cast<const float4*>(outp + o1);
+                if (accum && ok2) u2 = *reinterpret_cast<const float4*>(outp + o2);
+                acc1.x += r1.x + u1.x; acc1.y += r1.y + u1.y; acc1.z += r1.z + u1.z; acc1.w += r1.w + u1.w;
+                acc2.x += r2.x + u2.x; acc2.y += r2.y + u2.y; acc2.z += r2.z + u2.z; acc2.w += r2.w + u2.w;
+                if (ok1) {
+                    *reinterpret_cast<float4*>(outp + o1) = acc1;
+                    fs0 += (acc1.x + acc1.y) + (acc1.z + acc1.w);
+                    fs1 += (acc1.x * acc1.x + acc1.y * acc1.y) + (acc1.z * acc1.z + acc1.w * acc1.w);
+                }
+                if (ok2) {
+                    *reinterpret_cast<float4*>(outp + o2) = acc2;
+                    fs0 += (acc2.x + acc2.y) + (acc2.z + acc2.w);
+                    fs1 += (acc2.x * acc2.x + acc2.y * acc2.y) + (acc2.z * acc2.z + acc2.w * acc2.w);
+                }
+            } else {
+#pragma unroll 1
+                for (int u = 0; u < 2; u++) {
+                    if (!(u ? ok2 : ok1)) continue;
+                    const float4 acc = u ? acc2 : acc1;
+                    const size_t o = u ? o2 : o1;
+                    const float vals[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        if (co + i < Cout) {
+                            float x = vals[i];
+                            if (resid) x += resid[o + i];
+                            if (accum) x += outp[o + i];
+                            outp[o + i] = x;
+                            fs0 += x;
+                            fs1 += x * x;
+                        }
+                    }
+                }
+            }
+        }
+        if (a.gn_sums) {
+            double gs0 = (double)fs0, gs1 = (double)fs1;
+            const int g0 = __shfl_sync(0xffffffffu, g, 0);
+            const bool uniform = __all_sync(0xffffffffu, g == g0 || g < 0);
+            if (uniform) {
+                gs0 = warp_sum_f64(gs0);
+                gs1 = warp_sum_f64(gs1);
+                if (lane == 0 && g0 >= 0) {
+                    double* gp = a.gn_sums + ((size_t)b * a.gn_groups + g0) * 2;
+                    atomicAdd(gp, gs0);
+                    atomicAdd(gp + 1, gs1);
+                }
+            } else if (g >= 0) {
+                double* gp = a.gn_sums + ((size_t)b * a.gn_groups + g) * 2;
+                atomicAdd(gp, gs0);
+                atomicAdd(gp + 1, gs1);
+            }
+        }
+        if (threadIdx.x == 64) TS(6);
+    }
+    // a CTA's outgoing copies read ITS shared memory: nobody may exit before every receiver has its rows
+    if (ks > 1) cluster_sync_all();
     __syncthreads();
     if (warp == 1) {
-        __syncwarp();
         tc_fence_after();
         tmem_dealloc<BN>(tmem_base);
     }
+    if (threadIdx.x == 32) TS(7);
 }
 
 // --------------------------------------------------------------------------------------------
@@ -245,55 +384,84 @@ static EncodeFn get_encode() {
     return fn;
 }
 
-bool make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1_bytes,
-                  uint64_t stride2_bytes, uint32_t box0, uint32_t box1, uint32_t box2) {
+bool make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+               const uint32_t* box) {
     EncodeFn enc = get_encode();
     if (!enc) {
         set_error("cuTensorMapEncodeTiled driver entry point not available");
         return false;
     }
-    cuuint64_t dims[3] = {d0, d1, d2};
-    cuuint64_t strides[2] = {stride1_bytes, stride2_bytes};
-    cuuint32_t box[3] = {box0, box1, box2};
-    cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+    cuuint64_t d[5], st[4];
+    cuuint32_t bx[5], estr[5] = {1, 1, 1, 1, 1};
+    for (int i = 0; i < rank; i++) {
+        d[i] = dims[i];
+        bx[i] = box[i];
+        if (i > 0) st[i - 1] = strides_bytes[i - 1];
+    }
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), d, st, bx, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
-        set_error("cuTensorMapEncodeTiled failed (%d): dims %llu %llu %llu strides %llu %llu box %u %u %u", (int)r,
-                  (unsigned long long)d0, (unsigned long long)d1, (unsigned long long)d2,
-                  (unsigned long long)stride1_bytes, (unsigned long long)stride2_bytes, box0, box1, box2);
+        set_error("cuTensorMapEncodeTiled failed (%d): rank %d dims %llu %llu %llu box %u %u %u", (int)r, rank,
+                  (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)(rank > 2 ? dims[2] : 0),
+                  box[0], box[1], rank > 2 ? box[2] : 0);
         return false;
     }
     return true;
 }
 
+bool make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1_bytes,
+                  uint64_t stride2_bytes, uint32_t box0, uint32_t box1, uint32_t box2) {
+    const uint64_t dims[3] = {d0, d1, d2}, strides[2] = {stride1_bytes, stride2_bytes};
+    const uint32_t box[3] = {box0, box1, box2};
+    return make_tmap(out, base, 3, dims, strides, box);
+}
+
 }  // namespace tc
 
 template <int BN>
-static int launch_conv_tc(const void* in, const void* w, int Tdim, int Cin_p, const ConvTcArgs& a, cudaStream_t st) {
-    constexpr size_t smem = (size_t)TC_STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + 1024;
+static int launch_conv_tc(const void* in, const void* w, int Cin_p, int ksplit, ConvTcArgs a, cudaStream_t st) {
+    using Cfg = ConvTcCfg<BN>;
+    constexpr size_t smem_max = 227 * 1024;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(conv_fwd_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(conv_fwd_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max - 1024);
         if (e != cudaSuccess) {
-            set_error("conv_fwd_tc: cudaFuncSetAttribute(%zu): %s", smem, cudaGetErrorString(e));
+            set_error("conv_fwd_tc: cudaFuncSetAttribute(%zu): %s", smem_max, cudaGetErrorString(e));
             return VNB_E_CUDA;
         }
         attr_done = true;
     }
     CUtensorMap mx, mw;
     // activations (P, B, T, Cin_p): dims (ci, t, plane*b); box 64 x 128 x 1
-    if (!make_tmap_3d(&mx, in, (uint64_t)a.Cin, (uint64_t)Tdim, (uint64_t)a.P * a.B, (uint64_t)Cin_p * 2,
-                      (uint64_t)Tdim * Cin_p * 2, TC_BK, TC_BM, 1))
+    if (!make_tmap_3d(&mx, in, (uint64_t)a.Cin, (uint64_t)a.T, (uint64_t)a.P * a.B, (uint64_t)Cin_p * 2,
+                      (uint64_t)a.T * Cin_p * 2, TC_BK, TC_BM, 1))
         return VNB_E_CUDA;
     // weights (P, taps, Cout, Cin_p): dims (ci, co, plane*tap); box 64 x BN x 1
     if (!make_tmap_3d(&mw, w, (uint64_t)a.Cin, (uint64_t)a.Cout, (uint64_t)a.P * a.taps, (uint64_t)Cin_p * 2,
                       (uint64_t)a.Cout * Cin_p * 2, TC_BK, BN, 1))
         return VNB_E_CUDA;
-    dim3 grid(ceil_div(a.T, TC_BM), ceil_div(a.Cout, BN), a.B);
-    conv_fwd_tc_kernel<BN><<<grid, TC_THREADS, smem, st>>>(mx, mw, a);
-    VNB_LAUNCH_CHECK("conv_fwd_tc");
+    a.nstages = Cfg::stages(ksplit);
+    a.recv_off = Cfg::recv_offset(ksplit);
+    const size_t smem = (size_t)a.recv_off + Cfg::recv_bytes(ksplit) + 1024;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(ksplit, ceil_div(a.Cout, BN), a.B * ceil_div(a.T, TC_BM));
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = ksplit;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, conv_fwd_tc_kernel<BN>, mx, mw, a);
+    if (e != cudaSuccess) {
+        set_error("conv_fwd_tc: launch failed (BN %d, cluster %d): %s", BN, ksplit, cudaGetErrorString(e));
+        return VNB_E_CUDA;
+    }
+    count_launch();
     return VNB_OK;
 }
 
@@ -301,20 +469,58 @@ int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int
                 const float* bias, int bias_bstride, const float* residual, float* out, int accumulate,
                 double* gn_sums, int gn_groups, cudaStream_t st) {
     // shapes this backend takes; everything else goes to the SIMT backend (or errors under VNB_BACKEND_TC)
-    if (Cout < 8 || Cin < 8 || B > 65535) return 1;
-    if (gn_sums && ((Cout / gn_groups) & 31) != 0) return 1;      // statistics blocks of 32 channels must not straddle groups
-    static const int dbg = getenv("VNB_TC_DBG") ? atoi(getenv("VNB_TC_DBG")) : 0;
-    ConvTcArgs a{B, Cin, Cout, T, taps, dil, P, bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups, dbg};
-    const int Cin_p = round_up8(Cin);
-    // widest N tile that still gives the 148 SMs about one CTA each
     const int64_t mt = (int64_t)ceil_div(T, TC_BM) * B;
-    if (Cout > 128 && mt * ceil_div(Cout, 256) >= 112) return launch_conv_tc<256>(in, w, T, Cin_p, a, st);
-    if (Cout > 64 && mt * ceil_div(Cout, 128) >= 112) return launch_conv_tc<128>(in, w, T, Cin_p, a, st);
-    return launch_conv_tc<64>(in, w, T, Cin_p, a, st);
+    if (Cout < 8 || Cin < 8 || mt > 65535) return 1;
+    if (gn_sums && ((Cout / gn_groups) & 31) != 0) return 1;      // a thread's 4 channels must not straddle groups
+    static const int dbg = getenv("VNB_TC_DBG") ? atoi(getenv("VNB_TC_DBG")) : 0;
+    static const int force_bn = getenv("VNB_TC_BN") ? atoi(getenv("VNB_TC_BN")) : 0;
+    static const int force_ks = getenv("VNB_TC_KSPLIT") ? atoi(getenv("VNB_TC_KSPLIT")) : 0;
+    ConvTcArgs a{B, Cin, Cout, T, taps, dil, P, bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups, dbg, 0, 0};
+    const int Cin_p = round_up8(Cin);
+    // N tile and cluster split-K: as many CTAs as fit the 148 SMs in one wave (a tcgen05.mma issue costs the same
+    // ~70 cycles for a 32-cycle N=64 tile as for a 128-cycle N=256 one, so wide tiles are preferred on a tie),
+    // with the receive slots of the split-K exchange fitting beside the TMA ring
+    const int nkc = (P == 1 ? 1 : 6) * taps * ceil_div(Cin, TC_BK);
+    auto fits = [](int bn_, int ks_) {
+        const uint32_t pitch = bn_ + 4, stage_b = TC_BM * TC_BK * 2 + bn_ * TC_BK * 2;
+        const uint32_t recv = (uint32_t)(ks_ - 1) * (TC_BM / ks_) * pitch * 4, budget = 227 * 1024 - 2048;
+        if (recv + 2 * stage_b > budget) return false;
+        uint32_t ring = (budget - recv) / stage_b;
+        ring = (ring > 8 ? 8 : ring) * stage_b;
+        const uint32_t staging = TC_BM * pitch * 4;
+        const uint32_t off = ((ring > staging ? ring : staging) + 1023u) & ~1023u;
+        return off + recv + 1024 <= 227 * 1024 - 1024;
+    };
+    // cost model in SM cycles, fitted to the VNB_TC_DBG=9 timelines (profiles/r01_conv_tc_timeline.txt): ~610
+    // cycles per 64-deep k-chunk whatever the tile (the single issuing thread, not the tensor pipe, is the limit;
+    // 770 at BN=256 where the 48 KB stages meet the L2 limit), a fixed ~5.5k cycles of launch / TMEM / cold
+    // instruction fetch / epilogue, and ~5k more for a split-K exchange through distributed shared memory
+    int bn = 64, ks = 1;
+    int64_t best = INT64_MAX;
+    for (int cand = 64; cand <= 256; cand *= 2) {
+        if (cand > 64 && Cout <= cand / 2) break;                 // tile wider than needed
+        const int64_t tiles = mt * ceil_div(Cout, cand);
+        for (int k = 1; k <= 8; k *= 2) {
+            if (k > nkc || !fits(cand, k)) break;
+            const int64_t waves = (tiles * k + 147) / 148;
+            const int64_t cost = waves * ((int64_t)ceil_div(nkc, k) * (cand == 256 ? 770 : 610) + 5500 +
+                                          (k > 1 ? 4500 + 250 * k : 0) + (cand == 256 ? 2000 : 0));
+            if (cost < best) { best = cost; bn = cand; ks = k; }
+        }
+    }
+    if (force_bn) bn = force_bn;
+    if (force_ks) ks = force_ks;
+    if (!fits(bn, ks)) { set_error("conv_fwd_tc: BN %d with cluster %d does not fit shared memory", bn, ks); return VNB_E_ARG; }
+    if (bn == 256) return launch_conv_tc<256>(in, w, Cin_p, ks, a, st);
+    if (bn == 128) return launch_conv_tc<128>(in, w, Cin_p, ks, a, st);
+    return launch_conv_tc<64>(in, w, Cin_p, ks, a, st);
 }
 
 }  // namespace vnb
 // debug: number of bounded mbarrier waits that timed out since load (synchronises the device)
+extern "C" int vnb_debug_tc_timeline(long long* host_out128) {
+    return cudaMemcpyFromSymbol(host_out128, vnb::g_tc_ts, sizeof(long long) * 128) == cudaSuccess ? 0 : -2;
+}
 extern "C" int vnb_debug_tc_timeouts(void) {
     int v = -1;
     if (cudaMemcpyFromSymbol(&v, vnb::tc::g_tc_timeouts, sizeof(int)) != cudaSuccess) return -1;

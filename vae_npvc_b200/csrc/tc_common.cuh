@@ -27,6 +27,7 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 __device__ int g_tc_timeouts;
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
     const uint32_t addr = smem_u32(bar);
+#pragma unroll 1
     for (uint32_t spin = 0; spin < (1u << 22); ++spin) {
         uint32_t ok;
         asm volatile(
@@ -42,6 +43,84 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
     return false;
 }
 
+// non-blocking probe of a phase
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// device: thread-block clusters / distributed shared memory
+// ---------------------------------------------------------------------------------------------
+// barrier over ALL threads of ALL CTAs of the cluster (a plain launch is a cluster of one CTA)
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cta address -> the same offset in CTA `rank` of the cluster (shared::cluster address)
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, int rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ float4 ld_cluster_f4(uint32_t caddr) {
+    float4 v;
+    // volatile (ordered after the cluster barrier, itself a volatile asm) but no memory clobber, so that several
+    // loads can be in flight
+    asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(caddr));
+    return v;
+}
+
+__device__ __forceinline__ float4 ld_shared_f4(uint32_t saddr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+    return v;
+}
+__device__ __forceinline__ void st_cluster_f4(uint32_t caddr, float x, float y, float z, float w) {
+    asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(caddr), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+
+// generic-proxy writes to shared memory -> visible to the async proxy (TMA / bulk copies)
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+// bulk copy own shared memory -> a peer CTA's shared memory; completes `bytes` on the PEER's mbarrier
+__device__ __forceinline__ void bulk_copy_to_cta(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t bar_cluster) {
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst_cluster), "r"(src_cta), "r"(bytes), "r"(bar_cluster) : "memory");
+}
+
+// Warp-level wait: ONE lane polls, the rest of the warp parks at __syncwarp.  128 epilogue threads all
+// spinning on try_wait only burn issue slots; `backoff_ns` > 0 adds a nanosleep between polls for long
+// waits (the epilogue waiting for the whole main loop).
+__device__ __forceinline__ void mbar_wait_warp(uint64_t* bar, uint32_t parity, uint32_t backoff_ns = 0) {
+    if ((threadIdx.x & 31) == 0) {
+        const uint32_t addr = smem_u32(bar);
+#pragma unroll 1
+        for (uint32_t spin = 0; spin < (1u << 22); ++spin) {
+            uint32_t ok;
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                "selp.u32 %0, 1, 0, p;\n\t}"
+                : "=r"(ok)
+                : "r"(addr), "r"(parity)
+                : "memory");
+            if (ok) break;
+            if (backoff_ns) __nanosleep(backoff_ns);
+            if (spin == (1u << 22) - 1) atomicAdd(&g_tc_timeouts, 1);
+        }
+    }
+    __syncwarp();
+}
+
 // ---------------------------------------------------------------------------------------------
 // device: TMA
 // ---------------------------------------------------------------------------------------------
@@ -49,6 +128,12 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, u
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
         ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
         : "memory");
 }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
@@ -128,6 +213,9 @@ __host__ __device__ constexpr uint32_t instr_desc_bf16(int M, int N, int a_mn, i
 // dims 1 and 2.  Returns false (and sets the error string) on failure.
 bool make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1_bytes,
                   uint64_t stride2_bytes, uint32_t box0, uint32_t box1, uint32_t box2);
+// general form (rank <= 5): strides_bytes has rank-1 entries (dims 1..rank-1)
+bool make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+               const uint32_t* box);
 
 }  // namespace tc
 }  // namespace vnb

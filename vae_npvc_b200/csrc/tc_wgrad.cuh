@@ -168,7 +168,8 @@ static int launch_wgrad_tc(const void* dy, const void* u, WgradTcArgs a, cudaStr
         return VNB_E_CUDA;
     const int base = ceil_div(a.Cin, BN) * ceil_div(a.Cout, WG_BM) * a.taps;
     const int kblocks = a.B * ceil_div(a.T, WG_KT);
-    int ksplit = ceil_div(148, base);
+    static const int force_ks = getenv("VNB_WG_KSPLIT") ? atoi(getenv("VNB_WG_KSPLIT")) : 0;
+    int ksplit = force_ks ? force_ks : ceil_div(148, base);
     if (ksplit > kblocks) ksplit = kblocks;
     if (ksplit < 1) ksplit = 1;
     a.ksplit = ksplit;
