@@ -3,14 +3,21 @@
 //     dW[tap][co, ci] = sum_{pair} sum_{b} sum_{t} dY[pa][b][t][co] * U[pb][b][t + off(tap)][ci]
 //
 // The contraction runs over FRAMES, which are the rows of the channels-last planes, so both operands
-// are MN-major tiles: 64 frame rows x 64 channels (128 B, SWIZZLE_128B) per TMA box, the tap shift is
+// are MN-major tiles: 64 frame rows x 64 channels (128 B, SWIZZLE_128B) per box, the tap shift is
 // again a TMA row coordinate and the per-sample zero padding is out-of-bounds fill.
-//   A = dY planes (M = 128 output channels = two 64-channel boxes), 3-D map (co, t, plane*b)
-//   B = U  planes (N = BN input channels  = BN/64 boxes),           3-D map (ci, t, plane*b)
-// grid = (ci tiles, co tiles, taps * ksplit): the (sample, 64-frame block) list is split over ksplit
-// CTAs that reduce into dW with fp32 red.global.add (dW zeroed by the host wrapper when ksplit > 1).
-// Epilogue: TMEM lane = co, 32 consecutive ci per tcgen05.ld, scattered into the reference parameter
-// layout (d0, d1, k) - Conv1d dw[co][ci][tap], ConvTranspose1d dw[ci][co][taps-1-tap].
+//   A = "row" planes (M = 128 channels = two 64-channel boxes), B = "column" planes (N = BN channels).
+//   For Conv1d the rows are dY channels (co) and the columns U channels (ci): parameter (co, ci, k).
+//   For ConvTranspose1d the host SWAPS the operands (rows = ci from U, columns = co from dY), so that the
+//   parameter layout (ci, co, k) is again row-major in (row, column) and the stores stay coalesced.
+//   One TMA instruction per operand and stage: a 4-D map (64 ch, frame, 64-channel group, plane*sample)
+//   with box {64, 64, groups, 1} lands the groups as consecutive canonical 8 KB boxes (the group dimension
+//   has a SMALLER stride than the frame dimension; cuTensorMapEncodeTiled accepts that - tools/tma4d_probe.cu).
+//   Channel counts that are not a multiple of 64 use one 3-D box per group instead.
+// grid = (ksplit, row tiles * column tiles, taps), cluster (ksplit, 1, 1): the (sample, 64-frame block) list is
+// split over the CTAs of a cluster, which exchange their partial tiles through distributed shared memory with
+// bulk copies exactly like conv_fwd_tc_kernel (no atomics, no memset, deterministic).
+// Epilogue: 4 consecutive columns per thread, BN/4 threads per row, written into the reference parameter
+// layout  dw[(row * ncols + col) * taps + tap_index].
 #pragma once
 #include "tc_common.cuh"
 
@@ -20,178 +27,328 @@ using namespace tc;
 
 constexpr int WG_BM = 128;
 constexpr int WG_KT = 64;          // frames per pipeline stage
-constexpr int WG_STAGES = 4;
-constexpr int WG_THREADS = 192;
+constexpr int WG_THREADS = 256;
 constexpr uint32_t WG_BOX_BYTES = WG_KT * 128;      // one 64-channel x 64-frame box
 
 struct WgradTcArgs {
-    int B, Cout, Cin, T, taps, dil, P, transposed, ksplit, atomic;
+    int B, nrows, ncols, T, taps, P;
+    int dil, swapped;
+    int a4d, b4d;              // operand maps are 4-D (one TMA per stage) or 3-D (one per 64-channel group)
+    int nstages;
+    uint32_t recv_off;
     float* dw;
+};
+
+template <int BN> struct WgradTcCfg {
+    static constexpr int MAX_STAGES = 8;
+    static constexpr uint32_t A_BYTES = (WG_BM / 64) * WG_BOX_BYTES;
+    static constexpr uint32_t B_BYTES = (BN / 64) * WG_BOX_BYTES;
+    static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int PITCH = BN + 4;
+    static constexpr uint32_t STAGING_BYTES = (uint32_t)WG_BM * PITCH * 4;
+    static constexpr uint32_t SMEM_BUDGET = 227 * 1024 - 2048;
+    static uint32_t recv_bytes(int ks) { return (uint32_t)(ks - 1) * (WG_BM / ks) * PITCH * 4; }
+    static bool fits(int ks) {
+        if (recv_bytes(ks) + 2 * STAGE_BYTES > SMEM_BUDGET) return false;
+        return recv_offset(ks) + recv_bytes(ks) + 1024 <= 227 * 1024 - 1024;
+    }
+    static int stages(int ks) {
+        int n = (int)((SMEM_BUDGET - recv_bytes(ks)) / STAGE_BYTES);
+        return n > MAX_STAGES ? MAX_STAGES : n;
+    }
+    static uint32_t recv_offset(int ks) {
+        uint32_t ring = (uint32_t)stages(ks) * STAGE_BYTES;
+        uint32_t o = ring > STAGING_BYTES ? ring : STAGING_BYTES;
+        return (o + 1023u) & ~1023u;
+    }
 };
 
 template <int BN>
 __global__ void __launch_bounds__(WG_THREADS, 1)
-conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_constant__ CUtensorMap map_u,
+conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                      const WgradTcArgs a) {
-    constexpr uint32_t A_BYTES = (WG_BM / 64) * WG_BOX_BYTES;    // 16 KB
-    constexpr uint32_t B_BYTES = (BN / 64) * WG_BOX_BYTES;
-    constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+    using Cfg = WgradTcCfg<BN>;
+    constexpr int MAX_STAGES = Cfg::MAX_STAGES;
+    constexpr uint32_t A_BYTES = Cfg::A_BYTES, STAGE_BYTES = Cfg::STAGE_BYTES;
+    constexpr int PITCH = Cfg::PITCH;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    __shared__ __align__(8) uint64_t full_bar[WG_STAGES];
-    __shared__ __align__(8) uint64_t empty_bar[WG_STAGES];
+    __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
     __shared__ __align__(8) uint64_t tmem_full_bar;
+    __shared__ __align__(8) uint64_t recv_bar;
     __shared__ uint32_t tmem_slot;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int ci0 = blockIdx.x * BN, co0 = blockIdx.y * WG_BM;
-    const int tap = blockIdx.z / a.ksplit, split = blockIdx.z % a.ksplit;
+    const int STAGES = a.nstages;
+    const int ks = gridDim.x, kr = blockIdx.x;
+    const int ntiles = (a.ncols + BN - 1) / BN;
+    const int m0 = (blockIdx.y / ntiles) * WG_BM, n0 = (blockIdx.y % ntiles) * BN;
+    const int tap = blockIdx.z;
     const int off = (tap - (a.taps - 1) / 2) * a.dil;
+    const int off_a = a.swapped ? off : 0, off_b = a.swapped ? 0 : off;
+    const int tap_idx = a.swapped ? a.taps - 1 - tap : tap;
     const int pairs = a.P == 1 ? 1 : 6;
     const int tblocks = (a.T + WG_KT - 1) / WG_KT;
     const int kblocks = a.B * tblocks;
-    const int kb0 = (int)((int64_t)kblocks * split / a.ksplit), kb1 = (int)((int64_t)kblocks * (split + 1) / a.ksplit);
+    const int kb0 = (int)((int64_t)kblocks * kr / ks), kb1 = (int)((int64_t)kblocks * (kr + 1) / ks);
     const int nk = pairs * (kb1 - kb0);
 
     if (threadIdx.x == 0) {
-        tma_prefetch_desc(&map_dy);
-        tma_prefetch_desc(&map_u);
-        for (int s = 0; s < WG_STAGES; s++) {
+        tma_prefetch_desc(&map_a);
+        tma_prefetch_desc(&map_b);
+        for (int s = 0; s < STAGES; s++) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(&tmem_full_bar, 1);
+        mbar_init(&recv_bar, 1);
         fence_barrier_init();
+        if (ks > 1) mbar_expect_tx(&recv_bar, (uint32_t)(ks - 1) * (WG_BM / ks) * PITCH * 4);
     }
     if (warp == 1) tmem_alloc<BN>(&tmem_slot);
     tc_fence_before();
-    __syncthreads();
+    if (ks > 1) cluster_sync_all();
+    else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
 
-    if (nk == 0) {
-        // nothing to contract for this split (more splits than k-blocks): contributes zero
-    } else if (warp == 0) {
-        if (lane == 0) {
-            int kc = 0;
-            for (int pr = 0; pr < pairs; pr++) {
+    if (warp == 0) {
+        if (lane == 0 && nk > 0) {
+            // ===== TMA producer (one thread; no divisions in the loop) =====
+            int pr = 0;
+            int bb = kb0 / tblocks, tb = kb0 - bb * tblocks;
+            int s = 0;
+            uint32_t ph = 1;
+            for (int i = 0; i < nk; i++) {
                 const int pa = a.P == 1 ? 0 : c_pair_a[pr], pb = a.P == 1 ? 0 : c_pair_b[pr];
-                for (int kb = kb0; kb < kb1; kb++, kc++) {
-                    const int b = kb / tblocks, t0 = (kb - b * tblocks) * WG_KT;
-                    const int s = kc % WG_STAGES;
-                    if (kc >= WG_STAGES) mbar_wait(&empty_bar[s], ((kc / WG_STAGES) - 1) & 1);
-                    uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
-                    uint8_t* sb = sa + A_BYTES;
-                    mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                // the row operand takes the a-plane of the pair when it is dY, the b-plane when it is U (swapped)
+                const int pl_a = a.swapped ? pb : pa, pl_b = a.swapped ? pa : pb;
+                const int t0 = tb * WG_KT;
+                if (i >= STAGES) mbar_wait(&empty_bar[s], ph);
+                uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
+                uint8_t* sb = sa + A_BYTES;
+                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                if (a.a4d) {
+                    tma_load_4d(sa, &map_a, &full_bar[s], 0, t0 + off_a, m0 / 64, pl_a * a.B + bb);
+                } else {
 #pragma unroll
                     for (int m = 0; m < WG_BM / 64; m++)
-                        tma_load_3d(sa + m * WG_BOX_BYTES, &map_dy, &full_bar[s], co0 + m * 64, t0, pa * a.B + b);
+                        tma_load_3d(sa + m * WG_BOX_BYTES, &map_a, &full_bar[s], m0 + m * 64, t0 + off_a, pl_a * a.B + bb);
+                }
+                if (a.b4d) {
+                    tma_load_4d(sb, &map_b, &full_bar[s], 0, t0 + off_b, n0 / 64, pl_b * a.B + bb);
+                } else {
 #pragma unroll
                     for (int n = 0; n < BN / 64; n++)
-                        tma_load_3d(sb + n * WG_BOX_BYTES, &map_u, &full_bar[s], ci0 + n * 64, t0 + off, pb * a.B + b);
+                        tma_load_3d(sb + n * WG_BOX_BYTES, &map_b, &full_bar[s], n0 + n * 64, t0 + off_b, pl_b * a.B + bb);
                 }
+                if (++tb == tblocks) { tb = 0; ++bb; }
+                if (bb * tblocks + tb == kb1) { bb = kb0 / tblocks; tb = kb0 - bb * tblocks; ++pr; }   // next plane pair
+                if (++s == STAGES) { s = 0; ph ^= 1; }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
+            // ===== MMA issuer =====
             constexpr uint32_t idesc = instr_desc_bf16(WG_BM, BN, /*a_mn=*/1, /*b_mn=*/1);
-            for (int kc = 0; kc < nk; kc++) {
-                const int s = kc % WG_STAGES;
-                mbar_wait(&full_bar[s], (kc / WG_STAGES) & 1);
+            bool ready = nk > 0 && mbar_test(&full_bar[0], 0);
+            int s = 0;
+            uint32_t ph = 0;
+            for (int i = 0; i < nk; i++) {
+                if (!ready) mbar_wait(&full_bar[s], ph);
                 tc_fence_after();
+                int s1 = s + 1;
+                uint32_t ph1 = ph;
+                if (s1 == STAGES) { s1 = 0; ph1 ^= 1; }
+                bool next_ready = false;
+                if (i + 1 < nk) next_ready = mbar_test(&full_bar[s1], ph1);
                 const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
-                const uint32_t sb = sa + A_BYTES;
+                // MN-major: 16 frame rows of 128 B = 2048 B per UMMA_K (+128 in 16-byte descriptor units);
+                // 64-channel boxes are WG_BOX_BYTES apart (LBO); 8-row swizzle atoms 1024 B apart (SBO)
+                const uint64_t da = smem_desc_sw128(sa, WG_BOX_BYTES, 1024), db = smem_desc_sw128(sa + A_BYTES, WG_BOX_BYTES, 1024);
 #pragma unroll
-                for (int j = 0; j < WG_KT / 16; j++) {
-                    // MN-major: 16 frame rows of 128 B = 2048 B per UMMA_K; 64-channel boxes are
-                    // WG_BOX_BYTES apart (LBO); 8-row swizzle atoms 1024 B apart (SBO)
-                    const uint64_t da = smem_desc_sw128(sa + j * 2048, WG_BOX_BYTES, 1024);
-                    const uint64_t db = smem_desc_sw128(sb + j * 2048, WG_BOX_BYTES, 1024);
-                    umma_bf16(tmem_base, da, db, idesc, (kc | j) != 0);
-                }
+                for (int j = 0; j < WG_KT / 16; j++) umma_bf16(tmem_base, da + 128 * j, db + 128 * j, idesc, (i | j) != 0);
                 umma_commit(&empty_bar[s]);
+                ready = next_ready;
+                s = s1;
+                ph = ph1;
             }
             umma_commit(&tmem_full_bar);
         }
-    } else {
-        // epilogue: lane = output channel co
-        const int q = warp & 3;
-        const int co = co0 + q * 32 + lane;
-        mbar_wait(&tmem_full_bar, 0);
+    }
+
+    // ===== exchange + coalesced store: same scheme as conv_fwd_tc_kernel (see there) =====
+    float* stage = reinterpret_cast<float*>(smem);
+    const float* recv = reinterpret_cast<const float*>(smem + a.recv_off);
+    const int rows_own = WG_BM / ks, r_base = kr * rows_own;
+    {
+        const int q = warp & 3, h = warp >> 2;
+        mbar_wait_warp(&tmem_full_bar, 0, 32);
         tc_fence_after();
-        const bool row_ok = co < a.Cout;
+        float* srow = stage + (size_t)(q * 32 + lane) * PITCH;
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = h * (BN / 2); c0 < (h + 1) * (BN / 2); c0 += 32) {
             float v[32];
-            __syncwarp();
-            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
-            if (!row_ok) continue;
+            if (nk > 0) {
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+            } else {
 #pragma unroll
-            for (int i = 0; i < 32; i++) {
-                const int ci = ci0 + c0 + i;
-                if (ci >= a.Cin) break;
-                const int64_t o = a.transposed ? (((int64_t)ci * a.Cout + co) * a.taps + (a.taps - 1 - tap))
-                                               : (((int64_t)co * a.Cin + ci) * a.taps + tap);
-                if (a.atomic) atomicAdd(a.dw + o, v[i]);
-                else a.dw[o] = v[i];
+                for (int i = 0; i < 32; i++) v[i] = 0.f;
+            }
+#pragma unroll
+            for (int i = 0; i < 32; i += 4)
+                *reinterpret_cast<float4*>(srow + c0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        __syncthreads();
+        if (threadIdx.x == 64) {
+            const uint32_t slot_bytes = (uint32_t)rows_own * PITCH * 4;
+            for (int p = 0; p < ks; p++) {
+                if (p == kr) continue;
+                const int slot = kr < p ? kr : kr - 1;
+                bulk_copy_to_cta(map_to_cta(smem_u32(recv) + (uint32_t)slot * slot_bytes, p),
+                                 smem_u32(stage + (size_t)p * rows_own * PITCH), slot_bytes,
+                                 map_to_cta(smem_u32(&recv_bar), p));
+            }
+        }
+        if (ks > 1) mbar_wait_warp(&recv_bar, 0, 32);
+
+        constexpr int TPR = BN / 4;
+        constexpr int RPP = WG_THREADS / TPR;
+        const int tid = threadIdx.x;
+        const int cv = (tid % TPR) * 4, rsub = tid / TPR;
+        const int col = n0 + cv;
+        const int ncols = a.ncols, nrows = a.nrows, taps = a.taps;
+        const bool col_ok = col < ncols;
+        const bool vec_ok = taps == 1 && (ncols & 3) == 0;
+        float* __restrict__ dw = a.dw;
+        const uint32_t own_base = smem_u32(stage + (size_t)r_base * PITCH + cv);
+        const uint32_t recv_base = smem_u32(recv + cv);
+        const uint32_t slot_stride = (uint32_t)rows_own * PITCH * 4;
+#pragma unroll 1
+        for (int rl = rsub; rl < rows_own; rl += 2 * RPP) {
+            const int rl2 = rl + RPP;
+            const int row1 = m0 + r_base + rl, row2 = m0 + r_base + rl2;
+            const bool ok1 = col_ok && row1 < nrows;
+            const bool ok2 = col_ok && rl2 < rows_own && row2 < nrows;
+            float4 acc1 = make_float4(0.f, 0.f, 0.f, 0.f), acc2 = acc1;
+#pragma unroll 1
+            for (int p = 0; p < ks; p++) {
+                const uint32_t base = p == kr ? own_base : recv_base + (uint32_t)(p < kr ? p : p - 1) * slot_stride;
+                const float4 x1 = ok1 ? ld_shared_f4(base + (uint32_t)rl * (PITCH * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 x2 = ok2 ? ld_shared_f4(base + (uint32_t)rl2 * (PITCH * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                acc1.x += x1.x; acc1.y += x1.y; acc1.z += x1.z; acc1.w += x1.w;
+                acc2.x += x2.x; acc2.y += x2.y; acc2.z += x2.z; acc2.w += x2.w;
+            }
+#pragma unroll 1
+            for (int u = 0; u < 2; u++) {
+                if (!(u ? ok2 : ok1)) continue;
+                const float4 acc = u ? acc2 : acc1;
+                float* o = dw + ((size_t)(u ? row2 : row1) * ncols + col) * taps + tap_idx;
+                if (vec_ok) {
+                    *reinterpret_cast<float4*>(o) = acc;
+                } else {
+                    o[0] = acc.x;
+                    if (col + 1 < ncols) o[taps] = acc.y;
+                    if (col + 2 < ncols) o[2 * taps] = acc.z;
+                    if (col + 3 < ncols) o[3 * taps] = acc.w;
+                }
             }
         }
     }
-    tc_fence_before();
+    if (ks > 1) cluster_sync_all();
     __syncthreads();
     if (warp == 1) {
-        __syncwarp();
         tc_fence_after();
         tmem_dealloc<BN>(tmem_base);
     }
 }
 
+// 4-D (C % 64 == 0) or 3-D MN-major operand map of planes (P, B, T, Cp); `groups` = 64-channel boxes per load
+static bool make_wgrad_map(CUtensorMap* m, const void* base, int C, int T, int PB, int groups, int* is4d) {
+    const int Cp = round_up8(C);
+    if (C % 64 == 0) {
+        const uint64_t dims[4] = {64, (uint64_t)T, (uint64_t)C / 64, (uint64_t)PB};
+        const uint64_t strides[3] = {(uint64_t)Cp * 2, 128, (uint64_t)T * Cp * 2};
+        const uint32_t box[4] = {64, WG_KT, (uint32_t)groups, 1};
+        *is4d = 1;
+        return make_tmap(m, base, 4, dims, strides, box);
+    }
+    *is4d = 0;
+    return make_tmap_3d(m, base, (uint64_t)C, (uint64_t)T, (uint64_t)PB, (uint64_t)Cp * 2, (uint64_t)T * Cp * 2, 64, WG_KT, 1);
+}
+
 template <int BN>
-static int launch_wgrad_tc(const void* dy, const void* u, WgradTcArgs a, cudaStream_t st) {
-    constexpr size_t smem = (size_t)WG_STAGES * ((WG_BM / 64) + (BN / 64)) * WG_BOX_BYTES + 1024;
+static int launch_wgrad_tc(const void* rows_pl, const void* cols_pl, int ksplit, WgradTcArgs a, cudaStream_t st) {
+    using Cfg = WgradTcCfg<BN>;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
         if (e != cudaSuccess) {
-            set_error("conv_wgrad_tc: cudaFuncSetAttribute(%zu): %s", smem, cudaGetErrorString(e));
+            set_error("conv_wgrad_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
             return VNB_E_CUDA;
         }
         attr_done = true;
     }
-    const int Cout_p = round_up8(a.Cout), Cin_p = round_up8(a.Cin);
-    CUtensorMap mdy, mu;
-    if (!make_tmap_3d(&mdy, dy, (uint64_t)a.Cout, (uint64_t)a.T, (uint64_t)a.P * a.B, (uint64_t)Cout_p * 2,
-                      (uint64_t)a.T * Cout_p * 2, 64, WG_KT, 1))
+    CUtensorMap ma, mb;
+    if (!make_wgrad_map(&ma, rows_pl, a.nrows, a.T, a.P * a.B, WG_BM / 64, &a.a4d)) return VNB_E_CUDA;
+    if (!make_wgrad_map(&mb, cols_pl, a.ncols, a.T, a.P * a.B, BN / 64, &a.b4d)) return VNB_E_CUDA;
+    a.nstages = Cfg::stages(ksplit);
+    a.recv_off = Cfg::recv_offset(ksplit);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(ksplit, ceil_div(a.nrows, WG_BM) * ceil_div(a.ncols, BN), a.taps);
+    cfg.blockDim = dim3(WG_THREADS);
+    cfg.dynamicSmemBytes = (size_t)a.recv_off + Cfg::recv_bytes(ksplit) + 1024;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = ksplit;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, conv_wgrad_tc_kernel<BN>, ma, mb, a);
+    if (e != cudaSuccess) {
+        set_error("conv_wgrad_tc: launch failed (BN %d, cluster %d): %s", BN, ksplit, cudaGetErrorString(e));
         return VNB_E_CUDA;
-    if (!make_tmap_3d(&mu, u, (uint64_t)a.Cin, (uint64_t)a.T, (uint64_t)a.P * a.B, (uint64_t)Cin_p * 2,
-                      (uint64_t)a.T * Cin_p * 2, 64, WG_KT, 1))
-        return VNB_E_CUDA;
-    const int base = ceil_div(a.Cin, BN) * ceil_div(a.Cout, WG_BM) * a.taps;
-    const int kblocks = a.B * ceil_div(a.T, WG_KT);
-    static const int force_ks = getenv("VNB_WG_KSPLIT") ? atoi(getenv("VNB_WG_KSPLIT")) : 0;
-    int ksplit = force_ks ? force_ks : ceil_div(148, base);
-    if (ksplit > kblocks) ksplit = kblocks;
-    if (ksplit < 1) ksplit = 1;
-    a.ksplit = ksplit;
-    a.atomic = ksplit > 1;
-    if (a.atomic) {
-        cudaError_t e = cudaMemsetAsync(a.dw, 0, (size_t)a.Cout * a.Cin * a.taps * sizeof(float), st);
-        if (e != cudaSuccess) {
-            set_error("conv_wgrad_tc: memset: %s", cudaGetErrorString(e));
-            return VNB_E_CUDA;
-        }
     }
-    dim3 grid(ceil_div(a.Cin, BN), ceil_div(a.Cout, WG_BM), a.taps * ksplit);
-    conv_wgrad_tc_kernel<BN><<<grid, WG_THREADS, smem, st>>>(mdy, mu, a);
-    VNB_LAUNCH_CHECK("conv_wgrad_tc");
+    count_launch();
     return VNB_OK;
 }
 
 int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin, int T, int taps, int dil,
                   int transposed, float* dw, cudaStream_t st) {
-    if (Cout < 8 || Cin < 8 || (int64_t)P * B > 65535 || taps * 148 > 65535) return 1;
-    WgradTcArgs a{B, Cout, Cin, T, taps, dil, P, transposed, 1, 0, dw};
-    return Cin > 64 ? launch_wgrad_tc<128>(dy, u, a, st) : launch_wgrad_tc<64>(dy, u, a, st);
+    if (Cout < 8 || Cin < 8 || (int64_t)P * B > 65535 || taps > 65535) return 1;
+    // ConvTranspose1d parameters are (ci, co, k): swap the operands so that rows = ci, columns = co
+    const int nrows = transposed ? Cin : Cout, ncols = transposed ? Cout : Cin;
+    const void* rows_pl = transposed ? u : dy;
+    const void* cols_pl = transposed ? dy : u;
+    WgradTcArgs a{B, nrows, ncols, T, taps, P, dil, transposed ? 1 : 0, 0, 0, 0, 0, dw};
+    static const int force_bn = getenv("VNB_WG_BN") ? atoi(getenv("VNB_WG_BN")) : 0;
+    static const int force_ks = getenv("VNB_WG_KSPLIT") ? atoi(getenv("VNB_WG_KSPLIT")) : 0;
+    const int kblocks = B * ceil_div(T, WG_KT) * (P == 1 ? 1 : 6);
+    int bn = 64, ks = 1;
+    int64_t best = INT64_MAX;
+    for (int cand = 64; cand <= 256; cand *= 2) {
+        if (cand > 64 && ncols <= cand / 2) break;
+        const int64_t tiles = (int64_t)ceil_div(nrows, WG_BM) * ceil_div(ncols, cand) * taps;
+        for (int k = 1; k <= 8; k *= 2) {
+            const bool ok = cand == 256 ? WgradTcCfg<256>::fits(k) : cand == 128 ? WgradTcCfg<128>::fits(k) : WgradTcCfg<64>::fits(k);
+            if (k > kblocks || !ok) break;
+            const int64_t waves = (tiles * k + 147) / 148;
+            // same cost model as conv_fwd_tc (cycles): ~610 per 64-frame stage, fixed 5.5k, split-K exchange 4.5k+
+            const int64_t cost = waves * ((int64_t)ceil_div(kblocks, k) * (cand == 256 ? 770 : 610) + 5500 +
+                                          (k > 1 ? 4500 + 250 * k : 0) + (cand == 256 ? 2000 : 0));
+            if (cost < best) { best = cost; bn = cand; ks = k; }
+        }
+    }
+    if (force_bn) bn = force_bn;
+    if (force_ks) ks = force_ks;
+    if (bn == 256) return launch_wgrad_tc<256>(rows_pl, cols_pl, ks, a, st);
+    if (bn == 128) return launch_wgrad_tc<128>(rows_pl, cols_pl, ks, a, st);
+    return launch_wgrad_tc<64>(rows_pl, cols_pl, ks, a, st);
 }
 
 }  // namespace vnb
