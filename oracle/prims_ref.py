@@ -155,9 +155,9 @@ def _conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=N
     return r
 
 
-def wn_prepare_batch(flat_p, desc, row2layer, P, wbuf, w32buf):
+def wn_prepare_batch(flat_p, desc, row2layer, P, wbuf, w32buf, tile2layer=None, max_k=None, row_scale=None):
     for L in desc.tolist():
-        v_off, g_off, d0, d1, k, tr, wf_off, wb_off, w32_off, _ = L
+        v_off, g_off, d0, d1, k, tr, wf_off, wb_off, w32_off = L[:9]
         v = flat_p[v_off:v_off + d0 * d1 * k].view(d0, d1, k)
         g = flat_p[g_off:g_off + d0].view(d0, 1, 1) if g_off >= 0 else None
         W = wn_prepare(v, g, tr, P, wf_off >= 0, wb_off >= 0, w32_off >= 0)

@@ -5,7 +5,7 @@ The reference re-derives ``w = g * v / ||v||`` in a forward pre-hook of each of 
 separate weight-norm backward graphs.  Here the trainer keeps parameters and gradients in two flat fp32
 buffers; the bank holds a device-side table of where every conv's (v, g) sits in them and
 
-  * ``prepare()``          one launch: every layer's bf16 GEMM operand planes (forward operand ``wf``,
+  * ``prepare()``          two launches (row scales, then transposing tiles): every layer's bf16 GEMM operand planes (forward operand ``wf``,
                            data-gradient operand ``wb``, fp32 effective weight for the 1x1 speaker-
                            conditioning convs) straight from the flat parameter buffer
   * ``finish_backward()``  one launch: the weight-gradient GEMMs have written raw dW into the v slots of
@@ -38,8 +38,9 @@ class WeightBank(object):
         self.flat_p, self.flat_g = flat_p, flat_g
         dev = flat_p.device
         base, end = flat_p.data_ptr(), flat_p.data_ptr() + flat_p.numel() * 4
-        rows, desc, entries = [], [], []
-        w_off = w32_off = row0 = 0
+        rows, tiles, desc, entries = [], [], [], []
+        w_off = w32_off = row0 = tile0 = 0
+        self.max_k = 1
         for name, m in model.named_modules():
             if not isinstance(m, (nn.Conv1d, nn.ConvTranspose1d)):
                 continue
@@ -60,16 +61,22 @@ class WeightBank(object):
             if want32:
                 w32_off += _align(v.numel())
             desc.append([(v.data_ptr() - base) // 4, (g.data_ptr() - base) // 4 if g is not None else -1, d0, d1, k,
-                         int(transposed), wf_off, wb_off, e32, row0])
+                         int(transposed), wf_off, wb_off, e32, row0, tile0, 0])
             rows += [len(desc) - 1] * d0
             row0 += d0
+            n_tiles = ((d0 + 31) // 32) * ((d1 + 31) // 32)
+            tiles += [len(desc) - 1] * n_tiles
+            tile0 += n_tiles
+            self.max_k = max(self.max_k, k)
             entries.append((v, g, transposed, k, co, ci, wf_off, n_wf, wb_off, n_wb, e32))
         self.n_layers = len(desc)
         # zero-filled once: the pitch padding of the operand planes must stay finite
         self.wbuf = torch.zeros(max(w_off, 1), dtype=torch.bfloat16, device=dev)
         self.w32buf = torch.zeros(max(w32_off, 1), dtype=torch.float32, device=dev)
-        self.desc = torch.tensor(desc if desc else [[0] * 10], dtype=torch.int64, device=dev)
+        self.desc = torch.tensor(desc if desc else [[0] * 12], dtype=torch.int64, device=dev)
         self.row2layer = torch.tensor(rows if rows else [0], dtype=torch.int32, device=dev)
+        self.tile2layer = torch.tensor(tiles if tiles else [0], dtype=torch.int32, device=dev)
+        self.row_scale = torch.empty(max(row0, 1), dtype=torch.float32, device=dev)
         self.by_ptr = {}
         for (v, g, transposed, k, co, ci, wf_off, n_wf, wb_off, n_wb, e32) in entries:
             wf = self.wbuf[wf_off:wf_off + n_wf].view(P, k, co, Pm.pitch(ci))
@@ -86,7 +93,8 @@ class WeightBank(object):
 
     def prepare(self):
         if self.n_layers:
-            self.Pm.wn_prepare_batch(self.flat_p, self.desc, self.row2layer, self.P, self.wbuf, self.w32buf)
+            self.Pm.wn_prepare_batch(self.flat_p, self.desc, self.row2layer, self.P, self.wbuf, self.w32buf,
+                                     self.tile2layer, self.max_k, self.row_scale)
         self.fresh = True
 
     def finish_backward(self):

@@ -50,17 +50,34 @@ __global__ void __launch_bounds__(256) bwd_rows_kernel(const float* __restrict__
     if (c < Cn) {
         const int gi = b * groups + c / (Cn / groups);
         const float m = mean[gi], rs = rstd[gi];
-        for (int t = ty; t < T; t += 8) {
-            const int64_t r = (int64_t)b * T + t;
-            float d, xh;
-            if (GATE) d = gate_dn(dn, h, mean, rstd, gamma, beta, b, r, c, Cn / 2, xh);
-            else {
-                d = dn[r * Cn + c];
-                xh = (h[r * Cn + c] - m) * rs;
+        if (GATE) {
+            for (int t = ty; t < T; t += 8) {
+                const int64_t r = (int64_t)b * T + t;
+                float xh;
+                const float d = gate_dn(dn, h, mean, rstd, gamma, beta, b, r, c, Cn / 2, xh);
+                s0 += d;
+                s1 += d * xh;
+                s2 += xh;
             }
-            s0 += d;
-            s1 += d * xh;
-            s2 += xh;
+        } else {
+            for (int t0 = ty; t0 < T; t0 += 32) {          // four frames in flight
+                float d[4], hv[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int t = t0 + 8 * u;
+                    const int64_t r = (int64_t)b * T + (t < T ? t : 0);
+                    d[u] = t < T ? dn[r * Cn + c] : 0.f;
+                    hv[u] = h[r * Cn + c];
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    if (t0 + 8 * u >= T) continue;
+                    const float xh = (hv[u] - m) * rs;
+                    s0 += d[u];
+                    s1 += d[u] * xh;
+                    s2 += xh;
+                }
+            }
         }
     }
     red[0][ty][tx] = s0;
@@ -75,57 +92,85 @@ __global__ void __launch_bounds__(256) bwd_rows_kernel(const float* __restrict__
     }
 }
 
-// S[b,g,0..1] = sum_{c in g} gamma_c * R{0,1}[b,c]     (one block per (b,g))
-__global__ void __launch_bounds__(256) gn_bwd_groupsum_kernel(const float* __restrict__ R,
-                                                              const float* __restrict__ gamma, int C, int groups,
-                                                              float* __restrict__ S) {
-    __shared__ float red[32];
-    const int b = blockIdx.x / groups, g = blockIdx.x % groups;
+// GroupNorm backward finalisation in ONE launch (was: a (b,g) group-sum kernel, then a per-channel kernel on 4-8
+// blocks that walked the samples serially: 4 + 10 us for 200 KB of input).
+// grid ceil(C/32), block 16 warps.  Phase 1 (every block, redundantly - R is L2 resident): warp w computes
+//   S[b,g,0..1] = sum_{c in g} gamma_c * R{0,1}[b,c]   for b = w, w+16, ... into shared memory (block 0 also
+//   publishes S for gn_bwd_apply / gate_bwd_apply).
+// Phase 2: lane = channel, warp = sample: dgamma, dbeta and the time / batch sums of the pre-norm gradient
+//   dpre = rstd * (gamma*dn - S0/n - xhat*S1/n), reduced over the 16 warps in shared memory.
+__global__ void __launch_bounds__(512) gn_bwd_finalize_kernel(const float* __restrict__ R, const float* __restrict__ gamma,
+                                                              const float* __restrict__ rstd, int B, int C, int T, int groups,
+                                                              float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                              float* __restrict__ S, float* __restrict__ dpre_bsum,
+                                                              float* __restrict__ dpre_csum, float* __restrict__ dbeta2,
+                                                              float* __restrict__ dpre_csum2) {
+    extern __shared__ float fin_smem[];
+    float* Ss = fin_smem;                              // [B][groups][2]
+    float (*red)[16][33] = reinterpret_cast<float (*)[16][33]>(fin_smem + ((B * groups * 2 + 3) & ~3));
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int cg = C / groups;
-    float s0 = 0.f, s1 = 0.f;
-    for (int j = threadIdx.x; j < cg; j += blockDim.x) {
-        const int c = g * cg + j;
-        const float gm = gamma[c];
-        const float* r = R + ((int64_t)b * C + c) * 3;
-        s0 += gm * r[0];
-        s1 += gm * r[1];
-    }
-    s0 = block_sum(s0, red);
-    s1 = block_sum(s1, red);
-    if (threadIdx.x == 0) {
-        S[blockIdx.x * 2 + 0] = s0;
-        S[blockIdx.x * 2 + 1] = s1;
-    }
-}
-
-// per channel: dgamma, dbeta, and the time/batch sums of the pre-norm gradient
-__global__ void gn_bwd_channel_kernel(const float* __restrict__ R, const float* __restrict__ gamma,
-                                      const float* __restrict__ rstd, const float* __restrict__ S, int B, int C, int T,
-                                      int groups, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                      float* __restrict__ dpre_bsum, float* __restrict__ dpre_csum,
-                                      float* __restrict__ dbeta2, float* __restrict__ dpre_csum2) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
-    const int cg = C / groups, g = c / cg;
-    const float inv_n = 1.f / ((float)cg * (float)T);
-    const float gm = gamma[c];
-    float dgm = 0.f, dbt = 0.f, dcs = 0.f;
-    for (int b = 0; b < B; b++) {
-        const float* r = R + ((int64_t)b * C + c) * 3;
-        dbt += r[0];
-        dgm += r[1];
-        if (dpre_bsum || dpre_csum || dpre_csum2) {
-            const float* s = S + (b * groups + g) * 2;
-            const float v = rstd[b * groups + g] * (gm * r[0] - (float)T * s[0] * inv_n - r[2] * s[1] * inv_n);
-            if (dpre_bsum) dpre_bsum[(int64_t)b * C + c] = v;
-            dcs += v;
+    for (int b = w; b < B; b += 16) {
+        for (int g = 0; g < groups; g++) {
+            float s0 = 0.f, s1 = 0.f;
+            for (int j = lane; j < cg; j += 32) {
+                const int c = g * cg + j;
+                const float gm = gamma[c];
+                const float* r = R + ((int64_t)b * C + c) * 3;
+                s0 = fmaf(gm, r[0], s0);
+                s1 = fmaf(gm, r[1], s1);
+            }
+            s0 = warp_sum(s0);
+            s1 = warp_sum(s1);
+            if (lane == 0) {
+                Ss[(b * groups + g) * 2] = s0;
+                Ss[(b * groups + g) * 2 + 1] = s1;
+                if (blockIdx.x == 0) {
+                    S[(b * groups + g) * 2] = s0;
+                    S[(b * groups + g) * 2 + 1] = s1;
+                }
+            }
         }
     }
-    if (dgamma) dgamma[c] = dgm;
-    if (dbeta) dbeta[c] = dbt;
-    if (dpre_csum) dpre_csum[c] = dcs;
-    if (dbeta2) dbeta2[c] = dbt;
-    if (dpre_csum2) dpre_csum2[c] = dcs;
+    __syncthreads();
+    const int c = blockIdx.x * 32 + lane;
+    float dgm = 0.f, dbt = 0.f, dcs = 0.f;
+    if (c < C) {
+        const int g = c / cg;
+        const float inv_n = 1.f / ((float)cg * (float)T);
+        const float gm = gamma[c];
+        const bool want = dpre_bsum || dpre_csum || dpre_csum2;
+        for (int b = w; b < B; b += 16) {
+            const float* r = R + ((int64_t)b * C + c) * 3;
+            const float r0 = r[0], r1 = r[1];
+            dbt += r0;
+            dgm += r1;
+            if (want) {
+                const float* sp = Ss + (b * groups + g) * 2;
+                const float v = rstd[b * groups + g] * (gm * r0 - (float)T * sp[0] * inv_n - r[2] * sp[1] * inv_n);
+                if (dpre_bsum) dpre_bsum[(int64_t)b * C + c] = v;
+                dcs += v;
+            }
+        }
+    }
+    red[0][w][lane] = dgm;
+    red[1][w][lane] = dbt;
+    red[2][w][lane] = dcs;
+    __syncthreads();
+    if (w < 3 && c < C) {
+        float t = 0.f;
+#pragma unroll
+        for (int j = 0; j < 16; j++) t += red[w][j][lane];
+        if (w == 0) {
+            if (dgamma) dgamma[c] = t;
+        } else if (w == 1) {
+            if (dbeta) dbeta[c] = t;
+            if (dbeta2) dbeta2[c] = t;
+        } else {
+            if (dpre_csum) dpre_csum[c] = t;
+            if (dpre_csum2) dpre_csum2[c] = t;
+        }
+    }
 }
 
 template <int VEC>
@@ -158,29 +203,43 @@ __global__ void gn_bwd_apply_kernel(const float* __restrict__ dn, const float* _
     }
 }
 
-// da planes (rows, (2C)p) from dg (rows, C), a (rows, 2C)
+// da planes (rows, (2C)p) from dg (rows, C), a (rows, 2C).  A thread takes VEC channels c < C and produces BOTH
+// halves (tanh half at c, sigmoid half at C + c) from one tanh / exp pair and vector loads (the first version
+// recomputed the pair for each half with scalar loads: 14.7 us for 12 MB in, 4 MB out).
 template <int VEC>
 __global__ void gate_bwd_apply_kernel(const float* __restrict__ dg, const float* __restrict__ a,
                                       const float* __restrict__ mean, const float* __restrict__ rstd,
                                       const float* __restrict__ gamma, const float* __restrict__ beta,
                                       const float* __restrict__ S, int64_t rows, int C, int T, int Cp, int P,
                                       bf16* __restrict__ da_planes) {
-    const int C2 = 2 * C, Cv = C2 / VEC;
+    const int Cv = C / VEC;
     const int64_t n = rows * Cv, plane = rows * Cp;
     const float inv_n = 1.f / ((float)C * (float)T);
     GRID_STRIDE(i, n) {
         const int64_t r = i / Cv;
-        const int c2 = (int)(i - r * Cv) * VEC;
+        const int c = (int)(i - r * Cv) * VEC;
         const int b = (int)(r / T);
-        float v[VEC];
+        const float m1 = mean[2 * b], m2 = mean[2 * b + 1], rs1 = rstd[2 * b], rs2 = rstd[2 * b + 1];
+        const float S10 = S[4 * b] * inv_n, S11 = S[4 * b + 1] * inv_n, S20 = S[4 * b + 2] * inv_n, S21 = S[4 * b + 3] * inv_n;
+        float a1[VEC], a2[VEC], d[VEC], g1[VEC], g2[VEC], b1[VEC], b2[VEC], v1[VEC], v2[VEC];
+        ld_vec<VEC>(a + r * 2 * C + c, a1);
+        ld_vec<VEC>(a + r * 2 * C + C + c, a2);
+        ld_vec<VEC>(dg + r * C + c, d);
+        ld_vec<VEC>(gamma + c, g1);
+        ld_vec<VEC>(gamma + C + c, g2);
+        ld_vec<VEC>(beta + c, b1);
+        ld_vec<VEC>(beta + C + c, b2);
 #pragma unroll
         for (int j = 0; j < VEC; j++) {
-            const int gi = b * 2 + (c2 + j >= C ? 1 : 0);
-            float xh;
-            const float d = gate_dn(dg, a, mean, rstd, gamma, beta, b, r, c2 + j, C, xh);
-            v[j] = rstd[gi] * (gamma[c2 + j] * d - S[gi * 2] * inv_n - xh * S[gi * 2 + 1] * inv_n);
+            const float x1 = (a1[j] - m1) * rs1, x2 = (a2[j] - m2) * rs2;
+            const float th = tanhf(x1 * g1[j] + b1[j]);
+            const float sg = sigmoidf_(x2 * g2[j] + b2[j]);
+            const float dn1 = d[j] * sg * (1.f - th * th), dn2 = d[j] * th * sg * (1.f - sg);
+            v1[j] = rs1 * (g1[j] * dn1 - S10 - x1 * S11);
+            v2[j] = rs2 * (g2[j] * dn2 - S20 - x2 * S21);
         }
-        st_planes_vec<VEC>(da_planes, r * Cp + c2, plane, P, v);
+        st_planes_vec<VEC>(da_planes, r * Cp + c, plane, P, v1);
+        st_planes_vec<VEC>(da_planes, r * Cp + C + c, plane, P, v2);
     }
 }
 
@@ -194,22 +253,33 @@ __global__ void act_bwd_add_kernel(const float* __restrict__ du, const float* __
     }
 }
 
-// out[c] = sum over the B*T frame rows; one block (32 x 32) per 32 channels
-__global__ void __launch_bounds__(1024) channel_sum_kernel(const float* __restrict__ x, int64_t rows, int C,
-                                                           float* __restrict__ out) {
-    __shared__ float red[32][33];
+// out[c] += sum over a slice of the B*T frame rows; grid (ceil(C/32), row slices), block 32 x 8; `out` zeroed by
+// the host wrapper.  (One 1024-thread block per 32 channels used 16 SMs and took 11 us for 4 MB.)
+__global__ void __launch_bounds__(256) channel_sum_kernel(const float* __restrict__ x, int64_t rows, int C,
+                                                          float* __restrict__ out) {
+    __shared__ float red[8][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + tx;
-    float s = 0.f;
-    if (c < C)
-        for (int64_t r = ty; r < rows; r += 32) s += x[r * C + c];
-    red[ty][tx] = s;
+    const int64_t per = (rows + gridDim.y - 1) / gridDim.y;
+    const int64_t r0 = per * blockIdx.y, r1 = r0 + per < rows ? r0 + per : rows;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    if (c < C) {
+        int64_t r = r0 + ty;
+        for (; r + 24 < r1; r += 32) {          // four independent loads in flight
+            s0 += x[r * C + c];
+            s1 += x[(r + 8) * C + c];
+            s2 += x[(r + 16) * C + c];
+            s3 += x[(r + 24) * C + c];
+        }
+        for (; r < r1; r += 8) s0 += x[r * C + c];
+    }
+    red[ty][tx] = (s0 + s1) + (s2 + s3);
     __syncthreads();
     if (ty == 0 && c < C) {
         float t = 0.f;
 #pragma unroll
-        for (int j = 0; j < 32; j++) t += red[j][tx];
-        out[c] = t;
+        for (int j = 0; j < 8; j++) t += red[j][tx];
+        atomicAdd(out + c, t);
     }
 }
 
@@ -226,12 +296,61 @@ extern "C" int vnb_gn_bwd_rows(const float* dn, const float* h, const float* mea
     return VNB_OK;
 }
 
+namespace vnb {
+// Gate variant of bwd_rows: a thread owns channel c < C and accumulates the three row sums of BOTH halves
+// (tanh half c, sigmoid half C + c) from one tanh / exp pair per element, four frames in flight.
+// grid (ceil(C/32), B), block 32 x 8.
+__global__ void __launch_bounds__(256) gate_bwd_rows_kernel(const float* __restrict__ dg, const float* __restrict__ a,
+                                                            const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                            int C, int T, float* __restrict__ R) {
+    __shared__ float red[6][8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int b = blockIdx.y, c = blockIdx.x * 32 + tx;
+    float s[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (c < C) {
+        const float m1 = mean[2 * b], m2 = mean[2 * b + 1], rs1 = rstd[2 * b], rs2 = rstd[2 * b + 1];
+        const float g1 = gamma[c], g2 = gamma[C + c], b1 = beta[c], b2 = beta[C + c];
+        for (int t0 = ty; t0 < T; t0 += 32) {
+            float a1[4], a2[4], d[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int t = t0 + 8 * u;
+                const int64_t r = (int64_t)b * T + (t < T ? t : 0);
+                a1[u] = a[r * 2 * C + c];
+                a2[u] = a[r * 2 * C + C + c];
+                d[u] = t < T ? dg[r * C + c] : 0.f;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (t0 + 8 * u >= T) continue;
+                const float x1 = (a1[u] - m1) * rs1, x2 = (a2[u] - m2) * rs2;
+                const float th = tanhf(x1 * g1 + b1);
+                const float sg = sigmoidf_(x2 * g2 + b2);
+                const float dn1 = d[u] * sg * (1.f - th * th), dn2 = d[u] * th * sg * (1.f - sg);
+                s[0] += dn1; s[1] += dn1 * x1; s[2] += x1;
+                s[3] += dn2; s[4] += dn2 * x2; s[5] += x2;
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 6; k++) red[k][ty][tx] = s[k];
+    __syncthreads();
+    if (ty < 6 && c < C) {
+        float t = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; j++) t += red[ty][j][tx];
+        const int ch = ty < 3 ? c : C + c;
+        R[((int64_t)b * 2 * C + ch) * 3 + (ty % 3)] = t;
+    }
+}
+}  // namespace vnb
+
 extern "C" int vnb_gate_bwd_rows(const float* dg, const float* a, const float* mean, const float* rstd,
                                  const float* gamma, const float* beta, int B, int C, int T, float* R, void* stream) {
     VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && R && B > 0 && B <= 65535 && C > 0 && T > 0,
                 "gate_bwd_rows: bad arguments");
-    bwd_rows_kernel<true><<<dim3(ceil_div(2 * C, 32), B), 256, 0, (cudaStream_t)stream>>>(dg, a, mean, rstd, gamma, beta,
-                                                                                          2 * C, T, 2, R);
+    gate_bwd_rows_kernel<<<dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream>>>(dg, a, mean, rstd, gamma, beta, C, T, R);
     VNB_LAUNCH_CHECK("gate_bwd_rows");
     return VNB_OK;
 }
@@ -241,11 +360,11 @@ extern "C" int vnb_gn_bwd_finalize(const float* R, const float* gamma, const flo
                                    float* dpre_csum, float* dbeta2, float* dpre_csum2, void* stream) {
     VNB_REQUIRE(R && gamma && rstd && S && B > 0 && C > 0 && groups > 0 && C % groups == 0, "gn_bwd_finalize: bad arguments");
     cudaStream_t st = (cudaStream_t)stream;
-    gn_bwd_groupsum_kernel<<<B * groups, 256, 0, st>>>(R, gamma, C, groups, S);
-    VNB_LAUNCH_CHECK("gn_bwd_groupsum");
-    gn_bwd_channel_kernel<<<ceil_div(C, 128), 128, 0, st>>>(R, gamma, rstd, S, B, C, T, groups, dgamma, dbeta, dpre_bsum, dpre_csum, dbeta2,
-                                                            dpre_csum2);
-    VNB_LAUNCH_CHECK("gn_bwd_channel");
+    const size_t smem = ((size_t)((B * groups * 2 + 3) & ~3) + 3 * 16 * 33) * sizeof(float);
+    VNB_REQUIRE(smem <= 48 * 1024, "gn_bwd_finalize: B*groups = %d too large", B * groups);
+    gn_bwd_finalize_kernel<<<ceil_div(C, 32), 512, smem, st>>>(R, gamma, rstd, B, C, T, groups, dgamma, dbeta, S, dpre_bsum,
+                                                             dpre_csum, dbeta2, dpre_csum2);
+    VNB_LAUNCH_CHECK("gn_bwd_finalize");
     return VNB_OK;
 }
 
@@ -275,7 +394,7 @@ extern "C" int vnb_gate_bwd_apply(const float* dg, const float* a, const float* 
     VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && S && da_planes, "gate_bwd_apply: null pointer");
     VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "gate_bwd_apply: bad shape");
     const int64_t rows = (int64_t)B * T;
-    VEC_DISPATCH((C & 3) == 0, gate_bwd_apply_kernel, rows * 2 * C, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, S,
+    VEC_DISPATCH((C & 3) == 0, gate_bwd_apply_kernel, rows * C, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, S,
                  rows, C, T, round_up8(2 * C), P, (bf16*)da_planes);
     VNB_LAUNCH_CHECK("gate_bwd_apply");
     return VNB_OK;
@@ -291,7 +410,14 @@ extern "C" int vnb_act_bwd_add(const float* du, const float* c, const float* add
 
 extern "C" int vnb_channel_sum(const float* x, int B, int C, int T, float* out, void* stream) {
     VNB_REQUIRE(x && out && B > 0 && C > 0 && T > 0, "channel_sum: bad arguments");
-    channel_sum_kernel<<<ceil_div(C, 32), 1024, 0, (cudaStream_t)stream>>>(x, (int64_t)B * T, C, out);
+    const int64_t rows = (int64_t)B * T;
+    int slices = (int)(rows / 128);
+    slices = slices < 1 ? 1 : slices > 32 ? 32 : slices;
+    if (cudaMemsetAsync(out, 0, (size_t)C * sizeof(float), (cudaStream_t)stream) != cudaSuccess) {
+        set_error("channel_sum: memset failed");
+        return VNB_E_CUDA;
+    }
+    channel_sum_kernel<<<dim3(ceil_div(C, 32), slices), 256, 0, (cudaStream_t)stream>>>(x, rows, C, out);
     VNB_LAUNCH_CHECK("channel_sum");
     return VNB_OK;
 }

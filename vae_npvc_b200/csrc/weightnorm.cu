@@ -65,43 +65,84 @@ __global__ void __launch_bounds__(256) wn_backward_kernel(const float* __restric
 
 // ---- batched variants over the trainer's flat parameter / gradient buffers -------------------
 // desc: int64[n_layers][WN_DESC] = {v_off, g_off (-1: plain weight), d0, d1, k, transposed, wf_off, wb_off,
-// w32_off (-1: not wanted), row0};  row2layer: int32[total_rows].  One block per weight row of ANY layer.
-constexpr int WN_DESC = 10;
+// w32_off (-1: not wanted), row0, tile0, 0};  row2layer: int32[total_rows];  tile2layer: int32[total_tiles]
+// (a tile = 32 rows x 32 columns x k taps of one layer's (d0, d1, k) parameter).
+constexpr int WN_DESC = 12;
+constexpr int WN_TILE = 32;
 
-__global__ void __launch_bounds__(256) wn_prepare_batch_kernel(const float* __restrict__ flat_p,
-                                                               const int64_t* __restrict__ desc,
-                                                               const int* __restrict__ row2layer, int P,
-                                                               bf16* __restrict__ wbuf, float* __restrict__ w32buf) {
-    __shared__ float red[32];
-    const int64_t* L = desc + (int64_t)row2layer[blockIdx.x] * WN_DESC;
-    const int i = blockIdx.x - (int)L[9];
-    const int d0 = (int)L[2], d1 = (int)L[3], k = (int)L[4], transposed = (int)L[5];
-    const int n = d1 * k;
-    const float* row = flat_p + L[0] + (int64_t)i * n;
-    float scale = 1.f;
-    if (L[1] >= 0) {
-        float ss = 0.f;
-        for (int e = threadIdx.x; e < n; e += blockDim.x) {
-            const float x = row[e];
-            ss += x * x;
-        }
-        ss = block_sum(ss, red);
-        scale = flat_p[L[1] + i] / sqrtf(ss);
+// scale[row] = g / ||v_row||  (1 for plain weights): one warp per weight row of ANY layer
+__global__ void __launch_bounds__(256) wn_rowscale_kernel(const float* __restrict__ flat_p, const int64_t* __restrict__ desc,
+                                                          const int* __restrict__ row2layer, int total_rows,
+                                                          float* __restrict__ scale) {
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= total_rows) return;
+    const int64_t* L = desc + (int64_t)row2layer[row] * WN_DESC;
+    if (L[1] < 0) {
+        if (lane == 0) scale[row] = 1.f;
+        return;
     }
-    const int co_n = transposed ? d1 : d0, ci_n = transposed ? d0 : d1;
-    const int ci_p = (ci_n + 7) & ~7, co_p = (co_n + 7) & ~7;
-    const int64_t wf_plane = (int64_t)k * co_n * ci_p, wb_plane = (int64_t)k * ci_n * co_p;
-    bf16* wf = L[6] >= 0 ? wbuf + L[6] : nullptr;
-    bf16* wb = L[7] >= 0 ? wbuf + L[7] : nullptr;
+    const int i = row - (int)L[9];
+    const int n = (int)L[3] * (int)L[4];
+    const float* v = flat_p + L[0] + (int64_t)i * n;
+    float ss = 0.f;
+    if ((((uintptr_t)v) & 15) == 0 && (n & 3) == 0) {
+        const float4* v4 = reinterpret_cast<const float4*>(v);
+        for (int e = lane; e < n / 4; e += 32) {
+            const float4 x = v4[e];
+            ss += (x.x * x.x + x.y * x.y) + (x.z * x.z + x.w * x.w);
+        }
+    } else {
+        for (int e = lane; e < n; e += 32) ss += v[e] * v[e];
+    }
+    ss = warp_sum(ss);
+    if (lane == 0) scale[row] = flat_p[L[1] + i] / sqrtf(ss);
+}
+
+// One block per 32 x 32 x k tile: coalesced read of v, scaled by the row's g/||v||, staged in shared memory, then
+// written twice - once along d1 (the operand whose contraction index is d1: wf for Conv1d, wb for
+// ConvTranspose1d) and once TRANSPOSED along d0 (the other operand, taps flipped).  The row-per-block version
+// scattered 2-byte stores d0 * 2 bytes apart: 364 us for 125 MB in / 125 MB out.
+__global__ void __launch_bounds__(256) wn_tiles_kernel(const float* __restrict__ flat_p, const int64_t* __restrict__ desc,
+                                                       const int* __restrict__ tile2layer, const float* __restrict__ scale,
+                                                       int P, bf16* __restrict__ wbuf, float* __restrict__ w32buf) {
+    extern __shared__ float wn_tile[];                // [k][32][33]
+    const int64_t* L = desc + (int64_t)tile2layer[blockIdx.x] * WN_DESC;
+    const int d0 = (int)L[2], d1 = (int)L[3], k = (int)L[4], transposed = (int)L[5];
+    const int tcols = (d1 + WN_TILE - 1) / WN_TILE;
+    const int t = blockIdx.x - (int)L[10];
+    const int r0 = (t / tcols) * WN_TILE, c0 = (t % tcols) * WN_TILE;
+    const int nr = d0 - r0 < WN_TILE ? d0 - r0 : WN_TILE, nc = d1 - c0 < WN_TILE ? d1 - c0 : WN_TILE;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float* v = flat_p + L[0];
     float* w32 = L[8] >= 0 ? w32buf + L[8] : nullptr;
-    for (int e = threadIdx.x; e < n; e += blockDim.x) {
-        const int j1 = e / k, j = e - j1 * k;
-        const float w = row[e] * scale;
-        if (w32) w32[(int64_t)i * n + e] = w;
-        const int co = transposed ? j1 : i, ci = transposed ? i : j1;
-        const int tap = transposed ? (k - 1 - j) : j;
-        if (wf) store_planes(wf, ((int64_t)tap * co_n + co) * ci_p + ci, wf_plane, P, w);
-        if (wb) store_planes(wb, ((int64_t)(k - 1 - tap) * ci_n + ci) * co_p + co, wb_plane, P, w);
+    for (int rr = warp; rr < nr; rr += 8) {
+        const float sc = scale[(int)L[9] + r0 + rr];
+        const int64_t base = ((int64_t)(r0 + rr) * d1 + c0) * k;
+        for (int e = lane; e < nc * k; e += 32) {
+            const float w = v[base + e] * sc;
+            if (w32) w32[base + e] = w;
+            const int cc = e / k, j = e - cc * k;
+            wn_tile[(j * WN_TILE + rr) * 33 + cc] = w;
+        }
+    }
+    __syncthreads();
+    // direct: [j][row][col], pitch round8(d1);  transposed: [k-1-j][col][row], pitch round8(d0)
+    const int64_t off_d = transposed ? L[7] : L[6], off_t = transposed ? L[6] : L[7];
+    const int p1 = (d1 + 7) & ~7, p0 = (d0 + 7) & ~7;
+    const int64_t plane_d = (int64_t)k * d0 * p1, plane_t = (int64_t)k * d1 * p0;
+    if (off_d >= 0) {
+        bf16* D = wbuf + off_d;
+        for (int idx = warp; idx < k * nr; idx += 8) {
+            const int j = idx / nr, rr = idx - j * nr;
+            if (lane < nc) store_planes(D, ((int64_t)j * d0 + r0 + rr) * p1 + c0 + lane, plane_d, P, wn_tile[(j * WN_TILE + rr) * 33 + lane]);
+        }
+    }
+    if (off_t >= 0) {
+        bf16* Tt = wbuf + off_t;
+        for (int idx = warp; idx < k * nc; idx += 8) {
+            const int j = idx / nc, cc = idx - j * nc;
+            if (lane < nr) store_planes(Tt, ((int64_t)(k - 1 - j) * d1 + c0 + cc) * p0 + r0 + lane, plane_t, P, wn_tile[(j * WN_TILE + lane) * 33 + cc]);
+        }
     }
 }
 
@@ -117,6 +158,38 @@ __global__ void __launch_bounds__(256) wn_backward_batch_kernel(const float* __r
     const int n = (int)L[3] * (int)L[4];
     const float* vr = flat_p + L[0] + (int64_t)i * n;
     float* dr = flat_g + L[0] + (int64_t)i * n;
+    const float gi = flat_p[L[1] + i];
+    if ((n & 3) == 0 && n <= 4096 && ((((uintptr_t)vr) | ((uintptr_t)dr)) & 15) == 0) {
+        // one pass over global memory: the row (<= 4 float4 per thread of v and of dw) stays in registers
+        const float4* v4 = reinterpret_cast<const float4*>(vr);
+        float4* d4 = reinterpret_cast<float4*>(dr);
+        const int n4 = n >> 2;
+        float4 xv[4], xd[4];
+        float ss = 0.f, dot = 0.f;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int e = threadIdx.x + u * 256;
+            if (e < n4) {
+                xv[u] = v4[e];
+                xd[u] = d4[e];
+                ss += (xv[u].x * xv[u].x + xv[u].y * xv[u].y) + (xv[u].z * xv[u].z + xv[u].w * xv[u].w);
+                dot += (xv[u].x * xd[u].x + xv[u].y * xd[u].y) + (xv[u].z * xd[u].z + xv[u].w * xd[u].w);
+            }
+        }
+        ss = block_sum(ss, red);
+        dot = block_sum(dot, red);
+        const float norm = sqrtf(ss);
+        if (threadIdx.x == 0) flat_g[L[1] + i] = dot / norm;
+        const float a = gi / norm, b = gi * dot / (norm * ss);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int e = threadIdx.x + u * 256;
+            if (e < n4)
+                d4[e] = make_float4(a * xd[u].x - b * xv[u].x, a * xd[u].y - b * xv[u].y, a * xd[u].z - b * xv[u].z,
+                                    a * xd[u].w - b * xv[u].w);
+        }
+        return;
+    }
     float ss = 0.f, dot = 0.f;
     for (int e = threadIdx.x; e < n; e += blockDim.x) {
         const float x = vr[e];
@@ -126,7 +199,6 @@ __global__ void __launch_bounds__(256) wn_backward_batch_kernel(const float* __r
     ss = block_sum(ss, red);
     dot = block_sum(dot, red);
     const float norm = sqrtf(ss);
-    const float gi = flat_p[L[1] + i];
     if (threadIdx.x == 0) flat_g[L[1] + i] = dot / norm;
     const float a = gi / norm, b = gi * dot / (norm * ss);
     for (int e = threadIdx.x; e < n; e += blockDim.x) dr[e] = a * dr[e] - b * vr[e];
@@ -135,11 +207,17 @@ __global__ void __launch_bounds__(256) wn_backward_batch_kernel(const float* __r
 }  // namespace vnb
 
 extern "C" int vnb_wn_prepare_batch(const float* flat_p, const int64_t* desc, const int* row2layer, int total_rows,
-                                    int P, void* wbuf, float* w32buf, void* stream) {
-    VNB_REQUIRE(flat_p && desc && row2layer && wbuf && total_rows > 0 && (P == 1 || P == 3), "wn_prepare_batch: bad arguments");
-    vnb::wn_prepare_batch_kernel<<<total_rows, 256, 0, (cudaStream_t)stream>>>(flat_p, desc, row2layer, P,
-                                                                               (vnb::bf16*)wbuf, w32buf);
-    VNB_LAUNCH_CHECK("wn_prepare_batch");
+                                    const int* tile2layer, int total_tiles, int max_k, int P, float* row_scale,
+                                    void* wbuf, float* w32buf, void* stream) {
+    VNB_REQUIRE(flat_p && desc && row2layer && tile2layer && row_scale && wbuf && total_rows > 0 && total_tiles > 0 &&
+                    (P == 1 || P == 3), "wn_prepare_batch: bad arguments");
+    const size_t smem = (size_t)max_k * vnb::WN_TILE * 33 * sizeof(float);
+    VNB_REQUIRE(max_k >= 1 && smem <= 48 * 1024, "wn_prepare_batch: kernel size %d too large for the tile buffer", max_k);
+    cudaStream_t st = (cudaStream_t)stream;
+    vnb::wn_rowscale_kernel<<<vnb::ceil_div(total_rows, 8), 256, 0, st>>>(flat_p, desc, row2layer, total_rows, row_scale);
+    VNB_LAUNCH_CHECK("wn_rowscale");
+    vnb::wn_tiles_kernel<<<total_tiles, 256, smem, st>>>(flat_p, desc, tile2layer, row_scale, P, (vnb::bf16*)wbuf, w32buf);
+    VNB_LAUNCH_CHECK("wn_tiles");
     return VNB_OK;
 }
 

@@ -108,8 +108,9 @@ def wn_prepare(v, g, transposed, P, need_wf=True, need_wb=True, need_w32=False):
     return ConvWeights(wf, wb, w32, k, co, ci, bool(transposed))
 
 
-def wn_prepare_batch(flat_p, desc, row2layer, P, wbuf, w32buf):
-    _C.call('wn_prepare_batch', flat_p, desc, row2layer, row2layer.numel(), P, wbuf, w32buf)
+def wn_prepare_batch(flat_p, desc, row2layer, P, wbuf, w32buf, tile2layer, max_k, row_scale):
+    _C.call('wn_prepare_batch', flat_p, desc, row2layer, row2layer.numel(), tile2layer, tile2layer.numel(), max_k, P,
+            row_scale, wbuf, w32buf)
 
 
 def wn_backward_batch(flat_p, flat_g, desc, row2layer):
