@@ -70,11 +70,11 @@ int vnb_wn_backward(const float* dw, const float* v, const float* g, int d0, int
                     float* dv, float* dg, void* stream);
 
 /* Batched forms over the trainer's flat fp32 parameter / gradient buffers: all conv layers of the model (55 in
- * the VCC2020 recipe) in two launches (row scales g/||v||, then 32 x 32 x k tiles transposed through shared
+ * the VCC2020 recipe) in two launches (row scales g/||v||, then 64 x 64 x k tiles transposed through shared
  * memory).  desc: int64 [n_layers][12] = {v_off, g_off (-1 = plain weight), d0, d1, k, transposed, wf_off,
  * wb_off, w32_off (-1 = none), row0, tile0, 0} with element offsets into flat_p / wbuf (bf16) / w32buf;
  * row2layer: int32 [total_rows] (total_rows = sum of d0); tile2layer: int32 [total_tiles] (a layer has
- * ceil(d0/32)*ceil(d1/32) tiles, numbered row-major from tile0); max_k = largest k; row_scale: scratch of
+ * ceil(d0/64)*ceil(d1/64) tiles, numbered row-major from tile0); max_k = largest k; row_scale: scratch of
  * total_rows floats.
  * backward: on entry the v slot of flat_g holds dw (written there by vnb_conv_wgrad), on exit dv; the
  * g slot receives dg. */

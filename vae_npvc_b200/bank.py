@@ -64,7 +64,7 @@ class WeightBank(object):
                          int(transposed), wf_off, wb_off, e32, row0, tile0, 0])
             rows += [len(desc) - 1] * d0
             row0 += d0
-            n_tiles = ((d0 + 31) // 32) * ((d1 + 31) // 32)
+            n_tiles = ((d0 + 63) // 64) * ((d1 + 63) // 64)
             tiles += [len(desc) - 1] * n_tiles
             tile0 += n_tiles
             self.max_k = max(self.max_k, k)

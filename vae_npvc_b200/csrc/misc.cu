@@ -65,11 +65,25 @@ __global__ void __launch_bounds__(256) linear_bwd_y_kernel(const float* __restri
     if (i >= I) return;
     float s0 = 0.f, s1 = 0.f;
     const int on = O - o0 < 64 ? O - o0 : 64;
-#pragma unroll 8
-    for (int oo = 0; oo < on; oo++) {
-        const float w = W[(int64_t)(o0 + oo) * I + i];
-        s0 = fmaf(w, dps[ty][oo], s0);
-        s1 = fmaf(w, dps[ty + 8][oo], s1);
+    if (on == 64) {
+        // 4 batches of 16 independent loads: W is usually cold (DRAM latency), so keep many in flight
+#pragma unroll 1
+        for (int ob = 0; ob < 64; ob += 16) {
+            float w[16];
+#pragma unroll
+            for (int u = 0; u < 16; u++) w[u] = W[(int64_t)(o0 + ob + u) * I + i];
+#pragma unroll
+            for (int u = 0; u < 16; u++) {
+                s0 = fmaf(w[u], dps[ty][ob + u], s0);
+                s1 = fmaf(w[u], dps[ty + 8][ob + u], s1);
+            }
+        }
+    } else {
+        for (int oo = 0; oo < on; oo++) {
+            const float w = W[(int64_t)(o0 + oo) * I + i];
+            s0 = fmaf(w, dps[ty][oo], s0);
+            s1 = fmaf(w, dps[ty + 8][oo], s1);
+        }
     }
     if (b0 + ty < B) atomicAdd(dy + (int64_t)(b0 + ty) * I + i, s0);
     if (b0 + ty + 8 < B) atomicAdd(dy + (int64_t)(b0 + ty + 8) * I + i, s1);

@@ -66,9 +66,9 @@ __global__ void __launch_bounds__(256) wn_backward_kernel(const float* __restric
 // ---- batched variants over the trainer's flat parameter / gradient buffers -------------------
 // desc: int64[n_layers][WN_DESC] = {v_off, g_off (-1: plain weight), d0, d1, k, transposed, wf_off, wb_off,
 // w32_off (-1: not wanted), row0, tile0, 0};  row2layer: int32[total_rows];  tile2layer: int32[total_tiles]
-// (a tile = 32 rows x 32 columns x k taps of one layer's (d0, d1, k) parameter).
+// (a tile = 64 rows x 64 columns x k taps of one layer's (d0, d1, k) parameter).
 constexpr int WN_DESC = 12;
-constexpr int WN_TILE = 32;
+constexpr int WN_TILE = 64;
 
 // scale[row] = g / ||v_row||  (1 for plain weights): one warp per weight row of ANY layer
 __global__ void __launch_bounds__(256) wn_rowscale_kernel(const float* __restrict__ flat_p, const int64_t* __restrict__ desc,
@@ -98,14 +98,24 @@ __global__ void __launch_bounds__(256) wn_rowscale_kernel(const float* __restric
     if (lane == 0) scale[row] = flat_p[L[1] + i] / sqrtf(ss);
 }
 
-// One block per 32 x 32 x k tile: coalesced read of v, scaled by the row's g/||v||, staged in shared memory, then
-// written twice - once along d1 (the operand whose contraction index is d1: wf for Conv1d, wb for
-// ConvTranspose1d) and once TRANSPOSED along d0 (the other operand, taps flipped).  The row-per-block version
-// scattered 2-byte stores d0 * 2 bytes apart: 364 us for 125 MB in / 125 MB out.
+// One block per 64 x 64 x k tile: coalesced read of v, scaled by the row's g/||v||, staged in shared memory, then
+// written twice with 128-byte warp stores (2 bf16 per lane) - once along d1 (the operand whose contraction index
+// is d1: wf for Conv1d, wb for ConvTranspose1d) and once TRANSPOSED along d0 (the other operand, taps flipped).
+// The row-per-block version scattered 2-byte stores d0 * 2 bytes apart: 364 us for 125 MB in / 125 MB out.
+__device__ __forceinline__ void store_planes2(bf16* base, int64_t off, int64_t plane_stride, int P, float x, float y, bool two) {
+    if (P == 1 && two && (off & 1) == 0) {
+        *reinterpret_cast<__nv_bfloat162*>(base + off) = __floats2bfloat162_rn(x, y);
+    } else {
+        store_planes(base, off, plane_stride, P, x);
+        if (two) store_planes(base, off + 1, plane_stride, P, y);
+    }
+}
+
 __global__ void __launch_bounds__(256) wn_tiles_kernel(const float* __restrict__ flat_p, const int64_t* __restrict__ desc,
                                                        const int* __restrict__ tile2layer, const float* __restrict__ scale,
                                                        int P, bf16* __restrict__ wbuf, float* __restrict__ w32buf) {
-    extern __shared__ float wn_tile[];                // [k][32][33]
+    extern __shared__ float wn_tile[];                // [k][64][65]
+    constexpr int TP = WN_TILE + 1;
     const int64_t* L = desc + (int64_t)tile2layer[blockIdx.x] * WN_DESC;
     const int d0 = (int)L[2], d1 = (int)L[3], k = (int)L[4], transposed = (int)L[5];
     const int tcols = (d1 + WN_TILE - 1) / WN_TILE;
@@ -122,7 +132,7 @@ __global__ void __launch_bounds__(256) wn_tiles_kernel(const float* __restrict__
             const float w = v[base + e] * sc;
             if (w32) w32[base + e] = w;
             const int cc = e / k, j = e - cc * k;
-            wn_tile[(j * WN_TILE + rr) * 33 + cc] = w;
+            wn_tile[(j * WN_TILE + rr) * TP + cc] = w;
         }
     }
     __syncthreads();
@@ -134,14 +144,23 @@ __global__ void __launch_bounds__(256) wn_tiles_kernel(const float* __restrict__
         bf16* D = wbuf + off_d;
         for (int idx = warp; idx < k * nr; idx += 8) {
             const int j = idx / nr, rr = idx - j * nr;
-            if (lane < nc) store_planes(D, ((int64_t)j * d0 + r0 + rr) * p1 + c0 + lane, plane_d, P, wn_tile[(j * WN_TILE + rr) * 33 + lane]);
+            const int cc = 2 * lane;
+            if (cc < nc) {
+                const float* src = wn_tile + (j * WN_TILE + rr) * TP + cc;
+                store_planes2(D, ((int64_t)j * d0 + r0 + rr) * p1 + c0 + cc, plane_d, P, src[0], cc + 1 < nc ? src[1] : 0.f, cc + 1 < nc);
+            }
         }
     }
     if (off_t >= 0) {
         bf16* Tt = wbuf + off_t;
         for (int idx = warp; idx < k * nc; idx += 8) {
             const int j = idx / nc, cc = idx - j * nc;
-            if (lane < nr) store_planes(Tt, ((int64_t)(k - 1 - j) * d1 + c0 + cc) * p0 + r0 + lane, plane_t, P, wn_tile[(j * WN_TILE + lane) * 33 + cc]);
+            const int rr = 2 * lane;
+            if (rr < nr) {
+                const float* src = wn_tile + (j * WN_TILE + rr) * TP + cc;
+                store_planes2(Tt, ((int64_t)(k - 1 - j) * d1 + c0 + cc) * p0 + r0 + rr, plane_t, P, src[0],
+                              rr + 1 < nr ? src[TP] : 0.f, rr + 1 < nr);
+            }
         }
     }
 }
@@ -211,8 +230,16 @@ extern "C" int vnb_wn_prepare_batch(const float* flat_p, const int64_t* desc, co
                                     void* wbuf, float* w32buf, void* stream) {
     VNB_REQUIRE(flat_p && desc && row2layer && tile2layer && row_scale && wbuf && total_rows > 0 && total_tiles > 0 &&
                     (P == 1 || P == 3), "wn_prepare_batch: bad arguments");
-    const size_t smem = (size_t)max_k * vnb::WN_TILE * 33 * sizeof(float);
-    VNB_REQUIRE(max_k >= 1 && smem <= 48 * 1024, "wn_prepare_batch: kernel size %d too large for the tile buffer", max_k);
+    const size_t smem = (size_t)max_k * vnb::WN_TILE * (vnb::WN_TILE + 1) * sizeof(float);
+    VNB_REQUIRE(max_k >= 1 && smem <= 200 * 1024, "wn_prepare_batch: kernel size %d too large for the tile buffer", max_k);
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+        if (cudaFuncSetAttribute(vnb::wn_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+            vnb::set_error("wn_prepare_batch: cudaFuncSetAttribute(%zu) failed", smem);
+            return VNB_E_CUDA;
+        }
+        smem_set = smem;
+    }
     cudaStream_t st = (cudaStream_t)stream;
     vnb::wn_rowscale_kernel<<<vnb::ceil_div(total_rows, 8), 256, 0, st>>>(flat_p, desc, row2layer, total_rows, row_scale);
     VNB_LAUNCH_CHECK("wn_rowscale");

@@ -46,6 +46,17 @@ def get_bank():
     return _BANK['bank']
 
 
+_SIDE = {'stream': None}
+
+
+def set_side_stream(stream):
+    """Install (or remove, with None) a CUDA stream for the weight-gradient GEMMs.  Nothing in the backward
+    chain consumes dW - only the optimiser does - so with a bank installed they are forked onto this stream
+    (event after the producer of their operands) and run beside the data-gradient chain; the caller joins
+    the stream before it turns dW into (dv, dg).  Works under CUDA-graph capture (fork / join pattern)."""
+    _SIDE['stream'] = stream
+
+
 def _slot(p):
     """The gradient slot of leaf parameter ``p`` when gradients are written directly, else None."""
     if _BANK['bank'] is None or p is None or not getattr(p, 'is_leaf', False):
@@ -67,7 +78,17 @@ def _wgrad(dypl, upl, taps, dil, transposed, v, g):
     v gradient slot (the bank's finish_backward turns it into dv, dg)."""
     bank = _BANK['bank']
     if bank is not None and bank.has(v) and _slot(v) is not None:
-        Pm.conv_wgrad(dypl, upl, taps, dil, transposed, out=v.grad)
+        side = _SIDE['stream']
+        if side is None:
+            Pm.conv_wgrad(dypl, upl, taps, dil, transposed, out=v.grad)
+            return None, None
+        ev = torch.cuda.Event()
+        ev.record()
+        side.wait_event(ev)
+        with torch.cuda.stream(side):
+            Pm.conv_wgrad(dypl, upl, taps, dil, transposed, out=v.grad)
+        dypl.data.record_stream(side)        # operands were allocated on the main stream
+        upl.data.record_stream(side)
         return None, None
     return _dw_to_param_grads(Pm.conv_wgrad(dypl, upl, taps, dil, transposed), v, g)
 

@@ -16,7 +16,7 @@ B200-native differences (all behind the same API):
     (averaged) over NCCL and the EMA codebook statistics are all-reduced inside the model
 
 New optional config keys (defaults keep the reference behaviour): ``cuda_graph`` (True),
-``graph_warmup`` (3), ``precision`` ('bf16' | 'fp32'), ``device`` ('cuda').
+``graph_warmup`` (3), ``precision`` ('bf16' | 'fp32'), ``device`` ('cuda'), ``wgrad_stream`` (True).
 """
 from importlib import import_module
 
@@ -124,6 +124,9 @@ class Trainer(object):
         self.model.train()
 
         self.use_graph = bool(config.get('cuda_graph', True)) and self.device.type == 'cuda'
+        # weight-gradient GEMMs on a second stream, beside the data-gradient chain (functional.set_side_stream)
+        self._side = (torch.cuda.Stream(device=self.device)
+                      if self.device.type == 'cuda' and bool(config.get('wgrad_stream', True)) else None)
         self.graph_warmup = int(config.get('graph_warmup', 3))
         self._graphs = {}                 # (B, X, T) -> captured step
         self._eager_steps = 0
@@ -152,14 +155,18 @@ class Trainer(object):
         self._flat_g.zero_()
         _lvq.defer_items(True)
         Fn.set_bank(self.bank)
+        Fn.set_side_stream(self._side)
         try:
             self.bank.prepare()
             if jitter_src is not None:
                 self.model.jitter.sources = lambda length: jitter_src
             output, loss, detail = self.model([x, y])
             loss.backward()
+            if self._side is not None:
+                torch.cuda.current_stream().wait_stream(self._side)
             self.bank.finish_backward()
         finally:
+            Fn.set_side_stream(None)
             Fn.set_bank(None)
             _lvq.defer_items(False)
         dist = _dist()
