@@ -46,7 +46,7 @@ def get_bank():
     return _BANK['bank']
 
 
-_SIDE = {'stream': None}
+_SIDE = {'stream': None, 'aux': None}
 
 
 def set_side_stream(stream):
@@ -55,6 +55,46 @@ def set_side_stream(stream):
     (event after the producer of their operands) and run beside the data-gradient chain; the caller joins
     the stream before it turns dW into (dv, dg).  Works under CUDA-graph capture (fork / join pattern)."""
     _SIDE['stream'] = stream
+    if stream is None:
+        _SIDE['aux'] = None
+    else:
+        if _SIDE.get('aux_cached') is None or _SIDE['aux_cached'].device != stream.device:
+            _SIDE['aux_cached'] = torch.cuda.Stream(device=stream.device)
+        _SIDE['aux'] = _SIDE['aux_cached']
+
+
+class _Fork(object):
+    """Run an independent op on the auxiliary stream between ``with _Fork(tensors...)`` and ``join()``:
+    the encoder block's skip conv beside its k=3 conv chain, the skip-path data gradient beside the
+    GroupNorm backward chain.  A no-op when no side stream is installed."""
+
+    def __init__(self, *inputs):
+        self.aux = _SIDE['aux']
+        self.inputs = inputs
+
+    def __enter__(self):
+        if self.aux is not None:
+            ev = torch.cuda.Event()
+            ev.record()
+            self.aux.wait_event(ev)
+            self.ctx = torch.cuda.stream(self.aux)
+            self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self.aux is not None:
+            self.ctx.__exit__(*exc)
+            for t in self.inputs:
+                if t is not None:
+                    t.record_stream(self.aux)
+        return False
+
+    def join(self, *outputs):
+        if self.aux is not None:
+            torch.cuda.current_stream().wait_stream(self.aux)
+            for t in outputs:
+                if t is not None:
+                    t.record_stream(torch.cuda.current_stream())
 
 
 def _slot(p):
@@ -193,6 +233,11 @@ class EncBlockFn(Function):
         layers = []
         inp = upl
         y = ypl = yupl = None
+        # the 1x1 skip conv only depends on the block input: run it beside the k-tap conv chain
+        vs, gs, bs = params[5 * n_layers:5 * n_layers + 3]
+        Ws = _weights(vs, gs, False, P)
+        with _Fork(cpl.data) as fk:
+            s_skip = Pm.conv_fwd(cpl, Ws.wf, Ws.taps, 1, C, bs, 0)
         for j in range(n_layers):
             v, g, bias, gamma, beta = params[5 * j:5 * j + 5]
             d = dil if j == 0 else 1
@@ -201,10 +246,8 @@ class EncBlockFn(Function):
             if j < n_layers - 1:
                 yj, _, nxt = Pm.enc_out(h, None, mean, rstd, gamma, beta, P, True, False, True)
             else:
-                vs, gs, bs = params[5 * n_layers:5 * n_layers + 3]
-                Ws = _weights(vs, gs, False, P)
-                s = Pm.conv_fwd(cpl, Ws.wf, Ws.taps, 1, C, bs, 0)
-                y, ypl, yupl = Pm.enc_out(h, s, mean, rstd, gamma, beta, P, True, True, True)
+                fk.join(s_skip)
+                y, ypl, yupl = Pm.enc_out(h, s_skip, mean, rstd, gamma, beta, P, True, True, True)
                 yj, nxt = None, None
             layers.append(dict(inp=inp, h=h, mean=mean, rstd=rstd, wb=W.wb, taps=W.taps, d=d, yj=yj))
             inp = nxt
@@ -236,6 +279,9 @@ class EncBlockFn(Function):
             dpre, dnpl = Pm.gn_bwd_apply(dn, L['h'], L['mean'], L['rstd'], gamma, S, 1, P, last)
             if last:
                 dypl = dnpl
+                if ctx.needs_input_grad[0]:
+                    with _Fork(dypl.data) as fk:       # skip-path data gradient, beside the rest of the chain
+                        dcs = Pm.conv_fwd(dypl, ctx.ws_wb, 1, 1, C)
                 if slots['dbeta2'] is None:
                     grads[5 * n_layers + 2] = (dbeta if dbeta is not None else beta.grad).clone()
             dv, dg = _wgrad(dpre, L['inp'], L['taps'], L['d'], False, v, g)
@@ -247,7 +293,7 @@ class EncBlockFn(Function):
         grads[5 * n_layers], grads[5 * n_layers + 1] = _wgrad(dypl, ctx.cpl, 1, 1, False, vs, gs)
         dc = None
         if ctx.needs_input_grad[0]:
-            dcs = Pm.conv_fwd(dypl, ctx.ws_wb, 1, 1, C)
+            fk.join(dcs)
             dc = Pm.act_bwd_add(du, c, dcs, ACT_LRELU)
         return (dc, None, None, None, None) + tuple(grads)
 
