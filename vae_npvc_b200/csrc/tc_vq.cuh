@@ -32,7 +32,7 @@ struct VqTcArgs {
 };
 
 __global__ void __launch_bounds__(VQT_THREADS, 1)
-vq_lookup_tc_kernel(const __grid_constant__ CUtensorMap map_z, const __grid_constant__ CUtensorMap map_e,
+vq_lookup_tc_stream_kernel(const __grid_constant__ CUtensorMap map_z, const __grid_constant__ CUtensorMap map_e,
                     const VqTcArgs a) {
     constexpr uint32_t A_BYTES = VQT_BM * VQT_BK * 2, B_BYTES = VQT_BN * VQT_BK * 2;
     constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
@@ -157,14 +157,14 @@ vq_lookup_tc_kernel(const __grid_constant__ CUtensorMap map_z, const __grid_cons
     }
 }
 
-int vq_lookup_tc(const void* z_planes, const float* z_sq, const void* e_planes, const float* e_sq, int B, int D, int T,
+static int vq_lookup_tc_stream(const void* z_planes, const float* z_sq, const void* e_planes, const float* e_sq, int B, int D, int T,
                  int K, int64_t* idx, cudaStream_t st) {
     const int64_t N = (int64_t)B * T;
     if (D < 8 || K < 8 || N > (int64_t)1 << 30) return 1;
     constexpr size_t smem = (size_t)VQT_STAGES * (VQT_BM + VQT_BN) * VQT_BK * 2 + 1024;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(vq_lookup_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(vq_lookup_tc_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) {
             set_error("vq_lookup_tc: cudaFuncSetAttribute(%zu): %s", smem, cudaGetErrorString(e));
             return VNB_E_CUDA;
@@ -178,6 +178,214 @@ int vq_lookup_tc(const void* z_planes, const float* z_sq, const void* e_planes, 
     if (!make_tmap_3d(&me, e_planes, (uint64_t)D, (uint64_t)K, 3, (uint64_t)Dp * 2, (uint64_t)K * Dp * 2, VQT_BK, VQT_BN, 1))
         return VNB_E_CUDA;
     VqTcArgs a{N, D, K, z_sq, e_sq, idx};
+    vq_lookup_tc_stream_kernel<<<ceil_div(N, VQT_BM), VQT_THREADS, smem, st>>>(mz, me, a);
+    VNB_LAUNCH_CHECK("vq_lookup_tc");
+    return VNB_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------
+// Resident-frames variant (D <= 128): the main path.
+//   * the CTA's 128 frames (all three planes, 48 KB at D = 64) are loaded ONCE and stay in shared memory;
+//   * the codebook is walked in chunks of 256 codes (one 128 x 256 MMA = 128 tensor cycles per ~70-cycle issue;
+//     the 128-wide version was issue bound at 22-48 % of the tensor roof), each codebook plane of a chunk is
+//     loaded once and used by every frame plane it pairs with:  E2 x Z0 | E1 x (Z1, Z0) | E0 x (Z2, Z1, Z0)
+//     (small terms first), i.e. 3 instead of 6 operand loads per chunk and 96 KB instead of 288 KB of L2 traffic;
+//   * two 256-column accumulators fill TMEM (512 columns): the epilogue drains one while the MMAs fill the other.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int VQR_BN = 256;
+constexpr uint32_t VQR_A_BYTES = VQT_BM * VQT_BK * 2;        // 16 KB: 128 frames x 64 dims of one plane
+constexpr uint32_t VQR_B_BYTES = VQR_BN * VQT_BK * 2;        // 32 KB: 256 codes x 64 dims of one plane
+
+struct VqResArgs {
+    int64_t N;
+    int D, K, nstages;
+    const float* z_sq;
+    const float* e_sq;
+    int64_t* idx;
+};
+
+__global__ void __launch_bounds__(VQT_THREADS, 1)
+vq_lookup_tc_kernel(const __grid_constant__ CUtensorMap map_z, const __grid_constant__ CUtensorMap map_e,
+                    const VqResArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ __align__(8) uint64_t a_bar;
+    __shared__ __align__(8) uint64_t full_bar[8];
+    __shared__ __align__(8) uint64_t empty_bar[8];
+    __shared__ __align__(8) uint64_t tmem_full_bar[2];
+    __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+    __shared__ uint32_t tmem_slot;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t n0 = (int64_t)blockIdx.x * VQT_BM;
+    const int chunks = (a.K + VQR_BN - 1) / VQR_BN;
+    const int kd = (a.D + VQT_BK - 1) / VQT_BK;
+    const int STAGES = a.nstages;
+    uint8_t* smem_a = smem;                                       // [plane][d-chunk] 16 KB tiles
+    uint8_t* smem_b = smem + (size_t)3 * kd * VQR_A_BYTES;        // ring of 32 KB stages
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&map_z);
+        tma_prefetch_desc(&map_e);
+        mbar_init(&a_bar, 1);
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; s++) {
+            mbar_init(&tmem_full_bar[s], 1);
+            mbar_init(&tmem_empty_bar[s], 4);          // one arrival per epilogue warp
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<2 * VQR_BN>(&tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== producer: the frames once, then the codebook planes chunk by chunk =====
+            mbar_expect_tx(&a_bar, (uint32_t)3 * kd * VQR_A_BYTES);
+            for (int pl = 0; pl < 3; pl++)
+                for (int c = 0; c < kd; c++)
+                    tma_load_3d(smem_a + (size_t)(pl * kd + c) * VQR_A_BYTES, &map_z, &a_bar, c * VQT_BK, (int)n0, pl);
+            int s = 0, i = 0;
+            uint32_t ph = 1;
+            for (int ch = 0; ch < chunks; ch++)
+                for (int pb = 2; pb >= 0; pb--)
+                    for (int c = 0; c < kd; c++, i++) {
+                        if (i >= STAGES) mbar_wait(&empty_bar[s], ph);
+                        mbar_expect_tx(&full_bar[s], VQR_B_BYTES);
+                        tma_load_3d(smem_b + (size_t)s * VQR_B_BYTES, &map_e, &full_bar[s], c * VQT_BK, ch * VQR_BN, pb);
+                        if (++s == STAGES) { s = 0; ph ^= 1; }
+                    }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            constexpr uint32_t idesc = instr_desc_bf16(VQT_BM, VQR_BN, 0, 0);
+            mbar_wait(&a_bar, 0);
+            tc_fence_after();
+            const uint32_t sa0 = smem_u32(smem_a), sb0 = smem_u32(smem_b);
+            int s = 0;
+            uint32_t ph = 0;
+            bool ready = mbar_test(&full_bar[0], 0);
+            const int per_chunk = 3 * kd;
+            const int total = chunks * per_chunk;
+            int i = 0;
+            for (int ch = 0; ch < chunks; ch++) {
+                const int buf = ch & 1;
+                if (ch >= 2) {
+                    mbar_wait(&tmem_empty_bar[buf], ((ch >> 1) - 1) & 1);     // epilogue drained this buffer
+                    tc_fence_after();
+                }
+                const uint32_t tacc = tmem_base + (uint32_t)(buf * VQR_BN);
+                uint32_t acc = 0;
+                for (int pb = 2; pb >= 0; pb--) {
+                    for (int c = 0; c < kd; c++, i++) {
+                        if (!ready) mbar_wait(&full_bar[s], ph);
+                        tc_fence_after();
+                        int s1 = s + 1;
+                        uint32_t ph1 = ph;
+                        if (s1 == STAGES) { s1 = 0; ph1 ^= 1; }
+                        bool next_ready = false;
+                        if (i + 1 < total) next_ready = mbar_test(&full_bar[s1], ph1);
+                        const uint64_t db = smem_desc_sw128(sb0 + (uint32_t)s * VQR_B_BYTES, 16, 1024);
+                        // frame planes paired with codebook plane pb: pb = 2 -> {0}; 1 -> {1, 0}; 0 -> {2, 1, 0}
+                        for (int pa = 2 - pb; pa >= 0; pa--) {
+                            const uint64_t da = smem_desc_sw128(sa0 + (uint32_t)(pa * kd + c) * VQR_A_BYTES, 16, 1024);
+#pragma unroll
+                            for (int j = 0; j < VQT_BK / 16; j++) {
+                                umma_bf16(tacc, da + 2 * j, db + 2 * j, idesc, acc);
+                                acc = 1;
+                            }
+                        }
+                        umma_commit(&empty_bar[s]);
+                        ready = next_ready;
+                        s = s1;
+                        ph = ph1;
+                    }
+                }
+                umma_commit(&tmem_full_bar[buf]);
+            }
+        }
+    } else {
+        // ===== epilogue: lane = frame; running argmin over the codebook in registers =====
+        const int q = warp & 3;
+        const int64_t n = n0 + q * 32 + lane;
+        const bool row_ok = n < a.N;
+        const float zq = row_ok ? a.z_sq[n] : 0.f;
+        float best = INFINITY;
+        int bestk = 0;
+        for (int ch = 0; ch < chunks; ch++) {
+            const int buf = ch & 1;
+            mbar_wait_warp(&tmem_full_bar[buf], (ch >> 1) & 1, 20);
+            tc_fence_after();
+#pragma unroll 1
+            for (int c0 = 0; c0 < VQR_BN; c0 += 32) {
+                const int k0 = ch * VQR_BN + c0;
+                if (k0 >= a.K) break;                                   // warp-uniform
+                float v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * VQR_BN + c0), v);
+                const float es = k0 + lane < a.K ? __ldg(a.e_sq + k0 + lane) : INFINITY;
+#pragma unroll
+                for (int i = 0; i < 32; i++) {
+                    // torch: (z_sq + e_sq) - 2*dot  (layers_vq.py:103-105); codes >= K carry +inf
+                    const float dist = fmaf(-2.f, v[i], zq + __shfl_sync(0xffffffffu, es, i));
+                    if (dist < best) {
+                        best = dist;
+                        bestk = k0 + i;
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty_bar[buf])) : "memory");
+            }
+        }
+        if (row_ok) a.idx[n] = (int64_t)bestk;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        __syncwarp();
+        tc_fence_after();
+        tmem_dealloc<2 * VQR_BN>(tmem_base);
+    }
+}
+
+int vq_lookup_tc(const void* z_planes, const float* z_sq, const void* e_planes, const float* e_sq, int B, int D, int T,
+                 int K, int64_t* idx, cudaStream_t st) {
+    const int64_t N = (int64_t)B * T;
+    if (D < 8 || K < 8 || N > (int64_t)1 << 30) return 1;
+    static const int force_stream = getenv("VNB_VQ_STREAM") ? atoi(getenv("VNB_VQ_STREAM")) : 0;
+    const int kd = ceil_div(D, VQT_BK);
+    const size_t a_bytes = (size_t)3 * kd * VQR_A_BYTES;
+    const size_t budget = 227 * 1024 - 2048;
+    if (force_stream || a_bytes + 2 * VQR_B_BYTES > budget) return vq_lookup_tc_stream(z_planes, z_sq, e_planes, e_sq, B, D, T, K, idx, st);
+    int nst = (int)((budget - a_bytes) / VQR_B_BYTES);
+    nst = nst > 6 ? 6 : nst;
+    const size_t smem = a_bytes + (size_t)nst * VQR_B_BYTES + 1024;
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+        cudaError_t e = cudaFuncSetAttribute(vq_lookup_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) {
+            set_error("vq_lookup_tc: cudaFuncSetAttribute(%zu): %s", smem, cudaGetErrorString(e));
+            return VNB_E_CUDA;
+        }
+        smem_set = smem;
+    }
+    const int Dp = round_up8(D);
+    CUtensorMap mz, me;
+    if (!make_tmap_3d(&mz, z_planes, (uint64_t)D, (uint64_t)N, 3, (uint64_t)Dp * 2, (uint64_t)N * Dp * 2, VQT_BK, VQT_BM, 1))
+        return VNB_E_CUDA;
+    if (!make_tmap_3d(&me, e_planes, (uint64_t)D, (uint64_t)K, 3, (uint64_t)Dp * 2, (uint64_t)K * Dp * 2, VQT_BK, VQR_BN, 1))
+        return VNB_E_CUDA;
+    VqResArgs a{N, D, K, nst, z_sq, e_sq, idx};
     vq_lookup_tc_kernel<<<ceil_div(N, VQT_BM), VQT_THREADS, smem, st>>>(mz, me, a);
     VNB_LAUNCH_CHECK("vq_lookup_tc");
     return VNB_OK;
