@@ -32,6 +32,35 @@ int backend();
         vnb::count_launch();                                                        \
     } while (0)
 
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------------------
+// Every kernel of the library is launched with cudaLaunchAttributeProgrammaticStreamSerialization (captured as a
+// programmatic edge inside the trainer's CUDA graph) and starts with pdl_wait(): the next kernel's launch,
+// block scheduling and - for the tcgen05 kernels - barrier / TMEM / tensor-map prologue overlap the tail of the
+// previous one; pdl_wait() returns once every prerequisite grid has completed and flushed its memory, so data
+// dependences (RAW and WAR) are exactly those of plain stream order.  VNB_PDL=0 switches the attribute off.
+bool pdl_enabled();
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() {
+    asm volatile("griddepcontrol.launch_dependents;\n\tgriddepcontrol.wait;" ::: "memory");
+}
+#endif
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                   Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 static inline int round_up8(int x) { return (x + 7) & ~7; }
 

@@ -22,15 +22,16 @@ static inline int ew_grid(int64_t n) {
 #define VEC_DISPATCH(cond4, KERNEL, n_scalar, st, ...)                                        \
     do {                                                                                      \
         if (cond4)                                                                            \
-            KERNEL<4><<<ew_grid((n_scalar) / 4), EW_THREADS, 0, st>>>(__VA_ARGS__);           \
+            vnb::launch_k(KERNEL<4>, ew_grid((n_scalar) / 4), EW_THREADS, 0, st, __VA_ARGS__);           \
         else                                                                                  \
-            KERNEL<1><<<ew_grid(n_scalar), EW_THREADS, 0, st>>>(__VA_ARGS__);                 \
+            vnb::launch_k(KERNEL<1>, ew_grid(n_scalar), EW_THREADS, 0, st, __VA_ARGS__);                 \
     } while (0)
 
 // ------------------------------------------------------------------------------------------
 // (B, R, S) -> (B, S, R), 32x32 shared-memory tiles (both sides coalesced)
 __global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict__ in, int R, int S,
                                                         float* __restrict__ out) {
+    pdl_wait();
     __shared__ float tile[32][33];
     const int64_t base = (int64_t)blockIdx.z * R * S;
     const int s0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
@@ -50,6 +51,7 @@ __global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict_
 template <int VEC>
 __global__ void make_planes_kernel(const float* __restrict__ x, int64_t rows, int C, int Cp, int P, float scale,
                                    int act, bf16* __restrict__ out_id, bf16* __restrict__ out_act) {
+    pdl_wait();
     const int Cv = C / VEC;
     const int64_t n = rows * Cv, plane = rows * Cp;
     GRID_STRIDE(i, n) {
@@ -71,6 +73,7 @@ __global__ void make_planes_kernel(const float* __restrict__ x, int64_t rows, in
 template <int VEC>
 __global__ void concat_planes_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb, int Cb,
                                      int64_t rows, int Cp, int P, bf16* __restrict__ out) {
+    pdl_wait();
     const int Cc = Ca + Cb, Cv = Cc / VEC;
     const int64_t n = rows * Cv, plane = rows * Cp;
     GRID_STRIDE(i, n) {
@@ -92,6 +95,7 @@ constexpr int GN_MAX_GROUPS = 8;
 
 __global__ void __launch_bounds__(256) gn_stats_partial_kernel(const float* __restrict__ h, int C, int T, int groups,
                                                                int rows_per, float* __restrict__ ws) {
+    pdl_wait();
     __shared__ float acc[GN_MAX_GROUPS];
     __shared__ float lmean[GN_MAX_GROUPS];
     const int b = blockIdx.y, chunk = blockIdx.x, chunks = gridDim.x;
@@ -139,6 +143,7 @@ __global__ void __launch_bounds__(256) gn_stats_partial_kernel(const float* __re
 // one warp per (b, group)
 __global__ void gn_stats_merge_kernel(const float* __restrict__ ws, int BG, int chunks, int T, int rows_per, int cg,
                                       float eps, float* __restrict__ mean, float* __restrict__ rstd) {
+    pdl_wait();
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (w >= BG) return;
     const float* p = ws + (int64_t)w * chunks * 2;
@@ -165,6 +170,7 @@ __global__ void gn_stats_merge_kernel(const float* __restrict__ ws, int BG, int 
 // mean / rstd from the fp64 (sum, sum of squares) pairs accumulated by the conv epilogue
 __global__ void gn_finalize_kernel(const double* __restrict__ sums, int BG, double n, float eps,
                                    float* __restrict__ mean, float* __restrict__ rstd) {
+    pdl_wait();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= BG) return;
     const double m = sums[2 * i] / n;
@@ -181,6 +187,7 @@ __global__ void enc_out_kernel(const float* __restrict__ h, const float* __restr
                                const float* __restrict__ rstd, const float* __restrict__ gamma,
                                const float* __restrict__ beta, int64_t rows, int C, int T, int Cp, int P,
                                float* __restrict__ y, bf16* __restrict__ y_planes, bf16* __restrict__ u_planes) {
+    pdl_wait();
     const int Cv = C / VEC;
     const int64_t n = rows * Cv, plane = rows * Cp;
     GRID_STRIDE(i, n) {
@@ -217,6 +224,7 @@ __global__ void dec_gate_kernel(const float* __restrict__ a, const float* __rest
                                 const float* __restrict__ rstd, const float* __restrict__ gamma,
                                 const float* __restrict__ beta, int64_t rows, int C, int T, int Cp, int P,
                                 bf16* __restrict__ g_planes) {
+    pdl_wait();
     const int Cv = C / VEC;
     const int64_t n = rows * Cv, plane = rows * Cp;
     GRID_STRIDE(i, n) {
@@ -246,6 +254,7 @@ template <int VEC>
 __global__ void dec_out_kernel(const float* __restrict__ r, const float* __restrict__ x, int64_t rows, int C, int S,
                                int Cp, int P, float* __restrict__ x_out, bf16* __restrict__ x_planes,
                                float* __restrict__ skip_sum, int first) {
+    pdl_wait();
     const int Cc = C + S, Cv = Cc / VEC;
     const int64_t n = rows * Cv, plane = rows * Cp;
     GRID_STRIDE(i, n) {
@@ -281,7 +290,7 @@ using namespace vnb;
 extern "C" int vnb_transpose(const float* in, int B, int R, int S, float* out, void* stream) {
     VNB_REQUIRE(in && out && B > 0 && R > 0 && S > 0 && B <= 65535, "transpose: bad arguments");
     dim3 grid(ceil_div(S, 32), ceil_div(R, 32), B);
-    transpose_kernel<<<grid, 256, 0, ST>>>(in, R, S, out);
+    vnb::launch_k(transpose_kernel, grid, 256, 0, ST, in, R, S, out);
     VNB_LAUNCH_CHECK("transpose");
     return VNB_OK;
 }
@@ -320,10 +329,10 @@ extern "C" int vnb_gn_stats(const float* h, int B, int C, int T, int groups, flo
         rows_per = ceil_div(T, chunks);
         chunks = ceil_div(T, rows_per);
     }
-    gn_stats_partial_kernel<<<dim3(chunks, B), 256, 0, ST>>>(h, C, T, groups, rows_per, ws);
+    vnb::launch_k(gn_stats_partial_kernel, dim3(chunks, B), 256, 0, ST, h, C, T, groups, rows_per, ws);
     VNB_LAUNCH_CHECK("gn_stats_partial");
     const int BG = B * groups;
-    gn_stats_merge_kernel<<<ceil_div((int64_t)BG * 32, 128), 128, 0, ST>>>(ws, BG, chunks, T, rows_per, C / groups, eps,
+    vnb::launch_k(gn_stats_merge_kernel, ceil_div((int64_t)BG * 32, 128), 128, 0, ST, ws, BG, chunks, T, rows_per, C / groups, eps,
                                                                            mean, rstd);
     VNB_LAUNCH_CHECK("gn_stats_merge");
     return VNB_OK;
@@ -332,7 +341,7 @@ extern "C" int vnb_gn_stats(const float* h, int B, int C, int T, int groups, flo
 extern "C" int vnb_gn_finalize(const double* gn_sums, int BG, double n, float eps, float* mean, float* rstd,
                                void* stream) {
     VNB_REQUIRE(gn_sums && mean && rstd && BG > 0 && n > 0, "gn_finalize: bad arguments");
-    gn_finalize_kernel<<<ceil_div(BG, 128), 128, 0, ST>>>(gn_sums, BG, n, eps, mean, rstd);
+    vnb::launch_k(gn_finalize_kernel, ceil_div(BG, 128), 128, 0, ST, gn_sums, BG, n, eps, mean, rstd);
     VNB_LAUNCH_CHECK("gn_finalize");
     return VNB_OK;
 }

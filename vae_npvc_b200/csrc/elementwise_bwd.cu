@@ -43,6 +43,7 @@ __global__ void __launch_bounds__(256) bwd_rows_kernel(const float* __restrict__
                                                        const float* __restrict__ mean, const float* __restrict__ rstd,
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                                        int Cn, int T, int groups, float* __restrict__ R) {
+    pdl_wait();
     __shared__ float red[3][8][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int b = blockIdx.y, c = blockIdx.x * 32 + tx;
@@ -105,6 +106,7 @@ __global__ void __launch_bounds__(512) gn_bwd_finalize_kernel(const float* __res
                                                               float* __restrict__ S, float* __restrict__ dpre_bsum,
                                                               float* __restrict__ dpre_csum, float* __restrict__ dbeta2,
                                                               float* __restrict__ dpre_csum2) {
+    pdl_wait();
     extern __shared__ float fin_smem[];
     float* Ss = fin_smem;                              // [B][groups][2]
     float (*red)[16][33] = reinterpret_cast<float (*)[16][33]>(fin_smem + ((B * groups * 2 + 3) & ~3));
@@ -179,6 +181,7 @@ __global__ void gn_bwd_apply_kernel(const float* __restrict__ dn, const float* _
                                     const float* __restrict__ gamma, const float* __restrict__ S, int64_t rows, int C,
                                     int T, int groups, int Cp, int P, bf16* __restrict__ dpre_planes,
                                     bf16* __restrict__ dn_planes) {
+    pdl_wait();
     const int Cv = C / VEC;
     const int64_t n = rows * Cv, plane = rows * Cp;
     const int cg = C / groups;
@@ -212,6 +215,7 @@ __global__ void gate_bwd_apply_kernel(const float* __restrict__ dg, const float*
                                       const float* __restrict__ gamma, const float* __restrict__ beta,
                                       const float* __restrict__ S, int64_t rows, int C, int T, int Cp, int P,
                                       bf16* __restrict__ da_planes) {
+    pdl_wait();
     const int Cv = C / VEC;
     const int64_t n = rows * Cv, plane = rows * Cp;
     const float inv_n = 1.f / ((float)C * (float)T);
@@ -246,6 +250,7 @@ __global__ void gate_bwd_apply_kernel(const float* __restrict__ dg, const float*
 __global__ void act_bwd_add_kernel(const float* __restrict__ du, const float* __restrict__ c,
                                    const float* __restrict__ add, int64_t n, int act, float scale,
                                    float* __restrict__ out) {
+    pdl_wait();
     GRID_STRIDE(i, n) {
         float v = scale * du[i] * act_grad(c[i] * scale, act);
         if (add) v += add[i];
@@ -257,6 +262,7 @@ __global__ void act_bwd_add_kernel(const float* __restrict__ du, const float* __
 // the host wrapper.  (One 1024-thread block per 32 channels used 16 SMs and took 11 us for 4 MB.)
 __global__ void __launch_bounds__(256) channel_sum_kernel(const float* __restrict__ x, int64_t rows, int C,
                                                           float* __restrict__ out) {
+    pdl_wait();
     __shared__ float red[8][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + tx;
@@ -290,7 +296,7 @@ extern "C" int vnb_gn_bwd_rows(const float* dn, const float* h, const float* mea
                                int T, int groups, float* R, void* stream) {
     VNB_REQUIRE(dn && h && mean && rstd && R && B > 0 && B <= 65535 && C > 0 && T > 0 && groups > 0 && C % groups == 0,
                 "gn_bwd_rows: bad arguments");
-    bwd_rows_kernel<false><<<dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream>>>(dn, h, mean, rstd, nullptr, nullptr,
+    vnb::launch_k(bwd_rows_kernel<false>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dn, h, mean, rstd, nullptr, nullptr,
                                                                                        C, T, groups, R);
     VNB_LAUNCH_CHECK("gn_bwd_rows");
     return VNB_OK;
@@ -304,6 +310,7 @@ __global__ void __launch_bounds__(256) gate_bwd_rows_kernel(const float* __restr
                                                             const float* __restrict__ mean, const float* __restrict__ rstd,
                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
                                                             int C, int T, float* __restrict__ R) {
+    pdl_wait();
     __shared__ float red[6][8][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int b = blockIdx.y, c = blockIdx.x * 32 + tx;
@@ -350,7 +357,7 @@ extern "C" int vnb_gate_bwd_rows(const float* dg, const float* a, const float* m
                                  const float* gamma, const float* beta, int B, int C, int T, float* R, void* stream) {
     VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && R && B > 0 && B <= 65535 && C > 0 && T > 0,
                 "gate_bwd_rows: bad arguments");
-    gate_bwd_rows_kernel<<<dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream>>>(dg, a, mean, rstd, gamma, beta, C, T, R);
+    vnb::launch_k(gate_bwd_rows_kernel, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R);
     VNB_LAUNCH_CHECK("gate_bwd_rows");
     return VNB_OK;
 }
@@ -362,7 +369,7 @@ extern "C" int vnb_gn_bwd_finalize(const float* R, const float* gamma, const flo
     cudaStream_t st = (cudaStream_t)stream;
     const size_t smem = ((size_t)((B * groups * 2 + 3) & ~3) + 3 * 16 * 33) * sizeof(float);
     VNB_REQUIRE(smem <= 48 * 1024, "gn_bwd_finalize: B*groups = %d too large", B * groups);
-    gn_bwd_finalize_kernel<<<ceil_div(C, 32), 512, smem, st>>>(R, gamma, rstd, B, C, T, groups, dgamma, dbeta, S, dpre_bsum,
+    vnb::launch_k(gn_bwd_finalize_kernel, ceil_div(C, 32), 512, smem, st, R, gamma, rstd, B, C, T, groups, dgamma, dbeta, S, dpre_bsum,
                                                              dpre_csum, dbeta2, dpre_csum2);
     VNB_LAUNCH_CHECK("gn_bwd_finalize");
     return VNB_OK;
@@ -371,9 +378,9 @@ extern "C" int vnb_gn_bwd_finalize(const float* R, const float* gamma, const flo
 #define VEC_DISPATCH(cond4, KERNEL, n_scalar, st, ...)                                        \
     do {                                                                                      \
         if (cond4)                                                                            \
-            KERNEL<4><<<ew_grid((n_scalar) / 4), EW_THREADS, 0, st>>>(__VA_ARGS__);           \
+            vnb::launch_k(KERNEL<4>, ew_grid((n_scalar) / 4), EW_THREADS, 0, st, __VA_ARGS__);           \
         else                                                                                  \
-            KERNEL<1><<<ew_grid(n_scalar), EW_THREADS, 0, st>>>(__VA_ARGS__);                 \
+            vnb::launch_k(KERNEL<1>, ew_grid(n_scalar), EW_THREADS, 0, st, __VA_ARGS__);                 \
     } while (0)
 
 extern "C" int vnb_gn_bwd_apply(const float* dn, const float* h, const float* mean, const float* rstd,
@@ -403,7 +410,7 @@ extern "C" int vnb_gate_bwd_apply(const float* dg, const float* a, const float* 
 extern "C" int vnb_act_bwd_add(const float* du, const float* c, const float* add, int64_t n, int act, float scale,
                                float* out, void* stream) {
     VNB_REQUIRE(du && c && out && n > 0, "act_bwd_add: bad arguments");
-    act_bwd_add_kernel<<<ew_grid(n), EW_THREADS, 0, (cudaStream_t)stream>>>(du, c, add, n, act, scale, out);
+    vnb::launch_k(act_bwd_add_kernel, ew_grid(n), EW_THREADS, 0, (cudaStream_t)stream, du, c, add, n, act, scale, out);
     VNB_LAUNCH_CHECK("act_bwd_add");
     return VNB_OK;
 }
@@ -417,7 +424,7 @@ extern "C" int vnb_channel_sum(const float* x, int B, int C, int T, float* out, 
         set_error("channel_sum: memset failed");
         return VNB_E_CUDA;
     }
-    channel_sum_kernel<<<dim3(ceil_div(C, 32), slices), 256, 0, (cudaStream_t)stream>>>(x, rows, C, out);
+    vnb::launch_k(channel_sum_kernel, dim3(ceil_div(C, 32), slices), 256, 0, (cudaStream_t)stream, x, rows, C, out);
     VNB_LAUNCH_CHECK("channel_sum");
     return VNB_OK;
 }

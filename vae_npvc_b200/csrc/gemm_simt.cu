@@ -15,6 +15,7 @@ __global__ void __launch_bounds__(256) conv_fwd_simt_kernel(
     const bf16* __restrict__ in, int B, int Cin, int T, const bf16* __restrict__ w, int taps, int dil, int Cout,
     int Cin_p, const float* __restrict__ bias, int bias_bstride, const float* __restrict__ residual,
     float* __restrict__ out, int accumulate, double* __restrict__ gn_sums, int gn_groups) {
+    pdl_wait();
     __shared__ float Xs[KC][TM + 4];
     __shared__ float Ws[KC][TN + 4];
     const int t0 = blockIdx.x * TM, co0 = blockIdx.y * TN, b = blockIdx.z;
@@ -91,6 +92,7 @@ template <int P>
 __global__ void __launch_bounds__(256) conv_wgrad_simt_kernel(
     const bf16* __restrict__ dy, const bf16* __restrict__ u, int B, int Cout, int Cin, int T, int taps, int dil,
     int transposed, float* __restrict__ dw) {
+    pdl_wait();
     __shared__ float As[KC][TM + 4];
     __shared__ float Bs[KC][TN + 4];
     const int ci0 = blockIdx.x * TN, co0 = blockIdx.y * TM, tap = blockIdx.z;
@@ -161,6 +163,7 @@ __global__ void __launch_bounds__(256) vq_lookup_simt_kernel(const float* __rest
                                                              const float* __restrict__ e_hat,
                                                              const float* __restrict__ e_sq, int64_t N, int D,
                                                              int K, int64_t* __restrict__ idx) {
+    pdl_wait();
     extern __shared__ float sm[];
     float* zs = sm;                                   // [VQ_FR][D]
     float* bd = sm + VQ_FR * D;                       // [VQ_FR][256] best distance
@@ -239,10 +242,10 @@ int conv_fwd_simt(const void* in, int P, int B, int Cin, int T, const void* w, i
     dim3 grid(ceil_div(T, TM), ceil_div(Cout, TN), B);
     const int Cin_p = round_up8(Cin);
     if (P == 1)
-        conv_fwd_simt_kernel<1><<<grid, 256, 0, st>>>((const bf16*)in, B, Cin, T, (const bf16*)w, taps, dil, Cout, Cin_p,
+        vnb::launch_k(conv_fwd_simt_kernel<1>, grid, 256, 0, st, (const bf16*)in, B, Cin, T, (const bf16*)w, taps, dil, Cout, Cin_p,
                                                       bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups);
     else
-        conv_fwd_simt_kernel<3><<<grid, 256, 0, st>>>((const bf16*)in, B, Cin, T, (const bf16*)w, taps, dil, Cout, Cin_p,
+        vnb::launch_k(conv_fwd_simt_kernel<3>, grid, 256, 0, st, (const bf16*)in, B, Cin, T, (const bf16*)w, taps, dil, Cout, Cin_p,
                                                       bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups);
     VNB_LAUNCH_CHECK("conv_fwd_simt");
     return VNB_OK;
@@ -252,10 +255,10 @@ int conv_wgrad_simt(const void* dy, const void* u, int P, int B, int Cout, int C
                     int transposed, float* dw, cudaStream_t st) {
     dim3 grid(ceil_div(Cin, TN), ceil_div(Cout, TM), taps);
     if (P == 1)
-        conv_wgrad_simt_kernel<1><<<grid, 256, 0, st>>>((const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, taps, dil,
+        vnb::launch_k(conv_wgrad_simt_kernel<1>, grid, 256, 0, st, (const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, taps, dil,
                                                         transposed, dw);
     else
-        conv_wgrad_simt_kernel<3><<<grid, 256, 0, st>>>((const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, taps, dil,
+        vnb::launch_k(conv_wgrad_simt_kernel<3>, grid, 256, 0, st, (const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, taps, dil,
                                                         transposed, dw);
     VNB_LAUNCH_CHECK("conv_wgrad_simt");
     return VNB_OK;
@@ -272,7 +275,7 @@ int vq_lookup_simt(const float* zn, const float* z_sq, const float* e_hat, const
             return VNB_E_CUDA;
         }
     }
-    vq_lookup_simt_kernel<<<ceil_div(N, VQ_FR), 256, smem, st>>>(zn, z_sq, e_hat, e_sq, N, D, K, idx);
+    vnb::launch_k(vq_lookup_simt_kernel, ceil_div(N, VQ_FR), 256, smem, st, zn, z_sq, e_hat, e_sq, N, D, K, idx);
     VNB_LAUNCH_CHECK("vq_lookup_simt");
     return VNB_OK;
 }

@@ -8,6 +8,7 @@ namespace vnb {
 
 __global__ void embed_fwd_kernel(const float* __restrict__ table, const int64_t* __restrict__ idx, int n, int dim,
                                  float* __restrict__ out) {
+    pdl_wait();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n * dim) return;
     const int r = i / dim, d = i - r * dim;
@@ -17,6 +18,7 @@ __global__ void embed_fwd_kernel(const float* __restrict__ table, const int64_t*
 // deterministic scatter-add: thread per column, sequential over the (few) rows
 __global__ void embed_bwd_kernel(const float* __restrict__ dout, const int64_t* __restrict__ idx, int n, int dim,
                                  float* __restrict__ dtable) {
+    pdl_wait();
     const int d = blockIdx.x * blockDim.x + threadIdx.x;
     if (d >= dim) return;
     for (int r = 0; r < n; r++) dtable[idx[r] * dim + d] += dout[r * dim + d];
@@ -27,6 +29,7 @@ __global__ void __launch_bounds__(256) linear_fwd_kernel(const float* __restrict
                                                          const float* __restrict__ bias,
                                                          const float* __restrict__ bias2, int B, int I, int O,
                                                          float* __restrict__ p) {
+    pdl_wait();
     const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (w >= (int64_t)B * O) return;
     const int lane = threadIdx.x & 31;
@@ -39,6 +42,7 @@ __global__ void __launch_bounds__(256) linear_fwd_kernel(const float* __restrict
 
 __global__ void linear_bwd_w_kernel(const float* __restrict__ dp, const float* __restrict__ y, int B, int I, int O,
                                     float* __restrict__ dW) {
+    pdl_wait();
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= (int64_t)O * I) return;
     const int o = (int)(e / I), i = (int)(e - (int64_t)o * I);
@@ -54,6 +58,7 @@ __global__ void linear_bwd_w_kernel(const float* __restrict__ dp, const float* _
 // walked O/8 = 128 dependent L2 round trips: 24 us for a 0.5 MB matrix).
 __global__ void __launch_bounds__(256) linear_bwd_y_kernel(const float* __restrict__ dp, const float* __restrict__ W,
                                                            int B, int I, int O, float* __restrict__ dy) {
+    pdl_wait();
     __shared__ float dps[16][64];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int i = blockIdx.x * 32 + tx, o0 = blockIdx.y * 64, b0 = blockIdx.z * 16;
@@ -93,6 +98,7 @@ constexpr float LOG_2PI_F = 1.8378770664093453f;
 
 __global__ void __launch_bounds__(256) logloss_fwd_kernel(const float* __restrict__ xhat, const float* __restrict__ x,
                                                           int64_t n, float scale, float* __restrict__ acc) {
+    pdl_wait();
     __shared__ float red[32];
     float s = 0.f;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -105,12 +111,14 @@ __global__ void __launch_bounds__(256) logloss_fwd_kernel(const float* __restric
 
 __global__ void logloss_bwd_kernel(const float* __restrict__ xhat, const float* __restrict__ x,
                                    const float* __restrict__ g, int64_t n, float scale, float* __restrict__ dxhat) {
+    pdl_wait();
     const float gs = (g ? g[0] : 1.f) * scale;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
         dxhat[i] = gs * (xhat[i] - x[i]);
 }
 
 __global__ void __launch_bounds__(256) sqnorm_kernel(const float* __restrict__ g, int64_t n, float* __restrict__ acc) {
+    pdl_wait();
     __shared__ float red[32];
     float s = 0.f;
     const int64_t n4 = n >> 2;
@@ -130,6 +138,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
                                                    const float* __restrict__ sqn, float max_norm, float lr,
                                                    double beta1d, double beta2d, float eps,
                                                    const float* __restrict__ state, int step_size, float gamma) {
+    pdl_wait();
     __shared__ float sh[3];
     // like torch.optim.Adam: 1 - beta is formed in double, then used in fp32 arithmetic
     const float beta1 = (float)beta1d, beta2 = (float)beta2d;
@@ -182,6 +191,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
 }
 
 __global__ void adam_tick_kernel(float* state) {
+    pdl_wait();
     state[0] += 1.f;
     state[1] += 1.f;
 }
@@ -197,14 +207,14 @@ using namespace vnb;
 
 extern "C" int vnb_embed_fwd(const float* table, const int64_t* idx, int n, int dim, float* out, void* stream) {
     VNB_REQUIRE(table && idx && out && n > 0 && dim > 0, "embed_fwd: bad arguments");
-    embed_fwd_kernel<<<ceil_div((int64_t)n * dim, 256), 256, 0, (cudaStream_t)stream>>>(table, idx, n, dim, out);
+    vnb::launch_k(embed_fwd_kernel, ceil_div((int64_t)n * dim, 256), 256, 0, (cudaStream_t)stream, table, idx, n, dim, out);
     VNB_LAUNCH_CHECK("embed_fwd");
     return VNB_OK;
 }
 
 extern "C" int vnb_embed_bwd(const float* dout, const int64_t* idx, int n, int dim, float* dtable, void* stream) {
     VNB_REQUIRE(dout && idx && dtable && n > 0 && dim > 0, "embed_bwd: bad arguments");
-    embed_bwd_kernel<<<ceil_div(dim, 128), 128, 0, (cudaStream_t)stream>>>(dout, idx, n, dim, dtable);
+    vnb::launch_k(embed_bwd_kernel, ceil_div(dim, 128), 128, 0, (cudaStream_t)stream, dout, idx, n, dim, dtable);
     VNB_LAUNCH_CHECK("embed_bwd");
     return VNB_OK;
 }
@@ -212,7 +222,7 @@ extern "C" int vnb_embed_bwd(const float* dout, const int64_t* idx, int n, int d
 extern "C" int vnb_linear_fwd(const float* y, const float* W, const float* bias, const float* bias2, int B, int I,
                               int O, float* p, void* stream) {
     VNB_REQUIRE(y && W && p && B > 0 && I > 0 && O > 0, "linear_fwd: bad arguments");
-    linear_fwd_kernel<<<ceil_div((int64_t)B * O, 8), 256, 0, (cudaStream_t)stream>>>(y, W, bias, bias2, B, I, O, p);
+    vnb::launch_k(linear_fwd_kernel, ceil_div((int64_t)B * O, 8), 256, 0, (cudaStream_t)stream, y, W, bias, bias2, B, I, O, p);
     VNB_LAUNCH_CHECK("linear_fwd");
     return VNB_OK;
 }
@@ -222,7 +232,7 @@ extern "C" int vnb_linear_bwd(const float* dp, const float* y, const float* W, i
     VNB_REQUIRE(dp && y && W && B > 0 && I > 0 && O > 0, "linear_bwd: bad arguments");
     cudaStream_t st = (cudaStream_t)stream;
     if (dW) {
-        linear_bwd_w_kernel<<<ceil_div((int64_t)O * I, 256), 256, 0, st>>>(dp, y, B, I, O, dW);
+        vnb::launch_k(linear_bwd_w_kernel, ceil_div((int64_t)O * I, 256), 256, 0, st, dp, y, B, I, O, dW);
         VNB_LAUNCH_CHECK("linear_bwd_w");
     }
     if (dy) {
@@ -230,7 +240,7 @@ extern "C" int vnb_linear_bwd(const float* dp, const float* y, const float* W, i
             set_error("linear_bwd: memset failed");
             return VNB_E_CUDA;
         }
-        linear_bwd_y_kernel<<<dim3(ceil_div(I, 32), ceil_div(O, 64), ceil_div(B, 16)), 256, 0, st>>>(dp, W, B, I, O, dy);
+        vnb::launch_k(linear_bwd_y_kernel, dim3(ceil_div(I, 32), ceil_div(O, 64), ceil_div(B, 16)), 256, 0, st, dp, W, B, I, O, dy);
         VNB_LAUNCH_CHECK("linear_bwd_y");
     }
     return VNB_OK;
@@ -238,7 +248,7 @@ extern "C" int vnb_linear_bwd(const float* dp, const float* y, const float* W, i
 
 extern "C" int vnb_logloss_fwd(const float* xhat, const float* x, int64_t n, float scale, float* acc, void* stream) {
     VNB_REQUIRE(xhat && x && acc && n > 0, "logloss_fwd: bad arguments");
-    logloss_fwd_kernel<<<flat_grid(n), 256, 0, (cudaStream_t)stream>>>(xhat, x, n, scale, acc);
+    vnb::launch_k(logloss_fwd_kernel, flat_grid(n), 256, 0, (cudaStream_t)stream, xhat, x, n, scale, acc);
     VNB_LAUNCH_CHECK("logloss_fwd");
     return VNB_OK;
 }
@@ -246,14 +256,14 @@ extern "C" int vnb_logloss_fwd(const float* xhat, const float* x, int64_t n, flo
 extern "C" int vnb_logloss_bwd(const float* xhat, const float* x, const float* g, int64_t n, float scale, float* dxhat,
                                void* stream) {
     VNB_REQUIRE(xhat && x && dxhat && n > 0, "logloss_bwd: bad arguments");
-    logloss_bwd_kernel<<<flat_grid(n), 256, 0, (cudaStream_t)stream>>>(xhat, x, g, n, scale, dxhat);
+    vnb::launch_k(logloss_bwd_kernel, flat_grid(n), 256, 0, (cudaStream_t)stream, xhat, x, g, n, scale, dxhat);
     VNB_LAUNCH_CHECK("logloss_bwd");
     return VNB_OK;
 }
 
 extern "C" int vnb_sqnorm(const float* g, int64_t n, float* acc, void* stream) {
     VNB_REQUIRE(g && acc && n > 0 && ((uintptr_t)g & 15) == 0, "sqnorm: bad arguments (g must be 16-byte aligned)");
-    sqnorm_kernel<<<flat_grid(n), 256, 0, (cudaStream_t)stream>>>(g, n, acc);
+    vnb::launch_k(sqnorm_kernel, flat_grid(n), 256, 0, (cudaStream_t)stream, g, n, acc);
     VNB_LAUNCH_CHECK("sqnorm");
     return VNB_OK;
 }
@@ -264,9 +274,9 @@ extern "C" int vnb_adam_step(float* p, const float* g, float* m, float* v, int64
     VNB_REQUIRE(p && g && m && v && state && n > 0, "adam_step: bad arguments");
     VNB_REQUIRE((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0, "adam_step: buffers must be 16-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
-    adam_kernel<<<flat_grid(n), 256, 0, st>>>(p, g, m, v, n, sqn, max_norm, lr, beta1, beta2, eps, state, step_size, gamma);
+    vnb::launch_k(adam_kernel, flat_grid(n), 256, 0, st, p, g, m, v, n, sqn, max_norm, lr, beta1, beta2, eps, state, step_size, gamma);
     VNB_LAUNCH_CHECK("adam_step");
-    adam_tick_kernel<<<1, 1, 0, st>>>(state);
+    vnb::launch_k(adam_tick_kernel, 1, 1, 0, st, state);
     VNB_LAUNCH_CHECK("adam_tick");
     return VNB_OK;
 }

@@ -1,5 +1,6 @@
 // Error string, launch counter and backend switch of the C ABI.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <atomic>
 
@@ -19,6 +20,10 @@ void set_error(const char* fmt, ...) {
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 int backend() { return g_backend.load(std::memory_order_relaxed); }
+bool pdl_enabled() {
+    static const bool on = !(getenv("VNB_PDL") && atoi(getenv("VNB_PDL")) == 0);
+    return on;
+}
 
 }  // namespace vnb
 

@@ -68,6 +68,7 @@ vq_lookup_tc_stream_kernel(const __grid_constant__ CUtensorMap map_z, const __gr
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
+    pdl_wait();      // everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel's tail
 
     if (warp == 0) {
         if (lane == 0) {
@@ -178,7 +179,7 @@ static int vq_lookup_tc_stream(const void* z_planes, const float* z_sq, const vo
     if (!make_tmap_3d(&me, e_planes, (uint64_t)D, (uint64_t)K, 3, (uint64_t)Dp * 2, (uint64_t)K * Dp * 2, VQT_BK, VQT_BN, 1))
         return VNB_E_CUDA;
     VqTcArgs a{N, D, K, z_sq, e_sq, idx};
-    vq_lookup_tc_stream_kernel<<<ceil_div(N, VQT_BM), VQT_THREADS, smem, st>>>(mz, me, a);
+    vnb::launch_k(vq_lookup_tc_stream_kernel, ceil_div(N, VQT_BM), VQT_THREADS, smem, st, mz, me, a);
     VNB_LAUNCH_CHECK("vq_lookup_tc");
     return VNB_OK;
 }
@@ -244,6 +245,7 @@ vq_lookup_tc_kernel(const __grid_constant__ CUtensorMap map_z, const __grid_cons
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
+    pdl_wait();      // everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel's tail
 
     if (warp == 0) {
         if (lane == 0) {
@@ -386,7 +388,7 @@ int vq_lookup_tc(const void* z_planes, const float* z_sq, const void* e_planes, 
     if (!make_tmap_3d(&me, e_planes, (uint64_t)D, (uint64_t)K, 3, (uint64_t)Dp * 2, (uint64_t)K * Dp * 2, VQT_BK, VQR_BN, 1))
         return VNB_E_CUDA;
     VqResArgs a{N, D, K, nst, z_sq, e_sq, idx};
-    vq_lookup_tc_kernel<<<ceil_div(N, VQT_BM), VQT_THREADS, smem, st>>>(mz, me, a);
+    vnb::launch_k(vq_lookup_tc_kernel, ceil_div(N, VQT_BM), VQT_THREADS, smem, st, mz, me, a);
     VNB_LAUNCH_CHECK("vq_lookup_tc");
     return VNB_OK;
 }

@@ -112,6 +112,7 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
+    pdl_wait();      // everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel's tail
 
     if (warp == 0) {
         if (lane == 0 && nk > 0) {
@@ -302,13 +303,15 @@ static int launch_wgrad_tc(const void* rows_pl, const void* cols_pl, int ksplit,
     cfg.blockDim = dim3(WG_THREADS);
     cfg.dynamicSmemBytes = (size_t)a.recv_off + Cfg::recv_bytes(ksplit) + 1024;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = ksplit;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, conv_wgrad_tc_kernel<BN>, ma, mb, a);
     if (e != cudaSuccess) {
         set_error("conv_wgrad_tc: launch failed (BN %d, cluster %d): %s", BN, ksplit, cudaGetErrorString(e));

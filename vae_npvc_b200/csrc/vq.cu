@@ -11,6 +11,7 @@ __global__ void __launch_bounds__(128) vq_prep_codebook_kernel(float* __restrict
                                                                int inplace_renorm, float* __restrict__ e_hat,
                                                                bf16* __restrict__ e_planes,
                                                                float* __restrict__ e_sq) {
+    pdl_wait();
     __shared__ float red[32];
     const int k = blockIdx.x;
     float* row = E + (int64_t)k * D;
@@ -51,6 +52,7 @@ __global__ void __launch_bounds__(VQ_WARPS * 32) vq_prep_z_kernel(const float* _
                                                                   int normalize, float* __restrict__ zn,
                                                                   bf16* __restrict__ z_planes, float* __restrict__ z_sq,
                                                                   float* __restrict__ z_norm) {
+    pdl_wait();
     const int64_t n = (int64_t)blockIdx.x * VQ_WARPS + (threadIdx.x >> 5);
     if (n >= N) return;
     const int lane = threadIdx.x & 31;
@@ -81,6 +83,7 @@ __global__ void __launch_bounds__(VQ_WARPS * 32) vq_gather_kernel(const int64_t*
                                                                   const float* __restrict__ z, int64_t N, int D,
                                                                   float* __restrict__ q_out, float* __restrict__ sums,
                                                                   int* __restrict__ counts) {
+    pdl_wait();
     __shared__ float red[32];
     const int64_t n = (int64_t)blockIdx.x * VQ_WARPS + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
@@ -108,6 +111,7 @@ __global__ void __launch_bounds__(VQ_WARPS * 32) vq_gather_kernel(const int64_t*
 __global__ void __launch_bounds__(256) vq_finalize_kernel(const float* __restrict__ sums, const int* __restrict__ counts,
                                                           int K, float N, float scale, int normalize, float eps,
                                                           float* __restrict__ scal) {
+    pdl_wait();
     __shared__ float red[32];
     float h = 0.f;
     for (int k = threadIdx.x; k < K; k += blockDim.x) {
@@ -132,6 +136,7 @@ __global__ void __launch_bounds__(VQ_WARPS * 32) vq_bwd_kernel(const float* __re
                                                                const float* __restrict__ e_hat, int64_t N, int D,
                                                                float scale, int normalize, float* __restrict__ dz,
                                                                float* __restrict__ dE_hat) {
+    pdl_wait();
     const int64_t n = (int64_t)blockIdx.x * VQ_WARPS + (threadIdx.x >> 5);
     if (n >= N) return;
     const int lane = threadIdx.x & 31;
@@ -170,6 +175,7 @@ __global__ void __launch_bounds__(VQ_WARPS * 32) vq_bwd_kernel(const float* __re
 __global__ void __launch_bounds__(128) vq_bwd_codebook_kernel(const float* __restrict__ dE_hat,
                                                               const float* __restrict__ E, int D, int normalize,
                                                               float* __restrict__ dE) {
+    pdl_wait();
     __shared__ float red[32];
     const int k = blockIdx.x;
     const float* e = E + (int64_t)k * D;
@@ -195,6 +201,7 @@ __global__ void __launch_bounds__(VQ_WARPS * 32) vq_ema_scatter_kernel(const int
                                                                        const float* __restrict__ z, int64_t N, int D,
                                                                        float* __restrict__ zsum,
                                                                        int* __restrict__ counts) {
+    pdl_wait();
     const int64_t n = (int64_t)blockIdx.x * VQ_WARPS + (threadIdx.x >> 5);
     if (n >= N) return;
     const int lane = threadIdx.x & 31;
@@ -211,6 +218,7 @@ __global__ void __launch_bounds__(512) vq_ema_update_kernel(const float* __restr
                                                             float* __restrict__ emb_sum, float* __restrict__ emb_elem,
                                                             float* __restrict__ embeddings,
                                                             float* __restrict__ stats) {
+    pdl_wait();
     __shared__ float red[32];
     float ent = 0.f, used = 0.f, alive_n = 0.f, diff = 0.f;
     for (int k = threadIdx.x; k < K; k += blockDim.x) {
@@ -247,6 +255,7 @@ __global__ void __launch_bounds__(512) vq_ema_update_kernel(const float* __restr
 
 __global__ void vq_frame_rows_kernel(const float* __restrict__ z, const int64_t* __restrict__ perm, int64_t N, int D,
                                      int K, float* __restrict__ out) {
+    pdl_wait();
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (int64_t)K * D) return;
     const int k = (int)(i / D), d = (int)(i - (int64_t)k * D);
@@ -256,6 +265,7 @@ __global__ void vq_frame_rows_kernel(const float* __restrict__ z, const int64_t*
 // channels-last (B, T, D): out[b,t,:] = in[b,src[t],:]  (backward: zero the rows with src[t] != t)
 __global__ void jitter_kernel(const float* __restrict__ in, const int64_t* __restrict__ src, int64_t n, int D, int T,
                               int backward, float* __restrict__ out) {
+    pdl_wait();
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int64_t r = i / D;
@@ -272,7 +282,7 @@ using namespace vnb;
 extern "C" int vnb_vq_prep_codebook(float* E, int K, int D, int normalize, int inplace_renorm, float* e_hat,
                                     void* e_planes, float* e_sq, void* stream) {
     VNB_REQUIRE(E && K > 0 && D > 0, "vq_prep_codebook: bad arguments");
-    vq_prep_codebook_kernel<<<K, 128, 0, (cudaStream_t)stream>>>(E, K, D, normalize, inplace_renorm, e_hat,
+    vnb::launch_k(vq_prep_codebook_kernel, K, 128, 0, (cudaStream_t)stream, E, K, D, normalize, inplace_renorm, e_hat,
                                                                  (bf16*)e_planes, e_sq);
     VNB_LAUNCH_CHECK("vq_prep_codebook");
     return VNB_OK;
@@ -282,7 +292,7 @@ extern "C" int vnb_vq_prep_z(const float* z, int B, int D, int T, int normalize,
                              float* z_sq, float* z_norm, void* stream) {
     VNB_REQUIRE(z && B > 0 && D > 0 && T > 0, "vq_prep_z: bad arguments");
     const int64_t N = (int64_t)B * T;
-    vq_prep_z_kernel<<<ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream>>>(z, N, D, round_up8(D), normalize,
+    vnb::launch_k(vq_prep_z_kernel, ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream, z, N, D, round_up8(D), normalize,
                                                                                         zn, (bf16*)z_planes, z_sq, z_norm);
     VNB_LAUNCH_CHECK("vq_prep_z");
     return VNB_OK;
@@ -292,7 +302,7 @@ extern "C" int vnb_vq_gather(const int64_t* idx, const float* e_hat, const float
                              int T, int K, float* q_out, float* sums, int* counts, void* stream) {
     VNB_REQUIRE(idx && e_hat && zn && B > 0 && D > 0 && T > 0 && K > 0, "vq_gather: bad arguments");
     const int64_t N = (int64_t)B * T;
-    vq_gather_kernel<<<ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream>>>(idx, e_hat, zn, z, N, D, q_out,
+    vnb::launch_k(vq_gather_kernel, ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream, idx, e_hat, zn, z, N, D, q_out,
                                                                                         sums, counts);
     VNB_LAUNCH_CHECK("vq_gather");
     return VNB_OK;
@@ -301,7 +311,7 @@ extern "C" int vnb_vq_gather(const int64_t* idx, const float* e_hat, const float
 extern "C" int vnb_vq_finalize(const float* sums, const int* counts, int K, int64_t N, float scale, int normalize,
                                float eps, float* scal, void* stream) {
     VNB_REQUIRE(sums && counts && scal && K > 0 && N > 0, "vq_finalize: bad arguments");
-    vq_finalize_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(sums, counts, K, (float)N, scale, normalize, eps, scal);
+    vnb::launch_k(vq_finalize_kernel, 1, 256, 0, (cudaStream_t)stream, sums, counts, K, (float)N, scale, normalize, eps, scal);
     VNB_LAUNCH_CHECK("vq_finalize");
     return VNB_OK;
 }
@@ -314,7 +324,7 @@ extern "C" int vnb_vq_bwd(const float* g_out, const float* g_lq, const float* g_
     VNB_REQUIRE(idx && zn && e_hat && dz && B > 0 && D > 0 && T > 0, "vq_bwd: bad arguments");
     VNB_REQUIRE(!normalize || (z && z_norm), "vq_bwd: normalised mode needs z and z_norm");
     const int64_t N = (int64_t)B * T;
-    vq_bwd_kernel<<<ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream>>>(
+    vnb::launch_k(vq_bwd_kernel, ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream, 
         g_out, g_lq, g_le, idx, z, zn, z_norm, e_hat, N, D, scale, normalize, dz, dE_hat);
     VNB_LAUNCH_CHECK("vq_bwd");
     return VNB_OK;
@@ -323,7 +333,7 @@ extern "C" int vnb_vq_bwd(const float* g_out, const float* g_lq, const float* g_
 extern "C" int vnb_vq_bwd_codebook(const float* dE_hat, const float* E, int K, int D, int normalize, float* dE,
                                    void* stream) {
     VNB_REQUIRE(dE_hat && E && dE && K > 0 && D > 0, "vq_bwd_codebook: bad arguments");
-    vq_bwd_codebook_kernel<<<K, 128, 0, (cudaStream_t)stream>>>(dE_hat, E, D, normalize, dE);
+    vnb::launch_k(vq_bwd_codebook_kernel, K, 128, 0, (cudaStream_t)stream, dE_hat, E, D, normalize, dE);
     VNB_LAUNCH_CHECK("vq_bwd_codebook");
     return VNB_OK;
 }
@@ -333,7 +343,7 @@ extern "C" int vnb_vq_ema_scatter(const int64_t* idx, const float* z, int B, int
     (void)K;
     VNB_REQUIRE(idx && z && zsum && counts && B > 0 && D > 0 && T > 0, "vq_ema_scatter: bad arguments");
     const int64_t N = (int64_t)B * T;
-    vq_ema_scatter_kernel<<<ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream>>>(idx, z, N, D, zsum, counts);
+    vnb::launch_k(vq_ema_scatter_kernel, ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream, idx, z, N, D, zsum, counts);
     VNB_LAUNCH_CHECK("vq_ema_scatter");
     return VNB_OK;
 }
@@ -343,7 +353,7 @@ extern "C" int vnb_vq_ema_update(const float* zsum, const int* counts, int K, in
                                  float* embeddings, float* stats, void* stream) {
     VNB_REQUIRE(zsum && counts && rand_rows && emb_sum && emb_elem && embeddings && stats && K > 0 && D > 0 && n_frames > 0,
                 "vq_ema_update: bad arguments");
-    vq_ema_update_kernel<<<1, 512, 0, (cudaStream_t)stream>>>(zsum, counts, rand_rows, K, D, (float)n_frames, mu,
+    vnb::launch_k(vq_ema_update_kernel, 1, 512, 0, (cudaStream_t)stream, zsum, counts, rand_rows, K, D, (float)n_frames, mu,
                                                               threshold, emb_sum, emb_elem, embeddings, stats);
     VNB_LAUNCH_CHECK("vq_ema_update");
     return VNB_OK;
@@ -352,7 +362,7 @@ extern "C" int vnb_vq_ema_update(const float* zsum, const int* counts, int K, in
 extern "C" int vnb_vq_frame_rows(const float* z, const int64_t* perm, int B, int D, int T, int K, float* out,
                                  void* stream) {
     VNB_REQUIRE(z && perm && out && B > 0 && D > 0 && T > 0 && K > 0, "vq_frame_rows: bad arguments");
-    vq_frame_rows_kernel<<<ceil_div((int64_t)K * D, 256), 256, 0, (cudaStream_t)stream>>>(z, perm, (int64_t)B * T, D, K, out);
+    vnb::launch_k(vq_frame_rows_kernel, ceil_div((int64_t)K * D, 256), 256, 0, (cudaStream_t)stream, z, perm, (int64_t)B * T, D, K, out);
     VNB_LAUNCH_CHECK("vq_frame_rows");
     return VNB_OK;
 }
@@ -360,7 +370,7 @@ extern "C" int vnb_vq_frame_rows(const float* z, const int64_t* perm, int B, int
 extern "C" int vnb_jitter_fwd(const float* in, const int64_t* src, int B, int D, int T, float* out, void* stream) {
     VNB_REQUIRE(in && src && out && B > 0 && D > 0 && T > 0, "jitter_fwd: bad arguments");
     const int64_t n = (int64_t)B * D * T;
-    jitter_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(in, src, n, D, T, 0, out);
+    vnb::launch_k(jitter_kernel, ceil_div(n, 256), 256, 0, (cudaStream_t)stream, in, src, n, D, T, 0, out);
     VNB_LAUNCH_CHECK("jitter_fwd");
     return VNB_OK;
 }
@@ -368,7 +378,7 @@ extern "C" int vnb_jitter_fwd(const float* in, const int64_t* src, int B, int D,
 extern "C" int vnb_jitter_bwd(const float* dout, const int64_t* src, int B, int D, int T, float* din, void* stream) {
     VNB_REQUIRE(dout && src && din && B > 0 && D > 0 && T > 0, "jitter_bwd: bad arguments");
     const int64_t n = (int64_t)B * D * T;
-    jitter_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(dout, src, n, D, T, 1, din);
+    vnb::launch_k(jitter_kernel, ceil_div(n, 256), 256, 0, (cudaStream_t)stream, dout, src, n, D, T, 1, din);
     VNB_LAUNCH_CHECK("jitter_bwd");
     return VNB_OK;
 }

@@ -10,6 +10,7 @@ __global__ void __launch_bounds__(256) wn_prepare_kernel(const float* __restrict
                                                          int d0, int d1, int k, int transposed, int P,
                                                          bf16* __restrict__ wf, bf16* __restrict__ wb,
                                                          float* __restrict__ w32) {
+    pdl_wait();
     __shared__ float red[32];
     const int i = blockIdx.x;
     const int n = d1 * k;
@@ -44,6 +45,7 @@ __global__ void __launch_bounds__(256) wn_prepare_kernel(const float* __restrict
 __global__ void __launch_bounds__(256) wn_backward_kernel(const float* __restrict__ dw, const float* __restrict__ v,
                                                           const float* __restrict__ g, int n,
                                                           float* __restrict__ dv, float* __restrict__ dg) {
+    pdl_wait();
     __shared__ float red[32];
     const int i = blockIdx.x;
     const float* vr = v + (int64_t)i * n;
@@ -74,6 +76,7 @@ constexpr int WN_TILE = 64;
 __global__ void __launch_bounds__(256) wn_rowscale_kernel(const float* __restrict__ flat_p, const int64_t* __restrict__ desc,
                                                           const int* __restrict__ row2layer, int total_rows,
                                                           float* __restrict__ scale) {
+    pdl_wait();
     const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (row >= total_rows) return;
     const int64_t* L = desc + (int64_t)row2layer[row] * WN_DESC;
@@ -114,6 +117,7 @@ __device__ __forceinline__ void store_planes2(bf16* base, int64_t off, int64_t p
 __global__ void __launch_bounds__(256) wn_tiles_kernel(const float* __restrict__ flat_p, const int64_t* __restrict__ desc,
                                                        const int* __restrict__ tile2layer, const float* __restrict__ scale,
                                                        int P, bf16* __restrict__ wbuf, float* __restrict__ w32buf) {
+    pdl_wait();
     extern __shared__ float wn_tile[];                // [k][64][65]
     constexpr int TP = WN_TILE + 1;
     const int64_t* L = desc + (int64_t)tile2layer[blockIdx.x] * WN_DESC;
@@ -170,6 +174,7 @@ __global__ void __launch_bounds__(256) wn_backward_batch_kernel(const float* __r
                                                                 float* __restrict__ flat_g,
                                                                 const int64_t* __restrict__ desc,
                                                                 const int* __restrict__ row2layer) {
+    pdl_wait();
     __shared__ float red[32];
     const int64_t* L = desc + (int64_t)row2layer[blockIdx.x] * WN_DESC;
     if (L[1] < 0) return;                       // plain weight: dw already is its gradient
@@ -241,9 +246,9 @@ extern "C" int vnb_wn_prepare_batch(const float* flat_p, const int64_t* desc, co
         smem_set = smem;
     }
     cudaStream_t st = (cudaStream_t)stream;
-    vnb::wn_rowscale_kernel<<<vnb::ceil_div(total_rows, 8), 256, 0, st>>>(flat_p, desc, row2layer, total_rows, row_scale);
+    vnb::launch_k(vnb::wn_rowscale_kernel, vnb::ceil_div(total_rows, 8), 256, 0, st, flat_p, desc, row2layer, total_rows, row_scale);
     VNB_LAUNCH_CHECK("wn_rowscale");
-    vnb::wn_tiles_kernel<<<total_tiles, 256, smem, st>>>(flat_p, desc, tile2layer, row_scale, P, (vnb::bf16*)wbuf, w32buf);
+    vnb::launch_k(vnb::wn_tiles_kernel, total_tiles, 256, smem, st, flat_p, desc, tile2layer, row_scale, P, (vnb::bf16*)wbuf, w32buf);
     VNB_LAUNCH_CHECK("wn_tiles");
     return VNB_OK;
 }
@@ -251,7 +256,7 @@ extern "C" int vnb_wn_prepare_batch(const float* flat_p, const int64_t* desc, co
 extern "C" int vnb_wn_backward_batch(const float* flat_p, float* flat_g, const int64_t* desc, const int* row2layer,
                                      int total_rows, void* stream) {
     VNB_REQUIRE(flat_p && flat_g && desc && row2layer && total_rows > 0, "wn_backward_batch: bad arguments");
-    vnb::wn_backward_batch_kernel<<<total_rows, 256, 0, (cudaStream_t)stream>>>(flat_p, flat_g, desc, row2layer);
+    vnb::launch_k(vnb::wn_backward_batch_kernel, total_rows, 256, 0, (cudaStream_t)stream, flat_p, flat_g, desc, row2layer);
     VNB_LAUNCH_CHECK("wn_backward_batch");
     return VNB_OK;
 }
@@ -259,7 +264,7 @@ extern "C" int vnb_wn_backward_batch(const float* flat_p, float* flat_g, const i
 extern "C" int vnb_wn_prepare(const float* v, const float* g, int d0, int d1, int k, int transposed, int P,
                               void* wf, void* wb, float* w32, void* stream) {
     VNB_REQUIRE(v && d0 > 0 && d1 > 0 && k > 0 && (P == 1 || P == 3), "wn_prepare: bad arguments");
-    vnb::wn_prepare_kernel<<<d0, 256, 0, (cudaStream_t)stream>>>(v, g, d0, d1, k, transposed, P, (vnb::bf16*)wf,
+    vnb::launch_k(vnb::wn_prepare_kernel, d0, 256, 0, (cudaStream_t)stream, v, g, d0, d1, k, transposed, P, (vnb::bf16*)wf,
                                                                 (vnb::bf16*)wb, w32);
     VNB_LAUNCH_CHECK("wn_prepare");
     return VNB_OK;
@@ -268,7 +273,7 @@ extern "C" int vnb_wn_prepare(const float* v, const float* g, int d0, int d1, in
 extern "C" int vnb_wn_backward(const float* dw, const float* v, const float* g, int d0, int d1, int k, float* dv,
                                float* dg, void* stream) {
     VNB_REQUIRE(dw && v && g && dv && dg && d0 > 0, "wn_backward: bad arguments");
-    vnb::wn_backward_kernel<<<d0, 256, 0, (cudaStream_t)stream>>>(dw, v, g, d1 * k, dv, dg);
+    vnb::launch_k(vnb::wn_backward_kernel, d0, 256, 0, (cudaStream_t)stream, dw, v, g, d1 * k, dv, dg);
     VNB_LAUNCH_CHECK("wn_backward");
     return VNB_OK;
 }
