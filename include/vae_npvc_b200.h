@@ -105,12 +105,15 @@ int vnb_conv_wgrad(const void* dy_planes, const void* u_planes, int P, int B, in
 
 /* ---- layout conversion: (B, R, S) contiguous -> (B, S, R) contiguous (reference NCT <-> channels-last) */
 int vnb_transpose(const float* in, int B, int R, int S, float* out, void* stream);
-/* ---- operand planes from fp32 activations: out_id <- x*scale, out_act <- act(x*scale) */
+/* ---- operand planes from fp32 activations: out_id <- x*scale, out_act <- act(x*scale).
+ * csum (optional, C floats ZEROED by the caller): += per-channel sums over all frames of x*scale (the bias
+ * gradient of a conv whose output gradient is x, without a second pass) */
 int vnb_make_planes(const float* x, int B, int C, int T, int P, float scale, int act,
-                    void* out_id, void* out_act, void* stream);
-/* channel-concat [xa (B,Ca,T); xb (B,Cb,T)] -> planes (P,B,T,(Ca+Cb)p) */
+                    void* out_id, void* out_act, float* csum, void* stream);
+/* channel-concat [xa (B,Ca,T); xb (B,Cb,T)] -> planes (P,B,T,(Ca+Cb)p); csum (optional, Ca+Cb floats, zeroed by
+ * the caller): += per-channel sums */
 int vnb_concat_planes(const float* xa, int Ca, const float* xb, int Cb, int B, int T, int P,
-                      void* out, void* stream);
+                      void* out, float* csum, void* stream);
 
 /* ---- nn.GroupNorm statistics (layers.py:154,201): mean,rstd (B,groups), biased var, eps.
  * ws: scratch of vnb_gn_stats_ws_floats(B, groups) floats (chunk-wise mean/M2, merged exactly) */

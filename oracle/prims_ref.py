@@ -199,13 +199,18 @@ def _conv_wgrad(dy_pl, u_pl, taps, dil, transposed):
 
 
 # ---- planes ----------------------------------------------------------------------------------
-def make_planes(x, P, scale=1.0, act=ACT_NONE, want_id=True, want_act=False):
+def make_planes(x, P, scale=1.0, act=ACT_NONE, want_id=True, want_act=False, csum=None):
     v = x.detach() * scale
+    if csum is not None:
+        csum.add_(v.sum(dim=(0, 2)))
     return (Planes.of(v, P) if want_id else None, Planes.of(_act(v, act), P) if want_act else None)
 
 
-def concat_planes(xa, xb, P):
-    return Planes.of(torch.cat([xa, xb], dim=1), P)
+def concat_planes(xa, xb, P, csum=None):
+    cat = torch.cat([xa, xb], dim=1)
+    if csum is not None:
+        csum.add_(cat.detach().sum(dim=(0, 2)))
+    return Planes.of(cat, P)
 
 
 # ---- forward elementwise ---------------------------------------------------------------------

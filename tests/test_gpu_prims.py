@@ -106,6 +106,15 @@ def test_planes(Pm, P):
         assert rel_err(planes_val(cid), x * 0.7) < 1e-7          # hi+mid+lo reproduces fp32
     xb = g(3, 5, 21, seed=2)
     assert torch.equal(Pm.concat_planes(cu(x), cu(xb), P).data.cpu(), R.concat_planes(x, xb, P).data)
+    # fused per-channel sums (bias gradients), vector (C % 4 == 0) and scalar channel counts
+    for C1, C2 in ((7, 5), (8, 12), (512, 128)):
+        xa, xc = g(4, C1, 33, seed=3), g(4, C2, 33, seed=4)
+        cs = torch.zeros(C1, device='cuda')
+        Pm.make_planes(cu(xa), P, 0.5, R.ACT_NONE, True, False, csum=cs)
+        assert rel_err(cs, 0.5 * xa.sum(dim=(0, 2))) < 1e-5
+        cs2 = torch.zeros(C1 + C2, device='cuda')
+        Pm.concat_planes(cu(xa), cu(xc), P, csum=cs2)
+        assert rel_err(cs2, torch.cat([xa, xc], 1).sum(dim=(0, 2))) < 1e-5
 
 
 @pytest.mark.parametrize('B,C,T', [(2, 8, 20), (3, 64, 37), (2, 512, 128)])

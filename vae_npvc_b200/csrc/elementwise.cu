@@ -50,8 +50,14 @@ __global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict_
 // ------------------------------------------------------------------------------------------
 template <int VEC>
 __global__ void make_planes_kernel(const float* __restrict__ x, int64_t rows, int C, int Cp, int P, float scale,
-                                   int act, bf16* __restrict__ out_id, bf16* __restrict__ out_act) {
+                                   int act, bf16* __restrict__ out_id, bf16* __restrict__ out_act,
+                                   float* __restrict__ csum) {
     pdl_wait();
+    extern __shared__ float csum_s[];                 // [C] when csum != nullptr: per-channel sums of x*scale
+    if (csum) {
+        for (int c = threadIdx.x; c < C; c += blockDim.x) csum_s[c] = 0.f;
+        __syncthreads();
+    }
     const int Cv = C / VEC;
     const int64_t n = rows * Cv, plane = rows * Cp;
     GRID_STRIDE(i, n) {
@@ -67,14 +73,27 @@ __global__ void make_planes_kernel(const float* __restrict__ x, int64_t rows, in
         const int64_t o = r * Cp + c;
         if (out_id) st_planes_vec<VEC>(out_id, o, plane, P, v);
         if (out_act) st_planes_vec<VEC>(out_act, o, plane, P, u);
+        if (csum) {
+#pragma unroll
+            for (int j = 0; j < VEC; j++) atomicAdd(csum_s + c + j, v[j]);
+        }
+    }
+    if (csum) {
+        __syncthreads();
+        for (int c = threadIdx.x; c < C; c += blockDim.x) atomicAdd(csum + c, csum_s[c]);
     }
 }
 
 template <int VEC>
 __global__ void concat_planes_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb, int Cb,
-                                     int64_t rows, int Cp, int P, bf16* __restrict__ out) {
+                                     int64_t rows, int Cp, int P, bf16* __restrict__ out, float* __restrict__ csum) {
     pdl_wait();
+    extern __shared__ float csum_s[];                 // [Ca+Cb] when csum != nullptr
     const int Cc = Ca + Cb, Cv = Cc / VEC;
+    if (csum) {
+        for (int c = threadIdx.x; c < Cc; c += blockDim.x) csum_s[c] = 0.f;
+        __syncthreads();
+    }
     const int64_t n = rows * Cv, plane = rows * Cp;
     GRID_STRIDE(i, n) {
         const int64_t r = i / Cv;
@@ -83,6 +102,14 @@ __global__ void concat_planes_kernel(const float* __restrict__ xa, int Ca, const
         if (c < Ca) ld_vec<VEC>(xa + r * Ca + c, v);
         else ld_vec<VEC>(xb + r * Cb + (c - Ca), v);
         st_planes_vec<VEC>(out, r * Cp + c, plane, P, v);
+        if (csum) {
+#pragma unroll
+            for (int j = 0; j < VEC; j++) atomicAdd(csum_s + c + j, v[j]);
+        }
+    }
+    if (csum) {
+        __syncthreads();
+        for (int c = threadIdx.x; c < Cc; c += blockDim.x) atomicAdd(csum + c, csum_s[c]);
     }
 }
 
@@ -295,22 +322,36 @@ extern "C" int vnb_transpose(const float* in, int B, int R, int S, float* out, v
     return VNB_OK;
 }
 
+// csum (optional, C floats, ZEROED by the caller): also accumulates the per-channel sums over all frames of the
+// values written to the identity plane (x*scale) - the bias gradient, without a second pass over the tensor.
 extern "C" int vnb_make_planes(const float* x, int B, int C, int T, int P, float scale, int act, void* out_id,
-                               void* out_act, void* stream) {
+                               void* out_act, float* csum, void* stream) {
     VNB_REQUIRE(x && (out_id || out_act) && B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "make_planes: bad arguments");
+    VNB_REQUIRE(!csum || C <= 12000, "make_planes: too many channels for the fused channel sums");
     const int64_t rows = (int64_t)B * T;
-    VEC_DISPATCH((C & 3) == 0, make_planes_kernel, rows * C, ST, x, rows, C, round_up8(C), P, scale, act, (bf16*)out_id,
-                 (bf16*)out_act);
+    const bool v4 = (C & 3) == 0;
+    const int64_t n = v4 ? rows * C / 4 : rows * C;
+    int grid = ew_grid(n);
+    if (csum && grid > 296) grid = 296;                 // fewer flushes of the shared-memory sums
+    const size_t smem = csum ? (size_t)C * sizeof(float) : 0;
+    if (v4) vnb::launch_k(make_planes_kernel<4>, grid, EW_THREADS, smem, ST, x, rows, C, round_up8(C), P, scale, act, (bf16*)out_id, (bf16*)out_act, csum);
+    else vnb::launch_k(make_planes_kernel<1>, grid, EW_THREADS, smem, ST, x, rows, C, round_up8(C), P, scale, act, (bf16*)out_id, (bf16*)out_act, csum);
     VNB_LAUNCH_CHECK("make_planes");
     return VNB_OK;
 }
 
 extern "C" int vnb_concat_planes(const float* xa, int Ca, const float* xb, int Cb, int B, int T, int P, void* out,
-                                 void* stream) {
+                                 float* csum, void* stream) {
     VNB_REQUIRE(xa && xb && out && Ca > 0 && Cb > 0 && B > 0 && T > 0 && (P == 1 || P == 3), "concat_planes: bad arguments");
+    VNB_REQUIRE(!csum || Ca + Cb <= 12000, "concat_planes: too many channels for the fused channel sums");
     const int64_t rows = (int64_t)B * T;
-    VEC_DISPATCH(((Ca | Cb) & 3) == 0, concat_planes_kernel, rows * (Ca + Cb), ST, xa, Ca, xb, Cb, rows,
-                 round_up8(Ca + Cb), P, (bf16*)out);
+    const bool v4 = ((Ca | Cb) & 3) == 0;
+    const int64_t n = v4 ? rows * (Ca + Cb) / 4 : rows * (Ca + Cb);
+    int grid = ew_grid(n);
+    if (csum && grid > 296) grid = 296;
+    const size_t smem = csum ? (size_t)(Ca + Cb) * sizeof(float) : 0;
+    if (v4) vnb::launch_k(concat_planes_kernel<4>, grid, EW_THREADS, smem, ST, xa, Ca, xb, Cb, rows, round_up8(Ca + Cb), P, (bf16*)out, csum);
+    else vnb::launch_k(concat_planes_kernel<1>, grid, EW_THREADS, smem, ST, xa, Ca, xb, Cb, rows, round_up8(Ca + Cb), P, (bf16*)out, csum);
     VNB_LAUNCH_CHECK("concat_planes");
     return VNB_OK;
 }

@@ -193,13 +193,17 @@ class ConvFn(Function):
         x, v, g, bias = ctx.saved_tensors
         transposed, dil, act, scale, P, taps, Cin, has_bias = ctx.cfg
         dy = Pm.as_cl(dy)
-        dypl = Pm.make_planes(dy, P)[0]
         db = None
         if has_bias and ctx.needs_input_grad[3]:
+            # bias gradient = channel sums of dy, accumulated by the kernel that quantises dy (the gradient slot is
+            # zeroed by the trainer's flat-gradient memset)
             slot = _slot(bias)
-            db = Pm.channel_sum(dy, slot)
+            db = slot if slot is not None else torch.zeros_like(bias)
+            dypl = Pm.make_planes(dy, P, csum=db)[0]
             if slot is not None:
                 db = None
+        else:
+            dypl = Pm.make_planes(dy, P)[0]
         dx = None
         if ctx.needs_input_grad[0]:
             dx = Pm.conv_fwd(dypl, ctx.wb, taps, dil, Cin)
@@ -373,11 +377,9 @@ class DecBlockFn(Function):
         # dskip arrives in the physical (B, T, S) form of the skip accumulator
         dskip_phys = torch.zeros((B, T, S), device=dev) if dskip is None else dskip.contiguous()
         dskip = dskip_phys.transpose(1, 2)
-        drpl = Pm.concat_planes(dxo, dskip, P)
-        rs_slot = _slot(b_rs)
-        db_rs = rs_slot if rs_slot is not None else torch.empty((C + S,), dtype=torch.float32, device=dev)
-        Pm.channel_sum(dxo, db_rs[:C])
-        Pm.channel_sum(dskip, db_rs[C:])
+        rs_slot = _slot(b_rs)                  # zeroed by the trainer's flat-gradient memset
+        db_rs = rs_slot if rs_slot is not None else torch.zeros((C + S,), dtype=torch.float32, device=dev)
+        drpl = Pm.concat_planes(dxo, dskip, P, csum=db_rs)      # res/skip bias gradient rides along
         if rs_slot is not None:
             db_rs = None
         dg = Pm.conv_fwd(drpl, ctx.wrs_wb, 1, 1, C)

@@ -165,20 +165,22 @@ def conv_wgrad(dy_pl, u_pl, taps, dil, transposed, out=None):
 # --------------------------------------------------------------------------------------------
 # operand planes
 # --------------------------------------------------------------------------------------------
-def make_planes(x, P, scale=1.0, act=ACT_NONE, want_id=True, want_act=False):
+def make_planes(x, P, scale=1.0, act=ACT_NONE, want_id=True, want_act=False, csum=None):
+    """``csum``: optional ZEROED (C,) tensor that also receives the per-channel sums of x*scale."""
     B, C, T = x.shape
     pid = Planes.empty(P, B, C, T, x.device) if want_id else None
     pact = Planes.empty(P, B, C, T, x.device) if want_act else None
     _C.call('make_planes', _r(x), B, C, T, P, scale, act, pid.data if pid else None,
-            pact.data if pact else None)
+            pact.data if pact else None, csum)
     return pid, pact
 
 
-def concat_planes(xa, xb, P):
+def concat_planes(xa, xb, P, csum=None):
+    """``csum``: optional ZEROED (Ca+Cb,) tensor that also receives the per-channel sums."""
     B, Ca, T = xa.shape
     Cb = xb.shape[1]
     out = Planes.empty(P, B, Ca + Cb, T, xa.device)
-    _C.call('concat_planes', _r(xa), Ca, _r(xb), Cb, B, T, P, out.data)
+    _C.call('concat_planes', _r(xa), Ca, _r(xb), Cb, B, T, P, out.data, csum)
     return out
 
 
