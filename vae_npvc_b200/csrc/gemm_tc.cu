@@ -58,6 +58,7 @@ struct ConvTcArgs {
     int gn_groups;
     int dbg;              // VNB_TC_DBG (0 = normal, 9 = record the timeline)
     int nstages;          // depth of the TMA ring (<= 8)
+    int kch;              // 64-deep k-chunks per pipeline stage (1, or 2 with 4-D tensor maps when Cin % 128 == 0)
     uint32_t recv_off;    // byte offset of the receive slots in dynamic shared memory
 };
 
@@ -79,12 +80,12 @@ template <int BN> struct ConvTcCfg {
     static constexpr uint32_t STAGING_BYTES = (uint32_t)TC_BM * PITCH * 4;
     static constexpr uint32_t SMEM_BUDGET = 227 * 1024 - 2048;  // minus alignment slack and static barriers
     static uint32_t recv_bytes(int ks) { return (uint32_t)(ks - 1) * (TC_BM / ks) * PITCH * 4; }
-    static int stages(int ks) {
-        int n = (int)((SMEM_BUDGET - recv_bytes(ks)) / STAGE_BYTES);
+    static int stages(int ks, int kch) {
+        int n = (int)((SMEM_BUDGET - recv_bytes(ks)) / (STAGE_BYTES * kch));
         return n > MAX_STAGES ? MAX_STAGES : n;
     }
-    static uint32_t recv_offset(int ks) {
-        uint32_t ring = (uint32_t)stages(ks) * STAGE_BYTES;
+    static uint32_t recv_offset(int ks, int kch) {
+        uint32_t ring = (uint32_t)stages(ks, kch) * STAGE_BYTES * kch;
         uint32_t o = ring > STAGING_BYTES ? ring : STAGING_BYTES;
         return (o + 1023u) & ~1023u;
     }
@@ -97,7 +98,9 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     using Cfg = ConvTcCfg<BN>;
     constexpr int MAX_STAGES = Cfg::MAX_STAGES;
     const int STAGES = a.nstages;
-    constexpr uint32_t A_BYTES = Cfg::A_BYTES, STAGE_BYTES = Cfg::STAGE_BYTES;
+    constexpr uint32_t A_BYTES = Cfg::A_BYTES, B_BYTES = Cfg::B_BYTES;
+    const int kch = a.kch;
+    const uint32_t STAGE_BYTES = (uint32_t)kch * Cfg::STAGE_BYTES;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // 1024-byte alignment is required by SWIZZLE_128B (same offset in every CTA of the cluster)
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -113,7 +116,8 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     const int mtiles = (a.T + TC_BM - 1) / TC_BM;
     const int b = blockIdx.z / mtiles, t0 = (blockIdx.z - b * mtiles) * TC_BM, co0 = blockIdx.y * BN;
     const int pairs = a.P == 1 ? 1 : 6;
-    const int kc_per = (a.Cin + TC_BK - 1) / TC_BK;
+    // k runs over (plane pair, tap, group of kch 64-channel chunks): one pipeline stage each
+    const int kc_per = ((a.Cin + TC_BK - 1) / TC_BK) / kch;
     const int nkc = pairs * a.taps * kc_per;
     const int kc0 = (int)((int64_t)nkc * kr / ks), kc1 = (int)((int64_t)nkc * (kr + 1) / ks);
     const int nk = kc1 - kc0;                                  // may be 0 (more slices than chunks)
@@ -155,8 +159,14 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                 if (i >= STAGES) mbar_wait(&empty_bar[s], ph);
                 uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
                 mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-                tma_load_3d(sa, &map_x, &full_bar[s], c * TC_BK, t0 + off, pb * a.B + b);
-                tma_load_3d(sa + A_BYTES, &map_w, &full_bar[s], c * TC_BK, co0, pa * a.taps + tap);
+                if (kch == 1) {
+                    tma_load_3d(sa, &map_x, &full_bar[s], c * TC_BK, t0 + off, pb * a.B + b);
+                    tma_load_3d(sa + A_BYTES, &map_w, &full_bar[s], c * TC_BK, co0, pa * a.taps + tap);
+                } else {
+                    // 4-D maps (64 ch, row, 64-channel chunk, plane): ONE instruction lands kch canonical tiles
+                    tma_load_4d(sa, &map_x, &full_bar[s], 0, t0 + off, c * kch, pb * a.B + b);
+                    tma_load_4d(sa + kch * A_BYTES, &map_w, &full_bar[s], 0, co0, c * kch, pa * a.taps + tap);
+                }
                 if (++c == kc_per) { c = 0; if (++tap == a.taps) { tap = 0; ++pr; } }
                 if (++s == STAGES) { s = 0; ph ^= 1; }
             }
@@ -182,9 +192,13 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                 const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
                 // K-major operands: 16 K-elements = 32 bytes along the swizzled 128-byte row (+2 in the
                 // descriptor's 16-byte address units); 8-row groups are 1024 B apart (SBO); LBO unused
-                const uint64_t da = smem_desc_sw128(sa, 16, 1024), db = smem_desc_sw128(sa + A_BYTES, 16, 1024);
+                const uint64_t da = smem_desc_sw128(sa, 16, 1024), db = smem_desc_sw128(sa + kch * A_BYTES, 16, 1024);
+                for (int ch = 0; ch < kch; ch++) {
 #pragma unroll
-                for (int j = 0; j < TC_BK / 16; j++) umma_bf16(tmem_base, da + 2 * j, db + 2 * j, idesc, (i | j) != 0);
+                    for (int j = 0; j < TC_BK / 16; j++)
+                        umma_bf16(tmem_base, da + (uint64_t)(ch * (A_BYTES / 16) + 2 * j), db + (uint64_t)(ch * (B_BYTES / 16) + 2 * j),
+                                  idesc, (i | ch | j) != 0);
+                }
                 umma_commit(&empty_bar[s]);           // frees the smem stage when these MMAs retire
                 ready = next_ready;
                 s = s1;
@@ -434,16 +448,28 @@ static int launch_conv_tc(const void* in, const void* w, int Cin_p, int ksplit, 
         attr_done = true;
     }
     CUtensorMap mx, mw;
-    // activations (P, B, T, Cin_p): dims (ci, t, plane*b); box 64 x 128 x 1
-    if (!make_tmap_3d(&mx, in, (uint64_t)a.Cin, (uint64_t)a.T, (uint64_t)a.P * a.B, (uint64_t)Cin_p * 2,
-                      (uint64_t)a.T * Cin_p * 2, TC_BK, TC_BM, 1))
-        return VNB_E_CUDA;
-    // weights (P, taps, Cout, Cin_p): dims (ci, co, plane*tap); box 64 x BN x 1
-    if (!make_tmap_3d(&mw, w, (uint64_t)a.Cin, (uint64_t)a.Cout, (uint64_t)a.P * a.taps, (uint64_t)Cin_p * 2,
-                      (uint64_t)a.Cout * Cin_p * 2, TC_BK, BN, 1))
-        return VNB_E_CUDA;
-    a.nstages = Cfg::stages(ksplit);
-    a.recv_off = Cfg::recv_offset(ksplit);
+    if (a.kch == 1) {
+        // activations (P, B, T, Cin_p): dims (ci, t, plane*b); box 64 x 128 x 1
+        if (!make_tmap_3d(&mx, in, (uint64_t)a.Cin, (uint64_t)a.T, (uint64_t)a.P * a.B, (uint64_t)Cin_p * 2,
+                          (uint64_t)a.T * Cin_p * 2, TC_BK, TC_BM, 1))
+            return VNB_E_CUDA;
+        // weights (P, taps, Cout, Cin_p): dims (ci, co, plane*tap); box 64 x BN x 1
+        if (!make_tmap_3d(&mw, w, (uint64_t)a.Cin, (uint64_t)a.Cout, (uint64_t)a.P * a.taps, (uint64_t)Cin_p * 2,
+                          (uint64_t)a.Cout * Cin_p * 2, TC_BK, BN, 1))
+            return VNB_E_CUDA;
+    } else {
+        // Cin % 128 == 0: dims (64 ch, row, 64-channel chunk, plane) - the chunk dimension has the SMALLER stride
+        const uint64_t dx[4] = {64, (uint64_t)a.T, (uint64_t)a.Cin / 64, (uint64_t)a.P * a.B};
+        const uint64_t sx[3] = {(uint64_t)Cin_p * 2, 128, (uint64_t)a.T * Cin_p * 2};
+        const uint32_t bx[4] = {64, TC_BM, (uint32_t)a.kch, 1};
+        if (!make_tmap(&mx, in, 4, dx, sx, bx)) return VNB_E_CUDA;
+        const uint64_t dw[4] = {64, (uint64_t)a.Cout, (uint64_t)a.Cin / 64, (uint64_t)a.P * a.taps};
+        const uint64_t sw[3] = {(uint64_t)Cin_p * 2, 128, (uint64_t)a.Cout * Cin_p * 2};
+        const uint32_t bw[4] = {64, BN, (uint32_t)a.kch, 1};
+        if (!make_tmap(&mw, w, 4, dw, sw, bw)) return VNB_E_CUDA;
+    }
+    a.nstages = Cfg::stages(ksplit, a.kch);
+    a.recv_off = Cfg::recv_offset(ksplit, a.kch);
     const size_t smem = (size_t)a.recv_off + Cfg::recv_bytes(ksplit) + 1024;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(ksplit, ceil_div(a.Cout, BN), a.B * ceil_div(a.T, TC_BM));
@@ -478,14 +504,20 @@ int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int
     static const int dbg = getenv("VNB_TC_DBG") ? atoi(getenv("VNB_TC_DBG")) : 0;
     static const int force_bn = getenv("VNB_TC_BN") ? atoi(getenv("VNB_TC_BN")) : 0;
     static const int force_ks = getenv("VNB_TC_KSPLIT") ? atoi(getenv("VNB_TC_KSPLIT")) : 0;
-    ConvTcArgs a{B, Cin, Cout, T, taps, dil, P, bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups, dbg, 0, 0};
+    ConvTcArgs a{B, Cin, Cout, T, taps, dil, P, bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups, dbg, 0, 1, 0};
     const int Cin_p = round_up8(Cin);
     // N tile and cluster split-K: as many CTAs as fit the 148 SMs in one wave (a tcgen05.mma issue costs the same
     // ~70 cycles for a 32-cycle N=64 tile as for a 128-cycle N=256 one, so wide tiles are preferred on a tie),
     // with the receive slots of the split-K exchange fitting beside the TMA ring
-    const int nkc = (P == 1 ? 1 : 6) * taps * ceil_div(Cin, TC_BK);
-    auto fits = [](int bn_, int ks_) {
-        const uint32_t pitch = bn_ + 4, stage_b = TC_BM * TC_BK * 2 + bn_ * TC_BK * 2;
+    static const int force_kch = getenv("VNB_TC_KCH") ? atoi(getenv("VNB_TC_KCH")) : 0;
+    // two 64-deep chunks per pipeline stage when the channel count allows: one barrier round trip and two TMA
+    // instructions per 8 MMAs instead of per 4
+    int kch = (Cin % 128 == 0) ? 2 : 1;
+    if (force_kch == 1) kch = 1;
+    a.kch = kch;
+    const int nkc = (P == 1 ? 1 : 6) * taps * (ceil_div(Cin, TC_BK) / kch);
+    auto fits = [kch](int bn_, int ks_) {
+        const uint32_t pitch = bn_ + 4, stage_b = (TC_BM * TC_BK * 2 + bn_ * TC_BK * 2) * kch;
         const uint32_t recv = (uint32_t)(ks_ - 1) * (TC_BM / ks_) * pitch * 4, budget = 227 * 1024 - 2048;
         if (recv + 2 * stage_b > budget) return false;
         uint32_t ring = (budget - recv) / stage_b;
@@ -495,18 +527,19 @@ int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int
         return off + recv + 1024 <= 227 * 1024 - 1024;
     };
     // cost model in SM cycles, fitted to the VNB_TC_DBG=9 timelines (profiles/r01_conv_tc_timeline.txt): ~610
-    // cycles per 64-deep k-chunk whatever the tile (the single issuing thread, not the tensor pipe, is the limit;
-    // 770 at BN=256 where the 48 KB stages meet the L2 limit), a fixed ~5.5k cycles of launch / TMEM / cold
-    // instruction fetch / epilogue, and ~5k more for a split-K exchange through distributed shared memory
+    // cycles per single-chunk stage whatever the tile (the single issuing thread, not the tensor pipe, is the
+    // limit; 770 at BN=256 where the 48 KB stages meet the L2 limit), ~930 / 1300 per double-chunk stage, a fixed
+    // ~5.5k cycles of launch / TMEM / cold instruction fetch / epilogue, ~5k more for a split-K exchange
     int bn = 64, ks = 1;
     int64_t best = INT64_MAX;
     for (int cand = 64; cand <= 256; cand *= 2) {
         if (cand > 64 && Cout <= cand / 2) break;                 // tile wider than needed
         const int64_t tiles = mt * ceil_div(Cout, cand);
+        const int64_t per_stage = kch == 1 ? (cand == 256 ? 770 : 610) : (cand == 256 ? 1300 : 930);
         for (int k = 1; k <= 8; k *= 2) {
             if (k > nkc || !fits(cand, k)) break;
             const int64_t waves = (tiles * k + 147) / 148;
-            const int64_t cost = waves * ((int64_t)ceil_div(nkc, k) * (cand == 256 ? 770 : 610) + 5500 +
+            const int64_t cost = waves * ((int64_t)ceil_div(nkc, k) * per_stage + 5500 +
                                           (k > 1 ? 4500 + 250 * k : 0) + (cand == 256 ? 2000 : 0));
             if (cost < best) { best = cost; bn = cand; ks = k; }
         }

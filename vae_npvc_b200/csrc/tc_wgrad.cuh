@@ -3,14 +3,14 @@
 //     dW[tap][co, ci] = sum_{pair} sum_{b} sum_{t} dY[pa][b][t][co] * U[pb][b][t + off(tap)][ci]
 //
 // The contraction runs over FRAMES, which are the rows of the channels-last planes, so both operands
-// are MN-major tiles: 64 frame rows x 64 channels (128 B, SWIZZLE_128B) per box, the tap shift is
+// are MN-major tiles: 128 frame rows x 64 channels (128 B, SWIZZLE_128B) per box, the tap shift is
 // again a TMA row coordinate and the per-sample zero padding is out-of-bounds fill.
 //   A = "row" planes (M = 128 channels = two 64-channel boxes), B = "column" planes (N = BN channels).
 //   For Conv1d the rows are dY channels (co) and the columns U channels (ci): parameter (co, ci, k).
 //   For ConvTranspose1d the host SWAPS the operands (rows = ci from U, columns = co from dY), so that the
 //   parameter layout (ci, co, k) is again row-major in (row, column) and the stores stay coalesced.
 //   One TMA instruction per operand and stage: a 4-D map (64 ch, frame, 64-channel group, plane*sample)
-//   with box {64, 64, groups, 1} lands the groups as consecutive canonical 8 KB boxes (the group dimension
+//   with box {64, 128, groups, 1} lands the groups as consecutive canonical 16 KB boxes (the group dimension
 //   has a SMALLER stride than the frame dimension; cuTensorMapEncodeTiled accepts that - tools/tma4d_probe.cu).
 //   Channel counts that are not a multiple of 64 use one 3-D box per group instead.
 // grid = (ksplit, row tiles * column tiles, taps), cluster (ksplit, 1, 1): the (sample, 64-frame block) list is
@@ -26,9 +26,9 @@ namespace vnb {
 using namespace tc;
 
 constexpr int WG_BM = 128;
-constexpr int WG_KT = 64;          // frames per pipeline stage
+constexpr int WG_KT = 128;         // frames per pipeline stage (8 MMAs per barrier round trip)
 constexpr int WG_THREADS = 256;
-constexpr uint32_t WG_BOX_BYTES = WG_KT * 128;      // one 64-channel x 64-frame box
+constexpr uint32_t WG_BOX_BYTES = WG_KT * 128;      // one 64-channel x 128-frame box
 
 struct WgradTcArgs {
     int B, nrows, ncols, T, taps, P;
@@ -341,8 +341,8 @@ int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin
             const bool ok = cand == 256 ? WgradTcCfg<256>::fits(k) : cand == 128 ? WgradTcCfg<128>::fits(k) : WgradTcCfg<64>::fits(k);
             if (k > kblocks || !ok) break;
             const int64_t waves = (tiles * k + 147) / 148;
-            // same cost model as conv_fwd_tc (cycles): ~610 per 64-frame stage, fixed 5.5k, split-K exchange 4.5k+
-            const int64_t cost = waves * ((int64_t)ceil_div(kblocks, k) * (cand == 256 ? 770 : 610) + 5500 +
+            // same cost model as conv_fwd_tc (cycles): ~930 per 128-frame stage, fixed 5.5k, split-K exchange 4.5k+
+            const int64_t cost = waves * ((int64_t)ceil_div(kblocks, k) * (cand == 256 ? 1300 : 930) + 5500 +
                                           (k > 1 ? 4500 + 250 * k : 0) + (cand == 256 ? 2000 : 0));
             if (cost < best) { best = cost; bn = cand; ks = k; }
         }
