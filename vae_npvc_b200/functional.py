@@ -388,20 +388,25 @@ class DecBlockFn(Function):
         slots = {'dgamma': _slot(gamma), 'dbeta': _slot(beta), 'csum': _slot(b_in),
                  'csum2': _slot(b_c) if has_cond else None}          # both biases add to the GN input
         dgamma, dbeta, Ssum, bsum, csum = Pm.gn_bwd_finalize(R, gamma, rstd, T, 2, True, slots)
-        dapl = Pm.gate_bwd_apply(dg, a, mean, rstd, gamma, beta, Ssum, P)
-        dx = Pm.conv_fwd(dapl, ctx.win_wb, taps, dil, C, None, 0, dxo) if ctx.needs_input_grad[0] else None
-        dv_in, dg_in = _wgrad(dapl, ctx.xpl, taps, dil, True, v_in, g_in)
         dcond = dv_c = dg_c = db_c = None
-        if has_cond:
-            if slots['csum2'] is None:
-                db_c = (csum if csum is not None else b_in.grad).clone()
-            if bcast:
-                bank = get_bank()
+        fk_lin = None
+        if has_cond and bcast:
+            # the conditioning path's backward only needs bsum: forked beside the gate backward + k=3 data gradient
+            bank = get_bank()
+            with _Fork(bsum) as fk_lin:
                 if bank is not None and bank.has(v_c) and _slot(v_c) is not None:
                     _, dcond = Pm.linear_bwd(bsum, cond, ctx.wc32, None, v_c.grad.view(2 * C, -1))
                 else:
                     dwc, dcond = Pm.linear_bwd(bsum, cond, ctx.wc32)
                     dv_c, dg_c = _dw_to_param_grads(dwc.view_as(v_c), v_c, g_c)
+        dapl = Pm.gate_bwd_apply(dg, a, mean, rstd, gamma, beta, Ssum, P)
+        dx = Pm.conv_fwd(dapl, ctx.win_wb, taps, dil, C, None, 0, dxo) if ctx.needs_input_grad[0] else None
+        dv_in, dg_in = _wgrad(dapl, ctx.xpl, taps, dil, True, v_in, g_in)
+        if has_cond:
+            if slots['csum2'] is None:
+                db_c = (csum if csum is not None else b_in.grad).clone()
+            if bcast:
+                fk_lin.join(dcond, dv_c, dg_c)
             else:
                 dv_c, dg_c = _wgrad(dapl, ctx.cpl, 1, 1, False, v_c, g_c)
                 if ctx.needs_input_grad[1]:

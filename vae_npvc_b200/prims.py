@@ -127,6 +127,33 @@ def wn_backward(dw, v, g):
 # --------------------------------------------------------------------------------------------
 # GEMM-shaped ops
 # --------------------------------------------------------------------------------------------
+# Zeroed scratch for the fused GroupNorm statistics: the trainer zeroes ONE arena per step (stats_arena_begin)
+# and conv_fwd carves its (B, groups, 2) fp64 accumulators out of it, instead of one fill kernel per conv.
+_ARENA = {'buf': None, 'off': -1}
+
+
+def stats_arena_begin(device, n_doubles=1 << 16):
+    buf = _ARENA['buf']
+    if buf is None or buf.device != torch.device(device) or buf.numel() < n_doubles:
+        buf = torch.empty(n_doubles, dtype=torch.float64, device=device)
+        _ARENA['buf'] = buf
+    buf.zero_()
+    _ARENA['off'] = 0
+
+
+def stats_arena_end():
+    _ARENA['off'] = -1
+
+
+def _stats_zeros(B, groups, device):
+    n = B * groups * 2
+    buf, off = _ARENA['buf'], _ARENA['off']
+    if buf is not None and off >= 0 and buf.device == torch.device(device) and off + n <= buf.numel():
+        _ARENA['off'] = off + n
+        return buf[off:off + n].view(B, groups, 2)
+    return torch.zeros((B, groups, 2), dtype=torch.float64, device=device)
+
+
 def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False,
              gn_groups=0, eps=1e-5):
     """x_pl: Planes (B,Cin,T); w_op: (P,taps,Cout,Cin_p) bf16 -> out fp32, logical (B,Cout,T).
@@ -138,7 +165,7 @@ def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=No
         out = cl_empty(x_pl.B, Cout, x_pl.T, dev)
     elif not is_cl(out):                      # reference-layout buffer from a caller: stage through channels-last
         user_out, out = out, as_cl(out)
-    sums = torch.zeros((x_pl.B, gn_groups, 2), dtype=torch.float64, device=dev) if gn_groups else None
+    sums = _stats_zeros(x_pl.B, gn_groups, dev) if gn_groups else None
     _C.call('conv_fwd', x_pl.data, x_pl.P, x_pl.B, x_pl.C, x_pl.T, w_op, taps, dil, Cout, bias,
             bias_bstride, _r(residual), out.transpose(1, 2), int(accumulate), sums, gn_groups)
     if user_out is not None:

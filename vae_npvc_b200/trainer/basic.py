@@ -156,6 +156,8 @@ class Trainer(object):
         _lvq.defer_items(True)
         Fn.set_bank(self.bank)
         Fn.set_side_stream(self._side)
+        if hasattr(Pm, 'stats_arena_begin') and self.device.type == 'cuda':
+            Pm.stats_arena_begin(self.device)
         try:
             self.bank.prepare()
             if jitter_src is not None:
@@ -166,6 +168,8 @@ class Trainer(object):
                 torch.cuda.current_stream().wait_stream(self._side)
             self.bank.finish_backward()
         finally:
+            if hasattr(Pm, 'stats_arena_end'):
+                Pm.stats_arena_end()
             Fn.set_side_stream(None)
             Fn.set_bank(None)
             _lvq.defer_items(False)
