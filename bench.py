@@ -173,6 +173,7 @@ def run_ours(args, rank, world):
     cfg = dict(arch)
     warm = max(3, args.warmup)
     cfg.update(model_type='vae_npvc_b200.model.vqvae', precision=args.precision, cuda_graph=not args.no_graph,
+               overlap_allreduce=not bool(os.environ.get('VNB_NO_OVERLAP')),
                graph_warmup=min(3, warm - 1), learning_rate=1e-3, max_grad_norm=10, lr_scheduler='StepLR',
                lr_param={'step_size': 100000, 'gamma': 0.5, 'last_epoch': -1})
     torch.manual_seed(777)

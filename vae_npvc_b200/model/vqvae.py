@@ -184,6 +184,11 @@ class Model(nn.Module):
         z = self.encoder(x)
         z_vq, z_qut_loss, z_enc_loss, vq_detail = self.quantizer(z)
         z_vq = self.jitter(z_vq)
+        hook = getattr(self, '_decoder_backward_done', None)
+        if hook is not None and torch.is_tensor(z_vq) and z_vq.requires_grad:
+            # fires when the gradient wrt the decoder input exists, i.e. the whole decoder has been back-propagated:
+            # the data-parallel trainer starts all-reducing the decoder's gradients there (trainer/basic.py)
+            z_vq.register_hook(hook)
         xhat = self.decoder((z_vq, y))
         x_loss = log_loss(xhat, x)
         loss = x_loss + z_qut_loss + self.beta * z_enc_loss

@@ -122,6 +122,11 @@ class Trainer(object):
             self.scheduler = None
         self.iteration = 0
         self.model.train()
+        # contiguous slice of the flat buffers that holds the decoder's parameters (bucketed all-reduce)
+        self._comm = torch.cuda.Stream(device=self.device) if self._side_wanted() else None
+        self._dec_range = self._param_range('decoder.')
+        self._dec_reduced = False
+        self.overlap_allreduce = bool(config.get('overlap_allreduce', True))
 
         self.use_graph = bool(config.get('cuda_graph', True)) and self.device.type == 'cuda'
         # weight-gradient GEMMs on a second stream, beside the data-gradient chain (functional.set_side_stream)
@@ -132,6 +137,27 @@ class Trainer(object):
         self._eager_steps = 0
         self.last_step_on_graph = False
         self.launches_per_step = 0
+
+    def _side_wanted(self):
+        return self.device.type == 'cuda'
+
+    def _param_range(self, prefix):
+        """(lo, hi) element range of the parameters whose name starts with ``prefix`` when they are contiguous in
+        the flat buffers, else None."""
+        off, lo, hi, seen_after = 0, None, None, False
+        for n, p in self.model.named_parameters():
+            if not p.requires_grad:
+                continue
+            if n.startswith(prefix):
+                if seen_after:
+                    return None
+                if lo is None:
+                    lo = off
+                hi = off + p.numel()
+            elif lo is not None:
+                seen_after = True
+            off += p.numel()
+        return (lo, hi) if lo is not None else None
 
     # ---- flat parameter / gradient buffers -------------------------------------------------------
     def _flatten(self):
@@ -162,26 +188,56 @@ class Trainer(object):
             self.bank.prepare()
             if jitter_src is not None:
                 self.model.jitter.sources = lambda length: jitter_src
+            dist = _dist()
+            self._dec_reduced = False
+            if (dist is not None and self._side is not None and self._dec_range is not None and self.overlap_allreduce):
+                self.model._decoder_backward_done = self._reduce_decoder_grads       # registered during forward
             output, loss, detail = self.model([x, y])
             loss.backward()
+            self.model._decoder_backward_done = None
             if self._side is not None:
                 torch.cuda.current_stream().wait_stream(self._side)
+            # data parallel: sum the RAW weight gradients (weight-norm's backward is linear in dW, so it commutes
+            # with the sum); the decoder's two thirds of the buffer were already started behind its backward pass
+            if dist is not None:
+                if self._dec_reduced:
+                    lo, hi = self._dec_range
+                    if lo > 0:
+                        dist.all_reduce(self._flat_g[:lo])
+                    if hi < self._flat_g.numel():
+                        dist.all_reduce(self._flat_g[hi:])
+                    torch.cuda.current_stream().wait_stream(self._comm)
+                else:
+                    dist.all_reduce(self._flat_g)
             self.bank.finish_backward()
+            if dist is not None:
+                self._flat_g.mul_(1.0 / dist.get_world_size())
         finally:
+            self.model._decoder_backward_done = None
             if hasattr(Pm, 'stats_arena_end'):
                 Pm.stats_arena_end()
             Fn.set_side_stream(None)
             Fn.set_bank(None)
             _lvq.defer_items(False)
-        dist = _dist()
-        if dist is not None:
-            dist.all_reduce(self._flat_g)
-            self._flat_g.mul_(1.0 / dist.get_world_size())
         self.optimizer.step(self.max_grad_norm, self._step_size, self._gamma)
         self.bank.fresh = False
         keys = list(detail.keys())
         scal = torch.stack([detail[k].t.reshape(()).float() for k in keys])
         return keys, scal
+
+    def _reduce_decoder_grads(self, grad):
+        """Tensor hook on the decoder input's gradient: every decoder layer has been back-propagated (its weight
+        gradients are queued on the side stream), so their slice of the flat gradient buffer is all-reduced on a
+        communication stream while the quantiser and the encoder are still being back-propagated."""
+        import torch.distributed as dist
+        main = torch.cuda.current_stream()
+        self._comm.wait_stream(main)
+        self._comm.wait_stream(self._side)
+        lo, hi = self._dec_range
+        with torch.cuda.stream(self._comm):
+            dist.all_reduce(self._flat_g[lo:hi])
+        self._dec_reduced = True
+        return None
 
     def _capture(self, x, y):
         from .. import _C
