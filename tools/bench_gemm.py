@@ -1,6 +1,6 @@
 """CUDA-event timing of the conv GEMM kernels (vnb_conv_fwd / vnb_conv_wgrad) on the step's shapes.
 
-    python tools/bench_gemm.py [tag]
+    python tools/bench_gemm.py [tag [shape_index]]
 
 Kernel variants are selected with the library's env switches (VNB_TC_BN, VNB_TC_SHALLOW, ...).
 Two timings per shape: 'cold' flushes L2 with a 256 MB write before every launch (one event pair per
@@ -56,11 +56,12 @@ def timeit(fn, flush=None, iters=20):
 
 def main():
     tag = sys.argv[1] if len(sys.argv) > 1 else 'default'
+    only = int(sys.argv[2]) if len(sys.argv) > 2 else None          # index into SHAPES (for ncu captures)
     _C.require_cuda()
     P = 1
     flush = torch.empty(256 * 1024 * 1024 // 4, device='cuda')
     rows = []
-    for name, Cin, Cout, taps, transposed, gn in SHAPES:
+    for name, Cin, Cout, taps, transposed, gn in (SHAPES if only is None else SHAPES[only:only + 1]):
         x = torch.randn(B, Cin, T, device='cuda')
         v = torch.randn((Cin, Cout, taps) if transposed else (Cout, Cin, taps), device='cuda') * 0.02
         W = Pm.wn_prepare(v, None, transposed, P)

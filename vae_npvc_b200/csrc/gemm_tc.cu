@@ -110,7 +110,7 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     __shared__ __align__(8) uint64_t recv_bar;        // completes when every peer's partial rows have landed here
     __shared__ uint32_t tmem_slot;
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler
     // grid (ksplit, n tiles, samples * frame tiles), cluster (ksplit, 1, 1): blockIdx.x = k-slice = cluster rank
     const int ks = gridDim.x, kr = blockIdx.x;
     const int mtiles = (a.T + TC_BM - 1) / TC_BM;
@@ -146,8 +146,8 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     if (threadIdx.x == 0) TS(1);
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ===== TMA producer =====  (no divisions in the loop: this is ONE thread, nothing hides their latency)
+        {
+            // ===== TMA producer: the whole warp walks the ring (uniform registers), one elected lane issues =====
             const int per_pair = a.taps * kc_per;
             int pr = kc0 / per_pair, rem = kc0 - pr * per_pair;
             int tap = rem / kc_per, c = rem - tap * kc_per;
@@ -158,53 +158,60 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                 const int off = (tap - (a.taps - 1) / 2) * a.dil;
                 if (i >= STAGES) mbar_wait(&empty_bar[s], ph);
                 uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
-                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-                if (kch == 1) {
-                    tma_load_3d(sa, &map_x, &full_bar[s], c * TC_BK, t0 + off, pb * a.B + b);
-                    tma_load_3d(sa + A_BYTES, &map_w, &full_bar[s], c * TC_BK, co0, pa * a.taps + tap);
-                } else {
-                    // 4-D maps (64 ch, row, 64-channel chunk, plane): ONE instruction lands kch canonical tiles
-                    tma_load_4d(sa, &map_x, &full_bar[s], 0, t0 + off, c * kch, pb * a.B + b);
-                    tma_load_4d(sa + kch * A_BYTES, &map_w, &full_bar[s], 0, co0, c * kch, pa * a.taps + tap);
+                if (elect_one()) {
+                    mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                    if (kch == 1) {
+                        tma_load_3d(sa, &map_x, &full_bar[s], c * TC_BK, t0 + off, pb * a.B + b);
+                        tma_load_3d(sa + A_BYTES, &map_w, &full_bar[s], c * TC_BK, co0, pa * a.taps + tap);
+                    } else {
+                        // 4-D maps (64 ch, row, 64-channel chunk, plane): ONE instruction lands kch canonical tiles
+                        tma_load_4d(sa, &map_x, &full_bar[s], 0, t0 + off, c * kch, pb * a.B + b);
+                        tma_load_4d(sa + kch * A_BYTES, &map_w, &full_bar[s], 0, co0, c * kch, pa * a.taps + tap);
+                    }
                 }
+                __syncwarp();
                 if (++c == kc_per) { c = 0; if (++tap == a.taps) { tap = 0; ++pr; } }
                 if (++s == STAGES) { s = 0; ph ^= 1; }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ===== MMA issuer =====
+        {
+            // ===== MMA issuer: the whole warp walks the pipeline, one elected lane issues =====
             constexpr uint32_t idesc = instr_desc_bf16(TC_BM, BN, /*a_mn=*/0, /*b_mn=*/0);
             // the NEXT stage's barrier is probed (non-blocking) before this stage's MMAs are issued, so the
             // ~190-cycle barrier round trip overlaps the tensor work instead of preceding it
-            bool ready = nk > 0 && mbar_test(&full_bar[0], 0);
+            bool ready = nk > 0 && __all_sync(0xffffffffu, mbar_test(&full_bar[0], 0));
             int s = 0;
             uint32_t ph = 0;                          // (i / STAGES) & 1, kept incrementally
             for (int i = 0; i < nk; i++) {
                 if (!ready) mbar_wait(&full_bar[s], ph);
                 tc_fence_after();
-                if (i == 0) TS(2);
+                if (i == 0 && lane == 0) TS(2);
                 int s1 = s + 1;
                 uint32_t ph1 = ph;
                 if (s1 == STAGES) { s1 = 0; ph1 ^= 1; }
                 bool next_ready = false;
-                if (i + 1 < nk) next_ready = mbar_test(&full_bar[s1], ph1);
+                if (i + 1 < nk) next_ready = __all_sync(0xffffffffu, mbar_test(&full_bar[s1], ph1));
                 const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
                 // K-major operands: 16 K-elements = 32 bytes along the swizzled 128-byte row (+2 in the
                 // descriptor's 16-byte address units); 8-row groups are 1024 B apart (SBO); LBO unused
                 const uint64_t da = smem_desc_sw128(sa, 16, 1024), db = smem_desc_sw128(sa + kch * A_BYTES, 16, 1024);
-                for (int ch = 0; ch < kch; ch++) {
+                if (elect_one()) {
+                    for (int ch = 0; ch < kch; ch++) {
 #pragma unroll
-                    for (int j = 0; j < TC_BK / 16; j++)
-                        umma_bf16(tmem_base, da + (uint64_t)(ch * (A_BYTES / 16) + 2 * j), db + (uint64_t)(ch * (B_BYTES / 16) + 2 * j),
-                                  idesc, (i | ch | j) != 0);
+                        for (int j = 0; j < TC_BK / 16; j++)
+                            umma_bf16(tmem_base, da + (uint64_t)(ch * (A_BYTES / 16) + 2 * j), db + (uint64_t)(ch * (B_BYTES / 16) + 2 * j),
+                                      idesc, (i | ch | j) != 0);
+                    }
+                    umma_commit(&empty_bar[s]);       // frees the smem stage when these MMAs retire
                 }
-                umma_commit(&empty_bar[s]);           // frees the smem stage when these MMAs retire
+                __syncwarp();
                 ready = next_ready;
                 s = s1;
                 ph = ph1;
             }
-            umma_commit(&tmem_full_bar);              // accumulator complete (immediately, when nk == 0)
+            if (elect_one()) umma_commit(&tmem_full_bar);   // accumulator complete (immediately, when nk == 0)
+            __syncwarp();
         }
     }
 
@@ -316,12 +323,12 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                 acc1.x += r1.x + u1.x; acc1.y += r1.y + u1.y; acc1.z += r1.z + u1.z; acc1.w += r1.w + u1.w;
                 acc2.x += r2.x + u2.x; acc2.y += r2.y + u2.y; acc2.z += r2.z + u2.z; acc2.w += r2.w + u2.w;
                 if (ok1) {
-                    *reinterpret_cast<float4*>(outp + o1) = acc1;
+                    if (a.dbg != 31) *reinterpret_cast<float4*>(outp + o1) = acc1;
                     fs0 += (acc1.x + acc1.y) + (acc1.z + acc1.w);
                     fs1 += (acc1.x * acc1.x + acc1.y * acc1.y) + (acc1.z * acc1.z + acc1.w * acc1.w);
                 }
                 if (ok2) {
-                    *reinterpret_cast<float4*>(outp + o2) = acc2;
+                    if (a.dbg != 31) *reinterpret_cast<float4*>(outp + o2) = acc2;
                     fs0 += (acc2.x + acc2.y) + (acc2.z + acc2.w);
                     fs1 += (acc2.x * acc2.x + acc2.y * acc2.y) + (acc2.z * acc2.z + acc2.w * acc2.w);
                 }

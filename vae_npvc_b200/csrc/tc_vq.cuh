@@ -44,7 +44,7 @@ vq_lookup_tc_stream_kernel(const __grid_constant__ CUtensorMap map_z, const __gr
     __shared__ __align__(8) uint64_t tmem_empty_bar[2];
     __shared__ uint32_t tmem_slot;
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler
     const int64_t n0 = (int64_t)blockIdx.x * VQT_BM;
     const int chunks = (a.K + VQT_BN - 1) / VQT_BN;
     const int kd = (a.D + VQT_BK - 1) / VQT_BK;
@@ -70,8 +70,10 @@ vq_lookup_tc_stream_kernel(const __grid_constant__ CUtensorMap map_z, const __gr
     const uint32_t tmem_base = tmem_slot;
     pdl_wait();      // everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel's tail
 
+    // producer and issuer loops are walked by their whole (converged) warp so that counters and descriptors live in
+    // uniform registers; one elected lane issues the TMA / tcgen05 instructions (see conv_fwd_tc_kernel)
     if (warp == 0) {
-        if (lane == 0) {
+        {
             int kc = 0;
             for (int ch = 0; ch < chunks; ch++)
                 for (int pr = 0; pr < 6; pr++)
@@ -79,13 +81,16 @@ vq_lookup_tc_stream_kernel(const __grid_constant__ CUtensorMap map_z, const __gr
                         const int s = kc % VQT_STAGES;
                         if (kc >= VQT_STAGES) mbar_wait(&empty_bar[s], ((kc / VQT_STAGES) - 1) & 1);
                         uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
-                        mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-                        tma_load_3d(sa, &map_z, &full_bar[s], c * VQT_BK, (int)n0, c_pair_a[pr]);
-                        tma_load_3d(sa + A_BYTES, &map_e, &full_bar[s], c * VQT_BK, ch * VQT_BN, c_pair_b[pr]);
+                        if (elect_one()) {
+                            mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                            tma_load_3d(sa, &map_z, &full_bar[s], c * VQT_BK, (int)n0, c_pair_a[pr]);
+                            tma_load_3d(sa + A_BYTES, &map_e, &full_bar[s], c * VQT_BK, ch * VQT_BN, c_pair_b[pr]);
+                        }
+                        __syncwarp();
                     }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {
             constexpr uint32_t idesc = instr_desc_bf16(VQT_BM, VQT_BN, 0, 0);
             int kc = 0;
             for (int ch = 0; ch < chunks; ch++) {
@@ -101,13 +106,17 @@ vq_lookup_tc_stream_kernel(const __grid_constant__ CUtensorMap map_z, const __gr
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
                     const uint32_t sb = sa + A_BYTES;
+                    if (elect_one()) {
 #pragma unroll
-                    for (int j = 0; j < VQT_BK / 16; j++)
-                        umma_bf16(tacc, smem_desc_sw128(sa + j * 32, 16, 1024), smem_desc_sw128(sb + j * 32, 16, 1024),
-                                  idesc, (i | j) != 0);
-                    umma_commit(&empty_bar[s]);
+                        for (int j = 0; j < VQT_BK / 16; j++)
+                            umma_bf16(tacc, smem_desc_sw128(sa + j * 32, 16, 1024), smem_desc_sw128(sb + j * 32, 16, 1024),
+                                      idesc, (i | j) != 0);
+                        umma_commit(&empty_bar[s]);
+                    }
+                    __syncwarp();
                 }
-                umma_commit(&tmem_full_bar[buf]);
+                if (elect_one()) umma_commit(&tmem_full_bar[buf]);
+                __syncwarp();
             }
         }
     } else {
@@ -218,7 +227,7 @@ vq_lookup_tc_kernel(const __grid_constant__ CUtensorMap map_z, const __grid_cons
     __shared__ __align__(8) uint64_t tmem_empty_bar[2];
     __shared__ uint32_t tmem_slot;
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler
     const int64_t n0 = (int64_t)blockIdx.x * VQT_BM;
     const int chunks = (a.K + VQR_BN - 1) / VQR_BN;
     const int kd = (a.D + VQT_BK - 1) / VQT_BK;
@@ -248,33 +257,40 @@ vq_lookup_tc_kernel(const __grid_constant__ CUtensorMap map_z, const __grid_cons
     pdl_wait();      // everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel's tail
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ===== producer: the frames once, then the codebook planes chunk by chunk =====
-            mbar_expect_tx(&a_bar, (uint32_t)3 * kd * VQR_A_BYTES);
-            for (int pl = 0; pl < 3; pl++)
-                for (int c = 0; c < kd; c++)
-                    tma_load_3d(smem_a + (size_t)(pl * kd + c) * VQR_A_BYTES, &map_z, &a_bar, c * VQT_BK, (int)n0, pl);
+        {
+            // ===== producer (converged warp, elected lane issues): the frames once, then the codebook planes chunk
+            // by chunk =====
+            if (elect_one()) {
+                mbar_expect_tx(&a_bar, (uint32_t)3 * kd * VQR_A_BYTES);
+                for (int pl = 0; pl < 3; pl++)
+                    for (int c = 0; c < kd; c++)
+                        tma_load_3d(smem_a + (size_t)(pl * kd + c) * VQR_A_BYTES, &map_z, &a_bar, c * VQT_BK, (int)n0, pl);
+            }
+            __syncwarp();
             int s = 0, i = 0;
             uint32_t ph = 1;
             for (int ch = 0; ch < chunks; ch++)
                 for (int pb = 2; pb >= 0; pb--)
                     for (int c = 0; c < kd; c++, i++) {
                         if (i >= STAGES) mbar_wait(&empty_bar[s], ph);
-                        mbar_expect_tx(&full_bar[s], VQR_B_BYTES);
-                        tma_load_3d(smem_b + (size_t)s * VQR_B_BYTES, &map_e, &full_bar[s], c * VQT_BK, ch * VQR_BN, pb);
+                        if (elect_one()) {
+                            mbar_expect_tx(&full_bar[s], VQR_B_BYTES);
+                            tma_load_3d(smem_b + (size_t)s * VQR_B_BYTES, &map_e, &full_bar[s], c * VQT_BK, ch * VQR_BN, pb);
+                        }
+                        __syncwarp();
                         if (++s == STAGES) { s = 0; ph ^= 1; }
                     }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ===== MMA issuer =====
+        {
+            // ===== MMA issuer (converged warp, elected lane issues) =====
             constexpr uint32_t idesc = instr_desc_bf16(VQT_BM, VQR_BN, 0, 0);
             mbar_wait(&a_bar, 0);
             tc_fence_after();
             const uint32_t sa0 = smem_u32(smem_a), sb0 = smem_u32(smem_b);
             int s = 0;
             uint32_t ph = 0;
-            bool ready = mbar_test(&full_bar[0], 0);
+            bool ready = __all_sync(0xffffffffu, mbar_test(&full_bar[0], 0));
             const int per_chunk = 3 * kd;
             const int total = chunks * per_chunk;
             int i = 0;
@@ -294,24 +310,30 @@ vq_lookup_tc_kernel(const __grid_constant__ CUtensorMap map_z, const __grid_cons
                         uint32_t ph1 = ph;
                         if (s1 == STAGES) { s1 = 0; ph1 ^= 1; }
                         bool next_ready = false;
-                        if (i + 1 < total) next_ready = mbar_test(&full_bar[s1], ph1);
+                        if (i + 1 < total) next_ready = __all_sync(0xffffffffu, mbar_test(&full_bar[s1], ph1));
                         const uint64_t db = smem_desc_sw128(sb0 + (uint32_t)s * VQR_B_BYTES, 16, 1024);
                         // frame planes paired with codebook plane pb: pb = 2 -> {0}; 1 -> {1, 0}; 0 -> {2, 1, 0}
-                        for (int pa = 2 - pb; pa >= 0; pa--) {
-                            const uint64_t da = smem_desc_sw128(sa0 + (uint32_t)(pa * kd + c) * VQR_A_BYTES, 16, 1024);
+                        if (elect_one()) {
+                            uint32_t acc1 = acc;
+                            for (int pa = 2 - pb; pa >= 0; pa--) {
+                                const uint64_t da = smem_desc_sw128(sa0 + (uint32_t)(pa * kd + c) * VQR_A_BYTES, 16, 1024);
 #pragma unroll
-                            for (int j = 0; j < VQT_BK / 16; j++) {
-                                umma_bf16(tacc, da + 2 * j, db + 2 * j, idesc, acc);
-                                acc = 1;
+                                for (int j = 0; j < VQT_BK / 16; j++) {
+                                    umma_bf16(tacc, da + 2 * j, db + 2 * j, idesc, acc1);
+                                    acc1 = 1;
+                                }
                             }
+                            umma_commit(&empty_bar[s]);
                         }
-                        umma_commit(&empty_bar[s]);
+                        __syncwarp();
+                        acc = 1;
                         ready = next_ready;
                         s = s1;
                         ph = ph1;
                     }
                 }
-                umma_commit(&tmem_full_bar[buf]);
+                if (elect_one()) umma_commit(&tmem_full_bar[buf]);
+                __syncwarp();
             }
         }
     } else {

@@ -79,7 +79,7 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     __shared__ __align__(8) uint64_t recv_bar;
     __shared__ uint32_t tmem_slot;
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler
     const int STAGES = a.nstages;
     const int ks = gridDim.x, kr = blockIdx.x;
     const int ntiles = (a.ncols + BN - 1) / BN;
@@ -115,8 +115,9 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     pdl_wait();      // everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel's tail
 
     if (warp == 0) {
-        if (lane == 0 && nk > 0) {
-            // ===== TMA producer (one thread; no divisions in the loop) =====
+        if (nk > 0) {
+            // ===== TMA producer: the converged warp walks the ring, one elected lane issues (see conv_fwd_tc_kernel);
+            // no divisions in the loop =====
             int pr = 0;
             int bb = kb0 / tblocks, tb = kb0 - bb * tblocks;
             int s = 0;
@@ -129,31 +130,34 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                 if (i >= STAGES) mbar_wait(&empty_bar[s], ph);
                 uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
                 uint8_t* sb = sa + A_BYTES;
-                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-                if (a.a4d) {
-                    tma_load_4d(sa, &map_a, &full_bar[s], 0, t0 + off_a, m0 / 64, pl_a * a.B + bb);
-                } else {
+                if (elect_one()) {
+                    mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                    if (a.a4d) {
+                        tma_load_4d(sa, &map_a, &full_bar[s], 0, t0 + off_a, m0 / 64, pl_a * a.B + bb);
+                    } else {
 #pragma unroll
-                    for (int m = 0; m < WG_BM / 64; m++)
-                        tma_load_3d(sa + m * WG_BOX_BYTES, &map_a, &full_bar[s], m0 + m * 64, t0 + off_a, pl_a * a.B + bb);
-                }
-                if (a.b4d) {
-                    tma_load_4d(sb, &map_b, &full_bar[s], 0, t0 + off_b, n0 / 64, pl_b * a.B + bb);
-                } else {
+                        for (int m = 0; m < WG_BM / 64; m++)
+                            tma_load_3d(sa + m * WG_BOX_BYTES, &map_a, &full_bar[s], m0 + m * 64, t0 + off_a, pl_a * a.B + bb);
+                    }
+                    if (a.b4d) {
+                        tma_load_4d(sb, &map_b, &full_bar[s], 0, t0 + off_b, n0 / 64, pl_b * a.B + bb);
+                    } else {
 #pragma unroll
-                    for (int n = 0; n < BN / 64; n++)
-                        tma_load_3d(sb + n * WG_BOX_BYTES, &map_b, &full_bar[s], n0 + n * 64, t0 + off_b, pl_b * a.B + bb);
+                        for (int n = 0; n < BN / 64; n++)
+                            tma_load_3d(sb + n * WG_BOX_BYTES, &map_b, &full_bar[s], n0 + n * 64, t0 + off_b, pl_b * a.B + bb);
+                    }
                 }
+                __syncwarp();
                 if (++tb == tblocks) { tb = 0; ++bb; }
                 if (bb * tblocks + tb == kb1) { bb = kb0 / tblocks; tb = kb0 - bb * tblocks; ++pr; }   // next plane pair
                 if (++s == STAGES) { s = 0; ph ^= 1; }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ===== MMA issuer =====
+        {
+            // ===== MMA issuer (converged warp, elected lane) =====
             constexpr uint32_t idesc = instr_desc_bf16(WG_BM, BN, /*a_mn=*/1, /*b_mn=*/1);
-            bool ready = nk > 0 && mbar_test(&full_bar[0], 0);
+            bool ready = nk > 0 && __all_sync(0xffffffffu, mbar_test(&full_bar[0], 0));
             int s = 0;
             uint32_t ph = 0;
             for (int i = 0; i < nk; i++) {
@@ -163,19 +167,23 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                 uint32_t ph1 = ph;
                 if (s1 == STAGES) { s1 = 0; ph1 ^= 1; }
                 bool next_ready = false;
-                if (i + 1 < nk) next_ready = mbar_test(&full_bar[s1], ph1);
+                if (i + 1 < nk) next_ready = __all_sync(0xffffffffu, mbar_test(&full_bar[s1], ph1));
                 const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
                 // MN-major: 16 frame rows of 128 B = 2048 B per UMMA_K (+128 in 16-byte descriptor units);
                 // 64-channel boxes are WG_BOX_BYTES apart (LBO); 8-row swizzle atoms 1024 B apart (SBO)
                 const uint64_t da = smem_desc_sw128(sa, WG_BOX_BYTES, 1024), db = smem_desc_sw128(sa + A_BYTES, WG_BOX_BYTES, 1024);
+                if (elect_one()) {
 #pragma unroll
-                for (int j = 0; j < WG_KT / 16; j++) umma_bf16(tmem_base, da + 128 * j, db + 128 * j, idesc, (i | j) != 0);
-                umma_commit(&empty_bar[s]);
+                    for (int j = 0; j < WG_KT / 16; j++) umma_bf16(tmem_base, da + 128 * j, db + 128 * j, idesc, (i | j) != 0);
+                    umma_commit(&empty_bar[s]);
+                }
+                __syncwarp();
                 ready = next_ready;
                 s = s1;
                 ph = ph1;
             }
-            umma_commit(&tmem_full_bar);
+            if (elect_one()) umma_commit(&tmem_full_bar);
+            __syncwarp();
         }
     }
 
