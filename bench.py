@@ -42,7 +42,7 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi SM clock / throttle-reason samples during the timed region."""
+    """SM clock / throttle-reason samples during the timed region (NVML, else the nvidia-smi query)."""
     Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
          'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
 
@@ -50,7 +50,27 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.index, self.rows, self._stop_evt = index, [], threading.Event()
 
+    def _nvml(self):
+        """NVML (what nvidia-smi itself reads) sampled every 2 ms: a 50 ms timed region gets ~25 samples."""
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(self.index)
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        bits = ((0x8, 2), (0x40, 3), (0x20, 4), (0x4, 5))        # hw_slowdown, hw_thermal, sw_thermal, sw_power_cap
+        while not self._stop_evt.is_set():
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            row = [str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(mx), '', '', '', '']
+            for bit, col in bits:
+                row[col] = 'Active' if (r & bit) else 'Not Active'
+            self.rows.append(row)
+            self._stop_evt.wait(0.002)
+
     def run(self):
+        try:
+            self._nvml()
+            return
+        except Exception:
+            pass
         while not self._stop_evt.is_set():
             try:
                 out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
@@ -173,7 +193,8 @@ def run_ours(args, rank, world):
     cfg = dict(arch)
     warm = max(3, args.warmup)
     cfg.update(model_type='vae_npvc_b200.model.vqvae', precision=args.precision, cuda_graph=not args.no_graph,
-               overlap_allreduce=not bool(os.environ.get('VNB_NO_OVERLAP')),
+               overlap_allreduce=not bool(os.environ.get('VNB_NO_OVERLAP')), allreduce=os.environ.get('VNB_ALLREDUCE', 'multimem'),
+               allreduce_blocks=int(os.environ.get('VNB_AR_BLOCKS', 0)),
                graph_warmup=min(3, warm - 1), learning_rate=1e-3, max_grad_norm=10, lr_scheduler='StepLR',
                lr_param={'step_size': 100000, 'gamma': 0.5, 'last_epoch': -1})
     torch.manual_seed(777)

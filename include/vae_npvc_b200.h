@@ -237,6 +237,15 @@ int vnb_adam_step(float* p, const float* g, float* m, float* v, int64_t n, const
                   float max_norm, float lr, double beta1, double beta2, float eps, float* state,
                   int step_size, float gamma, void* stream);
 
+/* ---- data-parallel gradient mean over NVSwitch multicast memory (collective 1).  The reference
+ * has no multi-GPU path (train.py drives one device); this replaces the library all-reduce a DDP wrapper would
+ * issue.  mc_base = multicast address of the symmetric fp32 gradient buffer, [offset, offset+count) elements
+ * (both multiples of 4) are summed over all ranks by the switch, scaled and broadcast back in place.  flags =
+ * device array of `world` pointers to each rank's zero-initialised flag words (>= nblocks*world uint32).  Every
+ * rank launches the same sequence of calls. */
+int vnb_allreduce_multimem(void* mc_base, int64_t offset, int64_t count, const void* flags, int rank, int world,
+                           float scale, int nblocks, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -82,17 +82,42 @@ class Encoder(nn.Module, _WeightNormMixin):
     def forward(self, input):
         h = input
         pending = ACT_NONE                  # a LeakyReLU entry is fused into the next conv's operand
-        for m in self.encode:
+        for i, m in enumerate(self.encode):
             if isinstance(m, nn.LeakyReLU):
                 pending = ACT_LRELU
+                continue
             elif isinstance(m, nn.Conv1d):
                 h = run_conv(m, h, act=pending)
                 pending = ACT_NONE
             else:
                 assert pending == ACT_NONE
                 h = m(h)
+            h = _mark(h, 'encoder.encode.%d' % i)
         assert pending == ACT_NONE
         return h
+
+
+# ---- gradient-ready notifications for the data-parallel trainer ---------------------------------
+_GRAD_READY = None
+
+
+def set_grad_ready_callback(cb):
+    """``cb(name)`` is called during backward when the gradient wrt the OUTPUT of sub-module ``name`` exists, i.e.
+    when every module after ``name`` in forward order has been back-propagated ('decoder' = the decoder's input).
+    The data-parallel trainer starts all-reducing the finished part of the flat gradient buffer from there
+    (trainer/basic.py); None switches the hooks off."""
+    global _GRAD_READY
+    _GRAD_READY = cb
+
+
+def _mark(t, name):
+    cb = _GRAD_READY
+    if cb is not None and torch.is_tensor(t) and t.requires_grad:
+        def hook(grad, cb=cb, name=name):
+            cb(name)
+            return None
+        t.register_hook(hook)
+    return t
 
 
 class Decoder(nn.Module, _WeightNormMixin):
@@ -128,11 +153,12 @@ class Decoder(nn.Module, _WeightNormMixin):
         x, c = input
         c = c[:, :, 0].contiguous()
         skip = None
-        for layer in self.layers:
+        for i, layer in enumerate(self.layers):
             if isinstance(layer, DeConv1d_Layernorm_GLU_ResSkip):
                 x, skip = layer.forward_acc(x, c, skip)
             else:
                 x = run_conv(layer, x)
+            x = _mark(x, 'decoder.layers.%d' % i)
         # x_out * sqrt(1/len(layers)) then ReLU -> 1x1 -> ReLU -> 1x1 (vqvae.py:316-317)
         scale = math.sqrt(1.0 / len(self.layers))
         o = run_conv(self.final_layer[1], skip.transpose(1, 2), act=ACT_RELU, scale=scale)
@@ -184,11 +210,7 @@ class Model(nn.Module):
         z = self.encoder(x)
         z_vq, z_qut_loss, z_enc_loss, vq_detail = self.quantizer(z)
         z_vq = self.jitter(z_vq)
-        hook = getattr(self, '_decoder_backward_done', None)
-        if hook is not None and torch.is_tensor(z_vq) and z_vq.requires_grad:
-            # fires when the gradient wrt the decoder input exists, i.e. the whole decoder has been back-propagated:
-            # the data-parallel trainer starts all-reducing the decoder's gradients there (trainer/basic.py)
-            z_vq.register_hook(hook)
+        z_vq = _mark(z_vq, 'decoder')       # gradient wrt the decoder input: the whole decoder is back-propagated
         xhat = self.decoder((z_vq, y))
         x_loss = log_loss(xhat, x)
         loss = x_loss + z_qut_loss + self.beta * z_enc_loss

@@ -18,6 +18,7 @@ B200-native differences (all behind the same API):
 New optional config keys (defaults keep the reference behaviour): ``cuda_graph`` (True),
 ``graph_warmup`` (3), ``precision`` ('bf16' | 'fp32'), ``device`` ('cuda'), ``wgrad_stream`` (True).
 """
+import contextlib
 from importlib import import_module
 
 import numpy as np
@@ -27,6 +28,7 @@ from .. import functional as Fn
 from .. import prims as Pm
 from ..bank import WeightBank
 from ..model import layers_vq as _lvq
+from ..model import vqvae as _model_mod
 
 
 class FlatAdam(object):
@@ -110,6 +112,8 @@ class Trainer(object):
         self.model = model.to(self.device)
         self.learning_rate = learning_rate
         self.max_grad_norm = max_grad_norm
+        self._allreduce_kind = str(config.get('allreduce', 'multimem'))      # 'multimem' (NVSwitch, own kernel) | 'nccl'
+        self._allreduce_blocks = int(config.get('allreduce_blocks', 0))     # 0 = 16 CTAs at 2 ranks, 8 beyond (measured)
         self._flatten()
         self.optimizer = FlatAdam(self._params, self._flat_p, self._flat_g, learning_rate)
         # all conv weights materialised / back-propagated through weight-norm by one kernel each per step
@@ -122,10 +126,10 @@ class Trainer(object):
             self.scheduler = None
         self.iteration = 0
         self.model.train()
-        # contiguous slice of the flat buffers that holds the decoder's parameters (bucketed all-reduce)
+        # bucketed all-reduce: trigger name (model/vqvae.py set_grad_ready_callback) -> slice of the flat buffers
         self._comm = torch.cuda.Stream(device=self.device) if self._side_wanted() else None
-        self._dec_range = self._param_range('decoder.')
-        self._dec_reduced = False
+        self._buckets = self._plan_buckets()
+        self._reduced = []
         self.overlap_allreduce = bool(config.get('overlap_allreduce', True))
 
         self.use_graph = bool(config.get('cuda_graph', True)) and self.device.type == 'cuda'
@@ -141,30 +145,58 @@ class Trainer(object):
     def _side_wanted(self):
         return self.device.type == 'cuda'
 
-    def _param_range(self, prefix):
-        """(lo, hi) element range of the parameters whose name starts with ``prefix`` when they are contiguous in
-        the flat buffers, else None."""
-        off, lo, hi, seen_after = 0, None, None, False
+    def _plan_buckets(self):
+        """Slices of the flat gradient buffer that are complete at known points of the backward pass, keyed by the
+        model's gradient-ready notification (model/vqvae.py set_grad_ready_callback): the upper half of the
+        decoder's blocks (+ final layers) when the gradient reaches the middle of the decoder, the rest of the
+        decoder at the decoder's input, the upper half of the encoder in the middle of the encoder.  What remains
+        (lower encoder half, codebook, speaker table) is reduced after backward.  {} when the parameter order does
+        not allow it (sub-module slices not contiguous)."""
+        spans, order, off = {}, [], 0
         for n, p in self.model.named_parameters():
             if not p.requires_grad:
                 continue
-            if n.startswith(prefix):
-                if seen_after:
-                    return None
-                if lo is None:
-                    lo = off
-                hi = off + p.numel()
-            elif lo is not None:
-                seen_after = True
+            parts = n.split('.')
+            key = '.'.join(parts[:3]) if parts[0] in ('encoder', 'decoder') else parts[0]
+            if key not in spans:
+                if order and spans[order[-1]][1] != off:
+                    return {}
+                spans[key] = [off, off]
+                order.append(key)
+            elif spans[key][1] != off:
+                return {}                                   # a sub-module's parameters are not contiguous
+            spans[key][1] = off + p.numel()
             off += p.numel()
-        return (lo, hi) if lo is not None else None
+        dec = [k for k in order if k.startswith('decoder.layers.')]
+        enc = [k for k in order if k.startswith('encoder.encode.')]
+        dec_all = [k for k in order if k.startswith('decoder.')]
+        plan = {}
+        for k in spans:                     # 16-byte aligned bucket starts (the multimem kernel moves float4): a
+            spans[k][0] = (spans[k][0] + 3) // 4 * 4    # start moved UP leaves those elements to the later bucket
+
+        def _end(key):                      # aligned end of a slice = aligned start of the next one (or the buffer end)
+            i = order.index(key)
+            return spans[order[i + 1]][0] if i + 1 < len(order) else (off + 3) // 4 * 4
+
+        if len(dec) >= 4 and dec_all and order.index(dec_all[-1]) - order.index(dec_all[0]) == len(dec_all) - 1:
+            cut = len(dec) // 2
+            plan[dec[cut - 1]] = (spans[dec[cut]][0], _end(dec_all[-1]))
+            plan['decoder'] = (spans[dec_all[0]][0], spans[dec[cut]][0])
+        elif dec_all and order.index(dec_all[-1]) - order.index(dec_all[0]) == len(dec_all) - 1:
+            plan['decoder'] = (spans[dec_all[0]][0], _end(dec_all[-1]))
+        if len(enc) >= 4 and order.index(enc[-1]) - order.index(enc[0]) == len(enc) - 1:
+            cut = len(enc) // 2
+            plan[enc[cut - 1]] = (spans[enc[cut]][0], _end(enc[-1]))
+        return plan
 
     # ---- flat parameter / gradient buffers -------------------------------------------------------
     def _flatten(self):
         params = [p for p in self.model.parameters() if p.requires_grad]
         total = sum(p.numel() for p in params)
         flat_p = torch.empty(total, dtype=torch.float32, device=self.device)
-        flat_g = torch.zeros(total, dtype=torch.float32, device=self.device)
+        flat_g = self._symmetric_grad_buffer(total)
+        if flat_g is None:
+            flat_g = torch.zeros(total, dtype=torch.float32, device=self.device)
         off = 0
         for p in params:
             n = p.numel()
@@ -173,6 +205,55 @@ class Trainer(object):
             p.grad = flat_g[off:off + n].view_as(p)
             off += n
         self._params, self._flat_p, self._flat_g = params, flat_p, flat_g
+        self._grad_len = (total + 3) // 4 * 4 if self._mc is not None else total      # symmetric buffer is padded
+
+    def _symmetric_grad_buffer(self, total):
+        """Data parallel on NVSwitch: the flat gradient buffer is allocated in symmetric memory with a multicast
+        mapping so that csrc/allreduce.cu can have the switch sum and broadcast it (multimem.ld_reduce / .st).
+        The rendezvous is plumbing (torch symmetric memory); the collective itself is our kernel.  Returns None -
+        the NCCL all-reduce is used then - when there is one rank, no CUDA, ``allreduce: nccl`` is configured or
+        the rendezvous / multicast mapping is not available."""
+        self._mc = None
+        dist = _dist()
+        if dist is None or self.device.type != 'cuda' or self._allreduce_kind != 'multimem':
+            return None
+        try:
+            import torch.distributed._symmetric_memory as symm
+            world, rank = dist.get_world_size(), dist.get_rank()
+            group = dist.group.WORLD
+            padded = (total + 3) // 4 * 4
+            buf = symm.empty(padded, dtype=torch.float32, device=self.device)
+            buf.zero_()
+            hb = symm.rendezvous(buf, group)
+            nblocks = int(self._allreduce_blocks) or (16 if world <= 2 else 8)
+            flags = symm.empty(128 * world, dtype=torch.int32, device=self.device)
+            flags.zero_()
+            hf = symm.rendezvous(flags, group)
+            mc = int(hb.multicast_ptr)
+            ok = torch.tensor([1 if mc != 0 else 0], device=self.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)         # also orders the zero-fills before any peer's first signal
+            torch.cuda.synchronize()
+            if int(ok) == 0:
+                return None
+            self._mc = dict(mc=mc, buf=buf, flags=flags, handles=(hb, hf), rank=rank, world=world, nblocks=nblocks,
+                            flag_ptrs=torch.tensor([int(p) for p in hf.buffer_ptrs], dtype=torch.int64, device=self.device))
+            return buf[:total]
+        except Exception as e:                                   # no NVSwitch multicast on this machine / torch build
+            import warnings
+            warnings.warn('multimem all-reduce unavailable (%s: %s); using NCCL' % (type(e).__name__, e))
+            self._mc = None
+            return None
+
+    def _all_reduce_mean(self, lo, hi):
+        """Mean over ranks of flat_g[lo:hi] on the current stream (lo, hi multiples of 4 on the multimem path)."""
+        import torch.distributed as dist
+        if self._mc is not None:
+            from .. import _C
+            m = self._mc
+            _C.call('allreduce_multimem', m['mc'], lo, hi - lo, m['flag_ptrs'], m['rank'], m['world'], 1.0 / m['world'],
+                    m['nblocks'])
+        else:
+            dist.all_reduce(self._flat_g[lo:hi])
 
     # ---- one optimisation step on device-resident inputs -----------------------------------------
     def _step_body(self, x, y, jitter_src=None):
@@ -189,31 +270,39 @@ class Trainer(object):
             if jitter_src is not None:
                 self.model.jitter.sources = lambda length: jitter_src
             dist = _dist()
-            self._dec_reduced = False
-            if (dist is not None and self._side is not None and self._dec_range is not None and self.overlap_allreduce):
-                self.model._decoder_backward_done = self._reduce_decoder_grads       # registered during forward
+            self._reduced = []
+            overlap = (dist is not None and self._allreduce_kind != 'none' and self._side is not None and self._comm is not None and bool(self._buckets)
+                       and self.overlap_allreduce)
+            if overlap:
+                _model_mod.set_grad_ready_callback(self._grad_ready)                 # hooks registered during forward
             output, loss, detail = self.model([x, y])
             loss.backward()
-            self.model._decoder_backward_done = None
+            _model_mod.set_grad_ready_callback(None)
             if self._side is not None:
                 torch.cuda.current_stream().wait_stream(self._side)
             # data parallel: sum the RAW weight gradients (weight-norm's backward is linear in dW, so it commutes
-            # with the sum); the decoder's two thirds of the buffer were already started behind its backward pass
-            if dist is not None:
-                if self._dec_reduced:
-                    lo, hi = self._dec_range
-                    if lo > 0:
-                        dist.all_reduce(self._flat_g[:lo])
-                    if hi < self._flat_g.numel():
-                        dist.all_reduce(self._flat_g[hi:])
-                    torch.cuda.current_stream().wait_stream(self._comm)
-                else:
-                    dist.all_reduce(self._flat_g)
+            # with the sum); the slices that completed during backward are already in flight on the comm stream
+            if dist is not None and self._allreduce_kind != 'none':       # 'none': independent replicas (diagnostic)
+                # every collective of the step goes through the communication stream (one ordered sequence on
+                # every rank; the multimem kernel's flag words are per sequence)
+                comm = self._comm if (self._comm is not None and self.device.type == 'cuda') else None
+                if comm is not None:
+                    comm.wait_stream(torch.cuda.current_stream())
+                with (torch.cuda.stream(comm) if comm is not None else contextlib.nullcontext()):
+                    pos, total = 0, self._grad_len
+                    for lo, hi in sorted(self._reduced):
+                        if lo > pos:
+                            self._all_reduce_mean(pos, lo)
+                        pos = max(pos, hi)
+                    if pos < total:
+                        self._all_reduce_mean(pos, total)
+                if comm is not None:
+                    torch.cuda.current_stream().wait_stream(comm)
             self.bank.finish_backward()
-            if dist is not None:
-                self._flat_g.mul_(1.0 / dist.get_world_size())
+            if dist is not None and self._mc is None and self._allreduce_kind != 'none':
+                self._flat_g.mul_(1.0 / dist.get_world_size())      # the multimem kernel already scaled
         finally:
-            self.model._decoder_backward_done = None
+            _model_mod.set_grad_ready_callback(None)
             if hasattr(Pm, 'stats_arena_end'):
                 Pm.stats_arena_end()
             Fn.set_side_stream(None)
@@ -225,19 +314,18 @@ class Trainer(object):
         scal = torch.stack([detail[k].t.reshape(()).float() for k in keys])
         return keys, scal
 
-    def _reduce_decoder_grads(self, grad):
-        """Tensor hook on the decoder input's gradient: every decoder layer has been back-propagated (its weight
-        gradients are queued on the side stream), so their slice of the flat gradient buffer is all-reduced on a
-        communication stream while the quantiser and the encoder are still being back-propagated."""
-        import torch.distributed as dist
-        main = torch.cuda.current_stream()
-        self._comm.wait_stream(main)
+    def _grad_ready(self, name):
+        """Called from a tensor hook during backward (model/vqvae.py _mark): the modules after ``name`` have been
+        back-propagated and their weight-gradient GEMMs are queued on the side stream, so their slice of the flat
+        gradient buffer is all-reduced on the communication stream while the rest of backward runs."""
+        rng = self._buckets.get(name)
+        if rng is None or rng in self._reduced:
+            return
+        self._comm.wait_stream(torch.cuda.current_stream())
         self._comm.wait_stream(self._side)
-        lo, hi = self._dec_range
         with torch.cuda.stream(self._comm):
-            dist.all_reduce(self._flat_g[lo:hi])
-        self._dec_reduced = True
-        return None
+            self._all_reduce_mean(rng[0], rng[1])
+        self._reduced.append(rng)
 
     def _capture(self, x, y):
         from .. import _C
