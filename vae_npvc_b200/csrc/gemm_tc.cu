@@ -299,6 +299,45 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
         const int g = (a.gn_sums && col_ok) ? co / cg : -1;
         float fs0 = 0.f, fs1 = 0.f;
         const size_t row0 = (size_t)b * Tn + t0 + r_base;
+        // full tiles (every tile of the training shapes): no per-element predicates, ~20 instructions per row.  With
+        // 2 warps per scheduler this loop is issue-bound; the generic loop below costs ~70 instructions per row
+        // (measured 4.4k cycles for a 128 x 128 tile, against ~1.1k for the TMEM drain before it)
+        const bool full = vec_ok && co0 + BN <= Cout && t0 + TC_BM <= Tn && (rows_own % RPP) == 0;
+        if (full) {
+            const int iters = rows_own / RPP;
+            const size_t o0 = (row0 + rsub) * Cout + co;
+            const size_t ostep = (size_t)RPP * Cout;
+            const uint32_t rstep = RPP * PITCH * 4;
+            const uint32_t own0 = own_base + (uint32_t)rsub * (PITCH * 4), recv0 = recv_base + (uint32_t)rsub * (PITCH * 4);
+            if (ks == 1 && !resid && !accum) {
+#pragma unroll 4
+                for (int it = 0; it < iters; it++) {
+                    const float4 x = ld_shared_f4(own0 + (uint32_t)it * rstep);
+                    const float4 v = make_float4(x.x + bv.x, x.y + bv.y, x.z + bv.z, x.w + bv.w);
+                    *reinterpret_cast<float4*>(outp + o0 + it * ostep) = v;
+                    fs0 += (v.x + v.y) + (v.z + v.w);
+                    fs1 += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+                }
+            } else {
+#pragma unroll 2
+                for (int it = 0; it < iters; it++) {
+                    float4 v = bv;
+                    float4 r1 = make_float4(0.f, 0.f, 0.f, 0.f), u1 = r1;
+                    if (resid) r1 = *reinterpret_cast<const float4*>(resid + o0 + it * ostep);
+                    if (accum) u1 = *reinterpret_cast<const float4*>(outp + o0 + it * ostep);
+#pragma unroll 1
+                    for (int p = 0; p < ks; p++) {
+                        const uint32_t base = p == kr ? own0 : recv0 + (uint32_t)(p < kr ? p : p - 1) * slot_stride;
+                        const float4 x = ld_shared_f4(base + (uint32_t)it * rstep);
+                        v.x += x.x; v.y += x.y; v.z += x.z; v.w += x.w;
+                    }
+                    v.x += r1.x + u1.x; v.y += r1.y + u1.y; v.z += r1.z + u1.z; v.w += r1.w + u1.w;
+                    *reinterpret_cast<float4*>(outp + o0 + it * ostep) = v;
+                    fs0 += (v.x + v.y) + (v.z + v.w);
+                    fs1 += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+                }
+            }
+        } else
 #pragma unroll 1
         for (int rl = rsub; rl < rows_own; rl += 2 * RPP) {
             const int rl2 = rl + RPP;
@@ -533,21 +572,23 @@ int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int
         const uint32_t off = ((ring > staging ? ring : staging) + 1023u) & ~1023u;
         return off + recv + 1024 <= 227 * 1024 - 1024;
     };
-    // cost model in SM cycles, fitted to the VNB_TC_DBG=9 timelines (profiles/r01_conv_tc_timeline.txt): ~610
-    // cycles per single-chunk stage whatever the tile (the single issuing thread, not the tensor pipe, is the
-    // limit; 770 at BN=256 where the 48 KB stages meet the L2 limit), ~930 / 1300 per double-chunk stage, a fixed
-    // ~5.5k cycles of launch / TMEM / cold instruction fetch / epilogue, ~5k more for a split-K exchange
+    // cost model in SM cycles, fitted to the VNB_TC_DBG=9 timelines of the final kernel (profiles/
+    // r01_conv_tc_timeline.txt, sweep over BN x ksplit).  With the converged issuing warp the k-loop is bound by what
+    // one SM can take in from L2 (~65-75 B/cycle): per 64-channel chunk ~370 cycles at BN=64 (24 KB), ~430 at BN=128
+    // (32 KB), ~690 at BN=256; ~20 % more when a stage holds one chunk.  Fixed part (launch, TMEM, first load,
+    // TMEM drain, store): 4.7k / 6.3k cycles for BN = 64 / 128, and ~4k more when a cluster exchanges partials.
     int bn = 64, ks = 1;
     int64_t best = INT64_MAX;
     for (int cand = 64; cand <= 256; cand *= 2) {
         if (cand > 64 && Cout <= cand / 2) break;                 // tile wider than needed
+        const int ci = cand == 64 ? 0 : cand == 128 ? 1 : 2;
+        static const int64_t per_chunk[2][3] = {{450, 530, 770}, {372, 429, 690}};
+        static const int64_t fixed[3][4] = {{4700, 8600, 8900, 9500}, {6300, 10600, 11600, 12400}, {9000, 14000, 15000, 16000}};
         const int64_t tiles = mt * ceil_div(Cout, cand);
-        const int64_t per_stage = kch == 1 ? (cand == 256 ? 770 : 610) : (cand == 256 ? 1300 : 930);
-        for (int k = 1; k <= 8; k *= 2) {
+        for (int k = 1, ki = 0; k <= 8; k *= 2, ki++) {
             if (k > nkc || !fits(cand, k)) break;
             const int64_t waves = (tiles * k + 147) / 148;
-            const int64_t cost = waves * ((int64_t)ceil_div(nkc, k) * per_stage + 5500 +
-                                          (k > 1 ? 4500 + 250 * k : 0) + (cand == 256 ? 2000 : 0));
+            const int64_t cost = waves * ((int64_t)ceil_div(nkc, k) * kch * per_chunk[kch == 1 ? 0 : 1][ci] + fixed[ci][ki]);
             if (cost < best) { best = cost; bn = cand; ks = k; }
         }
     }

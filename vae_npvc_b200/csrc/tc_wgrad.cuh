@@ -236,6 +236,33 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         const uint32_t own_base = smem_u32(stage + (size_t)r_base * PITCH + cv);
         const uint32_t recv_base = smem_u32(recv + cv);
         const uint32_t slot_stride = (uint32_t)rows_own * PITCH * 4;
+        // full tiles: no per-element predicates (see conv_fwd_tc_kernel: the generic loop is issue-bound)
+        const bool full = m0 + WG_BM <= nrows && n0 + BN <= ncols && (rows_own % RPP) == 0;
+        if (full) {
+            const int iters = rows_own / RPP;
+            const uint32_t rstep = RPP * PITCH * 4;
+            const uint32_t own0 = own_base + (uint32_t)rsub * (PITCH * 4), recv0 = recv_base + (uint32_t)rsub * (PITCH * 4);
+            float* o = dw + ((size_t)(m0 + r_base + rsub) * ncols + col) * taps + tap_idx;
+            const size_t ostep = (size_t)RPP * ncols * taps;
+#pragma unroll 2
+            for (int it = 0; it < iters; it++, o += ostep) {
+                float4 v = ld_shared_f4((kr == 0 ? own0 : recv0) + (uint32_t)it * rstep);
+#pragma unroll 1
+                for (int p = 1; p < ks; p++) {
+                    const uint32_t base = p == kr ? own0 : recv0 + (uint32_t)(p < kr ? p : p - 1) * slot_stride;
+                    const float4 x = ld_shared_f4(base + (uint32_t)it * rstep);
+                    v.x += x.x; v.y += x.y; v.z += x.z; v.w += x.w;
+                }
+                if (vec_ok) {
+                    *reinterpret_cast<float4*>(o) = v;
+                } else {
+                    o[0] = v.x;
+                    o[taps] = v.y;
+                    o[2 * taps] = v.z;
+                    o[3 * taps] = v.w;
+                }
+            }
+        } else
 #pragma unroll 1
         for (int rl = rsub; rl < rows_own; rl += 2 * RPP) {
             const int rl2 = rl + RPP;
@@ -349,9 +376,12 @@ int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin
             const bool ok = cand == 256 ? WgradTcCfg<256>::fits(k) : cand == 128 ? WgradTcCfg<128>::fits(k) : WgradTcCfg<64>::fits(k);
             if (k > kblocks || !ok) break;
             const int64_t waves = (tiles * k + 147) / 148;
-            // same cost model as conv_fwd_tc (cycles): ~930 per 128-frame stage, fixed 5.5k, split-K exchange 4.5k+
-            const int64_t cost = waves * ((int64_t)ceil_div(kblocks, k) * (cand == 256 ? 1300 : 930) + 5500 +
-                                          (k > 1 ? 4500 + 250 * k : 0) + (cand == 256 ? 2000 : 0));
+            // same cost model as conv_fwd_tc (cycles): a 128-frame stage is two of its 64-deep chunks (L2-intake
+            // bound: ~745 / 860 / 1380 cycles at BN = 64 / 128 / 256), same fixed parts
+            static const int64_t per_stage[3] = {745, 860, 1380};
+            static const int64_t fixed[3][4] = {{4700, 8600, 8900, 9500}, {6300, 10600, 11600, 12400}, {9000, 14000, 15000, 16000}};
+            const int ci = cand == 64 ? 0 : cand == 128 ? 1 : 2, ki = k == 1 ? 0 : k == 2 ? 1 : k == 4 ? 2 : 3;
+            const int64_t cost = waves * ((int64_t)ceil_div(kblocks, k) * per_stage[ci] + fixed[ci][ki]);
             if (cost < best) { best = cost; bn = cand; ks = k; }
         }
     }
