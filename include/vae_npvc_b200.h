@@ -237,6 +237,26 @@ int vnb_adam_step(float* p, const float* g, float* m, float* v, int64_t n, const
                   float max_norm, float lr, double beta1, double beta2, float eps, float* state,
                   int step_size, float gamma, void* stream);
 
+/* ---- packed variable-length conversion / token extraction.  The reference converts one
+ * utterance per forward call (decoder/basic.py:58-75, bin/extract_bnf.py:47-67); here utterances of different
+ * lengths share one zero-padded (B, T, C) batch, lengths[b] (int32, device) valid frames each.
+ * mask_rows: zero the frames t >= lengths[b] of an fp32 activation x (B,T,C) and of up to three operand-plane
+ * buffers (P,B,T,Cp) (any of the four may be NULL) - a k=3 conv then reads zero padding past each utterance's end,
+ * exactly as it does for a lone utterance (layers.py:152,229). */
+int vnb_mask_rows(float* x, void* planes_a, void* planes_b, void* planes_c, int B, int C, int T, int P,
+                  const int* lengths, void* stream);
+/* GroupNorm over the valid frames only (layers.py:154,201 on a lone utterance): take the share of the frames
+ * t >= lengths[b] of h (B,C,T) out of the (B, groups, 2) fp64 sums the conv epilogue accumulated (vnb_conv_fwd
+ * gn_sums), then finalise with n = channels_per_group * lengths[b] (lengths[b] == 0: mean = rstd = 0) */
+int vnb_gn_sums_unpad(const float* h, int B, int C, int T, int groups, const int* lengths, double* gn_sums,
+                      void* stream);
+int vnb_gn_finalize_masked(const double* gn_sums, int B, int groups, int channels_per_group, int T,
+                           const int* lengths, float eps, float* mean, float* rstd, void* stream);
+/* 'csid' tokens of bin/extract_bnf.py:59-60 (Tensor.unique_consecutive) for every utterance of a batch:
+ * idx (B,T) int64 -> out[b, 0..out_len[b]) = ids of utterance b's first lengths[b] frames (NULL: all T) with
+ * consecutive repeats collapsed, out[b, out_len[b]..T) = -1 */
+int vnb_csid(const int64_t* idx, int B, int T, const int* lengths, int64_t* out, int* out_len, void* stream);
+
 /* ---- data-parallel gradient mean over NVSwitch multicast memory (collective 1).  The reference
  * has no multi-GPU path (train.py drives one device); this replaces the library all-reduce a DDP wrapper would
  * issue.  mc_base = multicast address of the symmetric fp32 gradient buffer, [offset, offset+count) elements

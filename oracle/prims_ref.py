@@ -128,12 +128,31 @@ def wn_backward(dw, v, g):
 
 # ---- GEMM-shaped -----------------------------------------------------------------------------
 def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False,
-             gn_groups=0, eps=1e-5):
+             gn_groups=0, eps=1e-5, lengths=None):
     r = _conv_fwd(x_pl, w_op, taps, dil, Cout, bias, bias_bstride, residual, out, accumulate)
     if not gn_groups:
         return r
-    mean, rstd = gn_stats(r, gn_groups, eps)
+    if lengths is None:
+        mean, rstd = gn_stats(r, gn_groups, eps)
+    else:
+        mean, rstd = gn_stats_masked(r, gn_groups, lengths, eps)
     return r, mean, rstd
+
+
+def gn_stats_masked(h, groups, lengths, eps=1e-5):
+    """GroupNorm statistics over the first lengths[b] frames of each sample (vnb_gn_sums_unpad +
+    vnb_gn_finalize_masked): what nn.GroupNorm (layers.py:154,201) computes on the lone utterance."""
+    B, C, T = h.shape
+    mean, rstd = torch.zeros(B, groups), torch.zeros(B, groups)
+    for b in range(B):
+        n = int(lengths[b])
+        if n <= 0:
+            continue
+        hb = h[b, :, :n].reshape(groups, -1).double()
+        m = hb.mean(dim=1)
+        var = (hb - m.unsqueeze(1)).pow(2).mean(dim=1)
+        mean[b], rstd[b] = m.float(), torch.rsqrt(var + eps).float()
+    return mean, rstd
 
 
 def _conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False):
@@ -252,6 +271,30 @@ def dec_out(r, x, S, P, skip_sum=None, first=True, want_x=True, want_xpl=True):
         else:
             skip_sum += r[:, C:]
     return (xo if want_x else None, Planes.of(xo, P) if want_xpl else None, skip_sum)
+
+
+# ---- packed variable-length conversion -------------------------------------------------------
+def mask_rows(lengths, x=None, *planes):
+    """vnb_mask_rows: zero the frames t >= lengths[b], in place."""
+    for b, n in enumerate(lengths.tolist()):
+        if x is not None:
+            x[b, :, n:] = 0
+        for p in planes:
+            if p is not None:
+                p.data[:, b, n:, :] = 0
+
+
+def csid(idx, lengths=None):
+    """vnb_csid: per-utterance torch.unique_consecutive (bin/extract_bnf.py:60), -1 filled."""
+    B, T = idx.shape
+    out = torch.full((B, T), -1, dtype=torch.int64)
+    out_len = torch.zeros((B,), dtype=torch.int32)
+    for b in range(B):
+        n = T if lengths is None else int(lengths[b])
+        u = torch.unique_consecutive(idx[b, :n])
+        out[b, :u.numel()] = u
+        out_len[b] = u.numel()
+    return out, out_len
 
 
 # ---- backward elementwise --------------------------------------------------------------------

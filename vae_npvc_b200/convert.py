@@ -1,0 +1,371 @@
+"""Packed, batched conversion and token extraction on frozen weights.
+
+The reference converts ONE utterance per forward call - ``Decoder.decode`` (vae_npvc/decoder/basic.py:58-75) and
+``extract_bnf`` (vae_npvc/bin/extract_bnf.py:47-67) loop ``model.infer`` / ``model.encode`` over a Kaldi table at
+batch 1, re-deriving all 55 weight-normed conv weights in every call (forward pre-hooks) - because utterances
+differ in length.  ``ConvertEngine`` turns that loop into a throughput path with the SAME per-utterance results:
+
+  * weights are frozen at conversion time, so every conv's bf16 GEMM operand planes are materialised once per
+    checkpoint (``refresh()``), not once per utterance per layer;
+  * utterances are sorted by length and packed into zero-padded (B, Tmax, X) batches.  Kaldi feature matrices are
+    (frames, dims) row-major, which IS this library's channels-last activation layout, so packing is a row copy
+    into a pinned staging buffer and one H2D transfer - no transpose on either side;
+  * every op of the path is per utterance; the two places that see the padding (the k=3 convs' reach across an
+    utterance end, GroupNorm statistics) are handled by ``vnb_mask_rows`` and ``vnb_gn_sums_unpad`` /
+    ``vnb_gn_finalize_masked`` (csrc/convert.cu), whose cost is proportional to the padding;
+  * inference needs no fp32 activations in the encoder at all: each block's epilogue writes only the operand
+    planes the next convs read;
+  * 'csid' tokens (unique_consecutive) are collapsed on the device for the whole batch (``vnb_csid``);
+  * results come back through pinned buffers; batch k+1 is packed on the host while batch k runs.
+
+The forward sequencing below restates Encoder.forward / Decoder.forward / Model.encode / decode / infer
+(vae_npvc/model/vqvae.py:45-67, 185-192, 298-318) directly on the primitives (no autograd graph is built).
+"""
+import math
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import functional as Fn
+from . import prims as Pm
+from .model.layers import Conv1d_Layernorm_LRelu_Residual, DeConv1d_Layernorm_GLU_ResSkip, conv_params
+from .prims import ACT_LRELU, ACT_NONE, ACT_RELU
+
+
+def plan_batches(lengths, max_batch=64, max_batch_frames=1 << 16, max_pad_frac=0.25):
+    """Greedy packing plan.  Utterances sorted by length (longest first); a batch takes the next utterance while
+    it stays within ``max_batch`` utterances, ``max_batch_frames`` padded frames (B * Tmax) and the padding of
+    the batch stays below ``max_pad_frac`` of its padded frames.  -> list of index lists (each longest first).
+    Zero-length utterances are never packed (the caller returns empty results for them)."""
+    order = sorted((i for i, n in enumerate(lengths) if n > 0), key=lambda i: (-lengths[i], i))
+    batches, cur, tmax, valid = [], [], 0, 0
+    for i in order:
+        n = lengths[i]
+        if cur:
+            B = len(cur) + 1
+            padded = B * tmax
+            if B <= max_batch and padded <= max_batch_frames and (padded - valid - n) <= max_pad_frac * padded:
+                cur.append(i)
+                valid += n
+                continue
+            batches.append(cur)
+        cur, tmax, valid = [i], n, n
+    if cur:
+        batches.append(cur)
+    return batches
+
+
+class _Act(object):
+    """Activation between layers of the frozen forward: fp32 tensor and/or operand planes ('id', 'lrelu')."""
+    __slots__ = ('x', 'id', 'lrelu')
+
+    def __init__(self, x=None, id=None, lrelu=None):
+        self.x, self.id, self.lrelu = x, id, lrelu
+
+
+class ConvertEngine(object):
+    def __init__(self, model, precision=None, max_batch=64, max_batch_frames=1 << 16, max_pad_frac=0.25, prims=None):
+        self.Pm = prims or Pm
+        self.model = model
+        self.P = {'bf16': 1, 'fp32': 3, 1: 1, 3: 3, None: Fn.get_precision()}[precision]
+        self.max_batch, self.max_batch_frames, self.max_pad_frac = max_batch, max_batch_frames, max_pad_frac
+        self.device = next(model.parameters()).device
+        self.x_dim = model.encoder.encode[0].in_channels
+        self.use_ema = bool(getattr(model, 'use_ema', False))
+        self.normalize = (not self.use_ema) and bool(model.quantizer.target_norm)
+        self.launches = 0
+        self.refresh()
+
+    # ---- frozen weights ---------------------------------------------------------------------------------------
+    def refresh(self):
+        """(Re-)materialise every conv's operand planes and the codebook operands from the model's current
+        parameters.  Call after ``load_state_dict``; conversion itself never touches weight-norm again."""
+        Pm_ = self.Pm
+        self._w = {}
+        with torch.no_grad():
+            for name, m in self.model.named_modules():
+                if isinstance(m, (nn.Conv1d, nn.ConvTranspose1d)):
+                    v, g, _ = conv_params(m)
+                    cond = name.endswith('conv_cond')
+                    self._w[m] = Pm_.wn_prepare(v.detach(), None if g is None else g.detach(),
+                                                isinstance(m, nn.ConvTranspose1d), self.P, need_wf=not cond,
+                                                need_wb=False, need_w32=cond)
+            E = self.model.quantizer.embeddings.detach()
+            self.e_hat, self.e_pl, self.e_sq = Pm_.vq_prep_codebook(E, self.normalize, False)
+        self.table = self.model.embeds._embedding.weight.detach()
+
+    # ---- forward on a packed batch ----------------------------------------------------------------------------
+    def _conv(self, m, planes, bias_override=None, bias_bstride=0, gn_groups=0, lengths=None):
+        W = self._w[m]
+        k, dil = m.kernel_size[0], m.dilation[0]
+        if m.stride[0] != 1 or m.padding[0] != (k - 1) // 2 * dil or k % 2 == 0:
+            raise NotImplementedError('only stride-1 "same" odd-kernel convolutions are on the hot path')
+        bias = m.bias.detach() if (bias_override is None and m.bias is not None) else bias_override
+        return self.Pm.conv_fwd(planes, W.wf, W.taps, dil, W.Cout, bias, bias_bstride, gn_groups=gn_groups,
+                                lengths=lengths)
+
+    def _planes(self, a, kind, both=False):
+        """Operand planes of activation ``a`` ('id' or 'lrelu'), made from the fp32 tensor when the producer did
+        not leave them (``both``: make the other kind in the same pass - an encoder block reads both)."""
+        if getattr(a, kind) is None or (both and (a.id is None or a.lrelu is None)):
+            want_id = a.id is None and (both or kind == 'id')
+            want_act = a.lrelu is None and (both or kind == 'lrelu')
+            pid, pact = self.Pm.make_planes(a.x, self.P, 1.0, ACT_LRELU, want_id, want_act)
+            a.id, a.lrelu = a.id or pid, a.lrelu or pact
+        return getattr(a, kind)
+
+    def _enc_block(self, blk, a, lengths):
+        """Conv1d_Layernorm_LRelu_Residual.forward (layers.py:168-176) without fp32 outputs: the epilogue writes
+        only the planes of y (the next block's skip conv operand) and of LeakyReLU(y) (its k=3 conv operand)."""
+        Pm_, P = self.Pm, self.P
+        s = self._conv(blk.skip_layer, self._planes(a, 'id', both=True))
+        inp = self._planes(a, 'lrelu')
+        n = blk.n_layers
+        for j in range(n):
+            conv, gn = blk.stack[3 * j + 1], blk.stack[3 * j + 2]
+            h, mean, rstd = self._conv(conv, inp, gn_groups=1, lengths=lengths)
+            last = j == n - 1
+            _, ypl, upl = Pm_.enc_out(h, s if last else None, mean, rstd, gn.weight.detach(), gn.bias.detach(), P,
+                                      False, last, True)
+            if lengths is not None:
+                Pm_.mask_rows(lengths, None, ypl, upl)
+            inp = upl
+        return _Act(None, ypl, upl)
+
+    def encode_z(self, x, lengths=None):
+        """Encoder.forward (vqvae.py:185-192) on x logical (B, X, T) channels-last, zero beyond lengths[b]
+        -> z (B, D, T) fp32."""
+        a = _Act(x)
+        pending = ACT_NONE
+        for m in self.model.encoder.encode:
+            if isinstance(m, nn.LeakyReLU):
+                pending = ACT_LRELU
+            elif isinstance(m, nn.Conv1d):
+                h = self._conv(m, self._planes(a, 'lrelu' if pending == ACT_LRELU else 'id'))
+                pending = ACT_NONE
+                a = _Act(h)
+                if lengths is not None:
+                    self.Pm.mask_rows(lengths, h)
+            elif isinstance(m, Conv1d_Layernorm_LRelu_Residual):
+                assert pending == ACT_NONE
+                a = self._enc_block(m, a, lengths)
+            else:
+                raise NotImplementedError(type(m).__name__)
+        assert pending == ACT_NONE and a.x is not None
+        return a.x
+
+    def lookup(self, z):
+        """VectorQuantizer.encode / EMAVectorQuantizer.encode (layers_vq.py:35-58, 236-252) -> idx (B, T) int64."""
+        B, D, T = z.shape
+        zn, zpl, z_sq, _ = self.Pm.vq_prep_z(z, self.normalize)
+        return self.Pm.vq_lookup(zn, zpl, z_sq, self.e_hat, self.e_pl, self.e_sq).view(B, T)
+
+    def decode_ids(self, idx, y_idx, lengths=None):
+        """Model.decode (vqvae.py:55-60): codebook rows -> Decoder.forward (vqvae.py:298-318).
+        idx (B, T) int64, y_idx (B,) int64 -> xhat logical (B, X, T), channels-last (physically (B, T, X))."""
+        Pm_, P = self.Pm, self.P
+        B, T = idx.shape
+        D = self.e_hat.shape[1]
+        q = Pm_.vq_gather(idx.reshape(-1), self.e_hat, Pm_.cl_empty(B, D, T, idx.device), None, True, False)[0]
+        if lengths is not None:
+            Pm_.mask_rows(lengths, q)
+        cond = Pm_.embed_fwd(self.table, y_idx.view(B, 1)).view(B, -1)
+        dec = self.model.decoder
+        a = _Act(q)
+        skip, first = None, True
+        for layer in dec.layers:
+            if isinstance(layer, nn.ConvTranspose1d):
+                x = self._conv(layer, self._planes(a, 'id'))
+                if lengths is not None:
+                    Pm_.mask_rows(lengths, x)
+                a = _Act(x)
+            elif isinstance(layer, DeConv1d_Layernorm_GLU_ResSkip):
+                C = layer.in_channels
+                S = layer.res_skip_layers.out_channels - C
+                if a.id is None:
+                    a.id = Pm_.make_planes(a.x, P)[0]
+                if layer.conv_cond is not None:
+                    # the cond conv sees a time-invariant input (c.repeat, vqvae.py:309-312): a per-utterance bias
+                    wc32 = self._w[layer.conv_cond].w32.view(2 * C, -1)
+                    p = Pm_.linear_fwd(cond, wc32, layer.conv_cond.bias.detach(), layer.conv_in.bias.detach())
+                    h, mean, rstd = self._conv(layer.conv_in, a.id, p, 2 * C, gn_groups=2, lengths=lengths)
+                else:
+                    h, mean, rstd = self._conv(layer.conv_in, a.id, gn_groups=2, lengths=lengths)
+                gpl = Pm_.dec_gate(h, mean, rstd, layer.norm_layer.weight.detach(), layer.norm_layer.bias.detach(), P)
+                r = self._conv(layer.res_skip_layers, gpl)
+                if skip is None:
+                    skip = Pm_.cl_empty(B, S, T, idx.device)
+                x_out, xpl, _ = Pm_.dec_out(r, a.x, S, P, skip, first)
+                first = False
+                if lengths is not None:
+                    Pm_.mask_rows(lengths, x_out, xpl)
+                a = _Act(x_out, xpl)
+            else:
+                raise NotImplementedError(type(layer).__name__)
+        # x_out * sqrt(1/len(layers)) -> ReLU -> 1x1 -> ReLU -> 1x1 (vqvae.py:316-317): per-frame ops, no masking
+        scale = math.sqrt(1.0 / len(dec.layers))
+        o = self._conv(dec.final_layer[1], Pm_.make_planes(skip, P, scale, ACT_RELU, False, True)[1])
+        return self._conv(dec.final_layer[3], Pm_.make_planes(o, P, 1.0, ACT_RELU, False, True)[1])
+
+    # ---- host side: packing, transfer, un-packing -------------------------------------------------------------
+    def _cuda(self):
+        return self.device.type == 'cuda'
+
+    def _host(self, shape, dtype):
+        return torch.zeros(shape, dtype=dtype, pin_memory=True) if self._cuda() else torch.zeros(shape, dtype=dtype)
+
+    def _pack(self, arrays, sel, width, dtype):
+        """Rows of the selected utterances into one zero-padded (B, Tmax, width) host buffer (pinned on CUDA)."""
+        B, tmax = len(sel), max(arrays[i].shape[0] for i in sel)
+        shape = (B, tmax) if width is None else (B, tmax, width)
+        buf = self._host(shape, dtype)
+        for b, i in enumerate(sel):
+            a = torch.as_tensor(np.ascontiguousarray(arrays[i]))
+            buf[b, :a.shape[0]] = a.to(dtype)
+        lens = torch.tensor([arrays[i].shape[0] for i in sel], dtype=torch.int32)
+        return buf, lens, tmax
+
+    def _dev(self, t):
+        return t.to(self.device, non_blocking=True) if self._cuda() else t
+
+    def _run(self, n_items, lengths_all, make_job):
+        """Plan batches, run ``make_job(sel) -> (device result, lens, finish)`` for each and un-pack.  The host
+        packs batch k+1 while batch k runs: every device call is asynchronous and a batch's results are only
+        waited for (its event) after the next batch has been queued."""
+        out = [None] * n_items
+        pending = None
+
+        def drain(job):
+            host, ev, sel, finish = job
+            if ev is not None:
+                ev.synchronize()
+            for b, i in enumerate(sel):
+                out[i] = finish(host, b, i)
+
+        for sel in plan_batches(lengths_all, self.max_batch, self.max_batch_frames, self.max_pad_frac):
+            host, finish = make_job(sel)
+            ev = None
+            if self._cuda():
+                ev = torch.cuda.Event()
+                ev.record()
+            if pending is not None:
+                drain(pending)
+            pending = (host, ev, sel, finish)
+        if pending is not None:
+            drain(pending)
+        return out
+
+    def _d2h(self, t):
+        if not self._cuda():
+            return t
+        host = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+        host.copy_(t, non_blocking=True)
+        return host
+
+    def _count(self, fn):
+        from . import _C
+        if not self._cuda():
+            return fn()
+        n0 = _C.launch_count()
+        r = fn()
+        self.launches += int(_C.launch_count() - n0)
+        return r
+
+    def _begin(self):
+        if self._cuda() and hasattr(self.Pm, 'stats_arena_begin'):
+            self.Pm.stats_arena_begin(self.device)
+
+    def _end(self):
+        if self._cuda() and hasattr(self.Pm, 'stats_arena_end'):
+            self.Pm.stats_arena_end()
+
+    def _lengths_arg(self, lens, tmax):
+        """None when no utterance of the batch is padded (no mask kernels are launched then)."""
+        return None if int(lens.min()) == tmax else self._dev(lens)
+
+    def _check_feats(self, feats):
+        for f in feats:
+            if f.ndim != 2 or f.shape[1] != self.x_dim:
+                raise ValueError('expected (frames, %d) feature matrices, got %s' % (self.x_dim, tuple(f.shape)))
+
+    def convert(self, feats, targets):
+        """Model.infer (vqvae.py:63-67) for a list of utterances: feats[i] (T_i, X) float array (Kaldi layout),
+        targets[i] speaker id (int, or a sequence whose first entry is used, as the reference's c[:,:,:1])
+        -> list of (T_i, X) float32 numpy arrays in input order."""
+        self._check_feats(feats)
+        tg = [int(np.asarray(t).reshape(-1)[0]) for t in targets]
+        assert len(tg) == len(feats)
+        X = self.x_dim
+
+        def job(sel):
+            buf, lens, tmax = self._pack(feats, sel, X, torch.float32)
+            y = torch.tensor([tg[i] for i in sel], dtype=torch.int64)
+            with torch.no_grad():
+                self._begin()
+                try:
+                    xd, yd = self._dev(buf), self._dev(y)
+                    ld = self._lengths_arg(lens, tmax)
+                    xhat = self._count(lambda: self.decode_ids(self.lookup(self.encode_z(xd.transpose(1, 2), ld)), yd, ld))
+                finally:
+                    self._end()
+                host = self._d2h(self.Pm.as_cl(xhat).transpose(1, 2))       # physical (B, Tmax, X)
+            return host, lambda h, b, i: h[b, :feats[i].shape[0]].numpy().copy()
+
+        out = self._run(len(feats), [f.shape[0] for f in feats], job)
+        return [o if o is not None else np.zeros((0, X), dtype=np.float32) for o in out]
+
+    def encode(self, feats, kind='id'):
+        """Model.encode per utterance as extract_bnf.py:47-62 emits it: kind 'id' -> (T_i,) int64 ids, 'csid' ->
+        ids with consecutive repeats collapsed, 'token' -> (1, T_i) (the reference's ``.t()`` of a (T,1) column)."""
+        assert kind in ('id', 'csid', 'token')
+        self._check_feats(feats)
+        X = self.x_dim
+
+        def job(sel):
+            buf, lens, tmax = self._pack(feats, sel, X, torch.float32)
+            with torch.no_grad():
+                self._begin()
+                try:
+                    xd = self._dev(buf)
+                    ld = self._lengths_arg(lens, tmax)
+                    idx = self._count(lambda: self.lookup(self.encode_z(xd.transpose(1, 2), ld)))
+                    if kind == 'csid':
+                        ids, n = self._count(lambda: self.Pm.csid(idx, self._dev(lens)))
+                        host = (self._d2h(ids), self._d2h(n))
+                    else:
+                        host = (self._d2h(idx), None)
+                finally:
+                    self._end()
+
+            def finish(h, b, i):
+                n = int(h[1][b]) if h[1] is not None else feats[i].shape[0]
+                ids = h[0][b, :n].numpy().copy()
+                return ids.reshape(1, -1) if kind == 'token' else ids
+            return host, finish
+
+        out = self._run(len(feats), [f.shape[0] for f in feats], job)
+        empty = np.zeros((1, 0) if kind == 'token' else (0,), dtype=np.int64)
+        return [o if o is not None else empty for o in out]
+
+    def decode(self, ids, targets):
+        """Model.decode (vqvae.py:55-60) per utterance: ids[i] (T_i,) int64 -> (T_i, X) float32."""
+        tg = [int(np.asarray(t).reshape(-1)[0]) for t in targets]
+        ids = [np.asarray(a).reshape(-1) for a in ids]
+        X = self._w[self.model.decoder.final_layer[3]].Cout
+
+        def job(sel):
+            buf, lens, tmax = self._pack(ids, sel, None, torch.int64)
+            y = torch.tensor([tg[i] for i in sel], dtype=torch.int64)
+            with torch.no_grad():
+                self._begin()
+                try:
+                    xhat = self._count(lambda: self.decode_ids(self._dev(buf), self._dev(y),
+                                                               self._lengths_arg(lens, tmax)))
+                finally:
+                    self._end()
+                host = self._d2h(self.Pm.as_cl(xhat).transpose(1, 2))
+            return host, lambda h, b, i: h[b, :ids[i].shape[0]].numpy().copy()
+
+        out = self._run(len(ids), [a.shape[0] for a in ids], job)
+        return [o if o is not None else np.zeros((0, X), dtype=np.float32) for o in out]

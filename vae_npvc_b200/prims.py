@@ -155,10 +155,11 @@ def _stats_zeros(B, groups, device):
 
 
 def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False,
-             gn_groups=0, eps=1e-5):
+             gn_groups=0, eps=1e-5, lengths=None):
     """x_pl: Planes (B,Cin,T); w_op: (P,taps,Cout,Cin_p) bf16 -> out fp32, logical (B,Cout,T).
     gn_groups > 0: also returns the GroupNorm (mean, rstd) (B, gn_groups) of the result, accumulated
-    in the GEMM epilogue -> (out, mean, rstd)."""
+    in the GEMM epilogue -> (out, mean, rstd).  ``lengths`` (B,) int32: packed variable-length batch - the
+    statistics cover the first lengths[b] frames of each sample only."""
     user_out = None
     dev = x_pl.data.device
     if out is None:
@@ -174,7 +175,11 @@ def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=No
     if not gn_groups:
         return out
     mean, rstd = _f32((x_pl.B, gn_groups), out), _f32((x_pl.B, gn_groups), out)
-    _C.call('gn_finalize', sums, x_pl.B * gn_groups, float(Cout // gn_groups * x_pl.T), eps, mean, rstd)
+    if lengths is not None:
+        _C.call('gn_sums_unpad', out.transpose(1, 2), x_pl.B, Cout, x_pl.T, gn_groups, lengths, sums)
+        _C.call('gn_finalize_masked', sums, x_pl.B, gn_groups, Cout // gn_groups, x_pl.T, lengths, eps, mean, rstd)
+    else:
+        _C.call('gn_finalize', sums, x_pl.B * gn_groups, float(Cout // gn_groups * x_pl.T), eps, mean, rstd)
     return out, mean, rstd
 
 
@@ -457,6 +462,33 @@ def jitter_bwd(dout, src):
     din = cl_empty(B, D, T, dout.device)
     _C.call('jitter_bwd', _r(dout), src, B, D, T, din.transpose(1, 2))
     return din
+
+
+# --------------------------------------------------------------------------------------------
+# packed variable-length conversion
+# --------------------------------------------------------------------------------------------
+def mask_rows(lengths, x=None, *planes):
+    """Zero the frames t >= lengths[b] of activation ``x`` (logical (B,C,T)) and of up to three Planes, in place."""
+    planes = [p for p in planes if p is not None]
+    assert len(planes) <= 3 and (x is not None or planes)
+    if x is not None:
+        B, C, T = x.shape
+        assert is_cl(x), 'mask_rows works on channels-last activations'
+    else:
+        B, C, T = planes[0].B, planes[0].C, planes[0].T
+    P = planes[0].P if planes else 1
+    assert all((p.B, p.C, p.T, p.P) == (B, C, T, P) for p in planes)
+    d = [p.data for p in planes] + [None] * (3 - len(planes))
+    _C.call('mask_rows', None if x is None else x.transpose(1, 2), d[0], d[1], d[2], B, C, T, P, lengths)
+
+
+def csid(idx, lengths=None):
+    """idx (B,T) int64 -> (out (B,T) int64 with consecutive repeats collapsed and -1 fill, out_len (B,) int32)."""
+    B, T = idx.shape
+    out = torch.empty((B, T), dtype=torch.int64, device=idx.device)
+    out_len = torch.empty((B,), dtype=torch.int32, device=idx.device)
+    _C.call('csid', idx.contiguous(), B, T, lengths, out, out_len)
+    return out, out_len
 
 
 # --------------------------------------------------------------------------------------------
