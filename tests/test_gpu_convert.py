@@ -28,6 +28,14 @@ def Pm():
     return prims
 
 
+@pytest.fixture(autouse=True)
+def _restore_precision():
+    import vae_npvc_b200.functional as Fn
+    old = Fn.get_precision()
+    yield
+    Fn.set_precision(old)
+
+
 def g(*shape, seed=0):
     return torch.randn(*shape, generator=torch.Generator().manual_seed(seed))
 

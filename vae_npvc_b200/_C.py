@@ -115,7 +115,7 @@ def call(name, *args):
     if has_stream:
         cargs.append(torch.cuda.current_stream().cuda_stream)
     r = getattr(lib, full)(*cargs)
-    if ret == 'int' and name not in ('version', 'get_backend', 'debug_tc_timeouts', 'gn_stats_ws_floats') and r != 0:
+    if ret == 'int' and name not in ('version', 'get_backend', 'get_option', 'debug_tc_timeouts', 'gn_stats_ws_floats') and r != 0:
         raise RuntimeError(f'{full} failed ({r}): {lib.vnb_last_error().decode()}')
     return r
 
@@ -126,6 +126,17 @@ def set_backend(b):
 
 def get_backend():
     return load().vnb_get_backend()
+
+
+OPT_EW_V2, OPT_FAST_GATE = 0, 1
+
+
+def set_option(which, value):
+    load().vnb_set_option(int(which), int(value))
+
+
+def get_option(which):
+    return load().vnb_get_option(int(which))
 
 
 def launch_count():

@@ -12,6 +12,16 @@ namespace vnb {
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
 int backend();
+int option(int which);
+void set_option(int which, int value);
+// compiled defaults of the runtime options (environment variables VNB_EW_V2 / VNB_FAST_GATE and vnb_set_option
+// override them)
+#ifndef VNB_EW_V2_DEFAULT
+#define VNB_EW_V2_DEFAULT 0
+#endif
+#ifndef VNB_FAST_GATE_DEFAULT
+#define VNB_FAST_GATE_DEFAULT 0
+#endif
 
 #define VNB_REQUIRE(cond, ...)              \
     do {                                    \

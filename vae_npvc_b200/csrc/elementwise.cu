@@ -6,6 +6,7 @@
 // Reference op sequences: vae_npvc/model/layers.py:151-155,168-176 (encoder residual block),
 // :229-247 (gated decoder block); math in SURVEY.md section 9 A/B.
 #include "common.cuh"
+#include "ew_v2.cuh"
 
 namespace vnb {
 
@@ -330,6 +331,15 @@ extern "C" int vnb_make_planes(const float* x, int B, int C, int T, int P, float
     VNB_REQUIRE(!csum || C <= 12000, "make_planes: too many channels for the fused channel sums");
     const int64_t rows = (int64_t)B * T;
     const bool v4 = (C & 3) == 0;
+    if (v4 && !csum && ew_v2_enabled()) {
+        const int g2 = v2_grid(rows, C / 4);
+        if (g2) {
+            if (P == 1) vnb::launch_k(make_planes_v2_kernel<1, 4>, g2, V2_THREADS, 0, ST, x, (int)rows, C, round_up8(C), scale, act, (bf16*)out_id, (bf16*)out_act);
+            else vnb::launch_k(make_planes_v2_kernel<3, 2>, g2, V2_THREADS, 0, ST, x, (int)rows, C, round_up8(C), scale, act, (bf16*)out_id, (bf16*)out_act);
+            VNB_LAUNCH_CHECK("make_planes_v2");
+            return VNB_OK;
+        }
+    }
     const int64_t n = v4 ? rows * C / 4 : rows * C;
     int grid = ew_grid(n);
     if (csum && grid > 296) grid = 296;                 // fewer flushes of the shared-memory sums
@@ -404,6 +414,17 @@ extern "C" int vnb_dec_gate(const float* a, const float* mean, const float* rstd
     VNB_REQUIRE(a && mean && rstd && gamma && beta && g_planes, "dec_gate: null pointer");
     VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "dec_gate: bad shape");
     const int64_t rows = (int64_t)B * T;
+    if ((C & 3) == 0 && ew_v2_enabled()) {
+        const int g2 = v2_grid(rows, C / 4);
+        if (g2) {
+            const int Cp = round_up8(C);
+            if (P == 1 && fast_gate_enabled()) vnb::launch_k(dec_gate_v2_kernel<1, 2, true>, g2, V2_THREADS, 0, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes);
+            else if (P == 1) vnb::launch_k(dec_gate_v2_kernel<1, 2, false>, g2, V2_THREADS, 0, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes);
+            else vnb::launch_k(dec_gate_v2_kernel<3, 2, false>, g2, V2_THREADS, 0, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes);
+            VNB_LAUNCH_CHECK("dec_gate_v2");
+            return VNB_OK;
+        }
+    }
     VEC_DISPATCH((C & 3) == 0, dec_gate_kernel, rows * C, ST, a, mean, rstd, gamma, beta, rows, C, T, round_up8(C), P,
                  (bf16*)g_planes);
     VNB_LAUNCH_CHECK("dec_gate");

@@ -2,6 +2,7 @@
 // finalisation, gradient application into operand planes, activation masks, bias sums.
 // Math: SURVEY.md section 9 A/B (restated from vae_npvc/model/layers.py:151-176, 229-247).
 #include "common.cuh"
+#include "ew_v2.cuh"
 
 namespace vnb {
 
@@ -389,6 +390,16 @@ extern "C" int vnb_gn_bwd_apply(const float* dn, const float* h, const float* me
     VNB_REQUIRE(dn && h && mean && rstd && gamma && S && dpre_planes, "gn_bwd_apply: null pointer");
     VNB_REQUIRE(B > 0 && C > 0 && T > 0 && groups > 0 && C % groups == 0 && (P == 1 || P == 3), "gn_bwd_apply: bad shape");
     const int64_t rows = (int64_t)B * T;
+    if ((C & 3) == 0 && ((C / groups) & 3) == 0 && ew_v2_enabled()) {
+        const int g2 = v2_grid(rows, C / 4);
+        if (g2) {
+            cudaStream_t st = (cudaStream_t)stream;
+            if (P == 1) vnb::launch_k(gn_bwd_apply_v2_kernel<1, 2>, g2, V2_THREADS, 0, st, dn, h, mean, rstd, gamma, S, (int)rows, C, T, groups, round_up8(C), (bf16*)dpre_planes, (bf16*)dn_planes);
+            else vnb::launch_k(gn_bwd_apply_v2_kernel<3, 2>, g2, V2_THREADS, 0, st, dn, h, mean, rstd, gamma, S, (int)rows, C, T, groups, round_up8(C), (bf16*)dpre_planes, (bf16*)dn_planes);
+            VNB_LAUNCH_CHECK("gn_bwd_apply_v2");
+            return VNB_OK;
+        }
+    }
     VEC_DISPATCH((C & 3) == 0, gn_bwd_apply_kernel, rows * C, (cudaStream_t)stream, dn, h, mean, rstd, gamma, S, rows, C, T,
                  groups, round_up8(C), P, (bf16*)dpre_planes, (bf16*)dn_planes);
     VNB_LAUNCH_CHECK("gn_bwd_apply");
@@ -401,6 +412,18 @@ extern "C" int vnb_gate_bwd_apply(const float* dg, const float* a, const float* 
     VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && S && da_planes, "gate_bwd_apply: null pointer");
     VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "gate_bwd_apply: bad shape");
     const int64_t rows = (int64_t)B * T;
+    if ((C & 3) == 0 && ew_v2_enabled()) {
+        const int g2 = v2_grid(rows, C / 4);
+        if (g2) {
+            cudaStream_t st = (cudaStream_t)stream;
+            const int Cp = round_up8(2 * C);
+            if (P == 1 && fast_gate_enabled()) vnb::launch_k(gate_bwd_apply_v2_kernel<1, 2, true>, g2, V2_THREADS, 0, st, dg, a, mean, rstd, gamma, beta, S, (int)rows, C, T, Cp, (bf16*)da_planes);
+            else if (P == 1) vnb::launch_k(gate_bwd_apply_v2_kernel<1, 2, false>, g2, V2_THREADS, 0, st, dg, a, mean, rstd, gamma, beta, S, (int)rows, C, T, Cp, (bf16*)da_planes);
+            else vnb::launch_k(gate_bwd_apply_v2_kernel<3, 2, false>, g2, V2_THREADS, 0, st, dg, a, mean, rstd, gamma, beta, S, (int)rows, C, T, Cp, (bf16*)da_planes);
+            VNB_LAUNCH_CHECK("gate_bwd_apply_v2");
+            return VNB_OK;
+        }
+    }
     VEC_DISPATCH((C & 3) == 0, gate_bwd_apply_kernel, rows * C, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, S,
                  rows, C, T, round_up8(2 * C), P, (bf16*)da_planes);
     VNB_LAUNCH_CHECK("gate_bwd_apply");

@@ -20,6 +20,27 @@ void set_error(const char* fmt, ...) {
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 int backend() { return g_backend.load(std::memory_order_relaxed); }
+// Runtime options (vnb_set_option): initial values from the environment, else the compiled defaults.
+static int env_or(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+static std::atomic<int> g_opts[VNB_OPT_COUNT_] = {};
+static std::atomic<bool> g_opts_init{false};
+static void opts_init() {
+    if (g_opts_init.load(std::memory_order_acquire)) return;
+    g_opts[VNB_OPT_EW_V2].store(env_or("VNB_EW_V2", VNB_EW_V2_DEFAULT));
+    g_opts[VNB_OPT_FAST_GATE].store(env_or("VNB_FAST_GATE", VNB_FAST_GATE_DEFAULT));
+    g_opts_init.store(true, std::memory_order_release);
+}
+int option(int which) {
+    opts_init();
+    return (which >= 0 && which < VNB_OPT_COUNT_) ? g_opts[which].load(std::memory_order_relaxed) : 0;
+}
+void set_option(int which, int value) {
+    opts_init();
+    if (which >= 0 && which < VNB_OPT_COUNT_) g_opts[which].store(value);
+}
 bool pdl_enabled() {
     static const bool on = !(getenv("VNB_PDL") && atoi(getenv("VNB_PDL")) == 0);
     return on;
@@ -34,4 +55,6 @@ int64_t vnb_launch_count(void) { return vnb::g_launches.load(); }
 void vnb_launch_count_reset(void) { vnb::g_launches.store(0); }
 void vnb_set_backend(int b) { vnb::g_backend.store(b); }
 int vnb_get_backend(void) { return vnb::g_backend.load(); }
+void vnb_set_option(int which, int value) { vnb::set_option(which, value); }
+int vnb_get_option(int which) { return vnb::option(which); }
 }
