@@ -254,6 +254,7 @@ def run_ours(args, rank, world):
                                    '10+10 blocks, codebook 512x64 (use_ema false, embed_norm true), Adam+clip+StepLR',
                        'frames_per_gpu_per_step': B_PER_GPU * T_FRAMES, 'parallelism': 'dp%d' % world,
                        'cuda_graph': bool(on_graph),
+                       'options': {'ew_v2': _C.get_option(_C.OPT_EW_V2), 'fast_gate': _C.get_option(_C.OPT_FAST_GATE)},
                        'l2': 'no explicit flush: each step streams params+grads+Adam moments+operand planes '
                              '(~0.7 GB) > 126 MB L2; the isolated-kernel timing flushes L2 with a 256 MB write',
                        'step_roofline_frac_tensor': value * FLOP_PER_FRAME / (world * pk['tf_sus'] * 1e12)},

@@ -1,6 +1,9 @@
 """Per-kernel roofline microbenchmarks (BASELINE config 5 and SURVEY.md section 8d).
 
-    python tools/bench_kernels.py [--quick]        # writes gpurun_out/bench_kernels.json
+    python tools/bench_kernels.py [--quick] [--mem-only] [--tag NAME]    # writes gpurun_out/bench_kernels[_NAME].json
+
+The streaming-kernel generation / gate math are whatever the options say (VNB_EW_V2, VNB_FAST_GATE in the
+environment); they are recorded in the output.
 
 * VQ lookup sweep: K in {256,512,1024,4096,16384} x D in {64,128,256}, N = 2^17 frames, z = randn, E = randn
   (the reference's own codebook init, layers_vq.py:18).  Reports frames/s, executed TFLOP/s (6 bf16 plane-pair
@@ -49,14 +52,18 @@ def timeit(fn, reps=5, flush=None):
 
 def main():
     quick = '--quick' in sys.argv
+    mem_only = '--mem-only' in sys.argv
+    tag = sys.argv[sys.argv.index('--tag') + 1] if '--tag' in sys.argv else ''
     _C.require_cuda()
     hbm, tf, src = peaks()
-    out = {'peaks': {'hbm_gbs': hbm, 'bf16_tflops': tf, 'source': src}, 'vq_lookup': [], 'memory_bound': []}
+    out = {'peaks': {'hbm_gbs': hbm, 'bf16_tflops': tf, 'source': src}, 'vq_lookup': [], 'memory_bound': [],
+           'options': {'ew_v2': _C.get_option(_C.OPT_EW_V2), 'fast_gate': _C.get_option(_C.OPT_FAST_GATE)}}
+    print('options:', out['options'], flush=True)
     flush = torch.empty(256 * 1024 * 1024 // 4, device='cuda')
     # ---------------- VQ lookup sweep ----------------
     N = 1 << 17
     Bv, Tv = N // 128, 128
-    for D in ([64] if quick else [64, 128, 256]):
+    for D in ([] if mem_only else [64] if quick else [64, 128, 256]):
         for K in ([512, 4096] if quick else [256, 512, 1024, 4096, 16384]):
             g = torch.Generator(device='cuda').manual_seed(0)
             z = torch.randn(Bv, D, Tv, device='cuda', generator=g)
@@ -154,7 +161,7 @@ def main():
     dt = timeit(lambda: Pm.sqnorm(g, sqn))
     rec('sqnorm (1 read)', dt, n * 4)
     os.makedirs(os.path.join(ROOT, 'gpurun_out'), exist_ok=True)
-    json.dump(out, open(os.path.join(ROOT, 'gpurun_out', 'bench_kernels.json'), 'w'), indent=1)
+    json.dump(out, open(os.path.join(ROOT, 'gpurun_out', 'bench_kernels%s.json' % ('_' + tag if tag else '')), 'w'), indent=1)
 
 
 if __name__ == '__main__':
