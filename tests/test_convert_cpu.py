@@ -132,3 +132,23 @@ def test_bad_feature_shape_raises():
     eng = ConvertEngine(m, precision='fp32', prims=prims_ref)
     with pytest.raises(ValueError):
         eng.convert([np.zeros((4, feats[0].shape[1] + 1), dtype=np.float32)], [0])
+
+
+def test_plan_shards_balances_frames_and_merge_scp_keeps_trial_order(tmp_path):
+    from vae_npvc_b200.convert import plan_shards
+    from vae_npvc_b200.decoder.basic import merge_scp
+    rng = np.random.RandomState(1)
+    lengths = [int(v) for v in rng.randint(50, 900, size=101)]
+    for world in (1, 2, 8):
+        shards = plan_shards(lengths, world)
+        assert len(shards) == world and sorted(i for s in shards for i in s) == list(range(101))
+        loads = [sum(lengths[i] for i in s) for s in shards]
+        assert max(loads) - min(loads) <= max(lengths)                  # greedy longest-first bound
+        assert all(s == sorted(s) for s in shards)
+    assert plan_shards([], 2) == [[], []]
+    keys = ['u%d' % i for i in range(6)]
+    (tmp_path / 'a.scp').write_text(''.join('%s A:%d\n' % (k, i) for i, k in enumerate(keys) if i % 2 == 0))
+    (tmp_path / 'b.scp').write_text(''.join('%s B:%d\n' % (k, i) for i, k in enumerate(keys) if i % 2 == 1))
+    merge_scp([str(tmp_path / 'a.scp'), str(tmp_path / 'b.scp')], str(tmp_path / 'm.scp'), keys)
+    got = (tmp_path / 'm.scp').read_text().splitlines()
+    assert [l.split()[0] for l in got] == keys and got[1] == 'u1 B:1' and got[4] == 'u4 A:4'

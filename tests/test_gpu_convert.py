@@ -191,30 +191,33 @@ def test_engine_equals_model_infer_batch1(Pm):
         Fn.set_precision(old)
 
 
-def test_engine_bf16_vcc2020_shape_packing_invariance(Pm):
-    """VCC2020-shape model (C512, 10+10 blocks, codebook 512x64), bf16 operands, utterances of 60-400 frames:
-    packed results equal the same engine run one utterance at a time (the padding is invisible), and stay within
-    the bf16 tolerance of the fp32 oracle on a sample of utterances."""
+def test_engine_vcc2020_shape_packing_invariance(Pm):
+    """VCC2020-shape model (C512, 10+10 blocks, codebook 512x64), utterances of 60-400 frames.
+    fp32-faithful planes: packed results equal the same engine run one utterance at a time - the padding is
+    invisible; only the GroupNorm sums are accumulated in a different order (fp64 atomics, then the padded share
+    taken out again).  bf16 planes: the same comparison is only a sanity bound, because a last-bit difference in a
+    GroupNorm mean flips bf16 roundings of the next operand plane and ten blocks amplify that into a few per cent
+    of re-assigned codebook ids (measured: 97 % of ids agree, features within 1e-2); the decoder alone is compared
+    with the fp32 oracle on the oracle's own ids."""
     from vae_npvc_b200.convert import ConvertEngine
     arch = synth.arch_config()
     rng = np.random.RandomState(3)
     lengths = [int(v) for v in rng.randint(60, 400, size=24)] + [400, 400]
     m, params, feats, targets = _setup(arch, seed=21, lengths=lengths)
-    packed = ConvertEngine(m, precision='bf16', max_batch=16, max_pad_frac=0.5)
-    single = ConvertEngine(m, precision='bf16', max_batch=1)
-    a, b = packed.convert(feats, targets), single.convert(feats, targets)
-    ia, ib = packed.encode(feats, 'id'), single.encode(feats, 'id')
-    assert packed.launches < single.launches
-    same = 0
-    for x, y, i, j in zip(a, b, ia, ib):
-        assert x.shape == y.shape and np.isfinite(x).all()
-        assert (i == j).mean() > 0.99
-        # identical math per utterance; only the GroupNorm sums are accumulated in a different order (fp64 atomics).
-        # (a code flip on a near-tie would change the decoder input itself, so compare where the ids agree)
-        if np.array_equal(i, j):
-            same += 1
-            assert rel_err(x, y) < 1e-3
-    assert same >= 0.8 * len(a)
+    for precision in ('fp32', 'bf16'):
+        packed = ConvertEngine(m, precision=precision, max_batch=16, max_pad_frac=0.5)
+        single = ConvertEngine(m, precision=precision, max_batch=1)
+        a, b = packed.convert(feats, targets), single.convert(feats, targets)
+        ia, ib = packed.encode(feats, 'id'), single.encode(feats, 'id')
+        assert packed.launches < single.launches
+        agree = np.mean([(i == j).mean() for i, j in zip(ia, ib)])
+        worst = max(rel_err(x, y) for x, y in zip(a, b))
+        assert all(x.shape == y.shape and np.isfinite(x).all() for x, y in zip(a, b))
+        if precision == 'fp32':
+            assert agree > 0.999 and worst < 5e-3            # a single near-tie flip moves one frame's features
+            assert np.median([rel_err(x, y) for x, y in zip(a, b)]) < 1e-5
+        else:
+            assert agree > 0.9 and worst < 5e-2
     # bf16 operands against the fp32 oracle: the decoder on the oracle's own ids (no near-tie flips involved);
     # a sanity bound - 21 chained bf16-operand GEMMs - the parity bar proper is the fp32 mode above
     for k in (0, 5):
@@ -222,6 +225,8 @@ def test_engine_bf16_vcc2020_shape_packing_invariance(Pm):
         want = O.model_decode(params, arch, torch.from_numpy(oid).view(1, -1), torch.tensor([[targets[k]]]))[0].t().numpy()
         got = packed.decode([oid], [targets[k]])[0]
         assert rel_err(got, want) < 5e-2
+        got32 = ConvertEngine(m, precision='fp32').decode([oid], [targets[k]])[0]
+        assert rel_err(got32, want) < 1e-4
 
 
 def test_decoder_mirror_end_to_end(Pm, tmp_path):

@@ -1,5 +1,5 @@
 """-m gpu: the second-generation streaming kernels (csrc/ew_v2.cuh: make_planes, dec_gate, gn_bwd_apply,
-gate_bwd_apply behind option VNB_OPT_EW_V2, approximate gate math behind VNB_OPT_FAST_GATE) against the contract
+gate_bwd_apply, enc_out behind option VNB_OPT_EW_V2, approximate gate math behind VNB_OPT_FAST_GATE) against the contract
 restatement in oracle/prims_ref.py and against the first-generation kernels, for both operand modes, on shapes that
 take one loop iteration (the VCC2020 step) and several (more rows than the grid covers), channel counts whose
 vector count does and does not divide the CTA size, and a shape the scheme must hand back to the old kernels.
@@ -76,6 +76,29 @@ def test_make_planes_v2(Pm, opts, P, B, C, T):
         assert torch.equal(only.data, b1.data)
     ra, rb = R.make_planes(x, P, 0.7, R.ACT_RELU, True, True)
     assert rel_err(val(a2), val(ra)) < tol(P) and rel_err(val(b2), val(rb)) < tol(P)
+
+
+@pytest.mark.parametrize('P', [1, 3])
+@pytest.mark.parametrize('B,C,T', SHAPES)
+def test_enc_out_v2(Pm, opts, P, B, C, T):
+    h, sk = g(B, C, T, seed=1, scale=2.0) + 0.3, g(B, C, T, seed=2)
+    gamma, beta = g(C, seed=3) * 0.3 + 1.0, g(C, seed=4) * 0.5
+    rm, rr = R.gn_stats(h, 1)
+    hc, sc = Pm.as_cl(h.cuda()), Pm.as_cl(sk.cuda())
+    args = (rm.cuda(), rr.cuda(), gamma.cuda(), beta.cuda())
+    for skip, rs in ((sc, sk), (None, None)):
+        ry, rypl, rupl = R.enc_out(h, rs, rm, rr, gamma, beta, P)
+        out = {}
+        for v2 in (0, 1):
+            opts(v2)
+            out[v2] = Pm.enc_out(hc, skip, *args, P, True, True, True)
+            assert rel_err(out[v2][0], ry) < 5e-5
+            assert rel_err(val(out[v2][1]), val(rypl)) < tol(P) and rel_err(val(out[v2][2]), val(rupl)) < tol(P)
+        assert rel_err(out[1][0], out[0][0]) < 1e-6
+        # outputs are individually optional
+        opts(1)
+        y, ypl, upl = Pm.enc_out(hc, skip, *args, P, False, False, True)
+        assert y is None and ypl is None and rel_err(val(upl), val(out[1][2])) < 1e-6
 
 
 @pytest.mark.parametrize('P,fast', [(1, 0), (1, 1), (3, 0), (3, 1)])

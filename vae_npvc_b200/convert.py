@@ -56,6 +56,19 @@ def plan_batches(lengths, max_batch=64, max_batch_frames=1 << 16, max_pad_frac=0
     return batches
 
 
+def plan_shards(lengths, world):
+    """Utterance shards for ``world`` ranks (one process per GPU, no data-path collective: every utterance is
+    independent).  Longest-first greedy assignment to the least-loaded rank balances FRAMES, not utterance counts.
+    -> list of ``world`` index lists, each in input order."""
+    load = [0] * world
+    shards = [[] for _ in range(world)]
+    for i in sorted(range(len(lengths)), key=lambda i: (-lengths[i], i)):
+        r = min(range(world), key=lambda k: (load[k], k))
+        shards[r].append(i)
+        load[r] += lengths[i]
+    return [sorted(s) for s in shards]
+
+
 class _Act(object):
     """Activation between layers of the frozen forward: fp32 tensor and/or operand planes ('id', 'lrelu')."""
     __slots__ = ('x', 'id', 'lrelu')

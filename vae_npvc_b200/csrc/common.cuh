@@ -15,12 +15,13 @@ int backend();
 int option(int which);
 void set_option(int which, int value);
 // compiled defaults of the runtime options (environment variables VNB_EW_V2 / VNB_FAST_GATE and vnb_set_option
-// override them)
+// override them).  Both on: the second generation passed the GPU parity suite and is 1.3-1.8x faster at large
+// frame counts (profiles/r01_kernels_ew_v1_vs_v2.txt).
 #ifndef VNB_EW_V2_DEFAULT
-#define VNB_EW_V2_DEFAULT 0
+#define VNB_EW_V2_DEFAULT 1
 #endif
 #ifndef VNB_FAST_GATE_DEFAULT
-#define VNB_FAST_GATE_DEFAULT 0
+#define VNB_FAST_GATE_DEFAULT 1
 #endif
 
 #define VNB_REQUIRE(cond, ...)              \

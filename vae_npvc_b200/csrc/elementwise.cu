@@ -403,6 +403,16 @@ extern "C" int vnb_enc_out(const float* h, const float* s, const float* mean, co
     VNB_REQUIRE(h && mean && rstd && gamma && beta && (y || y_planes || u_planes), "enc_out: null pointer");
     VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "enc_out: bad shape");
     const int64_t rows = (int64_t)B * T;
+    if ((C & 3) == 0 && ew_v2_enabled()) {
+        const int g2 = v2_grid(rows, C / 4);
+        if (g2) {
+            const int Cp = round_up8(C);
+            if (P == 1) vnb::launch_k(enc_out_v2_kernel<1, 2>, g2, V2_THREADS, 0, ST, h, s, mean, rstd, gamma, beta, (int)rows, C, T, Cp, y, (bf16*)y_planes, (bf16*)u_planes);
+            else vnb::launch_k(enc_out_v2_kernel<3, 2>, g2, V2_THREADS, 0, ST, h, s, mean, rstd, gamma, beta, (int)rows, C, T, Cp, y, (bf16*)y_planes, (bf16*)u_planes);
+            VNB_LAUNCH_CHECK("enc_out_v2");
+            return VNB_OK;
+        }
+    }
     VEC_DISPATCH((C & 3) == 0, enc_out_kernel, rows * C, ST, h, s, mean, rstd, gamma, beta, rows, C, T, round_up8(C), P,
                  y, (bf16*)y_planes, (bf16*)u_planes);
     VNB_LAUNCH_CHECK("enc_out");

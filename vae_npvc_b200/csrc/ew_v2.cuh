@@ -1,5 +1,5 @@
-// Second-generation streaming kernels for the memory-bound plane writers (make_planes, dec_gate, gn_bwd_apply,
-// gate_bwd_apply).  What the first versions left on the table at large frame counts (profiles/r01_kernels_final.txt:
+// Second-generation streaming kernels for the memory-bound plane writers (make_planes, enc_out, dec_gate,
+// gn_bwd_apply, gate_bwd_apply).  What the first versions left on the table at large frame counts (profiles/r01_kernels_final.txt:
 // 0.45-0.62 of the measured HBM peak at 2^17 frames):
 //   * ONE 16-byte load in flight per thread per tensor and loop iteration (2048 threads x 16 B = 32 KB per SM, about
 //     the bandwidth-delay product of one SM's share of HBM) - the kernels with three input tensors reached the roof,
@@ -114,6 +114,52 @@ __global__ void __launch_bounds__(V2_THREADS) make_planes_v2_kernel(const float*
             const int64_t o = (int64_t)r * Cp + c;
             if (out_id) st_planes4<P>(out_id, o, plane, v[u]);
             if (out_act) st_planes4<P>(out_act, o, plane, w);
+        }
+    }
+}
+
+// ---- encoder block epilogue: y = GN1(h)*gamma+beta (+ s) -> y fp32, planes(y), planes(lrelu(y)) ---------------
+template <int P, int U>
+__global__ void __launch_bounds__(V2_THREADS) enc_out_v2_kernel(const float* __restrict__ h, const float* __restrict__ s,
+                                                                const float* __restrict__ mean,
+                                                                const float* __restrict__ rstd,
+                                                                const float* __restrict__ gamma,
+                                                                const float* __restrict__ beta, int rows, int C, int T,
+                                                                int Cp, float* __restrict__ y, bf16* __restrict__ y_planes,
+                                                                bf16* __restrict__ u_planes) {
+    pdl_wait();
+    V2_FRAME(C >> 2);
+    const int64_t plane = (int64_t)rows * Cp;
+    float gm[4], bt[4];
+    ld_vec<4>(gamma + c, gm);
+    ld_vec<4>(beta + c, bt);
+    for (int r0 = r_first; r0 < rows; r0 += U * rstep) {
+        float v[U][4], sv[U][4];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int r = r0 + u * rstep;
+            if (r < rows) {
+                ld_vec<4>(h + (int64_t)r * C + c, v[u]);
+                if (s) ld_vec<4>(s + (int64_t)r * C + c, sv[u]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int r = r0 + u * rstep;
+            if (r >= rows) continue;
+            const int b = r / T;
+            const float m = mean[b], rs = rstd[b];
+            float w[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                v[u][j] = (v[u][j] - m) * rs * gm[j] + bt[j];
+                if (s) v[u][j] += sv[u][j];
+                w[j] = lrelu02(v[u][j]);
+            }
+            if (y) st_vec<4>(y + (int64_t)r * C + c, v[u]);
+            const int64_t o = (int64_t)r * Cp + c;
+            if (y_planes) st_planes4<P>(y_planes, o, plane, v[u]);
+            if (u_planes) st_planes4<P>(u_planes, o, plane, w);
         }
     }
 }

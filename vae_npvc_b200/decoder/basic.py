@@ -17,7 +17,27 @@ import numpy as np
 import torch
 
 from .. import kaldi_ark
-from ..convert import ConvertEngine
+from ..convert import ConvertEngine, plan_shards
+
+
+def _dist():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        return dist
+    return None
+
+
+def merge_scp(parts, out_path, order):
+    """Concatenate per-rank scp files into one, lines in ``order`` (the trial order)."""
+    lines = {}
+    for p in parts:
+        with open(p) as f:
+            for line in f:
+                if line.strip():
+                    lines[line.split(None, 1)[0]] = line if line.endswith('\n') else line + '\n'
+    with open(out_path, 'w') as w:
+        for k in order:
+            w.write(lines[k])
 
 
 class Decoder(object):
@@ -59,19 +79,40 @@ class Decoder(object):
         spk2spk_id = None
         if (decode_dir / 'spk2spk_id').exists():
             spk2spk_id = dict(line.strip().split(None, 1) for line in open(str(decode_dir / 'spk2spk_id')))
+        # one process per GPU: the trial list is sharded by frames (utt2num_frames when present, else round-robin);
+        # each rank writes feats.<rank>.ark / .scp and rank 0 merges the scp files in trial order - no collective
+        # touches the data path
+        dist = _dist()
+        rank, world = (dist.get_rank(), dist.get_world_size()) if dist else (0, 1)
+        mine = list(range(len(trials)))
+        if world > 1:
+            nf = decode_dir / 'utt2num_frames'
+            if nf.exists():
+                frames = dict(line.strip().split(None, 1) for line in open(str(nf)) if line.strip())
+                lengths = [int(frames.get(u, 1)) for u, _ in trials]
+            else:
+                lengths = [1] * len(trials)
+            mine = plan_shards(lengths, world)[rank]
         feats, targets = [], []
-        for utt, target in trials:
+        for i in mine:
+            utt, target = trials[i]
             feats.append(np.asarray(kaldi_ark.load_mat(feats_scp[utt]), dtype=np.float32))
-            ids = [int(spk2spk_id[t]) if spk2spk_id else int(t) for t in target.split()]
-            targets.append(ids)
+            targets.append([int(spk2spk_id[t]) if spk2spk_id else int(t) for t in target.split()])
         out = self.engine.convert(feats, targets)
         Path(output_dir).mkdir(parents=True, exist_ok=True)
-        with kaldi_ark.ArkWriter('{}/feats.ark'.format(output_dir), '{}/feats.scp'.format(output_dir),
-                                 compression_method=1 if compress else None) as wf:
-            for i, ((utt, target), mat) in enumerate(zip(trials, out)):       # written in trial order
+        stem = '{}/feats'.format(output_dir) if world == 1 else '{}/feats.{}'.format(output_dir, rank)
+        with kaldi_ark.ArkWriter(stem + '.ark', stem + '.scp', compression_method=1 if compress else None) as wf:
+            for i, mat in zip(mine, out):                                       # written in trial order
+                utt, target = trials[i]
                 if log is not None:
                     log('Decode {}: {} to {}'.format(i, utt, target))
                 wf[utt] = mat
+        if world > 1:
+            dist.barrier()
+            if rank == 0:
+                merge_scp(['{}/feats.{}.scp'.format(output_dir, r) for r in range(world)],
+                          '{}/feats.scp'.format(output_dir), [u for u, _ in trials])
+            dist.barrier()
         return len(out)
 
     def get_model_info(self):
