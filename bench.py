@@ -195,6 +195,7 @@ def run_ours(args, rank, world):
     cfg.update(model_type='vae_npvc_b200.model.vqvae', precision=args.precision, cuda_graph=not args.no_graph,
                overlap_allreduce=not bool(os.environ.get('VNB_NO_OVERLAP')), allreduce=os.environ.get('VNB_ALLREDUCE', 'multimem'),
                allreduce_blocks=int(os.environ.get('VNB_AR_BLOCKS', 0)),
+               bank_overlap=not bool(os.environ.get('VNB_NO_BANK_OVERLAP')),
                graph_warmup=min(3, warm - 1), learning_rate=1e-3, max_grad_norm=10, lr_scheduler='StepLR',
                lr_param={'step_size': 100000, 'gamma': 0.5, 'last_epoch': -1})
     torch.manual_seed(777)
@@ -254,7 +255,8 @@ def run_ours(args, rank, world):
                                    '10+10 blocks, codebook 512x64 (use_ema false, embed_norm true), Adam+clip+StepLR',
                        'frames_per_gpu_per_step': B_PER_GPU * T_FRAMES, 'parallelism': 'dp%d' % world,
                        'cuda_graph': bool(on_graph),
-                       'options': {'ew_v2': _C.get_option(_C.OPT_EW_V2), 'fast_gate': _C.get_option(_C.OPT_FAST_GATE)},
+                       'options': {'ew_v2': _C.get_option(_C.OPT_EW_V2), 'fast_gate': _C.get_option(_C.OPT_FAST_GATE),
+                                   'bank_overlap': bool(tr.bank_overlap)},
                        'l2': 'no explicit flush: each step streams params+grads+Adam moments+operand planes '
                              '(~0.7 GB) > 126 MB L2; the isolated-kernel timing flushes L2 with a 256 MB write',
                        'step_roofline_frac_tensor': value * FLOP_PER_FRAME / (world * pk['tf_sus'] * 1e12)},

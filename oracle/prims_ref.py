@@ -175,7 +175,10 @@ def _conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=N
 
 
 def wn_prepare_batch(flat_p, desc, row2layer, P, wbuf, w32buf, tile2layer=None, max_k=None, row_scale=None):
-    for L in desc.tolist():
+    present = set(row2layer.tolist())              # a segment call passes the rows of its layers only
+    for li, L in enumerate(desc.tolist()):
+        if li not in present:
+            continue
         v_off, g_off, d0, d1, k, tr, wf_off, wb_off, w32_off = L[:9]
         v = flat_p[v_off:v_off + d0 * d1 * k].view(d0, d1, k)
         g = flat_p[g_off:g_off + d0].view(d0, 1, 1) if g_off >= 0 else None
@@ -189,7 +192,10 @@ def wn_prepare_batch(flat_p, desc, row2layer, P, wbuf, w32buf, tile2layer=None, 
 
 
 def wn_backward_batch(flat_p, flat_g, desc, row2layer):
-    for L in desc.tolist():
+    present = set(row2layer.tolist())
+    for li, L in enumerate(desc.tolist()):
+        if li not in present:
+            continue
         v_off, g_off, d0, d1, k = L[:5]
         if g_off < 0:
             continue

@@ -256,3 +256,42 @@ def test_trainer_three_clipped_adam_steps(cpu_prims, monkeypatch, golden_meta, t
         if n != 'quantizer.embeddings':
             assert torch.equal(p.detach(), before[n]), n
     assert abs(float(tr.model.quantizer.embeddings.detach().norm(dim=1).mean()) - 1.0) < 1e-6
+
+
+def test_weight_bank_segments_equal_whole(cpu_prims):
+    """bank.py segments: materialising / back-propagating the encoder and the decoder layers by separate calls
+    (the trainer issues the decoder's on a side stream) gives the same operand planes and (dv, dg) as one call."""
+    import vae_npvc_b200.trainer.basic as TB
+    old = TB.Pm
+    TB.Pm = prims_ref
+    try:
+        arch = synth.small_config()
+        cfg = dict(arch, model_type='vae_npvc_b200.model.vqvae', device='cpu', cuda_graph=False, precision='fp32')
+        tr = TB.Trainer(cfg)
+        tr.model.load_state_dict(synth.synthetic_state_dict(arch, 777))
+        bank = tr.bank
+        assert len(bank.segments) == 2
+        (a0, a1), (b0, b1) = bank.segments[0]['layers'], bank.segments[1]['layers']
+        assert a0 == 0 and a1 == b0 and b1 == bank.n_layers                      # contiguous, cover every layer
+        assert bank.segments[0]['rows'][1] == bank.segments[1]['rows'][0]
+        assert bank.segments[1]['rows'][1] == bank.row2layer.numel()
+        assert bank.segments[1]['tiles'][1] == bank.tile2layer.numel()
+        bank.prepare()
+        whole_w, whole_w32 = bank.wbuf.clone(), bank.w32buf.clone()
+        bank.wbuf.zero_()
+        bank.w32buf.zero_()
+        bank.prepare(1)
+        assert not torch.equal(bank.wbuf, whole_w)                               # only the decoder so far
+        bank.prepare(0)
+        assert torch.equal(bank.wbuf, whole_w) and torch.equal(bank.w32buf, whole_w32)
+        g = torch.Generator().manual_seed(3)
+        dw = torch.randn(tr._flat_g.shape, generator=g)
+        tr._flat_g.copy_(dw)
+        bank.finish_backward()
+        whole_g = tr._flat_g.clone()
+        tr._flat_g.copy_(dw)
+        bank.finish_backward(1)
+        bank.finish_backward(0)
+        assert torch.equal(tr._flat_g, whole_g)
+    finally:
+        TB.Pm = old

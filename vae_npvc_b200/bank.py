@@ -41,6 +41,7 @@ class WeightBank(object):
         rows, tiles, desc, entries = [], [], [], []
         w_off = w32_off = row0 = tile0 = 0
         self.max_k = 1
+        seg_of_layer = []                 # segment index per layer: 0 = 'encoder.*', 1 = everything after it
         for name, m in model.named_modules():
             if not isinstance(m, (nn.Conv1d, nn.ConvTranspose1d)):
                 continue
@@ -60,6 +61,7 @@ class WeightBank(object):
             e32 = w32_off if want32 else -1
             if want32:
                 w32_off += _align(v.numel())
+            seg_of_layer.append(0 if name.startswith('encoder.') and (not seg_of_layer or seg_of_layer[-1] == 0) else 1)
             desc.append([(v.data_ptr() - base) // 4, (g.data_ptr() - base) // 4 if g is not None else -1, d0, d1, k,
                          int(transposed), wf_off, wb_off, e32, row0, tile0, 0])
             rows += [len(desc) - 1] * d0
@@ -77,8 +79,26 @@ class WeightBank(object):
         self.row2layer = torch.tensor(rows if rows else [0], dtype=torch.int32, device=dev)
         self.tile2layer = torch.tensor(tiles if tiles else [0], dtype=torch.int32, device=dev)
         self.row_scale = torch.empty(max(row0, 1), dtype=torch.float32, device=dev)
+        # Segments: contiguous layer ranges (module order) that can be materialised / back-propagated by separate
+        # launches, so that the decoder's share of the two parameter-sized passes runs on a side stream beside the
+        # encoder's forward / backward (trainer/basic.py).  A segment launch gets views of the row / tile tables that
+        # start at its first row / tile and a copy of the descriptor table with row0 / tile0 shifted accordingly.
+        self.segments = []
+        for sidx in sorted(set(seg_of_layer)):
+            layers = [i for i, s_ in enumerate(seg_of_layer) if s_ == sidx]
+            r0, t0 = desc[layers[0]][9], desc[layers[0]][10]
+            last = layers[-1]
+            r1 = desc[last][9] + desc[last][2]
+            t1 = desc[last][10] + ((desc[last][2] + 63) // 64) * ((desc[last][3] + 63) // 64)
+            d = self.desc.clone()
+            d[:, 9] -= r0
+            d[:, 10] -= t0
+            self.segments.append(dict(layers=(layers[0], last + 1), rows=(r0, r1), tiles=(t0, t1), desc=d))
+        self._pending = {}                # segment index -> CUDA event its prepare() was recorded with
+        self.seg_of_ptr = {}
         self.by_ptr = {}
-        for (v, g, transposed, k, co, ci, wf_off, n_wf, wb_off, n_wb, e32) in entries:
+        for li, (v, g, transposed, k, co, ci, wf_off, n_wf, wb_off, n_wb, e32) in enumerate(entries):
+            self.seg_of_ptr[v.data_ptr()] = seg_of_layer[li]
             wf = self.wbuf[wf_off:wf_off + n_wf].view(P, k, co, Pm.pitch(ci))
             wb = self.wbuf[wb_off:wb_off + n_wb].view(P, k, ci, Pm.pitch(co))
             w32 = self.w32buf[e32:e32 + v.numel()].view_as(v) if e32 >= 0 else None
@@ -89,14 +109,36 @@ class WeightBank(object):
         return v is not None and v.data_ptr() in self.by_ptr
 
     def weights(self, v):
+        if self._pending:
+            self.wait_ready(self.seg_of_ptr[v.data_ptr()])
         return self.by_ptr[v.data_ptr()].W
 
-    def prepare(self):
-        if self.n_layers:
-            self.Pm.wn_prepare_batch(self.flat_p, self.desc, self.row2layer, self.P, self.wbuf, self.w32buf,
-                                     self.tile2layer, self.max_k, self.row_scale)
-        self.fresh = True
+    def wait_ready(self, seg):
+        """Make the current stream wait for a segment whose prepare() was issued on another stream."""
+        ev = self._pending.pop(seg, None)
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
 
-    def finish_backward(self):
+    def prepare(self, seg=None, event=None):
+        """Materialise the operand planes of every layer (``seg`` None) or of one segment.  ``event``: a CUDA event
+        the caller records after this call on the stream it was issued on; the first use of one of the segment's
+        weights on another stream waits for it (weights())."""
         if self.n_layers:
-            self.Pm.wn_backward_batch(self.flat_p, self.flat_g, self.desc, self.row2layer)
+            for i, S in enumerate(self.segments):
+                if seg is not None and i != seg:
+                    continue
+                (r0, r1), (t0, t1) = S['rows'], S['tiles']
+                self.Pm.wn_prepare_batch(self.flat_p, S['desc'], self.row2layer[r0:r1], self.P, self.wbuf, self.w32buf,
+                                         self.tile2layer[t0:t1], self.max_k, self.row_scale[r0:r1])
+                if event is not None:
+                    self._pending[i] = event
+        if seg is None:
+            self.fresh = True
+
+    def finish_backward(self, seg=None):
+        if self.n_layers:
+            for i, S in enumerate(self.segments):
+                if seg is not None and i != seg:
+                    continue
+                r0, r1 = S['rows']
+                self.Pm.wn_backward_batch(self.flat_p, self.flat_g, S['desc'], self.row2layer[r0:r1])

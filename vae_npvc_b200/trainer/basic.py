@@ -16,7 +16,8 @@ B200-native differences (all behind the same API):
     (averaged) over NCCL and the EMA codebook statistics are all-reduced inside the model
 
 New optional config keys (defaults keep the reference behaviour): ``cuda_graph`` (True),
-``graph_warmup`` (3), ``precision`` ('bf16' | 'fp32'), ``device`` ('cuda'), ``wgrad_stream`` (True).
+``graph_warmup`` (3), ``precision`` ('bf16' | 'fp32'), ``device`` ('cuda'), ``wgrad_stream`` (True),
+``bank_overlap`` (True).
 """
 import contextlib
 from importlib import import_module
@@ -137,6 +138,10 @@ class Trainer(object):
         self._side = (torch.cuda.Stream(device=self.device)
                       if self.device.type == 'cuda' and bool(config.get('wgrad_stream', True)) else None)
         self.graph_warmup = int(config.get('graph_warmup', 3))
+        # the decoder's share of the two parameter-sized weight-norm passes on the side stream, beside the encoder's
+        # forward / backward (bank.py segments)
+        self.bank_overlap = bool(config.get('bank_overlap', True))
+        self._early_finished = False
         self._graphs = {}                 # (B, X, T) -> captured step
         self._eager_steps = 0
         self.last_step_on_graph = False
@@ -266,16 +271,36 @@ class Trainer(object):
         if hasattr(Pm, 'stats_arena_begin') and self.device.type == 'cuda':
             Pm.stats_arena_begin(self.device)
         try:
-            self.bank.prepare()
+            split = self.bank_overlap and self._side is not None and len(self.bank.segments) > 1
+            if split:
+                # encoder weights on this stream; the rest (decoder: 2/3 of the parameters) on the side stream while
+                # the encoder's forward runs - the first decoder conv waits for it (bank.weights)
+                ev0 = torch.cuda.Event()
+                ev0.record()
+                self._side.wait_event(ev0)
+                self.bank.prepare(0)
+                with torch.cuda.stream(self._side):
+                    ev1 = torch.cuda.Event()
+                    for sidx in range(1, len(self.bank.segments)):
+                        self.bank.prepare(sidx, event=ev1)
+                    ev1.record()
+                self.bank.fresh = True
+            else:
+                self.bank.prepare()
             if jitter_src is not None:
                 self.model.jitter.sources = lambda length: jitter_src
             dist = _dist()
             self._reduced = []
             overlap = (dist is not None and self._allreduce_kind != 'none' and self._side is not None and self._comm is not None and bool(self._buckets)
                        and self.overlap_allreduce)
+            self._early_finished = False
             if overlap:
                 _model_mod.set_grad_ready_callback(self._grad_ready)                 # hooks registered during forward
+            elif split and dist is None:
+                _model_mod.set_grad_ready_callback(self._decoder_done)
             output, loss, detail = self.model([x, y])
+            for sidx in range(len(self.bank.segments)):
+                self.bank.wait_ready(sidx)          # joins the side stream even if a segment was never used
             loss.backward()
             _model_mod.set_grad_ready_callback(None)
             if self._side is not None:
@@ -298,7 +323,10 @@ class Trainer(object):
                         self._all_reduce_mean(pos, total)
                 if comm is not None:
                     torch.cuda.current_stream().wait_stream(comm)
-            self.bank.finish_backward()
+            if self._early_finished:
+                self.bank.finish_backward(0)        # the other segments went through on the side stream already
+            else:
+                self.bank.finish_backward()
             if dist is not None and self._mc is None and self._allreduce_kind != 'none':
                 self._flat_g.mul_(1.0 / dist.get_world_size())      # the multimem kernel already scaled
         finally:
@@ -313,6 +341,18 @@ class Trainer(object):
         keys = list(detail.keys())
         scal = torch.stack([detail[k].t.reshape(()).float() for k in keys])
         return keys, scal
+
+    def _decoder_done(self, name):
+        """Single-GPU twin of _grad_ready: when the gradient reaches the decoder's input every decoder weight gradient
+        is final (its GEMMs are queued on the side stream), so the decoder's weight-norm backward runs there while the
+        encoder is back-propagated."""
+        if name != 'decoder' or self._early_finished:
+            return
+        self._side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self._side):
+            for sidx in range(1, len(self.bank.segments)):
+                self.bank.finish_backward(sidx)
+        self._early_finished = True
 
     def _grad_ready(self, name):
         """Called from a tensor hook during backward (model/vqvae.py _mark): the modules after ``name`` have been
