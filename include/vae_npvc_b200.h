@@ -54,15 +54,17 @@ void vnb_launch_count_reset(void);
 /* 0 = auto (TC where the shape allows), 1 = SIMT everywhere, 2 = TC (error if impossible) */
 void vnb_set_backend(int backend);
 int vnb_get_backend(void);
-/* runtime options; initial value = environment variable of the same name (VNB_EW_V2, VNB_FAST_GATE), else the
+/* runtime options; initial value = environment variable of the same name (VNB_EW_V2, VNB_FAST_GATE, VNB_WN_V2), else the
  * compiled default.
  *   VNB_OPT_EW_V2     second-generation streaming kernels for make_planes / dec_gate / gn_bwd_apply /
  *                     gate_bwd_apply (csrc/ew_v2.cuh); same results as the first versions
  *   VNB_OPT_FAST_GATE with EW_V2 and P == 1 (bf16 operand planes) only: tanh.approx / __expf in the gate, whose
- *                     2^-11 error is below the bf16 rounding of the result; P == 3 always uses tanhf / expf */
+ *                     2^-11 error is below the bf16 rounding of the result; P == 3 always uses tanhf / expf
+ *   VNB_OPT_WN_V2     warp-per-row weight-norm backward over the flat buffers (csrc/weightnorm.cu) */
 #define VNB_OPT_EW_V2 0
 #define VNB_OPT_FAST_GATE 1
-#define VNB_OPT_COUNT_ 2
+#define VNB_OPT_WN_V2 2
+#define VNB_OPT_COUNT_ 3
 void vnb_set_option(int which, int value);
 int vnb_get_option(int which);
 /* debug: how many bounded mbarrier waits of the tcgen05 kernels timed out since load (must stay 0);

@@ -160,6 +160,19 @@ def main():
     rec('adam_step (4 reads, 3 writes)', dt, n * 4 * 7)
     dt = timeit(lambda: Pm.sqnorm(g, sqn))
     rec('sqnorm (1 read)', dt, n * 4)
+    # ---------------- batched weight-norm passes over the VCC2020 model's flat buffers ----------------
+    del p, g, m, v
+    from oracle import synth
+    from vae_npvc_b200.trainer.basic import Trainer
+    arch = synth.arch_config()
+    tr = Trainer(dict(arch, model_type='vae_npvc_b200.model.vqvae', precision='bf16', cuda_graph=False))
+    pw = sum(e.v.numel() for e in tr.bank.by_ptr.values())
+    out['options']['wn_v2'] = _C.get_option(_C.OPT_WN_V2)
+    dt = timeit(lambda: tr.bank.prepare(), flush=flush)
+    rec('wn_prepare_batch (%.1f M weights -> 2 bf16 operands)' % (pw / 1e6), dt, pw * (4 + 2 + 2))
+    tr._flat_g.normal_()
+    dt = timeit(lambda: tr.bank.finish_backward(), flush=flush)
+    rec('wn_backward_batch (dw, v -> dv, dg)', dt, pw * 12)
     os.makedirs(os.path.join(ROOT, 'gpurun_out'), exist_ok=True)
     json.dump(out, open(os.path.join(ROOT, 'gpurun_out', 'bench_kernels%s.json' % ('_' + tag if tag else '')), 'w'), indent=1)
 

@@ -128,7 +128,7 @@ def get_backend():
     return load().vnb_get_backend()
 
 
-OPT_EW_V2, OPT_FAST_GATE = 0, 1
+OPT_EW_V2, OPT_FAST_GATE, OPT_WN_V2 = 0, 1, 2
 
 
 def set_option(which, value):

@@ -20,6 +20,9 @@ void set_option(int which, int value);
 #ifndef VNB_EW_V2_DEFAULT
 #define VNB_EW_V2_DEFAULT 1
 #endif
+#ifndef VNB_WN_V2_DEFAULT
+#define VNB_WN_V2_DEFAULT 1
+#endif
 #ifndef VNB_FAST_GATE_DEFAULT
 #define VNB_FAST_GATE_DEFAULT 1
 #endif

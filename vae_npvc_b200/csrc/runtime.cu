@@ -31,6 +31,7 @@ static void opts_init() {
     if (g_opts_init.load(std::memory_order_acquire)) return;
     g_opts[VNB_OPT_EW_V2].store(env_or("VNB_EW_V2", VNB_EW_V2_DEFAULT));
     g_opts[VNB_OPT_FAST_GATE].store(env_or("VNB_FAST_GATE", VNB_FAST_GATE_DEFAULT));
+    g_opts[VNB_OPT_WN_V2].store(env_or("VNB_WN_V2", VNB_WN_V2_DEFAULT));
     g_opts_init.store(true, std::memory_order_release);
 }
 int option(int which) {

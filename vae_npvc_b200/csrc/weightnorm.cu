@@ -114,9 +114,72 @@ __device__ __forceinline__ void store_planes2(bf16* base, int64_t off, int64_t p
     }
 }
 
-__global__ void __launch_bounds__(256) wn_tiles_kernel(const float* __restrict__ flat_p, const int64_t* __restrict__ desc,
+// Fast path of wn_tiles_kernel for a FULL 64 x 64 tile, bf16 operand mode (P == 1), k known at compile time:
+// no runtime divisions (the generic path divides by k for every element and by the tile width for every store
+// row), every load of the tile issued before the first use, and 8-byte stores (4 bf16 per lane, two tile rows per
+// warp instruction) instead of 4-byte ones.  The generic path is issue-bound (1.85 TB/s of traffic for a pass that
+// moves 8 bytes per parameter); this one does a third of its instructions.
+template <int K>
+__device__ __forceinline__ void wn_tile_full_p1(const float* __restrict__ v, float* __restrict__ w32,
+                                                const float* __restrict__ scale, int row0, int d0, int d1, int r0, int c0,
+                                                bf16* __restrict__ D, bf16* __restrict__ Tt, float* __restrict__ tile) {
+    constexpr int TP = WN_TILE + 1;
+    constexpr int SEG4 = WN_TILE * K / 4;              // float4 per tile row
+    constexpr int PER = SEG4 * WN_TILE / 256;          // float4 per thread: 4 * K
+    float4 x[PER];
+#pragma unroll
+    for (int u = 0; u < PER; u++) {
+        const int i = u * 256 + threadIdx.x;
+        const int rr = i / SEG4, e4 = i - rr * SEG4;
+        x[u] = *reinterpret_cast<const float4*>(v + ((int64_t)(r0 + rr) * d1 + c0) * K + 4 * e4);
+    }
+#pragma unroll
+    for (int u = 0; u < PER; u++) {
+        const int i = u * 256 + threadIdx.x;
+        const int rr = i / SEG4, e4 = i - rr * SEG4;
+        const float sc = scale[row0 + rr];
+        const float w[4] = {x[u].x * sc, x[u].y * sc, x[u].z * sc, x[u].w * sc};
+        if (w32) *reinterpret_cast<float4*>(w32 + ((int64_t)(r0 + rr) * d1 + c0) * K + 4 * e4) = make_float4(w[0], w[1], w[2], w[3]);
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const int e = 4 * e4 + q;
+            const int cc = e / K, j = e - cc * K;
+            tile[(j * WN_TILE + rr) * TP + cc] = w[q];
+        }
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int half = lane >> 4, l4 = (lane & 15) * 4;
+    const int p1 = (d1 + 7) & ~7, p0 = (d0 + 7) & ~7;
+    if (D) {                                           // [j][row][col]: a half-warp writes one 64-wide row
+#pragma unroll
+        for (int it = 0; it < K * WN_TILE / 16; it++) {
+            const int idx = it * 16 + warp * 2 + half;
+            const int j = idx / WN_TILE, rr = idx - j * WN_TILE;
+            const float* src = tile + (j * WN_TILE + rr) * TP + l4;
+            uint2 o;
+            o.x = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[0])) | ((uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[1])) << 16);
+            o.y = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[2])) | ((uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[3])) << 16);
+            *reinterpret_cast<uint2*>(D + ((int64_t)j * d0 + r0 + rr) * p1 + c0 + l4) = o;
+        }
+    }
+    if (Tt) {                                          // [K-1-j][col][row]: a half-warp writes 64 rows of one column
+#pragma unroll
+        for (int it = 0; it < K * WN_TILE / 16; it++) {
+            const int idx = it * 16 + warp * 2 + half;
+            const int j = idx / WN_TILE, cc = idx - j * WN_TILE;
+            const float* src = tile + (j * WN_TILE + l4) * TP + cc;
+            uint2 o;
+            o.x = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[0])) | ((uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[TP])) << 16);
+            o.y = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[2 * TP])) | ((uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[3 * TP])) << 16);
+            *reinterpret_cast<uint2*>(Tt + ((int64_t)(K - 1 - j) * d1 + c0 + cc) * p0 + r0 + l4) = o;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256, 3) wn_tiles_kernel(const float* __restrict__ flat_p, const int64_t* __restrict__ desc,
                                                        const int* __restrict__ tile2layer, const float* __restrict__ scale,
-                                                       int P, bf16* __restrict__ wbuf, float* __restrict__ w32buf) {
+                                                       int P, bf16* __restrict__ wbuf, float* __restrict__ w32buf, int fast) {
     pdl_wait();
     extern __shared__ float wn_tile[];                // [k][64][65]
     constexpr int TP = WN_TILE + 1;
@@ -134,6 +197,16 @@ __global__ void __launch_bounds__(256) wn_tiles_kernel(const float* __restrict__
     const int seg = nc * k;                            // contiguous floats per tile row
     const int total = nr * seg;
     const int row0 = (int)L[9] + r0;
+    if (fast && P == 1 && nr == WN_TILE && nc == WN_TILE && (k == 1 || k == 3) &&
+        ((((uintptr_t)(v + ((int64_t)r0 * d1 + c0) * k)) | ((uintptr_t)((int64_t)d1 * k * 4)) |
+          (w32 ? (uintptr_t)(w32 + ((int64_t)r0 * d1 + c0) * k) : 0)) & 15) == 0) {
+        const int64_t o_d = transposed ? L[7] : L[6], o_t = transposed ? L[6] : L[7];
+        bf16* Dp = o_d >= 0 ? wbuf + o_d : nullptr;
+        bf16* Tp = o_t >= 0 ? wbuf + o_t : nullptr;
+        if (k == 3) wn_tile_full_p1<3>(v, w32, scale, row0, d0, d1, r0, c0, Dp, Tp, wn_tile);
+        else wn_tile_full_p1<1>(v, w32, scale, row0, d0, d1, r0, c0, Dp, Tp, wn_tile);
+        return;
+    }
     if ((seg & 3) == 0 && ((((uintptr_t)(v + ((int64_t)r0 * d1 + c0) * k)) | ((uintptr_t)((int64_t)d1 * k * 4))) & 15) == 0) {
         const int seg4 = seg >> 2, total4 = nr * seg4;
         for (int b0 = 0; b0 < total4; b0 += 256 * 6) {
@@ -271,6 +344,127 @@ __global__ void __launch_bounds__(256) wn_backward_batch_kernel(const float* __r
     for (int e = threadIdx.x; e < n; e += blockDim.x) dr[e] = a * dr[e] - b * vr[e];
 }
 
+// Second generation of the same pass: ONE WARP per weight row, rows taken in a warp-strided loop.
+// The block-per-row kernel above keeps one row (<= 24 KB of v and dw) in flight per CTA and spends two block-wide
+// reductions (four __syncthreads) between its loads and its stores: at ~4 resident CTAs per SM that is ~50 KB in
+// flight per SM with idle phases, 0.42 of the HBM roof.  Here a warp keeps a whole row of up to 1536 floats in
+// registers (12 + 12 float4 per lane, all loads issued before the first use: 12 warps x 12 KB = 144 KB in flight
+// per SM), reduces with shuffles only and writes dv from the registers; longer rows (the decoder's 3072-float
+// ConvTranspose rows) take two passes, the second one re-reading the row from L2.
+constexpr int WNB_MAXV = 12;
+constexpr int WNB_CH = 8;
+
+__global__ void __launch_bounds__(128, 2) wn_backward_batch_v2_kernel(const float* __restrict__ flat_p,
+                                                                      float* __restrict__ flat_g,
+                                                                      const int64_t* __restrict__ desc,
+                                                                      const int* __restrict__ row2layer, int total_rows) {
+    pdl_wait();
+    const int lane = threadIdx.x & 31;
+    const int nwarps = gridDim.x * 4;
+    for (int row = blockIdx.x * 4 + (threadIdx.x >> 5); row < total_rows; row += nwarps) {
+        const int64_t* L = desc + (int64_t)row2layer[row] * WN_DESC;
+        if (L[1] < 0) continue;                     // plain weight: dw already is its gradient
+        const int i = row - (int)L[9];
+        const int n = (int)L[3] * (int)L[4];
+        const float* vr = flat_p + L[0] + (int64_t)i * n;
+        float* dr = flat_g + L[0] + (int64_t)i * n;
+        const float gi = flat_p[L[1] + i];
+        float ss = 0.f, dot = 0.f;
+        const bool vec = (n & 3) == 0 && ((((uintptr_t)vr) | ((uintptr_t)dr)) & 15) == 0;
+        if (vec && (n >> 2) <= 32 * WNB_MAXV) {
+            const float4* v4 = reinterpret_cast<const float4*>(vr);
+            float4* d4 = reinterpret_cast<float4*>(dr);
+            const int n4 = n >> 2;
+            float4 xv[WNB_MAXV], xd[WNB_MAXV];
+#pragma unroll
+            for (int u = 0; u < WNB_MAXV; u++) {
+                const int e = lane + 32 * u;
+                if (e < n4) {
+                    xv[u] = v4[e];
+                    xd[u] = d4[e];
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < WNB_MAXV; u++) {
+                if (lane + 32 * u < n4) {
+                    ss += (xv[u].x * xv[u].x + xv[u].y * xv[u].y) + (xv[u].z * xv[u].z + xv[u].w * xv[u].w);
+                    dot += (xv[u].x * xd[u].x + xv[u].y * xd[u].y) + (xv[u].z * xd[u].z + xv[u].w * xd[u].w);
+                }
+            }
+            ss = warp_sum(ss);
+            dot = warp_sum(dot);
+            const float norm = sqrtf(ss);
+            const float a = gi / norm, b = gi * dot / (norm * ss);
+#pragma unroll
+            for (int u = 0; u < WNB_MAXV; u++) {
+                const int e = lane + 32 * u;
+                if (e < n4)
+                    d4[e] = make_float4(a * xd[u].x - b * xv[u].x, a * xd[u].y - b * xv[u].y, a * xd[u].z - b * xv[u].z,
+                                        a * xd[u].w - b * xv[u].w);
+            }
+            if (lane == 0) flat_g[L[1] + i] = dot / norm;
+        } else if (vec) {
+            // longer rows: two passes in chunks of 8 float4 of each tensor in flight per lane; the second pass finds the row in L2
+            const float4* v4 = reinterpret_cast<const float4*>(vr);
+            float4* d4 = reinterpret_cast<float4*>(dr);
+            const int n4 = n >> 2;
+            for (int e0 = 0; e0 < n4; e0 += 32 * WNB_CH) {
+                float4 xv[WNB_CH], xd[WNB_CH];
+#pragma unroll
+                for (int u = 0; u < WNB_CH; u++) {
+                    const int e = e0 + lane + 32 * u;
+                    if (e < n4) {
+                        xv[u] = v4[e];
+                        xd[u] = d4[e];
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < WNB_CH; u++) {
+                    if (e0 + lane + 32 * u < n4) {
+                        ss += (xv[u].x * xv[u].x + xv[u].y * xv[u].y) + (xv[u].z * xv[u].z + xv[u].w * xv[u].w);
+                        dot += (xv[u].x * xd[u].x + xv[u].y * xd[u].y) + (xv[u].z * xd[u].z + xv[u].w * xd[u].w);
+                    }
+                }
+            }
+            ss = warp_sum(ss);
+            dot = warp_sum(dot);
+            const float norm = sqrtf(ss);
+            const float a = gi / norm, b = gi * dot / (norm * ss);
+            for (int e0 = 0; e0 < n4; e0 += 32 * WNB_CH) {
+                float4 xv[WNB_CH], xd[WNB_CH];
+#pragma unroll
+                for (int u = 0; u < WNB_CH; u++) {
+                    const int e = e0 + lane + 32 * u;
+                    if (e < n4) {
+                        xv[u] = v4[e];
+                        xd[u] = d4[e];
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < WNB_CH; u++) {
+                    const int e = e0 + lane + 32 * u;
+                    if (e < n4)
+                        d4[e] = make_float4(a * xd[u].x - b * xv[u].x, a * xd[u].y - b * xv[u].y,
+                                            a * xd[u].z - b * xv[u].z, a * xd[u].w - b * xv[u].w);
+                }
+            }
+            if (lane == 0) flat_g[L[1] + i] = dot / norm;
+        } else {
+            for (int e = lane; e < n; e += 32) {
+                const float x = vr[e];
+                ss += x * x;
+                dot += x * dr[e];
+            }
+            ss = warp_sum(ss);
+            dot = warp_sum(dot);
+            const float norm = sqrtf(ss);
+            const float a = gi / norm, b = gi * dot / (norm * ss);
+            for (int e = lane; e < n; e += 32) dr[e] = a * dr[e] - b * vr[e];
+            if (lane == 0) flat_g[L[1] + i] = dot / norm;
+        }
+    }
+}
+
 }  // namespace vnb
 
 extern "C" int vnb_wn_prepare_batch(const float* flat_p, const int64_t* desc, const int* row2layer, int total_rows,
@@ -291,7 +485,8 @@ extern "C" int vnb_wn_prepare_batch(const float* flat_p, const int64_t* desc, co
     cudaStream_t st = (cudaStream_t)stream;
     vnb::launch_k(vnb::wn_rowscale_kernel, vnb::ceil_div(total_rows, 8), 256, 0, st, flat_p, desc, row2layer, total_rows, row_scale);
     VNB_LAUNCH_CHECK("wn_rowscale");
-    vnb::launch_k(vnb::wn_tiles_kernel, total_tiles, 256, smem, st, flat_p, desc, tile2layer, row_scale, P, (vnb::bf16*)wbuf, w32buf);
+    vnb::launch_k(vnb::wn_tiles_kernel, total_tiles, 256, smem, st, flat_p, desc, tile2layer, row_scale, P, (vnb::bf16*)wbuf, w32buf,
+                  vnb::option(VNB_OPT_WN_V2));
     VNB_LAUNCH_CHECK("wn_tiles");
     return VNB_OK;
 }
@@ -299,6 +494,14 @@ extern "C" int vnb_wn_prepare_batch(const float* flat_p, const int64_t* desc, co
 extern "C" int vnb_wn_backward_batch(const float* flat_p, float* flat_g, const int64_t* desc, const int* row2layer,
                                      int total_rows, void* stream) {
     VNB_REQUIRE(flat_p && flat_g && desc && row2layer && total_rows > 0, "wn_backward_batch: bad arguments");
+    if (vnb::option(VNB_OPT_WN_V2)) {
+        int grid = vnb::ceil_div(total_rows, 4);
+        if (grid > 148 * 3 * 4) grid = 148 * 3 * 4;           // three resident 4-warp CTAs per SM, several rows per warp
+        vnb::launch_k(vnb::wn_backward_batch_v2_kernel, grid, 128, 0, (cudaStream_t)stream, flat_p, flat_g, desc, row2layer,
+                      total_rows);
+        VNB_LAUNCH_CHECK("wn_backward_batch_v2");
+        return VNB_OK;
+    }
     vnb::launch_k(vnb::wn_backward_batch_kernel, total_rows, 256, 0, (cudaStream_t)stream, flat_p, flat_g, desc, row2layer);
     VNB_LAUNCH_CHECK("wn_backward_batch");
     return VNB_OK;
