@@ -1,6 +1,6 @@
 """Benchmark of the VQ-VAE training step (BASELINE.json metric: train frames/s, fwd+bwd+optimiser).
 
-    python bench.py --gpus 1 --steps 20 --warmup 5                  # our CUDA path, one B200
+    python bench.py --gpus 1 --steps 100 --warmup 10                # our CUDA path, one B200
     torchrun --nproc-per-node N ... bench.py --gpus N ...           # batch-sharded DP, weak scaling
     python bench.py --impl reference ...                            # the reference's CPU path (oracle port)
 
@@ -196,6 +196,7 @@ def run_ours(args, rank, world):
                overlap_allreduce=not bool(os.environ.get('VNB_NO_OVERLAP')), allreduce=os.environ.get('VNB_ALLREDUCE', 'multimem'),
                allreduce_blocks=int(os.environ.get('VNB_AR_BLOCKS', 0)),
                bank_overlap=not bool(os.environ.get('VNB_NO_BANK_OVERLAP')),
+               sparse_grad_zero=not bool(os.environ.get('VNB_NO_SPARSE_ZERO')),
                graph_warmup=min(3, warm - 1), learning_rate=1e-3, max_grad_norm=10, lr_scheduler='StepLR',
                lr_param={'step_size': 100000, 'gamma': 0.5, 'last_epoch': -1})
     torch.manual_seed(777)
@@ -256,7 +257,7 @@ def run_ours(args, rank, world):
                        'frames_per_gpu_per_step': B_PER_GPU * T_FRAMES, 'parallelism': 'dp%d' % world,
                        'cuda_graph': bool(on_graph),
                        'options': {'ew_v2': _C.get_option(_C.OPT_EW_V2), 'fast_gate': _C.get_option(_C.OPT_FAST_GATE),
-                                   'bank_overlap': bool(tr.bank_overlap)},
+                                   'bank_overlap': bool(tr.bank_overlap), 'sparse_grad_zero': tr._zero_idx is not None},
                        'l2': 'no explicit flush: each step streams params+grads+Adam moments+operand planes '
                              '(~0.7 GB) > 126 MB L2; the isolated-kernel timing flushes L2 with a 256 MB write',
                        'step_roofline_frac_tensor': value * FLOP_PER_FRAME / (world * pk['tf_sus'] * 1e12)},
@@ -292,8 +293,8 @@ def run_ours(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=20)
-    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--steps', type=int, default=100)          # 0.2 s of timed steps: 20-step runs scatter by +-2 %
+    ap.add_argument('--warmup', type=int, default=10)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'])
     ap.add_argument('--no-graph', action='store_true')

@@ -154,6 +154,10 @@ int vnb_gn_bwd_rows(const float* dn, const float* h, const float* mean, const fl
  * a (B,2C,T) pre-norm */
 int vnb_gate_bwd_rows(const float* dg, const float* a, const float* mean, const float* rstd,
                       const float* gamma, const float* beta, int B, int C, int T, float* R, void* stream);
+/* same, told the operand mode of the step: with P == 1 (bf16 planes) and VNB_OPT_FAST_GATE the gate is re-evaluated
+ * with the approximate functions the forward and the apply kernel use in that mode; P == 3 is vnb_gate_bwd_rows */
+int vnb_gate_bwd_rows_p(const float* dg, const float* a, const float* mean, const float* rstd,
+                        const float* gamma, const float* beta, int B, int C, int T, int P, float* R, void* stream);
 /* from R: dgamma[c], dbeta[c], S[b,group,0..1] = sum_c gamma*R0, sum_c gamma*R1, and (optional)
  * dpre_bsum[b,c] = sum_t dpre, dpre_csum[c] = sum_{b,t} dpre  (dpre = grad wrt the GN input);
  * dbeta2 / dpre_csum2: optional second copies (two biases that receive the same gradient, written

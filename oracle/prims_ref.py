@@ -317,7 +317,7 @@ def _gate_dn(dg, a, mean, rstd, gamma, beta):
     return torch.cat([dg * sg * (1 - th * th), dg * th * sg * (1 - sg)], dim=1), xh
 
 
-def gate_bwd_rows(dg, a, mean, rstd, gamma, beta):
+def gate_bwd_rows(dg, a, mean, rstd, gamma, beta, P=3):
     dn, xh = _gate_dn(dg, a, mean, rstd, gamma, beta)
     return torch.stack([dn.sum(2), (dn * xh).sum(2), xh.sum(2)], dim=2)
 

@@ -307,6 +307,7 @@ namespace vnb {
 // Gate variant of bwd_rows: a thread owns channel c < C and accumulates the three row sums of BOTH halves
 // (tanh half c, sigmoid half C + c) from one tanh / exp pair per element, four frames in flight.
 // grid (ceil(C/32), B), block 32 x 8.
+template <bool FAST>
 __global__ void __launch_bounds__(256) gate_bwd_rows_kernel(const float* __restrict__ dg, const float* __restrict__ a,
                                                             const float* __restrict__ mean, const float* __restrict__ rstd,
                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
@@ -333,8 +334,8 @@ __global__ void __launch_bounds__(256) gate_bwd_rows_kernel(const float* __restr
             for (int u = 0; u < 4; u++) {
                 if (t0 + 8 * u >= T) continue;
                 const float x1 = (a1[u] - m1) * rs1, x2 = (a2[u] - m2) * rs2;
-                const float th = tanhf(x1 * g1 + b1);
-                const float sg = sigmoidf_(x2 * g2 + b2);
+                const float th = gate_tanh<FAST>(x1 * g1 + b1);
+                const float sg = gate_sigmoid<FAST>(x2 * g2 + b2);
                 const float dn1 = d[u] * sg * (1.f - th * th), dn2 = d[u] * th * sg * (1.f - sg);
                 s[0] += dn1; s[1] += dn1 * x1; s[2] += x1;
                 s[3] += dn2; s[4] += dn2 * x2; s[5] += x2;
@@ -354,13 +355,23 @@ __global__ void __launch_bounds__(256) gate_bwd_rows_kernel(const float* __restr
 }
 }  // namespace vnb
 
-extern "C" int vnb_gate_bwd_rows(const float* dg, const float* a, const float* mean, const float* rstd,
-                                 const float* gamma, const float* beta, int B, int C, int T, float* R, void* stream) {
-    VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && R && B > 0 && B <= 65535 && C > 0 && T > 0,
-                "gate_bwd_rows: bad arguments");
-    vnb::launch_k(gate_bwd_rows_kernel, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R);
+extern "C" int vnb_gate_bwd_rows_p(const float* dg, const float* a, const float* mean, const float* rstd,
+                                   const float* gamma, const float* beta, int B, int C, int T, int P, float* R,
+                                   void* stream) {
+    VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && R && B > 0 && B <= 65535 && C > 0 && T > 0 &&
+                    (P == 1 || P == 3), "gate_bwd_rows: bad arguments");
+    // the gate's approximate functions only where the operand planes are bf16 anyway (see ew_v2.cuh)
+    if (P == 1 && ew_v2_enabled() && fast_gate_enabled())
+        vnb::launch_k(gate_bwd_rows_kernel<true>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R);
+    else
+        vnb::launch_k(gate_bwd_rows_kernel<false>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R);
     VNB_LAUNCH_CHECK("gate_bwd_rows");
     return VNB_OK;
+}
+
+extern "C" int vnb_gate_bwd_rows(const float* dg, const float* a, const float* mean, const float* rstd,
+                                 const float* gamma, const float* beta, int B, int C, int T, float* R, void* stream) {
+    return vnb_gate_bwd_rows_p(dg, a, mean, rstd, gamma, beta, B, C, T, 3, R, stream);
 }
 
 extern "C" int vnb_gn_bwd_finalize(const float* R, const float* gamma, const float* rstd, int B, int C, int T,

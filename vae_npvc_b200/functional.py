@@ -384,7 +384,7 @@ class DecBlockFn(Function):
             db_rs = None
         dg = Pm.conv_fwd(drpl, ctx.wrs_wb, 1, 1, C)
         dv_rs, dg_rs = _wgrad(drpl, ctx.gpl, 1, 1, False, v_rs, g_rs)
-        R = Pm.gate_bwd_rows(dg, a, mean, rstd, gamma, beta)
+        R = Pm.gate_bwd_rows(dg, a, mean, rstd, gamma, beta, P)
         slots = {'dgamma': _slot(gamma), 'dbeta': _slot(beta), 'csum': _slot(b_in),
                  'csum2': _slot(b_c) if has_cond else None}          # both biases add to the GN input
         dgamma, dbeta, Ssum, bsum, csum = Pm.gn_bwd_finalize(R, gamma, rstd, T, 2, True, slots)

@@ -269,10 +269,11 @@ def gn_bwd_rows(dn, h, mean, rstd, groups):
     return R
 
 
-def gate_bwd_rows(dg, a, mean, rstd, gamma, beta):
+def gate_bwd_rows(dg, a, mean, rstd, gamma, beta, P=3):
+    """``P``: operand mode of the step (1 = bf16 planes: the gate may use the approximate functions)."""
     B, C2, T = a.shape
     R = _f32((B, C2, 3), a)
-    _C.call('gate_bwd_rows', _r(dg), _r(a), mean, rstd, gamma, beta, B, C2 // 2, T, R)
+    _C.call('gate_bwd_rows_p', _r(dg), _r(a), mean, rstd, gamma, beta, B, C2 // 2, T, P, R)
     return R
 
 

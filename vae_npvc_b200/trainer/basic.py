@@ -17,7 +17,7 @@ B200-native differences (all behind the same API):
 
 New optional config keys (defaults keep the reference behaviour): ``cuda_graph`` (True),
 ``graph_warmup`` (3), ``precision`` ('bf16' | 'fp32'), ``device`` ('cuda'), ``wgrad_stream`` (True),
-``bank_overlap`` (True).
+``bank_overlap`` (True), ``sparse_grad_zero`` (True).
 """
 import contextlib
 from importlib import import_module
@@ -119,6 +119,7 @@ class Trainer(object):
         self.optimizer = FlatAdam(self._params, self._flat_p, self._flat_g, learning_rate)
         # all conv weights materialised / back-propagated through weight-norm by one kernel each per step
         self.bank = WeightBank(self.model, self._flat_p, self._flat_g, Fn.get_precision(), Pm)
+        self._zero_idx = self._plan_grad_zero() if bool(config.get('sparse_grad_zero', True)) else None
         if lr_scheduler is not None:
             self._step_size, self._gamma = int(lr_param.get('step_size', 100000)), float(lr_param.get('gamma', 0.5))
             self.scheduler = 'StepLR'
@@ -194,6 +195,25 @@ class Trainer(object):
             plan[enc[cut - 1]] = (spans[enc[cut]][0], _end(enc[-1]))
         return plan
 
+    def _plan_grad_zero(self):
+        """zero_grad (trainer/basic.py:57) without the 125 MB memset: the weight-gradient GEMMs WRITE dW into the v
+        slots of the flat gradient buffer (99.6 % of it), so only the slots that are accumulated into - biases,
+        weight_g, GroupNorm affine, codebook, speaker table - need zeroing.  -> int64 index tensor of those elements
+        (None: nothing to gain).  Every conv of the model mirrors is used in every forward, which is what makes the
+        v slots fully rewritten each step."""
+        if self.device.type != 'cuda' or not self.bank.by_ptr:
+            return None
+        total = self._flat_g.numel()
+        keep = torch.ones(total, dtype=torch.bool)
+        base = self._flat_p.data_ptr()
+        for e in self.bank.by_ptr.values():
+            off = (e.v.data_ptr() - base) // 4
+            keep[off:off + e.v.numel()] = False
+        idx = keep.nonzero().view(-1)
+        if idx.numel() * 8 > total:
+            return None
+        return idx.to(self.device)
+
     # ---- flat parameter / gradient buffers -------------------------------------------------------
     def _flatten(self):
         params = [p for p in self.model.parameters() if p.requires_grad]
@@ -264,7 +284,10 @@ class Trainer(object):
     def _step_body(self, x, y, jitter_src=None):
         """zero_grad -> forward -> backward -> [all-reduce] -> clip + Adam + StepLR
         (trainer/basic.py:57-72).  Returns (loss-detail keys, stacked 0-d device scalars)."""
-        self._flat_g.zero_()
+        if self._zero_idx is not None:
+            self._flat_g.index_fill_(0, self._zero_idx, 0.0)
+        else:
+            self._flat_g.zero_()
         _lvq.defer_items(True)
         Fn.set_bank(self.bank)
         Fn.set_side_stream(self._side)
