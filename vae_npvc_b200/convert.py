@@ -243,9 +243,9 @@ class ConvertEngine(object):
         return t.to(self.device, non_blocking=True) if self._cuda() else t
 
     def _run(self, n_items, lengths_all, make_job):
-        """Plan batches, run ``make_job(sel) -> (device result, lens, finish)`` for each and un-pack.  The host
-        packs batch k+1 while batch k runs: every device call is asynchronous and a batch's results are only
-        waited for (its event) after the next batch has been queued."""
+        """Plan batches, run ``make_job(sel) -> (pinned host result, finish(host, b, i))`` for each and un-pack.
+        The host packs batch k+1 while batch k runs: every device call is asynchronous and a batch's results are
+        only waited for (its event) after the next batch has been queued."""
         out = [None] * n_items
         pending = None
 
