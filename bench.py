@@ -27,7 +27,7 @@ FLOP_PER_FRAME = 178_757_632          # algorithmic fwd+bwd FLOP/frame, SURVEY.m
 
 
 def workload_arch():
-    from oracle import synth
+    from vae_npvc_b200 import synth
     return synth.arch_config(X=80, C=512, D=64, K=512, Y=128, S=128, y_num=117, stacks=10, use_ema=False,
                              embed_norm=True)
 
@@ -180,7 +180,7 @@ def time_dominant_kernel(P, iters=20):
 def run_ours(args, rank, world):
     from vae_npvc_b200 import _C
     from vae_npvc_b200.trainer.basic import Trainer
-    from oracle import synth
+    from vae_npvc_b200 import synth
     _C.require_cuda()
     local = int(os.environ.get('LOCAL_RANK', 0))
     torch.cuda.set_device(local)

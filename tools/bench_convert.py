@@ -31,7 +31,7 @@ def main():
     ap.add_argument('--cpu-utts', type=int, default=3)
     ap.add_argument('--out', default='')
     a = ap.parse_args()
-    from oracle import synth
+    from vae_npvc_b200 import synth
     from oracle import vqvae_oracle as O
     import vae_npvc_b200.functional as Fn
     from vae_npvc_b200 import _C

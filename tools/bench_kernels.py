@@ -162,7 +162,7 @@ def main():
     rec('sqnorm (1 read)', dt, n * 4)
     # ---------------- batched weight-norm passes over the VCC2020 model's flat buffers ----------------
     del p, g, m, v
-    from oracle import synth
+    from vae_npvc_b200 import synth
     from vae_npvc_b200.trainer.basic import Trainer
     arch = synth.arch_config()
     tr = Trainer(dict(arch, model_type='vae_npvc_b200.model.vqvae', precision='bf16', cuda_graph=False))

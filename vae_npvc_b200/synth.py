@@ -1,0 +1,126 @@
+"""Synthetic workload generator: recipe-shaped configs, seeded weights and mel-like feature batches.
+
+BASELINE.json's north_star puts "a synthetic mel/SP feature generator of the recipe's shape" in the dataset's
+place; this is it (with ``dataset.utt2mel_spk.SyntheticDataset`` as the item-level form).  It lives in the product
+because ``bench.py`` and the conversion benchmark feed the CUDA path from it; the oracle and the tests use the SAME
+functions (``oracle/synth.py`` re-exports them), so both sides of every parity check see identical inputs.
+
+The reference's own initialisation cannot be re-derived without the reference (parity must copy a
+state_dict), and a 31 M-parameter state_dict is too big to commit.  So goldens are made from weights produced HERE
+by a seeded torch CPU generator - the same function feeds the imported reference (oracle/make_golden.py, build
+container only), the oracle and the CUDA path (any box).  Shapes and key names follow the reference
+``Model.state_dict()`` (vqvae.py:122-183, 220-296; layers.py:130-165, 182-215).
+"""
+import math
+
+import torch
+
+
+def arch_config(X=80, C=512, D=64, K=512, Y=128, S=128, y_num=117, stacks=10, use_ema=False,
+                embed_norm=True, jitter_p=0.0, beta=0.01, mu=0.9, stack_layers=1, dilation=False):
+    """A config dict with the keys of egs/vcc20/vae1/conf/train_pytorch_vqvae.yaml:28-61.
+    Defaults = BASELINE.json configs[0]/[1] ("VCC2020 shape", codebook 512x64)."""
+    return {
+        'model_type': 'vae_npvc.model.vqvae',
+        'y_dim': Y, 'y_num': y_num, 'z_dim': D, 'z_num': K,
+        'use_ema': use_ema, 'embed_norm': embed_norm, 'beta': beta, 'mu': mu, 'jitter_p': jitter_p,
+        'encoder': {
+            'in_channels': [X], 'out_channels': [C], 'kernel_size': 3, 'downsample_scales': [1],
+            'z_channels': D, 'dilation': dilation, 'stack_kernel_size': 3,
+            'stack_layers': stack_layers, 'stacks': [stacks], 'use_weight_norm': True,
+            'use_causal_conv': False,
+        },
+        'decoder': {
+            'in_channels': [D], 'out_channels': [C], 'cond_channels': Y, 'skip_channels': S,
+            'final_channels': X, 'kernel_size': 3, 'upsample_scales': [1], 'dilation': dilation,
+            'stack_kernel_size': 3, 'stacks': [stacks], 'use_weight_norm': True,
+            'use_causal_conv': False,
+        },
+    }
+
+
+def small_config(**kw):
+    """A tiny model whose full state and gradients fit in a committed fixture."""
+    base = dict(X=8, C=16, D=8, K=32, Y=8, S=12, y_num=5, stacks=2)
+    base.update(kw)
+    return arch_config(**base)
+
+
+def _conv(sd, gen, prefix, d0, d1, k, bias_n, fan_in):
+    """weight_v (d0,d1,k) ~ U(+-1/sqrt(fan_in)); weight_g = ||v|| * U(0.8,1.2) so the
+    normalisation is not the identity; bias ~ U(+-1/sqrt(fan_in))."""
+    bound = 1.0 / math.sqrt(fan_in)
+    v = (torch.rand(d0, d1, k, generator=gen) * 2 - 1) * bound
+    g = v.pow(2).sum(dim=(1, 2), keepdim=True).sqrt() * (0.8 + 0.4 * torch.rand(d0, 1, 1, generator=gen))
+    sd[prefix + '.bias'] = (torch.rand(bias_n, generator=gen) * 2 - 1) * bound
+    sd[prefix + '.weight_g'] = g
+    sd[prefix + '.weight_v'] = v
+
+
+def _gn(sd, gen, prefix, c):
+    sd[prefix + '.weight'] = 1.0 + 0.1 * torch.randn(c, generator=gen)
+    sd[prefix + '.bias'] = 0.1 * torch.randn(c, generator=gen)
+
+
+def synthetic_state_dict(arch, seed=777):
+    """Reference-keyed state_dict (insertion order == reference ``state_dict()`` order)."""
+    gen = torch.Generator().manual_seed(seed)
+    sd = {}
+    enc, dec = arch['encoder'], arch['decoder']
+    ks = enc.get('stack_kernel_size', 3)
+    idx = 0
+    for si, cin in enumerate(enc['in_channels']):
+        cout = enc['out_channels'][si]
+        k = enc.get('kernel_size', 3)
+        _conv(sd, gen, f'encoder.encode.{idx}', cout, cin, k, cout, cin * k)
+        idx += 1
+        for _ in range(enc['stacks'][si]):
+            p = f'encoder.encode.{idx}'
+            for j in range(enc.get('stack_layers', 2)):
+                _conv(sd, gen, f'{p}.stack.{3 * j + 1}', cout, cout, ks, cout, cout * ks)
+                _gn(sd, gen, f'{p}.stack.{3 * j + 2}', cout)
+            _conv(sd, gen, f'{p}.skip_layer', cout, cout, 1, cout, cout)
+            idx += 1
+        idx += 1                                            # the LeakyReLU entry
+    _conv(sd, gen, f'encoder.encode.{idx}', enc['z_channels'], enc['out_channels'][-1], 1,
+          enc['z_channels'], enc['out_channels'][-1])
+    idx = 0
+    kd = dec.get('stack_kernel_size', 3)
+    Y, S = dec['cond_channels'], dec['skip_channels']
+    for si, cin in enumerate(dec['in_channels']):
+        cout = dec['out_channels'][si]
+        k = dec.get('kernel_size', 5)
+        _conv(sd, gen, f'decoder.layers.{idx}', cin, cout, k, cout, cin * k)       # ConvT: (in,out,k)
+        idx += 1
+        for _ in range(dec['stacks'][si]):
+            p = f'decoder.layers.{idx}'
+            _conv(sd, gen, f'{p}.conv_in', cout, 2 * cout, kd, 2 * cout, cout * kd)   # ConvT (in,2in,k)
+            _gn(sd, gen, f'{p}.norm_layer', 2 * cout)
+            _conv(sd, gen, f'{p}.conv_cond', 2 * cout, Y, 1, 2 * cout, Y)
+            _conv(sd, gen, f'{p}.res_skip_layers', cout + S, cout, 1, cout + S, cout)
+            idx += 1
+    _conv(sd, gen, 'decoder.final_layer.1', S, S, 1, S, S)
+    _conv(sd, gen, 'decoder.final_layer.3', dec['final_channels'], S, 1, dec['final_channels'], S)
+    K, D = arch['z_num'], arch['z_dim']
+    if arch.get('use_ema', False):
+        sd['quantizer.emb_init'] = torch.tensor(0).bool()
+        sd['quantizer.emb_sum'] = torch.zeros(K, D)
+        sd['quantizer.emb_elem'] = torch.ones(K)
+        sd['quantizer.embeddings'] = torch.zeros(K, D)
+    else:
+        e = torch.randn(K, D, generator=gen)
+        if arch.get('embed_norm', True):
+            e = e / e.norm(dim=1, keepdim=True)              # ctor calls embed_norm() (layers_vq.py:20)
+        sd['quantizer.embeddings'] = e
+    sd['embeds._embedding.weight'] = torch.randn(arch['y_num'], arch['y_dim'], generator=gen)
+    return sd
+
+
+def synthetic_batch(arch, B, T, seed=777):
+    """x ~ N(0,1) (B,X,T) float32 (CMVN-normalised features, egs/vcc20/vae1/run.sh:106-120);
+    y ~ U{0..y_num-1} (B,1) int64 - the contract of dataset/utt2mel_spk.py:42-74 after
+    default collation."""
+    gen = torch.Generator().manual_seed(seed)
+    x = torch.randn(B, arch['encoder']['in_channels'][0], T, generator=gen)
+    y = torch.randint(0, arch['y_num'], (B, 1), generator=gen)
+    return x, y
