@@ -201,7 +201,7 @@ class Trainer(object):
         weight_g, GroupNorm affine, codebook, speaker table - need zeroing.  -> int64 index tensor of those elements
         (None: nothing to gain).  Every conv of the model mirrors is used in every forward, which is what makes the
         v slots fully rewritten each step."""
-        if self.device.type != 'cuda' or not self.bank.by_ptr:
+        if not self.bank.by_ptr:
             return None
         total = self._flat_g.numel()
         keep = torch.ones(total, dtype=torch.bool)
