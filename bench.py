@@ -2,7 +2,7 @@
 
     python bench.py --gpus 1 --steps 100 --warmup 10                # our CUDA path, one B200
     torchrun --nproc-per-node N ... bench.py --gpus N ...           # batch-sharded DP, weak scaling
-    python bench.py --impl reference ...                            # the reference's CPU path (oracle port)
+    python bench.py --impl reference ...                            # the reference's own modules (oracle/_ref) on the host CPU
 
 Prints ONE JSON line on rank 0.  A "step" = zero-grad, forward, backward, [all-reduce], clip, Adam,
 StepLR over one synthetic batch of 16 x 128 frames PER GPU of the VCC2020-shape model
@@ -24,6 +24,8 @@ import torch  # noqa: E402
 
 B_PER_GPU, T_FRAMES = 16, 128
 FLOP_PER_FRAME = 178_757_632          # algorithmic fwd+bwd FLOP/frame, SURVEY.md section 8(d)
+WORKLOAD_NAME = ('VQ-VAE VCC2020 shape (BASELINE configs[1]): 80-mel, 16x128 frames per GPU, C512, 10+10 blocks, '
+                 'codebook 512x64 (use_ema false, embed_norm true), Adam+clip+StepLR')
 
 
 def workload_arch():
@@ -114,19 +116,103 @@ def cpu_oracle_step_rate(steps, warmup, threads=None):
     return B_PER_GPU * T_FRAMES / dt, dt, cores
 
 
+def reference_available():
+    from oracle import build_ref
+    return build_ref.available()
+
+
+def reference_step_rate(steps, warmup, device='cpu', autocast=False, threads=None):
+    """The UNMODIFIED reference modules staged under oracle/_ref (oracle/build_ref.py): vae_npvc.model.vqvae.Model
+    with the train step of vae_npvc/trainer/basic.py:55-79 around it (zero_grad, forward, backward,
+    clip_grad_norm_(10), Adam(0.5, 0.999), StepLR).  On ``device='cuda'`` the reference's own Trainer class is used
+    as is (it hard-codes .cuda(), trainer/basic.py:28) - stock eager PyTorch on the B200; ``autocast`` wraps its
+    forward in torch.autocast(bfloat16).  -> (frames/s, s/step, cores)."""
+    from oracle import build_ref, synth
+    build_ref.import_reference()
+    arch = workload_arch()
+    cfg = dict(arch)
+    cfg.update(model_type='vae_npvc.model.vqvae', optim_type='Adam', learning_rate=1e-3, max_grad_norm=10,
+               lr_scheduler='StepLR', lr_param={'step_size': 100000, 'gamma': 0.5, 'last_epoch': -1})
+    sd = synth.synthetic_state_dict(arch, 777)
+    x, y = synth.synthetic_batch(arch, B_PER_GPU, T_FRAMES, 777)
+    cores = threads or os.cpu_count() or 1
+    import warnings
+    warnings.simplefilter('ignore')
+    if device == 'cuda':
+        from vae_npvc.trainer.basic import Trainer as RefTrainer
+        tr = RefTrainer(cfg)
+        tr.model.load_state_dict(sd)
+        xh, yh = x.pin_memory(), y.pin_memory()
+        if autocast:
+            fwd = tr.model.forward
+            tr.model.forward = lambda inp: _autocast_call(fwd, inp)
+
+        def step(i):
+            return tr.train_step([xh, yh], i)
+        sync = torch.cuda.synchronize
+    else:
+        torch.set_num_threads(cores)
+        from vae_npvc.model.vqvae import Model as RefModel
+        m = RefModel(cfg)
+        m.load_state_dict(sd)
+        m.train()
+        opt = torch.optim.Adam(m.parameters(), lr=1e-3, betas=(0.5, 0.999), weight_decay=0.0)
+        sch = torch.optim.lr_scheduler.StepLR(opt, step_size=100000, gamma=0.5)
+
+        def step(i):                                   # trainer/basic.py:55-79 without the hard-coded .cuda()
+            m.zero_grad()
+            _, loss, detail = m([x, y])
+            loss.backward()
+            torch.nn.utils.clip_grad_norm_(m.parameters(), 10)
+            opt.step()
+            sch.step()
+            return i + 1, detail
+
+        def sync():
+            return None
+    for i in range(warmup):
+        step(i)
+    sync()
+    t0 = time.perf_counter()
+    for i in range(steps):
+        step(i)
+    sync()
+    dt = (time.perf_counter() - t0) / steps
+    return B_PER_GPU * T_FRAMES / dt, dt, cores
+
+
+def _autocast_call(fwd, inp):
+    with torch.autocast('cuda', dtype=torch.bfloat16):
+        return fwd(inp)
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
-    steps, warm = max(1, min(args.steps, 12)), max(1, min(args.warmup, 3))
-    fps, dt, cores = cpu_oracle_step_rate(steps, warm)
+    on_gpu = args.ref_device == 'cuda'
+    cap = 200 if on_gpu else 12
+    steps, warm = max(1, min(args.steps, cap)), max(1, min(args.warmup, 10 if on_gpu else 3))
+    if reference_available():
+        fps, dt, cores = reference_step_rate(steps, warm, args.ref_device, args.ref_autocast)
+        kind = 'reference'
+        what = ('the reference\'s own vae_npvc.model.vqvae.Model (staged under oracle/_ref) + trainer/basic.py:55-79 step, '
+                + ('stock eager PyTorch on the B200 through the reference Trainer%s' % (' under bf16 autocast' if args.ref_autocast else ', fp32')
+                   if on_gpu else 'torch CPU fp32'))
+    else:
+        if on_gpu:
+            print(json.dumps({'impl': 'reference', 'unavailable': 'oracle/_ref not staged: no reference modules to run on the GPU'}))
+            return
+        fps, dt, cores = cpu_oracle_step_rate(steps, warm)
+        kind = 'port'
+        what = 'oracle restatement of the reference Model + trainer/basic.py step, torch CPU fp32'
     line = {
         'impl': 'reference', 'metric': 'train frames/sec (fwd+bwd+optimizer)', 'value': fps, 'unit': 'frames/s',
         'n_gpus': args.gpus, 'steps': steps, 'warmup': warm, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
-        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': 'VQ-VAE VCC2020 shape: 80-mel, 16x128 frames, C512, codebook 512x64, fp32 on host CPU'},
-        'cpu_baseline': {'value': fps, 'unit': 'frames/s', 'cores': cores, 'kind': 'port',
-                         'sample': '%d full train steps of 16x128 frames (oracle restatement of the reference '
-                                   'Model + trainer/basic.py step, torch CPU fp32)' % steps},
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16 autocast' if (on_gpu and args.ref_autocast) else 'f32',
+        'data': 'synthetic',
+        'config': {'workload': WORKLOAD_NAME, 'reference_device': args.ref_device},
+        'cpu_baseline': {'value': fps, 'unit': 'frames/s', 'cores': cores, 'kind': kind,
+                         'sample': '%d full train steps of 16x128 frames (%s)' % (steps, what)},
         'e2e': {'value': fps, 'unit': 'frames/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }
@@ -252,8 +338,7 @@ def run_ours(args, rank, world):
             'steps': args.steps, 'warmup': warm, 'ms_per_step': dt / args.steps * 1e3, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16' if P == 1 else 'f32 (3xbf16 split planes)',
             'data': 'synthetic',
-            'config': {'workload': 'VQ-VAE VCC2020 shape (BASELINE configs[1]): 80-mel, 16x128 frames per GPU, C512, '
-                                   '10+10 blocks, codebook 512x64 (use_ema false, embed_norm true), Adam+clip+StepLR',
+            'config': {'workload': WORKLOAD_NAME,
                        'frames_per_gpu_per_step': B_PER_GPU * T_FRAMES, 'parallelism': 'dp%d' % world,
                        'cuda_graph': bool(on_graph),
                        'options': {'ew_v2': _C.get_option(_C.OPT_EW_V2), 'fast_gate': _C.get_option(_C.OPT_FAST_GATE),
@@ -275,10 +360,15 @@ def run_ours(args, rank, world):
                          'executed_tflops': kexec / kdt / 1e12, 'peak_source': pk['src'], 'kernel_ms': kdt * 1e3},
         }
         if world == 1 and not args.no_cpu_baseline:
-            fps, cdt, cores = cpu_oracle_step_rate(8, 2)
-            line['cpu_baseline'] = {'value': fps, 'unit': 'frames/s', 'cores': cores, 'kind': 'port',
-                                    'sample': '8 full train steps of 16x128 frames (oracle restatement of the '
-                                              'reference Model + trainer step, torch CPU fp32), %.0f ms/step' % (cdt * 1e3)}
+            if reference_available():
+                fps, cdt, cores = reference_step_rate(8, 2)
+                kind, what = 'reference', "the reference's own vae_npvc.model.vqvae.Model (oracle/_ref) + trainer/basic.py:55-79 step"
+            else:
+                fps, cdt, cores = cpu_oracle_step_rate(8, 2)
+                kind, what = 'port', 'oracle restatement of the reference Model + trainer step'
+            line['cpu_baseline'] = {'value': fps, 'unit': 'frames/s', 'cores': cores, 'kind': kind,
+                                    'sample': '8 full train steps of 16x128 frames (%s, torch CPU fp32), %.0f ms/step'
+                                              % (what, cdt * 1e3)}
         print(json.dumps(line))
     if dist is not None:
         # no destroy_process_group(): tearing NCCL down while captured graphs still hold its kernels hung at
@@ -299,6 +389,10 @@ def main():
     ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'])
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    # diagnostics of the reference arm (defaults = the contract: the reference's CPU path on the host cores)
+    ap.add_argument('--ref-device', default='cpu', choices=['cpu', 'cuda'],
+                    help='cuda: the unmodified reference Trainer/Model on the B200 through stock eager PyTorch')
+    ap.add_argument('--ref-autocast', action='store_true', help='with --ref-device cuda: bf16 autocast forward')
     args = ap.parse_args()
     rank, world = int(os.environ.get('RANK', 0)), int(os.environ.get('WORLD_SIZE', 1))
     if args.impl == 'reference':

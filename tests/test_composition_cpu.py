@@ -258,6 +258,65 @@ def test_trainer_three_clipped_adam_steps(cpu_prims, monkeypatch, golden_meta, t
     assert abs(float(tr.model.quantizer.embeddings.detach().norm(dim=1).mean()) - 1.0) < 1e-6
 
 
+def test_resume_keeps_decayed_lr_like_torch(cpu_prims, monkeypatch, tmp_path):
+    """the reference builds Trainer (and StepLR) BEFORE load_checkpoint; optimizer.load_state_dict then
+    installs the checkpoint's DECAYED lr and the fresh StepLR keeps chaining gamma off it
+    (trainer/basic.py:43-46,117-121).  Checked against torch.optim.Adam + StepLR driven the same way."""
+    arch = synth.small_config(embed_norm=False)      # (the in-place codebook renormalisation is not an optimiser op)
+    extra = dict(learning_rate=1e-3, max_grad_norm=10, lr_scheduler='StepLR',
+                 lr_param={'step_size': 3, 'gamma': 0.5, 'last_epoch': -1})
+    tr = _trainer(cpu_prims, monkeypatch, arch, extra)
+    tr.model.load_state_dict(synth.synthetic_state_dict(arch, 777))
+    # torch's own optimiser + scheduler over a clone of the same parameters, fed OUR gradients
+    tp = [p.detach().clone().requires_grad_(True) for p in tr._params]
+    opt = torch.optim.Adam(tp, lr=1e-3, betas=(0.5, 0.999), weight_decay=0.0)
+    sch = torch.optim.lr_scheduler.StepLR(opt, step_size=3, gamma=0.5)
+
+    def torch_step(trn, params, o, s_):
+        off = 0
+        g = trn._flat_g.clone()
+        total = float(g.pow(2).sum().sqrt())
+        coef = min(1.0, 10 / (total + 1e-6))
+        for q in params:
+            n = q.numel()
+            q.grad = (g[off:off + n] * coef).view_as(q).clone()
+            off += n
+        o.step()
+        s_.step()
+
+    it = 0
+    for i in range(7):
+        x, y = synth.synthetic_batch(arch, 3, 20, 300 + i)
+        it, _ = tr.train_step([x, y], it)
+        torch_step(tr, tp, opt, sch)
+    assert abs(tr.optimizer.current_lr() - 2.5e-4) < 1e-12 and abs(opt.param_groups[0]['lr'] - 2.5e-4) < 1e-12
+    for a, b in zip(tr._params, tp):
+        assert rel_err(a, b) < 1e-5
+    ck = tmp_path / 'iter.7'
+    tr.save_checkpoint(str(ck))
+    data = torch.load(str(ck), map_location='cpu')
+    assert abs(data['optimizer']['param_groups'][0]['lr'] - 2.5e-4) < 1e-12          # what torch would have saved
+    assert abs(data['optimizer']['param_groups'][0]['initial_lr'] - 1e-3) < 1e-12
+    # resume: fresh trainer + fresh torch optimiser/scheduler, both load the checkpoint
+    tr2 = _trainer(cpu_prims, monkeypatch, arch, extra)
+    assert tr2.load_checkpoint(str(ck)) == 7
+    tp2 = [p.detach().clone().requires_grad_(True) for p in tr2._params]
+    opt2 = torch.optim.Adam(tp2, lr=1e-3, betas=(0.5, 0.999), weight_decay=0.0)
+    sch2 = torch.optim.lr_scheduler.StepLR(opt2, step_size=3, gamma=0.5)
+    opt2.load_state_dict(opt.state_dict())
+    lrs, want = [], []
+    for i in range(4):
+        x, y = synth.synthetic_batch(arch, 3, 20, 400 + i)
+        lrs.append(tr2.optimizer.current_lr())
+        want.append(opt2.param_groups[0]['lr'])
+        it, _ = tr2.train_step([x, y], it)
+        torch_step(tr2, tp2, opt2, sch2)
+    assert want == pytest.approx([2.5e-4, 2.5e-4, 2.5e-4, 1.25e-4])
+    assert lrs == pytest.approx(want)
+    for a, b in zip(tr2._params, tp2):
+        assert rel_err(a, b) < 1e-5
+
+
 def test_weight_bank_segments_equal_whole(cpu_prims):
     """bank.py segments: materialising / back-propagating the encoder and the decoder layers by separate calls
     (the trainer issues the decoder's on a side stream) gives the same operand planes and (dv, dg) as one call."""

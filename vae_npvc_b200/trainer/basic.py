@@ -44,15 +44,25 @@ class FlatAdam(object):
         self.state = torch.zeros(2, dtype=torch.float32, device=flat_p.device)   # [adam step, sched step]
         self.sqn = torch.zeros(1, dtype=torch.float32, device=flat_p.device)
         self.lr, self.betas, self.eps = lr, betas, eps
+        self.lr0 = lr                     # the config value ('initial_lr' of torch's StepLR)
+        self.step_size, self.gamma = 0, 1.0
         self.param_groups = [{'lr': lr, 'betas': betas, 'eps': eps, 'weight_decay': 0.0, 'amsgrad': False,
                               'params': list(range(len(params)))}]
 
     def step(self, max_grad_norm, step_size, gamma):
+        self.step_size, self.gamma = int(step_size), float(gamma)
         self.sqn.zero_()
         if max_grad_norm > 0:
             Pm.sqnorm(self.flat_g, self.sqn)
         Pm.adam_step(self.flat_p, self.flat_g, self.m, self.v, self.sqn, float(max_grad_norm), self.lr,
                      self.betas[0], self.betas[1], self.eps, self.state, int(step_size), float(gamma))
+
+    def current_lr(self):
+        """The learning rate StepLR has decayed to: lr * gamma ** floor(scheduler steps / step_size) - what
+        torch's ``optimizer.param_groups[0]['lr']`` holds at this point of the reference's run."""
+        if not self.step_size or self.gamma == 1.0:
+            return float(self.lr)
+        return float(self.lr) * float(self.gamma) ** int(float(self.state[1].item()) // self.step_size)
 
     def state_dict(self):
         step = float(self.state[0].item())
@@ -63,7 +73,13 @@ class FlatAdam(object):
                 st[i] = {'step': torch.tensor(step), 'exp_avg': self.m[off:off + n].view_as(p).clone(),
                          'exp_avg_sq': self.v[off:off + n].view_as(p).clone()}
             off += n
-        return {'state': st, 'param_groups': [dict(g) for g in self.param_groups]}
+        g = dict(self.param_groups[0])
+        # torch.optim.Adam + StepLR save the DECAYED lr in param_groups and the undecayed one as 'initial_lr'
+        # (trainer/basic.py:109-115 stores optimizer.state_dict() as is)
+        g['lr'] = self.current_lr()
+        if self.step_size:
+            g['initial_lr'] = float(self.lr0)
+        return {'state': st, 'param_groups': [g]}
 
     def load_state_dict(self, sd):
         off, step = 0, 0.0
@@ -76,9 +92,15 @@ class FlatAdam(object):
                 step = float(s['step'])
             off += n
         self.state[0] = step
-        # The LR is NOT taken from the checkpoint: the reference builds a fresh StepLR on resume,
-        # which resets lr to 'initial_lr' (= the config value) and restarts the decay
-        # (scheduler state is never saved, trainer/basic.py:109-115); state[1] stays 0.
+        # Resume semantics of the reference (trainer/basic.py:117-121): the Trainer - and its StepLR - is built
+        # BEFORE load_checkpoint; optimizer.load_state_dict then replaces param_groups, so training continues at
+        # the checkpoint's (decayed) lr, while the scheduler's own counter restarts at 0 (its state is never
+        # saved) and keeps chaining gamma off group['lr'] every step_size steps from here.
+        groups = sd.get('param_groups') or [{}]
+        if 'lr' in groups[0]:
+            self.lr = float(groups[0]['lr'])
+            self.param_groups[0]['lr'] = self.lr
+        self.state[1] = 0.0
 
 
 def _dist():
@@ -126,6 +148,7 @@ class Trainer(object):
         else:
             self._step_size, self._gamma = 0, 1.0
             self.scheduler = None
+        self.optimizer.step_size, self.optimizer.gamma = self._step_size, self._gamma
         self.iteration = 0
         self.model.train()
         # bucketed all-reduce: trigger name (model/vqvae.py set_grad_ready_callback) -> slice of the flat buffers
@@ -311,6 +334,7 @@ class Trainer(object):
             else:
                 self.bank.prepare()
             if jitter_src is not None:
+                self._saved_sources = self.model.jitter.__dict__.get('sources')
                 self.model.jitter.sources = lambda length: jitter_src
             dist = _dist()
             self._reduced = []
@@ -353,6 +377,11 @@ class Trainer(object):
             if dist is not None and self._mc is None and self._allreduce_kind != 'none':
                 self._flat_g.mul_(1.0 / dist.get_world_size())      # the multimem kernel already scaled
         finally:
+            if jitter_src is not None:                    # the pinned table is for THIS step only
+                if self._saved_sources is None:
+                    self.model.jitter.__dict__.pop('sources', None)
+                else:
+                    self.model.jitter.sources = self._saved_sources
             _model_mod.set_grad_ready_callback(None)
             if hasattr(Pm, 'stats_arena_end'):
                 Pm.stats_arena_end()
@@ -405,8 +434,13 @@ class Trainer(object):
         without synchronising."""
         jit = getattr(self.model, 'jitter', None)
         needs_host_draws = jit is not None and jit._probability != 0.0
-        if (self.use_graph and not needs_host_draws and self._eager_steps >= self.graph_warmup):
-            key = tuple(x.shape)
+        q = getattr(self.model, 'quantizer', None)
+        # an EMA codebook initialises itself from the first training batch (layers_vq.py:192-201): that step must
+        # run eagerly, a captured graph would repeat the initialisation on every replay (and .item() cannot be
+        # captured) - resolved here, on the host, before any capture
+        needs_init = q is not None and hasattr(q, '_is_init') and not q._is_init()
+        if (self.use_graph and not needs_host_draws and not needs_init and self._eager_steps >= self.graph_warmup):
+            key = (tuple(x.shape), tuple(y.shape))
             ent = self._graphs.get(key)
             if ent is None:
                 torch.cuda.synchronize()
@@ -443,8 +477,10 @@ class Trainer(object):
         Fn.set_bank(self.bank)
         try:
             with torch.no_grad():
-                if not self.bank.fresh:
-                    self.bank.prepare()
+                # the operand planes in the bank belong to the parameters BEFORE the last optimiser step (they are
+                # materialised at the start of a step; a graph replay never runs python, so no flag can tell):
+                # always re-derive them from the current parameters
+                self.bank.prepare()
                 input = [t.to(self.device) for t in input]
                 output, loss, loss_detail = self.model(input)
         finally:
@@ -466,4 +502,5 @@ class Trainer(object):
         self.model.load_state_dict(checkpoint_data['model'])
         self.bank.fresh = False
         self.optimizer.load_state_dict(checkpoint_data['optimizer'])
+        self._graphs = {}                  # captured steps hold the old learning rate as a kernel argument
         return checkpoint_data['iteration']
