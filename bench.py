@@ -258,7 +258,7 @@ def time_dominant_kernel(P, iters=20):
         e1.synchronize()
         times.append(e0.elapsed_time(e1) * 1e-3 / reps)
     dt = sum(times) / len(times)
-    pairs = 1 if P == 1 else 6
+    pairs = {1: 1, 2: 3, 3: 6}[P]
     flops = 2.0 * B * T * Cout * Cin * taps            # algorithmic (the fp32-faithful mode executes 6x)
     return dt, flops, flops * pairs
 
@@ -331,12 +331,12 @@ def run_ours(args, rank, world):
         frames = B_PER_GPU * T_FRAMES * world * args.steps
         value, e2e = frames / dt, frames / dt_e2e
         pk = peaks()
-        P = 1 if args.precision == 'bf16' else 3
+        P = {'bf16': 1, 'bf16x2': 2, 'fp32': 3}[args.precision]
         kdt, kflops, kexec = time_dominant_kernel(P)
         line = {
             'metric': 'train frames/sec (fwd+bwd+optimizer)', 'value': value, 'unit': 'frames/s', 'n_gpus': world,
             'steps': args.steps, 'warmup': warm, 'ms_per_step': dt / args.steps * 1e3, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16' if P == 1 else 'f32 (3xbf16 split planes)',
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': {1: 'bf16', 2: 'bf16x2 (hi+mid bf16 planes, fp32 accumulate)', 3: 'f32 (3xbf16 split planes)'}[P],
             'data': 'synthetic',
             'config': {'workload': WORKLOAD_NAME,
                        'frames_per_gpu_per_step': B_PER_GPU * T_FRAMES, 'parallelism': 'dp%d' % world,
@@ -386,7 +386,7 @@ def main():
     ap.add_argument('--steps', type=int, default=100)          # 0.2 s of timed steps: 20-step runs scatter by +-2 %
     ap.add_argument('--warmup', type=int, default=10)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'])
+    ap.add_argument('--precision', default='bf16', choices=['bf16', 'bf16x2', 'fp32'])
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     # diagnostics of the reference arm (defaults = the contract: the reference's CPU path on the host cores)

@@ -48,12 +48,14 @@ def _split(x, P):
         return hi.unsqueeze(0)
     r = x - hi.float()
     mid = r.to(torch.bfloat16)
+    if P == 2:
+        return torch.stack([hi, mid])
     lo = (r - mid.float()).to(torch.bfloat16)
     return torch.stack([hi, mid, lo])
 
 
 def _join(data):
-    return data.float().sum(0) if data.shape[0] == 3 else data[0].float()
+    return data.float().sum(0) if data.shape[0] > 1 else data[0].float()
 
 
 class Planes:

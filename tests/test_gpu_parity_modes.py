@@ -1,0 +1,76 @@
+"""-m gpu: per-tensor parity of every GEMM operand mode against the float64 oracle at the VCC2020 shape
+(BASELINE.json configs[1]), for the normalised, plain and EMA quantisers.
+
+Stated tolerances (north_star: losses, gradients and converted features within 1e-3 on the bf16 path, 1e-5 fp32):
+  'fp32'   (3 planes): losses <= 1e-5, xhat / converted features <= 2e-5
+  'bf16x2' (2 planes): losses, xhat, converted features <= 1e-3 (measured ~1e-5), gradients <= 1e-3 over all tensors
+                       and per tensor - except where the reference's OWN float32 arithmetic is already further than
+                       that from float64 (early-encoder gradients: LeakyReLU slope flips of pre-activations within
+                       round-off of 0, see tests/parity.py): there the bar is 3x the reference's own deviation
+  'bf16'   (1 plane):  losses <= 1e-3; gradients are reported, NOT asserted at 1e-3 (they are ~1e-2: the mode does not
+                       meet north_star's gradient tolerance, which is why bench.py's headline mode is 'bf16x2')
+Codebook indices: bit-exact wherever the top-2 distance gap of the float64 evaluation exceeds 1e-5 (fp32 / bf16x2).
+The full report goes to gpurun_out/parity_modes.json (committed as profiles/r02_parity_modes.json).
+"""
+import json
+import os
+
+import pytest
+import torch
+
+import parity as Pa
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_CACHE = {}
+_REPORT = {}
+
+
+def _oracle(name):
+    if name not in _CACHE:
+        arch, sd, x, y = Pa.case_inputs(name)
+        w64 = Pa.oracle_eval(arch, sd, x, y, torch.float64)
+        w32 = Pa.oracle_eval(arch, sd, x, y, torch.float32)
+        ref32 = Pa.compare(w32, w64)
+        per32 = {n: Pa.rel(w32['grads'][n], g) for n, g in w64['grads'].items()}
+        _CACHE[name] = (arch, sd, x, y, w64, ref32, per32)
+        _REPORT.setdefault(name, {})['ref32 (the reference arithmetic itself, float32 vs float64)'] = ref32
+    return _CACHE[name]
+
+
+def _dump():
+    out = os.path.join(ROOT, 'gpurun_out')
+    try:
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, 'parity_modes.json'), 'w') as f:
+            json.dump(_REPORT, f, indent=1, sort_keys=True)
+    except OSError:
+        pass
+
+
+@pytest.mark.parametrize('mode', ['fp32', 'bf16x2', 'bf16'])
+@pytest.mark.parametrize('name', list(Pa.CASES))
+def test_mode_parity_vs_float64_oracle(name, mode):
+    from vae_npvc_b200 import _C
+    _C.require_cuda()
+    arch, sd, x, y, w64, ref32, per32 = _oracle(name)
+    got = Pa.cuda_eval(arch, sd, x, y, mode)
+    rep = Pa.compare(got, w64)
+    _REPORT[name][mode] = rep
+    _dump()
+    assert not rep['grad_missing'], rep['grad_missing']
+    loss_tol = {'fp32': 1e-5, 'bf16x2': 1e-3, 'bf16': 1e-3}[mode]
+    for k in ('Total', 'X like'):
+        assert rep['losses_rel'][k] <= loss_tol, (k, rep['losses_rel'][k])
+    if mode == 'bf16':
+        assert rep['grad_rel_global'] < 0.1                       # sanity only, see the module docstring
+        return
+    feat_tol = {'fp32': 2e-5, 'bf16x2': 1e-3}[mode]
+    assert rep['ids_mismatch_where_gap_gt_1e-5'] == 0, rep
+    assert rep['xhat_rel'] <= feat_tol, rep['xhat_rel']
+    assert rep.get('infer_rel_ids_equal', 0.0) <= feat_tol, rep
+    assert rep['infer_utts_all_ids_equal'] >= 12, rep           # near-ties are rare: most utterances keep every id
+    assert rep['grad_rel_global'] <= 1e-3, rep['grad_rel_global']
+    for n, g in w64['grads'].items():
+        e = Pa.rel(got['grads'][n], g)
+        assert e <= max(1e-3, 3.0 * per32[n]), (n, e, per32[n])

@@ -1,0 +1,229 @@
+"""-m gpu: parity holes named by the round-1 review ("Next round" item 1c / Missing 4-6).
+
+  * the SHIPPED recipe's quantiser at full size: use_ema true (egs/vcc20/vae1/conf/train_pytorch_vqvae.yaml:33-35)
+    against the committed ``vcc2020_ema`` golden recorded from the reference
+  * Trainer.valid_step / valid (trainer/basic.py:82-103) on the GPU, also after CUDA-graph replays
+  * VectorQuantizer's five reductions (layers_vq.py:123-140) against tests/golden/vq_layer.npz
+  * codebook sizes 4096 and 16384 (BASELINE.json configs[4]) through the tcgen05 lookup
+  * conv shapes of the other named workloads: Cin = 513 (WORLD SP, pitch 520), Cin = 40 (MCC), Cin = 160 / S = 256
+  * the 2-plane operand mode ('bf16x2') of every GEMM against float64
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_npz, rel_err
+from oracle import prims_ref as R
+from oracle import synth
+from oracle import vqvae_oracle as O
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-5
+
+
+@pytest.fixture()
+def fp32_mode():
+    import vae_npvc_b200.functional as Fn
+    from vae_npvc_b200 import _C
+    _C.require_cuda()
+    old = Fn.get_precision()
+    Fn.set_precision('fp32')
+    yield Fn
+    Fn.set_precision(old)
+    _C.set_backend(_C.BACKEND_AUTO)
+
+
+def g(*shape, seed=0, scale=1.0):
+    return torch.randn(*shape, generator=torch.Generator().manual_seed(seed)) * scale
+
+
+def _model(arch, sd):
+    from vae_npvc_b200.model.vqvae import Model
+    m = Model(arch)
+    m.load_state_dict({k: v.clone() for k, v in sd.items()})
+    return m.cuda()
+
+
+def test_full_vcc2020_ema_matches_reference_golden(fp32_mode, golden_meta):
+    """The reference's first training call initialises the EMA codebook with K random rows of the batch
+    (layers_vq.py:192-201: _tile + randperm under torch.manual_seed(1234) in oracle/make_golden.py).  The draw is a
+    HOST RNG stream, so the test reproduces it on the host from the oracle's encoder output and hands the CUDA model
+    the initialised buffers; everything after the draw - lookup with the fresh codebook, EMA update, losses,
+    statistics, gradients - is then the reference's first step and is held against its recorded numbers."""
+    case = golden_meta['cases']['vcc2020_ema']
+    arch = case['arch']
+    sd = synth.synthetic_state_dict(arch, 777)
+    x, y = synth.synthetic_batch(arch, 16, 128, 777)
+    po = O.params_from_state_dict(sd, requires_grad=False)
+    with torch.no_grad():
+        z = O.encoder_forward(po, arch['encoder'], x)
+    zf = z.transpose(1, 2).reshape(-1, z.shape[1])
+    torch.manual_seed(1234)
+    rows = zf[torch.randperm(zf.shape[0])][:arch['z_num']].clone()
+    sd = dict(sd)
+    sd['quantizer.emb_init'] = torch.tensor(True)
+    sd['quantizer.embeddings'] = rows
+    sd['quantizer.emb_sum'] = rows.clone()
+    sd['quantizer.emb_elem'] = torch.ones(arch['z_num'])
+    m = _model(arch, sd).train()
+    xhat, loss, losses = m([x.cuda(), y.cuda()])
+    loss.backward()
+    for k, v in case['losses'].items():
+        assert abs(losses[k] - v) <= 5e-5 * max(1.0, abs(v)), (k, losses[k], v)
+    assert abs(float(xhat.double().norm()) - case['xhat_norm']) < 5e-5 * case['xhat_norm']
+    seen = 0
+    for n, p in m.named_parameters():
+        if n in case['grad_norms']:
+            gn = case['grad_norms'][n]
+            assert abs(float(p.grad.double().norm()) - gn) <= 5e-3 * gn + 1e-12, n
+            seen += 1
+    assert seen == len(case['grad_norms'])
+    # F6 (bug-compatible): the reconstruction loss never reaches the encoder - only beta * z_enc_loss does
+    assert float(m.encoder.encode[0].weight_v.grad.abs().max()) > 0
+
+
+@pytest.mark.parametrize('use_graph', [False, True])
+def test_trainer_valid_step_uses_current_parameters(fp32_mode, use_graph):
+    """trainer/basic.py:82-103.  valid_step after optimiser steps (eager, and replayed from the captured graph, where
+    no Python runs) must evaluate the CURRENT parameters: compared with the oracle's eval-mode forward on the
+    parameters read back from the trainer (stale operand planes after graph replays)."""
+    from vae_npvc_b200.trainer.basic import Trainer
+    arch = synth.small_config()
+    cfg = dict(arch)
+    cfg.update(model_type='vae_npvc_b200.model.vqvae', precision='fp32', cuda_graph=use_graph, graph_warmup=2,
+               learning_rate=5e-3, max_grad_norm=10)
+    tr = Trainer(cfg)
+    tr.model.load_state_dict(synth.synthetic_state_dict(arch, 777))
+    xv, yv = synth.synthetic_batch(arch, 3, 20, 99)
+    it = 0
+    for i in range(5):
+        x, y = synth.synthetic_batch(arch, 3, 20, 500 + i)
+        it, _ = tr.train_step([x, y], it)
+        if i in (1, 4):
+            assert tr.last_step_on_graph == (use_graph and i >= 2)
+            detail = tr.valid_step([xv, yv])
+            assert tr.model.training
+            po = O.params_from_state_dict({k: v.detach().cpu() for k, v in tr.model.state_dict().items()},
+                                          requires_grad=False)
+            with torch.no_grad():
+                _, _, want, _ = O.model_forward(po, arch, xv, yv, False)
+            for k, v in want.items():
+                assert abs(detail[k] - float(v)) <= 5 * TOL * max(1.0, abs(float(v))), (i, k, detail[k], float(v))
+    out = tr.valid([[xv, yv], [xv, yv]])
+    assert len(out['Total']) == 2 and all(isinstance(v, float) for v in out['Total'])
+    assert abs(out['Total'][0] - out['Total'][1]) < 1e-6 * abs(out['Total'][0])
+
+
+@pytest.mark.parametrize('normalize', [False, True])
+@pytest.mark.parametrize('red', ['sum', 'mean', 'batch_mean', 'frame_mean', 'none'])
+def test_vq_layer_all_reductions_gpu(fp32_mode, normalize, red):
+    """VectorQuantizer.forward for every reduction (layers_vq.py:123-140) against outputs recorded from the
+    reference class (tests/golden/vq_layer.npz)."""
+    from vae_npvc_b200.model.layers_vq import VectorQuantizer
+    gold = load_npz('vq_layer')
+    key = f'vq_n{int(normalize)}_{red}'
+    q = VectorQuantizer(16, 8, normalize=normalize, reduction=red).cuda()
+    with torch.no_grad():
+        q.embeddings.copy_(torch.tensor(gold['E']))
+    z = torch.tensor(gold['z']).cuda().requires_grad_(True)
+    zv, lq, le, det = q(z)
+    (zv.sum() * 0.5 + lq.sum() + 0.3 * le.sum()).backward()
+    assert rel_err(zv, gold[key + ':z_vq']) < 1e-6
+    assert rel_err(lq, gold[key + ':lq']) < 1e-5 and rel_err(le, gold[key + ':le']) < 1e-5
+    assert rel_err(z.grad, gold[key + ':dz']) < 2e-5 and rel_err(q.embeddings.grad, gold[key + ':dE']) < 2e-5
+    assert rel_err(q.embeddings.detach(), gold[key + ':E_after']) < 1e-6
+    assert abs(float(det['entropy']) - float(gold[key + ':entropy'])) < 1e-4
+
+
+@pytest.mark.parametrize('K,D,normalize', [(4096, 64, False), (4096, 128, True), (16384, 64, False), (16384, 256, False)])
+def test_vq_lookup_large_codebooks(fp32_mode, K, D, normalize):
+    """BASELINE.json configs[4]: codebook sweep up to 16384 codes.  Indices equal an fp64 argmin wherever the top-2
+    gap exceeds fp32 rounding; a frame equal to a code maps to that code."""
+    from vae_npvc_b200 import _C, prims as Pm
+    B, T = 8, 128
+    z, E = g(B, D, T, seed=1).cuda(), g(K, D, seed=2).cuda()
+    e_hat, e_pl, e_sq = Pm.vq_prep_codebook(E.clone(), normalize, False)
+    zn, zpl, z_sq, _ = Pm.vq_prep_z(z, normalize)
+    _C.set_backend(_C.BACKEND_TC)
+    idx = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
+    torch.cuda.synchronize()
+    assert _C.call('debug_tc_timeouts') == 0
+    zf = zn.double().transpose(1, 2).reshape(B * T, D)
+    d = (zf.pow(2).sum(1, keepdim=True) + e_hat.double().pow(2).sum(1).view(1, -1)) - 2 * zf @ e_hat.double().t()
+    top2 = d.topk(2, dim=1, largest=False)
+    clear = (top2.values[:, 1] - top2.values[:, 0]) > 1e-5 * d.abs().max()
+    assert clear.float().mean() > 0.9
+    assert torch.equal(idx[clear], top2.indices[clear, 0])
+    pick = torch.randint(0, K, (B * T,), generator=torch.Generator().manual_seed(6)).cuda()
+    zx = e_hat[pick].view(B, T, D).transpose(1, 2).contiguous()
+    zn2, zpl2, z_sq2, _ = Pm.vq_prep_z(zx, False)
+    got = Pm.vq_lookup(zn2, zpl2, z_sq2, e_hat, e_pl, e_sq)
+    # duplicates of a code cannot occur with random rows; exact self-match has distance 0
+    assert torch.equal(got, pick)
+
+
+WORKLOAD_CONV_SHAPES = [
+    # B, Cin, Cout, T, taps   (the first / last convs of the other named workloads)
+    (2, 513, 512, 128, 3),       # CDVAE: WORLD spectrum encoder input, channel pitch 520
+    (2, 128, 513, 128, 1),       # ... and its decoder's final 1x1
+    (2, 40, 512, 128, 3),        # CDVAE: MCC encoder input
+    (2, 128, 40, 128, 1),
+    (2, 160, 512, 128, 3),       # AISHELL-3: 160-mel input
+    (2, 512, 768, 128, 1),       # AISHELL-3: res/skip 1x1 with skip_channels 256
+    (2, 256, 160, 128, 1),       # AISHELL-3: final 1x1
+]
+
+
+@pytest.mark.parametrize('P', [1, 2, 3])
+@pytest.mark.parametrize('B,Cin,Cout,T,k', WORKLOAD_CONV_SHAPES)
+def test_workload_conv_shapes_fwd_dgrad_wgrad(fp32_mode, P, B, Cin, Cout, T, k):
+    from vae_npvc_b200 import _C, prims as Pm
+    _C.set_backend(_C.BACKEND_TC)
+    x = g(B, Cin, T, seed=1)
+    w = g(Cout, Cin, k, seed=2, scale=1.0 / (Cin * k) ** 0.5)
+    dy = g(B, Cout, T, seed=3)
+    xpl = Pm.make_planes(x.cuda(), P)[0]
+    dypl = Pm.make_planes(dy.cuda(), P)[0]
+    W = Pm.wn_prepare(w.cuda(), None, False, P)
+    out = Pm.conv_fwd(xpl, W.wf, k, 1, Cout)
+    dx = Pm.conv_fwd(dypl, W.wb, k, 1, Cin)
+    dw = Pm.conv_wgrad(dypl, xpl, k, 1, False)
+    torch.cuda.synchronize()
+    assert _C.call('debug_tc_timeouts') == 0
+    xd = x.double().requires_grad_(True)
+    wd = w.double().requires_grad_(True)
+    ref = torch.nn.functional.conv1d(xd, wd, padding=(k - 1) // 2)
+    ref.backward(dy.double())
+    tol = {1: 1e-2, 2: 1e-4, 3: 2e-5}[P]
+    assert rel_err(out, ref) < tol, rel_err(out, ref)
+    assert rel_err(dx, xd.grad) < tol, rel_err(dx, xd.grad)
+    assert rel_err(dw, wd.grad) < tol, rel_err(dw, wd.grad)
+
+
+@pytest.mark.parametrize('name', ['small_vqnorm', 'small_2layer_dil'])
+def test_small_model_two_plane_mode(golden_meta, name):
+    """'bf16x2' on the small golden models: every tensor within 1e-4 of the reference's outputs."""
+    import vae_npvc_b200.functional as Fn
+    from vae_npvc_b200 import _C
+    _C.require_cuda()
+    old = Fn.get_precision()
+    Fn.set_precision('bf16x2')
+    try:
+        case = golden_meta['cases'][name]
+        arch = case['arch']
+        x, y = synth.synthetic_batch(arch, case['B'], case['T'], 777)
+        m = _model(arch, synth.synthetic_state_dict(arch, 777)).train()
+        xhat, loss, losses = m([x.cuda(), y.cuda()])
+        loss.backward()
+        gold = load_npz(name)
+        assert rel_err(xhat, gold['xhat']) < 1e-4
+        with torch.no_grad():
+            assert np.array_equal(m.encode(x.cuda()).cpu().numpy().reshape(-1), gold['idx'])
+        for k, v in case['losses'].items():
+            assert abs(losses[k] - v) <= 1e-4 * max(1.0, abs(v)), k
+        params = dict(m.named_parameters())
+        for key, gv in gold.items():
+            if key.startswith('grad:'):
+                assert rel_err(params[key[5:]].grad, gv) < 3e-4, (key, rel_err(params[key[5:]].grad, gv))
+    finally:
+        Fn.set_precision(old)

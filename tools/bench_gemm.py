@@ -58,7 +58,7 @@ def main():
     tag = sys.argv[1] if len(sys.argv) > 1 else 'default'
     only = int(sys.argv[2]) if len(sys.argv) > 2 else None          # index into SHAPES (for ncu captures)
     _C.require_cuda()
-    P = 1
+    P = int(os.environ.get('VNB_BENCH_P', 1))
     flush = torch.empty(256 * 1024 * 1024 // 4, device='cuda')
     rows = []
     for name, Cin, Cout, taps, transposed, gn in (SHAPES if only is None else SHAPES[only:only + 1]):
@@ -80,13 +80,33 @@ def main():
         def wgrad():
             _C.call('conv_wgrad', dypl.data, xpl.data, P, B, Cout, Cin, T, taps, 1, int(transposed), dw)
 
-        fl = 2.0 * B * T * Cin * Cout * taps
+        fl = 2.0 * B * T * Cin * Cout * taps          # algorithmic (P = 2 / 3 execute 3x / 6x)
         for kind, fn in (('conv_fwd', fwd), ('wgrad', wgrad)):
             cold, warm = timeit(fn, flush), timeit(fn)
             rows.append(dict(tag=tag, shape=name, kind=kind, cold_us=round(cold, 2), warm_us=round(warm, 2),
                              warm_tflops=round(fl / warm / 1e6, 1), cold_tflops=round(fl / cold / 1e6, 1)))
             print('%-10s %-38s %-8s cold %7.2f us (%6.1f TF/s)  warm %7.2f us (%6.1f TF/s)'
                   % (tag, name, kind, cold, fl / cold / 1e6, warm, fl / warm / 1e6), flush=True)
+    if only is None:
+        # what the library GEMM gets at the same one-wave shapes (torch.matmul bf16 -> cuBLAS): the forward of the
+        # decoder conv_in is M = 2048 frames, N = 1024, K = 3 * 512; its weight gradient M = 512, N = 3 * 1024, K = 2048
+        for name, M, N, K in (('cuBLAS bf16 2048x1024x1536 (dec conv_in fwd)', 2048, 1024, 1536),
+                              ('cuBLAS bf16 2048x512x3072  (dec conv_in dgrad)', 2048, 512, 3072),
+                              ('cuBLAS bf16 512x3072x2048  (dec conv_in wgrad)', 512, 3072, 2048),
+                              ('cuBLAS bf16 2048x512x1536  (enc k3 fwd)', 2048, 512, 1536),
+                              ('cuBLAS bf16 2048x640x512   (dec res/skip fwd)', 2048, 640, 512)):
+            a_ = torch.randn(M, K, device='cuda', dtype=torch.bfloat16)
+            b_ = torch.randn(K, N, device='cuda', dtype=torch.bfloat16)
+            o_ = torch.empty(M, N, device='cuda', dtype=torch.bfloat16)
+
+            def mm():
+                torch.matmul(a_, b_, out=o_)
+            fl = 2.0 * M * N * K
+            cold, warm = timeit(mm, flush), timeit(mm)
+            rows.append(dict(tag=tag, shape=name, kind='cublas', cold_us=round(cold, 2), warm_us=round(warm, 2),
+                             warm_tflops=round(fl / warm / 1e6, 1), cold_tflops=round(fl / cold / 1e6, 1)))
+            print('%-10s %-38s %-8s cold %7.2f us (%6.1f TF/s)  warm %7.2f us (%6.1f TF/s)'
+                  % (tag, name, 'cublas', cold, fl / cold / 1e6, warm, fl / warm / 1e6), flush=True)
     os.makedirs(os.path.join(ROOT, 'gpurun_out'), exist_ok=True)
     with open(os.path.join(ROOT, 'gpurun_out', 'bench_gemm_%s.json' % tag), 'w') as f:
         json.dump(rows, f, indent=1)

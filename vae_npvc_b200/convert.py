@@ -81,7 +81,7 @@ class ConvertEngine(object):
     def __init__(self, model, precision=None, max_batch=64, max_batch_frames=1 << 16, max_pad_frac=0.25, prims=None):
         self.Pm = prims or Pm
         self.model = model
-        self.P = {'bf16': 1, 'fp32': 3, 1: 1, 3: 3, None: Fn.get_precision()}[precision]
+        self.P = Fn.get_precision() if precision is None else Fn._MODES[precision]
         self.max_batch, self.max_batch_frames, self.max_pad_frac = max_batch, max_batch_frames, max_pad_frac
         self.device = next(model.parameters()).device
         self.x_dim = model.encoder.encode[0].in_channels

@@ -90,7 +90,10 @@ __device__ __forceinline__ void split3(float x, bf16& hi, bf16& mid, bf16& lo) {
     lo = __float2bfloat16_rn(r);
 }
 
-// Write value x at element offset `off` of plane 0 (and planes 1,2 at +stride each for P==3).
+// Operand modes: P = 1 one bf16 plane (8 significant bits); P = 2 hi + mid (16 bits: the GEMMs contract hi*hi +
+// hi*mid + mid*hi, ~2^-16 relative); P = 3 hi + mid + lo (24 bits, 6 products: fp32-faithful).  The planes of P = 2
+// are the first two of P = 3.
+// Write value x at element offset `off` of plane 0 (and planes 1[,2] at +stride each for P >= 2).
 __device__ __forceinline__ void store_planes(bf16* base, int64_t off, int64_t plane_stride, int P, float x) {
     if (P == 1) {
         base[off] = __float2bfloat16_rn(x);
@@ -99,7 +102,7 @@ __device__ __forceinline__ void store_planes(bf16* base, int64_t off, int64_t pl
         split3(x, a, b, c);
         base[off] = a;
         base[off + plane_stride] = b;
-        base[off + 2 * plane_stride] = c;
+        if (P == 3) base[off + 2 * plane_stride] = c;
     }
 }
 
@@ -147,10 +150,8 @@ __device__ __forceinline__ void st_planes_vec(bf16* base, int64_t off, int64_t p
 
 __device__ __forceinline__ float load_planes(const bf16* base, int64_t off, int64_t plane_stride, int P) {
     float x = __bfloat162float(base[off]);
-    if (P == 3) {
-        x += __bfloat162float(base[off + plane_stride]);
-        x += __bfloat162float(base[off + 2 * plane_stride]);
-    }
+    if (P >= 2) x += __bfloat162float(base[off + plane_stride]);
+    if (P == 3) x += __bfloat162float(base[off + 2 * plane_stride]);
     return x;
 }
 

@@ -181,7 +181,7 @@ using namespace vnb;
 extern "C" int vnb_mask_rows(float* x, void* planes_a, void* planes_b, void* planes_c, int B, int C, int T, int P,
                              const int* lengths, void* stream) {
     VNB_REQUIRE(lengths && (x || planes_a || planes_b || planes_c), "mask_rows: null pointer");
-    VNB_REQUIRE(B > 0 && B <= 65535 && C > 0 && T > 0 && (P == 1 || P == 3), "mask_rows: bad shape");
+    VNB_REQUIRE(B > 0 && B <= 65535 && C > 0 && T > 0 && (P >= 1 && P <= 3), "mask_rows: bad shape");
     vnb::launch_k(mask_rows_kernel, dim3(ceil_div(T, MASK_ROWS_PER_CTA), B), 256, 0, ST, x, (bf16*)planes_a,
                   (bf16*)planes_b, (bf16*)planes_c, B, C, T, round_up8(C), P, lengths);
     VNB_LAUNCH_CHECK("mask_rows");

@@ -26,7 +26,7 @@ extern "C" int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T,
                             int accumulate, double* gn_sums, int gn_groups, void* stream) {
     VNB_REQUIRE(in_planes && w_planes && out, "conv_fwd: null pointer");
     VNB_REQUIRE(B > 0 && Cin > 0 && Cout > 0 && T > 0, "conv_fwd: bad shape B=%d Cin=%d Cout=%d T=%d", B, Cin, Cout, T);
-    VNB_REQUIRE((P == 1 || P == 3) && taps >= 1 && (taps & 1) && dil >= 1, "conv_fwd: P=%d taps=%d dil=%d unsupported", P, taps, dil);
+    VNB_REQUIRE((P >= 1 && P <= 3) && taps >= 1 && (taps & 1) && dil >= 1, "conv_fwd: P=%d taps=%d dil=%d unsupported", P, taps, dil);
     VNB_REQUIRE(!gn_sums || (gn_groups > 0 && Cout % gn_groups == 0), "conv_fwd: gn_groups=%d does not divide Cout=%d", gn_groups, Cout);
     if (!gn_sums) gn_groups = 0;
     cudaStream_t st = (cudaStream_t)stream;
@@ -48,7 +48,7 @@ extern "C" int vnb_conv_wgrad(const void* dy_planes, const void* u_planes, int P
                               int taps, int dil, int transposed, float* dw, void* stream) {
     VNB_REQUIRE(dy_planes && u_planes && dw, "conv_wgrad: null pointer");
     VNB_REQUIRE(B > 0 && Cin > 0 && Cout > 0 && T > 0, "conv_wgrad: bad shape");
-    VNB_REQUIRE((P == 1 || P == 3) && taps >= 1 && (taps & 1) && dil >= 1, "conv_wgrad: P=%d taps=%d dil=%d unsupported", P, taps, dil);
+    VNB_REQUIRE((P >= 1 && P <= 3) && taps >= 1 && (taps & 1) && dil >= 1, "conv_wgrad: P=%d taps=%d dil=%d unsupported", P, taps, dil);
     cudaStream_t st = (cudaStream_t)stream;
     const int be = backend();
     if (be != VNB_BACKEND_SIMT) {

@@ -327,7 +327,7 @@ extern "C" int vnb_transpose(const float* in, int B, int R, int S, float* out, v
 // values written to the identity plane (x*scale) - the bias gradient, without a second pass over the tensor.
 extern "C" int vnb_make_planes(const float* x, int B, int C, int T, int P, float scale, int act, void* out_id,
                                void* out_act, float* csum, void* stream) {
-    VNB_REQUIRE(x && (out_id || out_act) && B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "make_planes: bad arguments");
+    VNB_REQUIRE(x && (out_id || out_act) && B > 0 && C > 0 && T > 0 && (P >= 1 && P <= 3), "make_planes: bad arguments");
     VNB_REQUIRE(!csum || C <= 12000, "make_planes: too many channels for the fused channel sums");
     const int64_t rows = (int64_t)B * T;
     const bool v4 = (C & 3) == 0;
@@ -335,6 +335,7 @@ extern "C" int vnb_make_planes(const float* x, int B, int C, int T, int P, float
         const int g2 = v2_grid(rows, C / 4);
         if (g2) {
             if (P == 1) vnb::launch_k(make_planes_v2_kernel<1, 4>, g2, V2_THREADS, 0, ST, x, (int)rows, C, round_up8(C), scale, act, (bf16*)out_id, (bf16*)out_act);
+            else if (P == 2) vnb::launch_k(make_planes_v2_kernel<2, 2>, g2, V2_THREADS, 0, ST, x, (int)rows, C, round_up8(C), scale, act, (bf16*)out_id, (bf16*)out_act);
             else vnb::launch_k(make_planes_v2_kernel<3, 2>, g2, V2_THREADS, 0, ST, x, (int)rows, C, round_up8(C), scale, act, (bf16*)out_id, (bf16*)out_act);
             VNB_LAUNCH_CHECK("make_planes_v2");
             return VNB_OK;
@@ -352,7 +353,7 @@ extern "C" int vnb_make_planes(const float* x, int B, int C, int T, int P, float
 
 extern "C" int vnb_concat_planes(const float* xa, int Ca, const float* xb, int Cb, int B, int T, int P, void* out,
                                  float* csum, void* stream) {
-    VNB_REQUIRE(xa && xb && out && Ca > 0 && Cb > 0 && B > 0 && T > 0 && (P == 1 || P == 3), "concat_planes: bad arguments");
+    VNB_REQUIRE(xa && xb && out && Ca > 0 && Cb > 0 && B > 0 && T > 0 && (P >= 1 && P <= 3), "concat_planes: bad arguments");
     VNB_REQUIRE(!csum || Ca + Cb <= 12000, "concat_planes: too many channels for the fused channel sums");
     const int64_t rows = (int64_t)B * T;
     const bool v4 = ((Ca | Cb) & 3) == 0;
@@ -401,13 +402,14 @@ extern "C" int vnb_enc_out(const float* h, const float* s, const float* mean, co
                            const float* beta, int B, int C, int T, int P, float* y, void* y_planes, void* u_planes,
                            void* stream) {
     VNB_REQUIRE(h && mean && rstd && gamma && beta && (y || y_planes || u_planes), "enc_out: null pointer");
-    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "enc_out: bad shape");
+    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P >= 1 && P <= 3), "enc_out: bad shape");
     const int64_t rows = (int64_t)B * T;
     if ((C & 3) == 0 && ew_v2_enabled()) {
         const int g2 = v2_grid(rows, C / 4);
         if (g2) {
             const int Cp = round_up8(C);
             if (P == 1) vnb::launch_k(enc_out_v2_kernel<1, 2>, g2, V2_THREADS, 0, ST, h, s, mean, rstd, gamma, beta, (int)rows, C, T, Cp, y, (bf16*)y_planes, (bf16*)u_planes);
+            else if (P == 2) vnb::launch_k(enc_out_v2_kernel<2, 2>, g2, V2_THREADS, 0, ST, h, s, mean, rstd, gamma, beta, (int)rows, C, T, Cp, y, (bf16*)y_planes, (bf16*)u_planes);
             else vnb::launch_k(enc_out_v2_kernel<3, 2>, g2, V2_THREADS, 0, ST, h, s, mean, rstd, gamma, beta, (int)rows, C, T, Cp, y, (bf16*)y_planes, (bf16*)u_planes);
             VNB_LAUNCH_CHECK("enc_out_v2");
             return VNB_OK;
@@ -422,7 +424,7 @@ extern "C" int vnb_enc_out(const float* h, const float* s, const float* mean, co
 extern "C" int vnb_dec_gate(const float* a, const float* mean, const float* rstd, const float* gamma,
                             const float* beta, int B, int C, int T, int P, void* g_planes, void* stream) {
     VNB_REQUIRE(a && mean && rstd && gamma && beta && g_planes, "dec_gate: null pointer");
-    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "dec_gate: bad shape");
+    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P >= 1 && P <= 3), "dec_gate: bad shape");
     const int64_t rows = (int64_t)B * T;
     if ((C & 3) == 0 && ew_v2_enabled()) {
         const int g2 = v2_grid(rows, C / 4);
@@ -430,6 +432,7 @@ extern "C" int vnb_dec_gate(const float* a, const float* mean, const float* rstd
             const int Cp = round_up8(C);
             if (P == 1 && fast_gate_enabled()) vnb::launch_k(dec_gate_v2_kernel<1, 2, true>, g2, V2_THREADS, 0, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes);
             else if (P == 1) vnb::launch_k(dec_gate_v2_kernel<1, 2, false>, g2, V2_THREADS, 0, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes);
+            else if (P == 2) vnb::launch_k(dec_gate_v2_kernel<2, 2, false>, g2, V2_THREADS, 0, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes);
             else vnb::launch_k(dec_gate_v2_kernel<3, 2, false>, g2, V2_THREADS, 0, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes);
             VNB_LAUNCH_CHECK("dec_gate_v2");
             return VNB_OK;
@@ -443,7 +446,7 @@ extern "C" int vnb_dec_gate(const float* a, const float* mean, const float* rstd
 
 extern "C" int vnb_dec_out(const float* r, const float* x, int B, int C, int S, int T, int P, float* x_out,
                            void* x_planes, float* skip_sum, int first, void* stream) {
-    VNB_REQUIRE(r && x && B > 0 && C > 0 && S >= 0 && T > 0 && (P == 1 || P == 3), "dec_out: bad arguments");
+    VNB_REQUIRE(r && x && B > 0 && C > 0 && S >= 0 && T > 0 && (P >= 1 && P <= 3), "dec_out: bad arguments");
     const int64_t rows = (int64_t)B * T;
     VEC_DISPATCH(((C | S) & 3) == 0, dec_out_kernel, rows * (C + S), ST, r, x, rows, C, S, round_up8(C), P, x_out,
                  (bf16*)x_planes, skip_sum, first);

@@ -359,7 +359,7 @@ extern "C" int vnb_gate_bwd_rows_p(const float* dg, const float* a, const float*
                                    const float* gamma, const float* beta, int B, int C, int T, int P, float* R,
                                    void* stream) {
     VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && R && B > 0 && B <= 65535 && C > 0 && T > 0 &&
-                    (P == 1 || P == 3), "gate_bwd_rows: bad arguments");
+                    (P >= 1 && P <= 3), "gate_bwd_rows: bad arguments");
     // the gate's approximate functions only where the operand planes are bf16 anyway (see ew_v2.cuh)
     if (P == 1 && ew_v2_enabled() && fast_gate_enabled())
         vnb::launch_k(gate_bwd_rows_kernel<true>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R);
@@ -399,13 +399,14 @@ extern "C" int vnb_gn_bwd_apply(const float* dn, const float* h, const float* me
                                 const float* gamma, const float* S, int B, int C, int T, int groups, int P,
                                 void* dpre_planes, void* dn_planes, void* stream) {
     VNB_REQUIRE(dn && h && mean && rstd && gamma && S && dpre_planes, "gn_bwd_apply: null pointer");
-    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && groups > 0 && C % groups == 0 && (P == 1 || P == 3), "gn_bwd_apply: bad shape");
+    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && groups > 0 && C % groups == 0 && (P >= 1 && P <= 3), "gn_bwd_apply: bad shape");
     const int64_t rows = (int64_t)B * T;
     if ((C & 3) == 0 && ((C / groups) & 3) == 0 && ew_v2_enabled()) {
         const int g2 = v2_grid(rows, C / 4);
         if (g2) {
             cudaStream_t st = (cudaStream_t)stream;
             if (P == 1) vnb::launch_k(gn_bwd_apply_v2_kernel<1, 2>, g2, V2_THREADS, 0, st, dn, h, mean, rstd, gamma, S, (int)rows, C, T, groups, round_up8(C), (bf16*)dpre_planes, (bf16*)dn_planes);
+            else if (P == 2) vnb::launch_k(gn_bwd_apply_v2_kernel<2, 2>, g2, V2_THREADS, 0, st, dn, h, mean, rstd, gamma, S, (int)rows, C, T, groups, round_up8(C), (bf16*)dpre_planes, (bf16*)dn_planes);
             else vnb::launch_k(gn_bwd_apply_v2_kernel<3, 2>, g2, V2_THREADS, 0, st, dn, h, mean, rstd, gamma, S, (int)rows, C, T, groups, round_up8(C), (bf16*)dpre_planes, (bf16*)dn_planes);
             VNB_LAUNCH_CHECK("gn_bwd_apply_v2");
             return VNB_OK;
@@ -421,7 +422,7 @@ extern "C" int vnb_gate_bwd_apply(const float* dg, const float* a, const float* 
                                   const float* gamma, const float* beta, const float* S, int B, int C, int T, int P,
                                   void* da_planes, void* stream) {
     VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && S && da_planes, "gate_bwd_apply: null pointer");
-    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P == 1 || P == 3), "gate_bwd_apply: bad shape");
+    VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P >= 1 && P <= 3), "gate_bwd_apply: bad shape");
     const int64_t rows = (int64_t)B * T;
     if ((C & 3) == 0 && ew_v2_enabled()) {
         const int g2 = v2_grid(rows, C / 4);
@@ -430,6 +431,7 @@ extern "C" int vnb_gate_bwd_apply(const float* dg, const float* a, const float* 
             const int Cp = round_up8(2 * C);
             if (P == 1 && fast_gate_enabled()) vnb::launch_k(gate_bwd_apply_v2_kernel<1, 2, true>, g2, V2_THREADS, 0, st, dg, a, mean, rstd, gamma, beta, S, (int)rows, C, T, Cp, (bf16*)da_planes);
             else if (P == 1) vnb::launch_k(gate_bwd_apply_v2_kernel<1, 2, false>, g2, V2_THREADS, 0, st, dg, a, mean, rstd, gamma, beta, S, (int)rows, C, T, Cp, (bf16*)da_planes);
+            else if (P == 2) vnb::launch_k(gate_bwd_apply_v2_kernel<2, 2, false>, g2, V2_THREADS, 0, st, dg, a, mean, rstd, gamma, beta, S, (int)rows, C, T, Cp, (bf16*)da_planes);
             else vnb::launch_k(gate_bwd_apply_v2_kernel<3, 2, false>, g2, V2_THREADS, 0, st, dg, a, mean, rstd, gamma, beta, S, (int)rows, C, T, Cp, (bf16*)da_planes);
             VNB_LAUNCH_CHECK("gate_bwd_apply_v2");
             return VNB_OK;

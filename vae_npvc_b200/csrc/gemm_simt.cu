@@ -244,6 +244,9 @@ int conv_fwd_simt(const void* in, int P, int B, int Cin, int T, const void* w, i
     if (P == 1)
         vnb::launch_k(conv_fwd_simt_kernel<1>, grid, 256, 0, st, (const bf16*)in, B, Cin, T, (const bf16*)w, taps, dil, Cout, Cin_p,
                                                       bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups);
+    else if (P == 2)
+        vnb::launch_k(conv_fwd_simt_kernel<2>, grid, 256, 0, st, (const bf16*)in, B, Cin, T, (const bf16*)w, taps, dil, Cout, Cin_p,
+                                                      bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups);
     else
         vnb::launch_k(conv_fwd_simt_kernel<3>, grid, 256, 0, st, (const bf16*)in, B, Cin, T, (const bf16*)w, taps, dil, Cout, Cin_p,
                                                       bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups);
@@ -256,6 +259,9 @@ int conv_wgrad_simt(const void* dy, const void* u, int P, int B, int Cout, int C
     dim3 grid(ceil_div(Cin, TN), ceil_div(Cout, TM), taps);
     if (P == 1)
         vnb::launch_k(conv_wgrad_simt_kernel<1>, grid, 256, 0, st, (const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, taps, dil,
+                                                        transposed, dw);
+    else if (P == 2)
+        vnb::launch_k(conv_wgrad_simt_kernel<2>, grid, 256, 0, st, (const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, taps, dil,
                                                         transposed, dw);
     else
         vnb::launch_k(conv_wgrad_simt_kernel<3>, grid, 256, 0, st, (const bf16*)dy, (const bf16*)u, B, Cout, Cin, T, taps, dil,

@@ -39,9 +39,12 @@ constexpr int TC_BM = 128;         // frames per tile (UMMA M)
 constexpr int TC_BK = 64;          // K elements per pipeline stage (one 128-byte swizzle row)
 constexpr int TC_THREADS = 256;     // 8 warps: with one warp per scheduler every epilogue latency is exposed
 
-// plane pairs (a-plane, b-plane) of the 3-way split, smallest terms first
-__constant__ int c_pair_a[6] = {1, 2, 0, 1, 0, 0};
-__constant__ int c_pair_b[6] = {1, 0, 2, 0, 1, 0};
+// plane pairs (a-plane, b-plane), smallest terms first: entries 0..5 = the 6 significant products of the 3-way split
+// (P = 3), entries 6..8 = the 3 products of the 2-way split (P = 2: mid*hi, hi*mid, hi*hi)
+__constant__ int c_pair_a[9] = {1, 2, 0, 1, 0, 0, 1, 0, 0};
+__constant__ int c_pair_b[9] = {1, 0, 2, 0, 1, 0, 0, 1, 0};
+__host__ __device__ constexpr int n_pairs(int P) { return P == 1 ? 1 : P == 2 ? 3 : 6; }
+__host__ __device__ constexpr int pair_base(int P) { return P == 2 ? 6 : 0; }
 
 // debug timeline (VNB_TC_DBG=9): clock64 stamps of CTA (0,0,0), read by vnb_debug_tc_timeline
 __device__ long long g_tc_ts[2][64];
@@ -115,7 +118,7 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     const int ks = gridDim.x, kr = blockIdx.x;
     const int mtiles = (a.T + TC_BM - 1) / TC_BM;
     const int b = blockIdx.z / mtiles, t0 = (blockIdx.z - b * mtiles) * TC_BM, co0 = blockIdx.y * BN;
-    const int pairs = a.P == 1 ? 1 : 6;
+    const int pairs = n_pairs(a.P);
     // k runs over (plane pair, tap, group of kch 64-channel chunks): one pipeline stage each
     const int kc_per = ((a.Cin + TC_BK - 1) / TC_BK) / kch;
     const int nkc = pairs * a.taps * kc_per;
@@ -154,7 +157,7 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
             int s = 0;
             uint32_t ph = 1;                          // ((i / STAGES) - 1) & 1, kept incrementally
             for (int i = 0; i < nk; i++) {
-                const int pa = a.P == 1 ? 0 : c_pair_a[pr], pb = a.P == 1 ? 0 : c_pair_b[pr];
+                const int pa = a.P == 1 ? 0 : c_pair_a[pair_base(a.P) + pr], pb = a.P == 1 ? 0 : c_pair_b[pair_base(a.P) + pr];
                 const int off = (tap - (a.taps - 1) / 2) * a.dil;
                 if (i >= STAGES) mbar_wait(&empty_bar[s], ph);
                 uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
@@ -561,7 +564,7 @@ int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int
     int kch = (Cin % 128 == 0) ? 2 : 1;
     if (force_kch == 1) kch = 1;
     a.kch = kch;
-    const int nkc = (P == 1 ? 1 : 6) * taps * (ceil_div(Cin, TC_BK) / kch);
+    const int nkc = n_pairs(P) * taps * (ceil_div(Cin, TC_BK) / kch);
     auto fits = [kch](int bn_, int ks_) {
         const uint32_t pitch = bn_ + 4, stage_b = (TC_BM * TC_BK * 2 + bn_ * TC_BK * 2) * kch;
         const uint32_t recv = (uint32_t)(ks_ - 1) * (TC_BM / ks_) * pitch * 4, budget = 227 * 1024 - 2048;

@@ -88,7 +88,7 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     const int off = (tap - (a.taps - 1) / 2) * a.dil;
     const int off_a = a.swapped ? off : 0, off_b = a.swapped ? 0 : off;
     const int tap_idx = a.swapped ? a.taps - 1 - tap : tap;
-    const int pairs = a.P == 1 ? 1 : 6;
+    const int pairs = n_pairs(a.P);
     const int tblocks = (a.T + WG_KT - 1) / WG_KT;
     const int kblocks = a.B * tblocks;
     const int kb0 = (int)((int64_t)kblocks * kr / ks), kb1 = (int)((int64_t)kblocks * (kr + 1) / ks);
@@ -123,7 +123,7 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             int s = 0;
             uint32_t ph = 1;
             for (int i = 0; i < nk; i++) {
-                const int pa = a.P == 1 ? 0 : c_pair_a[pr], pb = a.P == 1 ? 0 : c_pair_b[pr];
+                const int pa = a.P == 1 ? 0 : c_pair_a[pair_base(a.P) + pr], pb = a.P == 1 ? 0 : c_pair_b[pair_base(a.P) + pr];
                 // the row operand takes the a-plane of the pair when it is dY, the b-plane when it is U (swapped)
                 const int pl_a = a.swapped ? pb : pa, pl_b = a.swapped ? pa : pb;
                 const int t0 = tb * WG_KT;
@@ -366,7 +366,7 @@ int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin
     WgradTcArgs a{B, nrows, ncols, T, taps, P, dil, transposed ? 1 : 0, 0, 0, 0, 0, dw};
     static const int force_bn = getenv("VNB_WG_BN") ? atoi(getenv("VNB_WG_BN")) : 0;
     static const int force_ks = getenv("VNB_WG_KSPLIT") ? atoi(getenv("VNB_WG_KSPLIT")) : 0;
-    const int kblocks = B * ceil_div(T, WG_KT) * (P == 1 ? 1 : 6);
+    const int kblocks = B * ceil_div(T, WG_KT) * n_pairs(P);
     int bn = 64, ks = 1;
     int64_t best = INT64_MAX;
     for (int cand = 64; cand <= 256; cand *= 2) {

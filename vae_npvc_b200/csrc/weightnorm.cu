@@ -119,7 +119,26 @@ __device__ __forceinline__ void store_planes2(bf16* base, int64_t off, int64_t p
 // row), every load of the tile issued before the first use, and 8-byte stores (4 bf16 per lane, two tile rows per
 // warp instruction) instead of 4-byte ones.  The generic path is issue-bound (1.85 TB/s of traffic for a pass that
 // moves 8 bytes per parameter); this one does a third of its instructions.
-template <int K>
+// pack 4 floats into the P planes' 8-byte words and store them plane_stride apart
+template <int P>
+__device__ __forceinline__ void wn_store4(bf16* __restrict__ dst, int64_t plane_stride, float a, float b, float c, float d) {
+    const float x[4] = {a, b, c, d};
+    bf16 h[3][4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        if constexpr (P == 1) h[0][j] = __float2bfloat16_rn(x[j]);
+        else split3(x[j], h[0][j], h[1][j], h[2][j]);
+    }
+#pragma unroll
+    for (int p = 0; p < P; p++) {
+        uint2 o;
+        o.x = (uint32_t)__bfloat16_as_ushort(h[p][0]) | ((uint32_t)__bfloat16_as_ushort(h[p][1]) << 16);
+        o.y = (uint32_t)__bfloat16_as_ushort(h[p][2]) | ((uint32_t)__bfloat16_as_ushort(h[p][3]) << 16);
+        *reinterpret_cast<uint2*>(dst + p * plane_stride) = o;
+    }
+}
+
+template <int K, int P>
 __device__ __forceinline__ void wn_tile_full_p1(const float* __restrict__ v, float* __restrict__ w32,
                                                 const float* __restrict__ scale, int row0, int d0, int d1, int r0, int c0,
                                                 bf16* __restrict__ D, bf16* __restrict__ Tt, float* __restrict__ tile) {
@@ -157,10 +176,7 @@ __device__ __forceinline__ void wn_tile_full_p1(const float* __restrict__ v, flo
             const int idx = it * 16 + warp * 2 + half;
             const int j = idx / WN_TILE, rr = idx - j * WN_TILE;
             const float* src = tile + (j * WN_TILE + rr) * TP + l4;
-            uint2 o;
-            o.x = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[0])) | ((uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[1])) << 16);
-            o.y = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[2])) | ((uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[3])) << 16);
-            *reinterpret_cast<uint2*>(D + ((int64_t)j * d0 + r0 + rr) * p1 + c0 + l4) = o;
+            wn_store4<P>(D + ((int64_t)j * d0 + r0 + rr) * p1 + c0 + l4, (int64_t)K * d0 * p1, src[0], src[1], src[2], src[3]);
         }
     }
     if (Tt) {                                          // [K-1-j][col][row]: a half-warp writes 64 rows of one column
@@ -169,10 +185,8 @@ __device__ __forceinline__ void wn_tile_full_p1(const float* __restrict__ v, flo
             const int idx = it * 16 + warp * 2 + half;
             const int j = idx / WN_TILE, cc = idx - j * WN_TILE;
             const float* src = tile + (j * WN_TILE + l4) * TP + cc;
-            uint2 o;
-            o.x = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[0])) | ((uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[TP])) << 16);
-            o.y = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[2 * TP])) | ((uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(src[3 * TP])) << 16);
-            *reinterpret_cast<uint2*>(Tt + ((int64_t)(K - 1 - j) * d1 + c0 + cc) * p0 + r0 + l4) = o;
+            wn_store4<P>(Tt + ((int64_t)(K - 1 - j) * d1 + c0 + cc) * p0 + r0 + l4, (int64_t)K * d1 * p0, src[0], src[TP], src[2 * TP],
+                         src[3 * TP]);
         }
     }
 }
@@ -197,14 +211,19 @@ __global__ void __launch_bounds__(256, 3) wn_tiles_kernel(const float* __restric
     const int seg = nc * k;                            // contiguous floats per tile row
     const int total = nr * seg;
     const int row0 = (int)L[9] + r0;
-    if (fast && P == 1 && nr == WN_TILE && nc == WN_TILE && (k == 1 || k == 3) &&
+    if (fast && P <= 2 && nr == WN_TILE && nc == WN_TILE && (k == 1 || k == 3) &&
         ((((uintptr_t)(v + ((int64_t)r0 * d1 + c0) * k)) | ((uintptr_t)((int64_t)d1 * k * 4)) |
           (w32 ? (uintptr_t)(w32 + ((int64_t)r0 * d1 + c0) * k) : 0)) & 15) == 0) {
         const int64_t o_d = transposed ? L[7] : L[6], o_t = transposed ? L[6] : L[7];
         bf16* Dp = o_d >= 0 ? wbuf + o_d : nullptr;
         bf16* Tp = o_t >= 0 ? wbuf + o_t : nullptr;
-        if (k == 3) wn_tile_full_p1<3>(v, w32, scale, row0, d0, d1, r0, c0, Dp, Tp, wn_tile);
-        else wn_tile_full_p1<1>(v, w32, scale, row0, d0, d1, r0, c0, Dp, Tp, wn_tile);
+        if (P == 1) {
+            if (k == 3) wn_tile_full_p1<3, 1>(v, w32, scale, row0, d0, d1, r0, c0, Dp, Tp, wn_tile);
+            else wn_tile_full_p1<1, 1>(v, w32, scale, row0, d0, d1, r0, c0, Dp, Tp, wn_tile);
+        } else {
+            if (k == 3) wn_tile_full_p1<3, 2>(v, w32, scale, row0, d0, d1, r0, c0, Dp, Tp, wn_tile);
+            else wn_tile_full_p1<1, 2>(v, w32, scale, row0, d0, d1, r0, c0, Dp, Tp, wn_tile);
+        }
         return;
     }
     if ((seg & 3) == 0 && ((((uintptr_t)(v + ((int64_t)r0 * d1 + c0) * k)) | ((uintptr_t)((int64_t)d1 * k * 4))) & 15) == 0) {
@@ -471,7 +490,7 @@ extern "C" int vnb_wn_prepare_batch(const float* flat_p, const int64_t* desc, co
                                     const int* tile2layer, int total_tiles, int max_k, int P, float* row_scale,
                                     void* wbuf, float* w32buf, void* stream) {
     VNB_REQUIRE(flat_p && desc && row2layer && tile2layer && row_scale && wbuf && total_rows > 0 && total_tiles > 0 &&
-                    (P == 1 || P == 3), "wn_prepare_batch: bad arguments");
+                    (P >= 1 && P <= 3), "wn_prepare_batch: bad arguments");
     const size_t smem = (size_t)max_k * vnb::WN_TILE * (vnb::WN_TILE + 1) * sizeof(float);
     VNB_REQUIRE(max_k >= 1 && smem <= 200 * 1024, "wn_prepare_batch: kernel size %d too large for the tile buffer", max_k);
     static size_t smem_set = 0;
@@ -509,7 +528,7 @@ extern "C" int vnb_wn_backward_batch(const float* flat_p, float* flat_g, const i
 
 extern "C" int vnb_wn_prepare(const float* v, const float* g, int d0, int d1, int k, int transposed, int P,
                               void* wf, void* wb, float* w32, void* stream) {
-    VNB_REQUIRE(v && d0 > 0 && d1 > 0 && k > 0 && (P == 1 || P == 3), "wn_prepare: bad arguments");
+    VNB_REQUIRE(v && d0 > 0 && d1 > 0 && k > 0 && (P >= 1 && P <= 3), "wn_prepare: bad arguments");
     vnb::launch_k(vnb::wn_prepare_kernel, d0, 256, 0, (cudaStream_t)stream, v, g, d0, d1, k, transposed, P, (vnb::bf16*)wf,
                                                                 (vnb::bf16*)wb, w32);
     VNB_LAUNCH_CHECK("wn_prepare");

@@ -19,13 +19,16 @@ from . import prims as Pm
 from .prims import ACT_LRELU, ACT_NONE, ACT_RELU
 
 _ACT_KIND = {ACT_NONE: 'id', ACT_LRELU: 'lrelu', ACT_RELU: 'relu'}
-_PRECISION = {'P': 3 if os.environ.get('VNB_PRECISION', 'bf16').lower() in ('fp32', 'f32', '3') else 1}
+_MODES = {'bf16': 1, 'bf16x2': 2, 'fp32': 3, 'f32': 3, '1': 1, '2': 2, '3': 3, 1: 1, 2: 2, 3: 3}
+_PRECISION = {'P': _MODES.get(os.environ.get('VNB_PRECISION', 'bf16').lower(), 1)}
 
 
 def set_precision(mode):
-    """'bf16' -> single bf16 operand plane (fast);  'fp32' -> hi/mid/lo split planes
-    (fp32-faithful contraction on the same kernels)."""
-    _PRECISION['P'] = {'bf16': 1, 'fp32': 3, 1: 1, 3: 3}[mode]
+    """GEMM operand mode (number of bf16 planes an fp32 operand is split into; accumulation is always fp32 in TMEM):
+    'bf16'   -> 1 plane  (8 significant bits per operand, 1 product)             - fastest, ~1e-2 on gradients
+    'bf16x2' -> 2 planes (hi + mid, 16 bits, products hi*hi + hi*mid + mid*hi)   - <= 1e-3 on losses, gradients, features
+    'fp32'   -> 3 planes (hi + mid + lo, 24 bits, 6 products)                    - fp32-faithful, the strict parity mode."""
+    _PRECISION['P'] = _MODES[mode]
 
 
 def get_precision():

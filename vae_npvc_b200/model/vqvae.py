@@ -6,7 +6,7 @@ plugin mechanism, vae_npvc/trainer/basic.py:24-26).  Constructor keys, sub-modul
 protocol are the reference's; a reference checkpoint loads unchanged.  All arithmetic runs on
 the CUDA op-groups; calling the model on CPU tensors raises.
 
-Optional NEW config key (reference-preserving default): ``precision: 'bf16' | 'fp32'`` - GEMM
+Optional NEW config key (reference-preserving default): ``precision: 'bf16' | 'bf16x2' | 'fp32'`` - GEMM
 operand planes (see functional.set_precision).
 """
 import math

@@ -16,7 +16,7 @@ B200-native differences (all behind the same API):
     (averaged) over NCCL and the EMA codebook statistics are all-reduced inside the model
 
 New optional config keys (defaults keep the reference behaviour): ``cuda_graph`` (True),
-``graph_warmup`` (3), ``precision`` ('bf16' | 'fp32'), ``device`` ('cuda'), ``wgrad_stream`` (True),
+``graph_warmup`` (3), ``precision`` ('bf16' | 'bf16x2' | 'fp32'), ``device`` ('cuda'), ``wgrad_stream`` (True),
 ``bank_overlap`` (True), ``sparse_grad_zero`` (True).
 """
 import contextlib
