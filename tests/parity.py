@@ -147,3 +147,16 @@ def compare(got, want):
         rep['infer_rel_ids_equal'] = rel(got['infer'][ok_utt], want['infer'][ok_utt])
         rep['infer_max_rel_ids_equal'] = max_rel(got['infer'][ok_utt], want['infer'][ok_utt])
     return rep
+
+
+def perturbed_sensitivity(arch, sd, x, y, w64, eps, seed=1):
+    """Conditioning of the gradients: per-tensor relative change of the EXACT (float64) gradients when every parameter
+    is perturbed by a relative ``eps`` (Gaussian).  The model has 21 LeakyReLU / 2 ReLU layers over 2048 x 512
+    activations: a pre-activation that crosses 0 flips a slope, and one flip moves an upstream weight gradient by
+    ~1e-3 norm-wise.  An implementation whose forward values carry a relative error eps cannot be closer to the
+    float64 gradients than this, whatever its backward arithmetic."""
+    g = torch.Generator().manual_seed(seed)
+    sd2 = {k: (v * (1 + eps * torch.randn(v.shape, generator=g)) if v.is_floating_point() and v.dim() > 0 else v)
+           for k, v in sd.items()}
+    w2 = oracle_eval(arch, sd2, x, y, torch.float64)
+    return {n: rel(w2['grads'][n], gr) for n, gr in w64['grads'].items()}, compare(w2, w64)
