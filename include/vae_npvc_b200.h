@@ -64,7 +64,19 @@ int vnb_get_backend(void);
 #define VNB_OPT_EW_V2 0
 #define VNB_OPT_FAST_GATE 1
 #define VNB_OPT_WN_V2 2
-#define VNB_OPT_COUNT_ 3
+/*   VNB_OPT_GEMM_V3   third-generation conv / weight-gradient GEMMs (CTA pairs, all operand planes of a chunk per
+ *                     pipeline stage; csrc/tc_conv3.cuh): 0 off, 1 where the cost model prefers them (default), 2 always
+ *   VNB_OPT_TC3_BN / _PAIR / _STAGES   tuning overrides of those kernels (0 / -1 / 0 = automatic)
+ *   VNB_OPT_TC_DBG    9: the tcgen05 conv kernels record the clock64 timeline of CTA (0,0,0) (vnb_debug_tc_timeline) */
+#define VNB_OPT_GEMM_V3 3
+#define VNB_OPT_TC3_BN 4
+#define VNB_OPT_TC3_PAIR 5
+#define VNB_OPT_TC3_STAGES 6
+#define VNB_OPT_TC_DBG 7
+/*   VNB_OPT_TC3_SMEM_KB  cap on the dynamic shared memory of the third-generation GEMMs (0 = none): <= 110 lets two CTAs
+ *                     share an SM, so that the next kernel's prologue overlaps this kernel's epilogue */
+#define VNB_OPT_TC3_SMEM_KB 8
+#define VNB_OPT_COUNT_ 9
 void vnb_set_option(int which, int value);
 int vnb_get_option(int which);
 /* debug: how many bounded mbarrier waits of the tcgen05 kernels timed out since load (must stay 0);

@@ -543,6 +543,10 @@ static int launch_conv_tc(const void* in, const void* w, int Cin_p, int ksplit, 
     return VNB_OK;
 }
 
+}  // namespace vnb
+#include "tc_conv3.cuh"
+namespace vnb {
+
 int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int taps, int dil, int Cout,
                 const float* bias, int bias_bstride, const float* residual, float* out, int accumulate,
                 double* gn_sums, int gn_groups, cudaStream_t st) {
@@ -550,7 +554,7 @@ int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int
     const int64_t mt = (int64_t)ceil_div(T, TC_BM) * B;
     if (Cout < 8 || Cin < 8 || mt > 65535) return 1;
     if (gn_sums && ((Cout / gn_groups) & 31) != 0) return 1;      // a thread's 4 channels must not straddle groups
-    static const int dbg = getenv("VNB_TC_DBG") ? atoi(getenv("VNB_TC_DBG")) : 0;
+    const int dbg = option(VNB_OPT_TC_DBG);
     static const int force_bn = getenv("VNB_TC_BN") ? atoi(getenv("VNB_TC_BN")) : 0;
     static const int force_ks = getenv("VNB_TC_KSPLIT") ? atoi(getenv("VNB_TC_KSPLIT")) : 0;
     ConvTcArgs a{B, Cin, Cout, T, taps, dil, P, bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups, dbg, 0, 1, 0};
@@ -594,6 +598,13 @@ int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int
             const int64_t cost = waves * ((int64_t)ceil_div(nkc, k) * kch * per_chunk[kch == 1 ? 0 : 1][ci] + fixed[ci][ki]);
             if (cost < best) { best = cost; bn = cand; ks = k; }
         }
+    }
+    {
+        // third-generation kernel (CTA pairs, all operand planes of a chunk per stage) unless the round-1 kernel's
+        // cluster split-K is modelled faster for this shape
+        const int r3 = conv_fwd_tc3(in, P, B, Cin, T, w, taps, dil, Cout, bias, bias_bstride, residual, out, accumulate, gn_sums,
+                                    gn_groups, (force_bn || force_ks) ? 0 : best, st);
+        if (r3 <= 0) return r3;
     }
     if (force_bn) bn = force_bn;
     if (force_ks) ks = force_ks;

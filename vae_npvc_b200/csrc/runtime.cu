@@ -32,6 +32,12 @@ static void opts_init() {
     g_opts[VNB_OPT_EW_V2].store(env_or("VNB_EW_V2", VNB_EW_V2_DEFAULT));
     g_opts[VNB_OPT_FAST_GATE].store(env_or("VNB_FAST_GATE", VNB_FAST_GATE_DEFAULT));
     g_opts[VNB_OPT_WN_V2].store(env_or("VNB_WN_V2", VNB_WN_V2_DEFAULT));
+    g_opts[VNB_OPT_GEMM_V3].store(env_or("VNB_GEMM_V3", 1));
+    g_opts[VNB_OPT_TC3_BN].store(env_or("VNB_TC3_BN", 0));
+    g_opts[VNB_OPT_TC3_PAIR].store(env_or("VNB_TC3_PAIR", -1));
+    g_opts[VNB_OPT_TC3_STAGES].store(env_or("VNB_TC3_STAGES", 0));
+    g_opts[VNB_OPT_TC_DBG].store(env_or("VNB_TC_DBG", 0));
+    g_opts[VNB_OPT_TC3_SMEM_KB].store(env_or("VNB_TC3_SMEM_KB", 0));
     g_opts_init.store(true, std::memory_order_release);
 }
 int option(int which) {
