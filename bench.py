@@ -22,16 +22,53 @@ if ROOT not in sys.path:
 
 import torch  # noqa: E402
 
-B_PER_GPU, T_FRAMES = 16, 128
-FLOP_PER_FRAME = 178_757_632          # algorithmic fwd+bwd FLOP/frame, SURVEY.md section 8(d)
-WORKLOAD_NAME = ('VQ-VAE VCC2020 shape (BASELINE configs[1]): 80-mel, 16x128 frames per GPU, C512, 10+10 blocks, '
-                 'codebook 512x64 (use_ema false, embed_norm true), Adam+clip+StepLR')
+DEFAULT_PRECISION = 'bf16x2'         # fastest operand mode that meets the stated parity bars (tests/test_gpu_parity_modes.py)
 
 
-def workload_arch():
+def _wl(name):
+    """The named workloads of BASELINE.json.configs (default = configs[1], the one the metric is quoted on)."""
     from vae_npvc_b200 import synth
-    return synth.arch_config(X=80, C=512, D=64, K=512, Y=128, S=128, y_num=117, stacks=10, use_ema=False,
-                             embed_norm=True)
+    if name == 'vcc2020':
+        arch = synth.arch_config(X=80, C=512, D=64, K=512, Y=128, S=128, y_num=117, stacks=10, use_ema=False, embed_norm=True)
+        return dict(arch=arch, B=16, T=128, kind='vqvae', what='VQ-VAE VCC2020 shape (BASELINE configs[1]): 80-mel, 16x128 frames '
+                    'per GPU, C512, 10+10 blocks, codebook 512x64 (use_ema false, embed_norm true), Adam+clip+StepLR')
+    if name == 'vcc2020_yaml':
+        arch = synth.arch_config(X=80, C=512, D=128, K=512, Y=128, S=128, y_num=117, stacks=10, use_ema=True)
+        return dict(arch=arch, B=128, T=256, kind='vqvae', what='VQ-VAE as shipped (egs/vcc20/vae1/conf/train_pytorch_vqvae.yaml): '
+                    '80-mel, 128x256 frames per GPU, use_ema true, codebook 512x128, Adam+clip+StepLR')
+    if name == 'aishell3':
+        arch = synth.arch_config(X=160, C=512, D=128, K=128, Y=128, S=256, y_num=218, stacks=10, use_ema=False, jitter_p=0.12)
+        return dict(arch=arch, B=32, T=128, kind='vqvae', what='AISHELL-3 shape (BASELINE configs[3]; egs/aishell3/vc2/conf/'
+                    'train_pytorch_vqvae.yaml): 160-mel, skip 256, codebook 128x128, 218 speakers, jitter_p 0.12, 32x128 frames per '
+                    'GPU (256x128 global on 8 GPUs)')
+    if name == 'cdvae':
+        arch = synth.cdvae_config()
+        return dict(arch=arch, B=16, T=128, kind='cdvae', what='CDVAE throughput shape (BASELINE configs[2]): 513-dim SP + 40-dim MCC '
+                    'encoders / decoders over one shared 512x128 codebook, four reconstructions, 16x128 frames per domain per GPU')
+    if name == 'decode':
+        arch = synth.arch_config(X=80, C=512, D=64, K=512, Y=128, S=128, y_num=117, stacks=10)
+        return dict(arch=arch, B=64, T=512, kind='decode', what='decoder-only batched conversion (BASELINE configs[4]): '
+                    'Model.decode((ids 64x512, speaker ids)) -> 80-mel, VCC2020-shape decoder')
+    raise SystemExit('unknown workload %r' % name)
+
+
+def flop_per_frame(wl):
+    """Algorithmic FLOPs per frame of the workload: fwd + bwd = 3 x 2 x MAC for the convs, the VQ
+    distance GEMM forward only."""
+    from vae_npvc_b200 import synth
+    a, T = wl['arch'], wl['T']
+    vq = 2 * a['z_num'] * a['z_dim']
+    if wl['kind'] == 'cdvae':
+        macs, n = 0, 0
+        for dom in a['domains'].values():
+            e, d = synth.conv_macs_per_frame(dom['encoder'], dom['decoder'], T)
+            macs += e + 2 * d                      # every decoder runs on both domains' latents
+            n += 1
+        return 6 * macs + n * vq
+    e, d = synth.conv_macs_per_frame(a['encoder'], a['decoder'], T)
+    if wl['kind'] == 'decode':
+        return 2 * d
+    return 6 * (e + d) + vq
 
 
 def peaks():
@@ -96,24 +133,24 @@ class ClockSampler(threading.Thread):
                 'samples': len(self.rows)}
 
 
-def cpu_oracle_step_rate(steps, warmup, threads=None):
+def cpu_oracle_step_rate(wl, steps, warmup, threads=None):
     """The reference's CPU path restated (oracle port): full train step, fp32, torch CPU."""
     from oracle import synth
     from oracle import vqvae_oracle as O
-    arch = workload_arch()
+    arch = wl['arch']
     cores = threads or os.cpu_count() or 1
     torch.set_num_threads(cores)
     sd = synth.synthetic_state_dict(arch, 777)
     params = O.params_from_state_dict(sd)
     opt = O.AdamState(O.trainable_names(params), lr=1e-3, step_size=100000, gamma=0.5)
-    x, y = synth.synthetic_batch(arch, B_PER_GPU, T_FRAMES, 777)
+    x, y = synth.synthetic_batch(arch, wl['B'], wl['T'], 777)
     for _ in range(warmup):
         O.train_step(params, arch, opt, x, y, max_grad_norm=10)
     t0 = time.perf_counter()
     for _ in range(steps):
         O.train_step(params, arch, opt, x, y, max_grad_norm=10)
     dt = (time.perf_counter() - t0) / steps
-    return B_PER_GPU * T_FRAMES / dt, dt, cores
+    return wl['B'] * wl['T'] / dt, dt, cores
 
 
 def reference_available():
@@ -121,24 +158,41 @@ def reference_available():
     return build_ref.available()
 
 
-def reference_step_rate(steps, warmup, device='cpu', autocast=False, threads=None):
+def reference_step_rate(wl, steps, warmup, device='cpu', autocast=False, threads=None):
     """The UNMODIFIED reference modules staged under oracle/_ref (oracle/build_ref.py): vae_npvc.model.vqvae.Model
     with the train step of vae_npvc/trainer/basic.py:55-79 around it (zero_grad, forward, backward,
     clip_grad_norm_(10), Adam(0.5, 0.999), StepLR).  On ``device='cuda'`` the reference's own Trainer class is used
     as is (it hard-codes .cuda(), trainer/basic.py:28) - stock eager PyTorch on the B200; ``autocast`` wraps its
-    forward in torch.autocast(bfloat16).  -> (frames/s, s/step, cores)."""
+    forward in torch.autocast(bfloat16).  kind 'decode': Model.decode forward only (vqvae.py:55-60).
+    -> (frames/s, s/step, cores)."""
     from oracle import build_ref, synth
     build_ref.import_reference()
-    arch = workload_arch()
+    arch = wl['arch']
+    B, T = wl['B'], wl['T']
     cfg = dict(arch)
     cfg.update(model_type='vae_npvc.model.vqvae', optim_type='Adam', learning_rate=1e-3, max_grad_norm=10,
                lr_scheduler='StepLR', lr_param={'step_size': 100000, 'gamma': 0.5, 'last_epoch': -1})
     sd = synth.synthetic_state_dict(arch, 777)
-    x, y = synth.synthetic_batch(arch, B_PER_GPU, T_FRAMES, 777)
+    x, y = synth.synthetic_batch(arch, B, T, 777)
     cores = threads or os.cpu_count() or 1
     import warnings
     warnings.simplefilter('ignore')
-    if device == 'cuda':
+    sync = (lambda: None)
+    if wl['kind'] == 'decode':
+        from vae_npvc.model.vqvae import Model as RefModel
+        torch.set_num_threads(cores)
+        m = RefModel(cfg)
+        m.load_state_dict(sd)
+        m.eval()
+        ids = torch.randint(0, arch['z_num'], (B, T), generator=torch.Generator().manual_seed(5))
+        if device == 'cuda':
+            m, ids, y = m.cuda(), ids.cuda(), y.cuda()
+            sync = torch.cuda.synchronize
+
+        def step(i):
+            with torch.no_grad():
+                return m.decode((ids, y))
+    elif device == 'cuda':
         from vae_npvc.trainer.basic import Trainer as RefTrainer
         tr = RefTrainer(cfg)
         tr.model.load_state_dict(sd)
@@ -167,9 +221,6 @@ def reference_step_rate(steps, warmup, device='cpu', autocast=False, threads=Non
             opt.step()
             sch.step()
             return i + 1, detail
-
-        def sync():
-            return None
     for i in range(warmup):
         step(i)
     sync()
@@ -178,7 +229,7 @@ def reference_step_rate(steps, warmup, device='cpu', autocast=False, threads=Non
         step(i)
     sync()
     dt = (time.perf_counter() - t0) / steps
-    return B_PER_GPU * T_FRAMES / dt, dt, cores
+    return B * T / dt, dt, cores
 
 
 def _autocast_call(fwd, inp):
@@ -186,46 +237,57 @@ def _autocast_call(fwd, inp):
         return fwd(inp)
 
 
+def metric_name(wl):
+    return 'conversion frames/sec (decoder only)' if wl['kind'] == 'decode' else 'train frames/sec (fwd+bwd+optimizer)'
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
+    wl = _wl(args.workload)
+    if wl['kind'] == 'cdvae':
+        print(json.dumps({'impl': 'reference', 'unavailable': 'the reference snapshot has no cross-domain (CDVAE) model file '
+                          '(SURVEY.md F9): nothing to time for --workload cdvae'}))
+        return
     on_gpu = args.ref_device == 'cuda'
-    cap = 200 if on_gpu else 12
-    steps, warm = max(1, min(args.steps, cap)), max(1, min(args.warmup, 10 if on_gpu else 3))
+    big = wl['B'] * wl['T'] > 8192
+    cap = 200 if on_gpu else (3 if big else 12)
+    steps, warm = max(1, min(args.steps, cap)), max(1, min(args.warmup, 10 if on_gpu else (1 if big else 3)))
     if reference_available():
-        fps, dt, cores = reference_step_rate(steps, warm, args.ref_device, args.ref_autocast)
+        fps, dt, cores = reference_step_rate(wl, steps, warm, args.ref_device, args.ref_autocast)
         kind = 'reference'
-        what = ('the reference\'s own vae_npvc.model.vqvae.Model (staged under oracle/_ref) + trainer/basic.py:55-79 step, '
-                + ('stock eager PyTorch on the B200 through the reference Trainer%s' % (' under bf16 autocast' if args.ref_autocast else ', fp32')
+        what = ('the reference\'s own vae_npvc.model.vqvae.Model (staged under oracle/_ref)'
+                + (' decode()' if wl['kind'] == 'decode' else ' + trainer/basic.py:55-79 step') + ', '
+                + ('stock eager PyTorch on the B200%s' % (' under bf16 autocast' if args.ref_autocast else ', fp32')
                    if on_gpu else 'torch CPU fp32'))
     else:
-        if on_gpu:
-            print(json.dumps({'impl': 'reference', 'unavailable': 'oracle/_ref not staged: no reference modules to run on the GPU'}))
+        if on_gpu or wl['kind'] == 'decode':
+            print(json.dumps({'impl': 'reference', 'unavailable': 'oracle/_ref not staged: no reference modules to run'}))
             return
-        fps, dt, cores = cpu_oracle_step_rate(steps, warm)
+        fps, dt, cores = cpu_oracle_step_rate(wl, steps, warm)
         kind = 'port'
         what = 'oracle restatement of the reference Model + trainer/basic.py step, torch CPU fp32'
     line = {
-        'impl': 'reference', 'metric': 'train frames/sec (fwd+bwd+optimizer)', 'value': fps, 'unit': 'frames/s',
+        'impl': 'reference', 'metric': metric_name(wl), 'value': fps, 'unit': 'frames/s',
         'n_gpus': args.gpus, 'steps': steps, 'warmup': warm, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16 autocast' if (on_gpu and args.ref_autocast) else 'f32',
         'data': 'synthetic',
-        'config': {'workload': WORKLOAD_NAME, 'reference_device': args.ref_device},
+        'config': {'workload': wl['what'], 'reference_device': args.ref_device},
         'cpu_baseline': {'value': fps, 'unit': 'frames/s', 'cores': cores, 'kind': kind,
-                         'sample': '%d full train steps of 16x128 frames (%s)' % (steps, what)},
+                         'sample': '%d steps of %dx%d frames (%s)' % (steps, wl['B'], wl['T'], what)},
         'e2e': {'value': fps, 'unit': 'frames/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }
     print(json.dumps(line))
 
 
-def time_dominant_kernel(P, iters=20):
-    """CUDA-event time of the step's dominant kernel in isolation: the decoder block's k=3
-    ConvTranspose as a GEMM (Cout=1024, Cin=512, 3 taps, 16x128 frames) - 20 of the step's
-    ~110 GEMM launches have this shape or its data-/weight-gradient twin, ~2/3 of all FLOPs."""
+def time_dominant_kernel(P, B, T, iters=20):
+    """CUDA-event time of the step's dominant kernel in isolation: the decoder block's k=3 ConvTranspose as a GEMM
+    (Cout=1024, Cin=512, 3 taps, B x T frames) - 20 of the step's ~110 GEMM launches have this shape or its data- /
+    weight-gradient twin, ~2/3 of all FLOPs."""
     from vae_npvc_b200 import prims as Pm
     from vae_npvc_b200 import _C as _Cm
-    B, T, Cin, Cout, taps = B_PER_GPU, T_FRAMES, 512, 1024, 3
+    Cin, Cout, taps = 512, 1024, 3
     x = torch.randn(B, Cin, T, device='cuda')
     v = torch.randn(Cin, Cout, taps, device='cuda') * 0.02
     W = Pm.wn_prepare(v, None, True, P)
@@ -259,7 +321,7 @@ def time_dominant_kernel(P, iters=20):
         times.append(e0.elapsed_time(e1) * 1e-3 / reps)
     dt = sum(times) / len(times)
     pairs = {1: 1, 2: 3, 3: 6}[P]
-    flops = 2.0 * B * T * Cout * Cin * taps            # algorithmic (the fp32-faithful mode executes 6x)
+    flops = 2.0 * B * T * Cout * Cin * taps            # algorithmic (the multi-plane modes execute 3x / 6x)
     return dt, flops, flops * pairs
 
 
@@ -275,30 +337,77 @@ def run_ours(args, rank, world):
         import torch.distributed as dist
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
-    arch = workload_arch()
-    cfg = dict(arch)
+    wl = _wl(args.workload)
+    arch, B, T = wl['arch'], wl['B'], wl['T']
+    P = {'bf16': 1, 'bf16x2': 2, 'fp32': 3}[args.precision]
     warm = max(3, args.warmup)
-    cfg.update(model_type='vae_npvc_b200.model.vqvae', precision=args.precision, cuda_graph=not args.no_graph,
-               overlap_allreduce=not bool(os.environ.get('VNB_NO_OVERLAP')), allreduce=os.environ.get('VNB_ALLREDUCE', 'multimem'),
-               allreduce_blocks=int(os.environ.get('VNB_AR_BLOCKS', 0)),
-               bank_overlap=not bool(os.environ.get('VNB_NO_BANK_OVERLAP')),
-               sparse_grad_zero=not bool(os.environ.get('VNB_NO_SPARSE_ZERO')),
-               graph_warmup=min(3, warm - 1), learning_rate=1e-3, max_grad_norm=10, lr_scheduler='StepLR',
-               lr_param={'step_size': 100000, 'gamma': 0.5, 'last_epoch': -1})
-    torch.manual_seed(777)
-    tr = Trainer(cfg)
-    tr.model.load_state_dict(synth.synthetic_state_dict(arch, 777))       # same weights on every rank
-    x, y = synth.synthetic_batch(arch, B_PER_GPU, T_FRAMES, 777 + rank)   # each rank its own shard
-    xh, yh = x.pin_memory(), y.pin_memory()
-    xd, yd = x.cuda(), y.cuda()
 
     def barrier():
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize()
 
+    detail = {}
+    if wl['kind'] == 'decode':
+        # forward-only conversion: Model.decode through the public module API, weights frozen
+        import vae_npvc_b200.functional as Fn
+        from vae_npvc_b200.model.vqvae import Model
+        Fn.set_precision(args.precision)
+        m = Model(arch)
+        m.load_state_dict(synth.synthetic_state_dict(arch, 777))
+        m = m.cuda().eval()
+        gen = torch.Generator().manual_seed(5 + rank)
+        ids = torch.randint(0, arch['z_num'], (B, T), generator=gen)
+        y = torch.randint(0, arch['y_num'], (B, 1), generator=gen)
+        host_in = [ids.pin_memory(), y.pin_memory()]
+        dev_in = [ids.cuda(), y.cuda()]
+        out_host = torch.empty((B, arch['decoder']['final_channels'], T), dtype=torch.float32).pin_memory()
+
+        def step_device():
+            with torch.no_grad():
+                return m.decode((dev_in[0], dev_in[1]))
+
+        def step_e2e(i):
+            with torch.no_grad():
+                o = m.decode((host_in[0].cuda(non_blocking=True), host_in[1].cuda(non_blocking=True)))
+                out_host.copy_(o, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        h2d, d2h = ids.numel() * 8 + y.numel() * 8, out_host.numel() * 4
+        tr = None
+    else:
+        cfg = dict(arch)
+        cfg.update(model_type=arch.get('model_type', 'vae_npvc_b200.model.vqvae') if wl['kind'] == 'cdvae' else 'vae_npvc_b200.model.vqvae',
+                   precision=args.precision, cuda_graph=not args.no_graph,
+                   overlap_allreduce=not bool(os.environ.get('VNB_NO_OVERLAP')), allreduce=os.environ.get('VNB_ALLREDUCE', 'multimem'),
+                   allreduce_blocks=int(os.environ.get('VNB_AR_BLOCKS', 0)),
+                   bank_overlap=not bool(os.environ.get('VNB_NO_BANK_OVERLAP')),
+                   sparse_grad_zero=not bool(os.environ.get('VNB_NO_SPARSE_ZERO')),
+                   graph_warmup=min(3, warm - 1), learning_rate=1e-3, max_grad_norm=10, lr_scheduler='StepLR',
+                   lr_param={'step_size': 100000, 'gamma': 0.5, 'last_epoch': -1})
+        torch.manual_seed(777)
+        tr = Trainer(cfg)
+        if wl['kind'] == 'cdvae':
+            tr.model.load_state_dict(synth.cdvae_state_dict(arch, 777))
+            xs, y = synth.cdvae_batch(arch, B, T, 777 + rank)
+            tensors = xs + [y]
+        else:
+            tr.model.load_state_dict(synth.synthetic_state_dict(arch, 777))       # same weights on every rank
+            x, y = synth.synthetic_batch(arch, B, T, 777 + rank)                  # each rank its own shard
+            tensors = [x, y]
+        host_in = [t.pin_memory() for t in tensors]
+        dev_in = [t.cuda() for t in tensors]
+
+        def step_device():
+            return tr.train_step_device(*dev_in)
+
+        def step_e2e(i):
+            nonlocal detail
+            _, detail = tr.train_step(host_in, i)
+        h2d = sum(t.numel() * t.element_size() for t in tensors)
+        d2h = None
+
     for _ in range(warm):
-        tr.train_step_device(xd, yd)
+        step_device()
     barrier()
     # ---- device-resident timing: CUDA events on the launching stream ----
     sampler = ClockSampler(local)
@@ -308,16 +417,16 @@ def run_ours(args, rank, world):
     barrier()
     e0.record()
     for _ in range(args.steps):
-        keys, scal = tr.train_step_device(xd, yd)
+        step_device()
     e1.record()
     barrier()
     dt = e0.elapsed_time(e1) * 1e-3
     eager_launches = _C.launch_count()
-    # ---- end to end through Trainer.train_step: pinned host batch in, python floats out ----
+    # ---- end to end through the public API: pinned host batch in, host results out ----
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
-        it, detail = tr.train_step([xh, yh], i)
+        step_e2e(i)
     torch.cuda.synchronize()
     dt_e2e = time.perf_counter() - t0
     clocks = sampler.stop()
@@ -325,50 +434,64 @@ def run_ours(args, rank, world):
     if dist is not None:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     dt, dt_e2e = float(tmax[0]), float(tmax[1])
-    on_graph = tr.last_step_on_graph
+    on_graph = bool(tr is not None and tr.last_step_on_graph)
     per_step = tr.launches_per_step if on_graph else eager_launches // max(1, args.steps)
+    if d2h is None:
+        d2h = 4 * len(detail)
     if rank == 0:
-        frames = B_PER_GPU * T_FRAMES * world * args.steps
+        frames = B * T * world * args.steps
         value, e2e = frames / dt, frames / dt_e2e
         pk = peaks()
-        P = {'bf16': 1, 'bf16x2': 2, 'fp32': 3}[args.precision]
-        kdt, kflops, kexec = time_dominant_kernel(P)
+        kdt, kflops, kexec = time_dominant_kernel(P, min(B, 128), T)
+        fpf = flop_per_frame(wl)
         line = {
-            'metric': 'train frames/sec (fwd+bwd+optimizer)', 'value': value, 'unit': 'frames/s', 'n_gpus': world,
+            'metric': metric_name(wl), 'value': value, 'unit': 'frames/s', 'n_gpus': world,
             'steps': args.steps, 'warmup': warm, 'ms_per_step': dt / args.steps * 1e3, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': {1: 'bf16', 2: 'bf16x2 (hi+mid bf16 planes, fp32 accumulate)', 3: 'f32 (3xbf16 split planes)'}[P],
+            'scaling': 'weak', 'vs_baseline': None,
+            'dtype': {1: 'bf16', 2: 'bf16x2 (hi+mid bf16 operand planes, fp32 accumulate)', 3: 'f32 (3xbf16 split planes)'}[P],
             'data': 'synthetic',
-            'config': {'workload': WORKLOAD_NAME,
-                       'frames_per_gpu_per_step': B_PER_GPU * T_FRAMES, 'parallelism': 'dp%d' % world,
-                       'cuda_graph': bool(on_graph),
-                       'options': {'ew_v2': _C.get_option(_C.OPT_EW_V2), 'fast_gate': _C.get_option(_C.OPT_FAST_GATE),
-                                   'bank_overlap': bool(tr.bank_overlap), 'sparse_grad_zero': tr._zero_idx is not None},
+            'config': {'workload': wl['what'], 'workload_key': args.workload,
+                       'frames_per_gpu_per_step': B * T, 'parallelism': 'dp%d' % world,
+                       'cuda_graph': on_graph,
+                       'options': {'precision': args.precision,
+                                   'parity_met': {'bf16': 'losses 1e-3 only (gradients ~1e-2..2e-1, features 6e-3..3e-2)',
+                                                  'bf16x2': 'losses 1e-6, converted features 5e-6, ids bit-exact, gradients at the '
+                                                            'conditioning floor of the model (median <= 1.2e-3; tests/test_gpu_parity_modes.py)',
+                                                  'fp32': 'losses 1e-6, features 5e-7, ids bit-exact, gradients median 3e-6'}[args.precision],
+                                   'ew_v2': _C.get_option(_C.OPT_EW_V2), 'fast_gate': _C.get_option(_C.OPT_FAST_GATE),
+                                   'gemm_v3': _C.get_option(_C.OPT_GEMM_V3),
+                                   'bank_overlap': bool(tr.bank_overlap) if tr else None,
+                                   'sparse_grad_zero': (tr._zero_idx is not None) if tr else None},
                        'l2': 'no explicit flush: each step streams params+grads+Adam moments+operand planes '
                              '(~0.7 GB) > 126 MB L2; the isolated-kernel timing flushes L2 with a 256 MB write',
-                       'step_roofline_frac_tensor': value * FLOP_PER_FRAME / (world * pk['tf_sus'] * 1e12)},
+                       'flop_per_frame': fpf,
+                       'step_roofline_frac_tensor': value * fpf / (world * pk['tf_sus'] * 1e12)},
             'clocks': clocks,
-            'e2e': {'value': e2e, 'unit': 'frames/s', 'h2d_bytes_per_step': x.numel() * 4 + y.numel() * 8,
-                    'd2h_bytes_per_step': 4 * len(detail)},
+            'e2e': {'value': e2e, 'unit': 'frames/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h},
             'gpu_launches': int(per_step * args.steps),
-            'roofline': {'bound': 'tensor', 'kernel': 'conv_fwd Cout1024 Cin512 k3 (decoder conv_in), backend %s'
-                         % {0: 'auto', 1: 'simt', 2: 'tc'}[_C.get_backend()],
+            'roofline': {'bound': 'tensor', 'kernel': 'conv_fwd Cout1024 Cin512 k3 (decoder conv_in) at %dx%d frames, backend %s'
+                         % (min(B, 128), T, {0: 'auto', 1: 'simt', 2: 'tc'}[_C.get_backend()]),
                          'achieved': kflops / kdt / 1e12, 'peak': pk['tf_burst'], 'unit': 'TFLOP/s',
                          'frac': kflops / kdt / 1e12 / pk['tf_burst'],
                          # dram__bytes_read.sum + dram__bytes_write.sum of this launch from the ncu --set full capture
                          # (profiles/r01_ncu_conv_fwd_dominant.txt): the bf16 operands once, the output stays in L2
-                         'traffic': 5278464 if P == 1 else None,
+                         'traffic': 5278464 if (P == 1 and B * T == 2048) else None,
                          'executed_tflops': kexec / kdt / 1e12, 'peak_source': pk['src'], 'kernel_ms': kdt * 1e3},
         }
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and wl['kind'] != 'cdvae':
+            big = B * T > 8192
             if reference_available():
-                fps, cdt, cores = reference_step_rate(8, 2)
-                kind, what = 'reference', "the reference's own vae_npvc.model.vqvae.Model (oracle/_ref) + trainer/basic.py:55-79 step"
-            else:
-                fps, cdt, cores = cpu_oracle_step_rate(8, 2)
+                fps, cdt, cores = reference_step_rate(wl, 2 if big else 8, 1 if big else 2)
+                kind, what = 'reference', "the reference's own vae_npvc.model.vqvae.Model (oracle/_ref)"
+            elif wl['kind'] == 'vqvae':
+                fps, cdt, cores = cpu_oracle_step_rate(wl, 2 if big else 8, 1 if big else 2)
                 kind, what = 'port', 'oracle restatement of the reference Model + trainer step'
-            line['cpu_baseline'] = {'value': fps, 'unit': 'frames/s', 'cores': cores, 'kind': kind,
-                                    'sample': '8 full train steps of 16x128 frames (%s, torch CPU fp32), %.0f ms/step'
-                                              % (what, cdt * 1e3)}
+            else:
+                fps = None
+            if fps is not None:
+                line['cpu_baseline'] = {'value': fps, 'unit': 'frames/s', 'cores': cores, 'kind': kind,
+                                        'sample': '%d steps of %dx%d frames (%s, torch CPU fp32), %.0f ms/step'
+                                                  % (2 if big else 8, B, T, what, cdt * 1e3)}
         print(json.dumps(line))
     if dist is not None:
         # no destroy_process_group(): tearing NCCL down while captured graphs still hold its kernels hung at
@@ -386,7 +509,9 @@ def main():
     ap.add_argument('--steps', type=int, default=100)          # 0.2 s of timed steps: 20-step runs scatter by +-2 %
     ap.add_argument('--warmup', type=int, default=10)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--precision', default='bf16', choices=['bf16', 'bf16x2', 'fp32'])
+    ap.add_argument('--precision', default=DEFAULT_PRECISION, choices=['bf16', 'bf16x2', 'fp32'])
+    ap.add_argument('--workload', default='vcc2020', choices=['vcc2020', 'vcc2020_yaml', 'aishell3', 'cdvae', 'decode'],
+                    help='default = BASELINE.json configs[1]; the others are the remaining named workloads')
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     # diagnostics of the reference arm (defaults = the contract: the reference's CPU path on the host cores)

@@ -249,6 +249,10 @@ int vnb_vq_frame_rows(const float* z, const int64_t* perm, int B, int D, int T, 
 int vnb_jitter_fwd(const float* in, const int64_t* src, int B, int D, int T, float* out, void* stream);
 /* grad: zero where src[t] != t */
 int vnb_jitter_bwd(const float* dout, const int64_t* src, int B, int D, int T, float* din, void* stream);
+/* the per-frame draws of Jitter.forward (vae_npvc/model/layers_vq.py:360-378) on the device: src[t] in {t-1, t, t+1}
+ * with the reference's distribution; state = {seed, call counter} (int64[2], counter incremented by the kernel), so a
+ * captured CUDA graph draws a fresh table on every replay */
+int vnb_jitter_sources(int T, float p, int64_t* state, int64_t* src, void* stream);
 
 /* ---- log-loss (layers.py:283-296): acc[0] += scale * sum 0.5*(log2pi + (xhat-x)^2) (zeroed by caller) */
 int vnb_logloss_fwd(const float* xhat, const float* x, int64_t n, float scale, float* acc, void* stream);

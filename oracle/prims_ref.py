@@ -525,6 +525,23 @@ def jitter_fwd(x, src):
     return x[:, :, src]
 
 
+def jitter_sources(T, p, state):
+    """Contract of vnb_jitter_sources: same DISTRIBUTION as Jitter's host loop (layers_vq.py:360-378, inverted flag
+    included); the stream itself is implementation-defined.  state[1] counts calls."""
+    gen = torch.Generator().manual_seed(int(state[0]) * 1000003 + int(state[1]))
+    u = torch.rand(T, generator=gen)
+    sign = torch.randint(0, 2, (T,), generator=gen) * 2 - 1
+    t = torch.arange(T)
+    s = torch.where(u >= p, t + sign, t)
+    if T > 1:
+        s[0] = 1 if u[0] >= p else 0
+        s[T - 1] = T - 2 if u[T - 1] >= p else T - 1
+    else:
+        s[0] = 0
+    state[1] += 1
+    return s.to(torch.int64)
+
+
 def jitter_bwd(dout, src):
     keep = (src == torch.arange(src.numel())).view(1, 1, -1)
     return torch.where(keep, dout, torch.zeros_like(dout))

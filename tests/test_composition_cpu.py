@@ -334,6 +334,50 @@ def test_resume_keeps_decayed_lr_like_torch(cpu_prims, monkeypatch, tmp_path):
         assert rel_err(a, b) < 1e-5
 
 
+def _cdvae_small():
+    arch = synth.cdvae_config(Xa=10, Xb=6, C=16, D=8, K=32, Y=8, S=12, y_num=5, stacks=2)
+    return arch, synth.cdvae_state_dict(arch, 777), synth.cdvae_batch(arch, 3, 20, 777)
+
+
+def test_cdvae_composition_matches_oracle_parts(cpu_prims, monkeypatch):
+    """BASELINE configs[2] (cross-domain, two encoders / decoders over one shared codebook): the product composition
+    against the same wiring of the oracle's parts - outputs, losses, every gradient; then the Trainer takes steps on
+    its three-tensor batch."""
+    from oracle import cdvae_oracle as CO
+    from vae_npvc_b200.model.cdvae import Model
+    arch, sd, (xs, y) = _cdvae_small()
+    m = Model(arch)
+    assert list(m.state_dict().keys()) == list(sd.keys())
+    m.load_state_dict({k: v.clone() for k, v in sd.items()})
+    m.train()
+    outs, loss, losses = m(xs + [y])
+    loss.backward()
+    po = O.params_from_state_dict(sd)
+    oouts, oloss, olosses, _ = CO.cdvae_forward(po, arch, xs, y)
+    oloss.backward()
+    for a, b in zip(outs, oouts):
+        assert a.shape == b.shape and rel_err(a, b) < TOL
+    assert set(losses) == set(olosses)
+    for k, v in olosses.items():
+        assert abs(losses[k] - v) <= TOL * max(1.0, abs(v)), k
+    n = 0
+    for name, p in m.named_parameters():
+        if po[name].grad is not None:
+            assert rel_err(p.grad, po[name].grad) < 5 * TOL, name
+            n += 1
+    assert n > 100
+    import vae_npvc_b200.trainer.basic as TB
+    monkeypatch.setattr(TB, 'Pm', prims_ref)
+    cfg = dict(arch, device='cpu', cuda_graph=False, precision='fp32', learning_rate=1e-3, max_grad_norm=10)
+    tr = TB.Trainer(cfg)
+    tr.model.load_state_dict(sd)
+    it, d1 = tr.train_step(xs + [y], 0)
+    assert abs(d1['Total'] - olosses['Total']) <= TOL * abs(olosses['Total'])
+    for _ in range(3):
+        it, d2 = tr.train_step(xs + [y], it)
+    assert it == 4 and d2['Total'] < d1['Total']
+
+
 def test_weight_bank_segments_equal_whole(cpu_prims):
     """bank.py segments: materialising / back-propagating the encoder and the decoder layers by separate calls
     (the trainer issues the decoder's on a side stream) gives the same operand planes and (dv, dg) as one call."""

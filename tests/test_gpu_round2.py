@@ -227,3 +227,100 @@ def test_small_model_two_plane_mode(golden_meta, name):
                 assert rel_err(params[key[5:]].grad, gv) < 3e-4, (key, rel_err(params[key[5:]].grad, gv))
     finally:
         Fn.set_precision(old)
+
+
+def test_aishell3_shape_matches_oracle(fp32_mode):
+    """BASELINE configs[3] / egs/aishell3/vc2/conf/train_pytorch_vqvae.yaml:30-38,53-54: 160-mel, skip 256, codebook
+    128 x 128, jitter_p 0.12 (pinned source table, as the reference's np.random stream cannot be reproduced on a GPU)."""
+    arch = synth.arch_config(X=160, C=512, D=128, K=128, Y=128, S=256, y_num=218, stacks=10, use_ema=False, jitter_p=0.12)
+    B, T = 4, 128
+    sd = synth.synthetic_state_dict(arch, 777)
+    x, y = synth.synthetic_batch(arch, B, T, 777)
+    src = O.jitter_sources(T, 0.12, np.random.RandomState(7))
+    m = _model(arch, sd).train()
+    m.jitter.sources = lambda length: np.asarray(src)
+    xhat, loss, losses = m([x.cuda(), y.cuda()])
+    loss.backward()
+    po = O.params_from_state_dict(sd)
+    oxhat, oloss, olosses, oidx = O.model_forward(po, arch, x, y, True, src)
+    oloss.backward()
+    assert rel_err(xhat, oxhat) < 5e-5
+    for k, v in olosses.items():
+        assert abs(losses[k] - v) <= 5e-5 * max(1.0, abs(v)), (k, losses[k], v)
+    worst = max(rel_err(p.grad, po[n].grad) for n, p in m.named_parameters() if po[n].grad is not None)
+    assert worst < 5e-3, worst                                 # LeakyReLU-kink floor of full-width layers (make_golden.py)
+    with torch.no_grad():
+        assert torch.equal(m.encode(x.cuda()).cpu(), O.model_encode(O.params_from_state_dict(sd, requires_grad=False), arch, x))
+
+
+def test_device_jitter_draws_distribution_and_graph(fp32_mode):
+    """layers_vq.py:353-379 on the device: src[t] in {t-1, t, t+1}, boundaries clamp inwards, a frame is replaced with
+    probability 1 - p (the reference's inverted flag), left / right equally likely, and every call draws afresh."""
+    from vae_npvc_b200 import prims as Pm
+    T, p = 4096, 0.12
+    state = torch.tensor([12345, 0], dtype=torch.int64, device='cuda')
+    a = Pm.jitter_sources(T, p, state)
+    b = Pm.jitter_sources(T, p, state)
+    assert int(state[1]) == 2 and not torch.equal(a, b)
+    t = torch.arange(T, device='cuda')
+    for s in (a, b):
+        d = s - t
+        assert int(d.abs().max()) <= 1 and int(s.min()) >= 0 and int(s.max()) < T
+        rep = (d != 0).float().mean().item()
+        assert abs(rep - (1 - p)) < 0.03, rep
+        right = (d[1:-1] == 1).float().sum().item() / max(1.0, (d[1:-1] != 0).float().sum().item())
+        assert abs(right - 0.5) < 0.05, right
+        assert int(s[0]) in (0, 1) and int(s[-1]) in (T - 2, T - 1)
+    # the Trainer keeps the captured graph with jitter on and draws a new table on every replay
+    from vae_npvc_b200.trainer.basic import Trainer
+    arch = synth.small_config(jitter_p=0.3)
+    cfg = dict(arch, model_type='vae_npvc_b200.model.vqvae', precision='fp32', cuda_graph=True, graph_warmup=2)
+    tr = Trainer(cfg)
+    tr.model.load_state_dict(synth.synthetic_state_dict(arch, 777))
+    x, y = synth.synthetic_batch(arch, 3, 20, 777)
+    it, seen = 0, []
+    for i in range(5):
+        it, detail = tr.train_step([x, y], it)
+        seen.append(int(tr.model.jitter._dev_state[1]))
+    assert tr.last_step_on_graph and seen == [1, 2, 3, 4, 5]
+
+
+def test_cdvae_shape_on_gpu_matches_oracle_parts(fp32_mode):
+    """BASELINE configs[2]: 513-dim spectrum + 40-dim MCC through the same kernels (channel pitch 520 / 40), two blocks
+    per stack to keep the CPU oracle short."""
+    from oracle import cdvae_oracle as CO
+    from vae_npvc_b200.model.cdvae import Model
+    arch = synth.cdvae_config(stacks=2)
+    sd = synth.cdvae_state_dict(arch, 777)
+    xs, y = synth.cdvae_batch(arch, 2, 128, 777)
+    m = Model(arch)
+    m.load_state_dict({k: v.clone() for k, v in sd.items()})
+    m = m.cuda().train()
+    outs, loss, losses = m([t.cuda() for t in xs] + [y.cuda()])
+    loss.backward()
+    po = O.params_from_state_dict(sd)
+    oouts, oloss, olosses, _ = CO.cdvae_forward(po, arch, xs, y)
+    oloss.backward()
+    for a, b in zip(outs, oouts):
+        assert rel_err(a, b) < 5e-5
+    for k, v in olosses.items():
+        assert abs(losses[k] - v) <= 5e-5 * max(1.0, abs(v)), (k, losses[k], v)
+    worst = max(rel_err(p.grad, po[n].grad) for n, p in m.named_parameters() if po[n].grad is not None)
+    assert worst < 5e-3, worst
+
+
+def test_decoder_only_conversion_batch(fp32_mode):
+    """BASELINE configs[4]: Model.decode((ids (B,T) int64, speaker ids)) -> (B,X,T), the decoder-only batched conversion
+    (vqvae.py:55-60), at T = 512."""
+    arch = synth.arch_config(stacks=3)
+    sd = synth.synthetic_state_dict(arch, 777)
+    B, T = 3, 512
+    gen = torch.Generator().manual_seed(5)
+    ids = torch.randint(0, arch['z_num'], (B, T), generator=gen)
+    y = torch.randint(0, arch['y_num'], (B, 1), generator=gen)
+    m = _model(arch, sd).eval()
+    with torch.no_grad():
+        got = m.decode((ids.cuda(), y.cuda()))
+    want = O.model_decode(O.params_from_state_dict(sd, requires_grad=False), arch, ids, y)
+    assert tuple(got.shape) == (B, 80, T) and got.is_contiguous()
+    assert rel_err(got, want) < 2e-5

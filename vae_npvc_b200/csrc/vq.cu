@@ -276,8 +276,44 @@ __global__ void jitter_kernel(const float* __restrict__ in, const int64_t* __res
     out[i] = backward ? (s == t ? in[i] : 0.f) : in[(b * T + s) * D + d];
 }
 
+// Jitter's per-frame draws (layers_vq.py:360-378) made on the device, so that a recipe with jitter_p != 0 stays inside
+// the captured CUDA graph.  state[0] = seed, state[1] = call counter (incremented here): every replay draws afresh.
+// Same distribution as the reference's host loop, including its inverted flag (a frame is replaced with probability
+// 1 - p, layers_vq.py:364): first frame -> t+1, last -> t-1, others t-1 / t+1 with probability 1/2.
+__device__ __forceinline__ uint64_t mix64(uint64_t z) {          // splitmix64 finaliser
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+__global__ void jitter_sources_kernel(int T, float p, int64_t* __restrict__ state, int64_t* __restrict__ src) {
+    pdl_wait();
+    const uint64_t seed = (uint64_t)state[0], call = (uint64_t)state[1];
+    for (int t = threadIdx.x; t < T; t += blockDim.x) {
+        const uint64_t h = mix64(mix64(seed ^ (call * 0xD1B54A32D192ED03ull)) + (uint64_t)t);
+        const float u1 = (float)(h >> 40) * (1.0f / 16777216.0f);            // [0, 1)
+        const bool replace = u1 >= p;                                          // probability 1 - p (reference behaviour)
+        int s = t;
+        if (replace && T > 1) {
+            if (t == 0) s = 1;
+            else if (t == T - 1) s = T - 2;
+            else s = t + (((h >> 8) & 1) ? 1 : -1);
+        }
+        src[t] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) state[1] = (int64_t)(call + 1);
+}
+
 }  // namespace vnb
 using namespace vnb;
+
+extern "C" int vnb_jitter_sources(int T, float p, int64_t* state, int64_t* src, void* stream) {
+    VNB_REQUIRE(state && src && T > 0 && p >= 0.f && p <= 1.f, "jitter_sources: bad arguments");
+    vnb::launch_k(jitter_sources_kernel, 1, 256, 0, (cudaStream_t)stream, T, p, state, src);
+    VNB_LAUNCH_CHECK("jitter_sources");
+    return VNB_OK;
+}
 
 extern "C" int vnb_vq_prep_codebook(float* E, int K, int D, int normalize, int inplace_renorm, float* e_hat,
                                     void* e_planes, float* e_sq, void* stream) {

@@ -282,6 +282,17 @@ class Jitter(nn.Module):
     def __init__(self, probability=0.12):
         super(Jitter, self).__init__()
         self._probability = probability
+        # 'host': np.random draws in the reference's order (the module-level default).  'device': the table is drawn
+        # by a kernel from (seed, call counter) - the Trainer switches to it so that the step stays inside its CUDA
+        # graph; same distribution, different stream.
+        self.draws = 'host'
+        self._dev_state = None
+
+    def device_sources(self, length, device):
+        if self._dev_state is None or self._dev_state.device != device:
+            seed = int(np.random.randint(0, 2 ** 31 - 1))          # derived from the stream the reference would use
+            self._dev_state = torch.tensor([seed, 0], dtype=torch.int64, device=device)
+        return Pm.jitter_sources(length, self._probability, self._dev_state)
 
     def sources(self, length):
         p = self._probability
@@ -300,6 +311,8 @@ class Jitter(nn.Module):
     def forward(self, quantized, src=None):
         if self._probability == 0.0 or not self.training:
             return quantized
+        if src is None and self.draws == 'device' and 'sources' not in self.__dict__:
+            return Fn.JitterFn.apply(quantized, self.device_sources(quantized.size(2), quantized.device))
         if src is None:
             src = self.sources(quantized.size(2))
         src_t = torch.as_tensor(np.asarray(src), dtype=torch.int64).to(quantized.device, non_blocking=True)

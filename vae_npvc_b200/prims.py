@@ -458,6 +458,13 @@ def jitter_fwd(x, src):
     return out
 
 
+def jitter_sources(T, p, state):
+    """Device-side draws of the jitter source table; ``state`` int64[2] = (seed, call counter)."""
+    src = torch.empty((T,), dtype=torch.int64, device=state.device)
+    _C.call('jitter_sources', T, float(p), state, src)
+    return src
+
+
 def jitter_bwd(dout, src):
     B, D, T = dout.shape
     din = cl_empty(B, D, T, dout.device)

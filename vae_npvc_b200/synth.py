@@ -124,3 +124,57 @@ def synthetic_batch(arch, B, T, seed=777):
     x = torch.randn(B, arch['encoder']['in_channels'][0], T, generator=gen)
     y = torch.randint(0, arch['y_num'], (B, 1), generator=gen)
     return x, y
+
+
+def cdvae_config(Xa=513, Xb=40, C=512, D=128, K=512, Y=128, S=128, y_num=117, stacks=10, embed_norm=True, beta=0.01):
+    """BASELINE.json configs[2]: 513-dim WORLD spectrum + 40-dim MCC encoders / decoders over one shared latent
+    (vae_npvc_b200/model/cdvae.py).  Each domain is a single-stage Encoder / Decoder of the VCC2020 recipe's shape."""
+    doms = {}
+    for name, X in (('sp', Xa), ('mcc', Xb)):
+        a = arch_config(X=X, C=C, D=D, K=K, Y=Y, S=S, y_num=y_num, stacks=stacks)
+        doms[name] = {'encoder': a['encoder'], 'decoder': a['decoder']}
+    return {'model_type': 'vae_npvc_b200.model.cdvae', 'domains': doms, 'y_dim': Y, 'y_num': y_num, 'z_dim': D, 'z_num': K,
+            'embed_norm': embed_norm, 'beta': beta}
+
+
+def cdvae_state_dict(arch, seed=777):
+    """Seeded weights keyed like cdvae.Model.state_dict()."""
+    sd = {}
+    for i, (name, dom) in enumerate(arch['domains'].items()):
+        single = dict(arch, encoder=dom['encoder'], decoder=dom['decoder'], use_ema=False)
+        part = synthetic_state_dict(single, seed + 31 * i)
+        for k, v in part.items():
+            if k.startswith('encoder.'):
+                sd['encoders.%s.%s' % (name, k[len('encoder.'):])] = v
+            elif k.startswith('decoder.'):
+                sd['decoders.%s.%s' % (name, k[len('decoder.'):])] = v
+            elif i == 0:
+                sd[k] = v                                   # quantizer.embeddings, embeds._embedding.weight
+    # nn.Module order: encoders.*, decoders.*, quantizer, embeds
+    order = ([k for k in sd if k.startswith('encoders.')] + [k for k in sd if k.startswith('decoders.')]
+             + [k for k in sd if k.startswith('quantizer.')] + [k for k in sd if k.startswith('embeds.')])
+    return {k: sd[k] for k in order}
+
+
+def cdvae_batch(arch, B, T, seed=777):
+    gen = torch.Generator().manual_seed(seed)
+    xs = [torch.randn(B, dom['encoder']['in_channels'][0], T, generator=gen) for dom in arch['domains'].values()]
+    y = torch.randint(0, arch['y_num'], (B, 1), generator=gen)
+    return xs, y
+
+
+def conv_macs_per_frame(enc, dec, T):
+    """Algorithmic conv multiply-accumulates per frame of one Encoder and one Decoder pass (the
+    time-invariant conditioning conv counted once per utterance, i.e. / T per frame)."""
+    e = 0
+    for cin, cout, st in zip(enc['in_channels'], enc['out_channels'], enc['stacks']):
+        e += cin * cout * enc.get('kernel_size', 3)
+        e += st * enc.get('stack_layers', 2) * cout * cout * enc.get('stack_kernel_size', 3) + st * cout * cout
+    e += enc['out_channels'][-1] * enc['z_channels']
+    d = 0
+    Y, S = dec['cond_channels'], dec['skip_channels']
+    for cin, cout, st in zip(dec['in_channels'], dec['out_channels'], dec['stacks']):
+        d += cin * cout * dec.get('kernel_size', 5)
+        d += st * (cout * 2 * cout * dec.get('stack_kernel_size', 3) + cout * (cout + S)) + st * Y * 2 * cout / T
+    d += S * S + S * dec['final_channels']
+    return e, d

@@ -17,7 +17,7 @@ B200-native differences (all behind the same API):
 
 New optional config keys (defaults keep the reference behaviour): ``cuda_graph`` (True),
 ``graph_warmup`` (3), ``precision`` ('bf16' | 'bf16x2' | 'fp32'), ``device`` ('cuda'), ``wgrad_stream`` (True),
-``bank_overlap`` (True), ``sparse_grad_zero`` (True).
+``bank_overlap`` (True), ``sparse_grad_zero`` (True), ``jitter_draws`` ('device' on CUDA | 'host').
 """
 import contextlib
 from importlib import import_module
@@ -151,6 +151,11 @@ class Trainer(object):
         self.optimizer.step_size, self.optimizer.gamma = self._step_size, self._gamma
         self.iteration = 0
         self.model.train()
+        # Jitter (layers_vq.py:353-379) draws on the host in the reference; 'device' (default here) draws the same
+        # distribution in a kernel so that recipes with jitter_p != 0 (AISHELL-3) keep the captured graph
+        jit = getattr(self.model, 'jitter', None)
+        if jit is not None and hasattr(jit, 'draws'):
+            jit.draws = str(config.get('jitter_draws', 'device' if self.device.type == 'cuda' else 'host'))
         # bucketed all-reduce: trigger name (model/vqvae.py set_grad_ready_callback) -> slice of the flat buffers
         self._comm = torch.cuda.Stream(device=self.device) if self._side_wanted() else None
         self._buckets = self._plan_buckets()
@@ -304,7 +309,7 @@ class Trainer(object):
             dist.all_reduce(self._flat_g[lo:hi])
 
     # ---- one optimisation step on device-resident inputs -----------------------------------------
-    def _step_body(self, x, y, jitter_src=None):
+    def _step_body(self, *inputs, jitter_src=None):
         """zero_grad -> forward -> backward -> [all-reduce] -> clip + Adam + StepLR
         (trainer/basic.py:57-72).  Returns (loss-detail keys, stacked 0-d device scalars)."""
         if self._zero_idx is not None:
@@ -345,7 +350,7 @@ class Trainer(object):
                 _model_mod.set_grad_ready_callback(self._grad_ready)                 # hooks registered during forward
             elif split and dist is None:
                 _model_mod.set_grad_ready_callback(self._decoder_done)
-            output, loss, detail = self.model([x, y])
+            output, loss, detail = self.model(list(inputs))
             for sidx in range(len(self.bank.segments)):
                 self.bank.wait_ready(sidx)          # joins the side stream even if a segment was never used
             loss.backward()
@@ -419,46 +424,46 @@ class Trainer(object):
             self._all_reduce_mean(rng[0], rng[1])
         self._reduced.append(rng)
 
-    def _capture(self, x, y):
+    def _capture(self, *inputs):
         from .. import _C
-        static_x, static_y = x.clone(), y.clone()
+        static = [t.clone() for t in inputs]
         g = torch.cuda.CUDAGraph()
         n0 = _C.launch_count()
         with torch.cuda.graph(g):
-            keys, scal = self._step_body(static_x, static_y)
+            keys, scal = self._step_body(*static)
         self.launches_per_step = int(_C.launch_count() - n0)      # our kernels inside one replay
-        return dict(graph=g, x=static_x, y=static_y, keys=keys, scal=scal)
+        return dict(graph=g, inputs=static, keys=keys, scal=scal)
 
-    def train_step_device(self, x, y):
-        """The step on inputs already resident on the device.  Returns (keys, scalars tensor)
-        without synchronising."""
+    def train_step_device(self, *inputs):
+        """The step on inputs already resident on the device ((x, y) for vqvae.Model; (x_a, x_b, y) for the
+        cross-domain model).  Returns (keys, scalars tensor) without synchronising."""
         jit = getattr(self.model, 'jitter', None)
-        needs_host_draws = jit is not None and jit._probability != 0.0
+        needs_host_draws = (jit is not None and jit._probability != 0.0
+                            and (getattr(jit, 'draws', 'host') != 'device' or 'sources' in jit.__dict__))
         q = getattr(self.model, 'quantizer', None)
         # an EMA codebook initialises itself from the first training batch (layers_vq.py:192-201): that step must
         # run eagerly, a captured graph would repeat the initialisation on every replay (and .item() cannot be
         # captured) - resolved here, on the host, before any capture
         needs_init = q is not None and hasattr(q, '_is_init') and not q._is_init()
         if (self.use_graph and not needs_host_draws and not needs_init and self._eager_steps >= self.graph_warmup):
-            key = (tuple(x.shape), tuple(y.shape))
+            key = tuple(tuple(t.shape) for t in inputs)
             ent = self._graphs.get(key)
             if ent is None:
                 torch.cuda.synchronize()
-                ent = self._capture(x, y)
+                ent = self._capture(*inputs)
                 self._graphs[key] = ent
-            ent['x'].copy_(x, non_blocking=True)
-            ent['y'].copy_(y, non_blocking=True)
+            for dst, src in zip(ent['inputs'], inputs):
+                dst.copy_(src, non_blocking=True)
             ent['graph'].replay()
             self.last_step_on_graph = True
             return ent['keys'], ent['scal']
         self._eager_steps += 1
         self.last_step_on_graph = False
-        return self._step_body(x, y)
+        return self._step_body(*inputs)
 
     def train_step(self, input, iteration=None):
         assert self.model.training
-        x, y = [t.to(self.device, non_blocking=True) for t in input]
-        keys, scal = self.train_step_device(x, y)
+        keys, scal = self.train_step_device(*[t.to(self.device, non_blocking=True) for t in input])
         vals = scal.tolist()                                   # the step's only device->host sync
         loss_detail = dict(zip(keys, vals))
         self.iteration += 1                                    # (reference :74-77, with its inverted
