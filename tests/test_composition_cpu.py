@@ -290,14 +290,12 @@ def test_resume_keeps_decayed_lr_like_torch(cpu_prims, monkeypatch, tmp_path):
     sch = torch.optim.lr_scheduler.StepLR(opt, step_size=3, gamma=0.5)
 
     def torch_step(trn, params, o, s_):
-        off = 0
         g = trn._flat_g.clone()
         total = float(g.pow(2).sum().sqrt())
         coef = min(1.0, 10 / (total + 1e-6))
-        for q in params:
+        for q, off in zip(params, trn._offsets):
             n = q.numel()
             q.grad = (g[off:off + n] * coef).view_as(q).clone()
-            off += n
         o.step()
         s_.step()
 

@@ -36,8 +36,14 @@ class FlatAdam(object):
     """Adam state over flat buffers, serialised in torch.optim.Adam's state_dict layout so that
     reference checkpoints (trainer/basic.py:109-121) load and save unchanged."""
 
-    def __init__(self, params, flat_p, flat_g, lr, betas=(0.5, 0.999), eps=1e-8):
+    def __init__(self, params, flat_p, flat_g, lr, betas=(0.5, 0.999), eps=1e-8, offsets=None):
         self.params = params
+        if offsets is None:
+            offsets, off = [], 0
+            for p in params:
+                offsets.append(off)
+                off += p.numel()
+        self.offsets = list(offsets)        # element offset of every parameter in the flat buffers (16-byte aligned)
         self.flat_p, self.flat_g = flat_p, flat_g
         self.m = torch.zeros_like(flat_p)
         self.v = torch.zeros_like(flat_p)
@@ -66,13 +72,12 @@ class FlatAdam(object):
 
     def state_dict(self):
         step = float(self.state[0].item())
-        st, off = {}, 0
+        st = {}
         for i, p in enumerate(self.params):
-            n = p.numel()
+            n, off = p.numel(), self.offsets[i]
             if step > 0:
                 st[i] = {'step': torch.tensor(step), 'exp_avg': self.m[off:off + n].view_as(p).clone(),
                          'exp_avg_sq': self.v[off:off + n].view_as(p).clone()}
-            off += n
         g = dict(self.param_groups[0])
         # torch.optim.Adam + StepLR save the DECAYED lr in param_groups and the undecayed one as 'initial_lr'
         # (trainer/basic.py:109-115 stores optimizer.state_dict() as is)
@@ -82,15 +87,14 @@ class FlatAdam(object):
         return {'state': st, 'param_groups': [g]}
 
     def load_state_dict(self, sd):
-        off, step = 0, 0.0
+        step = 0.0
         for i, p in enumerate(self.params):
-            n = p.numel()
+            n, off = p.numel(), self.offsets[i]
             s = sd['state'].get(i)
             if s is not None:
                 self.m[off:off + n].copy_(s['exp_avg'].reshape(-1))
                 self.v[off:off + n].copy_(s['exp_avg_sq'].reshape(-1))
                 step = float(s['step'])
-            off += n
         self.state[0] = step
         # Resume semantics of the reference (trainer/basic.py:117-121): the Trainer - and its StepLR - is built
         # BEFORE load_checkpoint; optimizer.load_state_dict then replaces param_groups, so training continues at
@@ -138,7 +142,7 @@ class Trainer(object):
         self._allreduce_kind = str(config.get('allreduce', 'multimem'))      # 'multimem' (NVSwitch, own kernel) | 'nccl'
         self._allreduce_blocks = int(config.get('allreduce_blocks', 0))     # 0 = 16 CTAs at 2 ranks, 8 beyond (measured)
         self._flatten()
-        self.optimizer = FlatAdam(self._params, self._flat_p, self._flat_g, learning_rate)
+        self.optimizer = FlatAdam(self._params, self._flat_p, self._flat_g, learning_rate, offsets=self._offsets)
         # all conv weights materialised / back-propagated through weight-norm by one kernel each per step
         self.bank = WeightBank(self.model, self._flat_p, self._flat_g, Fn.get_precision(), Pm)
         self._zero_idx = self._plan_grad_zero() if bool(config.get('sparse_grad_zero', True)) else None
@@ -187,9 +191,11 @@ class Trainer(object):
         (lower encoder half, codebook, speaker table) is reduced after backward.  {} when the parameter order does
         not allow it (sub-module slices not contiguous)."""
         spans, order, off = {}, [], 0
+        offs = {id(p): o for p, o in zip(self._params, self._offsets)}
         for n, p in self.model.named_parameters():
             if not p.requires_grad:
                 continue
+            off = offs[id(p)]
             parts = n.split('.')
             key = '.'.join(parts[:3]) if parts[0] in ('encoder', 'decoder') else parts[0]
             if key not in spans:
@@ -199,8 +205,8 @@ class Trainer(object):
                 order.append(key)
             elif spans[key][1] != off:
                 return {}                                   # a sub-module's parameters are not contiguous
-            spans[key][1] = off + p.numel()
-            off += p.numel()
+            spans[key][1] = off + (p.numel() + 3) // 4 * 4
+            off = spans[key][1]
         dec = [k for k in order if k.startswith('decoder.layers.')]
         enc = [k for k in order if k.startswith('encoder.encode.')]
         dec_all = [k for k in order if k.startswith('decoder.')]
@@ -244,21 +250,25 @@ class Trainer(object):
 
     # ---- flat parameter / gradient buffers -------------------------------------------------------
     def _flatten(self):
+        """Parameters, gradients (and, in FlatAdam, both moments) as views of flat fp32 buffers.  Every parameter starts
+        on a 16-byte boundary (the kernels read biases / GroupNorm affine / weight rows as float4): a 513-entry bias
+        must not shift everything behind it.  The padding elements stay zero in all four buffers."""
         params = [p for p in self.model.parameters() if p.requires_grad]
-        total = sum(p.numel() for p in params)
-        flat_p = torch.empty(total, dtype=torch.float32, device=self.device)
+        offsets, total = [], 0
+        for p in params:
+            offsets.append(total)
+            total += (p.numel() + 3) // 4 * 4
+        flat_p = torch.zeros(total, dtype=torch.float32, device=self.device)
         flat_g = self._symmetric_grad_buffer(total)
         if flat_g is None:
             flat_g = torch.zeros(total, dtype=torch.float32, device=self.device)
-        off = 0
-        for p in params:
+        for p, off in zip(params, offsets):
             n = p.numel()
             flat_p[off:off + n].copy_(p.data.reshape(-1))
             p.data = flat_p[off:off + n].view_as(p)
             p.grad = flat_g[off:off + n].view_as(p)
-            off += n
-        self._params, self._flat_p, self._flat_g = params, flat_p, flat_g
-        self._grad_len = (total + 3) // 4 * 4 if self._mc is not None else total      # symmetric buffer is padded
+        self._params, self._flat_p, self._flat_g, self._offsets = params, flat_p, flat_g, offsets
+        self._grad_len = total                          # a multiple of 4 by construction
 
     def _symmetric_grad_buffer(self, total):
         """Data parallel on NVSwitch: the flat gradient buffer is allocated in symmetric memory with a multicast
