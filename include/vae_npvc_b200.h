@@ -201,6 +201,13 @@ int vnb_linear_fwd(const float* y, const float* W, const float* bias, const floa
 /* dW[o,i] = sum_b dp[b,o]*y[b,i];  dy[b,i] (+)= sum_o W[o,i]*dp[b,o] */
 int vnb_linear_bwd(const float* dp, const float* y, const float* W, int B, int I, int O, float* dW,
                    float* dy, int accumulate_dy, void* stream);
+/* the conditioning 1x1 convs of ALL gated decoder blocks on the same time-invariant speaker embedding in one launch
+ * (vqvae.py:309-312, layers.py:231).  ptrs: L x 4 int64 DEVICE addresses {W_l (O x I fp32), bias_l | 0, bias2_l | 0,
+ * dW_l | 0}.  fwd: p (L, B, O) = y W_l^T + bias_l + bias2_l.  bwd: dW_l = dp[l]^T y written to ptrs[.][3] (skipped when 0);
+ * dy (B, I) += sum_l dp[l] W_l, accumulated into a ZEROED buffer (NULL: skipped) */
+int vnb_linear_fwd_batch(const float* y, const int64_t* ptrs, int L, int B, int I, int O, float* p, void* stream);
+int vnb_linear_bwd_batch(const float* dp, const float* y, const int64_t* ptrs, int L, int B, int I, int O, float* dy,
+                         void* stream);
 
 /* ---- vector quantiser (layers_vq.py:79-150 VectorQuantizer.forward, :268-323 EMA) */
 /* codebook: normalize!=0 -> E <- E/||E|| IN PLACE (embed_norm, :28-33) then e_hat = E/||E||;

@@ -328,10 +328,12 @@ def gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums=False, out=None):
     out = out or {}
     dgamma, dbeta, S, bsum, csum = _gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums or out.get('csum') is not None
                                                     or out.get('csum2') is not None)
-    res = {'dgamma': dgamma, 'dbeta': dbeta, 'csum': csum, 'dbeta2': dbeta, 'csum2': csum}
+    res = {'dgamma': dgamma, 'dbeta': dbeta, 'csum': csum, 'dbeta2': dbeta, 'csum2': csum, 'bsum': bsum}
     for k, dst in out.items():
         if dst is not None:
             dst.copy_(res[k])
+    if out.get('bsum') is not None:
+        bsum = out['bsum']
     return (None if out.get('dgamma') is not None else dgamma, None if out.get('dbeta') is not None else dbeta, S,
             bsum if want_sums else None, None if out.get('csum') is not None else (csum if want_sums else None))
 
@@ -419,6 +421,21 @@ def linear_bwd(dp, y, W, dy=None, dW_out=None):
 
 
 # ---- vector quantiser ------------------------------------------------------------------------
+def linear_fwd_batch(y, Ws, b1s, b2s):
+    return torch.stack([linear_fwd(y, Ws[l], b1s[l], b2s[l]) for l in range(len(Ws))])
+
+
+def linear_bwd_batch(dp, y, Ws, dWs, want_dy=True):
+    dy = torch.zeros_like(y) if want_dy else None
+    for l in range(len(Ws)):
+        dW, d = linear_bwd(dp[l], y, Ws[l])
+        if dWs[l] is not None:
+            dWs[l].copy_(dW.view_as(dWs[l]))
+        if want_dy:
+            dy += d
+    return dy
+
+
 def vq_prep_codebook(E, normalize, inplace_renorm=True):
     K, D = E.shape
     if normalize:

@@ -326,3 +326,40 @@ def test_decoder_only_conversion_batch(fp32_mode):
     want = O.model_decode(O.params_from_state_dict(sd, requires_grad=False), arch, ids, y)
     assert tuple(got.shape) == (B, 80, T) and got.is_contiguous()
     assert rel_err(got, want) < 2e-5
+
+
+def test_batched_conditioning_linear_kernels(fp32_mode):
+    """vnb_linear_fwd_batch / vnb_linear_bwd_batch (all decoder blocks' conditioning convs in one launch each way)
+    against the per-layer contract."""
+    from vae_npvc_b200 import prims as Pm
+    L, B, I, O = 10, 16, 128, 1024
+    y = g(B, I, seed=1)
+    Ws = [g(O, I, seed=10 + l, scale=0.1) for l in range(L)]
+    b1 = [g(O, seed=30 + l) for l in range(L)]
+    b2 = [g(O, seed=50 + l) if l % 2 else None for l in range(L)]
+    dp = g(L, B, O, seed=3)
+    want_p = R.linear_fwd_batch(y, Ws, b1, b2)
+    cW = [w.cuda() for w in Ws]
+    got_p = Pm.linear_fwd_batch(y.cuda(), cW, [b.cuda() for b in b1], [b.cuda() if b is not None else None for b in b2])
+    assert rel_err(got_p, want_p) < 1e-5
+    rdW = [torch.zeros(O, I) for _ in range(L)]
+    rdW[3] = None
+    want_dy = R.linear_bwd_batch(dp, y, Ws, rdW)
+    cdW = [torch.zeros(O, I, device='cuda') if w is not None else None for w in rdW]
+    got_dy = Pm.linear_bwd_batch(dp.cuda(), y.cuda(), cW, cdW)
+    assert rel_err(got_dy, want_dy) < 1e-5
+    for a, b in zip(cdW, rdW):
+        if b is not None:
+            assert rel_err(a, b) < 1e-5
+    assert Pm.linear_bwd_batch(dp.cuda(), y.cuda(), cW, cdW, want_dy=False) is None
+    # odd sizes: B not a multiple of 16, O not a multiple of 64, I not a multiple of 32
+    L, B, I, O = 3, 5, 24, 100
+    y, dp = g(B, I, seed=4), g(L, B, O, seed=5)
+    Ws = [g(O, I, seed=60 + l) for l in range(L)]
+    rdW = [torch.zeros(O, I) for _ in range(L)]
+    want_dy = R.linear_bwd_batch(dp, y, Ws, rdW)
+    cdW = [torch.zeros(O, I, device='cuda') for _ in range(L)]
+    got_dy = Pm.linear_bwd_batch(dp.cuda(), y.cuda(), [w.cuda() for w in Ws], cdW)
+    assert rel_err(got_dy, want_dy) < 1e-5 and all(rel_err(a, b) < 1e-5 for a, b in zip(cdW, rdW))
+    assert rel_err(Pm.linear_fwd_batch(y.cuda(), [w.cuda() for w in Ws], [None] * L, [None] * L),
+                   R.linear_fwd_batch(y, Ws, [None] * L, [None] * L)) < 1e-5

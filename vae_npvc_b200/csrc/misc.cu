@@ -94,6 +94,82 @@ __global__ void __launch_bounds__(256) linear_bwd_y_kernel(const float* __restri
     if (b0 + ty + 8 < B) atomicAdd(dy + (int64_t)(b0 + ty + 8) * I + i, s1);
 }
 
+// ---- the conditioning path of ALL gated decoder blocks in one launch each way ---------------------------------------
+// Every block applies its own 1x1 conv to the SAME time-invariant speaker embedding (vqvae.py:309-312, layers.py:231):
+// P[l][b][o] = sum_i W_l[o][i] * y[b][i] + bias_l[o] + bias2_l[o].  ptrs: L rows of 4 int64 device addresses
+// {W_l (O x I), bias_l | 0, bias2_l | 0, dW_l | 0}.  One warp per (l, o): the weight row stays in registers for all B samples.
+__global__ void __launch_bounds__(256) linear_fwd_batch_kernel(const float* __restrict__ y, const int64_t* __restrict__ ptrs,
+                                                               int L, int B, int I, int O, float* __restrict__ p) {
+    pdl_wait();
+    const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (w >= (int64_t)L * O) return;
+    const int lane = threadIdx.x & 31;
+    const int l = (int)(w / O), o = (int)(w - (int64_t)l * O);
+    const float* W = reinterpret_cast<const float*>(ptrs[4 * l]) + (int64_t)o * I;
+    const float* b1 = reinterpret_cast<const float*>(ptrs[4 * l + 1]);
+    const float* b2 = reinterpret_cast<const float*>(ptrs[4 * l + 2]);
+    const float bias = (b1 ? b1[o] : 0.f) + (b2 ? b2[o] : 0.f);
+    for (int b = 0; b < B; b++) {
+        float s = 0.f;
+        for (int i = lane; i < I; i += 32) s = fmaf(W[i], y[(int64_t)b * I + i], s);
+        s = warp_sum(s);
+        if (lane == 0) p[((int64_t)l * B + b) * O + o] = s + bias;
+    }
+}
+
+// backward of the above, both halves in ONE launch (block-role split):
+//   blocks [0, nW):  dW_l[o][i] = sum_b dp[l][b][o] * y[b][i]       (written, thread per element)
+//   blocks [nW, ..): dy[b][i] += sum_l sum_o W_l[o][i] * dp[l][b][o] (atomicAdd into ZEROED dy; a block owns (l, 64 rows of
+//                    W_l, 32 columns i) and up to 16 samples per pass)
+__global__ void __launch_bounds__(256) linear_bwd_batch_kernel(const float* __restrict__ dp, const float* __restrict__ y,
+                                                               const int64_t* __restrict__ ptrs, int L, int B, int I, int O,
+                                                               int nW, float* __restrict__ dy) {
+    pdl_wait();
+    if ((int)blockIdx.x < nW) {
+        const int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x;
+        if (e >= (int64_t)L * O * I) return;
+        const int l = (int)(e / ((int64_t)O * I));
+        const int64_t r = e - (int64_t)l * O * I;
+        const int o = (int)(r / I), i = (int)(r - (int64_t)o * I);
+        float* dW = reinterpret_cast<float*>(ptrs[4 * l + 3]);
+        if (!dW) return;
+        float s = 0.f;
+        for (int b = 0; b < B; b++) s = fmaf(dp[((int64_t)l * B + b) * O + o], y[(int64_t)b * I + i], s);
+        dW[r] = s;
+        return;
+    }
+    if (!dy) return;
+    __shared__ float dps[16][64];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int it_n = (I + 31) / 32, ot_n = (O + 63) / 64;
+    int blk = (int)blockIdx.x - nW;
+    const int it = blk % it_n;
+    blk /= it_n;
+    const int ot = blk % ot_n, l = blk / ot_n;
+    const int i = it * 32 + tx, o0 = ot * 64;
+    const float* W = reinterpret_cast<const float*>(ptrs[4 * l]);
+    const int on = O - o0 < 64 ? O - o0 : 64;
+    for (int b0 = 0; b0 < B; b0 += 16) {
+        __syncthreads();
+        for (int e = threadIdx.x; e < 16 * 64; e += 256) {
+            const int bb = e >> 6, oo = e & 63;
+            dps[bb][oo] = (b0 + bb < B && oo < on) ? dp[((int64_t)l * B + b0 + bb) * O + o0 + oo] : 0.f;
+        }
+        __syncthreads();
+        if (i < I) {
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll 4
+            for (int oo = 0; oo < on; oo++) {
+                const float w = W[(int64_t)(o0 + oo) * I + i];
+                s0 = fmaf(w, dps[ty][oo], s0);
+                s1 = fmaf(w, dps[ty + 8][oo], s1);
+            }
+            if (b0 + ty < B) atomicAdd(dy + (int64_t)(b0 + ty) * I + i, s0);
+            if (b0 + ty + 8 < B) atomicAdd(dy + (int64_t)(b0 + ty + 8) * I + i, s1);
+        }
+    }
+}
+
 constexpr float LOG_2PI_F = 1.8378770664093453f;
 
 __global__ void __launch_bounds__(256) logloss_fwd_kernel(const float* __restrict__ xhat, const float* __restrict__ x,
@@ -243,6 +319,23 @@ extern "C" int vnb_linear_bwd(const float* dp, const float* y, const float* W, i
         vnb::launch_k(linear_bwd_y_kernel, dim3(ceil_div(I, 32), ceil_div(O, 64), ceil_div(B, 16)), 256, 0, st, dp, W, B, I, O, dy);
         VNB_LAUNCH_CHECK("linear_bwd_y");
     }
+    return VNB_OK;
+}
+
+extern "C" int vnb_linear_fwd_batch(const float* y, const int64_t* ptrs, int L, int B, int I, int O, float* p, void* stream) {
+    VNB_REQUIRE(y && ptrs && p && L > 0 && B > 0 && I > 0 && O > 0, "linear_fwd_batch: bad arguments");
+    vnb::launch_k(linear_fwd_batch_kernel, ceil_div((int64_t)L * O, 8), 256, 0, (cudaStream_t)stream, y, ptrs, L, B, I, O, p);
+    VNB_LAUNCH_CHECK("linear_fwd_batch");
+    return VNB_OK;
+}
+
+extern "C" int vnb_linear_bwd_batch(const float* dp, const float* y, const int64_t* ptrs, int L, int B, int I, int O,
+                                    float* dy, void* stream) {
+    VNB_REQUIRE(dp && y && ptrs && L > 0 && B > 0 && I > 0 && O > 0, "linear_bwd_batch: bad arguments");
+    const int nW = ceil_div((int64_t)L * O * I, 256);
+    const int nY = dy ? L * ceil_div(O, 64) * ceil_div(I, 32) : 0;
+    vnb::launch_k(linear_bwd_batch_kernel, nW + nY, 256, 0, (cudaStream_t)stream, dp, y, ptrs, L, B, I, O, nW, dy);
+    VNB_LAUNCH_CHECK("linear_bwd_batch");
     return VNB_OK;
 }
 

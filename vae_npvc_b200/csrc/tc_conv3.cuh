@@ -418,7 +418,22 @@ static int conv_fwd_tc3(const void* in, int P, int B, int Cin, int T, const void
         }
     }
     if (best.cost == INT64_MAX) return 1;
-    if (mode == 1 && P == 1 && v2_cost < best.cost) return 1;
+    if (mode == 1) {
+        // Measured on B200 at 16 x 128 frames (profiles/r02b_gemm_sweep_timelines.txt): the k-loop is bound by one SM's
+        // L2 intake (~74 B/cycle) for every variant.  The pair halves the weight intake (441 -> 367 cycles per chunk at
+        // BN = 128) but pays ~2000 cycles of cluster launch + 2-CTA TMEM allocation, a wash at this size; all planes per
+        // stage wins where the tile grid fills the chip WITHOUT split-K (decoder conv_in forward, P = 2: 24.0 -> 21.3 us,
+        // P = 3: 41.6 -> 32.6 us; res/skip P = 3: 17.0 -> 14.3 us) and loses to the round-1 kernel's cluster split-K
+        // where it does not (N = 512: 17.4 vs 20.3 us).  Policy: single-CTA BN = 128 with every plane per stage for the
+        // multi-plane modes when >= 100 tiles exist; everything else stays on the round-1 kernel.
+        (void)v2_cost;
+        if (P == 1 || force_bn || force_cta2 >= 0) { if (P == 1 && !force_bn && force_cta2 < 0) return 1; }
+        if (!force_bn && force_cta2 < 0) {
+            ConvTc3Plan pl;
+            if (mt * ceil_div(Cout, 128) < 100 || Cout <= 64 || !conv3_plan_one(128, 0, P, Cin, Cout, taps, mt, &pl)) return 1;
+            best = pl;
+        }
+    }
     if (force_st >= 2 && force_st < best.stages) best.stages = force_st;
     ConvTc3Args a{B, Cin, Cout, T, taps, dil, P, (int)mt, 1, 2, bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups,
                   option(VNB_OPT_TC_DBG)};

@@ -332,10 +332,15 @@ class DecBlockFn(Function):
         S = v_rs.shape[0] - C
         xpl = _input_planes(x, P)
         Win = _weights(v_in, g_in, True, P, need_wb=ctx.needs_input_grad[0])
-        has_cond = v_c is not None and cond is not None
+        # cond_slot (box['cond_slot'] = (l, shared, is_first)): ``cond`` is CondAllFn's (L, B, 2C) table of per-utterance
+        # conditioning biases of ALL blocks (both conv biases folded in); this block uses row l
+        cond_slot = box.get('cond_slot') if box is not None else None
+        has_cond = v_c is not None and cond is not None and cond_slot is None
         bcast = has_cond and cond.dim() == 2
         cpl = wc32 = wc_wb = None
-        if has_cond and bcast:
+        if cond_slot is not None:
+            a, mean, rstd = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, cond[cond_slot[0]], 2 * C, gn_groups=2)
+        elif has_cond and bcast:
             cond = cond.contiguous()
             Wc = _weights(v_c, g_c, False, P, need_wf=False, need_wb=False, need_w32=True)
             wc32 = Wc.w32.view(2 * C, -1)
@@ -365,6 +370,7 @@ class DecBlockFn(Function):
             box['id'] = xopl
         ctx.save_for_backward(cond if has_cond else None, a, mean, rstd, gamma, beta, v_in, g_in, v_c, g_c, v_rs, g_rs,
                               b_in, b_c, b_rs)
+        ctx.cond_slot = cond_slot
         ctx.xpl, ctx.gpl, ctx.cpl = xpl, gpl, cpl
         ctx.win_wb, ctx.wrs_wb, ctx.wc_wb, ctx.wc32 = Win.wb, Wrs.wb, wc_wb, wc32
         ctx.cfg = (P, dil, B, C, S, T, Win.taps, has_cond, bcast)
@@ -388,8 +394,12 @@ class DecBlockFn(Function):
         dg = Pm.conv_fwd(drpl, ctx.wrs_wb, 1, 1, C)
         dv_rs, dg_rs = _wgrad(drpl, ctx.gpl, 1, 1, False, v_rs, g_rs)
         R = Pm.gate_bwd_rows(dg, a, mean, rstd, gamma, beta, P)
+        cond_slot = ctx.cond_slot
+        any_cond = has_cond or (cond_slot is not None and b_c is not None)
         slots = {'dgamma': _slot(gamma), 'dbeta': _slot(beta), 'csum': _slot(b_in),
-                 'csum2': _slot(b_c) if has_cond else None}          # both biases add to the GN input
+                 'csum2': _slot(b_c) if any_cond else None}          # both biases add to the GN input
+        if cond_slot is not None:
+            slots['bsum'] = cond_slot[1]['dP'][cond_slot[0]]          # d(cond bias) of this block -> CondAllFn's table
         dgamma, dbeta, Ssum, bsum, csum = Pm.gn_bwd_finalize(R, gamma, rstd, T, 2, True, slots)
         dcond = dv_c = dg_c = db_c = None
         fk_lin = None
@@ -405,6 +415,11 @@ class DecBlockFn(Function):
         dapl = Pm.gate_bwd_apply(dg, a, mean, rstd, gamma, beta, Ssum, P)
         dx = Pm.conv_fwd(dapl, ctx.win_wb, taps, dil, C, None, 0, dxo) if ctx.needs_input_grad[0] else None
         dv_in, dg_in = _wgrad(dapl, ctx.xpl, taps, dil, True, v_in, g_in)
+        if cond_slot is not None:
+            if b_c is not None and slots['csum2'] is None:
+                db_c = (csum if csum is not None else b_in.grad).clone()
+            # the whole table of gradients is handed to autograd once, by the block whose backward runs last
+            dcond = cond_slot[1]['dP'] if cond_slot[2] else None
         if has_cond:
             if slots['csum2'] is None:
                 db_c = (csum if csum is not None else b_in.grad).clone()
@@ -420,10 +435,70 @@ class DecBlockFn(Function):
                 dv_rs, dg_rs, db_rs)
 
 
-def dec_block(x, cond, params, skip_acc=None, dil=1, P=None):
+class CondAllFn(Function):
+    """The 1x1 conditioning convs of ALL gated decoder blocks on the same time-invariant speaker embedding
+    (vqvae.py:309-312 feeds c.repeat(1,1,T) to every block; layers.py:231) in ONE launch:
+        p[l] = conv_cond_l(c) + b_cond_l + b_in_l                       (L, B, 2C)
+    and, in backward, ONE launch for every dW_l and dc = sum_l W_l^T dp_l (30 launches and 9 gradient adds per step
+    before).  params = L x (v_c, g_c, b_c, b_in); the bias gradients are produced by the blocks (they are the channel
+    sums of the GroupNorm input gradient), so they return None here.  ``shared['dP']``: the (L, B, 2C) buffer the
+    blocks' backward write their rows into."""
+
+    @staticmethod
+    def forward(ctx, cond, shared, P, *params):
+        cond = cond.contiguous()
+        L = len(params) // 4
+        Ws, b1, b2 = [], [], []
+        for l in range(L):
+            v_c, g_c, b_c, b_in = params[4 * l:4 * l + 4]
+            W = _weights(v_c, g_c, False, P, need_wf=False, need_wb=False, need_w32=True)
+            Ws.append(W.w32.view(v_c.shape[0], -1))
+            b1.append(b_c)
+            b2.append(b_in)
+        p_all = Pm.linear_fwd_batch(cond, Ws, b1, b2)
+        shared['dP'] = torch.empty_like(p_all)
+        ctx.save_for_backward(cond, *params)
+        ctx.Ws, ctx.L = Ws, L
+        return p_all
+
+    @staticmethod
+    def backward(ctx, dP):
+        cond, *params = ctx.saved_tensors
+        L = ctx.L
+        bank = _BANK['bank']
+        targets, tmp = [], []
+        for l in range(L):
+            v_c, g_c = params[4 * l], params[4 * l + 1]
+            if not ctx.needs_input_grad[3 + 4 * l]:
+                targets.append(None)
+            elif bank is not None and bank.has(v_c) and _slot(v_c) is not None:
+                targets.append(v_c.grad.view(v_c.shape[0], -1))          # raw dW into the slot (bank.finish_backward)
+            else:
+                t = torch.empty((v_c.shape[0], v_c.shape[1] * v_c.shape[2]), dtype=torch.float32, device=cond.device)
+                targets.append(t)
+                tmp.append(l)
+        dy = Pm.linear_bwd_batch(dP.contiguous(), cond, ctx.Ws, targets, ctx.needs_input_grad[0])
+        grads = [None] * (4 * L)
+        for l in tmp:
+            v_c, g_c = params[4 * l], params[4 * l + 1]
+            grads[4 * l], grads[4 * l + 1] = _dw_to_param_grads(targets[l].view_as(v_c), v_c, g_c)
+        return (dy, None, None) + tuple(grads)
+
+
+def cond_all(cond, params, P=None):
+    """-> (p_all (L, B, 2C), shared) for dec_block(..., cond_slot=(l, shared, is_first))."""
+    shared = {}
+    return CondAllFn.apply(cond, shared, P or get_precision(), *params), shared
+
+
+def dec_block(x, cond, params, skip_acc=None, dil=1, P=None, cond_slot=None):
     """params = (v_in, g_in, b_in, gamma, beta, v_c, g_c, b_c, v_rs, g_rs, b_rs) -> (x', skip_phys);
-    skip_acc / skip_phys are physical (B, T, S) tensors (see DecBlockFn)."""
+    skip_acc / skip_phys are physical (B, T, S) tensors (see DecBlockFn).  ``cond_slot`` = (l, shared, is_first):
+    ``cond`` is cond_all's table and this block takes row l."""
     box = {}
+    if cond_slot is not None:
+        box['cond_slot'] = cond_slot
+        params = tuple(params[:5]) + (None, None, params[7]) + tuple(params[8:])      # conv_cond weights live in CondAllFn
     x_out, skip = DecBlockFn.apply(x, cond, skip_acc, P or get_precision(), dil, box, *params)
     attach_planes(x_out, 'id', box.get('id'))
     return x_out, skip

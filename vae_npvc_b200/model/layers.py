@@ -137,12 +137,14 @@ class DeConv1d_Layernorm_GLU_ResSkip(nn.Module):
         x, skip = self.forward_acc(x, c, None)
         return x, skip.transpose(1, 2)
 
-    def forward_acc(self, x, c, skip_acc):
+    def forward_acc(self, x, c, skip_acc, cond_slot=None):
         """As forward, but the skip output is ADDED IN PLACE into ``skip_acc``, the Decoder's running
-        skip sum in its physical channels-last (B, T, S) form (None: a fresh one is returned)."""
-        if c is not None and c.dim() == 3 and c.size(2) == 1:
+        skip sum in its physical channels-last (B, T, S) form (None: a fresh one is returned).
+        ``cond_slot`` = (l, shared, is_first): ``c`` is the Decoder's table of conditioning biases of all blocks
+        (functional.cond_all) and this block takes row l."""
+        if cond_slot is None and c is not None and c.dim() == 3 and c.size(2) == 1:
             c = c.squeeze(2)
-        return Fn.dec_block(x, c, self._params(), skip_acc, self.dilation)
+        return Fn.dec_block(x, c, self._params(), skip_acc, self.dilation, cond_slot=cond_slot)
 
 
 def log_loss(x, mu, reduction='frame_mean'):

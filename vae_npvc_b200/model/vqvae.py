@@ -16,8 +16,8 @@ import torch.nn as nn
 
 from .. import functional as Fn
 from ..prims import ACT_LRELU, ACT_NONE, ACT_RELU
-from .layers import (Conditions, Conv1d_Layernorm_LRelu_Residual, DeConv1d_Layernorm_GLU_ResSkip, log_loss,
-                     run_conv)
+from .layers import (Conditions, Conv1d_Layernorm_LRelu_Residual, DeConv1d_Layernorm_GLU_ResSkip, conv_params,
+                     log_loss, run_conv)
 from .layers_vq import EMAVectorQuantizer, Jitter, VectorQuantizer, host_value
 
 
@@ -141,6 +141,7 @@ class Decoder(nn.Module, _WeightNormMixin):
                                                           dilation=2 ** j if dilation else 1, dropout=0.0,
                                                           use_causal_conv=use_causal_conv)]
         self.layers = layers
+        self.batch_cond = True            # one launch for the conditioning convs of all blocks (functional.CondAllFn)
         self.final_layer = nn.Sequential(nn.ReLU(), nn.Conv1d(skip_channels, skip_channels, 1), nn.ReLU(),
                                          nn.Conv1d(skip_channels, final_channels, 1))
         if use_weight_norm:
@@ -153,9 +154,23 @@ class Decoder(nn.Module, _WeightNormMixin):
         x, c = input
         c = c[:, :, 0].contiguous()
         skip = None
+        # the conditioning 1x1 convs of all gated blocks see the same (B, Y) embedding: one batched launch for all of
+        # them (and one for their backward) instead of one small linear per block
+        gated = [m for m in self.layers if isinstance(m, DeConv1d_Layernorm_GLU_ResSkip)]
+        table = shared = None
+        if len(gated) > 1 and all(m.conv_cond is not None for m in gated) and self.batch_cond:
+            params = []
+            for m in gated:
+                params += list(conv_params(m.conv_cond)) + [m.conv_in.bias]
+            table, shared = Fn.cond_all(c, params)
+        gi = 0
         for i, layer in enumerate(self.layers):
             if isinstance(layer, DeConv1d_Layernorm_GLU_ResSkip):
-                x, skip = layer.forward_acc(x, c, skip)
+                if table is not None:
+                    x, skip = layer.forward_acc(x, table, skip, cond_slot=(gi, shared, gi == 0))
+                else:
+                    x, skip = layer.forward_acc(x, c, skip)
+                gi += 1
             else:
                 x = run_conv(layer, x)
             x = _mark(x, 'decoder.layers.%d' % i)

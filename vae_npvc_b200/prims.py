@@ -286,7 +286,7 @@ def gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums=False, out=None):
     dgamma = out.get('dgamma') if out.get('dgamma') is not None else _f32((C,), R)
     dbeta = out.get('dbeta') if out.get('dbeta') is not None else _f32((C,), R)
     S = _f32((B, groups, 2), R)
-    bsum = _f32((B, C), R) if want_sums else None
+    bsum = out.get('bsum') if out.get('bsum') is not None else (_f32((B, C), R) if want_sums else None)
     csum = out.get('csum') if out.get('csum') is not None else (_f32((C,), R) if want_sums else None)
     _C.call('gn_bwd_finalize', R, gamma, rstd, B, C, T, groups, dgamma, dbeta, S, bsum, csum, out.get('dbeta2'),
             out.get('csum2'))
@@ -361,6 +361,41 @@ def linear_bwd(dp, y, W, dy=None, dW_out=None):
         dy = _f32((B, I), y)
     _C.call('linear_bwd', dp, y, W, B, I, O, dW, dy, int(acc))
     return dW, dy
+
+
+_PTR_TABLES = {}
+
+
+def _ptr_table(rows, device):
+    """(L, 4) int64 device table of raw addresses (None -> 0), cached per address tuple."""
+    key = tuple(0 if t is None else t.data_ptr() for row in rows for t in row)
+    tab = _PTR_TABLES.get(key)
+    if tab is None or tab.device != torch.device(device):
+        if len(_PTR_TABLES) > 64:
+            _PTR_TABLES.clear()
+        tab = torch.tensor(key, dtype=torch.int64).view(len(rows), 4).to(device)
+        _PTR_TABLES[key] = tab
+    return tab
+
+
+def linear_fwd_batch(y, Ws, b1s, b2s):
+    """p (L,B,O): p[l] = y @ Ws[l].T + b1s[l] + b2s[l] for all L layers in one launch (biases may be None)."""
+    B, I = y.shape
+    L, O = len(Ws), Ws[0].shape[0]
+    tab = _ptr_table([(Ws[l], b1s[l], b2s[l], None) for l in range(L)], y.device)
+    p = _f32((L, B, O), y)
+    _C.call('linear_fwd_batch', y, tab, L, B, I, O, p)
+    return p
+
+
+def linear_bwd_batch(dp, y, Ws, dWs, want_dy=True):
+    """dWs[l] (O,I) <- dp[l].T @ y (written; entries may be None);  -> dy (B,I) = sum_l dp[l] @ Ws[l] (or None)."""
+    B, I = y.shape
+    L, O = len(Ws), Ws[0].shape[0]
+    tab = _ptr_table([(Ws[l], None, None, dWs[l]) for l in range(L)], y.device)
+    dy = torch.zeros((B, I), dtype=torch.float32, device=y.device) if want_dy else None
+    _C.call('linear_bwd_batch', dp, y, tab, L, B, I, O, dy)
+    return dy
 
 
 # --------------------------------------------------------------------------------------------

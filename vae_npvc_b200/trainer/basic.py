@@ -192,12 +192,13 @@ class Trainer(object):
         not allow it (sub-module slices not contiguous)."""
         spans, order, off = {}, [], 0
         offs = {id(p): o for p, o in zip(self._params, self._offsets)}
-        for n, p in self.model.named_parameters():
-            if not p.requires_grad:
-                continue
-            off = offs[id(p)]
+        flat_order = sorted(((offs[id(p)], n, p) for n, p in self.model.named_parameters() if p.requires_grad),
+                            key=lambda t: t[0])
+        for off, n, p in flat_order:
             parts = n.split('.')
             key = '.'.join(parts[:3]) if parts[0] in ('encoder', 'decoder') else parts[0]
+            if '.conv_cond.' in n:
+                key = 'cond'                                # trailing group, reduced after backward
             if key not in spans:
                 if order and spans[order[-1]][1] != off:
                     return {}
@@ -253,11 +254,16 @@ class Trainer(object):
         """Parameters, gradients (and, in FlatAdam, both moments) as views of flat fp32 buffers.  Every parameter starts
         on a 16-byte boundary (the kernels read biases / GroupNorm affine / weight rows as float4): a 513-entry bias
         must not shift everything behind it.  The padding elements stay zero in all four buffers."""
-        params = [p for p in self.model.parameters() if p.requires_grad]
-        offsets, total = [], 0
-        for p in params:
-            offsets.append(total)
-            total += (p.numel() + 3) // 4 * 4
+        named = [(n, p) for n, p in self.model.named_parameters() if p.requires_grad]
+        params = [p for _, p in named]                  # reference order = torch.optim's state indices
+        # flat order: the conditioning convs of the decoder blocks go LAST - their weight gradients are produced by
+        # one batched kernel after the whole decoder has been back-propagated (functional.CondAllFn), so they must
+        # not sit inside the decoder slices that the data-parallel trainer all-reduces while backward still runs
+        order = sorted(range(len(named)), key=lambda i: ('.conv_cond.' in named[i][0], i))
+        offsets, total = [0] * len(named), 0
+        for i in order:
+            offsets[i] = total
+            total += (params[i].numel() + 3) // 4 * 4
         flat_p = torch.zeros(total, dtype=torch.float32, device=self.device)
         flat_g = self._symmetric_grad_buffer(total)
         if flat_g is None:
