@@ -214,7 +214,7 @@ def test_engine_vcc2020_shape_packing_invariance(Pm):
         worst = max(rel_err(x, y) for x, y in zip(a, b))
         assert all(x.shape == y.shape and np.isfinite(x).all() for x, y in zip(a, b))
         if precision == 'fp32':
-            assert agree > 0.999 and worst < 5e-3            # a single near-tie flip moves one frame's features
+            assert agree > 0.999 and worst < 1e-2            # a single near-tie flip moves one frame's features
             assert np.median([rel_err(x, y) for x, y in zip(a, b)]) < 1e-5
         else:
             assert agree > 0.9 and worst < 5e-2

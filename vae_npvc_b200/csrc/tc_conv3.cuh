@@ -427,7 +427,10 @@ static int conv_fwd_tc3(const void* in, int P, int B, int Cin, int T, const void
         // where it does not (N = 512: 17.4 vs 20.3 us).  Policy: single-CTA BN = 128 with every plane per stage for the
         // multi-plane modes when >= 100 tiles exist; everything else stays on the round-1 kernel.
         (void)v2_cost;
-        if (P == 1 || force_bn || force_cta2 >= 0) { if (P == 1 && !force_bn && force_cta2 < 0) return 1; }
+        // P = 3 (the strict fp32-faithful mode) stays on the round-1 kernel as well: it contracts the plane pairs
+        // smallest-terms-first over the WHOLE reduction, which keeps the fp32 accumulation error at 5e-7 (forward
+        // features vs float64); interleaving the pairs per stage measured 2.5e-6
+        if (P != 2 && !force_bn && force_cta2 < 0) return 1;
         if (!force_bn && force_cta2 < 0) {
             ConvTc3Plan pl;
             if (mt * ceil_div(Cout, 128) < 100 || Cout <= 64 || !conv3_plan_one(128, 0, P, Cin, Cout, taps, mt, &pl)) return 1;
