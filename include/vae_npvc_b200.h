@@ -153,6 +153,14 @@ int vnb_enc_out(const float* h, const float* s, const float* mean, const float* 
 /* decoder gate (layers.py:236-242): hn = GN2(a); g = tanh(hn[:C])*sigmoid(hn[C:]) -> planes of g */
 int vnb_dec_gate(const float* a, const float* mean, const float* rstd, const float* gamma,
                  const float* beta, int B, int C, int T, int P, void* g_planes, void* stream);
+/* vnb_enc_out / vnb_dec_gate that FINALISE the conv's fused GroupNorm statistics themselves (gn_sums as accumulated by
+ * vnb_conv_fwd: (B, groups, 2) fp64 sum / sum of squares over C*T resp. C*T per half) and store (mean, rstd) for the
+ * backward pass - one launch less per normalisation; same arithmetic as vnb_gn_finalize (bit-identical values) */
+int vnb_enc_out_s(const float* h, const float* s, const double* gn_sums, float eps, const float* gamma,
+                  const float* beta, int B, int C, int T, int P, float* y, void* y_planes, void* u_planes,
+                  float* mean_out, float* rstd_out, void* stream);
+int vnb_dec_gate_s(const float* a, const double* gn_sums, float eps, const float* gamma, const float* beta, int B,
+                   int C, int T, int P, void* g_planes, float* mean_out, float* rstd_out, void* stream);
 /* decoder residual/skip split (layers.py:246-247, vqvae.py:313): r (B,C+S,T);
  * x_out = r[:C]+x (fp32 + planes);  skip_sum (+)= r[C:]  (first=1 assigns) */
 int vnb_dec_out(const float* r, const float* x, int B, int C, int S, int T, int P,
@@ -170,6 +178,15 @@ int vnb_gate_bwd_rows(const float* dg, const float* a, const float* mean, const 
  * with the approximate functions the forward and the apply kernel use in that mode; P == 3 is vnb_gate_bwd_rows */
 int vnb_gate_bwd_rows_p(const float* dg, const float* a, const float* mean, const float* rstd,
                         const float* gamma, const float* beta, int B, int C, int T, int P, float* R, void* stream);
+/* row sums as vnb_gn_bwd_rows / vnb_gate_bwd_rows_p, ALSO producing the per-(sample, group) sums
+ * S (B, groups, 2) = sum_{c in group} gamma_c * R[b,c,0..1] that vnb_gn_bwd_apply / vnb_gate_bwd_apply read, so that
+ * vnb_gn_bwd_finalize (parameter gradients only) leaves the critical path.  S64: B * groups * 2 + 1 ZEROED doubles
+ * (fp64 accumulators + a ticket slot); 32 must divide the channels per group. */
+int vnb_gn_bwd_rows_s(const float* dn, const float* h, const float* mean, const float* rstd, const float* gamma,
+                      int B, int C, int T, int groups, float* R, double* S64, float* S, void* stream);
+int vnb_gate_bwd_rows_s(const float* dg, const float* a, const float* mean, const float* rstd,
+                        const float* gamma, const float* beta, int B, int C, int T, int P, float* R, double* S64,
+                        float* S, void* stream);
 /* from R: dgamma[c], dbeta[c], S[b,group,0..1] = sum_c gamma*R0, sum_c gamma*R1, and (optional)
  * dpre_bsum[b,c] = sum_t dpre, dpre_csum[c] = sum_{b,t} dpre  (dpre = grad wrt the GN input);
  * dbeta2 / dpre_csum2: optional second copies (two biases that receive the same gradient, written

@@ -130,7 +130,7 @@ def wn_backward(dw, v, g):
 
 # ---- GEMM-shaped -----------------------------------------------------------------------------
 def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False,
-             gn_groups=0, eps=1e-5, lengths=None):
+             gn_groups=0, eps=1e-5, lengths=None, defer_stats=False):
     r = _conv_fwd(x_pl, w_op, taps, dil, Cout, bias, bias_bstride, residual, out, accumulate)
     if not gn_groups:
         return r
@@ -306,7 +306,21 @@ def csid(idx, lengths=None):
 
 
 # ---- backward elementwise --------------------------------------------------------------------
-def gn_bwd_rows(dn, h, mean, rstd, groups):
+def _group_sums(R, gamma, groups):
+    B, C, _ = R.shape
+    gm = gamma.detach().view(1, C)
+    cg = C // groups
+    return torch.stack([(gm * R[:, :, 0]).view(B, groups, cg).sum(2), (gm * R[:, :, 1]).view(B, groups, cg).sum(2)], dim=2)
+
+
+def gn_bwd_rows(dn, h, mean, rstd, groups, gamma=None):
+    if gamma is not None:
+        R = gn_bwd_rows(dn, h, mean, rstd, groups)
+        return R, _group_sums(R, gamma, groups)
+    return _gn_bwd_rows(dn, h, mean, rstd, groups)
+
+
+def _gn_bwd_rows(dn, h, mean, rstd, groups):
     xh = _xhat(h, mean, rstd, groups)
     return torch.stack([dn.sum(2), (dn * xh).sum(2), xh.sum(2)], dim=2)
 
@@ -319,9 +333,10 @@ def _gate_dn(dg, a, mean, rstd, gamma, beta):
     return torch.cat([dg * sg * (1 - th * th), dg * th * sg * (1 - sg)], dim=1), xh
 
 
-def gate_bwd_rows(dg, a, mean, rstd, gamma, beta, P=3):
+def gate_bwd_rows(dg, a, mean, rstd, gamma, beta, P=3, want_S=False):
     dn, xh = _gate_dn(dg, a, mean, rstd, gamma, beta)
-    return torch.stack([dn.sum(2), (dn * xh).sum(2), xh.sum(2)], dim=2)
+    R = torch.stack([dn.sum(2), (dn * xh).sum(2), xh.sum(2)], dim=2)
+    return (R, _group_sums(R, gamma, 2)) if want_S else R
 
 
 def gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums=False, out=None):

@@ -364,3 +364,64 @@ def test_batched_conditioning_linear_kernels(fp32_mode):
     assert rel_err(got_dy, want_dy) < 1e-5 and all(rel_err(a, b) < 1e-5 for a, b in zip(cdW, rdW))
     assert rel_err(Pm.linear_fwd_batch(y.cuda(), [w.cuda() for w in Ws], [None] * L, [None] * L),
                    R.linear_fwd_batch(y, Ws, [None] * L, [None] * L)) < 1e-5
+
+
+@pytest.mark.parametrize('P', [1, 2, 3])
+def test_consumers_finalise_groupnorm_statistics(fp32_mode, P):
+    """vnb_enc_out_s / vnb_dec_gate_s (statistics finalised inside the consumer) == vnb_gn_finalize + vnb_enc_out /
+    vnb_dec_gate, bit for bit, and the stored (mean, rstd) are the finalised ones."""
+    from vae_npvc_b200 import prims as Pm
+    B, C, T = 5, 256, 72
+    x = g(B, C, T, seed=1)
+    w1 = g(C, C, 3, seed=2, scale=0.05)
+    w2 = g(2 * C, C, 3, seed=3, scale=0.05)
+    gamma1, beta1 = g(C, seed=4) + 1.0, g(C, seed=5)
+    gamma2, beta2 = g(2 * C, seed=6) + 1.0, g(2 * C, seed=7)
+    sk = g(B, C, T, seed=8)
+    xpl = Pm.make_planes(x.cuda(), P)[0]
+    W1, W2 = Pm.wn_prepare(w1.cuda(), None, False, P), Pm.wn_prepare(w2.cuda(), None, False, P)
+    for groups, W, Cout in ((1, W1, C), (2, W2, 2 * C)):
+        h_a, mean_a, rstd_a = Pm.conv_fwd(xpl, W.wf, 3, 1, Cout, gn_groups=groups)
+        h_b, mean_b, rstd_b = Pm.conv_fwd(xpl, W.wf, 3, 1, Cout, gn_groups=groups, defer_stats=True)
+        assert hasattr(mean_b, '_vnb_stats') and torch.equal(h_a, h_b)
+        if groups == 1:
+            ya = Pm.enc_out(h_a, sk.cuda(), mean_a, rstd_a, gamma1.cuda(), beta1.cuda(), P)
+            yb = Pm.enc_out(h_b, sk.cuda(), mean_b, rstd_b, gamma1.cuda(), beta1.cuda(), P)
+            assert torch.equal(ya[0], yb[0]) and torch.equal(ya[1].data, yb[1].data) and torch.equal(ya[2].data, yb[2].data)
+        else:
+            ga = Pm.dec_gate(h_a, mean_a, rstd_a, gamma2.cuda(), beta2.cuda(), P)
+            gb = Pm.dec_gate(h_b, mean_b, rstd_b, gamma2.cuda(), beta2.cuda(), P)
+            assert torch.equal(ga.data, gb.data)
+        assert not hasattr(mean_b, '_vnb_stats')
+        assert torch.equal(mean_a, mean_b) and torch.equal(rstd_a, rstd_b)
+
+
+def test_row_sum_kernels_publish_group_sums(fp32_mode):
+    """vnb_gn_bwd_rows_s / vnb_gate_bwd_rows_s: same R as the plain kernels, and S == the group sums
+    vnb_gn_bwd_finalize derives from R (so the apply kernels no longer wait for the finalisation)."""
+    from vae_npvc_b200 import prims as Pm
+    B, C, T = 6, 128, 50
+    dn, h = g(B, C, T, seed=1).cuda(), g(B, C, T, seed=2).cuda()
+    gamma = (g(C, seed=3) + 1.0).cuda()
+    for groups in (1, 2, 4):
+        mean, rstd = Pm.gn_stats(h, groups)
+        R0 = Pm.gn_bwd_rows(dn, h, mean, rstd, groups)
+        R1, S1 = Pm.gn_bwd_rows(dn, h, mean, rstd, groups, gamma)
+        assert S1 is not None and torch.equal(R0, R1)
+        _, _, S0, _, _ = Pm.gn_bwd_finalize(R0, gamma, rstd, T, groups)
+        assert rel_err(S1, S0) < 1e-6
+        want = R.gn_bwd_rows(dn.cpu(), h.cpu(), mean.cpu(), rstd.cpu(), groups, gamma.cpu())[1]
+        assert rel_err(S1, want) < 1e-5
+    Cg = 64
+    a, dg = g(B, 2 * Cg, T, seed=4).cuda(), g(B, Cg, T, seed=5).cuda()
+    gamma2, beta2 = (g(2 * Cg, seed=6) + 1.0).cuda(), g(2 * Cg, seed=7).cuda()
+    mean, rstd = Pm.gn_stats(a, 2)
+    for P in (1, 3):
+        R0 = Pm.gate_bwd_rows(dg, a, mean, rstd, gamma2, beta2, P)
+        R1, S1 = Pm.gate_bwd_rows(dg, a, mean, rstd, gamma2, beta2, P, want_S=True)
+        assert S1 is not None and torch.equal(R0, R1)
+        _, _, S0, _, _ = Pm.gn_bwd_finalize(R0, gamma2, rstd, T, 2)
+        assert rel_err(S1, S0) < 1e-6
+    # shapes whose groups are not multiples of 32 channels fall back (S None)
+    assert Pm.gn_bwd_rows(dn[:, :48].contiguous(), h[:, :48].contiguous(), *Pm.gn_stats(h[:, :48].contiguous(), 1), 1,
+                          gamma[:48].contiguous())[1] is None

@@ -398,22 +398,30 @@ extern "C" int vnb_gn_finalize(const double* gn_sums, int BG, double n, float ep
     return VNB_OK;
 }
 
-extern "C" int vnb_enc_out(const float* h, const float* s, const float* mean, const float* rstd, const float* gamma,
-                           const float* beta, int B, int C, int T, int P, float* y, void* y_planes, void* u_planes,
-                           void* stream) {
-    VNB_REQUIRE(h && mean && rstd && gamma && beta && (y || y_planes || u_planes), "enc_out: null pointer");
+static int enc_out_impl(const float* h, const float* s, const float* mean, const float* rstd, const float* gamma,
+                        const float* beta, int B, int C, int T, int P, float* y, void* y_planes, void* u_planes,
+                        const double* sums, float eps, float* mean_out, float* rstd_out, void* stream) {
+    VNB_REQUIRE(h && (sums ? (mean_out && rstd_out) : (mean && rstd)) && gamma && beta && (y || y_planes || u_planes), "enc_out: null pointer");
     VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P >= 1 && P <= 3), "enc_out: bad shape");
     const int64_t rows = (int64_t)B * T;
     if ((C & 3) == 0 && ew_v2_enabled()) {
         const int g2 = v2_grid(rows, C / 4);
-        if (g2) {
+        if (g2 && (!sums || B <= 4096)) {
             const int Cp = round_up8(C);
-            if (P == 1) vnb::launch_k(enc_out_v2_kernel<1, 2>, g2, V2_THREADS, 0, ST, h, s, mean, rstd, gamma, beta, (int)rows, C, T, Cp, y, (bf16*)y_planes, (bf16*)u_planes);
-            else if (P == 2) vnb::launch_k(enc_out_v2_kernel<2, 2>, g2, V2_THREADS, 0, ST, h, s, mean, rstd, gamma, beta, (int)rows, C, T, Cp, y, (bf16*)y_planes, (bf16*)u_planes);
-            else vnb::launch_k(enc_out_v2_kernel<3, 2>, g2, V2_THREADS, 0, ST, h, s, mean, rstd, gamma, beta, (int)rows, C, T, Cp, y, (bf16*)y_planes, (bf16*)u_planes);
+            const size_t smem = sums ? (size_t)B * 2 * sizeof(float) : 0;
+            const double n = (double)C * (double)T;
+            if (P == 1) vnb::launch_k(enc_out_v2_kernel<1, 2>, g2, V2_THREADS, smem, ST, h, s, mean, rstd, gamma, beta, (int)rows, C, T, Cp, y, (bf16*)y_planes, (bf16*)u_planes, sums, n, eps, mean_out, rstd_out);
+            else if (P == 2) vnb::launch_k(enc_out_v2_kernel<2, 2>, g2, V2_THREADS, smem, ST, h, s, mean, rstd, gamma, beta, (int)rows, C, T, Cp, y, (bf16*)y_planes, (bf16*)u_planes, sums, n, eps, mean_out, rstd_out);
+            else vnb::launch_k(enc_out_v2_kernel<3, 2>, g2, V2_THREADS, smem, ST, h, s, mean, rstd, gamma, beta, (int)rows, C, T, Cp, y, (bf16*)y_planes, (bf16*)u_planes, sums, n, eps, mean_out, rstd_out);
             VNB_LAUNCH_CHECK("enc_out_v2");
             return VNB_OK;
         }
+    }
+    if (sums) {                                   // shapes the fused path does not take: finalise separately
+        vnb::launch_k(gn_finalize_kernel, ceil_div(B, 128), 128, 0, ST, sums, B, (double)C * (double)T, eps, mean_out, rstd_out);
+        VNB_LAUNCH_CHECK("gn_finalize");
+        mean = mean_out;
+        rstd = rstd_out;
     }
     VEC_DISPATCH((C & 3) == 0, enc_out_kernel, rows * C, ST, h, s, mean, rstd, gamma, beta, rows, C, T, round_up8(C), P,
                  y, (bf16*)y_planes, (bf16*)u_planes);
@@ -421,27 +429,60 @@ extern "C" int vnb_enc_out(const float* h, const float* s, const float* mean, co
     return VNB_OK;
 }
 
-extern "C" int vnb_dec_gate(const float* a, const float* mean, const float* rstd, const float* gamma,
-                            const float* beta, int B, int C, int T, int P, void* g_planes, void* stream) {
-    VNB_REQUIRE(a && mean && rstd && gamma && beta && g_planes, "dec_gate: null pointer");
+extern "C" int vnb_enc_out(const float* h, const float* s, const float* mean, const float* rstd, const float* gamma,
+                           const float* beta, int B, int C, int T, int P, float* y, void* y_planes, void* u_planes,
+                           void* stream) {
+    return enc_out_impl(h, s, mean, rstd, gamma, beta, B, C, T, P, y, y_planes, u_planes, nullptr, 0.f, nullptr, nullptr, stream);
+}
+
+extern "C" int vnb_enc_out_s(const float* h, const float* s, const double* gn_sums, float eps, const float* gamma,
+                             const float* beta, int B, int C, int T, int P, float* y, void* y_planes, void* u_planes,
+                             float* mean_out, float* rstd_out, void* stream) {
+    VNB_REQUIRE(gn_sums, "enc_out_s: null statistics");
+    return enc_out_impl(h, s, nullptr, nullptr, gamma, beta, B, C, T, P, y, y_planes, u_planes, gn_sums, eps, mean_out, rstd_out, stream);
+}
+
+static int dec_gate_impl(const float* a, const float* mean, const float* rstd, const float* gamma, const float* beta, int B,
+                         int C, int T, int P, void* g_planes, const double* sums, float eps, float* mean_out, float* rstd_out,
+                         void* stream) {
+    VNB_REQUIRE(a && (sums ? (mean_out && rstd_out) : (mean && rstd)) && gamma && beta && g_planes, "dec_gate: null pointer");
     VNB_REQUIRE(B > 0 && C > 0 && T > 0 && (P >= 1 && P <= 3), "dec_gate: bad shape");
     const int64_t rows = (int64_t)B * T;
     if ((C & 3) == 0 && ew_v2_enabled()) {
         const int g2 = v2_grid(rows, C / 4);
-        if (g2) {
+        if (g2 && (!sums || B <= 2048)) {
             const int Cp = round_up8(C);
-            if (P == 1 && fast_gate_enabled()) vnb::launch_k(dec_gate_v2_kernel<1, 2, true>, g2, V2_THREADS, 0, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes);
-            else if (P == 1) vnb::launch_k(dec_gate_v2_kernel<1, 2, false>, g2, V2_THREADS, 0, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes);
-            else if (P == 2) vnb::launch_k(dec_gate_v2_kernel<2, 2, false>, g2, V2_THREADS, 0, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes);
-            else vnb::launch_k(dec_gate_v2_kernel<3, 2, false>, g2, V2_THREADS, 0, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes);
+            const size_t smem = sums ? (size_t)B * 4 * sizeof(float) : 0;
+            const double n = (double)C * (double)T;
+            if (P == 1 && fast_gate_enabled()) vnb::launch_k(dec_gate_v2_kernel<1, 2, true>, g2, V2_THREADS, smem, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes, sums, n, eps, mean_out, rstd_out);
+            else if (P == 1) vnb::launch_k(dec_gate_v2_kernel<1, 2, false>, g2, V2_THREADS, smem, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes, sums, n, eps, mean_out, rstd_out);
+            else if (P == 2) vnb::launch_k(dec_gate_v2_kernel<2, 2, false>, g2, V2_THREADS, smem, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes, sums, n, eps, mean_out, rstd_out);
+            else vnb::launch_k(dec_gate_v2_kernel<3, 2, false>, g2, V2_THREADS, smem, ST, a, mean, rstd, gamma, beta, (int)rows, C, T, Cp, (bf16*)g_planes, sums, n, eps, mean_out, rstd_out);
             VNB_LAUNCH_CHECK("dec_gate_v2");
             return VNB_OK;
         }
+    }
+    if (sums) {
+        vnb::launch_k(gn_finalize_kernel, ceil_div(2 * B, 128), 128, 0, ST, sums, 2 * B, (double)C * (double)T, eps, mean_out, rstd_out);
+        VNB_LAUNCH_CHECK("gn_finalize");
+        mean = mean_out;
+        rstd = rstd_out;
     }
     VEC_DISPATCH((C & 3) == 0, dec_gate_kernel, rows * C, ST, a, mean, rstd, gamma, beta, rows, C, T, round_up8(C), P,
                  (bf16*)g_planes);
     VNB_LAUNCH_CHECK("dec_gate");
     return VNB_OK;
+}
+
+extern "C" int vnb_dec_gate(const float* a, const float* mean, const float* rstd, const float* gamma,
+                            const float* beta, int B, int C, int T, int P, void* g_planes, void* stream) {
+    return dec_gate_impl(a, mean, rstd, gamma, beta, B, C, T, P, g_planes, nullptr, 0.f, nullptr, nullptr, stream);
+}
+
+extern "C" int vnb_dec_gate_s(const float* a, const double* gn_sums, float eps, const float* gamma, const float* beta, int B,
+                              int C, int T, int P, void* g_planes, float* mean_out, float* rstd_out, void* stream) {
+    VNB_REQUIRE(gn_sums, "dec_gate_s: null statistics");
+    return dec_gate_impl(a, nullptr, nullptr, gamma, beta, B, C, T, P, g_planes, gn_sums, eps, mean_out, rstd_out, stream);
 }
 
 extern "C" int vnb_dec_out(const float* r, const float* x, int B, int C, int S, int T, int P, float* x_out,

@@ -37,13 +37,38 @@ __device__ __forceinline__ float gate_dn(const float* __restrict__ dg, const flo
     return d * th * sg * (1.f - sg);
 }
 
+// Round 2: the row-sum kernels can also produce the per-(sample, group) sums S[b,g,k] = sum_{c in g} gamma_c R[b,c,k]
+// (k = 0, 1) that the apply kernels need, so that gn_bwd_finalize (7 us for a B x groups problem) leaves the critical
+// path: a block's 32 channels lie in one group (host checks 32 | C / groups), each of its two sum warps adds
+// gamma-weighted partials to a ZEROED fp64 accumulator, and the LAST block to finish (ticket counter) publishes the
+// sums as fp32 for the apply kernel.
+__device__ __forceinline__ void publish_group_sums(float t, float gm, bool valid, int k, int slot, double* S64, float* S32,
+                                                   unsigned* counter, int n_slots2) {
+    __shared__ int last_flag;
+    if (k < 2) {
+        float v = valid ? t * gm : 0.f;
+        v = warp_sum(v);
+        if ((threadIdx.x & 31) == 0) atomicAdd(S64 + (size_t)slot * 2 + k, (double)v);
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last_flag = atomicAdd(counter, 1u) == gridDim.x * gridDim.y - 1 ? 1 : 0;
+    __syncthreads();
+    if (last_flag) {
+        __threadfence();
+        for (int i = threadIdx.x; i < n_slots2; i += blockDim.x) S32[i] = (float)__ldcg(S64 + i);
+    }
+}
+
 // R[b,c] = { sum_t dn, sum_t dn*xhat, sum_t xhat }.  grid (ceil(C/32), B), block 32 x 8: a warp reads
 // 32 consecutive channels of one frame, the 8 warps stride over frames, shared-memory reduce.
 template <bool GATE>
 __global__ void __launch_bounds__(256) bwd_rows_kernel(const float* __restrict__ dn, const float* __restrict__ h,
                                                        const float* __restrict__ mean, const float* __restrict__ rstd,
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                       int Cn, int T, int groups, float* __restrict__ R) {
+                                                       int Cn, int T, int groups, float* __restrict__ R,
+                                                       double* __restrict__ S64, float* __restrict__ S32,
+                                                       unsigned* __restrict__ counter) {
     pdl_wait();
     __shared__ float red[3][8][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -86,11 +111,16 @@ __global__ void __launch_bounds__(256) bwd_rows_kernel(const float* __restrict__
     red[1][ty][tx] = s1;
     red[2][ty][tx] = s2;
     __syncthreads();
+    float s = 0.f;
     if (ty < 3 && c < Cn) {
-        float s = 0.f;
 #pragma unroll
         for (int j = 0; j < 8; j++) s += red[ty][j][tx];
         R[((int64_t)b * Cn + c) * 3 + ty] = s;
+    }
+    if (S64) {
+        const int c0 = blockIdx.x * 32;
+        publish_group_sums(s, (c < Cn && ty < 2) ? gamma[c] : 0.f, c < Cn, ty, b * groups + c0 / (Cn / groups), S64, S32, counter,
+                           gridDim.y * groups * 2);
     }
 }
 
@@ -298,8 +328,19 @@ extern "C" int vnb_gn_bwd_rows(const float* dn, const float* h, const float* mea
     VNB_REQUIRE(dn && h && mean && rstd && R && B > 0 && B <= 65535 && C > 0 && T > 0 && groups > 0 && C % groups == 0,
                 "gn_bwd_rows: bad arguments");
     vnb::launch_k(bwd_rows_kernel<false>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dn, h, mean, rstd, nullptr, nullptr,
-                                                                                       C, T, groups, R);
+                                                                                       C, T, groups, R, nullptr, nullptr, nullptr);
     VNB_LAUNCH_CHECK("gn_bwd_rows");
+    return VNB_OK;
+}
+
+extern "C" int vnb_gn_bwd_rows_s(const float* dn, const float* h, const float* mean, const float* rstd, const float* gamma,
+                                 int B, int C, int T, int groups, float* R, double* S64, float* S, void* stream) {
+    VNB_REQUIRE(dn && h && mean && rstd && gamma && R && S64 && S && B > 0 && B <= 65535 && C > 0 && T > 0 && groups > 0 &&
+                    C % groups == 0 && ((C / groups) & 31) == 0, "gn_bwd_rows_s: bad arguments (32 must divide C / groups)");
+    // S64: B * groups * 2 ZEROED doubles followed by one zeroed 8-byte ticket slot
+    vnb::launch_k(bwd_rows_kernel<false>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dn, h, mean, rstd, gamma, nullptr,
+                  C, T, groups, R, S64, S, reinterpret_cast<unsigned*>(S64 + (size_t)B * groups * 2));
+    VNB_LAUNCH_CHECK("gn_bwd_rows_s");
     return VNB_OK;
 }
 
@@ -311,7 +352,8 @@ template <bool FAST>
 __global__ void __launch_bounds__(256) gate_bwd_rows_kernel(const float* __restrict__ dg, const float* __restrict__ a,
                                                             const float* __restrict__ mean, const float* __restrict__ rstd,
                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                            int C, int T, float* __restrict__ R) {
+                                                            int C, int T, float* __restrict__ R, double* __restrict__ S64,
+                                                            float* __restrict__ S32, unsigned* __restrict__ counter) {
     pdl_wait();
     __shared__ float red[6][8][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -345,12 +387,18 @@ __global__ void __launch_bounds__(256) gate_bwd_rows_kernel(const float* __restr
 #pragma unroll
     for (int k = 0; k < 6; k++) red[k][ty][tx] = s[k];
     __syncthreads();
+    float t = 0.f;
+    const int ch = ty < 3 ? c : C + c;
     if (ty < 6 && c < C) {
-        float t = 0.f;
 #pragma unroll
         for (int j = 0; j < 8; j++) t += red[ty][j][tx];
-        const int ch = ty < 3 ? c : C + c;
         R[((int64_t)b * 2 * C + ch) * 3 + (ty % 3)] = t;
+    }
+    if (S64) {
+        // warps 0..2 hold the tanh half (group 0), 3..5 the sigmoid half (group 1); warps 6, 7 only take part in the barrier
+        const int k = ty < 6 ? ty % 3 : 2;
+        publish_group_sums(t, (c < C && ty < 6 && k < 2) ? gamma[ch] : 0.f, c < C && ty < 6, k, b * 2 + (ty >= 3 && ty < 6 ? 1 : 0), S64, S32,
+                           counter, gridDim.y * 4);
     }
 }
 }  // namespace vnb
@@ -362,10 +410,28 @@ extern "C" int vnb_gate_bwd_rows_p(const float* dg, const float* a, const float*
                     (P >= 1 && P <= 3), "gate_bwd_rows: bad arguments");
     // the gate's approximate functions only where the operand planes are bf16 anyway (see ew_v2.cuh)
     if (P == 1 && ew_v2_enabled() && fast_gate_enabled())
-        vnb::launch_k(gate_bwd_rows_kernel<true>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R);
+        vnb::launch_k(gate_bwd_rows_kernel<true>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
+                      nullptr, nullptr, nullptr);
     else
-        vnb::launch_k(gate_bwd_rows_kernel<false>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R);
+        vnb::launch_k(gate_bwd_rows_kernel<false>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
+                      nullptr, nullptr, nullptr);
     VNB_LAUNCH_CHECK("gate_bwd_rows");
+    return VNB_OK;
+}
+
+extern "C" int vnb_gate_bwd_rows_s(const float* dg, const float* a, const float* mean, const float* rstd,
+                                   const float* gamma, const float* beta, int B, int C, int T, int P, float* R, double* S64,
+                                   float* S, void* stream) {
+    VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && R && S64 && S && B > 0 && B <= 65535 && C > 0 && (C & 31) == 0 &&
+                    T > 0 && (P >= 1 && P <= 3), "gate_bwd_rows_s: bad arguments (32 must divide C)");
+    unsigned* counter = reinterpret_cast<unsigned*>(S64 + (size_t)B * 4);
+    if (P == 1 && ew_v2_enabled() && fast_gate_enabled())
+        vnb::launch_k(gate_bwd_rows_kernel<true>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
+                      S64, S, counter);
+    else
+        vnb::launch_k(gate_bwd_rows_kernel<false>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
+                      S64, S, counter);
+    VNB_LAUNCH_CHECK("gate_bwd_rows_s");
     return VNB_OK;
 }
 

@@ -86,6 +86,28 @@ __device__ __forceinline__ float gate_sigmoid(float x) {
     const int rstep = (int)(v2_nthr / (uint32_t)(Cv_));                                 \
     const int r_first = (int)(v2_tid / (uint32_t)(Cv_))
 
+// Round 2: the consumers of a conv's fused GroupNorm statistics finalise them THEMSELVES (one less launch per
+// normalisation on the forward critical path): every CTA turns the fp64 (sum, sum of squares) pairs into (mean, rstd)
+// in shared memory - the arithmetic of gn_finalize_kernel, so the values are bit-identical - and CTA 0 also stores them
+// for the backward pass.
+__device__ __forceinline__ void v2_finalize_stats(const double* __restrict__ sums, int BG, double n, float eps,
+                                                  float* __restrict__ sm, float* __restrict__ sr,
+                                                  float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+    for (int i = threadIdx.x; i < BG; i += blockDim.x) {
+        const double m = sums[2 * i] / n;
+        double var = sums[2 * i + 1] / n - m * m;
+        if (var < 0.0) var = 0.0;
+        const float mf = (float)m, rf = (float)(1.0 / sqrt(var + (double)eps));
+        sm[i] = mf;
+        sr[i] = rf;
+        if (blockIdx.x == 0) {
+            mean_out[i] = mf;
+            rstd_out[i] = rf;
+        }
+    }
+    __syncthreads();
+}
+
 // ---- fp32 activation -> operand planes (identity and/or activated) -------------------------------------------
 template <int P, int U>
 __global__ void __launch_bounds__(V2_THREADS) make_planes_v2_kernel(const float* __restrict__ x, int rows, int C, int Cp,
@@ -121,13 +143,24 @@ __global__ void __launch_bounds__(V2_THREADS) make_planes_v2_kernel(const float*
 // ---- encoder block epilogue: y = GN1(h)*gamma+beta (+ s) -> y fp32, planes(y), planes(lrelu(y)) ---------------
 template <int P, int U>
 __global__ void __launch_bounds__(V2_THREADS) enc_out_v2_kernel(const float* __restrict__ h, const float* __restrict__ s,
-                                                                const float* __restrict__ mean,
-                                                                const float* __restrict__ rstd,
+                                                                const float* __restrict__ mean_in,
+                                                                const float* __restrict__ rstd_in,
                                                                 const float* __restrict__ gamma,
                                                                 const float* __restrict__ beta, int rows, int C, int T,
                                                                 int Cp, float* __restrict__ y, bf16* __restrict__ y_planes,
-                                                                bf16* __restrict__ u_planes) {
+                                                                bf16* __restrict__ u_planes, const double* __restrict__ sums,
+                                                                double n_stat, float eps, float* __restrict__ mean_out,
+                                                                float* __restrict__ rstd_out) {
     pdl_wait();
+    extern __shared__ float v2_stats[];
+    const float* mean = mean_in;
+    const float* rstd = rstd_in;
+    if (sums) {
+        const int BG = rows / T;
+        v2_finalize_stats(sums, BG, n_stat, eps, v2_stats, v2_stats + BG, mean_out, rstd_out);
+        mean = v2_stats;
+        rstd = v2_stats + BG;
+    }
     V2_FRAME(C >> 2);
     const int64_t plane = (int64_t)rows * Cp;
     float gm[4], bt[4];
@@ -166,12 +199,23 @@ __global__ void __launch_bounds__(V2_THREADS) enc_out_v2_kernel(const float* __r
 
 // ---- decoder gate: a (rows, 2C) -> planes of tanh(GN2(a)[:C]) * sigmoid(GN2(a)[C:]) ---------------------------
 template <int P, int U, bool FAST>
-__global__ void __launch_bounds__(V2_THREADS) dec_gate_v2_kernel(const float* __restrict__ a, const float* __restrict__ mean,
-                                                                 const float* __restrict__ rstd,
+__global__ void __launch_bounds__(V2_THREADS) dec_gate_v2_kernel(const float* __restrict__ a, const float* __restrict__ mean_in,
+                                                                 const float* __restrict__ rstd_in,
                                                                  const float* __restrict__ gamma,
                                                                  const float* __restrict__ beta, int rows, int C, int T,
-                                                                 int Cp, bf16* __restrict__ g_planes) {
+                                                                 int Cp, bf16* __restrict__ g_planes,
+                                                                 const double* __restrict__ sums, double n_stat, float eps,
+                                                                 float* __restrict__ mean_out, float* __restrict__ rstd_out) {
     pdl_wait();
+    extern __shared__ float v2_stats[];
+    const float* mean = mean_in;
+    const float* rstd = rstd_in;
+    if (sums) {
+        const int BG = 2 * (rows / T);
+        v2_finalize_stats(sums, BG, n_stat, eps, v2_stats, v2_stats + BG, mean_out, rstd_out);
+        mean = v2_stats;
+        rstd = v2_stats + BG;
+    }
     V2_FRAME(C >> 2);
     const int64_t plane = (int64_t)rows * Cp;
     float g1[4], g2[4], b1[4], b2[4];

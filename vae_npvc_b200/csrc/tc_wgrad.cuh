@@ -37,6 +37,12 @@ struct WgradTcArgs {
     int nstages;
     uint32_t recv_off;
     float* dw;
+    // frames per pipeline stage (128, or 64 when `multi`) and, round 2, `multi`: a stage holds BOTH planes of both
+    // operands of the two-plane mode (P = 2) and the three products hi*hi + hi*mid + mid*hi are issued from it - the
+    // operands are loaded twice instead of three times (the k-loop is bound by the SM's L2 intake, profiles/
+    // r02b_gemm_sweep_timelines.txt).  P = 3 keeps one pass per plane pair: smallest terms first over the whole
+    // reduction is what keeps that mode fp32-faithful.
+    int kt, multi;
 };
 
 template <int BN> struct WgradTcCfg {
@@ -48,6 +54,8 @@ template <int BN> struct WgradTcCfg {
     static constexpr uint32_t STAGING_BYTES = (uint32_t)WG_BM * PITCH * 4;
     static constexpr uint32_t SMEM_BUDGET = 227 * 1024 - 2048;
     static uint32_t recv_bytes(int ks) { return (uint32_t)(ks - 1) * (WG_BM / ks) * PITCH * 4; }
+    // stage bytes: STAGE_BYTES (128 frames, one plane) for the one-pass-per-pair path, 2 planes x 64 frames = the same
+    // number of bytes for the all-planes-per-stage path - every formula below holds for both
     static bool fits(int ks) {
         if (recv_bytes(ks) + 2 * STAGE_BYTES > SMEM_BUDGET) return false;
         return recv_offset(ks) + recv_bytes(ks) + 1024 <= 227 * 1024 - 1024;
@@ -88,11 +96,16 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     const int off = (tap - (a.taps - 1) / 2) * a.dil;
     const int off_a = a.swapped ? off : 0, off_b = a.swapped ? 0 : off;
     const int tap_idx = a.swapped ? a.taps - 1 - tap : tap;
-    const int pairs = n_pairs(a.P);
-    const int tblocks = (a.T + WG_KT - 1) / WG_KT;
+    const int multi = a.multi, kt = a.kt;
+    const int pairs = multi ? 1 : n_pairs(a.P);
+    const int tblocks = (a.T + kt - 1) / kt;
     const int kblocks = a.B * tblocks;
     const int kb0 = (int)((int64_t)kblocks * kr / ks), kb1 = (int)((int64_t)kblocks * (kr + 1) / ks);
     const int nk = pairs * (kb1 - kb0);
+    // bytes of ONE plane of an operand in a stage (kt frames); with `multi` the P planes follow one another
+    const uint32_t box_bytes = (uint32_t)kt * 128u;
+    const uint32_t a_plane = (WG_BM / 64) * box_bytes, b_plane = (BN / 64) * box_bytes;
+    const uint32_t a_all = multi ? (uint32_t)a.P * a_plane : a_plane;
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&map_a);
@@ -126,25 +139,31 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                 const int pa = a.P == 1 ? 0 : c_pair_a[pair_base(a.P) + pr], pb = a.P == 1 ? 0 : c_pair_b[pair_base(a.P) + pr];
                 // the row operand takes the a-plane of the pair when it is dY, the b-plane when it is U (swapped)
                 const int pl_a = a.swapped ? pb : pa, pl_b = a.swapped ? pa : pb;
-                const int t0 = tb * WG_KT;
+                const int t0 = tb * kt;
                 if (i >= STAGES) mbar_wait(&empty_bar[s], ph);
                 uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
-                uint8_t* sb = sa + A_BYTES;
+                uint8_t* sb = sa + a_all;
                 if (elect_one()) {
                     mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-                    if (a.a4d) {
-                        tma_load_4d(sa, &map_a, &full_bar[s], 0, t0 + off_a, m0 / 64, pl_a * a.B + bb);
-                    } else {
+                    const int npl = multi ? a.P : 1;
+                    for (int q = 0; q < npl; q++) {
+                        const int qa = multi ? q : pl_a, qb = multi ? q : pl_b;
+                        uint8_t* da_ = sa + (uint32_t)q * a_plane;
+                        uint8_t* db_ = sb + (uint32_t)q * b_plane;
+                        if (a.a4d) {
+                            tma_load_4d(da_, &map_a, &full_bar[s], 0, t0 + off_a, m0 / 64, qa * a.B + bb);
+                        } else {
 #pragma unroll
-                        for (int m = 0; m < WG_BM / 64; m++)
-                            tma_load_3d(sa + m * WG_BOX_BYTES, &map_a, &full_bar[s], m0 + m * 64, t0 + off_a, pl_a * a.B + bb);
-                    }
-                    if (a.b4d) {
-                        tma_load_4d(sb, &map_b, &full_bar[s], 0, t0 + off_b, n0 / 64, pl_b * a.B + bb);
-                    } else {
+                            for (int m = 0; m < WG_BM / 64; m++)
+                                tma_load_3d(da_ + m * box_bytes, &map_a, &full_bar[s], m0 + m * 64, t0 + off_a, qa * a.B + bb);
+                        }
+                        if (a.b4d) {
+                            tma_load_4d(db_, &map_b, &full_bar[s], 0, t0 + off_b, n0 / 64, qb * a.B + bb);
+                        } else {
 #pragma unroll
-                        for (int n = 0; n < BN / 64; n++)
-                            tma_load_3d(sb + n * WG_BOX_BYTES, &map_b, &full_bar[s], n0 + n * 64, t0 + off_b, pl_b * a.B + bb);
+                            for (int n = 0; n < BN / 64; n++)
+                                tma_load_3d(db_ + n * box_bytes, &map_b, &full_bar[s], n0 + n * 64, t0 + off_b, qb * a.B + bb);
+                        }
                     }
                 }
                 __syncwarp();
@@ -171,10 +190,22 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                 const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
                 // MN-major: 16 frame rows of 128 B = 2048 B per UMMA_K (+128 in 16-byte descriptor units);
                 // 64-channel boxes are WG_BOX_BYTES apart (LBO); 8-row swizzle atoms 1024 B apart (SBO)
-                const uint64_t da = smem_desc_sw128(sa, WG_BOX_BYTES, 1024), db = smem_desc_sw128(sa + A_BYTES, WG_BOX_BYTES, 1024);
                 if (elect_one()) {
+                    if (multi) {
+                        // both planes of both operands are in the stage: every significant product from it
+                        const int np = n_pairs(a.P), pb0 = pair_base(a.P);
+                        for (int pr = 0; pr < np; pr++) {
+                            const int pa = c_pair_a[pb0 + pr], pb = c_pair_b[pb0 + pr];
+                            const int qa = a.swapped ? pb : pa, qb = a.swapped ? pa : pb;
+                            const uint64_t da = smem_desc_sw128(sa + (uint32_t)qa * a_plane, box_bytes, 1024);
+                            const uint64_t db = smem_desc_sw128(sa + a_all + (uint32_t)qb * b_plane, box_bytes, 1024);
+                            for (int j = 0; j < kt / 16; j++) umma_bf16(tmem_base, da + 128 * j, db + 128 * j, idesc, (i | pr | j) != 0);
+                        }
+                    } else {
+                        const uint64_t da = smem_desc_sw128(sa, WG_BOX_BYTES, 1024), db = smem_desc_sw128(sa + A_BYTES, WG_BOX_BYTES, 1024);
 #pragma unroll
-                    for (int j = 0; j < WG_KT / 16; j++) umma_bf16(tmem_base, da + 128 * j, db + 128 * j, idesc, (i | j) != 0);
+                        for (int j = 0; j < WG_KT / 16; j++) umma_bf16(tmem_base, da + 128 * j, db + 128 * j, idesc, (i | j) != 0);
+                    }
                     umma_commit(&empty_bar[s]);
                 }
                 __syncwarp();
@@ -303,17 +334,17 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
 }
 
 // 4-D (C % 64 == 0) or 3-D MN-major operand map of planes (P, B, T, Cp); `groups` = 64-channel boxes per load
-static bool make_wgrad_map(CUtensorMap* m, const void* base, int C, int T, int PB, int groups, int* is4d) {
+static bool make_wgrad_map(CUtensorMap* m, const void* base, int C, int T, int PB, int groups, int* is4d, int kt = WG_KT) {
     const int Cp = round_up8(C);
     if (C % 64 == 0) {
         const uint64_t dims[4] = {64, (uint64_t)T, (uint64_t)C / 64, (uint64_t)PB};
         const uint64_t strides[3] = {(uint64_t)Cp * 2, 128, (uint64_t)T * Cp * 2};
-        const uint32_t box[4] = {64, WG_KT, (uint32_t)groups, 1};
+        const uint32_t box[4] = {64, (uint32_t)kt, (uint32_t)groups, 1};
         *is4d = 1;
         return make_tmap(m, base, 4, dims, strides, box);
     }
     *is4d = 0;
-    return make_tmap_3d(m, base, (uint64_t)C, (uint64_t)T, (uint64_t)PB, (uint64_t)Cp * 2, (uint64_t)T * Cp * 2, 64, WG_KT, 1);
+    return make_tmap_3d(m, base, (uint64_t)C, (uint64_t)T, (uint64_t)PB, (uint64_t)Cp * 2, (uint64_t)T * Cp * 2, 64, (uint32_t)kt, 1);
 }
 
 template <int BN>
@@ -329,8 +360,8 @@ static int launch_wgrad_tc(const void* rows_pl, const void* cols_pl, int ksplit,
         attr_done = true;
     }
     CUtensorMap ma, mb;
-    if (!make_wgrad_map(&ma, rows_pl, a.nrows, a.T, a.P * a.B, WG_BM / 64, &a.a4d)) return VNB_E_CUDA;
-    if (!make_wgrad_map(&mb, cols_pl, a.ncols, a.T, a.P * a.B, BN / 64, &a.b4d)) return VNB_E_CUDA;
+    if (!make_wgrad_map(&ma, rows_pl, a.nrows, a.T, a.P * a.B, WG_BM / 64, &a.a4d, a.kt)) return VNB_E_CUDA;
+    if (!make_wgrad_map(&mb, cols_pl, a.ncols, a.T, a.P * a.B, BN / 64, &a.b4d, a.kt)) return VNB_E_CUDA;
     a.nstages = Cfg::stages(ksplit);
     a.recv_off = Cfg::recv_offset(ksplit);
     cudaLaunchConfig_t cfg = {};
@@ -363,10 +394,13 @@ int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin
     const int nrows = transposed ? Cin : Cout, ncols = transposed ? Cout : Cin;
     const void* rows_pl = transposed ? u : dy;
     const void* cols_pl = transposed ? dy : u;
-    WgradTcArgs a{B, nrows, ncols, T, taps, P, dil, transposed ? 1 : 0, 0, 0, 0, 0, dw};
+    // all planes per stage for the two-plane mode (VNB_OPT_GEMM_V3 = 0 keeps the round-1 pass per plane pair)
+    const int multi = (P == 2 && option(VNB_OPT_GEMM_V3) != 0) ? 1 : 0;
+    WgradTcArgs a{B, nrows, ncols, T, taps, P, dil, transposed ? 1 : 0, 0, 0, 0, 0, dw, multi ? WG_KT / 2 : WG_KT, multi};
     static const int force_bn = getenv("VNB_WG_BN") ? atoi(getenv("VNB_WG_BN")) : 0;
     static const int force_ks = getenv("VNB_WG_KSPLIT") ? atoi(getenv("VNB_WG_KSPLIT")) : 0;
-    const int kblocks = B * ceil_div(T, WG_KT) * n_pairs(P);
+    // stages walked by a tile: (sample, frame block) x plane pairs - or, all planes per stage, half-size frame blocks
+    const int kblocks = multi ? B * ceil_div(T, WG_KT / 2) : B * ceil_div(T, WG_KT) * n_pairs(P);
     int bn = 64, ks = 1;
     int64_t best = INT64_MAX;
     for (int cand = 64; cand <= 256; cand *= 2) {

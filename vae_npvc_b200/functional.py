@@ -249,7 +249,7 @@ class EncBlockFn(Function):
             v, g, bias, gamma, beta = params[5 * j:5 * j + 5]
             d = dil if j == 0 else 1
             W = _weights(v, g, False, P)
-            h, mean, rstd = Pm.conv_fwd(inp, W.wf, W.taps, d, C, bias, 0, gn_groups=1)
+            h, mean, rstd = Pm.conv_fwd(inp, W.wf, W.taps, d, C, bias, 0, gn_groups=1, defer_stats=True)
             if j < n_layers - 1:
                 yj, _, nxt = Pm.enc_out(h, None, mean, rstd, gamma, beta, P, True, False, True)
             else:
@@ -274,15 +274,23 @@ class EncBlockFn(Function):
         grads = [None] * len(params)
         dn = dy
         dypl = None
+        finals = []
         for j in range(n_layers - 1, -1, -1):
             L = ctx.layers[j]
             v, g, bias, gamma, beta = params[5 * j:5 * j + 5]
             last = j == n_layers - 1
-            R = Pm.gn_bwd_rows(dn, L['h'], L['mean'], L['rstd'], 1)
+            # the row-sum kernel also publishes the group sums the apply kernel needs; the finalisation (parameter
+            # gradients only) then runs beside the rest of the chain
+            R, S = Pm.gn_bwd_rows(dn, L['h'], L['mean'], L['rstd'], 1, gamma)
             bs = params[5 * n_layers + 2]
             slots = {'dgamma': _slot(gamma), 'dbeta': _slot(beta), 'csum': _slot(bias),
                      'dbeta2': _slot(bs) if last else None}          # skip bias grad = sum_{b,t} dy = dbeta
-            dgamma, dbeta, S, _, csum = Pm.gn_bwd_finalize(R, gamma, L['rstd'], T, 1, True, slots)
+            if S is None:
+                dgamma, dbeta, S, _, csum = Pm.gn_bwd_finalize(R, gamma, L['rstd'], T, 1, True, slots)
+            else:
+                with _Fork(R) as fk_fin:
+                    dgamma, dbeta, _, _, csum = Pm.gn_bwd_finalize(R, gamma, L['rstd'], T, 1, True, slots)
+                finals.append((fk_fin, dgamma, dbeta, csum))
             dpre, dnpl = Pm.gn_bwd_apply(dn, L['h'], L['mean'], L['rstd'], gamma, S, 1, P, last)
             if last:
                 dypl = dnpl
@@ -302,6 +310,8 @@ class EncBlockFn(Function):
         if ctx.needs_input_grad[0]:
             fk.join(dcs)
             dc = Pm.act_bwd_add(du, c, dcs, ACT_LRELU)
+        for fk_fin, a_, b_, c_ in finals:
+            fk_fin.join(a_, b_, c_)
         return (dc, None, None, None, None) + tuple(grads)
 
 
@@ -339,15 +349,15 @@ class DecBlockFn(Function):
         bcast = has_cond and cond.dim() == 2
         cpl = wc32 = wc_wb = None
         if cond_slot is not None:
-            a, mean, rstd = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, cond[cond_slot[0]], 2 * C, gn_groups=2)
+            a, mean, rstd = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, cond[cond_slot[0]], 2 * C, gn_groups=2, defer_stats=True)
         elif has_cond and bcast:
             cond = cond.contiguous()
             Wc = _weights(v_c, g_c, False, P, need_wf=False, need_wb=False, need_w32=True)
             wc32 = Wc.w32.view(2 * C, -1)
             p = Pm.linear_fwd(cond, wc32, b_c, b_in)
-            a, mean, rstd = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, p, 2 * C, gn_groups=2)
+            a, mean, rstd = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, p, 2 * C, gn_groups=2, defer_stats=True)
         elif not has_cond:
-            a, mean, rstd = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, b_in, 0, gn_groups=2)
+            a, mean, rstd = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, b_in, 0, gn_groups=2, defer_stats=True)
         else:
             a = Pm.conv_fwd(xpl, Win.wf, Win.taps, dil, 2 * C, b_in, 0)
             if has_cond:
@@ -355,7 +365,7 @@ class DecBlockFn(Function):
                 cpl = _input_planes(cond, P)
                 Wc = _weights(v_c, g_c, False, P, need_wb=ctx.needs_input_grad[1])
                 wc_wb = Wc.wb
-                a, mean, rstd = Pm.conv_fwd(cpl, Wc.wf, 1, 1, 2 * C, b_c, 0, None, a, True, gn_groups=2)
+                a, mean, rstd = Pm.conv_fwd(cpl, Wc.wf, 1, 1, 2 * C, b_c, 0, None, a, True, gn_groups=2, defer_stats=True)
         gpl = Pm.dec_gate(a, mean, rstd, gamma, beta, P)
         Wrs = _weights(v_rs, g_rs, False, P)
         r = Pm.conv_fwd(gpl, Wrs.wf, 1, 1, C + S, b_rs, 0)
@@ -393,14 +403,22 @@ class DecBlockFn(Function):
             db_rs = None
         dg = Pm.conv_fwd(drpl, ctx.wrs_wb, 1, 1, C)
         dv_rs, dg_rs = _wgrad(drpl, ctx.gpl, 1, 1, False, v_rs, g_rs)
-        R = Pm.gate_bwd_rows(dg, a, mean, rstd, gamma, beta, P)
+        R, S_rows = Pm.gate_bwd_rows(dg, a, mean, rstd, gamma, beta, P, want_S=True)
         cond_slot = ctx.cond_slot
         any_cond = has_cond or (cond_slot is not None and b_c is not None)
         slots = {'dgamma': _slot(gamma), 'dbeta': _slot(beta), 'csum': _slot(b_in),
                  'csum2': _slot(b_c) if any_cond else None}          # both biases add to the GN input
         if cond_slot is not None:
             slots['bsum'] = cond_slot[1]['dP'][cond_slot[0]]          # d(cond bias) of this block -> CondAllFn's table
-        dgamma, dbeta, Ssum, bsum, csum = Pm.gn_bwd_finalize(R, gamma, rstd, T, 2, True, slots)
+        fk_fin = None
+        if S_rows is None:
+            dgamma, dbeta, Ssum, bsum, csum = Pm.gn_bwd_finalize(R, gamma, rstd, T, 2, True, slots)
+        else:
+            # the group sums came with the row sums: the finalisation (parameter gradients, conditioning-bias gradient)
+            # leaves the critical path
+            with _Fork(R) as fk_fin:
+                dgamma, dbeta, _, bsum, csum = Pm.gn_bwd_finalize(R, gamma, rstd, T, 2, True, slots)
+            Ssum = S_rows
         dcond = dv_c = dg_c = db_c = None
         fk_lin = None
         if has_cond and bcast:
@@ -415,6 +433,8 @@ class DecBlockFn(Function):
         dapl = Pm.gate_bwd_apply(dg, a, mean, rstd, gamma, beta, Ssum, P)
         dx = Pm.conv_fwd(dapl, ctx.win_wb, taps, dil, C, None, 0, dxo) if ctx.needs_input_grad[0] else None
         dv_in, dg_in = _wgrad(dapl, ctx.xpl, taps, dil, True, v_in, g_in)
+        if fk_fin is not None:
+            fk_fin.join(dgamma, dbeta, bsum, csum)
         if cond_slot is not None:
             if b_c is not None and slots['csum2'] is None:
                 db_c = (csum if csum is not None else b_in.grad).clone()

@@ -155,7 +155,7 @@ def _stats_zeros(B, groups, device):
 
 
 def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=None, out=None, accumulate=False,
-             gn_groups=0, eps=1e-5, lengths=None):
+             gn_groups=0, eps=1e-5, lengths=None, defer_stats=False):
     """x_pl: Planes (B,Cin,T); w_op: (P,taps,Cout,Cin_p) bf16 -> out fp32, logical (B,Cout,T).
     gn_groups > 0: also returns the GroupNorm (mean, rstd) (B, gn_groups) of the result, accumulated
     in the GEMM epilogue -> (out, mean, rstd).  ``lengths`` (B,) int32: packed variable-length batch - the
@@ -175,6 +175,10 @@ def conv_fwd(x_pl, w_op, taps, dil, Cout, bias=None, bias_bstride=0, residual=No
     if not gn_groups:
         return out
     mean, rstd = _f32((x_pl.B, gn_groups), out), _f32((x_pl.B, gn_groups), out)
+    if defer_stats and lengths is None:
+        # the consumer (enc_out / dec_gate) finalises the statistics itself and fills mean / rstd for the backward pass
+        mean._vnb_stats = (sums, float(eps))
+        return out, mean, rstd
     if lengths is not None:
         _C.call('gn_sums_unpad', out.transpose(1, 2), x_pl.B, Cout, x_pl.T, gn_groups, lengths, sums)
         _C.call('gn_finalize_masked', sums, x_pl.B, gn_groups, Cout // gn_groups, x_pl.T, lengths, eps, mean, rstd)
@@ -232,8 +236,14 @@ def enc_out(h, s, mean, rstd, gamma, beta, P, want_y=True, want_ypl=True, want_u
     y = cl_empty(B, C, T, h.device) if want_y else None
     ypl = Planes.empty(P, B, C, T, h.device) if want_ypl else None
     upl = Planes.empty(P, B, C, T, h.device) if want_upl else None
-    _C.call('enc_out', _r(h), _r(s), mean, rstd, gamma, beta, B, C, T, P, _r(y), ypl.data if ypl else None,
-            upl.data if upl else None)
+    st = getattr(mean, '_vnb_stats', None)
+    if st is not None:
+        _C.call('enc_out_s', _r(h), _r(s), st[0], st[1], gamma, beta, B, C, T, P, _r(y), ypl.data if ypl else None,
+                upl.data if upl else None, mean, rstd)
+        del mean._vnb_stats
+    else:
+        _C.call('enc_out', _r(h), _r(s), mean, rstd, gamma, beta, B, C, T, P, _r(y), ypl.data if ypl else None,
+                upl.data if upl else None)
     return y, ypl, upl
 
 
@@ -241,7 +251,12 @@ def dec_gate(a, mean, rstd, gamma, beta, P):
     B, C2, T = a.shape
     C = C2 // 2
     gpl = Planes.empty(P, B, C, T, a.device)
-    _C.call('dec_gate', _r(a), mean, rstd, gamma, beta, B, C, T, P, gpl.data)
+    st = getattr(mean, '_vnb_stats', None)
+    if st is not None:
+        _C.call('dec_gate_s', _r(a), st[0], st[1], gamma, beta, B, C, T, P, gpl.data, mean, rstd)
+        del mean._vnb_stats
+    else:
+        _C.call('dec_gate', _r(a), mean, rstd, gamma, beta, B, C, T, P, gpl.data)
     return gpl
 
 
@@ -262,19 +277,40 @@ def dec_out(r, x, S, P, skip_sum=None, first=True, want_x=True, want_xpl=True):
 # --------------------------------------------------------------------------------------------
 # backward elementwise / reductions
 # --------------------------------------------------------------------------------------------
-def gn_bwd_rows(dn, h, mean, rstd, groups):
+def _group_sum_scratch(B, groups, like):
+    """zeroed fp64 accumulators + ticket slot for the fused group sums (carved from the per-step arena)"""
+    n = B * groups * 2 + 1
+    buf, off = _ARENA['buf'], _ARENA['off']
+    if buf is not None and off >= 0 and buf.device == like.device and off + n <= buf.numel():
+        _ARENA['off'] = off + n
+        return buf[off:off + n]
+    return torch.zeros((n,), dtype=torch.float64, device=like.device)
+
+
+def gn_bwd_rows(dn, h, mean, rstd, groups, gamma=None):
+    """-> R (B,C,3); with ``gamma`` -> (R, S (B,groups,2) | None): the group sums the apply kernel needs, fused into
+    this launch when the shape allows (else None: take S from gn_bwd_finalize)."""
     B, C, T = h.shape
     R = _f32((B, C, 3), h)
+    if gamma is not None and (C // groups) % 32 == 0:
+        S = _f32((B, groups, 2), h)
+        _C.call('gn_bwd_rows_s', _r(dn), _r(h), mean, rstd, gamma, B, C, T, groups, R, _group_sum_scratch(B, groups, h), S)
+        return R, S
     _C.call('gn_bwd_rows', _r(dn), _r(h), mean, rstd, B, C, T, groups, R)
-    return R
+    return (R, None) if gamma is not None else R
 
 
-def gate_bwd_rows(dg, a, mean, rstd, gamma, beta, P=3):
-    """``P``: operand mode of the step (1 = bf16 planes: the gate may use the approximate functions)."""
+def gate_bwd_rows(dg, a, mean, rstd, gamma, beta, P=3, want_S=False):
+    """``P``: operand mode of the step (1 = bf16 planes: the gate may use the approximate functions).
+    ``want_S`` -> (R, S (B,2,2) | None) as gn_bwd_rows."""
     B, C2, T = a.shape
     R = _f32((B, C2, 3), a)
+    if want_S and (C2 // 2) % 32 == 0:
+        S = _f32((B, 2, 2), a)
+        _C.call('gate_bwd_rows_s', _r(dg), _r(a), mean, rstd, gamma, beta, B, C2 // 2, T, P, R, _group_sum_scratch(B, 2, a), S)
+        return R, S
     _C.call('gate_bwd_rows_p', _r(dg), _r(a), mean, rstd, gamma, beta, B, C2 // 2, T, P, R)
-    return R
+    return (R, None) if want_S else R
 
 
 def gn_bwd_finalize(R, gamma, rstd, T, groups, want_sums=False, out=None):
