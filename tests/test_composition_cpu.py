@@ -388,18 +388,19 @@ def test_weight_bank_segments_equal_whole(cpu_prims):
         tr = TB.Trainer(cfg)
         tr.model.load_state_dict(synth.synthetic_state_dict(arch, 777))
         bank = tr.bank
-        assert len(bank.segments) == 2
-        (a0, a1), (b0, b1) = bank.segments[0]['layers'], bank.segments[1]['layers']
-        assert a0 == 0 and a1 == b0 and b1 == bank.n_layers                      # contiguous, cover every layer
-        assert bank.segments[0]['rows'][1] == bank.segments[1]['rows'][0]
-        assert bank.segments[1]['rows'][1] == bank.row2layer.numel()
-        assert bank.segments[1]['tiles'][1] == bank.tile2layer.numel()
+        assert len(bank.segments) == 3 and bank.segment_kinds == [0, 1, 2]     # encoder | decoder | conditioning convs
+        for sa, sb in zip(bank.segments[:-1], bank.segments[1:]):               # contiguous, cover every layer
+            assert sa['layers'][1] == sb['layers'][0] and sa['rows'][1] == sb['rows'][0] and sa['tiles'][1] == sb['tiles'][0]
+        assert bank.segments[0]['layers'][0] == 0 and bank.segments[-1]['layers'][1] == bank.n_layers
+        assert bank.segments[-1]['rows'][1] == bank.row2layer.numel()
+        assert bank.segments[-1]['tiles'][1] == bank.tile2layer.numel()
         bank.prepare()
         whole_w, whole_w32 = bank.wbuf.clone(), bank.w32buf.clone()
         bank.wbuf.zero_()
         bank.w32buf.zero_()
         bank.prepare(1)
         assert not torch.equal(bank.wbuf, whole_w)                               # only the decoder so far
+        bank.prepare(2)
         bank.prepare(0)
         assert torch.equal(bank.wbuf, whole_w) and torch.equal(bank.w32buf, whole_w32)
         g = torch.Generator().manual_seed(3)
@@ -410,6 +411,7 @@ def test_weight_bank_segments_equal_whole(cpu_prims):
         tr._flat_g.copy_(dw)
         bank.finish_backward(1)
         bank.finish_backward(0)
+        bank.finish_backward(2)
         assert torch.equal(tr._flat_g, whole_g)
     finally:
         TB.Pm = old

@@ -41,10 +41,19 @@ class WeightBank(object):
         rows, tiles, desc, entries = [], [], [], []
         w_off = w32_off = row0 = tile0 = 0
         self.max_k = 1
-        seg_of_layer = []                 # segment index per layer: 0 = 'encoder.*', 1 = everything after it
-        for name, m in model.named_modules():
-            if not isinstance(m, (nn.Conv1d, nn.ConvTranspose1d)):
-                continue
+        seg_of_layer = []                 # segment index per layer (see ``segments`` below)
+        # Table order = segment order: 0 the leading 'encoder.*' convs, 1 every other conv except 2, the decoders'
+        # conditioning 1x1 convs.  The conditioning convs get their weight gradients from ONE batched kernel after the
+        # whole decoder has been back-propagated (functional.CondAllFn), i.e. later than the moment the trainer starts
+        # the decoder segment's weight-norm backward on a side stream - so they must not be part of that segment.
+        convs = [(name, m) for name, m in model.named_modules() if isinstance(m, (nn.Conv1d, nn.ConvTranspose1d))]
+
+        def _seg(name):
+            if '.conv_cond' in name:
+                return 2
+            return 0 if name.startswith('encoder.') else 1
+        convs.sort(key=lambda nm: _seg(nm[0]))            # stable: module order inside a segment
+        for name, m in convs:
             if hasattr(m, 'weight_g'):
                 v, g = m.weight_v, m.weight_g
             else:
@@ -61,7 +70,7 @@ class WeightBank(object):
             e32 = w32_off if want32 else -1
             if want32:
                 w32_off += _align(v.numel())
-            seg_of_layer.append(0 if name.startswith('encoder.') and (not seg_of_layer or seg_of_layer[-1] == 0) else 1)
+            seg_of_layer.append(_seg(name))
             desc.append([(v.data_ptr() - base) // 4, (g.data_ptr() - base) // 4 if g is not None else -1, d0, d1, k,
                          int(transposed), wf_off, wb_off, e32, row0, tile0, 0])
             rows += [len(desc) - 1] * d0
@@ -84,7 +93,8 @@ class WeightBank(object):
         # encoder's forward / backward (trainer/basic.py).  A segment launch gets views of the row / tile tables that
         # start at its first row / tile and a copy of the descriptor table with row0 / tile0 shifted accordingly.
         self.segments = []
-        for sidx in sorted(set(seg_of_layer)):
+        self.segment_kinds = sorted(set(seg_of_layer))    # which of {0 encoder, 1 other, 2 conditioning} exist, in table order
+        for sidx in self.segment_kinds:
             layers = [i for i, s_ in enumerate(seg_of_layer) if s_ == sidx]
             r0, t0 = desc[layers[0]][9], desc[layers[0]][10]
             last = layers[-1]
@@ -98,7 +108,7 @@ class WeightBank(object):
         self.seg_of_ptr = {}
         self.by_ptr = {}
         for li, (v, g, transposed, k, co, ci, wf_off, n_wf, wb_off, n_wb, e32) in enumerate(entries):
-            self.seg_of_ptr[v.data_ptr()] = seg_of_layer[li]
+            self.seg_of_ptr[v.data_ptr()] = self.segment_kinds.index(seg_of_layer[li])
             wf = self.wbuf[wf_off:wf_off + n_wf].view(P, k, co, Pm.pitch(ci))
             wb = self.wbuf[wb_off:wb_off + n_wb].view(P, k, ci, Pm.pitch(co))
             w32 = self.w32buf[e32:e32 + v.numel()].view_as(v) if e32 >= 0 else None

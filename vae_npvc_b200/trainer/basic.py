@@ -162,6 +162,10 @@ class Trainer(object):
             jit.draws = str(config.get('jitter_draws', 'device' if self.device.type == 'cuda' else 'host'))
         # bucketed all-reduce: trigger name (model/vqvae.py set_grad_ready_callback) -> slice of the flat buffers
         self._comm = torch.cuda.Stream(device=self.device) if self._side_wanted() else None
+        # gradient slices all-reduced while backward still runs: (decoder, encoder) counts; what is left after the
+        # last one (the lowest encoder group, codebook, speaker table, conditioning convs) follows backward
+        self._n_buckets = tuple(config.get('allreduce_buckets', (3, 3)))
+        self._early_segments = set()
         self._buckets = self._plan_buckets()
         self._reduced = []
         self.overlap_allreduce = bool(config.get('overlap_allreduce', True))
@@ -219,15 +223,28 @@ class Trainer(object):
             i = order.index(key)
             return spans[order[i + 1]][0] if i + 1 < len(order) else (off + 3) // 4 * 4
 
-        if len(dec) >= 4 and dec_all and order.index(dec_all[-1]) - order.index(dec_all[0]) == len(dec_all) - 1:
-            cut = len(dec) // 2
-            plan[dec[cut - 1]] = (spans[dec[cut]][0], _end(dec_all[-1]))
-            plan['decoder'] = (spans[dec_all[0]][0], spans[dec[cut]][0])
-        elif dec_all and order.index(dec_all[-1]) - order.index(dec_all[0]) == len(dec_all) - 1:
+        def _cuts(n, parts):                # split n modules into `parts` groups: start indices of groups 1..parts-1
+            return sorted({(n * j) // parts for j in range(1, parts)} - {0})
+
+        self._dec_buckets_complete = False
+        contiguous = lambda ks: bool(ks) and order.index(ks[-1]) - order.index(ks[0]) == len(ks) - 1
+        if len(dec) >= 4 and contiguous(dec_all):
+            # decoder: `nb` slices; slice j (modules dec[c_j] ..) is complete when the gradient reaches the OUTPUT of
+            # dec[c_j - 1]; the first slice (from the decoder's first module) at the decoder's input
+            cuts = _cuts(len(dec), int(self._n_buckets[0]))
+            ends = cuts[1:] + [None]
+            for c, e in zip(cuts, ends):
+                plan[dec[c - 1]] = (spans[dec[c]][0], spans[dec[e]][0] if e is not None else _end(dec_all[-1]))
+            plan['decoder'] = (spans[dec_all[0]][0], spans[dec[cuts[0]]][0])
+            self._dec_buckets_complete = True
+        elif contiguous(dec_all):
             plan['decoder'] = (spans[dec_all[0]][0], _end(dec_all[-1]))
-        if len(enc) >= 4 and order.index(enc[-1]) - order.index(enc[0]) == len(enc) - 1:
-            cut = len(enc) // 2
-            plan[enc[cut - 1]] = (spans[enc[cut]][0], _end(enc[-1]))
+            self._dec_buckets_complete = True
+        if len(enc) >= 4 and contiguous(enc):
+            cuts = _cuts(len(enc), int(self._n_buckets[1]) + 1)      # the lowest group stays for after backward
+            ends = cuts[1:] + [None]
+            for c, e in zip(cuts, ends):
+                plan[enc[c - 1]] = (spans[enc[c]][0], spans[enc[e]][0] if e is not None else _end(enc[-1]))
         return plan
 
     def _plan_grad_zero(self):
@@ -362,6 +379,7 @@ class Trainer(object):
             overlap = (dist is not None and self._allreduce_kind != 'none' and self._side is not None and self._comm is not None and bool(self._buckets)
                        and self.overlap_allreduce)
             self._early_finished = False
+            self._early_segments = set()
             if overlap:
                 _model_mod.set_grad_ready_callback(self._grad_ready)                 # hooks registered during forward
             elif split and dist is None:
@@ -391,10 +409,9 @@ class Trainer(object):
                         self._all_reduce_mean(pos, total)
                 if comm is not None:
                     torch.cuda.current_stream().wait_stream(comm)
-            if self._early_finished:
-                self.bank.finish_backward(0)        # the other segments went through on the side stream already
-            else:
-                self.bank.finish_backward()
+            for sidx in range(len(self.bank.segments)):
+                if sidx not in self._early_segments:      # (the decoder's went through on a side stream already)
+                    self.bank.finish_backward(sidx)
             if dist is not None and self._mc is None and self._allreduce_kind != 'none':
                 self._flat_g.mul_(1.0 / dist.get_world_size())      # the multimem kernel already scaled
         finally:
@@ -421,11 +438,18 @@ class Trainer(object):
         encoder is back-propagated."""
         if name != 'decoder' or self._early_finished:
             return
+        segs = self._decoder_segments()
         self._side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self._side):
-            for sidx in range(1, len(self.bank.segments)):
+            for sidx in segs:
                 self.bank.finish_backward(sidx)
+        self._early_segments.update(segs)
         self._early_finished = True
+
+    def _decoder_segments(self):
+        """Bank segments whose weight gradients are final when the gradient reaches the decoder's input: the decoder's
+        convs WITHOUT the conditioning convs (their gradients come from one batched kernel later, functional.CondAllFn)."""
+        return [i for i, kind in enumerate(self.bank.segment_kinds) if kind == 1]
 
     def _grad_ready(self, name):
         """Called from a tensor hook during backward (model/vqvae.py _mark): the modules after ``name`` have been
@@ -438,6 +462,14 @@ class Trainer(object):
         self._comm.wait_stream(self._side)
         with torch.cuda.stream(self._comm):
             self._all_reduce_mean(rng[0], rng[1])
+            if name == 'decoder' and self._dec_buckets_complete and not self._early_finished:
+                # every decoder slice has been averaged: the decoder's weight-norm backward follows on the
+                # communication stream instead of waiting behind the last bucket after backward
+                segs = self._decoder_segments()
+                for sidx in segs:
+                    self.bank.finish_backward(sidx)
+                self._early_segments.update(segs)
+                self._early_finished = True
         self._reduced.append(rng)
 
     def _capture(self, *inputs):
