@@ -77,6 +77,8 @@ int vnb_get_backend(void);
  *                     share an SM, so that the next kernel's prologue overlaps this kernel's epilogue */
 #define VNB_OPT_TC3_SMEM_KB 8
 #define VNB_OPT_COUNT_ 9
+/* diagnostics: buf[slot] = %globaltimer (ns) when `stream` reaches this launch; usable inside captured graphs */
+int vnb_debug_stamp(int64_t* buf, int slot, void* stream);
 void vnb_set_option(int which, int value);
 int vnb_get_option(int which);
 /* debug: how many bounded mbarrier waits of the tcgen05 kernels timed out since load (must stay 0);

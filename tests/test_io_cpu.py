@@ -143,3 +143,21 @@ def test_extract_bnf_text_and_ark_outputs(tmp_path):
     assert all(np.array_equal(back[u], ids[u]) for u in feats)
     for u in feats:
         assert np.array_equal(res[u], torch.unique_consecutive(torch.from_numpy(ids[u])).numpy())
+
+
+def test_datasets_shard_by_rank_without_launcher_changes():
+    """The reference's train.py builds one seeded shuffling DataLoader on every process (bin/train.py:44-46,68-76): the
+    datasets map the SAME index to DIFFERENT items per rank, so ranks read disjoint utterances."""
+    from vae_npvc_b200.dataset.utt2mel_spk import SyntheticDataset, rank_world
+    cfg = {'encoder': {'in_channels': [8]}, 'crop_length': 16, 'y_num': 5, 'synthetic_utterances': 64}
+    full = SyntheticDataset(None, cfg)
+    parts = [SyntheticDataset(None, dict(cfg, ddp_rank=r, ddp_world=4)) for r in range(4)]
+    assert len(full) == 64 and all(len(p) == 16 for p in parts) and rank_world({}) == (0, 1)
+    seen = set()
+    for r, p in enumerate(parts):
+        for i in range(len(p)):
+            x, y = p[i]
+            fx, fy = full[i * 4 + r]
+            assert torch.equal(x, fx) and torch.equal(y, fy)
+            seen.add(i * 4 + r)
+    assert seen == set(range(64))

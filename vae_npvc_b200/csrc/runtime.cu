@@ -55,6 +55,23 @@ bool pdl_enabled() {
 
 }  // namespace vnb
 
+namespace vnb {
+__global__ void debug_stamp_kernel(long long* buf, int slot) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    buf[slot] = (long long)t;
+}
+}  // namespace vnb
+
+// diagnostics: write the GPU's nanosecond timer into buf[slot] when the stream reaches this point (works inside a
+// captured graph, where CUDA events cannot be read back) - tools/diag_ddp_timeline.py
+extern "C" int vnb_debug_stamp(int64_t* buf, int slot, void* stream) {
+    VNB_REQUIRE(buf && slot >= 0, "debug_stamp: bad arguments");
+    vnb::debug_stamp_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((long long*)buf, slot);
+    VNB_LAUNCH_CHECK("debug_stamp");
+    return VNB_OK;
+}
+
 extern "C" {
 const char* vnb_last_error(void) { return vnb::g_err; }
 int vnb_version(void) { return 100; }

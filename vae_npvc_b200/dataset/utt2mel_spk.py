@@ -14,6 +14,7 @@ each batch in one of two pinned host buffers and copies it to the device on its 
 trainer, so the H2D transfer of step k+1 overlaps step k (the reference does a synchronous ``x.cuda()`` at the top
 of every step, trainer/basic.py:59).  The trainer's ``t.to(device)`` on an already-resident tensor is a no-op.
 """
+import os
 import random
 from pathlib import Path
 
@@ -21,6 +22,17 @@ import numpy as np
 import torch
 
 from .. import kaldi_ark
+
+
+def rank_world(config=None):
+    """(rank, world) of this process under torchrun (RANK / WORLD_SIZE), overridable by config keys ``ddp_rank`` /
+    ``ddp_world``.  The reference's train.py builds ONE seeded shuffling DataLoader (bin/train.py:44-46,68-76): with
+    equal seeds every rank draws the SAME index sequence, so the datasets below map index i to item i * world + rank
+    and report len // world - the ranks then read disjoint utterances without any change to the launcher."""
+    config = config or {}
+    world = int(config.get('ddp_world', os.environ.get('WORLD_SIZE', '1')))
+    rank = int(config.get('ddp_rank', os.environ.get('RANK', '0')))
+    return (rank, world) if world > 1 else (0, 1)
 
 
 def load_dict_data(data_file):
@@ -41,10 +53,11 @@ class Dataset(torch.utils.data.Dataset):
         self.feats_scp = load_dict_data(data_dir / 'feats.scp')
         self.utt2num_frames = load_dict_data(data_dir / 'utt2num_frames')
         self.utt2spks = load_list_data(data_dir / 'utt2spk_id')
-        self.num_data = len(self.utt2spks)
+        self.rank, self.world = rank_world(config)
+        self.num_data = len(self.utt2spks) // self.world
 
     def __getitem__(self, index):
-        utt, spk = self.utt2spks[index]
+        utt, spk = self.utt2spks[index * self.world + self.rank]
         feat_length = int(self.utt2num_frames[utt])
         if feat_length <= self.crop_length:
             feat_start, feat_end = 0, feat_length
@@ -68,10 +81,12 @@ class SyntheticDataset(torch.utils.data.Dataset):
         self.crop_length = config.get('valid_crop_length' if valid else 'train_crop_length',
                                       config.get('crop_length', 256))
         self.y_num = config.get('y_num', 10)
-        self.num_data = int(config.get('synthetic_utterances', num_data))
+        self.rank, self.world = rank_world(config)
+        self.num_data = int(config.get('synthetic_utterances', num_data)) // self.world
         self.seed = int(config.get('seed', 777)) + (1 << 20 if valid else 0)
 
     def __getitem__(self, index):
+        index = index * self.world + self.rank
         g = torch.Generator().manual_seed(self.seed + index)
         feat = torch.randn(self.x_dim, self.crop_length, generator=g)
         return feat, torch.tensor([index % self.y_num]).long()

@@ -107,6 +107,27 @@ class FlatAdam(object):
         self.state[1] = 0.0
 
 
+def _maybe_init_distributed(config):
+    """One process per GPU under torchrun WITHOUT touching the reference's launcher: vae_npvc/bin/train.py knows nothing
+    about ranks, so when the torchrun environment is present (WORLD_SIZE > 1) and no process group exists
+    yet, the Trainer binds this process to cuda:LOCAL_RANK and opens the NCCL group itself.  Returns the device string
+    to use (config 'device' wins when given)."""
+    import os
+    import torch.distributed as dist
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    dev = config.get('device', 'cuda')
+    if world <= 1 or not str(dev).startswith('cuda') or not dist.is_available() or not bool(config.get('ddp', True)):
+        return dev
+    local = int(os.environ.get('LOCAL_RANK', os.environ.get('RANK', '0')))
+    if torch.cuda.is_available():
+        torch.cuda.set_device(local)
+    if not dist.is_initialized():
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        os.environ.setdefault('MASTER_PORT', '29500')
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    return 'cuda:%d' % local if 'device' not in config else dev
+
+
 def _dist():
     import torch.distributed as dist
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
@@ -132,7 +153,7 @@ class Trainer(object):
         model_name = 'Model' if len(model_type) < 2 else model_type[1]
         model = getattr(module, model_name)(config)
 
-        self.device = torch.device(config.get('device', 'cuda'))
+        self.device = torch.device(_maybe_init_distributed(config))
         if self.device.type == 'cuda':
             from .. import _C
             _C.require_cuda()
@@ -165,6 +186,10 @@ class Trainer(object):
         # gradient slices all-reduced while backward still runs: (decoder, encoder) counts; what is left after the
         # last one (the lowest encoder group, codebook, speaker table, conditioning convs) follows backward
         self._n_buckets = tuple(config.get('allreduce_buckets', (3, 3)))
+        # diagnostics (tools/diag_ddp_timeline.py): GPU-timer stamps at the step's milestones, readable after a replay
+        self._stamps = (torch.zeros(64, dtype=torch.int64, device=self.device)
+                        if bool(config.get('debug_stamps', False)) and self.device.type == 'cuda' else None)
+        self._stamp_next = 10
         self._early_segments = set()
         self._buckets = self._plan_buckets()
         self._reduced = []
@@ -330,8 +355,23 @@ class Trainer(object):
             self._mc = None
             return None
 
+    def _stamp(self, slot):
+        if self._stamps is not None:
+            from .. import _C
+            _C.call('debug_stamp', self._stamps, slot)
+
     def _all_reduce_mean(self, lo, hi):
         """Mean over ranks of flat_g[lo:hi] on the current stream (lo, hi multiples of 4 on the multimem path)."""
+        if self._stamps is not None and self._stamp_next < 62:
+            k = self._stamp_next
+            self._stamp_next += 2
+            self._stamp(k)
+            self._all_reduce_mean_(lo, hi)
+            self._stamp(k + 1)
+            return
+        self._all_reduce_mean_(lo, hi)
+
+    def _all_reduce_mean_(self, lo, hi):
         import torch.distributed as dist
         if self._mc is not None:
             from .. import _C
@@ -384,10 +424,14 @@ class Trainer(object):
                 _model_mod.set_grad_ready_callback(self._grad_ready)                 # hooks registered during forward
             elif split and dist is None:
                 _model_mod.set_grad_ready_callback(self._decoder_done)
+            self._stamp_next = 10
+            self._stamp(0)
             output, loss, detail = self.model(list(inputs))
             for sidx in range(len(self.bank.segments)):
                 self.bank.wait_ready(sidx)          # joins the side stream even if a segment was never used
+            self._stamp(1)
             loss.backward()
+            self._stamp(2)
             _model_mod.set_grad_ready_callback(None)
             if self._side is not None:
                 torch.cuda.current_stream().wait_stream(self._side)
@@ -409,9 +453,11 @@ class Trainer(object):
                         self._all_reduce_mean(pos, total)
                 if comm is not None:
                     torch.cuda.current_stream().wait_stream(comm)
+            self._stamp(3)
             for sidx in range(len(self.bank.segments)):
                 if sidx not in self._early_segments:      # (the decoder's went through on a side stream already)
                     self.bank.finish_backward(sidx)
+            self._stamp(4)
             if dist is not None and self._mc is None and self._allreduce_kind != 'none':
                 self._flat_g.mul_(1.0 / dist.get_world_size())      # the multimem kernel already scaled
         finally:
@@ -427,6 +473,7 @@ class Trainer(object):
             Fn.set_bank(None)
             _lvq.defer_items(False)
         self.optimizer.step(self.max_grad_norm, self._step_size, self._gamma)
+        self._stamp(5)
         self.bank.fresh = False
         keys = list(detail.keys())
         scal = torch.stack([detail[k].t.reshape(()).float() for k in keys])
@@ -545,6 +592,9 @@ class Trainer(object):
         return self.model
 
     def save_checkpoint(self, checkpoint_file):
+        dist = _dist()
+        if dist is not None and dist.get_rank() != 0:
+            return                         # replicas are bit-identical: rank 0 writes (train.py calls this on every rank)
         torch.save({'model': self.model.state_dict(), 'optimizer': self.optimizer.state_dict(),
                     'iteration': self.iteration}, checkpoint_file)
         print('Saved state dict. to {}'.format(checkpoint_file))
