@@ -380,6 +380,8 @@ def run_ours(args, rank, world):
                    precision=args.precision, cuda_graph=not args.no_graph,
                    overlap_allreduce=not bool(os.environ.get('VNB_NO_OVERLAP')), allreduce=os.environ.get('VNB_ALLREDUCE', 'multimem'),
                    allreduce_blocks=int(os.environ.get('VNB_AR_BLOCKS', 0)),
+                   **({'allreduce_buckets': tuple(int(v) for v in os.environ['VNB_BUCKETS'].split(','))}
+                      if os.environ.get('VNB_BUCKETS') else {}),
                    bank_overlap=not bool(os.environ.get('VNB_NO_BANK_OVERLAP')),
                    sparse_grad_zero=not bool(os.environ.get('VNB_NO_SPARSE_ZERO')),
                    graph_warmup=min(3, warm - 1), learning_rate=1e-3, max_grad_norm=10, lr_scheduler='StepLR',

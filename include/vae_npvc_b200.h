@@ -76,7 +76,10 @@ int vnb_get_backend(void);
 /*   VNB_OPT_TC3_SMEM_KB  cap on the dynamic shared memory of the third-generation GEMMs (0 = none): <= 110 lets two CTAs
  *                     share an SM, so that the next kernel's prologue overlaps this kernel's epilogue */
 #define VNB_OPT_TC3_SMEM_KB 8
-#define VNB_OPT_COUNT_ 9
+/*   VNB_OPT_FAST_EPI  conv GEMM epilogue of full tiles without residual / accumulate: bias and GroupNorm statistics in
+ *                     registers on the way out of TMEM, rows stored by the bulk-copy engine (default 1) */
+#define VNB_OPT_FAST_EPI 9
+#define VNB_OPT_COUNT_ 10
 /* diagnostics: buf[slot] = %globaltimer (ns) when `stream` reaches this launch; usable inside captured graphs */
 int vnb_debug_stamp(int64_t* buf, int slot, void* stream);
 void vnb_set_option(int which, int value);

@@ -63,12 +63,64 @@ struct ConvTcArgs {
     int nstages;          // depth of the TMA ring (<= 8)
     int kch;              // 64-deep k-chunks per pipeline stage (1, or 2 with 4-D tensor maps when Cin % 128 == 0)
     uint32_t recv_off;    // byte offset of the receive slots in dynamic shared memory
+    int fast_epi;         // VNB_OPT_FAST_EPI: register epilogue + bulk row stores for full tiles
 };
 
 __device__ __forceinline__ double warp_sum_f64(double v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
+}
+
+// Round 2 - register epilogue for FULL tiles without residual / accumulate (100 of the step's 110 conv launches): the
+// bias add and the fused GroupNorm statistics happen on the values as they leave TMEM (a thread owns one frame row and
+// 32 consecutive channels: the bias is a warp-uniform broadcast load, the statistics two running sums), the staged tile
+// is then handed to the copy engine row by row (cp.async.bulk shared -> global) instead of being re-read and stored by
+// the threads.  The store loop this replaces was 2.1k (3.1k with statistics) of a 14-17k cycle kernel
+// (profiles/r02b_gemm_sweep_timelines.txt: "staged" -> "stored").
+template <int BN>
+__device__ __forceinline__ void epilogue_regs_bulk(uint32_t tmem_base, float* stage, const float* __restrict__ bias,
+                                                   float* __restrict__ out_tile, int Cout, double* gn_pair, int warp, int lane) {
+    constexpr int PITCH = BN + 4;
+    const int q = warp & 3, h = warp >> 2;
+    float* srow = stage + (size_t)(q * 32 + lane) * PITCH;
+    float fs0 = 0.f, fs1 = 0.f;
+#pragma unroll 1
+    for (int c0 = h * (BN / 2); c0 < (h + 1) * (BN / 2); c0 += 32) {
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+        if (bias) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+                const float4 bb = __ldg(reinterpret_cast<const float4*>(bias + c0 + i));
+                v[i] += bb.x; v[i + 1] += bb.y; v[i + 2] += bb.z; v[i + 3] += bb.w;
+            }
+        }
+        if (gn_pair) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+                fs0 += (v[i] + v[i + 1]) + (v[i + 2] + v[i + 3]);
+                fs1 += (v[i] * v[i] + v[i + 1] * v[i + 1]) + (v[i + 2] * v[i + 2] + v[i + 3] * v[i + 3]);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 32; i += 4)
+            *reinterpret_cast<float4*>(srow + c0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+    }
+    if (gn_pair) {
+        double gs0 = warp_sum_f64((double)fs0), gs1 = warp_sum_f64((double)fs1);
+        if (lane == 0) {
+            atomicAdd(gn_pair, gs0);
+            atomicAdd(gn_pair + 1, gs1);
+        }
+    }
+    tc_fence_before();
+    fence_proxy_async_smem();                          // generic-proxy stores -> visible to the bulk-copy engine
+    __syncthreads();
+    if (threadIdx.x < TC_BM) {
+        bulk_store_row(out_tile + (size_t)threadIdx.x * Cout, smem_u32(stage + (size_t)threadIdx.x * PITCH), BN * 4);
+        bulk_store_commit_wait_read();
+    }
 }
 
 // Shared-memory plan (dynamic, after 1 KB alignment):  [ TMA ring: nstages x (16 KB + BN*128 B) | receive slots ]
@@ -228,7 +280,19 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     float* stage = reinterpret_cast<float*>(smem);
     const float* recv = reinterpret_cast<const float*>(smem + a.recv_off);
     const int rows_own = TC_BM / ks, r_base = kr * rows_own;
-    {
+    // full tile, one k-slice, nothing to add from memory: register epilogue + bulk row stores (see epilogue_regs_bulk)
+    const bool fast_epi = a.fast_epi && ks == 1 && nk > 0 && !a.residual && !a.accumulate && (a.Cout & 3) == 0 &&
+                          co0 + BN <= a.Cout && t0 + TC_BM <= a.T && (!a.gn_sums || ((a.Cout / a.gn_groups) % BN) == 0) &&
+                          ((((uintptr_t)a.bias) | ((uintptr_t)a.out) | ((uintptr_t)a.bias_bstride * 4)) & 15) == 0;
+    if (fast_epi) {
+        mbar_wait_warp(&tmem_full_bar, 0, 32);
+        tc_fence_after();
+        if (threadIdx.x == 64) TS(3);
+        const float* bias = a.bias ? a.bias + (size_t)b * a.bias_bstride + co0 : nullptr;
+        double* gp = a.gn_sums ? a.gn_sums + ((size_t)b * a.gn_groups + co0 / (a.Cout / a.gn_groups)) * 2 : nullptr;
+        epilogue_regs_bulk<BN>(tmem_base, stage, bias, a.out + ((size_t)b * a.T + t0) * a.Cout + co0, a.Cout, gp, warp, lane);
+        if (threadIdx.x == 64) TS(6);
+    } else {
         // all 8 warps: TMEM lane quarter = warp % 4 (hardware rule), column half = warp / 4
         const int q = warp & 3, h = warp >> 2;
         mbar_wait_warp(&tmem_full_bar, 0, 32);        // (lanes 1..31 of warps 0/1 arrive here while lane 0 still issues)
@@ -557,7 +621,8 @@ int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int
     const int dbg = option(VNB_OPT_TC_DBG);
     static const int force_bn = getenv("VNB_TC_BN") ? atoi(getenv("VNB_TC_BN")) : 0;
     static const int force_ks = getenv("VNB_TC_KSPLIT") ? atoi(getenv("VNB_TC_KSPLIT")) : 0;
-    ConvTcArgs a{B, Cin, Cout, T, taps, dil, P, bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups, dbg, 0, 1, 0};
+    ConvTcArgs a{B, Cin, Cout, T, taps, dil, P, bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups, dbg, 0, 1, 0,
+                 option(VNB_OPT_FAST_EPI)};
     const int Cin_p = round_up8(Cin);
     // N tile and cluster split-K: as many CTAs as fit the 148 SMs in one wave (a tcgen05.mma issue costs the same
     // ~70 cycles for a 32-cycle N=64 tile as for a 128-cycle N=256 one, so wide tiles are preferred on a tie),

@@ -97,6 +97,16 @@ __device__ __forceinline__ void bulk_copy_to_cta(uint32_t dst_cluster, uint32_t 
                  ::"r"(dst_cluster), "r"(src_cta), "r"(bytes), "r"(bar_cluster) : "memory");
 }
 
+// bulk copy own shared memory -> global memory (TMA engine, bulk async-group): the threads hand a whole staged row to
+// the copy engine instead of moving it through registers
+__device__ __forceinline__ void bulk_store_row(void* gdst, uint32_t src_cta, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(src_cta), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_store_commit_wait_read() {
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");      // the source rows may be reused / the CTA may exit
+}
+
 // Warp-level wait: ONE lane polls, the rest of the warp parks at __syncwarp.  128 epilogue threads all
 // spinning on try_wait only burn issue slots; `backoff_ns` > 0 adds a nanosleep between polls for long
 // waits (the epilogue waiting for the whole main loop).

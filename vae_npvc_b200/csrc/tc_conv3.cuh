@@ -37,6 +37,7 @@ struct ConvTc3Args {
     double* gn_sums;
     int gn_groups;
     int dbg;
+    int fast_epi;
 };
 
 template <int BN, bool CTA2>
@@ -171,7 +172,17 @@ conv_fwd_tc3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 
     // ===== epilogue (every CTA for its own 128 x BN accumulator): TMEM -> shared staging -> coalesced store =====
     float* stage = reinterpret_cast<float*>(smem);
-    {
+    const bool fast_epi = a.fast_epi && live && !a.residual && !a.accumulate && (a.Cout & 3) == 0 && co0 + BN <= a.Cout &&
+                          t0 + TC_BM <= a.T && (!a.gn_sums || ((a.Cout / a.gn_groups) % BN) == 0) &&
+                          ((((uintptr_t)a.bias) | ((uintptr_t)a.out) | ((uintptr_t)a.bias_bstride * 4)) & 15) == 0;
+    if (fast_epi) {
+        mbar_wait_warp(&tmem_full_bar, 0, 32);
+        tc_fence_after();
+        if (threadIdx.x == 64) TS(3);
+        const float* bias = a.bias ? a.bias + (size_t)b * a.bias_bstride + co0 : nullptr;
+        double* gp = a.gn_sums ? a.gn_sums + ((size_t)b * a.gn_groups + co0 / (a.Cout / a.gn_groups)) * 2 : nullptr;
+        epilogue_regs_bulk<BN>(tmem_base, stage, bias, a.out + ((size_t)b * a.T + t0) * a.Cout + co0, a.Cout, gp, warp, lane);
+    } else {
         const int q = warp & 3, h = warp >> 2;
         mbar_wait_warp(&tmem_full_bar, 0, 32);
         tc_fence_after();
@@ -439,7 +450,7 @@ static int conv_fwd_tc3(const void* in, int P, int B, int Cin, int T, const void
     }
     if (force_st >= 2 && force_st < best.stages) best.stages = force_st;
     ConvTc3Args a{B, Cin, Cout, T, taps, dil, P, (int)mt, 1, 2, bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups,
-                  option(VNB_OPT_TC_DBG)};
+                  option(VNB_OPT_TC_DBG), option(VNB_OPT_FAST_EPI)};
 #define VNB_TC3_CASE(BN_, C2_) \
     if (best.bn == BN_ && best.cta2 == C2_) return launch_conv_tc3<BN_, C2_ != 0>(in, w, best, a, st);
     VNB_TC3_CASE(64, 0)

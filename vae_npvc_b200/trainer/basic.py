@@ -260,7 +260,7 @@ class Trainer(object):
             ends = cuts[1:] + [None]
             for c, e in zip(cuts, ends):
                 plan[dec[c - 1]] = (spans[dec[c]][0], spans[dec[e]][0] if e is not None else _end(dec_all[-1]))
-            plan['decoder'] = (spans[dec_all[0]][0], spans[dec[cuts[0]]][0])
+            plan['decoder'] = (spans[dec_all[0]][0], spans[dec[cuts[0]]][0] if cuts else _end(dec_all[-1]))
             self._dec_buckets_complete = True
         elif contiguous(dec_all):
             plan['decoder'] = (spans[dec_all[0]][0], _end(dec_all[-1]))
