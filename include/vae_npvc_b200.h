@@ -77,7 +77,9 @@ int vnb_get_backend(void);
  *                     share an SM, so that the next kernel's prologue overlaps this kernel's epilogue */
 #define VNB_OPT_TC3_SMEM_KB 8
 /*   VNB_OPT_FAST_EPI  conv GEMM epilogue of full tiles without residual / accumulate: bias and GroupNorm statistics in
- *                     registers on the way out of TMEM, rows stored by the bulk-copy engine (default 1) */
+ *                     registers on the way out of TMEM, rows stored by the bulk-copy engine.  Default 0: measured no faster
+ *                     (4.2k vs 3.9k cycles for a 128 x 128 fp32 tile, profiles/r02f_fast_epilogue.txt) - the epilogue is
+ *                     bound by writing 8 MB of fp32 output into L2 from 128 CTAs at once, not by how the threads do it */
 #define VNB_OPT_FAST_EPI 9
 #define VNB_OPT_COUNT_ 10
 /* diagnostics: buf[slot] = %globaltimer (ns) when `stream` reaches this launch; usable inside captured graphs */

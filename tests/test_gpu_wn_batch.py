@@ -58,12 +58,12 @@ def test_prepare_and_backward_generations_agree(wn_opt, shape, precision):
         # per segment (the trainer's side-stream schedule) == whole
         wn_opt(1)
         bank.wbuf.zero_()
-        bank.prepare(1)
-        bank.prepare(0)
+        for sidx in reversed(range(len(bank.segments))):          # encoder | decoder | conditioning convs
+            bank.prepare(sidx)
         assert torch.equal(bank.wbuf, planes[1])
         tr._flat_g.copy_(dw)
-        bank.finish_backward(1)
-        bank.finish_backward(0)
+        for sidx in reversed(range(len(bank.segments))):
+            bank.finish_backward(sidx)
         assert torch.equal(tr._flat_g, grads[1])
         if shape == 'small':
             # the contract restatement on the same flat buffers
