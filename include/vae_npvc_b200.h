@@ -81,7 +81,10 @@ int vnb_get_backend(void);
  *                     (4.2k vs 3.9k cycles for a 128 x 128 fp32 tile, profiles/r02f_fast_epilogue.txt) - the epilogue is
  *                     bound by writing 8 MB of fp32 output into L2 from 128 CTAs at once, not by how the threads do it */
 #define VNB_OPT_FAST_EPI 9
-#define VNB_OPT_COUNT_ 10
+/*   VNB_OPT_VQ_FUSED  fused VQ lookup (frame preparation + one-product tensor-core shortlist + exact fp32 re-rank +
+ *                     gather + loss sums + histogram in one kernel, csrc/tc_vq_fused.cuh; default 1) */
+#define VNB_OPT_VQ_FUSED 10
+#define VNB_OPT_COUNT_ 11
 /* diagnostics: buf[slot] = %globaltimer (ns) when `stream` reaches this launch; usable inside captured graphs */
 int vnb_debug_stamp(int64_t* buf, int slot, void* stream);
 void vnb_set_option(int which, int value);
@@ -245,6 +248,14 @@ int vnb_vq_prep_z(const float* z, int B, int D, int T, int normalize, float* zn,
 int vnb_vq_lookup(const float* zn, const void* z_planes, const float* z_sq, const float* e_hat,
                   const void* e_planes, const float* e_sq, int B, int D, int T, int K,
                   int64_t* idx, void* stream);
+/* layers_vq.py:85-150 in one launch: z (B*T, D) channels-last frames -> [normalised frames zn_out, norms z_norm_out,]
+ * idx (int64), gathered rows q_out, sums[0] += sum (q - zn)^2, sums[1] += sum (zn - z)^2 (normalize only), counts[idx]++.
+ * e_planes: the bf16 planes of vnb_vq_prep_codebook (plane 0 is used).  Indices = the fp32 argmin of
+ * (|zn|^2 + |e|^2) - 2 zn.e wherever its top-2 gap exceeds fp32 rounding (bf16 tensor-core shortlist + exact fp32
+ * re-rank).  Returns 1 WITHOUT launching when the shape is not supported (caller falls back to prep_z + lookup + gather). */
+int vnb_vq_fused(const float* z, int B, int D, int T, int normalize, const float* e_hat, const void* e_planes,
+                 const float* e_sq, int K, float* zn_out, float* z_norm_out, int64_t* idx, float* q_out,
+                 float* sums, int* counts, void* stream);
 /* q = e_hat[idx] -> q_out (B,D,T); sums[0] += sum (q-zn)^2, sums[1] += sum (zn-z)^2;
  * counts[k] += #{idx==k}  (sums, counts must be zeroed by the caller) */
 int vnb_vq_gather(const int64_t* idx, const float* e_hat, const float* zn, const float* z, int B, int D,

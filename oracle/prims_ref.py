@@ -482,6 +482,14 @@ def vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq):
     return torch.argmin(d, dim=1)
 
 
+def vq_fused(z, normalize, e_hat, e_pl, e_sq, want_q=True, want_stats=True):
+    """Contract of vnb_vq_fused = vq_prep_z + vq_lookup + vq_gather."""
+    zn, zpl, z_sq, z_norm = vq_prep_z(z, normalize)
+    idx = vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
+    q, sums, counts = vq_gather(idx, e_hat, zn, z if normalize else None, want_q, want_stats)
+    return zn, (z_norm if normalize else None), idx, q, sums, counts
+
+
 def vq_gather(idx, e_hat, zn, z, want_q=True, want_stats=True):
     B, D, T = zn.shape
     q = e_hat[idx].view(B, T, D).transpose(1, 2).contiguous()

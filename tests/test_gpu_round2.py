@@ -425,3 +425,45 @@ def test_row_sum_kernels_publish_group_sums(fp32_mode):
     # shapes whose groups are not multiples of 32 channels fall back (S None)
     assert Pm.gn_bwd_rows(dn[:, :48].contiguous(), h[:, :48].contiguous(), *Pm.gn_stats(h[:, :48].contiguous(), 1), 1,
                           gamma[:48].contiguous())[1] is None
+
+
+@pytest.mark.parametrize('normalize', [False, True])
+@pytest.mark.parametrize('B,D,T,K', [(16, 64, 128, 512), (3, 128, 77, 300), (2, 16, 50, 40), (5, 32, 128, 4096),
+                                     (4, 64, 100, 1024), (2, 64, 33, 16384)])
+def test_vq_fused_lookup_gather(fp32_mode, normalize, B, D, T, K):
+    """vnb_vq_fused (one bf16 tensor-core product as a shortlist + exact fp32 re-rank, frames read once, rows gathered
+    in the same kernel) against the contract of prep_z + lookup + gather: indices bit-exact wherever the fp64 top-2
+    gap exceeds fp32 rounding (north_star), gathered rows, loss sums, histogram, normalised frames."""
+    from vae_npvc_b200 import _C, prims as Pm
+    z, E = g(B, D, T, seed=1, scale=1.5), g(K, D, seed=2)
+    e_hat, e_pl, e_sq = Pm.vq_prep_codebook(E.clone().cuda(), normalize, False)
+    got = Pm.vq_fused(Pm.as_cl(z.cuda()), normalize, e_hat, e_pl, e_sq)
+    assert got is not None
+    zn, z_norm, idx, q, sums, counts = got
+    torch.cuda.synchronize()
+    assert _C.call('debug_tc_timeouts') == 0
+    rzn, rzpl, rz_sq, rz_norm = R.vq_prep_z(z, normalize)
+    assert rel_err(zn, rzn) < 1e-6
+    if normalize:
+        assert rel_err(z_norm, rz_norm) < 1e-6
+    zf = rzn.double().transpose(1, 2).reshape(B * T, D)
+    eh = e_hat.double().cpu()
+    d = (zf.pow(2).sum(1, keepdim=True) + eh.pow(2).sum(1).view(1, -1)) - 2 * zf @ eh.t()
+    top2 = d.topk(2, dim=1, largest=False)
+    clear = (top2.values[:, 1] - top2.values[:, 0]) > 1e-5 * d.abs().max()
+    assert clear.float().mean() > 0.9
+    assert torch.equal(idx.cpu()[clear], top2.indices[clear, 0])
+    # whatever a near-tie resolved to, the chosen code is within rounding of the minimum
+    chosen = d.gather(1, idx.cpu().view(-1, 1)).squeeze(1)
+    assert float((chosen - top2.values[:, 0]).max()) <= 2e-5 * float(d.abs().max())
+    # downstream values on the kernel's own indices
+    rq, rsums, rcounts = R.vq_gather(idx.cpu(), e_hat.cpu(), rzn, z if normalize else None)
+    assert rel_err(q, rq) < 1e-6 and torch.equal(counts.cpu(), rcounts)
+    assert abs(float(sums[0]) - float(rsums[0])) <= 1e-5 * abs(float(rsums[0]))
+    if normalize:
+        assert abs(float(sums[1]) - float(rsums[1])) <= 1e-4 * abs(float(rsums[1])) + 1e-6
+    # a frame equal to a code maps to that code (distance 0 to itself)
+    pick = torch.randint(0, K, (B * T,), generator=torch.Generator().manual_seed(6)).cuda()
+    zx = e_hat[pick].view(B, T, D).transpose(1, 2).contiguous()
+    got2 = Pm.vq_fused(Pm.as_cl(zx), False, e_hat, e_pl, e_sq, want_q=False, want_stats=False)
+    assert torch.equal(got2[2], pick)

@@ -90,6 +90,32 @@ def main():
                   'alg %.0f GB/s (%.2f)  argmin agreement %.4f' % (K, D, dt * 1e6, N / dt / 1e6, ex_tf, ex_tf / tf, src,
                                                                   bytes_alg / dt / 1e9, bytes_alg / dt / 1e9 / hbm, agree),
                   flush=True)
+            # round 2: the fused kernel (frames read once, one bf16 product + exact fp32 re-rank, rows gathered and written):
+            # read z + write q + write idx = the algorithmic bytes of the WHOLE lookup
+            zc = Pm.as_cl(z)
+            fused = Pm.vq_fused(zc, False, e_hat, e_pl, e_sq)
+            if fused is not None:
+                qf = Pm.cl_empty(Bv, D, Tv, 'cuda')
+                sums = torch.zeros(2, device='cuda')
+                counts = torch.zeros(K, dtype=torch.int32, device='cuda')
+                idx2 = torch.empty((N,), dtype=torch.int64, device='cuda')
+
+                def run_f():
+                    _C.call('vq_fused', zc.transpose(1, 2), Bv, D, Tv, 0, e_hat, e_pl, e_sq, K, None, None, idx2, qf.transpose(1, 2),
+                            sums, counts)
+
+                dtf = timeit(run_f, flush=flush)
+                agree_f = float((dist.argmin(1) == idx2[:4096]).float().mean())
+                same = float((idx2 == idx).float().mean())
+                alg_tf = 2.0 * N * K * D / dtf / 1e12
+                rowf = dict(K=K, D=D, N=N, kernel='vq_fused', us=dtf * 1e6, frames_per_s=N / dtf, executed_tflops=alg_tf,
+                            tensor_frac=alg_tf / tf, hbm_gbs=bytes_alg / dtf / 1e9, hbm_frac=bytes_alg / dtf / 1e9 / hbm,
+                            argmin_agreement_vs_torch_fp32=agree_f, same_as_six_product_kernel=same)
+                out['vq_lookup'].append(rowf)
+                print('vq_fused  K=%5d D=%3d: %8.1f us  %7.2f Mframes/s  executed %6.1f TF/s (%.2f of %s peak)  '
+                      'alg %.0f GB/s (%.2f)  argmin agreement %.4f  same as 6-product kernel %.6f'
+                      % (K, D, dtf * 1e6, N / dtf / 1e6, alg_tf, alg_tf / tf, src, bytes_alg / dtf / 1e9,
+                         bytes_alg / dtf / 1e9 / hbm, agree_f, same), flush=True)
             del z, E, zn, zpl, idx
     # ---------------- memory-bound fused kernels ----------------
     B, T, C, S, P = (256 if quick else 1024), 128, 512, 128, 1

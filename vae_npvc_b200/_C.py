@@ -115,6 +115,8 @@ def call(name, *args):
     if has_stream:
         cargs.append(torch.cuda.current_stream().cuda_stream)
     r = getattr(lib, full)(*cargs)
+    if name == 'vq_fused' and r == 1:
+        return 1                          # shape not taken by the fused kernel: the caller falls back
     if ret == 'int' and name not in ('version', 'get_backend', 'get_option', 'debug_tc_timeouts', 'gn_stats_ws_floats') and r != 0:
         raise RuntimeError(f'{full} failed ({r}): {lib.vnb_last_error().decode()}')
     return r
@@ -128,7 +130,7 @@ def get_backend():
     return load().vnb_get_backend()
 
 
-OPT_EW_V2, OPT_FAST_GATE, OPT_WN_V2, OPT_GEMM_V3, OPT_TC3_BN, OPT_TC3_PAIR, OPT_TC3_STAGES, OPT_TC_DBG, OPT_TC3_SMEM_KB, OPT_FAST_EPI = range(10)
+OPT_EW_V2, OPT_FAST_GATE, OPT_WN_V2, OPT_GEMM_V3, OPT_TC3_BN, OPT_TC3_PAIR, OPT_TC3_STAGES, OPT_TC_DBG, OPT_TC3_SMEM_KB, OPT_FAST_EPI, OPT_VQ_FUSED = range(11)
 
 
 def set_option(which, value):

@@ -17,6 +17,8 @@ int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin
                   int transposed, float* dw, cudaStream_t st);
 int vq_lookup_tc(const void* z_planes, const float* z_sq, const void* e_planes, const float* e_sq, int B, int D,
                  int T, int K, int64_t* idx, cudaStream_t st);
+int vq_fused_tc(const float* z, int B, int D, int T, int normalize, const float* e_hat, const void* e_planes, const float* e_sq,
+                int K, float* zn_out, float* z_norm_out, int64_t* idx, float* q_out, float* sums, int* counts, cudaStream_t st);
 }  // namespace vnb
 
 using namespace vnb;
@@ -78,4 +80,18 @@ extern "C" int vnb_vq_lookup(const float* zn, const void* z_planes, const float*
         }
     }
     return vq_lookup_simt(zn, z_sq, e_hat, e_sq, B, D, T, K, idx, st);
+}
+
+// Fused frame preparation + lookup + gather (csrc/tc_vq_fused.cuh).  Returns 1 (no error string) when the shape is not
+// taken by the fused kernel (D not in {16, 32, 64, 128}, K < 8, SIMT backend forced): the caller then runs
+// vnb_vq_prep_z + vnb_vq_lookup + vnb_vq_gather.
+extern "C" int vnb_vq_fused(const float* z, int B, int D, int T, int normalize, const float* e_hat, const void* e_planes,
+                            const float* e_sq, int K, float* zn_out, float* z_norm_out, int64_t* idx, float* q_out,
+                            float* sums, int* counts, void* stream) {
+    VNB_REQUIRE(z && e_hat && e_planes && e_sq && idx, "vq_fused: null pointer");
+    VNB_REQUIRE(B > 0 && D > 0 && T > 0 && K > 0, "vq_fused: bad shape");
+    VNB_REQUIRE(!normalize || (zn_out && z_norm_out), "vq_fused: the normalised quantiser needs zn_out and z_norm_out");
+    if (backend() == VNB_BACKEND_SIMT || option(VNB_OPT_VQ_FUSED) == 0) return 1;
+    return vq_fused_tc(z, B, D, T, normalize, e_hat, e_planes, e_sq, K, zn_out, z_norm_out, idx, q_out, sums, counts,
+                       (cudaStream_t)stream);
 }

@@ -691,3 +691,4 @@ extern "C" int vnb_debug_tc_timeouts(void) {
 }
 #include "tc_wgrad.cuh"
 #include "tc_vq.cuh"
+#include "tc_vq_fused.cuh"

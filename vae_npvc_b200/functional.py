@@ -529,6 +529,20 @@ def _vq_scale(reduction, B, T, D):
     return {'sum': 1.0, 'mean': 1.0 / (B * T * D), 'batch_mean': 1.0 / B, 'frame_mean': 1.0 / (B * T)}[reduction]
 
 
+def _vq_lookup_gather(z, normalize, e_hat, e_pl, e_sq, want_q=True, want_stats=True):
+    """-> (zn, z_norm, idx, q, sums, counts): one fused launch where the shape allows (prims.vq_fused), else the three
+    separate kernels (frame preparation, six-product tensor-core lookup or SIMT lookup, gather)."""
+    fused = Pm.vq_fused(z, normalize, e_hat, e_pl, e_sq, want_q, want_stats) if hasattr(Pm, 'vq_fused') else None
+    if fused is not None:
+        return fused
+    zn, zpl, z_sq, z_norm = Pm.vq_prep_z(z, normalize)
+    idx = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
+    q = sums = counts = None
+    if want_q or want_stats:
+        q, sums, counts = Pm.vq_gather(idx, e_hat, zn, z if normalize else None, want_q, want_stats)
+    return zn, z_norm, idx, q, sums, counts
+
+
 class VQFn(Function):
     """VectorQuantizer.forward for the scalar reductions (layers_vq.py:79-150): in-place codebook
     renormalisation, distance GEMM + argmin, gather, both losses, perplexity, straight-through
@@ -539,9 +553,7 @@ class VQFn(Function):
         z = Pm.as_cl(z)
         B, D, T = z.shape
         e_hat, e_pl, e_sq = Pm.vq_prep_codebook(E.detach(), normalize, True)
-        zn, zpl, z_sq, z_norm = Pm.vq_prep_z(z, normalize)
-        idx = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
-        q, sums, counts = Pm.vq_gather(idx, e_hat, zn, z if normalize else None)
+        zn, z_norm, idx, q, sums, counts = _vq_lookup_gather(z, normalize, e_hat, e_pl, e_sq)
         scale = _vq_scale(reduction, B, T, D)
         scal = Pm.vq_finalize(sums, counts, B * T, scale, normalize, 1e-10)
         ctx.save_for_backward(z, zn, z_norm, e_hat, E, idx)
@@ -575,8 +587,7 @@ class VQLookupFn(Function):
     def forward(ctx, z, E, normalize):
         z = Pm.as_cl(z)
         e_hat, e_pl, e_sq = Pm.vq_prep_codebook(E.detach(), normalize, False)
-        zn, zpl, z_sq, _ = Pm.vq_prep_z(z, normalize)
-        idx = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
+        idx = _vq_lookup_gather(z, normalize, e_hat, e_pl, e_sq, want_q=False, want_stats=False)[2]
         ctx.mark_non_differentiable(idx)
         return idx
 
@@ -595,9 +606,7 @@ class EMAVQFn(Function):
         z = Pm.as_cl(z)
         B, D, T = z.shape
         e_hat, e_pl, e_sq = Pm.vq_prep_codebook(embeddings, False, False)
-        zn, zpl, z_sq, _ = Pm.vq_prep_z(z, False)
-        idx = Pm.vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq)
-        q, sums, counts = Pm.vq_gather(idx, e_hat, zn, None)
+        _, _, idx, q, sums, counts = _vq_lookup_gather(z, False, e_hat, e_pl, e_sq)
         scale = _vq_scale(reduction, B, T, D)
         scal = Pm.vq_finalize(sums, counts, B * T, scale, False, 1e-8)
         ctx.save_for_backward(z, e_hat, idx)

@@ -463,6 +463,28 @@ def vq_lookup(zn, zpl, z_sq, e_hat, e_pl, e_sq):
     return idx
 
 
+def vq_fused(z, normalize, e_hat, e_pl, e_sq, want_q=True, want_stats=True):
+    """Frame preparation + lookup + gather in ONE launch (csrc/tc_vq_fused.cuh).
+    -> (zn, z_norm, idx, q | None, sums | None, counts | None), or None when the shape is not taken by the fused kernel
+    (the caller then runs vq_prep_z + vq_lookup + vq_gather).  zn is z itself when not normalising."""
+    B, D, T = z.shape
+    K = e_hat.shape[0]
+    if D not in (16, 32, 64, 128) or K < 8 or not z.is_cuda:
+        return None
+    zc = as_cl(z)
+    zn = cl_empty(B, D, T, z.device) if normalize else zc
+    z_norm = _f32((B * T,), z) if normalize else None
+    idx = torch.empty((B * T,), dtype=torch.int64, device=z.device)
+    q = cl_empty(B, D, T, z.device) if want_q else None
+    sums = torch.zeros((2,), dtype=torch.float32, device=z.device) if want_stats else None
+    counts = torch.zeros((K,), dtype=torch.int32, device=z.device) if want_stats else None
+    r = _C.call('vq_fused', _r(zc), B, D, T, int(normalize), e_hat, e_pl, e_sq, K, _r(zn) if normalize else None, z_norm,
+                idx, _r(q), sums, counts)
+    if r == 1:
+        return None
+    return zn, z_norm, idx, q, sums, counts
+
+
 def vq_gather(idx, e_hat, zn, z, want_q=True, want_stats=True):
     """-> q (B,D,T), sums (2,) [sum (q-zn)^2, sum (zn-z)^2], counts (K,) int32"""
     B, D, T = zn.shape
