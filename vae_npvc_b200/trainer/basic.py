@@ -185,7 +185,7 @@ class Trainer(object):
         self._comm = torch.cuda.Stream(device=self.device) if self._side_wanted() else None
         # gradient slices all-reduced while backward still runs: (decoder, encoder) counts; what is left after the
         # last one (the lowest encoder group, codebook, speaker table, conditioning convs) follows backward
-        self._n_buckets = tuple(config.get('allreduce_buckets', (3, 3)))
+        self._n_buckets = tuple(config.get('allreduce_buckets', (6, 6)))     # measured best at 2 and 8 GPUs (profiles/r02g_*)
         # diagnostics (tools/diag_ddp_timeline.py): GPU-timer stamps at the step's milestones, readable after a replay
         self._stamps = (torch.zeros(64, dtype=torch.int64, device=self.device)
                         if bool(config.get('debug_stamps', False)) and self.device.type == 'cuda' else None)
