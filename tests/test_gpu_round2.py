@@ -429,10 +429,10 @@ def test_row_sum_kernels_publish_group_sums(fp32_mode):
 
 @pytest.mark.parametrize('normalize', [False, True])
 @pytest.mark.parametrize('B,D,T,K', [(16, 64, 128, 512), (3, 128, 77, 300), (2, 16, 50, 40), (5, 32, 128, 4096),
-                                     (4, 64, 100, 1024), (2, 64, 33, 16384)])
+                                     (4, 64, 100, 1024), (2, 64, 33, 8192)])
 def test_vq_fused_lookup_gather(fp32_mode, normalize, B, D, T, K):
-    """vnb_vq_fused (one bf16 tensor-core product as a shortlist + exact fp32 re-rank, frames read once, rows gathered
-    in the same kernel) against the contract of prep_z + lookup + gather: indices bit-exact wherever the fp64 top-2
+    """vnb_vq_fused (three bf16 plane products on the tensor cores as a shortlist + rigorous window + exact fp32 re-rank,
+    frames read once, rows gathered in the same kernel) against the contract of prep_z + lookup + gather: indices bit-exact wherever the fp64 top-2
     gap exceeds fp32 rounding (north_star), gathered rows, loss sums, histogram, normalised frames."""
     from vae_npvc_b200 import _C, prims as Pm
     z, E = g(B, D, T, seed=1, scale=1.5), g(K, D, seed=2)
@@ -467,3 +467,36 @@ def test_vq_fused_lookup_gather(fp32_mode, normalize, B, D, T, K):
     zx = e_hat[pick].view(B, T, D).transpose(1, 2).contiguous()
     got2 = Pm.vq_fused(Pm.as_cl(zx), False, e_hat, e_pl, e_sq, want_q=False, want_stats=False)
     assert torch.equal(got2[2], pick)
+
+
+@pytest.mark.parametrize('copies', [2, 3, 5])
+def test_vq_fused_duplicate_codes_take_the_lowest_index(fp32_mode, copies):
+    """Ties: torch.argmin returns the lowest index (layers_vq.py:107).  Two equal codes go through the exact two-candidate
+    re-rank, three or more put a third score inside the window and take the exhaustive fp32 search."""
+    from vae_npvc_b200 import _C, prims as Pm
+    K, D, B, T = 300, 64, 3, 100
+    E = g(K, D, seed=3)
+    where = [7, 70, 133, 200, 290][:copies]
+    for w in where[1:]:
+        E[w] = E[where[0]]
+    e_hat, e_pl, e_sq = Pm.vq_prep_codebook(E.clone().cuda(), False, False)
+    z = g(B, D, T, seed=4)
+    # a third of the frames sit next to the duplicated code
+    zz = z.transpose(1, 2).reshape(B * T, D)
+    zz[::3] = E[where[0]] + 1e-3 * zz[::3]
+    z = zz.view(B, T, D).transpose(1, 2).contiguous()
+    got = Pm.vq_fused(Pm.as_cl(z.cuda()), False, e_hat, e_pl, e_sq)
+    torch.cuda.synchronize()
+    assert _C.call('debug_tc_timeouts') == 0
+    idx = got[2].cpu()
+    assert bool((idx[::3] == where[0]).all())
+    d = (zz.double().pow(2).sum(1, keepdim=True) + E.double().pow(2).sum(1).view(1, -1)) - 2 * zz.double() @ E.double().t()
+    top2 = d.topk(2, dim=1, largest=False)
+    clear = (top2.values[:, 1] - top2.values[:, 0]) > 1e-5 * d.abs().max()
+    assert torch.equal(idx[clear], top2.indices[clear, 0])
+
+
+def test_vq_fused_leaves_huge_codebooks_to_the_three_kernel_path(fp32_mode):
+    from vae_npvc_b200 import prims as Pm
+    e_hat, e_pl, e_sq = Pm.vq_prep_codebook(g(16384, 64, seed=2).cuda(), False, False)
+    assert Pm.vq_fused(Pm.as_cl(g(2, 64, 33, seed=1).cuda()), False, e_hat, e_pl, e_sq) is None

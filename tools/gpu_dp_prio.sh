@@ -1,0 +1,23 @@
+#!/bin/bash
+# communication-stream priority experiment (2 GPUs): bench.py bf16x2, 100 steps each
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+NG=${NG:-2}
+run() {
+  local tag=$1; shift
+  env "$@" timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29520 bench.py --gpus $NG --steps 100 --warmup 10 --no-cpu-baseline > gpurun_out/dp_$tag.json 2> gpurun_out/dp_$tag.err
+  python - <<PY
+import json
+try:
+    d=json.loads([l for l in open('gpurun_out/dp_$tag.json') if l.startswith('{')][-1])
+    print('$tag', round(d['ms_per_step'],3),'ms', round(d['value']),'f/s')
+except Exception as e:
+    print('$tag failed', e); print(open('gpurun_out/dp_$tag.err').read()[-800:])
+PY
+}
+timeout 100 python bench.py --steps 100 --warmup 10 --no-cpu-baseline 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('single', round(d['ms_per_step'],3))"
+run prio_high VNB_COMM_PRIO=-1
+run prio_normal VNB_COMM_PRIO=0
+run prio_high_b VNB_COMM_PRIO=-1
+run prio_normal_b VNB_COMM_PRIO=0
+run prio_high_nccl VNB_COMM_PRIO=-1 VNB_ALLREDUCE=nccl

@@ -31,15 +31,15 @@ namespace vnb {
 
 using namespace tc;
 
-constexpr int VQF_BM = 128, VQF_BN = 256, VQF_BK = 64;
+constexpr int VQF_BM = 128, VQF_BN = 128, VQF_BK = 64;   // 128-code chunks: 2 x 128 TMEM columns, two CTAs per SM
 constexpr int VQF_EPI_WARPS = 8, VQF_THREADS = 64 + 32 * VQF_EPI_WARPS;   // TMA warp, MMA warp, 8 epilogue warps
 constexpr uint32_t VQF_A_BYTES = VQF_BM * VQF_BK * 2;       // 16 KB: 128 frames x 64 dims bf16
-constexpr uint32_t VQF_B_BYTES = VQF_BN * VQF_BK * 2;       // 32 KB: 256 codes x 64 dims bf16 (ONE plane = one stage)
+constexpr uint32_t VQF_B_BYTES = VQF_BN * VQF_BK * 2;       // 16 KB: 128 codes x 64 dims bf16 (ONE plane = one stage)
 constexpr float VQF_NEG = -3.0e38f;
 
 struct VqFusedArgs {
     int64_t N;
-    int D, K, normalize, nstages;
+    int D, K, normalize, nstages, dbg;
     const float* z;          // (N, D) frames, channels-last rows
     const float* e_hat;      // (K, D) fp32 (normalised) codebook
     const float* e_sq;       // (K)
@@ -69,7 +69,7 @@ __device__ __forceinline__ void top3_insert(Top3& t, float x, int id) {
 __device__ __forceinline__ float tag_score(float s, int i) { return __int_as_float((__float_as_int(s) & ~31) | i); }
 __device__ __forceinline__ int tagged_code(float r, int g) { return (g << 5) | (__float_as_int(r) & 31); }
 
-__global__ void __launch_bounds__(VQF_THREADS, 1)
+__global__ void __launch_bounds__(VQF_THREADS, 2)
 vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -93,6 +93,7 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
     uint8_t* smem_a = smem;                                              // [plane hi | mid][kd] tiles of 16 KB (SWIZZLE_128B)
     uint8_t* smem_b = smem + (size_t)2 * kd * VQF_A_BYTES;               // ring of 32 KB stages: one codebook plane tile each
     const float* znp = a.normalize ? a.zn_out : a.z;                     // fp32 frames as the exact re-rank / gather read them
+    long long* ts = ((a.dbg == 9 && blockIdx.x == 0) || (a.dbg == 10 && blockIdx.x == gridDim.x - 1)) ? g_tc_ts[1] : nullptr;     // VNB_TC_DBG=9 / 10: clock64 timeline of the first / last CTA
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&map_e);
@@ -108,6 +109,7 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
     }
     if (warp == 1) tmem_alloc<2 * VQF_BN>(&tmem_slot);
     pdl_wait();
+    if (threadIdx.x == 0) TS(0);
 
     // ===== prologue (all warps): frames -> z_n (fp32, global), |z_n|^2, |z|, bf16 hi / mid operand tiles =====
     {
@@ -120,43 +122,52 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
             __syncthreads();
         }
         const int passes = (VQF_BM + rows_per_pass - 1) / rows_per_pass;
-#pragma unroll 4
-        for (int ps = 0; ps < passes; ps++) {
-            const int r = rsub + ps * rows_per_pass;
-            const int64_t n = n0 + r;
-            const bool ok = r < VQF_BM && n < a.N;
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ok) v = __ldg(reinterpret_cast<const float4*>(a.z + n * D) + l);
-            float ss = (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
-            for (int o = L >> 1; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-            const float nrm = sqrtf(ss);
-            if (a.normalize && ok) {
-                v.x = v.x / nrm; v.y = v.y / nrm; v.z = v.z / nrm; v.w = v.w / nrm;
-            }
-            float qq = (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
-            for (int o = L >> 1; o > 0; o >>= 1) qq += __shfl_xor_sync(0xffffffffu, qq, o);
-            if (r >= VQF_BM) continue;
-            if (ok && a.zn_out) *(reinterpret_cast<float4*>(a.zn_out + n * D) + l) = v;
-            if (l == 0) {
-                s_zsq[r] = qq;
-                s_nrm[r] = nrm;
-                if (ok && a.z_norm_out) a.z_norm_out[n] = nrm;
-            }
-            // bf16 planes into the K-major SWIZZLE_128B tiles: row r = 128 B, 16-byte chunk index XOR (r & 7)
-            const int d = 4 * l, tile = d >> 6, dc = d & 63;
-            const uint32_t off = (uint32_t)tile * VQF_A_BYTES + (uint32_t)r * 128u + (uint32_t)(((dc >> 3) ^ (r & 7)) << 4) +
-                                 (uint32_t)(dc & 7) * 2u;
-            const float vv[4] = {v.x, v.y, v.z, v.w};
-            bf16 hi[4], mid[4], lo_;
+        for (int p0 = 0; p0 < passes; p0 += 8) {           // eight row loads in flight per thread before the first is used
+            float4 vb[8];
 #pragma unroll
-            for (int j = 0; j < 4; j++) split3(vv[j], hi[j], mid[j], lo_);
-            uint2 pk;
-            pk.x = (uint32_t)__bfloat16_as_ushort(hi[0]) | ((uint32_t)__bfloat16_as_ushort(hi[1]) << 16);
-            pk.y = (uint32_t)__bfloat16_as_ushort(hi[2]) | ((uint32_t)__bfloat16_as_ushort(hi[3]) << 16);
-            *reinterpret_cast<uint2*>(smem_a + off) = pk;
-            pk.x = (uint32_t)__bfloat16_as_ushort(mid[0]) | ((uint32_t)__bfloat16_as_ushort(mid[1]) << 16);
-            pk.y = (uint32_t)__bfloat16_as_ushort(mid[2]) | ((uint32_t)__bfloat16_as_ushort(mid[3]) << 16);
-            *reinterpret_cast<uint2*>(smem_a + (size_t)kd * VQF_A_BYTES + off) = pk;
+            for (int u = 0; u < 8; u++) {
+                const int r = rsub + (p0 + u) * rows_per_pass;
+                vb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (p0 + u < passes && r < VQF_BM && n0 + r < a.N) vb[u] = __ldg(reinterpret_cast<const float4*>(a.z + (n0 + r) * D) + l);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                if (p0 + u >= passes) break;               // uniform
+                const int r = rsub + (p0 + u) * rows_per_pass;
+                const int64_t n = n0 + r;
+                const bool ok = r < VQF_BM && n < a.N;
+                float4 v = vb[u];
+                float ss = (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+                for (int o = L >> 1; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+                const float nrm = sqrtf(ss);
+                if (a.normalize && ok) {
+                    v.x = v.x / nrm; v.y = v.y / nrm; v.z = v.z / nrm; v.w = v.w / nrm;
+                }
+                float qq = (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+                for (int o = L >> 1; o > 0; o >>= 1) qq += __shfl_xor_sync(0xffffffffu, qq, o);
+                if (r >= VQF_BM) continue;
+                if (ok && a.zn_out) *(reinterpret_cast<float4*>(a.zn_out + n * D) + l) = v;
+                if (l == 0) {
+                    s_zsq[r] = qq;
+                    s_nrm[r] = nrm;
+                    if (ok && a.z_norm_out) a.z_norm_out[n] = nrm;
+                }
+                // bf16 planes into the K-major SWIZZLE_128B tiles: row r = 128 B, 16-byte chunk index XOR (r & 7)
+                const int d = 4 * l, tile = d >> 6, dc = d & 63;
+                const uint32_t off = (uint32_t)tile * VQF_A_BYTES + (uint32_t)r * 128u + (uint32_t)(((dc >> 3) ^ (r & 7)) << 4) +
+                                     (uint32_t)(dc & 7) * 2u;
+                const float vv[4] = {v.x, v.y, v.z, v.w};
+                bf16 hi[4], mid[4], lo_;
+#pragma unroll
+                for (int j = 0; j < 4; j++) split3(vv[j], hi[j], mid[j], lo_);
+                uint2 pk;
+                pk.x = (uint32_t)__bfloat16_as_ushort(hi[0]) | ((uint32_t)__bfloat16_as_ushort(hi[1]) << 16);
+                pk.y = (uint32_t)__bfloat16_as_ushort(hi[2]) | ((uint32_t)__bfloat16_as_ushort(hi[3]) << 16);
+                *reinterpret_cast<uint2*>(smem_a + off) = pk;
+                pk.x = (uint32_t)__bfloat16_as_ushort(mid[0]) | ((uint32_t)__bfloat16_as_ushort(mid[1]) << 16);
+                pk.y = (uint32_t)__bfloat16_as_ushort(mid[2]) | ((uint32_t)__bfloat16_as_ushort(mid[3]) << 16);
+                *reinterpret_cast<uint2*>(smem_a + (size_t)kd * VQF_A_BYTES + off) = pk;
+            }
         }
     }
     fence_proxy_async_smem();                              // the operand tiles were written through the generic proxy
@@ -164,9 +175,10 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
+    if (threadIdx.x == 0) TS(1);
 
     if (warp == 0) {
-        // ===== producer: per chunk of 256 codes and 64-dim slice: the mid plane tile, then the hi plane tile =====
+        // ===== producer: per chunk of 128 codes and 64-dim slice: the mid plane tile, then the hi plane tile =====
         int s = 0, i = 0;
         uint32_t ph = 1;
         for (int ch = 0; ch < chunks; ch++)
@@ -193,6 +205,7 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
                 tc_fence_after();
             }
             const uint32_t tacc = tmem_base + (uint32_t)(buf * VQF_BN);
+            if (ch < 4 && lane == 0) TS(2 + 4 * ch);
             for (int c = 0; c < kd; c++) {
                 const int ksteps = (D - c * VQF_BK >= VQF_BK ? VQF_BK : D - c * VQF_BK) / 16;
                 const uint64_t da_hi = smem_desc_sw128(sa0 + (uint32_t)c * VQF_A_BYTES, 16, 1024);
@@ -200,6 +213,7 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
                 for (int step = 0; step < 2; step++) {
                     mbar_wait(&full_bar[s], ph);
                     tc_fence_after();
+                    if (ch < 4 && lane == 0 && c == 0) TS(3 + 4 * ch + step);
                     const uint64_t db = smem_desc_sw128(sb0 + (uint32_t)s * VQF_B_BYTES, 16, 1024);
                     if (elect_one()) {
                         if (step == 0) {
@@ -216,6 +230,7 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
             }
             if (elect_one()) umma_commit(&tmem_full_bar[buf]);
             __syncwarp();
+            if (ch < 4 && lane == 0) TS(5 + 4 * ch);
         }
     } else {
         // ===== epilogue: 8 warps; lane = frame, each warp scans one column half of every chunk =====
@@ -226,25 +241,28 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
         const int64_t n = n0 + r;
         Top3 t{VQF_NEG, VQF_NEG, VQF_NEG, 0, 0};
         float hmax = 0.f;
-        float e_next;
-        {
+        const bool es_loader = ew < VQF_BN / 32;           // these warps stage |e|^2 / 2 of every chunk
+        float e_next = 3.0e38f;
+        if (es_loader) {
             const int k = ew * 32 + lane;
             e_next = k < K ? 0.5f * __ldg(a.e_sq + k) : 3.0e38f;
         }
         for (int ch = 0; ch < chunks; ch++) {
             const int buf = ch & 1;
-            s_es[buf][ew * 32 + lane] = e_next;            // codes >= K: score -3e38, never a candidate (K >= 8)
+            if (es_loader) s_es[buf][ew * 32 + lane] = e_next;   // codes >= K: score -3e38, never a candidate (K >= 8)
             if (e_next < 1.0e38f) hmax = fmaxf(hmax, e_next);
-            if (ch + 1 < chunks) {
+            if (es_loader && ch + 1 < chunks) {
                 const int k = (ch + 1) * VQF_BN + ew * 32 + lane;
                 e_next = k < K ? 0.5f * __ldg(a.e_sq + k) : 3.0e38f;
             }
             named_bar_sync(1, 32 * VQF_EPI_WARPS);
+            if (ch < 4 && ew == 0 && lane == 0) TS(20 + 4 * ch);
             mbar_wait_warp(&tmem_full_bar[buf], (ch >> 1) & 1, 20);
             tc_fence_after();
+            if (ch < 4 && ew == 0 && lane == 0) TS(21 + 4 * ch);
 #pragma unroll 1
-            for (int b = 0; b < 4; b++) {
-                const int c0 = half * 128 + b * 32;
+            for (int b = 0; b < VQF_BN / 64; b++) {
+                const int c0 = half * (VQF_BN / 2) + b * 32;
                 const int k0 = ch * VQF_BN + c0;
                 if (k0 >= K) break;                                  // warp-uniform
                 float v[32];
@@ -253,11 +271,13 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
 #pragma unroll
                 for (int i = 0; i < 8; i++) {
                     const float4 e = es4[i];                         // broadcast read
-                    v[4 * i + 0] = tag_score(v[4 * i + 0] - e.x, 4 * i + 0);
-                    v[4 * i + 1] = tag_score(v[4 * i + 1] - e.y, 4 * i + 1);
-                    v[4 * i + 2] = tag_score(v[4 * i + 2] - e.z, 4 * i + 2);
-                    v[4 * i + 3] = tag_score(v[4 * i + 3] - e.w, 4 * i + 3);
+                    v[4 * i + 0] -= e.x;
+                    v[4 * i + 1] -= e.y;
+                    v[4 * i + 2] -= e.z;
+                    v[4 * i + 3] -= e.w;
                 }
+#pragma unroll
+                for (int i = 0; i < 32; i++) v[i] = tag_score(v[i], i);
                 // the block's two best tagged scores (tree: independent min/max, no serial chain)
                 float hi[16], lo[16];
 #pragma unroll
@@ -275,16 +295,16 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
                         lo[j] = l2;
                     }
                 }
-                if (__any_sync(0xffffffffu, hi[0] > t.r2)) {
-                    const int id = k0 >> 5;
-                    top3_insert(t, hi[0], id);
-                    top3_insert(t, lo[0], id);
-                }
+                const int id = k0 >> 5;
+                top3_insert(t, hi[0], id);
+                top3_insert(t, lo[0], id);
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty_bar[buf])) : "memory");
+            if (ch < 4 && ew == 0 && lane == 0) TS(22 + 4 * ch);
         }
+        if (ew == 0 && lane == 0) TS(40);
         // ----- hand the second half's top-3 to the first, largest code norm -----
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) hmax = fmaxf(hmax, __shfl_xor_sync(0xffffffffu, hmax, o));
@@ -324,9 +344,35 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
                 for (int j = 0; j < 4; j++) zreg[j] = (j < per && lane + 32 * j < D) ? zr[lane + 32 * j] : 0.f;
                 float bd = INFINITY;
                 int bk = 0x7fffffff;
-                const int total = ov ? K : 2;
-                for (int c = 0; c < total; c++) {
-                    const int k = ov ? c : (c == 0 ? c0k : c1k);
+                if (ov) {
+                    // a third code inside the window (~1e-5 of the frames): exact search of the whole codebook, the lanes
+                    // splitting the codes (a lane's codes ascend, so its ties keep the lowest index)
+                    const float4* z4 = reinterpret_cast<const float4*>(zr);
+                    for (int k = lane; k < K; k += 32) {
+                        const float4* er4 = reinterpret_cast<const float4*>(a.e_hat + (size_t)k * D);
+                        float d0 = 0.f, d1 = 0.f, d2 = 0.f, d3 = 0.f;
+                        for (int j = 0; j < (D >> 2); j++) {
+                            const float4 e = __ldg(er4 + j), zz = z4[j];
+                            d0 = fmaf(zz.x, e.x, d0); d1 = fmaf(zz.y, e.y, d1); d2 = fmaf(zz.z, e.z, d2); d3 = fmaf(zz.w, e.w, d3);
+                        }
+                        const float dist = (zs + __ldg(a.e_sq + k)) - 2.f * ((d0 + d1) + (d2 + d3));
+                        if (dist < bd) {
+                            bd = dist;
+                            bk = k;
+                        }
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {
+                        const float od = __shfl_xor_sync(0xffffffffu, bd, o);
+                        const int ok2 = __shfl_xor_sync(0xffffffffu, bk, o);
+                        if (od < bd || (od == bd && ok2 < bk)) {
+                            bd = od;
+                            bk = ok2;
+                        }
+                    }
+                }
+                for (int c = 0; c < (ov ? 0 : 2); c++) {
+                    const int k = c == 0 ? c0k : c1k;
                     const float* er = a.e_hat + (size_t)k * D;
                     float dot = 0.f;
 #pragma unroll
@@ -354,6 +400,7 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
             }
         }
         named_bar_sync(1, 32 * VQF_EPI_WARPS);
+        if (ew == 0 && lane == 0) TS(41);
         // ----- gather the winning rows, loss sum: 16 frames per warp, float4 lanes, loads of four passes in flight -----
         {
             const int L = D >> 2, fpp = 32 / L, sub = lane / L, l = lane % L;
@@ -386,9 +433,11 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
                 if (lane == 0) atomicAdd(&a.sums[0], lq);
             }
         }
+        if (ew == 0 && lane == 0) TS(43);
     }
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) TS(42);
     if (warp == 1) {
         __syncwarp();
         tc_fence_after();
@@ -400,15 +449,17 @@ vq_fused_kernel(const __grid_constant__ CUtensorMap map_e, const VqFusedArgs a) 
 int vq_fused_tc(const float* z, int B, int D, int T, int normalize, const float* e_hat, const void* e_planes, const float* e_sq,
                 int K, float* zn_out, float* z_norm_out, int64_t* idx, float* q_out, float* sums, int* counts, cudaStream_t st) {
     const int64_t N = (int64_t)B * T;
-    if (!(D == 16 || D == 32 || D == 64 || D == 128) || K < 8 || N > (int64_t)1 << 30) return 1;
+    // K > 8192: the six-product kernel already runs at the tensor roof there and the three-kernel path is as fast
+    // (profiles/r02h_vq_sweep.txt: 0.90x at K 16384 x D 128)
+    if (!(D == 16 || D == 32 || D == 64 || D == 128) || K < 8 || K > 8192 || N > (int64_t)1 << 30) return 1;
     if ((((uintptr_t)z) | ((uintptr_t)zn_out) | ((uintptr_t)q_out)) & 15) return 1;
     if (normalize && !zn_out) return 1;                    // the exact re-rank reads the normalised frames back (L2)
     const int kd = ceil_div(D, VQF_BK);
     const size_t fixed = (size_t)2 * kd * VQF_A_BYTES;
-    const size_t budget = 227 * 1024 - 10 * 1024;          // static shared memory: barriers, per-frame scalars, top-3 hand-over
+    const size_t budget = 104 * 1024;                      // + 7 KB static < 113 KB: two CTAs per SM overlap each other's phases
     int nst = (int)((budget - fixed) / VQF_B_BYTES);
     if (nst < 2) return 1;
-    nst = nst > 6 ? 6 : nst;
+    nst = nst > 4 ? 4 : nst;
     const size_t smem = fixed + (size_t)nst * VQF_B_BYTES + 1024;
     static size_t smem_set = 0;
     if (smem > smem_set) {
@@ -424,7 +475,7 @@ int vq_fused_tc(const float* z, int B, int D, int T, int normalize, const float*
     // hi and mid are planes 0 and 1 of the (3, K, Dp) codebook planes
     if (!make_tmap_3d(&me, e_planes, (uint64_t)D, (uint64_t)K, 2, (uint64_t)Dp * 2, (uint64_t)K * Dp * 2, VQF_BK, VQF_BN, 1))
         return VNB_E_CUDA;
-    VqFusedArgs a{N, D, K, normalize, nst, z, e_hat, e_sq, zn_out, z_norm_out, idx, q_out, sums, counts};
+    VqFusedArgs a{N, D, K, normalize, nst, option(VNB_OPT_TC_DBG), z, e_hat, e_sq, zn_out, z_norm_out, idx, q_out, sums, counts};
     vnb::launch_k(vq_fused_kernel, ceil_div(N, VQF_BM), VQF_THREADS, smem, st, me, a);
     VNB_LAUNCH_CHECK("vq_fused");
     return VNB_OK;

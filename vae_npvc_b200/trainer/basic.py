@@ -19,6 +19,7 @@ New optional config keys (defaults keep the reference behaviour): ``cuda_graph``
 ``graph_warmup`` (3), ``precision`` ('bf16' | 'bf16x2' | 'fp32'), ``device`` ('cuda'), ``wgrad_stream`` (True),
 ``bank_overlap`` (True), ``sparse_grad_zero`` (True), ``jitter_draws`` ('device' on CUDA | 'host').
 """
+import os
 import contextlib
 from importlib import import_module
 
@@ -182,7 +183,11 @@ class Trainer(object):
         if jit is not None and hasattr(jit, 'draws'):
             jit.draws = str(config.get('jitter_draws', 'device' if self.device.type == 'cuda' else 'host'))
         # bucketed all-reduce: trigger name (model/vqvae.py set_grad_ready_callback) -> slice of the flat buffers
-        self._comm = torch.cuda.Stream(device=self.device) if self._side_wanted() else None
+        # its CTAs are placed ahead of the queued GEMM CTAs (stream priority, kept by graph capture): the collective's
+        # progress beside backward sets the exposed tail (profiles/r02g_dp_sweep.txt)
+        self._comm = (torch.cuda.Stream(device=self.device, priority=int(config.get('comm_priority',
+                                                                                  os.environ.get('VNB_COMM_PRIO', -1))))
+                      if self._side_wanted() else None)
         # gradient slices all-reduced while backward still runs: (decoder, encoder) counts; what is left after the
         # last one (the lowest encoder group, codebook, speaker table, conditioning convs) follows backward
         self._n_buckets = tuple(config.get('allreduce_buckets', (6, 6)))     # measured best at 2 and 8 GPUs (profiles/r02g_*)
