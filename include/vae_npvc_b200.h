@@ -155,6 +155,17 @@ int vnb_concat_planes(const float* xa, int Ca, const float* xb, int Cb, int B, i
 int vnb_gn_stats_ws_floats(int B, int groups);
 int vnb_gn_stats(const float* h, int B, int C, int T, int groups, float eps, float* ws, float* mean,
                  float* rstd, void* stream);
+/* vnb_gn_stats WITHOUT a caller-provided workspace.  No counterpart in the reference: added
+ * for callers that cannot allocate device memory (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  The chunk-wise workspace is a file-scope static __device__ array of
+ * vnb_gn_stats_static_max_floats() = 65536 floats (256 KB, held by every GPU that loads the library until exit);
+ * shapes with B * groups > 512 are rejected with VNB_E_ARG (use vnb_gn_stats).  The call allocates nothing and
+ * returns what vnb_gn_stats returns (to fp32 rounding: the chunk sums use float atomics).  ALL calls share the one array (it keeps the last call's
+ * contents; nothing in it needs clearing): calls that overlap on the GPU - different streams without an ordering
+ * between them - race. */
+int vnb_gn_stats_static_max_floats(void);
+int vnb_gn_stats_static(const float* h, int B, int C, int T, int groups, float eps, float* mean, float* rstd,
+                        void* stream);
 /* encoder residual block epilogue (layers.py:176): y = GN1(h)*gamma+beta (+ s); optional outputs:
  * y fp32, planes of y, planes of LeakyReLU_0.2(y) */
 int vnb_enc_out(const float* h, const float* s, const float* mean, const float* rstd,

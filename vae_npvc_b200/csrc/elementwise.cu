@@ -390,6 +390,52 @@ extern "C" int vnb_gn_stats(const float* h, int B, int C, int T, int groups, flo
     return VNB_OK;
 }
 
+// ---- vnb_gn_stats without a caller-provided workspace (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA-graph capture, serving loops).  The chunk-wise mean / M2
+// workspace lives in this file-scope device array: 256 KB held by every GPU that loads the library, until exit.
+// Every call shares it: calls that overlap on the GPU (different streams, no ordering between them) RACE.  Nothing
+// in it has to start at zero - gn_stats_partial_kernel writes every (sample, group, chunk) entry the merge reads.
+constexpr int GN_STATIC_WS_FLOATS = 65536;
+static __device__ __align__(256) float g_gn_static_ws[GN_STATIC_WS_FLOATS];
+
+// host side: the symbol's name is NOT a device address - resolve it once per device, with that device current
+static float* gn_static_ws_ptr() {
+    constexpr int MAX_DEV = 64;
+    static float* ptrs[MAX_DEV] = {};
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+        set_error("gn_stats_static: cudaGetDevice failed or device index >= %d", MAX_DEV);
+        return nullptr;
+    }
+    float* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_gn_static_ws);
+        if (e != cudaSuccess || !p) {
+            set_error("gn_stats_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return nullptr;
+        }
+        __atomic_store_n(&ptrs[dev], p, __ATOMIC_RELEASE);     // every thread resolves the same address: benign if two race here
+    }
+    return p;
+}
+
+extern "C" int vnb_gn_stats_static_max_floats(void) { return GN_STATIC_WS_FLOATS; }
+
+extern "C" int vnb_gn_stats_static(const float* h, int B, int C, int T, int groups, float eps, float* mean, float* rstd,
+                                   void* stream) {
+    VNB_REQUIRE(B > 0 && groups > 0 && groups <= GN_MAX_GROUPS, "gn_stats_static: bad arguments");
+    const int64_t need = (int64_t)B * groups * GN_MAX_CHUNKS * 2;
+    if (need > GN_STATIC_WS_FLOATS) {
+        set_error("gn_stats_static: B * groups = %lld needs %lld workspace floats, the static workspace holds %d "
+                  "(B * groups <= %d); use vnb_gn_stats with a caller-provided workspace",
+                  (long long)B * groups, (long long)need, GN_STATIC_WS_FLOATS, GN_STATIC_WS_FLOATS / (GN_MAX_CHUNKS * 2));
+        return VNB_E_ARG;
+    }
+    float* ws = gn_static_ws_ptr();
+    if (!ws) return VNB_E_CUDA;
+    return vnb_gn_stats(h, B, C, T, groups, eps, ws, mean, rstd, stream);
+}
+
 extern "C" int vnb_gn_finalize(const double* gn_sums, int BG, double n, float eps, float* mean, float* rstd,
                                void* stream) {
     VNB_REQUIRE(gn_sums && mean && rstd && BG > 0 && n > 0, "gn_finalize: bad arguments");
