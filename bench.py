@@ -475,9 +475,10 @@ def run_ours(args, rank, world):
                          % (min(B, 128), T, {0: 'auto', 1: 'simt', 2: 'tc'}[_C.get_backend()]),
                          'achieved': kflops / kdt / 1e12, 'peak': pk['tf_burst'], 'unit': 'TFLOP/s',
                          'frac': kflops / kdt / 1e12 / pk['tf_burst'],
-                         # dram__bytes_read.sum + dram__bytes_write.sum of this launch from the ncu --set full capture
-                         # (profiles/r01_ncu_conv_fwd_dominant.txt): the bf16 operands once, the output stays in L2
-                         'traffic': 5278464 if (P == 1 and B * T == 2048) else None,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of this launch from the ncu --set full captures
+                         # (P 1: profiles/r01_ncu_conv_fwd_dominant.txt, P 2: profiles/r02i_ncu_conv_fwd_dominant.txt):
+                         # the bf16 operand planes once, the fp32 output stays in L2
+                         'traffic': ({1: 5278464, 2: 10530000}.get(P) if B * T == 2048 and args.workload == 'vcc2020' else None),
                          'executed_tflops': kexec / kdt / 1e12, 'peak_source': pk['src'], 'kernel_ms': kdt * 1e3},
         }
         if world == 1 and not args.no_cpu_baseline and wl['kind'] != 'cdvae':
