@@ -352,6 +352,26 @@ int vnb_csid(const int64_t* idx, int B, int T, const int* lengths, int64_t* out,
 int vnb_allreduce_multimem(void* mc_base, int64_t offset, int64_t count, const void* flags, int rank, int world,
                            float scale, int nblocks, void* stream);
 
+/* ---- hierarchical VQ-VAE2 + global style tokens (vqvae2.py, layers_gst.py).  Channels-last rows.
+ * The strided down-sampling convs (vqvae2.py:204-212) need no entry of their own: a stride-s, kernel-2s conv on
+ * channels-last frames is vnb_conv_fwd with 3 taps over rows of s frames (functional.strided_conv1d). */
+/* out[b, t, off + c] = src[b, min(t / (T / Ts), Ts - 1), c]: Model.upsample (vqvae2.py:130-143: repeat each frame
+ * T // Ts times, cut or pad with the last frame) written into the channel slice [off, off + C) of the (B, T, Ct)
+ * concatenation (vqvae2.py:104,110,114).  C, Ct, off multiples of 4. */
+int vnb_upsample_cat_fwd(const float* src, int B, int C, int Ts, float* out, int Ct, int off, int T, void* stream);
+/* dsrc[b, ts, c] = sum of dout[b, t, off + c] over the frames t that read (b, ts, c) */
+int vnb_upsample_cat_bwd(const float* dout, int B, int Ct, int off, int T, float* dsrc, int C, int Ts, void* stream);
+/* out[b, c] = mean_t x[b, t, c] (vqvae2.py:96) and its backward dx[b, t, c] = dy[b, c] / T */
+int vnb_time_mean_fwd(const float* x, int B, int C, int T, float* out, void* stream);
+int vnb_time_mean_bwd(const float* dy, int B, int C, int T, float* dx, void* stream);
+/* style-token attention core (layers_gst.py:128-147, one query per utterance, no mask, dropout 0):
+ * q (B, H*dk), K, V (N, H*dk) -> attn (B, H, N) = softmax_n(q_h . K_nh / sqrt(dk)), ctx (B, H*dk) = attn V.  N <= 32. */
+int vnb_gst_attn_fwd(const float* q, const float* K, const float* V, int B, int N, int H, int dk, float* attn,
+                     float* ctx, void* stream);
+/* backward: ds (B, H, N) scratch; dq (B, H*dk); dK, dV (N, H*dk) summed over the batch (deterministic order) */
+int vnb_gst_attn_bwd(const float* dctx, const float* q, const float* K, const float* V, const float* attn, int B,
+                     int N, int H, int dk, float* ds, float* dq, float* dK, float* dV, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -615,3 +615,52 @@ def adam_step(p, g, m, v, sqn, max_norm, lr, beta1, beta2, eps, state, step_size
     p.sub_((lr_t / (1 - beta1 ** t)) * m / (v.sqrt() / math.sqrt(1 - beta2 ** t) + eps))
     state[0] += 1
     state[1] += 1
+
+
+# ---- hierarchical VQ-VAE2 + style tokens (csrc/hier.cu; vqvae2.py:96,104-114,130-143; layers_gst.py:128-147) --------
+def _up_index(T, Ts):
+    return torch.clamp(torch.arange(T) // (T // Ts), max=Ts - 1)
+
+
+def upsample_cat_fwd(srcs, T):
+    return torch.cat([s[:, :, _up_index(T, s.shape[2])] for s in srcs], dim=1)
+
+
+def upsample_cat_bwd(dout, shapes):
+    B, Ct, T = dout.shape
+    outs, off = [], 0
+    for C, Ts in shapes:
+        d = torch.zeros(B, C, Ts, dtype=dout.dtype)
+        d.index_add_(2, _up_index(T, Ts), dout[:, off:off + C])
+        outs.append(d)
+        off += C
+    return outs
+
+
+def time_mean_fwd(x):
+    return x.mean(dim=2)
+
+
+def time_mean_bwd(dy, T):
+    return (dy / T).unsqueeze(2).expand(-1, -1, T).contiguous()
+
+
+def gst_attn_fwd(q, K, V, H):
+    B, Fd = q.shape
+    N, dk = K.shape[0], Fd // H
+    s = torch.einsum('bhd,nhd->bhn', q.view(B, H, dk), K.view(N, H, dk)) / math.sqrt(dk)
+    attn = torch.softmax(s, dim=-1)
+    return attn, torch.einsum('bhn,nhd->bhd', attn, V.view(N, H, dk)).reshape(B, Fd)
+
+
+def gst_attn_bwd(dctx, q, K, V, attn):
+    B, H, N = attn.shape
+    Fd = q.shape[1]
+    dk = Fd // H
+    dc, qh, Kh, Vh = dctx.view(B, H, dk), q.view(B, H, dk), K.view(N, H, dk), V.view(N, H, dk)
+    da = torch.einsum('bhd,nhd->bhn', dc, Vh)
+    ds = attn * (da - (attn * da).sum(-1, keepdim=True))
+    dq = torch.einsum('bhn,nhd->bhd', ds, Kh).reshape(B, Fd) / math.sqrt(dk)
+    dK = torch.einsum('bhn,bhd->nhd', ds, qh).reshape(N, Fd) / math.sqrt(dk)
+    dV = torch.einsum('bhn,bhd->nhd', attn, dc).reshape(N, Fd)
+    return dq, dK, dV

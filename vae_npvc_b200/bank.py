@@ -60,6 +60,8 @@ class WeightBank(object):
                 v, g = m.weight, None
             if not (base <= v.data_ptr() < end) or (g is not None and not (base <= g.data_ptr() < end)):
                 continue                                  # not a flat-buffer parameter (frozen / foreign)
+            if getattr(m, '_vnb_no_bank', False):
+                continue                                  # strided conv (model/vqvae2.py): its operand is a re-laid view
             transposed = isinstance(m, nn.ConvTranspose1d)
             d0, d1, k = v.shape
             co, ci = (d1, d0) if transposed else (d0, d1)

@@ -671,3 +671,100 @@ class EmbedFn(Function):
         slot = _slot(table)                    # zeroed by the trainer's flat-gradient memset
         dt = Pm.embed_bwd(dout, idx, ctx.rows, slot)
         return (None if slot is not None else dt), None
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# hierarchical VQ-VAE2 + global style tokens (vae_npvc/model/vqvae2.py, layers_gst.py)
+# ---------------------------------------------------------------------------------------------------------------
+def strided_conv1d(x, v, g, bias, s, act=ACT_NONE, P=None):
+    """The down-sampling conv of a vqvae2 Encoder stage (vqvae2.py:204-212): kernel 2s, stride s, padding s/2 (s even).
+
+    On channels-last frames no strided kernel is needed: the (B, T, C) buffer viewed as (B, T/s, s*C) - rows of s
+    consecutive frames, a free view - turns the conv into a 3-TAP STRIDE-1 'same' conv with s*C input channels.  Output
+    frame t reads input frames s*t - s/2 ... s*t + 3s/2 - 1, i.e. the upper half of row t-1, all of row t and the lower
+    half of row t+1:
+        v'[o, j*C + c, dr + 1] = v[o, c, s*dr + j + s/2]   where that tap exists, else 0        (dr in -1..1, j in 0..s-1)
+    The zeros do not change the weight-norm (||v'|| = ||v||), the conv's own zero padding of one row each side is the
+    reference's padding of s/2 frames, and the re-laid weight is a (differentiable) pad + permute of the parameter, so
+    the existing tcgen05 conv, its data gradient and its weight-gradient GEMM serve (1.5x the FLOPs of the 2s taps).
+    ``act`` is applied to x first (the previous stage's LeakyReLU, vqvae2.py:226)."""
+    assert s >= 2 and s % 2 == 0, 'down-sampling scales of the shipped recipe are 2 and 4 (even)'
+    B, C, T = x.shape
+    if T % s != 0:
+        raise NotImplementedError('vae_npvc_b200: strided conv needs a frame count divisible by the stride (got T=%d, s=%d)' % (T, s))
+    Cout, Cin, k = v.shape
+    assert k == 2 * s and Cin == C
+    p = s // 2
+    vp = torch.nn.functional.pad(v, (s - p, p))                                    # (Cout, C, 3s): tap index m + s - p
+    v3 = vp.view(Cout, C, 3, s).permute(0, 3, 1, 2).reshape(Cout, s * C, 3)         # [o, j*C + c, dr + 1]
+    xt = x.transpose(1, 2)                                                           # physical (B, T, C) of a channels-last x
+    if not xt.is_contiguous():
+        xt = xt.contiguous()                                                         # (autograd-aware copy of a foreign layout)
+    rows = xt.reshape(B, T // s, s * C).transpose(1, 2)                              # logical (B, s*C, T/s), channels-last
+    return conv1d(rows, v3, g, bias, False, 1, act, 1.0, P)
+
+
+class UpsampleCatFn(Function):
+    """torch.cat([upsample(z_i, T) for i], dim=1) (vqvae2.py:104-114, 130-143) in one pass per source."""
+
+    @staticmethod
+    def forward(ctx, T, *srcs):
+        srcs = [Pm.as_cl(s) for s in srcs]
+        ctx.shapes = [(s.shape[1], s.shape[2]) for s in srcs]
+        return Pm.upsample_cat_fwd(srcs, T)
+
+    @staticmethod
+    def backward(ctx, dout):
+        return (None,) + tuple(Pm.upsample_cat_bwd(Pm.as_cl(dout), ctx.shapes))
+
+
+def upsample_cat(srcs, T):
+    return UpsampleCatFn.apply(T, *srcs)
+
+
+class TimeMeanFn(Function):
+    """z.mean(dim=-1) (vqvae2.py:96): (B, C, T) -> (B, C)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        x = Pm.as_cl(x)
+        ctx.T = x.shape[2]
+        return Pm.time_mean_fwd(x)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return Pm.time_mean_bwd(dy.contiguous(), ctx.T)
+
+
+class LinearFn(Function):
+    """torch.nn.Linear on (rows, in) (layers_gst.py:94-96, 137)."""
+
+    @staticmethod
+    def forward(ctx, x, W, b):
+        x = x.contiguous()
+        ctx.save_for_backward(x, W)
+        return Pm.linear_fwd(x, W, b)
+
+    @staticmethod
+    def backward(ctx, dp):
+        x, W = ctx.saved_tensors
+        dp = dp.contiguous()
+        dW, dx = Pm.linear_bwd(dp, x, W)
+        return dx, dW, Pm.channel_sum(dp.unsqueeze(0).transpose(1, 2))         # bias gradient: column sums of dp
+
+
+class GstAttnFn(Function):
+    """softmax(q K^T / sqrt(dk)) V per head, one query per utterance (layers_gst.py:128-147)."""
+
+    @staticmethod
+    def forward(ctx, q, K, V, H):
+        q, K, V = q.contiguous(), K.contiguous(), V.contiguous()
+        attn, out = Pm.gst_attn_fwd(q, K, V, H)
+        ctx.save_for_backward(q, K, V, attn)
+        return out
+
+    @staticmethod
+    def backward(ctx, dctx):
+        q, K, V, attn = ctx.saved_tensors
+        dq, dK, dV = Pm.gst_attn_bwd(dctx.contiguous(), q, K, V, attn)
+        return dq, dK, dV, None

@@ -616,3 +616,62 @@ def sqnorm(g, acc):
 
 def adam_step(p, g, m, v, sqn, max_norm, lr, beta1, beta2, eps, state, step_size, gamma):
     _C.call('adam_step', p, g, m, v, p.numel(), sqn, max_norm, lr, beta1, beta2, eps, state, step_size, gamma)
+
+
+# --------------------------------------------------------------------------------------------
+# hierarchical VQ-VAE2 + style tokens (csrc/hier.cu)
+# --------------------------------------------------------------------------------------------
+def upsample_cat_fwd(srcs, T):
+    """Channel concatenation of nearest-neighbour upsampled sources (vqvae2.py:104-114, 130-143):
+    srcs = [(B, C_i, T_i) channels-last, T_i <= T] -> (B, sum C_i, T) channels-last."""
+    B = srcs[0].shape[0]
+    Ct = sum(s.shape[1] for s in srcs)
+    out = cl_empty(B, Ct, T, srcs[0].device)
+    off = 0
+    for s in srcs:
+        _, C, Ts = s.shape
+        _C.call('upsample_cat_fwd', _r(s), B, C, Ts, _r(out), Ct, off, T)
+        off += C
+    return out
+
+
+def upsample_cat_bwd(dout, shapes):
+    """-> [d src_i (B, C_i, T_i)] for ``shapes`` = [(C_i, T_i)]"""
+    B, Ct, T = dout.shape
+    outs, off = [], 0
+    for C, Ts in shapes:
+        d = cl_empty(B, C, Ts, dout.device)
+        _C.call('upsample_cat_bwd', _r(dout), B, Ct, off, T, _r(d), C, Ts)
+        outs.append(d)
+        off += C
+    return outs
+
+
+def time_mean_fwd(x):
+    B, C, T = x.shape
+    out = _f32((B, C), x)
+    _C.call('time_mean_fwd', _r(x), B, C, T, out)
+    return out
+
+
+def time_mean_bwd(dy, T):
+    B, C = dy.shape
+    dx = cl_empty(B, C, T, dy.device)
+    _C.call('time_mean_bwd', dy, B, C, T, _r(dx))
+    return dx
+
+
+def gst_attn_fwd(q, K, V, H):
+    B, F = q.shape
+    N = K.shape[0]
+    attn, ctx = _f32((B, H, N), q), _f32((B, F), q)
+    _C.call('gst_attn_fwd', q, K, V, B, N, H, F // H, attn, ctx)
+    return attn, ctx
+
+
+def gst_attn_bwd(dctx, q, K, V, attn):
+    B, H, N = attn.shape
+    F = q.shape[1]
+    ds, dq, dK, dV = _f32((B, H, N), q), _f32((B, F), q), _f32((N, F), q), _f32((N, F), q)
+    _C.call('gst_attn_bwd', dctx, q, K, V, attn, B, N, H, F // H, ds, dq, dK, dV)
+    return dq, dK, dV

@@ -178,3 +178,77 @@ def conv_macs_per_frame(enc, dec, T):
         d += st * (cout * 2 * cout * dec.get('stack_kernel_size', 3) + cout * (cout + S)) + st * Y * 2 * cout / T
     d += S * S + S * dec['final_channels']
     return e, d
+
+
+# ---- hierarchical VQ-VAE2 + style tokens (egs/vcc20/vae2/conf/train_pytorch_vqvae2.yaml:28-127) ---------------------
+def vqvae2_config(X=80, C=512, D=128, K=512, Y=128, S=128, y_num=117, stacks=(6, 3, 3), dec_stacks=(10, 6, 6),
+                  tokens=10, heads=4, scales=((1,), (2, 2), (4, 4))):
+    """The shipped three-level recipe (defaults) or a scaled-down model of the same topology."""
+    def enc(cin, n_stage, ds, st):
+        return {'in_channels': [cin] + [C] * (n_stage - 1), 'out_channels': [C] * n_stage, 'kernel_size': 3,
+                'downsample_scales': list(ds), 'z_channels': D, 'dilation': False, 'stack_kernel_size': 3,
+                'stack_layers': 1, 'stacks': [st] * n_stage, 'use_weight_norm': True, 'use_causal_conv': False}
+
+    def dec(cin, cond, final, st):
+        return {'in_channels': [cin], 'out_channels': [C], 'cond_channels': cond, 'skip_channels': S,
+                'final_channels': final, 'kernel_size': 3, 'upsample_scales': [1], 'dilation': False,
+                'stack_kernel_size': 3, 'stacks': [st], 'use_weight_norm': True, 'use_causal_conv': False}
+    return {
+        'model_type': 'vae_npvc.model.vqvae2', 'levels': 3, 'y_dim': Y, 'y_num': y_num, 'beta': 0.01, 'use_gst': True,
+        'use_ema': False, 'jitter_p': 0.0,
+        'encoder.0': enc(X, len(scales[0]), scales[0], stacks[0]),
+        'encoder.1': enc(C, len(scales[1]), scales[1], stacks[1]),
+        'encoder.2': enc(C, len(scales[2]), scales[2], stacks[2]),
+        'quantizer.0': {'z_dim': D, 'z_num': K, 'normalize': True},
+        'quantizer.1': {'z_dim': D, 'z_num': K, 'normalize': True},
+        'quantizer.2': {'ref_embed_dim': D, 'gst_tokens': tokens, 'gst_token_dim': D, 'gst_heads': heads},
+        'decoder.0': dec(3 * D, Y, X, dec_stacks[0]),
+        'decoder.1': dec(D, 2 * D, D, dec_stacks[1]),
+        'decoder.2': dec(D, D, D, dec_stacks[2]),
+    }
+
+
+def vqvae2_small_config():
+    return vqvae2_config(X=8, C=16, D=8, K=32, Y=8, S=12, y_num=5, stacks=(2, 1, 1), dec_stacks=(2, 2, 1), tokens=5, heads=2)
+
+
+def vqvae2_state_dict(arch, seed=777):
+    """Seeded weights keyed like ``vqvae2.Model.state_dict()`` (the key list and shapes come from the mirror model,
+    whose sub-module names are the reference's)."""
+    from .model.vqvae2 import Model
+    shapes = {k: tuple(v.shape) for k, v in Model(arch).state_dict().items()}
+    gen = torch.Generator().manual_seed(seed)
+    sd = {}
+    for k, shp in shapes.items():
+        if k.endswith('.weight_g'):
+            continue                                            # written with its weight_v
+        if k.endswith('.weight_v'):
+            pre = k[:-len('.weight_v')]
+            transposed = '.conv_in' in k or (k.startswith('decoders.') and '.layers.' in k and k.count('.') == 4)
+            fan_in = (shp[0] if transposed else shp[1]) * shp[2]
+            bound = 1.0 / math.sqrt(fan_in)
+            v = (torch.rand(*shp, generator=gen) * 2 - 1) * bound
+            sd[pre + '.weight_g'] = v.pow(2).sum(dim=(1, 2), keepdim=True).sqrt() * (0.8 + 0.4 * torch.rand(shp[0], 1, 1, generator=gen))
+            sd[k] = v
+        elif k.endswith('.embeddings'):
+            e = torch.randn(*shp, generator=gen)
+            sd[k] = e / e.norm(dim=1, keepdim=True)
+        elif k.endswith('gst_embs') or k.endswith('_embedding.weight'):
+            sd[k] = torch.randn(*shp, generator=gen)
+        elif '.mha.' in k:
+            fan_in = shapes[k.rsplit('.', 1)[0] + '.weight'][1]
+            sd[k] = (torch.rand(*shp, generator=gen) * 2 - 1) / math.sqrt(fan_in)
+        elif k.endswith('.weight'):                             # GroupNorm scale
+            sd[k] = 1.0 + 0.1 * torch.randn(*shp, generator=gen)
+        elif k.endswith('.bias'):
+            sd[k] = 0.1 * (torch.rand(*shp, generator=gen) * 2 - 1)
+        else:
+            raise KeyError('vqvae2_state_dict: unexpected key %s' % k)
+    return {k: sd[k] for k in shapes}
+
+
+def vqvae2_batch(arch, B, T, seed=777):
+    gen = torch.Generator().manual_seed(seed)
+    x = torch.randn(B, arch['encoder.0']['in_channels'][0], T, generator=gen)
+    y = torch.randint(0, arch['y_num'], (B, 1), generator=gen)
+    return x, y
