@@ -49,6 +49,11 @@ def _wl(name):
         arch = synth.arch_config(X=80, C=512, D=64, K=512, Y=128, S=128, y_num=117, stacks=10)
         return dict(arch=arch, B=64, T=512, kind='decode', what='decoder-only batched conversion (BASELINE configs[4]): '
                     'Model.decode((ids 64x512, speaker ids)) -> 80-mel, VCC2020-shape decoder')
+    if name == 'vqvae2':
+        arch = synth.vqvae2_config()
+        return dict(arch=arch, B=32, T=256, kind='vqvae2', what='hierarchical VQ-VAE2 + global style tokens as shipped '
+                    '(egs/vcc20/vae2/conf/train_pytorch_vqvae2.yaml; SURVEY 8 f4): 80-mel, three levels (strides 1 / 2x2 / 4x4), '
+                    'two 512x128 codebooks + 10 style tokens, 32x256 frames per GPU (recipe batch 96x256 on 3 GPUs), Adam+clip+StepLR')
     raise SystemExit('unknown workload %r' % name)
 
 
@@ -57,6 +62,8 @@ def flop_per_frame(wl):
     distance GEMM forward only."""
     from vae_npvc_b200 import synth
     a, T = wl['arch'], wl['T']
+    if wl['kind'] == 'vqvae2':
+        return None                                # per-level frame rates differ; no single per-frame figure is quoted
     vq = 2 * a['z_num'] * a['z_dim']
     if wl['kind'] == 'cdvae':
         macs, n = 0, 0
@@ -170,10 +177,15 @@ def reference_step_rate(wl, steps, warmup, device='cpu', autocast=False, threads
     arch = wl['arch']
     B, T = wl['B'], wl['T']
     cfg = dict(arch)
-    cfg.update(model_type='vae_npvc.model.vqvae', optim_type='Adam', learning_rate=1e-3, max_grad_norm=10,
-               lr_scheduler='StepLR', lr_param={'step_size': 100000, 'gamma': 0.5, 'last_epoch': -1})
-    sd = synth.synthetic_state_dict(arch, 777)
-    x, y = synth.synthetic_batch(arch, B, T, 777)
+    v2 = wl['kind'] == 'vqvae2'
+    cfg.update(model_type='vae_npvc.model.vqvae2' if v2 else 'vae_npvc.model.vqvae', optim_type='Adam', learning_rate=1e-3,
+               max_grad_norm=10, lr_scheduler='StepLR', lr_param={'step_size': 100000, 'gamma': 0.5, 'last_epoch': -1})
+    if v2:
+        sd = synth.vqvae2_state_dict(arch, 777)
+        x, y = synth.vqvae2_batch(arch, B, T, 777)
+    else:
+        sd = synth.synthetic_state_dict(arch, 777)
+        x, y = synth.synthetic_batch(arch, B, T, 777)
     cores = threads or os.cpu_count() or 1
     import warnings
     warnings.simplefilter('ignore')
@@ -195,7 +207,7 @@ def reference_step_rate(wl, steps, warmup, device='cpu', autocast=False, threads
     elif device == 'cuda':
         from vae_npvc.trainer.basic import Trainer as RefTrainer
         tr = RefTrainer(cfg)
-        tr.model.load_state_dict(sd)
+        torch.nn.Module.load_state_dict(tr.model, sd)          # (vqvae2's own override reads an undefined attribute)
         xh, yh = x.pin_memory(), y.pin_memory()
         if autocast:
             fwd = tr.model.forward
@@ -206,9 +218,12 @@ def reference_step_rate(wl, steps, warmup, device='cpu', autocast=False, threads
         sync = torch.cuda.synchronize
     else:
         torch.set_num_threads(cores)
-        from vae_npvc.model.vqvae import Model as RefModel
+        if v2:
+            from vae_npvc.model.vqvae2 import Model as RefModel
+        else:
+            from vae_npvc.model.vqvae import Model as RefModel
         m = RefModel(cfg)
-        m.load_state_dict(sd)
+        torch.nn.Module.load_state_dict(m, sd)
         m.train()
         opt = torch.optim.Adam(m.parameters(), lr=1e-3, betas=(0.5, 0.999), weight_decay=0.0)
         sch = torch.optim.lr_scheduler.StepLR(opt, step_size=100000, gamma=0.5)
@@ -256,7 +271,7 @@ def run_reference(args, rank):
     if reference_available():
         fps, dt, cores = reference_step_rate(wl, steps, warm, args.ref_device, args.ref_autocast)
         kind = 'reference'
-        what = ('the reference\'s own vae_npvc.model.vqvae.Model (staged under oracle/_ref)'
+        what = ('the reference\'s own vae_npvc.model.%s.Model (staged under oracle/_ref)' % ('vqvae2' if wl['kind'] == 'vqvae2' else 'vqvae')
                 + (' decode()' if wl['kind'] == 'decode' else ' + trainer/basic.py:55-79 step') + ', '
                 + ('stock eager PyTorch on the B200%s' % (' under bf16 autocast' if args.ref_autocast else ', fp32')
                    if on_gpu else 'torch CPU fp32'))
@@ -376,7 +391,8 @@ def run_ours(args, rank, world):
         tr = None
     else:
         cfg = dict(arch)
-        cfg.update(model_type=arch.get('model_type', 'vae_npvc_b200.model.vqvae') if wl['kind'] == 'cdvae' else 'vae_npvc_b200.model.vqvae',
+        cfg.update(model_type={'cdvae': arch.get('model_type', 'vae_npvc_b200.model.vqvae'),
+                               'vqvae2': 'vae_npvc_b200.model.vqvae2'}.get(wl['kind'], 'vae_npvc_b200.model.vqvae'),
                    precision=args.precision, cuda_graph=not args.no_graph,
                    overlap_allreduce=not bool(os.environ.get('VNB_NO_OVERLAP')), allreduce=os.environ.get('VNB_ALLREDUCE', 'multimem'),
                    allreduce_blocks=int(os.environ.get('VNB_AR_BLOCKS', 0)),
@@ -392,6 +408,10 @@ def run_ours(args, rank, world):
             tr.model.load_state_dict(synth.cdvae_state_dict(arch, 777))
             xs, y = synth.cdvae_batch(arch, B, T, 777 + rank)
             tensors = xs + [y]
+        elif wl['kind'] == 'vqvae2':
+            tr.model.load_state_dict(synth.vqvae2_state_dict(arch, 777))
+            x, y = synth.vqvae2_batch(arch, B, T, 777 + rank)
+            tensors = [x, y]
         else:
             tr.model.load_state_dict(synth.synthetic_state_dict(arch, 777))       # same weights on every rank
             x, y = synth.synthetic_batch(arch, B, T, 777 + rank)                  # each rank its own shard
@@ -467,7 +487,7 @@ def run_ours(args, rank, world):
                        'l2': 'no explicit flush: each step streams params+grads+Adam moments+operand planes '
                              '(~0.7 GB) > 126 MB L2; the isolated-kernel timing flushes L2 with a 256 MB write',
                        'flop_per_frame': fpf,
-                       'step_roofline_frac_tensor': value * fpf / (world * pk['tf_sus'] * 1e12)},
+                       'step_roofline_frac_tensor': (value * fpf / (world * pk['tf_sus'] * 1e12)) if fpf else None},
             'clocks': clocks,
             'e2e': {'value': e2e, 'unit': 'frames/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h},
             'gpu_launches': int(per_step * args.steps),
@@ -485,7 +505,7 @@ def run_ours(args, rank, world):
             big = B * T > 8192
             if reference_available():
                 fps, cdt, cores = reference_step_rate(wl, 2 if big else 8, 1 if big else 2)
-                kind, what = 'reference', "the reference's own vae_npvc.model.vqvae.Model (oracle/_ref)"
+                kind, what = 'reference', "the reference's own vae_npvc.model.%s.Model (oracle/_ref)" % ('vqvae2' if wl['kind'] == 'vqvae2' else 'vqvae')
             elif wl['kind'] == 'vqvae':
                 fps, cdt, cores = cpu_oracle_step_rate(wl, 2 if big else 8, 1 if big else 2)
                 kind, what = 'port', 'oracle restatement of the reference Model + trainer step'
@@ -513,7 +533,7 @@ def main():
     ap.add_argument('--warmup', type=int, default=10)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--precision', default=DEFAULT_PRECISION, choices=['bf16', 'bf16x2', 'fp32'])
-    ap.add_argument('--workload', default='vcc2020', choices=['vcc2020', 'vcc2020_yaml', 'aishell3', 'cdvae', 'decode'],
+    ap.add_argument('--workload', default='vcc2020', choices=['vcc2020', 'vcc2020_yaml', 'aishell3', 'cdvae', 'decode', 'vqvae2'],
                     help='default = BASELINE.json configs[1]; the others are the remaining named workloads')
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-cpu-baseline', action='store_true')
