@@ -268,7 +268,8 @@ int vnb_vq_fused(const float* z, int B, int D, int T, int normalize, const float
                  const float* e_sq, int K, float* zn_out, float* z_norm_out, int64_t* idx, float* q_out,
                  float* sums, int* counts, void* stream);
 /* q = e_hat[idx] -> q_out (B,D,T); sums[0] += sum (q-zn)^2, sums[1] += sum (zn-z)^2;
- * counts[k] += #{idx==k}  (sums, counts must be zeroed by the caller) */
+ * counts[k] += #{idx==k}  (sums, counts must be zeroed by the caller).  zn may be null for a pure gather
+ * (sums and z null): Model.decode, layers_vq.py:62-77 */
 int vnb_vq_gather(const int64_t* idx, const float* e_hat, const float* zn, const float* z, int B, int D,
                   int T, int K, float* q_out, float* sums, int* counts, void* stream);
 /* scal[0]=l_q, scal[1]=l_e, scal[2]=perplexity(eps) from sums/counts; scale = 1/(B*T) etc. */

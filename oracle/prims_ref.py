@@ -490,8 +490,11 @@ def vq_fused(z, normalize, e_hat, e_pl, e_sq, want_q=True, want_stats=True):
     return zn, (z_norm if normalize else None), idx, q, sums, counts
 
 
-def vq_gather(idx, e_hat, zn, z, want_q=True, want_stats=True):
-    B, D, T = zn.shape
+def vq_gather(idx, e_hat, zn, z, want_q=True, want_stats=True, shape=None):
+    if zn is None:
+        (B, T), D = shape, e_hat.shape[1]
+    else:
+        B, D, T = zn.shape
     q = e_hat[idx].view(B, T, D).transpose(1, 2).contiguous()
     sums = counts = None
     if want_stats:

@@ -93,10 +93,13 @@ __global__ void __launch_bounds__(VQ_WARPS * 32) vq_gather_kernel(const int64_t*
         const float* er = e_hat + (int64_t)k * D;
         for (int d = lane; d < D; d += 32) {
             const int64_t o = n * D + d;
-            const float q = er[d], a = zn[o];
+            const float q = er[d];
             if (q_out) q_out[o] = q;
-            lq += (q - a) * (q - a);
-            if (z) ln += (a - z[o]) * (a - z[o]);
+            if (zn) {                                   // null: rows only (Model.decode, layers_vq.py:62-77)
+                const float a = zn[o];
+                lq += (q - a) * (q - a);
+                if (z) ln += (a - z[o]) * (a - z[o]);
+            }
         }
         if (counts && lane == 0) atomicAdd(&counts[k], 1);
     }
@@ -336,7 +339,7 @@ extern "C" int vnb_vq_prep_z(const float* z, int B, int D, int T, int normalize,
 
 extern "C" int vnb_vq_gather(const int64_t* idx, const float* e_hat, const float* zn, const float* z, int B, int D,
                              int T, int K, float* q_out, float* sums, int* counts, void* stream) {
-    VNB_REQUIRE(idx && e_hat && zn && B > 0 && D > 0 && T > 0 && K > 0, "vq_gather: bad arguments");
+    VNB_REQUIRE(idx && e_hat && (zn || (!sums && !z)) && B > 0 && D > 0 && T > 0 && K > 0, "vq_gather: bad arguments (zn may be null only for a pure gather)");
     const int64_t N = (int64_t)B * T;
     vnb::launch_k(vq_gather_kernel, ceil_div(N, VQ_WARPS), VQ_WARPS * 32, 0, (cudaStream_t)stream, idx, e_hat, zn, z, N, D, q_out,
                                                                                         sums, counts);

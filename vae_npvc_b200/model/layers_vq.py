@@ -74,8 +74,7 @@ class VectorQuantizer(nn.Module):
         B, T = z_id.shape
         with torch.no_grad():
             e_hat, _, _ = Pm.vq_prep_codebook(self.embeddings.detach(), bool(self.target_norm), False)
-            q, _, _ = Pm.vq_gather(z_id.contiguous().view(-1), e_hat, _dummy_zn(B, e_hat.shape[1], T, e_hat), None,
-                                   True, False)
+            q, _, _ = Pm.vq_gather(z_id.contiguous().view(-1), e_hat, None, None, True, False, shape=(B, T))
         return q if time_last else q.transpose(1, 2).contiguous()
 
     def forward(self, z, time_last=True):
@@ -129,11 +128,6 @@ class VectorQuantizer(nn.Module):
         if self.normalize is not False:
             s += ', normalize=True'
         return s.format(**self.__dict__)
-
-
-def _dummy_zn(B, D, T, like):
-    # vq_gather needs a zn pointer even when only the gathered rows are wanted
-    return torch.empty((B, D, T), dtype=torch.float32, device=like.device)
 
 
 def _dist_world():
@@ -227,8 +221,7 @@ class EMAVectorQuantizer(nn.Module):
     def decode(self, z_id, time_last=True):
         B, T = z_id.shape
         with torch.no_grad():
-            q, _, _ = Pm.vq_gather(z_id.contiguous().view(-1), self.embeddings,
-                                   _dummy_zn(B, self.z_dim, T, self.embeddings), None, True, False)
+            q, _, _ = Pm.vq_gather(z_id.contiguous().view(-1), self.embeddings, None, None, True, False, shape=(B, T))
         return q if time_last else q.transpose(1, 2).contiguous()
 
     def forward(self, z, time_last=True):

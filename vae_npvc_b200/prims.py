@@ -485,13 +485,19 @@ def vq_fused(z, normalize, e_hat, e_pl, e_sq, want_q=True, want_stats=True):
     return zn, z_norm, idx, q, sums, counts
 
 
-def vq_gather(idx, e_hat, zn, z, want_q=True, want_stats=True):
-    """-> q (B,D,T), sums (2,) [sum (q-zn)^2, sum (zn-z)^2], counts (K,) int32"""
-    B, D, T = zn.shape
-    K = e_hat.shape[0]
-    q = cl_empty(B, D, T, zn.device) if want_q else None
-    sums = torch.zeros((2,), dtype=torch.float32, device=zn.device) if want_stats else None
-    counts = torch.zeros((K,), dtype=torch.int32, device=zn.device) if want_stats else None
+def vq_gather(idx, e_hat, zn, z, want_q=True, want_stats=True, shape=None):
+    """-> q (B,D,T), sums (2,) [sum (q-zn)^2, sum (zn-z)^2], counts (K,) int32.
+    ``zn`` None with ``shape`` = (B, T): rows only (want_stats must be False)."""
+    K, D = e_hat.shape
+    if zn is None:
+        assert shape is not None and not want_stats and z is None
+        B, T = shape
+    else:
+        B, D, T = zn.shape
+    dev = e_hat.device
+    q = cl_empty(B, D, T, dev) if want_q else None
+    sums = torch.zeros((2,), dtype=torch.float32, device=dev) if want_stats else None
+    counts = torch.zeros((K,), dtype=torch.int32, device=dev) if want_stats else None
     _C.call('vq_gather', idx, e_hat, _r(zn), _r(z), B, D, T, K, _r(q), sums, counts)
     return q, sums, counts
 
