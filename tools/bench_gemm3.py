@@ -87,11 +87,11 @@ def main():
 
             fl = 2.0 * B * T * Cin * Cout * taps
             configs = [('v2 (round 1)', 0, 0, -1, 0), ('v3 auto', 2, 0, -1, 0)]
-            if P == 1 or 'conv_in fwd' in name or 'enc k3' in name:
+            if P == 1 or 'conv_in fwd' in name or 'enc k3' in name or os.environ.get('VNB_SWEEP_ALL'):
                 for bn in (64, 128, 256):
                     for pair in (0, 1):
                         configs.append(('v3 BN%d %s' % (bn, 'pair' if pair else 'single'), 2, bn, pair, 0))
-            if P == 1:
+            if P == 1 or os.environ.get('VNB_SWEEP_ALL'):
                 configs += [('v3 BN128 single 100KB', 2, 128, 0, 100), ('v3 BN64 single 100KB', 2, 64, 0, 100),
                             ('v3 BN128 pair 100KB', 2, 128, 1, 100), ('v3 BN64 pair 100KB', 2, 64, 1, 100)]
             for cname, mode, bn, pair, st in configs:
