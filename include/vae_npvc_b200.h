@@ -131,6 +131,13 @@ int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T,
  * sum and sum-of-squares of the final output values per (sample, channel group) - the GroupNorm
  * statistics of layers.py:154,201 without a second pass over the activation.
  * vnb_gn_finalize turns them into mean / rstd (biased variance, eps), n = values per (sample, group) */
+/* vnb_conv_fwd with an activation backward folded into the epilogue (the data gradient of a conv whose input went
+ * through LeakyReLU / ReLU: layers.py:152,165 stack, vqvae.py:281-286 final layers):
+ *   out = mask_scale * conv(in) * act'(mask * mask_scale) [+ residual]      mask, residual, out: (B, T, Cout) fp32
+ * = vnb_conv_fwd followed by vnb_act_bwd_add, without the extra pass over the result. */
+int vnb_conv_fwd_mask(const void* in_planes, int P, int B, int Cin, int T, const void* w_planes, int taps,
+                      int dil, int Cout, const float* residual, float* out, const float* mask, int mask_act,
+                      float mask_scale, void* stream);
 int vnb_gn_finalize(const double* gn_sums, int BG, double n, float eps, float* mean, float* rstd, void* stream);
 /* weight gradient in the reference parameter layout (d0,d1,k):
  * conv tap j: dW[co][ci][j] = sum_{b,t} dy[b,co,t] * u[b,ci,t+(j-(taps-1)/2)*dil];

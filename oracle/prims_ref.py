@@ -390,6 +390,11 @@ def gate_bwd_apply(dg, a, mean, rstd, gamma, beta, S, P):
     return Planes.of(_gn_dpre(dn, xh, rstd, gamma, S, 2), P)
 
 
+def conv_dgrad_act(xpl, w, taps, dil, Cout, mask_src, act, scale=1.0, residual=None):
+    """conv_fwd + act_bwd_add in one call (vnb_conv_fwd_mask)."""
+    return act_bwd_add(conv_fwd(xpl, w, taps, dil, Cout), mask_src, residual, act, scale)
+
+
 def act_bwd_add(du, c, add, act, scale=1.0):
     out = scale * du * _act_grad(c * scale, act)
     return out + add if add is not None else out

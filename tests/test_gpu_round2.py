@@ -500,3 +500,25 @@ def test_vq_fused_leaves_huge_codebooks_to_the_three_kernel_path(fp32_mode):
     from vae_npvc_b200 import prims as Pm
     e_hat, e_pl, e_sq = Pm.vq_prep_codebook(g(16384, 64, seed=2).cuda(), False, False)
     assert Pm.vq_fused(Pm.as_cl(g(2, 64, 33, seed=1).cuda()), False, e_hat, e_pl, e_sq) is None
+
+
+@pytest.mark.parametrize('P', [1, 2, 3])
+@pytest.mark.parametrize('B,Cin,Cout,T,taps', [(16, 512, 512, 128, 3), (4, 128, 80, 128, 1), (3, 24, 20, 37, 3), (16, 1024, 512, 128, 3)])
+def test_conv_with_activation_backward_in_the_epilogue(fp32_mode, P, B, Cin, Cout, T, taps):
+    """vnb_conv_fwd_mask = vnb_conv_fwd followed by vnb_act_bwd_add (full tiles, ragged tiles, cluster split-K shapes),
+    with and without a residual, on both backends."""
+    from vae_npvc_b200 import _C, prims as Pm
+    x = g(B, Cin, T, seed=1).cuda()
+    v = (g(Cout, Cin, taps, seed=2) / (Cin * taps) ** 0.5).cuda()
+    W = Pm.wn_prepare(v, None, False, P)
+    xpl = Pm.make_planes(Pm.as_cl(x), P)[0]
+    m = Pm.as_cl(g(B, Cout, T, seed=3).cuda())
+    res = Pm.as_cl(g(B, Cout, T, seed=4).cuda())
+    for backend in (_C.BACKEND_AUTO, _C.BACKEND_SIMT):
+        _C.set_backend(backend)
+        for act, scale, r in [(Pm.ACT_LRELU, 1.0, None), (Pm.ACT_RELU, 0.5, res), (Pm.ACT_LRELU, 1.0, res)]:
+            want = Pm.act_bwd_add(Pm.conv_fwd(xpl, W.wf, taps, 1, Cout), m, r, act, scale)
+            got = Pm.conv_dgrad_act(xpl, W.wf, taps, 1, Cout, m, act, scale, r)
+            torch.cuda.synchronize()
+            assert rel_err(got, want) < 1e-6, (backend, act, scale, r is not None)
+    assert _C.call('debug_tc_timeouts') == 0

@@ -12,7 +12,8 @@ int vq_lookup_simt(const float* zn, const float* z_sq, const float* e_hat, const
 // tensor-core backend: return VNB_OK, a negative error, or +1 = "shape not taken by this backend"
 int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int taps, int dil, int Cout,
                 const float* bias, int bias_bstride, const float* residual, float* out, int accumulate,
-                double* gn_sums, int gn_groups, cudaStream_t st);
+                double* gn_sums, int gn_groups, cudaStream_t st, const float* mask = nullptr, int mask_act = 0,
+                float mask_scale = 1.f);
 int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin, int T, int taps, int dil,
                   int transposed, float* dw, cudaStream_t st);
 int vq_lookup_tc(const void* z_planes, const float* z_sq, const void* e_planes, const float* e_sq, int B, int D,
@@ -44,6 +45,35 @@ extern "C" int vnb_conv_fwd(const void* in_planes, int P, int B, int Cin, int T,
     }
     return conv_fwd_simt(in_planes, P, B, Cin, T, w_planes, taps, dil, Cout, bias, bias_bstride, residual, out,
                          accumulate, gn_sums, gn_groups, st);
+}
+
+// conv + activation backward in the GEMM epilogue: out = mask_scale * conv(in) * act'(mask * mask_scale) + residual.
+// The data gradient of a conv whose input went through an activation (EncBlockFn / ConvFn backward) then needs no
+// separate vnb_act_bwd_add pass over the result.
+extern "C" int vnb_act_bwd_add(const float* du, const float* c, const float* add, int64_t n, int act, float scale,
+                               float* out, void* stream);
+extern "C" int vnb_conv_fwd_mask(const void* in_planes, int P, int B, int Cin, int T, const void* w_planes, int taps,
+                                 int dil, int Cout, const float* residual, float* out, const float* mask, int mask_act,
+                                 float mask_scale, void* stream) {
+    VNB_REQUIRE(in_planes && w_planes && out && mask, "conv_fwd_mask: null pointer");
+    VNB_REQUIRE(B > 0 && Cin > 0 && Cout > 0 && T > 0, "conv_fwd_mask: bad shape B=%d Cin=%d Cout=%d T=%d", B, Cin, Cout, T);
+    VNB_REQUIRE((P >= 1 && P <= 3) && taps >= 1 && (taps & 1) && dil >= 1, "conv_fwd_mask: P=%d taps=%d dil=%d unsupported", P, taps, dil);
+    VNB_REQUIRE(out != residual && out != mask, "conv_fwd_mask: out must not alias residual / mask");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int be = backend();
+    if (be != VNB_BACKEND_SIMT) {
+        int r = conv_fwd_tc(in_planes, P, B, Cin, T, w_planes, taps, dil, Cout, nullptr, 0, residual, out, 0, nullptr, 0, st,
+                            mask, mask_act, mask_scale);
+        if (r <= 0) return r;
+        if (be == VNB_BACKEND_TC) {
+            set_error("conv_fwd_mask: shape not supported by the tcgen05 backend (Cin=%d Cout=%d T=%d)", Cin, Cout, T);
+            return VNB_E_ARG;
+        }
+    }
+    // SIMT backend: the conv, then the activation backward as its own (in-place, elementwise) pass
+    int r = conv_fwd_simt(in_planes, P, B, Cin, T, w_planes, taps, dil, Cout, nullptr, 0, nullptr, out, 0, nullptr, 0, st);
+    if (r != VNB_OK) return r;
+    return vnb_act_bwd_add(out, mask, residual, (int64_t)B * T * Cout, mask_act, mask_scale, out, stream);
 }
 
 extern "C" int vnb_conv_wgrad(const void* dy_planes, const void* u_planes, int P, int B, int Cout, int Cin, int T,

@@ -64,6 +64,11 @@ struct ConvTcArgs {
     int kch;              // 64-deep k-chunks per pipeline stage (1, or 2 with 4-D tensor maps when Cin % 128 == 0)
     uint32_t recv_off;    // byte offset of the receive slots in dynamic shared memory
     int fast_epi;         // VNB_OPT_FAST_EPI: register epilogue + bulk row stores for full tiles
+    // optional activation backward folded into the epilogue (vnb_conv_fwd_mask): out = mask_scale * acc *
+    // act'(mask * mask_scale) [+ residual / accumulate], mask (B, T, Cout) fp32 = the activation's input
+    const float* mask;
+    int mask_act;
+    float mask_scale;
 };
 
 __device__ __forceinline__ double warp_sum_f64(double v) {
@@ -281,7 +286,7 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     const float* recv = reinterpret_cast<const float*>(smem + a.recv_off);
     const int rows_own = TC_BM / ks, r_base = kr * rows_own;
     // full tile, one k-slice, nothing to add from memory: register epilogue + bulk row stores (see epilogue_regs_bulk)
-    const bool fast_epi = a.fast_epi && ks == 1 && nk > 0 && !a.residual && !a.accumulate && (a.Cout & 3) == 0 &&
+    const bool fast_epi = a.fast_epi && ks == 1 && nk > 0 && !a.residual && !a.accumulate && !a.mask && (a.Cout & 3) == 0 &&
                           co0 + BN <= a.Cout && t0 + TC_BM <= a.T && (!a.gn_sums || ((a.Cout / a.gn_groups) % BN) == 0) &&
                           ((((uintptr_t)a.bias) | ((uintptr_t)a.out) | ((uintptr_t)a.bias_bstride * 4)) & 15) == 0;
     if (fast_epi) {
@@ -343,6 +348,9 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
         const bool vec_ok = (Cout & 3) == 0;
         const bool col_ok = co < Cout;
         const float* __restrict__ resid = a.residual;
+        const float* __restrict__ maskp = a.mask;
+        const int mact = a.mask_act;
+        const float mscale = a.mask_scale;
         float* __restrict__ outp = a.out;
         const bool accum = a.accumulate != 0;
         const float* bias = a.bias ? a.bias + (size_t)b * a.bias_bstride : nullptr;
@@ -376,7 +384,7 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
             const size_t ostep = (size_t)RPP * Cout;
             const uint32_t rstep = RPP * PITCH * 4;
             const uint32_t own0 = own_base + (uint32_t)rsub * (PITCH * 4), recv0 = recv_base + (uint32_t)rsub * (PITCH * 4);
-            if (ks == 1 && !resid && !accum) {
+            if (ks == 1 && !resid && !accum && !maskp) {
 #pragma unroll 4
                 for (int it = 0; it < iters; it++) {
                     const float4 x = ld_shared_f4(own0 + (uint32_t)it * rstep);
@@ -390,13 +398,19 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                 for (int it = 0; it < iters; it++) {
                     float4 v = bv;
                     float4 r1 = make_float4(0.f, 0.f, 0.f, 0.f), u1 = r1;
+                    float4 m1 = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (resid) r1 = *reinterpret_cast<const float4*>(resid + o0 + it * ostep);
                     if (accum) u1 = *reinterpret_cast<const float4*>(outp + o0 + it * ostep);
+                    if (maskp) m1 = *reinterpret_cast<const float4*>(maskp + o0 + it * ostep);
 #pragma unroll 1
                     for (int p = 0; p < ks; p++) {
                         const uint32_t base = p == kr ? own0 : recv0 + (uint32_t)(p < kr ? p : p - 1) * slot_stride;
                         const float4 x = ld_shared_f4(base + (uint32_t)it * rstep);
                         v.x += x.x; v.y += x.y; v.z += x.z; v.w += x.w;
+                    }
+                    if (maskp) {
+                        v.x *= mscale * act_grad(m1.x * mscale, mact); v.y *= mscale * act_grad(m1.y * mscale, mact);
+                        v.z *= mscale * act_grad(m1.z * mscale, mact); v.w *= mscale * act_grad(m1.w * mscale, mact);
                     }
                     v.x += r1.x + u1.x; v.y += r1.y + u1.y; v.z += r1.z + u1.z; v.w += r1.w + u1.w;
                     *reinterpret_cast<float4*>(outp + o0 + it * ostep) = v;
@@ -426,6 +440,15 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                 if (resid && ok2) r2 = *reinterpret_cast<const float4*>(resid + o2);
                 if (accum && ok1) u1 = *reinterpret_cast<const float4*>(outp + o1);
                 if (accum && ok2) u2 = *reinterpret_cast<const float4*>(outp + o2);
+                if (maskp) {
+                    float4 m1 = make_float4(0.f, 0.f, 0.f, 0.f), m2 = m1;
+                    if (ok1) m1 = *reinterpret_cast<const float4*>(maskp + o1);
+                    if (ok2) m2 = *reinterpret_cast<const float4*>(maskp + o2);
+                    acc1.x *= mscale * act_grad(m1.x * mscale, mact); acc1.y *= mscale * act_grad(m1.y * mscale, mact);
+                    acc1.z *= mscale * act_grad(m1.z * mscale, mact); acc1.w *= mscale * act_grad(m1.w * mscale, mact);
+                    acc2.x *= mscale * act_grad(m2.x * mscale, mact); acc2.y *= mscale * act_grad(m2.y * mscale, mact);
+                    acc2.z *= mscale * act_grad(m2.z * mscale, mact); acc2.w *= mscale * act_grad(m2.w * mscale, mact);
+                }
                 acc1.x += r1.x + u1.x; acc1.y += r1.y + u1.y; acc1.z += r1.z + u1.z; acc1.w += r1.w + u1.w;
                 acc2.x += r2.x + u2.x; acc2.y += r2.y + u2.y; acc2.z += r2.z + u2.z; acc2.w += r2.w + u2.w;
                 if (ok1) {
@@ -449,6 +472,7 @@ conv_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                     for (int i = 0; i < 4; i++) {
                         if (co + i < Cout) {
                             float x = vals[i];
+                            if (maskp) x *= mscale * act_grad(maskp[o + i] * mscale, mact);
                             if (resid) x += resid[o + i];
                             if (accum) x += outp[o + i];
                             outp[o + i] = x;
@@ -613,7 +637,7 @@ namespace vnb {
 
 int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int taps, int dil, int Cout,
                 const float* bias, int bias_bstride, const float* residual, float* out, int accumulate,
-                double* gn_sums, int gn_groups, cudaStream_t st) {
+                double* gn_sums, int gn_groups, cudaStream_t st, const float* mask, int mask_act, float mask_scale) {
     // shapes this backend takes; everything else goes to the SIMT backend (or errors under VNB_BACKEND_TC)
     const int64_t mt = (int64_t)ceil_div(T, TC_BM) * B;
     if (Cout < 8 || Cin < 8 || mt > 65535) return 1;
@@ -622,7 +646,7 @@ int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int
     static const int force_bn = getenv("VNB_TC_BN") ? atoi(getenv("VNB_TC_BN")) : 0;
     static const int force_ks = getenv("VNB_TC_KSPLIT") ? atoi(getenv("VNB_TC_KSPLIT")) : 0;
     ConvTcArgs a{B, Cin, Cout, T, taps, dil, P, bias, bias_bstride, residual, out, accumulate, gn_sums, gn_groups, dbg, 0, 1, 0,
-                 option(VNB_OPT_FAST_EPI)};
+                 option(VNB_OPT_FAST_EPI), mask, mask_act, mask_scale};
     const int Cin_p = round_up8(Cin);
     // N tile and cluster split-K: as many CTAs as fit the 148 SMs in one wave (a tcgen05.mma issue costs the same
     // ~70 cycles for a 32-cycle N=64 tile as for a 128-cycle N=256 one, so wide tiles are preferred on a tie),
@@ -664,9 +688,9 @@ int conv_fwd_tc(const void* in, int P, int B, int Cin, int T, const void* w, int
             if (cost < best) { best = cost; bn = cand; ks = k; }
         }
     }
-    {
+    if (!mask) {
         // third-generation kernel (CTA pairs, all operand planes of a chunk per stage) unless the round-1 kernel's
-        // cluster split-K is modelled faster for this shape
+        // cluster split-K is modelled faster for this shape (its epilogue has no activation-backward mask)
         const int r3 = conv_fwd_tc3(in, P, B, Cin, T, w, taps, dil, Cout, bias, bias_bstride, residual, out, accumulate, gn_sums,
                                     gn_groups, (force_bn || force_ks) ? 0 : best, st);
         if (r3 <= 0) return r3;

@@ -209,9 +209,11 @@ class ConvFn(Function):
             dypl = Pm.make_planes(dy, P)[0]
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = Pm.conv_fwd(dypl, ctx.wb, taps, dil, Cin)
             if x is not None:
-                dx = Pm.act_bwd_add(dx, x, None, act, scale)
+                # the activation's backward rides in the data-gradient GEMM's epilogue
+                dx = Pm.conv_dgrad_act(dypl, ctx.wb, taps, dil, Cin, x, act, scale)
+            else:
+                dx = Pm.conv_fwd(dypl, ctx.wb, taps, dil, Cin)
         dv = dg = None
         if ctx.needs_input_grad[1]:
             dv, dg = _wgrad(dypl, ctx.xpl, taps, dil, transposed, v, g)

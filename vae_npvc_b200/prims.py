@@ -346,6 +346,15 @@ def gate_bwd_apply(dg, a, mean, rstd, gamma, beta, S, P):
     return da
 
 
+def conv_dgrad_act(xpl, w, taps, dil, Cout, mask_src, act, scale=1.0, residual=None):
+    """conv_fwd whose epilogue also applies an activation backward: scale * conv(x) * act'(mask_src * scale) + residual
+    (= conv_fwd + act_bwd_add in one kernel)."""
+    out = cl_empty(xpl.B, Cout, xpl.T, xpl.data.device)
+    _C.call('conv_fwd_mask', xpl.data, xpl.P, xpl.B, xpl.C, xpl.T, w, taps, dil, Cout, _r(residual), _r(out), _r(mask_src),
+            act, scale)
+    return out
+
+
 def act_bwd_add(du, c, add, act, scale=1.0):
     B, C, T = du.shape
     out = cl_empty(B, C, T, du.device)
