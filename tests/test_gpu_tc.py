@@ -86,6 +86,8 @@ WGRAD_SHAPES = [
     (2, 128, 80, 64, 1, 1),          # final layer
     (1, 72, 96, 37, 3, 2),           # ragged everything, dilation 2
     (2, 16, 16, 24, 3, 1),           # the small golden model
+    (3, 64, 192, 50, 3, 2),          # tap-fused tiles (columns % 64 == 0) with dilation 2 and ragged T
+    (2, 128, 64, 77, 3, 4),          # tap-fused, rows < 128 when transposed, dilation 4
 ]
 
 

@@ -43,6 +43,13 @@ struct WgradTcArgs {
     // r02b_gemm_sweep_timelines.txt).  P = 3 keeps one pass per plane pair: smallest terms first over the whole
     // reduction is what keeps that mode fp32-faithful.
     int kt, multi;
+    int dbg;                   // VNB_TC_DBG = 9: clock64 timeline of CTA (0,0,0) into g_tc_ts[0]
+    // round 2, `fuse` (kernel template FUSE, BN = 192): the three taps of a k = 3 conv are three 64-column groups of ONE
+    // accumulator - the row operand is loaded once for all taps, the column operand once per tap with its frame shift,
+    // and a CTA owns 64 columns x 3 taps = 192 CONSECUTIVE floats of every parameter row (the tap-per-CTA grid wrote
+    // every third float: 14 k of 57 k cycles in the store loop, profiles/r02m_wgrad_timelines.txt)
+    int fuse;
+    uint32_t stage_bytes;      // fuse: bytes of a pipeline stage (64 frame-planes of both operands)
 };
 
 template <int BN> struct WgradTcCfg {
@@ -71,7 +78,7 @@ template <int BN> struct WgradTcCfg {
     }
 };
 
-template <int BN>
+template <int BN, bool FUSE>
 __global__ void __launch_bounds__(WG_THREADS, 1)
 conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                      const WgradTcArgs a) {
@@ -90,11 +97,15 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler
     const int STAGES = a.nstages;
     const int ks = gridDim.x, kr = blockIdx.x;
-    const int ntiles = (a.ncols + BN - 1) / BN;
-    const int m0 = (blockIdx.y / ntiles) * WG_BM, n0 = (blockIdx.y % ntiles) * BN;
+    constexpr int NCOL = FUSE ? 64 : BN;                 // parameter columns a CTA owns
+    const int ntiles = (a.ncols + NCOL - 1) / NCOL;
+    const int m0 = (blockIdx.y / ntiles) * WG_BM, n0 = (blockIdx.y % ntiles) * NCOL;
     const int tap = blockIdx.z;
     const int off = (tap - (a.taps - 1) / 2) * a.dil;
-    const int off_a = a.swapped ? off : 0, off_b = a.swapped ? 0 : off;
+    // FUSE: the row operand never shifts; output tap index g reads the column operand shifted by (g - 1) * dil -
+    // for Conv1d that is U[t + off(g)], for the swapped ConvTranspose1d operands the substitution t' = t + off turns
+    // sum_t U[t + off][ci] dY[t][co] (parameter tap taps-1-g) into sum_t' U[t'][ci] dY[t' - off][co]: the same rule
+    const int off_a = FUSE ? 0 : (a.swapped ? off : 0), off_b = a.swapped ? 0 : off;
     const int tap_idx = a.swapped ? a.taps - 1 - tap : tap;
     const int multi = a.multi, kt = a.kt;
     const int pairs = multi ? 1 : n_pairs(a.P);
@@ -106,6 +117,9 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     const uint32_t box_bytes = (uint32_t)kt * 128u;
     const uint32_t a_plane = (WG_BM / 64) * box_bytes, b_plane = (BN / 64) * box_bytes;
     const uint32_t a_all = multi ? (uint32_t)a.P * a_plane : a_plane;
+    const uint32_t stage_stride = FUSE ? a.stage_bytes : STAGE_BYTES;
+    long long* ts = (a.dbg >= 9 && (blockIdx.x | blockIdx.y | blockIdx.z) == 0) ? g_tc_ts[0] : nullptr;
+    if (threadIdx.x == 0) TS(0);
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&map_a);
@@ -119,13 +133,14 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         fence_barrier_init();
         if (ks > 1) mbar_expect_tx(&recv_bar, (uint32_t)(ks - 1) * (WG_BM / ks) * PITCH * 4);
     }
-    if (warp == 1) tmem_alloc<BN>(&tmem_slot);
+    if (warp == 1) tmem_alloc<(BN == 192 ? 256 : BN)>(&tmem_slot);
     tc_fence_before();
     if (ks > 1) cluster_sync_all();
     else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
     pdl_wait();      // everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel's tail
+    if (threadIdx.x == 0) TS(1);
 
     if (warp == 0) {
         if (nk > 0) {
@@ -141,10 +156,10 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                 const int pl_a = a.swapped ? pb : pa, pl_b = a.swapped ? pa : pb;
                 const int t0 = tb * kt;
                 if (i >= STAGES) mbar_wait(&empty_bar[s], ph);
-                uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
+                uint8_t* sa = smem + (size_t)s * stage_stride;
                 uint8_t* sb = sa + a_all;
                 if (elect_one()) {
-                    mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                    mbar_expect_tx(&full_bar[s], stage_stride);
                     const int npl = multi ? a.P : 1;
                     for (int q = 0; q < npl; q++) {
                         const int qa = multi ? q : pl_a, qb = multi ? q : pl_b;
@@ -157,7 +172,11 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                             for (int m = 0; m < WG_BM / 64; m++)
                                 tma_load_3d(da_ + m * box_bytes, &map_a, &full_bar[s], m0 + m * 64, t0 + off_a, qa * a.B + bb);
                         }
-                        if (a.b4d) {
+                        if constexpr (FUSE) {
+#pragma unroll
+                            for (int g = 0; g < 3; g++)
+                                tma_load_4d(db_ + g * box_bytes, &map_b, &full_bar[s], 0, t0 + (g - 1) * a.dil, n0 / 64, qb * a.B + bb);
+                        } else if (a.b4d) {
                             tma_load_4d(db_, &map_b, &full_bar[s], 0, t0 + off_b, n0 / 64, qb * a.B + bb);
                         } else {
 #pragma unroll
@@ -171,6 +190,7 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                 if (bb * tblocks + tb == kb1) { bb = kb0 / tblocks; tb = kb0 - bb * tblocks; ++pr; }   // next plane pair
                 if (++s == STAGES) { s = 0; ph ^= 1; }
             }
+            if (lane == 0) TS(8);
         }
     } else if (warp == 1) {
         {
@@ -182,12 +202,13 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             for (int i = 0; i < nk; i++) {
                 if (!ready) mbar_wait(&full_bar[s], ph);
                 tc_fence_after();
+                if (i == 0 && lane == 0) TS(2);
                 int s1 = s + 1;
                 uint32_t ph1 = ph;
                 if (s1 == STAGES) { s1 = 0; ph1 ^= 1; }
                 bool next_ready = false;
                 if (i + 1 < nk) next_ready = __all_sync(0xffffffffu, mbar_test(&full_bar[s1], ph1));
-                const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
+                const uint32_t sa = smem_u32(smem + (size_t)s * stage_stride);
                 // MN-major: 16 frame rows of 128 B = 2048 B per UMMA_K (+128 in 16-byte descriptor units);
                 // 64-channel boxes are WG_BOX_BYTES apart (LBO); 8-row swizzle atoms 1024 B apart (SBO)
                 if (elect_one()) {
@@ -202,9 +223,8 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                             for (int j = 0; j < kt / 16; j++) umma_bf16(tmem_base, da + 128 * j, db + 128 * j, idesc, (i | pr | j) != 0);
                         }
                     } else {
-                        const uint64_t da = smem_desc_sw128(sa, WG_BOX_BYTES, 1024), db = smem_desc_sw128(sa + A_BYTES, WG_BOX_BYTES, 1024);
-#pragma unroll
-                        for (int j = 0; j < WG_KT / 16; j++) umma_bf16(tmem_base, da + 128 * j, db + 128 * j, idesc, (i | j) != 0);
+                        const uint64_t da = smem_desc_sw128(sa, box_bytes, 1024), db = smem_desc_sw128(sa + a_all, box_bytes, 1024);
+                        for (int j = 0; j < kt / 16; j++) umma_bf16(tmem_base, da + 128 * j, db + 128 * j, idesc, (i | j) != 0);
                     }
                     umma_commit(&empty_bar[s]);
                 }
@@ -215,6 +235,7 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             }
             if (elect_one()) umma_commit(&tmem_full_bar);
             __syncwarp();
+            if (lane == 0) TS(9);
         }
     }
 
@@ -226,6 +247,7 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         const int q = warp & 3, h = warp >> 2;
         mbar_wait_warp(&tmem_full_bar, 0, 32);
         tc_fence_after();
+        if (threadIdx.x == 64) TS(3);
         float* srow = stage + (size_t)(q * 32 + lane) * PITCH;
 #pragma unroll 1
         for (int c0 = h * (BN / 2); c0 < (h + 1) * (BN / 2); c0 += 32) {
@@ -236,13 +258,21 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
 #pragma unroll
                 for (int i = 0; i < 32; i++) v[i] = 0.f;
             }
+            if constexpr (FUSE) {
+                // accumulator column g * 64 + c  ->  position c * 3 + g of the parameter row (64 columns x 3 taps)
+                const int g = c0 >> 6, cb = c0 & 63;
 #pragma unroll
-            for (int i = 0; i < 32; i += 4)
-                *reinterpret_cast<float4*>(srow + c0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+                for (int i = 0; i < 32; i++) srow[(cb + i) * 3 + g] = v[i];
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; i += 4)
+                    *reinterpret_cast<float4*>(srow + c0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+            }
         }
         tc_fence_before();
         fence_proxy_async_smem();
         __syncthreads();
+        if (threadIdx.x == 64) TS(4);
         if (threadIdx.x == 64) {
             const uint32_t slot_bytes = (uint32_t)rows_own * PITCH * 4;
             for (int p = 0; p < ks; p++) {
@@ -254,7 +284,32 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             }
         }
         if (ks > 1) mbar_wait_warp(&recv_bar, 0, 32);
+        if (threadIdx.x == 64) TS(5);
 
+        if constexpr (FUSE) {
+            // the drain above left every staged row in PARAMETER order (position c * 3 + g): a row of this tile is 192
+            // consecutive floats of the parameter.  Warp per row, float4 per lane (48 per row), partial sums in sender order.
+            const int ncols = a.ncols, nrows = a.nrows;
+            const uint32_t own_b = smem_u32(stage + (size_t)r_base * PITCH), recv_b = smem_u32(recv);
+            const uint32_t slot_stride = (uint32_t)rows_own * PITCH * 4;
+            for (int rl = warp; rl < rows_own; rl += WG_THREADS / 32) {
+                const int row = m0 + r_base + rl;
+                if (row >= nrows) break;
+                float* o = a.dw + ((size_t)row * ncols + n0) * 3;
+                const uint32_t roff = (uint32_t)rl * (PITCH * 4);
+#pragma unroll
+                for (int v4 = lane; v4 < 48; v4 += 32) {
+                    float4 v = ld_shared_f4((kr == 0 ? own_b : recv_b) + roff + (uint32_t)v4 * 16);
+#pragma unroll 1
+                    for (int p = 1; p < ks; p++) {
+                        const uint32_t base = p == kr ? own_b : recv_b + (uint32_t)(p < kr ? p : p - 1) * slot_stride;
+                        const float4 x = ld_shared_f4(base + roff + (uint32_t)v4 * 16);
+                        v.x += x.x; v.y += x.y; v.z += x.z; v.w += x.w;
+                    }
+                    if (a.dbg != 31) *reinterpret_cast<float4*>(o + 4 * v4) = v;
+                }
+            }
+        } else {
         constexpr int TPR = BN / 4;
         constexpr int RPP = WG_THREADS / TPR;
         const int tid = threadIdx.x;
@@ -324,12 +379,15 @@ conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                 }
             }
         }
+        }
     }
+    if (threadIdx.x == 64) TS(6);
     if (ks > 1) cluster_sync_all();
     __syncthreads();
+    if (threadIdx.x == 0) TS(7);
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc<BN>(tmem_base);
+        tmem_dealloc<(BN == 192 ? 256 : BN)>(tmem_base);
     }
 }
 
@@ -347,12 +405,32 @@ static bool make_wgrad_map(CUtensorMap* m, const void* base, int C, int T, int P
     return make_tmap_3d(m, base, (uint64_t)C, (uint64_t)T, (uint64_t)PB, (uint64_t)Cp * 2, (uint64_t)T * Cp * 2, 64, (uint32_t)kt, 1);
 }
 
-template <int BN>
+// shared memory plan of the tap-fused variant (BN = 192): stages of `stage_bytes`, the staging tile reuses the ring
+struct WgradFusePlan {
+    int nstages;
+    uint32_t recv_off, recv_bytes, smem;
+    bool ok;
+};
+static WgradFusePlan wgrad_fuse_plan(int ks, uint32_t stage_bytes) {
+    using Cfg = WgradTcCfg<192>;
+    WgradFusePlan p{};
+    p.recv_bytes = Cfg::recv_bytes(ks);
+    if (p.recv_bytes + 2 * stage_bytes > Cfg::SMEM_BUDGET) return p;
+    int n = (int)((Cfg::SMEM_BUDGET - p.recv_bytes) / stage_bytes);
+    p.nstages = n > Cfg::MAX_STAGES ? Cfg::MAX_STAGES : n;
+    const uint32_t ring = (uint32_t)p.nstages * stage_bytes;
+    p.recv_off = ((ring > Cfg::STAGING_BYTES ? ring : Cfg::STAGING_BYTES) + 1023u) & ~1023u;
+    p.smem = p.recv_off + p.recv_bytes + 1024;
+    p.ok = p.smem <= 227 * 1024 - 1024;
+    return p;
+}
+
+template <int BN, bool FUSE = false>
 static int launch_wgrad_tc(const void* rows_pl, const void* cols_pl, int ksplit, WgradTcArgs a, cudaStream_t st) {
     using Cfg = WgradTcCfg<BN>;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<BN, FUSE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
         if (e != cudaSuccess) {
             set_error("conv_wgrad_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
             return VNB_E_CUDA;
@@ -361,13 +439,22 @@ static int launch_wgrad_tc(const void* rows_pl, const void* cols_pl, int ksplit,
     }
     CUtensorMap ma, mb;
     if (!make_wgrad_map(&ma, rows_pl, a.nrows, a.T, a.P * a.B, WG_BM / 64, &a.a4d, a.kt)) return VNB_E_CUDA;
-    if (!make_wgrad_map(&mb, cols_pl, a.ncols, a.T, a.P * a.B, BN / 64, &a.b4d, a.kt)) return VNB_E_CUDA;
-    a.nstages = Cfg::stages(ksplit);
-    a.recv_off = Cfg::recv_offset(ksplit);
+    if (!make_wgrad_map(&mb, cols_pl, a.ncols, a.T, a.P * a.B, FUSE ? 1 : BN / 64, &a.b4d, a.kt)) return VNB_E_CUDA;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(ksplit, ceil_div(a.nrows, WG_BM) * ceil_div(a.ncols, BN), a.taps);
+    if (FUSE) {
+        const WgradFusePlan pl = wgrad_fuse_plan(ksplit, a.stage_bytes);
+        if (!pl.ok || !a.b4d) { set_error("conv_wgrad_tc: tap-fused plan does not fit (cluster %d)", ksplit); return VNB_E_ARG; }
+        a.nstages = pl.nstages;
+        a.recv_off = pl.recv_off;
+        cfg.gridDim = dim3(ksplit, ceil_div(a.nrows, WG_BM) * (a.ncols / 64), 1);
+        cfg.dynamicSmemBytes = pl.smem;
+    } else {
+        a.nstages = Cfg::stages(ksplit);
+        a.recv_off = Cfg::recv_offset(ksplit);
+        cfg.gridDim = dim3(ksplit, ceil_div(a.nrows, WG_BM) * ceil_div(a.ncols, BN), a.taps);
+        cfg.dynamicSmemBytes = (size_t)a.recv_off + Cfg::recv_bytes(ksplit) + 1024;
+    }
     cfg.blockDim = dim3(WG_THREADS);
-    cfg.dynamicSmemBytes = (size_t)a.recv_off + Cfg::recv_bytes(ksplit) + 1024;
     cfg.stream = st;
     cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -378,7 +465,7 @@ static int launch_wgrad_tc(const void* rows_pl, const void* cols_pl, int ksplit,
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, conv_wgrad_tc_kernel<BN>, ma, mb, a);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, conv_wgrad_tc_kernel<BN, FUSE>, ma, mb, a);
     if (e != cudaSuccess) {
         set_error("conv_wgrad_tc: launch failed (BN %d, cluster %d): %s", BN, ksplit, cudaGetErrorString(e));
         return VNB_E_CUDA;
@@ -396,9 +483,23 @@ int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin
     const void* cols_pl = transposed ? dy : u;
     // all planes per stage for the two-plane mode (VNB_OPT_GEMM_V3 = 0 keeps the round-1 pass per plane pair)
     const int multi = (P == 2 && option(VNB_OPT_GEMM_V3) != 0) ? 1 : 0;
-    WgradTcArgs a{B, nrows, ncols, T, taps, P, dil, transposed ? 1 : 0, 0, 0, 0, 0, dw, multi ? WG_KT / 2 : WG_KT, multi};
+    WgradTcArgs a{B, nrows, ncols, T, taps, P, dil, transposed ? 1 : 0, 0, 0, 0, 0, dw, multi ? WG_KT / 2 : WG_KT, multi, option(VNB_OPT_TC_DBG), 0, 0};
     static const int force_bn = getenv("VNB_WG_BN") ? atoi(getenv("VNB_WG_BN")) : 0;
     static const int force_ks = getenv("VNB_WG_KSPLIT") ? atoi(getenv("VNB_WG_KSPLIT")) : 0;
+    static const int fuse_env = getenv("VNB_WG_FUSE") ? atoi(getenv("VNB_WG_FUSE")) : 1;
+    if (taps == 3 && ncols % 64 == 0 && fuse_env && option(VNB_OPT_GEMM_V3) != 0 && (force_bn == 0 || force_bn == 192)) {
+        // tap-fused tiles: 128 rows x 64 columns x 3 taps; 64 frame-planes per stage (40 KB)
+        const int npl = multi ? P : 1;
+        a.fuse = 1;
+        a.kt = 64 / npl >= 16 ? (64 / npl) / 16 * 16 : 16;
+        a.stage_bytes = (uint32_t)npl * (uint32_t)a.kt * 128u * (WG_BM / 64 + 3);
+        const int kb = multi ? B * ceil_div(T, a.kt) : B * ceil_div(T, a.kt) * n_pairs(P);
+        const int64_t tiles = (int64_t)ceil_div(nrows, WG_BM) * (ncols / 64);
+        int ksf = 1;
+        while (ksf < 8 && tiles * ksf * 2 <= 148 && ksf * 2 <= kb && wgrad_fuse_plan(ksf * 2, a.stage_bytes).ok) ksf *= 2;
+        if (force_ks) ksf = force_ks;
+        return launch_wgrad_tc<192, true>(rows_pl, cols_pl, ksf, a, st);
+    }
     // stages walked by a tile: (sample, frame block) x plane pairs - or, all planes per stage, half-size frame blocks
     const int kblocks = multi ? B * ceil_div(T, WG_KT / 2) : B * ceil_div(T, WG_KT) * n_pairs(P);
     int bn = 64, ks = 1;

@@ -62,7 +62,7 @@ def set_side_stream(stream):
         _SIDE['aux'] = None
     else:
         if _SIDE.get('aux_cached') is None or _SIDE['aux_cached'].device != stream.device:
-            _SIDE['aux_cached'] = torch.cuda.Stream(device=stream.device)
+            _SIDE['aux_cached'] = torch.cuda.Stream(device=stream.device, priority=int(os.environ.get('VNB_AUX_PRIO', 0)))
         _SIDE['aux'] = _SIDE['aux_cached']
 
 
