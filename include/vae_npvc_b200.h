@@ -84,7 +84,10 @@ int vnb_get_backend(void);
 /*   VNB_OPT_VQ_FUSED  fused VQ lookup (frame preparation + one-product tensor-core shortlist + exact fp32 re-rank +
  *                     gather + loss sums + histogram in one kernel, csrc/tc_vq_fused.cuh; default 1) */
 #define VNB_OPT_VQ_FUSED 10
-#define VNB_OPT_COUNT_ 11
+/*   VNB_OPT_WG_FUSE   tap-fused weight-gradient tiles for k = 3 convs (one N-192 accumulator per 64 columns x 3 taps,
+ *                     csrc/tc_wgrad.cuh; default 0: faster per launch, slower under data parallelism - DESIGN.md 5.4) */
+#define VNB_OPT_WG_FUSE 11
+#define VNB_OPT_COUNT_ 12
 /* diagnostics: buf[slot] = %globaltimer (ns) when `stream` reaches this launch; usable inside captured graphs */
 int vnb_debug_stamp(int64_t* buf, int slot, void* stream);
 void vnb_set_option(int which, int value);

@@ -91,11 +91,15 @@ WGRAD_SHAPES = [
 ]
 
 
+@pytest.mark.parametrize('fuse', [0, 1])
 @pytest.mark.parametrize('P', [1, 2, 3])
 @pytest.mark.parametrize('transposed', [False, True])
 @pytest.mark.parametrize('B,Cin,Cout,T,k,dil', WGRAD_SHAPES)
-def test_conv_wgrad_tc_vs_simt(backends, P, transposed, B, Cin, Cout, T, k, dil):
+def test_conv_wgrad_tc_vs_simt(backends, fuse, P, transposed, B, Cin, Cout, T, k, dil):
     _C, Pm = backends
+    if fuse and (k != 3 or (Cout if transposed else Cin) % 64 != 0):
+        pytest.skip('tap-fused tiles need k = 3 and a column count divisible by 64')
+    _C.set_option(_C.OPT_WG_FUSE, fuse)
     dy, u = g(B, Cout, T, seed=5), g(B, Cin, T, seed=6)
     dypl, upl = Pm.make_planes(dy.cuda(), P)[0], Pm.make_planes(u.cuda(), P)[0]
     _C.set_backend(_C.BACKEND_SIMT)
@@ -103,6 +107,7 @@ def test_conv_wgrad_tc_vs_simt(backends, P, transposed, B, Cin, Cout, T, k, dil)
     _C.set_backend(_C.BACKEND_TC)
     b = Pm.conv_wgrad(dypl, upl, k, dil, transposed)
     torch.cuda.synchronize()
+    _C.set_option(_C.OPT_WG_FUSE, 0)
     assert _C.call('debug_tc_timeouts') == 0
     assert a.shape == b.shape == ((Cin, Cout, k) if transposed else (Cout, Cin, k))
     assert rel_err(b, a) < 2e-5, rel_err(b, a)

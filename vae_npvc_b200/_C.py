@@ -130,7 +130,7 @@ def get_backend():
     return load().vnb_get_backend()
 
 
-OPT_EW_V2, OPT_FAST_GATE, OPT_WN_V2, OPT_GEMM_V3, OPT_TC3_BN, OPT_TC3_PAIR, OPT_TC3_STAGES, OPT_TC_DBG, OPT_TC3_SMEM_KB, OPT_FAST_EPI, OPT_VQ_FUSED = range(11)
+OPT_EW_V2, OPT_FAST_GATE, OPT_WN_V2, OPT_GEMM_V3, OPT_TC3_BN, OPT_TC3_PAIR, OPT_TC3_STAGES, OPT_TC_DBG, OPT_TC3_SMEM_KB, OPT_FAST_EPI, OPT_VQ_FUSED, OPT_WG_FUSE = range(12)
 
 
 def set_option(which, value):

@@ -40,6 +40,7 @@ static void opts_init() {
     g_opts[VNB_OPT_TC3_SMEM_KB].store(env_or("VNB_TC3_SMEM_KB", 0));
     g_opts[VNB_OPT_FAST_EPI].store(env_or("VNB_FAST_EPI", 0));
     g_opts[VNB_OPT_VQ_FUSED].store(env_or("VNB_VQ_FUSED", 1));
+    g_opts[VNB_OPT_WG_FUSE].store(env_or("VNB_WG_FUSE", 0));
     g_opts_init.store(true, std::memory_order_release);
 }
 int option(int which) {

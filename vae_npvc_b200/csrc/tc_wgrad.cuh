@@ -486,7 +486,10 @@ int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin
     WgradTcArgs a{B, nrows, ncols, T, taps, P, dil, transposed ? 1 : 0, 0, 0, 0, 0, dw, multi ? WG_KT / 2 : WG_KT, multi, option(VNB_OPT_TC_DBG), 0, 0};
     static const int force_bn = getenv("VNB_WG_BN") ? atoi(getenv("VNB_WG_BN")) : 0;
     static const int force_ks = getenv("VNB_WG_KSPLIT") ? atoi(getenv("VNB_WG_KSPLIT")) : 0;
-    static const int fuse_env = getenv("VNB_WG_FUSE") ? atoi(getenv("VNB_WG_FUSE")) : 1;
+    // default OFF: 15 % faster per launch, no change of the single-GPU step, but the 2-GPU step went from 3.20 to 3.30 ms with
+    // it (whatever its CTA budget: profiles/r02m_wgrad_timelines.txt) - the overlapped all-reduce loses more than the
+    // weight gradients gain.  VNB_WG_FUSE=1 / vnb_set_option(VNB_OPT_WG_FUSE, 1) switches it on.
+    const int fuse_env = option(VNB_OPT_WG_FUSE);
     if (taps == 3 && ncols % 64 == 0 && fuse_env && option(VNB_OPT_GEMM_V3) != 0 && (force_bn == 0 || force_bn == 192)) {
         // tap-fused tiles: 128 rows x 64 columns x 3 taps; 64 frame-planes per stage (40 KB)
         const int npl = multi ? P : 1;
@@ -496,7 +499,8 @@ int conv_wgrad_tc(const void* dy, const void* u, int P, int B, int Cout, int Cin
         const int kb = multi ? B * ceil_div(T, a.kt) : B * ceil_div(T, a.kt) * n_pairs(P);
         const int64_t tiles = (int64_t)ceil_div(nrows, WG_BM) * (ncols / 64);
         int ksf = 1;
-        while (ksf < 8 && tiles * ksf * 2 <= 148 && ksf * 2 <= kb && wgrad_fuse_plan(ksf * 2, a.stage_bytes).ok) ksf *= 2;
+        static const int max_cta = getenv("VNB_WG_FUSE_MAXCTA") ? atoi(getenv("VNB_WG_FUSE_MAXCTA")) : 148;
+        while (ksf < 8 && tiles * ksf * 2 <= max_cta && ksf * 2 <= kb && wgrad_fuse_plan(ksf * 2, a.stage_bytes).ok) ksf *= 2;
         if (force_ks) ksf = force_ks;
         return launch_wgrad_tc<192, true>(rows_pl, cols_pl, ksf, a, st);
     }

@@ -539,7 +539,7 @@ class Trainer(object):
         if self._cap_stream is None or self._cap_stream_prio != prio:
             self._cap_stream = torch.cuda.Stream(device=self.device, priority=prio)
             self._cap_stream_prio = prio
-        with torch.cuda.graph(g, stream=self._cap_stream):
+        with (torch.cuda.graph(g, stream=self._cap_stream) if os.environ.get('VNB_CAP_STREAM', '1') != '0' else torch.cuda.graph(g)):
             keys, scal = self._step_body(*static)
         self.launches_per_step = int(_C.launch_count() - n0)      # our kernels inside one replay
         return dict(graph=g, inputs=static, keys=keys, scal=scal)
