@@ -14,9 +14,7 @@ except Exception as e:
     print('$tag failed', e); print(open('gpurun_out/dp_$tag.err').read()[-800:])
 PY
 }
-run fuse_148 VNB_WG_FUSE=1
-run fuse_100 VNB_WG_FUSE=1 VNB_WG_FUSE_MAXCTA=100
-run fuse_64 VNB_WG_FUSE=1 VNB_WG_FUSE_MAXCTA=64
-run no_fuse VNB_WG_FUSE=0
-for v in 148 100 64; do VNB_WG_FUSE=1 VNB_WG_FUSE_MAXCTA=$v timeout 100 python bench.py --steps 100 --warmup 10 --no-cpu-baseline 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('single fuse_$v', round(d['ms_per_step'],3))"; done
-VNB_WG_FUSE=0 timeout 100 python bench.py --steps 100 --warmup 10 --no-cpu-baseline 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('single no_fuse', round(d['ms_per_step'],3))"
+run early_cond A=1
+run late_cond VNB_EARLY_COND=0
+run early_cond_b A=1
+run late_cond_b VNB_EARLY_COND=0

@@ -152,7 +152,7 @@ class Decoder(nn.Module, _WeightNormMixin):
         """input = (x (B,in,T), c (B,cond,>=1)); only c[:,:,:1] is used (vqvae.py:309) - it is
         time-invariant, so each block's 1x1 cond conv collapses to a per-utterance bias."""
         x, c = input
-        c = c[:, :, 0].contiguous()
+        c = _mark(c[:, :, 0].contiguous(), 'cond')   # its gradient exists once every conditioning conv has been back-propagated
         skip = None
         # the conditioning 1x1 convs of all gated blocks see the same (B, Y) embedding: one batched launch for all of
         # them (and one for their backward) instead of one small linear per block

@@ -196,6 +196,7 @@ class Trainer(object):
                         if bool(config.get('debug_stamps', False)) and self.device.type == 'cuda' else None)
         self._stamp_next = 10
         self._early_segments = set()
+        self.config_early_cond = bool(int(config.get('early_cond_bucket', os.environ.get('VNB_EARLY_COND', 1))))
         self._buckets = self._plan_buckets()
         self._reduced = []
         self.overlap_allreduce = bool(config.get('overlap_allreduce', True))
@@ -277,6 +278,10 @@ class Trainer(object):
             ends = cuts[1:] + [None]
             for c, e in zip(cuts, ends):
                 plan[enc[c - 1]] = (spans[enc[c]][0], spans[enc[e]][0] if e is not None else _end(enc[-1]))
+        if 'cond' in spans and bool(self.config_early_cond):
+            # the conditioning convs' gradients are final when the gradient reaches the speaker embedding the decoder was
+            # given (model/vqvae.py marks it 'cond': functional.CondAllFn's backward has run) - mid-backward, not at its end
+            plan['cond'] = (spans['cond'][0], _end('cond'))
         return plan
 
     def _plan_grad_zero(self):
