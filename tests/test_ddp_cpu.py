@@ -26,7 +26,7 @@ def _free_port():
     return p
 
 
-def _make_trainer(arch):
+def _make_trainer(arch, model_type='vae_npvc_b200.model.vqvae'):
     from oracle import prims_ref
     import vae_npvc_b200.functional as Fn
     import vae_npvc_b200.model.layers_vq as LVQ
@@ -34,12 +34,12 @@ def _make_trainer(arch):
     Fn.Pm = LVQ.Pm = TB.Pm = prims_ref
     Fn.set_precision('fp32')
     cfg = dict(arch)
-    cfg.update(model_type='vae_npvc_b200.model.vqvae', device='cpu', cuda_graph=False, precision='fp32',
+    cfg.update(model_type=model_type, device='cpu', cuda_graph=False, precision='fp32',
                learning_rate=1e-3, max_grad_norm=10)
     return TB.Trainer(cfg)
 
 
-def _run(rank, world, port, use_ema, steps, out_dir):
+def _run(rank, world, port, use_ema, steps, out_dir, kind='vqvae'):
     sys.path.insert(0, ROOT)
     import torch.distributed as dist
     from oracle import synth
@@ -47,10 +47,11 @@ def _run(rank, world, port, use_ema, steps, out_dir):
     if world > 1:
         os.environ['MASTER_ADDR'], os.environ['MASTER_PORT'] = '127.0.0.1', str(port)
         dist.init_process_group('gloo', rank=rank, world_size=world)
-    arch = synth.small_config(use_ema=use_ema)
+    v2 = kind == 'vqvae2'
+    arch = synth.vqvae2_small_config() if v2 else synth.small_config(use_ema=use_ema)
     torch.manual_seed(777)
-    tr = _make_trainer(arch)
-    tr.model.load_state_dict(synth.synthetic_state_dict(arch, 777))
+    tr = _make_trainer(arch, 'vae_npvc_b200.model.vqvae2' if v2 else 'vae_npvc_b200.model.vqvae')
+    tr.model.load_state_dict(synth.vqvae2_state_dict(arch, 777) if v2 else synth.synthetic_state_dict(arch, 777))
     if use_ema:
         # start from an initialised EMA state with every code well alive, so that neither the random
         # init nor the dead-code restart (rank-local random draws, layers_vq.py:212-221) is involved
@@ -58,10 +59,10 @@ def _run(rank, world, port, use_ema, steps, out_dir):
         q.emb_init.fill_(True)
         q.emb_elem.fill_(10.0)
         q.emb_sum.copy_(q.embeddings * 10.0)
-    B, T = 4, 20
+    B, T = (4, 64) if v2 else (4, 20)
     details = []
     for s in range(steps):
-        x, y = synth.synthetic_batch(arch, B, T, 100 + s)
+        x, y = synth.vqvae2_batch(arch, B, T, 100 + s) if v2 else synth.synthetic_batch(arch, B, T, 100 + s)
         if world > 1:
             h = B // world
             x, y = x[rank * h:(rank + 1) * h], y[rank * h:(rank + 1) * h]
@@ -97,3 +98,24 @@ def test_two_rank_gloo_step_equals_single_process(tmp_path, use_ema):
         for key in ('Total', 'X like', 'VQ loss'):
             m = 0.5 * (r0['details'][s][key] + r1['details'][s][key])
             assert abs(m - one['details'][s][key]) <= 2e-5 * max(1.0, abs(one['details'][s][key])), (s, key)
+
+
+def test_two_rank_gloo_step_hierarchical_model(tmp_path):
+    """The same for model/vqvae2.py: strided convs outside the weight bank (their gradients come
+    through autograd and are averaged with the rest of the flat buffer), style-token level, per-level quantisers."""
+    steps = 2
+    out = str(tmp_path)
+    _run(0, 1, 0, False, steps, out, 'vqvae2')
+    mp.spawn(_run, args=(2, _free_port(), False, steps, out, 'vqvae2'), nprocs=2, join=True)
+    one = torch.load(os.path.join(out, 'w1_r0.pt'))
+    r0 = torch.load(os.path.join(out, 'w2_r0.pt'))
+    r1 = torch.load(os.path.join(out, 'w2_r1.pt'))
+    for k, v in one['state'].items():
+        a, b = r0['state'][k], r1['state'][k]
+        assert torch.equal(a, b), 'ranks diverged on ' + k
+        err = float((a.double() - v.double()).norm() / (v.double().norm() + 1e-30))
+        assert err < 5e-5, (k, err)
+    for s_ in range(steps):
+        for key in ('Total', 'X like', 'VQ loss'):
+            m = 0.5 * (r0['details'][s_][key] + r1['details'][s_][key])
+            assert abs(m - one['details'][s_][key]) <= 2e-5 * max(1.0, abs(one['details'][s_][key])), (s_, key)

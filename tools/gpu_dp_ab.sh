@@ -14,7 +14,9 @@ except Exception as e:
     print('$tag failed', e); print(open('gpurun_out/dp_$tag.err').read()[-800:])
 PY
 }
-run early_cond A=1
-run late_cond VNB_EARLY_COND=0
-run early_cond_b A=1
-run late_cond_b VNB_EARLY_COND=0
+run b_6_6 A=1
+run b_6_10 VNB_BUCKETS=6,10
+run b_10_10 VNB_BUCKETS=10,10
+run b_8_9 VNB_BUCKETS=8,9
+run b_6_6_b A=1
+run b_10_10_b VNB_BUCKETS=10,10
