@@ -94,7 +94,7 @@ def model_forward(params, arch, x, y_idx):
     -> (xhat, loss, detail, [ids per quantised level, in the reference's order: top-down])"""
     levels = arch.get('levels', 3)
     use_gst = arch.get('use_gst', True)
-    assert not arch.get('use_ema', True) or use_gst is None or True
+    assert not arch.get('use_ema', True), 'the oracle restates the shipped recipe: non-EMA quantisers (use_ema: false)'
     y = params['embeds._embedding.weight'][y_idx[..., :1]].transpose(1, 2)          # (B, Y, 1)
     z_levels, time_levels = [], [x.shape[-1]]
     x_ = x
