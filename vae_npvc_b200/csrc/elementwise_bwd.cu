@@ -60,17 +60,18 @@ __device__ __forceinline__ void publish_group_sums(float t, float gm, bool valid
     }
 }
 
-// R[b,c] = { sum_t dn, sum_t dn*xhat, sum_t xhat }.  grid (ceil(C/32), B), block 32 x 8: a warp reads
-// 32 consecutive channels of one frame, the 8 warps stride over frames, shared-memory reduce.
-template <bool GATE>
-__global__ void __launch_bounds__(256) bwd_rows_kernel(const float* __restrict__ dn, const float* __restrict__ h,
+// R[b,c] = { sum_t dn, sum_t dn*xhat, sum_t xhat }.  grid (ceil(C/32), B), block 32 x NW: a warp reads
+// 32 consecutive channels of one frame, the NW warps stride over frames, shared-memory reduce.  NW = 32 for T >= 128:
+// at 16 x 128 frames the kernel is latency-bound (four dependent rounds of loads with 8 warps, one with 32).
+template <bool GATE, int NW>
+__global__ void __launch_bounds__(32 * NW) bwd_rows_kernel(const float* __restrict__ dn, const float* __restrict__ h,
                                                        const float* __restrict__ mean, const float* __restrict__ rstd,
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                                        int Cn, int T, int groups, float* __restrict__ R,
                                                        double* __restrict__ S64, float* __restrict__ S32,
                                                        unsigned* __restrict__ counter) {
     pdl_wait();
-    __shared__ float red[3][8][33];
+    __shared__ float red[3][NW][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int b = blockIdx.y, c = blockIdx.x * 32 + tx;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f;
@@ -78,7 +79,7 @@ __global__ void __launch_bounds__(256) bwd_rows_kernel(const float* __restrict__
         const int gi = b * groups + c / (Cn / groups);
         const float m = mean[gi], rs = rstd[gi];
         if (GATE) {
-            for (int t = ty; t < T; t += 8) {
+            for (int t = ty; t < T; t += NW) {
                 const int64_t r = (int64_t)b * T + t;
                 float xh;
                 const float d = gate_dn(dn, h, mean, rstd, gamma, beta, b, r, c, Cn / 2, xh);
@@ -87,18 +88,18 @@ __global__ void __launch_bounds__(256) bwd_rows_kernel(const float* __restrict__
                 s2 += xh;
             }
         } else {
-            for (int t0 = ty; t0 < T; t0 += 32) {          // four frames in flight
+            for (int t0 = ty; t0 < T; t0 += 4 * NW) {      // four frames in flight
                 float d[4], hv[4];
 #pragma unroll
                 for (int u = 0; u < 4; u++) {
-                    const int t = t0 + 8 * u;
+                    const int t = t0 + NW * u;
                     const int64_t r = (int64_t)b * T + (t < T ? t : 0);
                     d[u] = t < T ? dn[r * Cn + c] : 0.f;
                     hv[u] = h[r * Cn + c];
                 }
 #pragma unroll
                 for (int u = 0; u < 4; u++) {
-                    if (t0 + 8 * u >= T) continue;
+                    if (t0 + NW * u >= T) continue;
                     const float xh = (hv[u] - m) * rs;
                     s0 += d[u];
                     s1 += d[u] * xh;
@@ -114,7 +115,7 @@ __global__ void __launch_bounds__(256) bwd_rows_kernel(const float* __restrict__
     float s = 0.f;
     if (ty < 3 && c < Cn) {
 #pragma unroll
-        for (int j = 0; j < 8; j++) s += red[ty][j][tx];
+        for (int j = 0; j < NW; j++) s += red[ty][j][tx];
         R[((int64_t)b * Cn + c) * 3 + ty] = s;
     }
     if (S64) {
@@ -327,7 +328,11 @@ extern "C" int vnb_gn_bwd_rows(const float* dn, const float* h, const float* mea
                                int T, int groups, float* R, void* stream) {
     VNB_REQUIRE(dn && h && mean && rstd && R && B > 0 && B <= 65535 && C > 0 && T > 0 && groups > 0 && C % groups == 0,
                 "gn_bwd_rows: bad arguments");
-    vnb::launch_k(bwd_rows_kernel<false>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dn, h, mean, rstd, nullptr, nullptr,
+    if (T >= 128)
+        vnb::launch_k(bwd_rows_kernel<false, 32>, dim3(ceil_div(C, 32), B), 1024, 0, (cudaStream_t)stream, dn, h, mean, rstd, nullptr, nullptr,
+                                                                                       C, T, groups, R, nullptr, nullptr, nullptr);
+    else
+        vnb::launch_k(bwd_rows_kernel<false, 8>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dn, h, mean, rstd, nullptr, nullptr,
                                                                                        C, T, groups, R, nullptr, nullptr, nullptr);
     VNB_LAUNCH_CHECK("gn_bwd_rows");
     return VNB_OK;
@@ -338,7 +343,11 @@ extern "C" int vnb_gn_bwd_rows_s(const float* dn, const float* h, const float* m
     VNB_REQUIRE(dn && h && mean && rstd && gamma && R && S64 && S && B > 0 && B <= 65535 && C > 0 && T > 0 && groups > 0 &&
                     C % groups == 0 && ((C / groups) & 31) == 0, "gn_bwd_rows_s: bad arguments (32 must divide C / groups)");
     // S64: B * groups * 2 ZEROED doubles followed by one zeroed 8-byte ticket slot
-    vnb::launch_k(bwd_rows_kernel<false>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dn, h, mean, rstd, gamma, nullptr,
+    if (T >= 128)
+        vnb::launch_k(bwd_rows_kernel<false, 32>, dim3(ceil_div(C, 32), B), 1024, 0, (cudaStream_t)stream, dn, h, mean, rstd, gamma, nullptr,
+                  C, T, groups, R, S64, S, reinterpret_cast<unsigned*>(S64 + (size_t)B * groups * 2));
+    else
+        vnb::launch_k(bwd_rows_kernel<false, 8>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dn, h, mean, rstd, gamma, nullptr,
                   C, T, groups, R, S64, S, reinterpret_cast<unsigned*>(S64 + (size_t)B * groups * 2));
     VNB_LAUNCH_CHECK("gn_bwd_rows_s");
     return VNB_OK;
@@ -347,26 +356,28 @@ extern "C" int vnb_gn_bwd_rows_s(const float* dn, const float* h, const float* m
 namespace vnb {
 // Gate variant of bwd_rows: a thread owns channel c < C and accumulates the three row sums of BOTH halves
 // (tanh half c, sigmoid half C + c) from one tanh / exp pair per element, four frames in flight.
-// grid (ceil(C/32), B), block 32 x 8.
-template <bool FAST>
-__global__ void __launch_bounds__(256) gate_bwd_rows_kernel(const float* __restrict__ dg, const float* __restrict__ a,
+// grid (ceil(C/32), B), block 32 x NW.  NW = 16 for T >= 64 (10.8 -> 9.6 us at 16 x 128 frames; VNB_GATE_ROWS_NW16=0: 8 warps);
+// with 32 warps (64 registers per thread around libm tanh / exp) it measured SLOWER (12.1 us), unlike the plain GroupNorm
+// row sums (9.6 -> 7.9 us with 32 warps).
+template <bool FAST, int NW>
+__global__ void __launch_bounds__(32 * NW) gate_bwd_rows_kernel(const float* __restrict__ dg, const float* __restrict__ a,
                                                             const float* __restrict__ mean, const float* __restrict__ rstd,
                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
                                                             int C, int T, float* __restrict__ R, double* __restrict__ S64,
                                                             float* __restrict__ S32, unsigned* __restrict__ counter) {
     pdl_wait();
-    __shared__ float red[6][8][33];
+    __shared__ float red[6][NW][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int b = blockIdx.y, c = blockIdx.x * 32 + tx;
     float s[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (c < C) {
         const float m1 = mean[2 * b], m2 = mean[2 * b + 1], rs1 = rstd[2 * b], rs2 = rstd[2 * b + 1];
         const float g1 = gamma[c], g2 = gamma[C + c], b1 = beta[c], b2 = beta[C + c];
-        for (int t0 = ty; t0 < T; t0 += 32) {
+        for (int t0 = ty; t0 < T; t0 += 4 * NW) {
             float a1[4], a2[4], d[4];
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                const int t = t0 + 8 * u;
+                const int t = t0 + NW * u;
                 const int64_t r = (int64_t)b * T + (t < T ? t : 0);
                 a1[u] = a[r * 2 * C + c];
                 a2[u] = a[r * 2 * C + C + c];
@@ -374,7 +385,7 @@ __global__ void __launch_bounds__(256) gate_bwd_rows_kernel(const float* __restr
             }
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                if (t0 + 8 * u >= T) continue;
+                if (t0 + NW * u >= T) continue;
                 const float x1 = (a1[u] - m1) * rs1, x2 = (a2[u] - m2) * rs2;
                 const float th = gate_tanh<FAST>(x1 * g1 + b1);
                 const float sg = gate_sigmoid<FAST>(x2 * g2 + b2);
@@ -391,11 +402,11 @@ __global__ void __launch_bounds__(256) gate_bwd_rows_kernel(const float* __restr
     const int ch = ty < 3 ? c : C + c;
     if (ty < 6 && c < C) {
 #pragma unroll
-        for (int j = 0; j < 8; j++) t += red[ty][j][tx];
+        for (int j = 0; j < NW; j++) t += red[ty][j][tx];
         R[((int64_t)b * 2 * C + ch) * 3 + (ty % 3)] = t;
     }
     if (S64) {
-        // warps 0..2 hold the tanh half (group 0), 3..5 the sigmoid half (group 1); warps 6, 7 only take part in the barrier
+        // warps 0..2 hold the tanh half (group 0), 3..5 the sigmoid half (group 1); warps 6 and up only take part in the barrier
         const int k = ty < 6 ? ty % 3 : 2;
         publish_group_sums(t, (c < C && ty < 6 && k < 2) ? gamma[ch] : 0.f, c < C && ty < 6, k, b * 2 + (ty >= 3 && ty < 6 ? 1 : 0), S64, S32,
                            counter, gridDim.y * 4);
@@ -409,12 +420,18 @@ extern "C" int vnb_gate_bwd_rows_p(const float* dg, const float* a, const float*
     VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && R && B > 0 && B <= 65535 && C > 0 && T > 0 &&
                     (P >= 1 && P <= 3), "gate_bwd_rows: bad arguments");
     // the gate's approximate functions only where the operand planes are bf16 anyway (see ew_v2.cuh)
+    static const int nw16_env = getenv("VNB_GATE_ROWS_NW16") ? atoi(getenv("VNB_GATE_ROWS_NW16")) : 1;
+    const bool nw16 = nw16_env && T >= 64;
     if (P == 1 && ew_v2_enabled() && fast_gate_enabled())
-        vnb::launch_k(gate_bwd_rows_kernel<true>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
-                      nullptr, nullptr, nullptr);
+        (nw16 ? vnb::launch_k(gate_bwd_rows_kernel<true, 16>, dim3(ceil_div(C, 32), B), 512, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
+                      nullptr, nullptr, nullptr)
+              : vnb::launch_k(gate_bwd_rows_kernel<true, 8>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
+                      nullptr, nullptr, nullptr));
     else
-        vnb::launch_k(gate_bwd_rows_kernel<false>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
-                      nullptr, nullptr, nullptr);
+        (nw16 ? vnb::launch_k(gate_bwd_rows_kernel<false, 16>, dim3(ceil_div(C, 32), B), 512, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
+                      nullptr, nullptr, nullptr)
+              : vnb::launch_k(gate_bwd_rows_kernel<false, 8>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
+                      nullptr, nullptr, nullptr));
     VNB_LAUNCH_CHECK("gate_bwd_rows");
     return VNB_OK;
 }
@@ -425,12 +442,18 @@ extern "C" int vnb_gate_bwd_rows_s(const float* dg, const float* a, const float*
     VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && R && S64 && S && B > 0 && B <= 65535 && C > 0 && (C & 31) == 0 &&
                     T > 0 && (P >= 1 && P <= 3), "gate_bwd_rows_s: bad arguments (32 must divide C)");
     unsigned* counter = reinterpret_cast<unsigned*>(S64 + (size_t)B * 4);
+    static const int nw16_env = getenv("VNB_GATE_ROWS_NW16") ? atoi(getenv("VNB_GATE_ROWS_NW16")) : 1;
+    const bool nw16 = nw16_env && T >= 64;
     if (P == 1 && ew_v2_enabled() && fast_gate_enabled())
-        vnb::launch_k(gate_bwd_rows_kernel<true>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
-                      S64, S, counter);
+        (nw16 ? vnb::launch_k(gate_bwd_rows_kernel<true, 16>, dim3(ceil_div(C, 32), B), 512, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
+                      S64, S, counter)
+              : vnb::launch_k(gate_bwd_rows_kernel<true, 8>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
+                      S64, S, counter));
     else
-        vnb::launch_k(gate_bwd_rows_kernel<false>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
-                      S64, S, counter);
+        (nw16 ? vnb::launch_k(gate_bwd_rows_kernel<false, 16>, dim3(ceil_div(C, 32), B), 512, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
+                      S64, S, counter)
+              : vnb::launch_k(gate_bwd_rows_kernel<false, 8>, dim3(ceil_div(C, 32), B), 256, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
+                      S64, S, counter));
     VNB_LAUNCH_CHECK("gate_bwd_rows_s");
     return VNB_OK;
 }
