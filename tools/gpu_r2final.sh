@@ -26,6 +26,7 @@ run wl_aishell3 100 python bench.py --workload aishell3 --steps 50 --warmup 10 -
 run wl_cdvae 100 python bench.py --workload cdvae --steps 50 --warmup 10 --no-cpu-baseline
 run wl_decode 100 python bench.py --workload decode --steps 50 --warmup 10 --no-cpu-baseline
 run gemm_p2 100 env VNB_BENCH_P=2 python tools/bench_gemm.py r2final
+run kernel_timeline 100 python tools/diag_kernel_timeline.py bf16x2
 if grep -q "bench_default exit 0" $S; then
 run ncu_launches 300 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches_final.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline
 fi
