@@ -156,7 +156,7 @@ int vnb_transpose(const float* in, int B, int R, int S, float* out, void* stream
 int vnb_make_planes(const float* x, int B, int C, int T, int P, float scale, int act,
                     void* out_id, void* out_act, float* csum, void* stream);
 /* channel-concat [xa (B,Ca,T); xb (B,Cb,T)] -> planes (P,B,T,(Ca+Cb)p); csum (optional, Ca+Cb floats, zeroed by
- * the caller): += per-channel sums */
+ * the caller): += per-channel sums.  xa may be null (= zeros). */
 int vnb_concat_planes(const float* xa, int Ca, const float* xb, int Cb, int B, int T, int P,
                       void* out, float* csum, void* stream);
 

@@ -233,7 +233,9 @@ def make_planes(x, P, scale=1.0, act=ACT_NONE, want_id=True, want_act=False, csu
     return (Planes.of(v, P) if want_id else None, Planes.of(_act(v, act), P) if want_act else None)
 
 
-def concat_planes(xa, xb, P, csum=None):
+def concat_planes(xa, xb, P, csum=None, Ca=None):
+    if xa is None:
+        xa = torch.zeros((xb.shape[0], Ca, xb.shape[2]), dtype=xb.dtype)
     cat = torch.cat([xa, xb], dim=1)
     if csum is not None:
         csum.add_(cat.detach().sum(dim=(0, 2)))

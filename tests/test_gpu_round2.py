@@ -522,3 +522,26 @@ def test_conv_with_activation_backward_in_the_epilogue(fp32_mode, P, B, Cin, Cou
             torch.cuda.synchronize()
             assert rel_err(got, want) < 1e-6, (backend, act, scale, r is not None)
     assert _C.call('debug_tc_timeouts') == 0
+
+
+@pytest.mark.parametrize('P', [1, 2, 3])
+@pytest.mark.parametrize('Ca,Cb', [(512, 128), (16, 12), (10, 6)])
+def test_concat_planes_with_sums_and_missing_first_operand(fp32_mode, P, Ca, Cb):
+    """vnb_concat_planes: the channel-sum path (register accumulation) against the restatement, and a null first operand
+    (a gradient that does not exist) against explicit zeros."""
+    from vae_npvc_b200 import prims as Pm
+    B, T = 16, 128
+    xa, xb = g(B, Ca, T, seed=1), g(B, Cb, T, seed=2)
+    cs = torch.zeros(Ca + Cb, device='cuda')
+    got = Pm.concat_planes(Pm.as_cl(xa.cuda()), Pm.as_cl(xb.cuda()), P, csum=cs)
+    rcs = torch.zeros(Ca + Cb)
+    want = R.concat_planes(xa, xb, P, csum=rcs)
+    torch.cuda.synchronize()
+    assert torch.equal(got.data.cpu().view(torch.int16), want.data.view(torch.int16))
+    assert rel_err(cs, rcs) < 1e-5
+    cs0, cs1 = torch.zeros(Ca + Cb, device='cuda'), torch.zeros(Ca + Cb, device='cuda')
+    a = Pm.concat_planes(None, Pm.as_cl(xb.cuda()), P, csum=cs0, Ca=Ca)
+    b = Pm.concat_planes(Pm.as_cl(torch.zeros(B, Ca, T).cuda()), Pm.as_cl(xb.cuda()), P, csum=cs1)
+    assert torch.equal(a.data.view(torch.int16), b.data.view(torch.int16)) and rel_err(cs0, cs1) < 1e-6
+    c = Pm.concat_planes(None, Pm.as_cl(xb.cuda()), P, Ca=Ca)            # without sums: the first-generation kernel
+    assert torch.equal(c.data.view(torch.int16), b.data.view(torch.int16))

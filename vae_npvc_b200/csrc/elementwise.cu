@@ -100,8 +100,13 @@ __global__ void concat_planes_kernel(const float* __restrict__ xa, int Ca, const
         const int64_t r = i / Cv;
         const int c = (int)(i - r * Cv) * VEC;
         float v[VEC];
-        if (c < Ca) ld_vec<VEC>(xa + r * Ca + c, v);
-        else ld_vec<VEC>(xb + r * Cb + (c - Ca), v);
+        if (c < Ca) {
+            if (xa) ld_vec<VEC>(xa + r * Ca + c, v);
+            else {
+#pragma unroll
+                for (int j = 0; j < VEC; j++) v[j] = 0.f;       // null first operand = zeros
+            }
+        } else ld_vec<VEC>(xb + r * Cb + (c - Ca), v);
         st_planes_vec<VEC>(out, r * Cp + c, plane, P, v);
         if (csum) {
 #pragma unroll
@@ -129,7 +134,7 @@ __global__ void __launch_bounds__(256) concat_planes_v2_kernel(const float* __re
     __syncthreads();
     const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
     const int c = (tid % Cv) * 4, r0 = tid / Cv, rstep = nthr / Cv;
-    const float* __restrict__ src = c < Ca ? xa + c : xb + (c - Ca);
+    const float* __restrict__ src = c < Ca ? (xa ? xa + c : nullptr) : xb + (c - Ca);      // xa null: zeros
     const int stride = c < Ca ? Ca : Cb;
     const int64_t plane = (int64_t)rows * Cp;
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
@@ -138,7 +143,7 @@ __global__ void __launch_bounds__(256) concat_planes_v2_kernel(const float* __re
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             const int ru = r + u * rstep;
-            v[u] = ru < rows ? __ldg(reinterpret_cast<const float4*>(src + (int64_t)ru * stride)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            v[u] = (ru < rows && src) ? __ldg(reinterpret_cast<const float4*>(src + (int64_t)ru * stride)) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
         for (int u = 0; u < 4; u++) {
@@ -394,7 +399,7 @@ extern "C" int vnb_make_planes(const float* x, int B, int C, int T, int P, float
 
 extern "C" int vnb_concat_planes(const float* xa, int Ca, const float* xb, int Cb, int B, int T, int P, void* out,
                                  float* csum, void* stream) {
-    VNB_REQUIRE(xa && xb && out && Ca > 0 && Cb > 0 && B > 0 && T > 0 && (P >= 1 && P <= 3), "concat_planes: bad arguments");
+    VNB_REQUIRE(xb && out && Ca > 0 && Cb > 0 && B > 0 && T > 0 && (P >= 1 && P <= 3), "concat_planes: bad arguments");
     VNB_REQUIRE(!csum || Ca + Cb <= 12000, "concat_planes: too many channels for the fused channel sums");
     const int64_t rows = (int64_t)B * T;
     const bool v4 = ((Ca | Cb) & 3) == 0;

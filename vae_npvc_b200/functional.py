@@ -394,13 +394,15 @@ class DecBlockFn(Function):
         cond, a, mean, rstd, gamma, beta, v_in, g_in, v_c, g_c, v_rs, g_rs, b_in, b_c, b_rs = ctx.saved_tensors
         P, dil, B, C, S, T, taps, has_cond, bcast = ctx.cfg
         dev = a.device
-        dxo = Pm.cl_zeros(B, C, T, dev) if dxo is None else Pm.as_cl(dxo)
+        # (the last block's x output is unused: its gradient does not exist and is never materialised as zeros)
+        no_dxo = dxo is None
+        dxo = None if no_dxo else (Pm.cl_zeros(B, C, T, dev) if dxo is None else Pm.as_cl(dxo))
         # dskip arrives in the physical (B, T, S) form of the skip accumulator
         dskip_phys = torch.zeros((B, T, S), device=dev) if dskip is None else dskip.contiguous()
         dskip = dskip_phys.transpose(1, 2)
         rs_slot = _slot(b_rs)                  # zeroed by the trainer's flat-gradient memset
         db_rs = rs_slot if rs_slot is not None else torch.zeros((C + S,), dtype=torch.float32, device=dev)
-        drpl = Pm.concat_planes(dxo, dskip, P, csum=db_rs)      # res/skip bias gradient rides along
+        drpl = Pm.concat_planes(dxo, dskip, P, csum=db_rs, Ca=C)      # res/skip bias gradient rides along
         if rs_slot is not None:
             db_rs = None
         dg = Pm.conv_fwd(drpl, ctx.wrs_wb, 1, 1, C)

@@ -211,11 +211,13 @@ def make_planes(x, P, scale=1.0, act=ACT_NONE, want_id=True, want_act=False, csu
     return pid, pact
 
 
-def concat_planes(xa, xb, P, csum=None):
-    """``csum``: optional ZEROED (Ca+Cb,) tensor that also receives the per-channel sums."""
-    B, Ca, T = xa.shape
-    Cb = xb.shape[1]
-    out = Planes.empty(P, B, Ca + Cb, T, xa.device)
+def concat_planes(xa, xb, P, csum=None, Ca=None):
+    """``csum``: optional ZEROED (Ca+Cb,) tensor that also receives the per-channel sums.  ``xa`` None with ``Ca``: the
+    first Ca channels are zeros (a gradient that does not exist) - no tensor of zeros is materialised."""
+    B, Cb, T = xb.shape
+    if xa is not None:
+        Ca = xa.shape[1]
+    out = Planes.empty(P, B, Ca + Cb, T, xb.device)
     _C.call('concat_planes', _r(xa), Ca, _r(xb), Cb, B, T, P, out.data, csum)
     return out
 
@@ -449,7 +451,8 @@ def linear_bwd_batch(dp, y, Ws, dWs, want_dy=True):
 def vq_prep_codebook(E, normalize, inplace_renorm=True):
     K, D = E.shape
     e_hat = torch.empty_like(E)
-    e_pl = torch.zeros((3, K, pitch(D)), dtype=torch.bfloat16, device=E.device)
+    # the pitch padding of the planes (D not a multiple of 8) must be finite: zero-fill only then
+    e_pl = (torch.zeros if pitch(D) != D else torch.empty)((3, K, pitch(D)), dtype=torch.bfloat16, device=E.device)
     e_sq = _f32((K,), E)
     _C.call('vq_prep_codebook', E, K, D, int(normalize), int(inplace_renorm), e_hat, e_pl, e_sq)
     return e_hat, e_pl, e_sq
@@ -485,8 +488,10 @@ def vq_fused(z, normalize, e_hat, e_pl, e_sq, want_q=True, want_stats=True):
     z_norm = _f32((B * T,), z) if normalize else None
     idx = torch.empty((B * T,), dtype=torch.int64, device=z.device)
     q = cl_empty(B, D, T, z.device) if want_q else None
-    sums = torch.zeros((2,), dtype=torch.float32, device=z.device) if want_stats else None
-    counts = torch.zeros((K,), dtype=torch.int32, device=z.device) if want_stats else None
+    sums = counts = None
+    if want_stats:
+        buf = torch.zeros((K + 2,), dtype=torch.int32, device=z.device)       # one zero-fill for both accumulators
+        sums, counts = buf[:2].view(torch.float32), buf[2:]
     r = _C.call('vq_fused', _r(zc), B, D, T, int(normalize), e_hat, e_pl, e_sq, K, _r(zn) if normalize else None, z_norm,
                 idx, _r(q), sums, counts)
     if r == 1:
