@@ -81,7 +81,7 @@ int vnb_get_backend(void);
  *                     (4.2k vs 3.9k cycles for a 128 x 128 fp32 tile, profiles/r02f_fast_epilogue.txt) - the epilogue is
  *                     bound by writing 8 MB of fp32 output into L2 from 128 CTAs at once, not by how the threads do it */
 #define VNB_OPT_FAST_EPI 9
-/*   VNB_OPT_VQ_FUSED  fused VQ lookup (frame preparation + one-product tensor-core shortlist + exact fp32 re-rank +
+/*   VNB_OPT_VQ_FUSED  fused VQ lookup (frame preparation + three-plane-product tensor-core shortlist with a rigorous error window + exact fp32 re-rank +
  *                     gather + loss sums + histogram in one kernel, csrc/tc_vq_fused.cuh; default 1) */
 #define VNB_OPT_VQ_FUSED 10
 /*   VNB_OPT_WG_FUSE   tap-fused weight-gradient tiles for k = 3 convs (one N-192 accumulator per 64 columns x 3 taps,
