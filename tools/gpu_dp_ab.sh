@@ -14,9 +14,8 @@ except Exception as e:
     print('$tag failed', e); print(open('gpurun_out/dp_$tag.err').read()[-800:])
 PY
 }
-run b_6_6 A=1
-run b_6_10 VNB_BUCKETS=6,10
-run b_10_10 VNB_BUCKETS=10,10
-run b_8_9 VNB_BUCKETS=8,9
-run b_6_6_b A=1
-run b_10_10_b VNB_BUCKETS=10,10
+run default A=1
+run gate_nw8 VNB_GATE_ROWS_NW16=0
+run gn_nw8 VNB_GN_ROWS_NW32=0
+run both_nw8 VNB_GATE_ROWS_NW16=0 VNB_GN_ROWS_NW32=0
+run concat_2 VNB_CONCAT_CTAS_PER_SM=2

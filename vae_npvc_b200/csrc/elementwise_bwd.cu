@@ -61,8 +61,8 @@ __device__ __forceinline__ void publish_group_sums(float t, float gm, bool valid
 }
 
 // R[b,c] = { sum_t dn, sum_t dn*xhat, sum_t xhat }.  grid (ceil(C/32), B), block 32 x NW: a warp reads
-// 32 consecutive channels of one frame, the NW warps stride over frames, shared-memory reduce.  NW = 32 for T >= 128:
-// at 16 x 128 frames the kernel is latency-bound (four dependent rounds of loads with 8 warps, one with 32).
+// 32 consecutive channels of one frame, the NW warps stride over frames, shared-memory reduce.  NW = 32 (opt-in, see
+// gn_rows_nw32()): at 16 x 128 frames the kernel is latency-bound (four dependent rounds of loads with 8 warps, one with 32).
 template <bool GATE, int NW>
 __global__ void __launch_bounds__(32 * NW) bwd_rows_kernel(const float* __restrict__ dn, const float* __restrict__ h,
                                                        const float* __restrict__ mean, const float* __restrict__ rstd,
@@ -321,6 +321,13 @@ __global__ void __launch_bounds__(256) channel_sum_kernel(const float* __restric
     }
 }
 
+// Wide blocks for the row-sum kernels (32 / 16 warps: VNB_GN_ROWS_NW32=1, VNB_GATE_ROWS_NW16=1) are 1.7 / 1.2 us faster per
+// launch on one GPU (9.6 -> 7.9, 10.8 -> 9.6 us) but cost the 2-GPU step 0.1 ms (3.19 -> 3.29 ms): blocks that fill an SM's
+// thread slots keep the overlapped all-reduce's CTAs off the SMs.  Default: 8 warps.
+static inline bool gn_rows_nw32() {
+    static const int v = getenv("VNB_GN_ROWS_NW32") ? atoi(getenv("VNB_GN_ROWS_NW32")) : 0;
+    return v != 0;
+}
 }  // namespace vnb
 using namespace vnb;
 
@@ -328,7 +335,7 @@ extern "C" int vnb_gn_bwd_rows(const float* dn, const float* h, const float* mea
                                int T, int groups, float* R, void* stream) {
     VNB_REQUIRE(dn && h && mean && rstd && R && B > 0 && B <= 65535 && C > 0 && T > 0 && groups > 0 && C % groups == 0,
                 "gn_bwd_rows: bad arguments");
-    if (T >= 128)
+    if (T >= 128 && gn_rows_nw32())
         vnb::launch_k(bwd_rows_kernel<false, 32>, dim3(ceil_div(C, 32), B), 1024, 0, (cudaStream_t)stream, dn, h, mean, rstd, nullptr, nullptr,
                                                                                        C, T, groups, R, nullptr, nullptr, nullptr);
     else
@@ -343,7 +350,7 @@ extern "C" int vnb_gn_bwd_rows_s(const float* dn, const float* h, const float* m
     VNB_REQUIRE(dn && h && mean && rstd && gamma && R && S64 && S && B > 0 && B <= 65535 && C > 0 && T > 0 && groups > 0 &&
                     C % groups == 0 && ((C / groups) & 31) == 0, "gn_bwd_rows_s: bad arguments (32 must divide C / groups)");
     // S64: B * groups * 2 ZEROED doubles followed by one zeroed 8-byte ticket slot
-    if (T >= 128)
+    if (T >= 128 && gn_rows_nw32())
         vnb::launch_k(bwd_rows_kernel<false, 32>, dim3(ceil_div(C, 32), B), 1024, 0, (cudaStream_t)stream, dn, h, mean, rstd, gamma, nullptr,
                   C, T, groups, R, S64, S, reinterpret_cast<unsigned*>(S64 + (size_t)B * groups * 2));
     else
@@ -356,9 +363,8 @@ extern "C" int vnb_gn_bwd_rows_s(const float* dn, const float* h, const float* m
 namespace vnb {
 // Gate variant of bwd_rows: a thread owns channel c < C and accumulates the three row sums of BOTH halves
 // (tanh half c, sigmoid half C + c) from one tanh / exp pair per element, four frames in flight.
-// grid (ceil(C/32), B), block 32 x NW.  NW = 16 for T >= 64 (10.8 -> 9.6 us at 16 x 128 frames; VNB_GATE_ROWS_NW16=0: 8 warps);
-// with 32 warps (64 registers per thread around libm tanh / exp) it measured SLOWER (12.1 us), unlike the plain GroupNorm
-// row sums (9.6 -> 7.9 us with 32 warps).
+// grid (ceil(C/32), B), block 32 x NW (8 by default; 16 with VNB_GATE_ROWS_NW16=1: 10.8 -> 9.6 us at 16 x 128 frames, but see
+// gn_rows_nw32() below for why it is off; 32 warps - 64 registers per thread around libm tanh / exp - measured slower).
 template <bool FAST, int NW>
 __global__ void __launch_bounds__(32 * NW) gate_bwd_rows_kernel(const float* __restrict__ dg, const float* __restrict__ a,
                                                             const float* __restrict__ mean, const float* __restrict__ rstd,
@@ -420,7 +426,7 @@ extern "C" int vnb_gate_bwd_rows_p(const float* dg, const float* a, const float*
     VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && R && B > 0 && B <= 65535 && C > 0 && T > 0 &&
                     (P >= 1 && P <= 3), "gate_bwd_rows: bad arguments");
     // the gate's approximate functions only where the operand planes are bf16 anyway (see ew_v2.cuh)
-    static const int nw16_env = getenv("VNB_GATE_ROWS_NW16") ? atoi(getenv("VNB_GATE_ROWS_NW16")) : 1;
+    static const int nw16_env = getenv("VNB_GATE_ROWS_NW16") ? atoi(getenv("VNB_GATE_ROWS_NW16")) : 0;
     const bool nw16 = nw16_env && T >= 64;
     if (P == 1 && ew_v2_enabled() && fast_gate_enabled())
         (nw16 ? vnb::launch_k(gate_bwd_rows_kernel<true, 16>, dim3(ceil_div(C, 32), B), 512, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
@@ -442,7 +448,7 @@ extern "C" int vnb_gate_bwd_rows_s(const float* dg, const float* a, const float*
     VNB_REQUIRE(dg && a && mean && rstd && gamma && beta && R && S64 && S && B > 0 && B <= 65535 && C > 0 && (C & 31) == 0 &&
                     T > 0 && (P >= 1 && P <= 3), "gate_bwd_rows_s: bad arguments (32 must divide C)");
     unsigned* counter = reinterpret_cast<unsigned*>(S64 + (size_t)B * 4);
-    static const int nw16_env = getenv("VNB_GATE_ROWS_NW16") ? atoi(getenv("VNB_GATE_ROWS_NW16")) : 1;
+    static const int nw16_env = getenv("VNB_GATE_ROWS_NW16") ? atoi(getenv("VNB_GATE_ROWS_NW16")) : 0;
     const bool nw16 = nw16_env && T >= 64;
     if (P == 1 && ew_v2_enabled() && fast_gate_enabled())
         (nw16 ? vnb::launch_k(gate_bwd_rows_kernel<true, 16>, dim3(ceil_div(C, 32), B), 512, 0, (cudaStream_t)stream, dg, a, mean, rstd, gamma, beta, C, T, R,
